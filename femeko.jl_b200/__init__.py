@@ -1,0 +1,6 @@
+"""femeko.jl_b200 -- B200-native hot path of Femeko.jl (P1 tet assembly, Jacobi-PCG, field recovery).
+
+Host-side mirror of the reference interface (src/FEM3D.jl, src/mesh.jl, src/magneticProperties.jl)
+above the C-ABI library ``csrc/libfemeko_cuda.so``.  Imported as ``femeko_jl_b200``.
+"""
+from .mesh import MESH, kuhn_cube, delaunay_ball, elementVolume, areaTriangle, normalSurface, mu0  # noqa: F401

@@ -1,0 +1,1042 @@
+// C ABI of libfemeko_cuda.so (see include/femeko_cuda.h).  Host-side orchestration only: every
+// floating-point operation of the hot path runs in the kernels of kernels.cuh on the GPU; there is
+// no CPU fallback (fk_create fails when no CUDA device is present).
+#include <algorithm>
+#include <cfloat>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <memory>
+
+#include "comm.hpp"
+#include "handle.hpp"
+
+namespace fk {
+
+static thread_local std::string g_err;
+void set_error(const std::string& s) { g_err = s; }
+
+template <class F>
+static int guard(F&& f) {
+  try {
+    return f();
+  } catch (const std::exception& e) {
+    set_error(e.what());
+    return 1;
+  } catch (...) {
+    set_error("fk: unknown error");
+    return 1;
+  }
+}
+
+static void need(bool ok, const char* msg) {
+  if (!ok) throw std::runtime_error(msg);
+}
+static void check_slot(int s) { need(s >= 0 && s < FK_NUM_SLOTS, "fk: matrix slot out of range"); }
+
+struct DeviceGuard {
+  int prev = -1;
+  explicit DeviceGuard(int dev) {
+    FK_CUDA(cudaGetDevice(&prev));
+    if (prev != dev) FK_CUDA(cudaSetDevice(dev));
+    else prev = -1;
+  }
+  ~DeviceGuard() {
+    if (prev >= 0) cudaSetDevice(prev);
+  }
+};
+
+static inline int cdiv(long long a, int b) { return (int)((a + b - 1) / b); }
+
+static double* slot_vals(fk_handle h, int slot) {
+  check_slot(slot);
+  h->vals[slot].ensure((size_t)h->nnz);
+  return h->vals[slot].ptr;
+}
+
+// ------------------------------------------------------------------------------------------------
+// assembly launcher
+// ------------------------------------------------------------------------------------------------
+static AsmArgs base_args(fk_handle h, double* vals) {
+  AsmArgs a{};
+  a.p4 = h->p4.ptr;
+  a.t4 = h->t4.ptr;
+  a.VE = h->user_ve ? h->VE.ptr : nullptr;
+  a.tile_elem_ptr = h->tile_elem_ptr.ptr;
+  a.tile_elems = h->tile_elems.ptr;
+  a.tile_nnz_ptr = h->tile_nnz_ptr.ptr;
+  a.tile_gidx = h->tile_gidx.ptr;
+  a.tile_coff = h->tile_coff.ptr;
+  a.tile_ent_ptr = h->tile_ent_ptr.ptr;
+  a.tile_ents = h->tile_ents.ptr;
+  a.vals = vals;
+  a.e_pad = h->e_pad;
+  a.spl = h->spl;
+  return a;
+}
+
+template <int MODE>
+static void launch_assemble(fk_handle h, const AsmArgs& a) {
+  if (h->sym.ntiles == 0) return;
+  assemble_kernel<MODE><<<h->sym.ntiles, kAsmThreads, h->asm_smem, h->stream>>>(a);
+  FK_CUDA(cudaGetLastError());
+  h->launches++;
+}
+
+static void assemble_stiffness_dev(fk_handle h, int slot, const double* f_dev) {
+  AsmArgs a = base_args(h, slot_vals(h, slot));
+  a.coef = f_dev;
+  launch_assemble<ASM_STIFF>(h, a);
+}
+static void assemble_mass_dev(fk_handle h, int slot, const double* rho_dev) {
+  AsmArgs a = base_args(h, slot_vals(h, slot));
+  a.coef = rho_dev;
+  launch_assemble<ASM_MASS>(h, a);
+}
+static void assemble_tangential_dev(fk_handle h, int slot, const double* H_dev, const double* dmu_dev) {
+  AsmArgs a = base_args(h, slot_vals(h, slot));
+  a.coef = dmu_dev;
+  a.Hvec = H_dev;
+  launch_assemble<ASM_TANGENT>(h, a);
+}
+
+static void ensure_state(fk_handle h) {
+  if (h->mu.ptr) return;
+  h->mu.ensure((size_t)h->nt);
+  h->dmu.ensure((size_t)h->nt);
+  h->Hn.ensure((size_t)h->nt);
+  h->Hfield.ensure((size_t)3 * h->nt);
+  h->matid.ensure((size_t)h->nt);
+  h->tile_max.ensure((size_t)std::max(1, h->sym.ntiles));
+  h->errflag.ensure(1);
+  h->scal.ensure(8);
+  const int g = std::min(cdiv(h->nt, 256), 65535);
+  fill_kernel<<<g, 256, 0, h->stream>>>(h->mu.ptr, 4e-7 * 3.14159265358979323846, h->nt);  // mu0 (magneticField.jl:38)
+  FK_CUDA(cudaMemsetAsync(h->dmu.ptr, 0, sizeof(double) * (size_t)h->nt, h->stream));
+  FK_CUDA(cudaMemsetAsync(h->Hn.ptr, 0, sizeof(double) * (size_t)h->nt, h->stream));
+  FK_CUDA(cudaMemsetAsync(h->Hfield.ptr, 0, sizeof(double) * (size_t)3 * h->nt, h->stream));
+  FK_CUDA(cudaMemsetAsync(h->matid.ptr, 0, (size_t)h->nt, h->stream));
+  FK_CUDA(cudaMemsetAsync(h->errflag.ptr, 0, sizeof(int), h->stream));
+  h->launches++;
+}
+
+// ------------------------------------------------------------------------------------------------
+// SpMV / PCG launchers
+// ------------------------------------------------------------------------------------------------
+static void launch_spmv(fk_handle h, cudaStream_t s, const double* vals, const double* x, double* y, bool dot,
+                        const PcgCtl* ctl, int j) {
+  const int nblk = (int)h->sym.blk_row.size() - 1;
+  if (nblk <= 0) return;
+  const size_t smem = (size_t)h->spmv_cap * sizeof(double);
+  if (dot)
+    spmv_kernel<true><<<h->grid_spmv, kSpmvThreads, smem, s>>>(h->rowptr.ptr, h->colind.ptr, vals, x, y, h->blk_row.ptr, nblk,
+                                                               h->spmv_cap, h->part.ptr, ctl, j);
+  else
+    spmv_kernel<false><<<h->grid_spmv, kSpmvThreads, smem, s>>>(h->rowptr.ptr, h->colind.ptr, vals, x, y, h->blk_row.ptr, nblk,
+                                                                h->spmv_cap, nullptr, ctl, j);
+  FK_CUDA(cudaGetLastError());
+}
+
+static void ensure_pcg(fk_handle h) {
+  if (h->x.ptr) return;
+  const size_t nvec = (size_t)h->nv;  // vectors carry halo rows too (SpMV input)
+  h->x.ensure(nvec);
+  h->r.ensure(nvec);
+  h->p.ensure(nvec);
+  h->Ap.ensure(nvec);
+  h->dinv.ensure(nvec);
+  h->bvec.ensure(nvec);
+  h->part.ensure((size_t)4 * std::max(h->grid_spmv, h->grid_vec) + 16);
+  h->ctl.ensure(1);
+  h->scal.ensure(8);
+  FK_CUDA(cudaMemsetAsync(h->p.ptr, 0, nvec * sizeof(double), h->stream));
+  FK_CUDA(cudaMemsetAsync(h->x.ptr, 0, nvec * sizeof(double), h->stream));
+  if (!h->ctl_host) FK_CUDA(cudaMallocHost((void**)&h->ctl_host, sizeof(PcgCtl)));
+}
+
+// one PCG iteration (index j inside a chunk) issued into stream s; single-GPU form
+static void issue_iteration(fk_handle h, cudaStream_t s, const double* vals, int j) {
+  const int n = h->n_rows;
+  PcgCtl* ctl = h->ctl.ptr;
+  double* part = h->part.ptr;
+  const int gs = h->grid_spmv, gv = h->grid_vec;
+  launch_spmv(h, s, vals, h->p.ptr, h->Ap.ptr, true, ctl, j);
+  pcg_update_kernel<<<gv, kVecThreads, 0, s>>>(h->x.ptr, h->r.ptr, h->p.ptr, h->Ap.ptr, h->dinv.ptr, n, part, gs,
+                                               part + gs, ctl, j);
+  pcg_direction_kernel<<<gv, kVecThreads, 0, s>>>(h->p.ptr, h->r.ptr, h->dinv.ptr, n, part + gs, gv, gv, ctl, j);
+  FK_CUDA(cudaGetLastError());
+}
+
+static void build_graph(fk_handle h, int slot, int chunk) {
+  if (h->graph[slot] && h->graph_chunk[slot] == chunk) return;
+  if (h->graph[slot]) {
+    cudaGraphExecDestroy(h->graph[slot]);
+    h->graph[slot] = nullptr;
+  }
+  if (!h->cap_stream) FK_CUDA(cudaStreamCreateWithFlags(&h->cap_stream, cudaStreamNonBlocking));
+  cudaGraph_t g = nullptr;
+  FK_CUDA(cudaStreamBeginCapture(h->cap_stream, cudaStreamCaptureModeThreadLocal));
+  try {
+    for (int j = 0; j < chunk; j++) issue_iteration(h, h->cap_stream, h->vals[slot].ptr, j);
+    pcg_advance_kernel<<<1, 1, 0, h->cap_stream>>>(h->ctl.ptr, chunk);
+  } catch (...) {
+    cudaStreamEndCapture(h->cap_stream, &g);
+    if (g) cudaGraphDestroy(g);
+    throw;
+  }
+  FK_CUDA(cudaStreamEndCapture(h->cap_stream, &g));
+  cudaError_t e = cudaGraphInstantiate(&h->graph[slot], g, 0);
+  cudaGraphDestroy(g);
+  FK_CUDA(e);
+  h->graph_chunk[slot] = chunk;
+}
+
+static void pcg_dev(fk_handle h, int slot, const double* b_dev, double* x_dev, const fk_pcg_opts* o, int* iters_out,
+                    double* relres_out) {
+  check_slot(slot);
+  need(h->vals[slot].ptr != nullptr, "fk_pcg: matrix slot has not been assembled");
+  ensure_pcg(h);
+  const int n = h->n_rows;
+  fk_pcg_opts opt{};
+  if (o) opt = *o;
+  // tol_disable: tol = 0 -> threshold = DBL_MIN, never undercut by a non-zero residual
+  const double tol = opt.tol_disable ? 0.0 : (opt.tol > 0 ? opt.tol : DBL_EPSILON);
+  const int max_iter = opt.max_iter > 0 ? opt.max_iter : 2 * n;
+  int chunk = opt.check_every > 0 ? opt.check_every : 32;
+  chunk = std::min(chunk, std::max(2, max_iter));
+  if (chunk & 1) chunk++;  // scalar ping-pong parity must line up across chunks
+  cudaStream_t s = h->stream;
+  const int gv = h->grid_vec;
+
+  jacobi_kernel<<<cdiv(n, 256), 256, 0, s>>>(h->vals[slot].ptr, h->diag.ptr, n, opt.no_precond, h->dinv.ptr);
+  const double* Ax0 = nullptr;
+  if (opt.warm_start) {
+    FK_CUDA(cudaMemcpyAsync(h->x.ptr, x_dev, sizeof(double) * (size_t)n, cudaMemcpyDeviceToDevice, s));
+    if (h->comm) comm_halo_exchange(h, s, h->x.ptr);
+    launch_spmv(h, s, h->vals[slot].ptr, h->x.ptr, h->Ap.ptr, false, nullptr, 0);
+    Ax0 = h->Ap.ptr;
+    h->launches++;
+  } else {
+    FK_CUDA(cudaMemsetAsync(h->x.ptr, 0, sizeof(double) * (size_t)n, s));
+  }
+  pcg_init_kernel<<<gv, kVecThreads, 0, s>>>(b_dev, Ax0, h->dinv.ptr, n, h->r.ptr, h->p.ptr, h->part.ptr);
+  if (h->comm) {
+    fold_partials_kernel<<<1, 256, 0, s>>>(h->part.ptr, gv, gv, 3, h->scal.ptr);
+    comm_allreduce_sum(h, s, h->scal.ptr, 3);
+    pcg_init_fin_kernel<<<1, 256, 0, s>>>(h->scal.ptr, 1, 1, tol, max_iter, h->ctl.ptr);
+    h->launches++;
+  } else {
+    pcg_init_fin_kernel<<<1, 256, 0, s>>>(h->part.ptr, gv, gv, tol, max_iter, h->ctl.ptr);
+  }
+  FK_CUDA(cudaGetLastError());
+  h->launches += 3;
+
+  if (!h->comm) build_graph(h, slot, chunk);
+  int launched = 0;
+  while (true) {
+    if (h->comm) {
+      for (int j = 0; j < chunk; j++) comm_issue_iteration(h, s, h->vals[slot].ptr, j);
+      pcg_advance_kernel<<<1, 1, 0, s>>>(h->ctl.ptr, chunk);
+      h->launches += (long long)chunk * 6 + 1;
+    } else {
+      FK_CUDA(cudaGraphLaunch(h->graph[slot], s));
+      h->launches += (long long)chunk * 3 + 1;
+    }
+    launched += chunk;
+    FK_CUDA(cudaMemcpyAsync(h->ctl_host, h->ctl.ptr, sizeof(PcgCtl), cudaMemcpyDeviceToHost, s));
+    FK_CUDA(cudaStreamSynchronize(s));
+    if (h->ctl_host->done || launched >= max_iter) break;
+  }
+  const PcgCtl& c = *h->ctl_host;
+  const int iters = c.done ? c.iters : max_iter;
+  if (c.rhs2 == 0.0) {  // x = 0 (ConjugateGradient.h:43-49)
+    FK_CUDA(cudaMemsetAsync(x_dev, 0, sizeof(double) * (size_t)n, s));
+  } else {
+    FK_CUDA(cudaMemcpyAsync(x_dev, h->x.ptr, sizeof(double) * (size_t)n, cudaMemcpyDeviceToDevice, s));
+  }
+  if (iters_out) *iters_out = iters;
+  if (relres_out) *relres_out = c.rhs2 > 0.0 ? std::sqrt(c.r2 / c.rhs2) : 0.0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// host spline helpers (FITPACK curfit(k=3,s=0) knots + collocation solve; fpbspl evaluation)
+// ------------------------------------------------------------------------------------------------
+static int find_interval(const double* t, int n, int k, double x) {
+  int lo = k, hi = n - k - 2;
+  while (lo < hi) {
+    int mid = (lo + hi + 1) >> 1;
+    if (t[mid] <= x) lo = mid; else hi = mid - 1;
+  }
+  return lo;
+}
+static void bspline_basis(const double* t, int k, int l, double x, double* h) {
+  double hh[6];
+  h[0] = 1.0;
+  for (int j = 1; j <= k; j++) {
+    for (int i = 0; i < j; i++) hh[i] = h[i];
+    h[0] = 0.0;
+    for (int i = 0; i < j; i++) {
+      const double tli = t[l + i + 1], tlj = t[l + i + 1 - j];
+      if (tli == tlj) { h[i + 1] = 0.0; continue; }
+      const double f = hh[i] / (tli - tlj);
+      h[i] = h[i] + f * (tli - x);
+      h[i + 1] = f * (x - tlj);
+    }
+  }
+}
+static int spline_eval_host(const double* t, const double* c, int n, int k, int bc, double x, double* out) {
+  const double tb = t[k], te = t[n - k - 1];
+  if (x < tb || x > te || x != x) {
+    if (bc == FK_BC_ZERO) { *out = 0.0; return 0; }
+    if (bc == FK_BC_ERROR || x != x) { *out = NAN; return 2; }
+    if (bc == FK_BC_NEAREST) x = (x < tb) ? tb : te;
+  }
+  const int l = find_interval(t, n, k, x);
+  double h[6];
+  bspline_basis(t, k, l, x, h);
+  double sp = 0.0;
+  for (int j = 0; j <= k; j++) sp += c[l - k + j] * h[j];
+  *out = sp;
+  return 0;
+}
+
+}  // namespace fk
+
+using namespace fk;
+
+// =================================================================================================
+struct fk_symbolic_s { fk::Symbolic S; };
+
+static SymbolicOpts to_symbolic_opts(const fk_create_opts& o) {
+  SymbolicOpts so;
+  if (o.tile_max_elems > 0) so.tile_max_elems = o.tile_max_elems;
+  if (o.tile_max_rows > 0) so.tile_max_rows = o.tile_max_rows;
+  so.natural_order = o.natural_order != 0;
+  if (o.spmv_block_nnz > 0) so.spmv_block_nnz = o.spmv_block_nnz;
+  if (o.n_owned > 0) so.n_owned = o.n_owned;
+  return so;
+}
+
+template <class T, class U>
+static void copy_vec(const std::vector<T>& v, U* dst) {
+  static_assert(sizeof(T) == sizeof(U), "size mismatch");
+  if (dst && !v.empty()) std::memcpy(dst, v.data(), sizeof(T) * v.size());
+}
+
+extern "C" {
+
+const char* fk_last_error(void) { return fk::g_err.c_str(); }
+int fk_version(void) { return 100; }
+
+int fk_create(const double* p, const int* t, int nv, int nt, const double* VE, const fk_create_opts* opts, fk_handle* out) {
+  return guard([&]() {
+    need(out != nullptr, "fk_create: out is NULL");
+    *out = nullptr;
+    need(p && t, "fk_create: p and t must not be NULL");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+      throw std::runtime_error("fk_create: no CUDA device available (this library has no CPU path)");
+    fk_create_opts o{};
+    if (opts) o = *opts;
+    int dev = o.device;
+    if (opts == nullptr || dev < 0) FK_CUDA(cudaGetDevice(&dev));
+    need(dev < ndev, "fk_create: device ordinal out of range");
+    DeviceGuard dg(dev);
+    std::unique_ptr<fk_handle_s> h(new fk_handle_s());
+    h->device = dev;
+    cudaDeviceProp prop;
+    FK_CUDA(cudaGetDeviceProperties(&prop, dev));
+    h->num_sms = prop.multiProcessorCount;
+    h->nv = nv;
+    h->nt = nt;
+
+    SymbolicOpts so = to_symbolic_opts(o);
+    build_symbolic(p, t, nv, nt, so, h->sym);
+    const Symbolic& S = h->sym;
+    h->n_rows = S.n_rows;
+    h->nnz = S.nnz;
+
+    cudaStream_t s = h->stream;
+    // mesh: nodes padded to 32 B, connectivity as int4
+    h->st_a.upload(p, (size_t)3 * nv, s);
+    h->p4.ensure((size_t)nv);
+    pad_nodes_kernel<<<cdiv(nv, 256), 256, 0, s>>>(h->st_a.ptr, nv, h->p4.ptr);
+    h->t4.ensure((size_t)nt);
+    FK_CUDA(cudaMemcpyAsync(h->t4.ptr, t, sizeof(int) * 4 * (size_t)nt, cudaMemcpyHostToDevice, s));
+    h->VE.ensure((size_t)nt);
+    if (VE) {
+      h->user_ve = true;
+      FK_CUDA(cudaMemcpyAsync(h->VE.ptr, VE, sizeof(double) * (size_t)nt, cudaMemcpyHostToDevice, s));
+    } else {
+      volumes_kernel<<<cdiv(nt, 256), 256, 0, s>>>(h->p4.ptr, h->t4.ptr, nt, h->VE.ptr);
+    }
+    h->rowptr.upload(S.rowptr, s);
+    h->colind.upload(S.colind, s);
+    h->diag.upload(S.diag, s);
+    h->blk_row.upload(S.blk_row, s);
+    h->tile_gidx.upload(S.tile_gidx, s);
+    h->tile_elems.upload(S.tile_elems, s);
+    h->tile_coff.upload(S.tile_coff, s);
+    h->tile_ents.upload(S.tile_ents, s);
+    {
+      std::vector<long long> a(S.tile_elem_ptr.begin(), S.tile_elem_ptr.end()), b(S.tile_nnz_ptr.begin(), S.tile_nnz_ptr.end()),
+          c(S.tile_ent_ptr.begin(), S.tile_ent_ptr.end());
+      h->tile_elem_ptr.upload(a, s);
+      h->tile_nnz_ptr.upload(b, s);
+      h->tile_ent_ptr.upload(c, s);
+      FK_CUDA(cudaStreamSynchronize(s));
+    }
+    h->e_pad = (S.max_tile_elems + 31) & ~31;
+    h->asm_smem = (size_t)10 * h->e_pad * sizeof(double);
+    need(h->asm_smem <= (size_t)prop.sharedMemPerBlockOptin, "fk_create: assembly tile does not fit in shared memory");
+    FK_CUDA(cudaFuncSetAttribute(assemble_kernel<ASM_STIFF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->asm_smem));
+    FK_CUDA(cudaFuncSetAttribute(assemble_kernel<ASM_MASS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->asm_smem));
+    FK_CUDA(cudaFuncSetAttribute(assemble_kernel<ASM_TANGENT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->asm_smem));
+    FK_CUDA(cudaFuncSetAttribute(assemble_kernel<ASM_PICARD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->asm_smem));
+    FK_CUDA(cudaFuncSetAttribute(assemble_kernel<ASM_LAGRANGE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->asm_smem));
+
+    // launch geometry of the persistent SpMV / vector kernels: full residency, fixed for determinism
+    h->spmv_cap = std::max(32, std::min(S.max_blk_nnz, std::max(so.spmv_block_nnz, 2048)));
+    const size_t smem = (size_t)h->spmv_cap * sizeof(double);
+    FK_CUDA(cudaFuncSetAttribute(spmv_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    FK_CUDA(cudaFuncSetAttribute(spmv_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int occ = 1;
+    FK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, spmv_kernel<true>, kSpmvThreads, smem));
+    occ = std::max(1, occ);
+    const int nblk = (int)S.blk_row.size() - 1;
+    h->grid_spmv = std::max(1, std::min(nblk, h->num_sms * occ));
+    h->grid_vec = std::max(1, std::min(cdiv(std::max(1, h->n_rows), kVecThreads), h->num_sms * 8));
+    FK_CUDA(cudaStreamSynchronize(s));
+    h->st_a.release();
+    h->launches += 2;
+    *out = h.release();
+    return 0;
+  });
+}
+
+int fk_destroy(fk_handle h) {
+  return guard([&]() {
+    if (!h) return 0;
+    DeviceGuard dg(h->device);
+    cudaDeviceSynchronize();
+    for (int s = 0; s < FK_NUM_SLOTS; s++)
+      if (h->graph[s]) cudaGraphExecDestroy(h->graph[s]);
+    if (h->cap_stream) cudaStreamDestroy(h->cap_stream);
+    if (h->ctl_host) cudaFreeHost(h->ctl_host);
+    comm_destroy(h);
+    delete h;
+    return 0;
+  });
+}
+
+int fk_set_stream(fk_handle h, void* stream) {
+  return guard([&]() {
+    need(h, "fk: NULL handle");
+    h->stream = (cudaStream_t)stream;
+    return 0;
+  });
+}
+
+int fk_synchronize(fk_handle h) {
+  return guard([&]() {
+    need(h, "fk: NULL handle");
+    DeviceGuard dg(h->device);
+    FK_CUDA(cudaStreamSynchronize(h->stream));
+    return 0;
+  });
+}
+
+int fk_launch_count(fk_handle h, long long* n) {
+  return guard([&]() {
+    need(h && n, "fk: NULL argument");
+    *n = h->launches;
+    return 0;
+  });
+}
+
+int fk_sizes(fk_handle h, int* nv, int* nt, long long* nnz, int* ntiles) {
+  return guard([&]() {
+    need(h, "fk: NULL handle");
+    if (nv) *nv = h->nv;
+    if (nt) *nt = h->nt;
+    if (nnz) *nnz = h->nnz;
+    if (ntiles) *ntiles = h->sym.ntiles;
+    return 0;
+  });
+}
+
+int fk_csr_pattern(fk_handle h, int* rowptr, int* colind) {
+  return guard([&]() {
+    need(h, "fk: NULL handle");
+    if (rowptr) std::memcpy(rowptr, h->sym.rowptr.data(), sizeof(int) * ((size_t)h->nv + 1));
+    if (colind) std::memcpy(colind, h->sym.colind.data(), sizeof(int) * (size_t)h->nnz);
+    return 0;
+  });
+}
+
+int fk_elem2nnz(fk_handle h, int* map) {
+  return guard([&]() {
+    need(h && map, "fk: NULL argument");
+    std::memcpy(map, h->sym.e2nnz.data(), sizeof(int) * 16 * (size_t)h->nt);
+    return 0;
+  });
+}
+
+int fk_tile_stats(fk_handle h, long long* staged_elems, int* max_elems, int* max_nnz, int* max_ents) {
+  return guard([&]() {
+    need(h, "fk: NULL handle");
+    if (staged_elems) *staged_elems = (long long)h->sym.tile_elems.size();
+    if (max_elems) *max_elems = h->sym.max_tile_elems;
+    if (max_nnz) *max_nnz = h->sym.max_tile_nnz;
+    if (max_ents) *max_ents = h->sym.max_tile_ents;
+    return 0;
+  });
+}
+
+int fk_volumes(fk_handle h, double* VE) {
+  return guard([&]() {
+    need(h && VE, "fk: NULL argument");
+    DeviceGuard dg(h->device);
+    FK_CUDA(cudaMemcpyAsync(VE, h->VE.ptr, sizeof(double) * (size_t)h->nt, cudaMemcpyDeviceToHost, h->stream));
+    FK_CUDA(cudaStreamSynchronize(h->stream));
+    return 0;
+  });
+}
+
+int fk_device_ptr(fk_handle h, int which, void** ptr) {
+  return guard([&]() {
+    need(h && ptr, "fk: NULL argument");
+    DeviceGuard dg(h->device);
+    if (which >= 16 && which < 16 + FK_NUM_SLOTS) { *ptr = slot_vals(h, which - 16); return 0; }
+    if (which >= 3 && which <= 6) ensure_state(h);
+    switch (which) {
+      case 0: *ptr = h->rowptr.ptr; break;
+      case 1: *ptr = h->colind.ptr; break;
+      case 2: *ptr = h->VE.ptr; break;
+      case 3: *ptr = h->mu.ptr; break;
+      case 4: *ptr = h->Hn.ptr; break;
+      case 5: *ptr = h->Hfield.ptr; break;
+      case 6: h->u.ensure((size_t)h->nv); *ptr = h->u.ptr; break;
+      case 7: *ptr = h->dmu.ptr; break;
+      default: throw std::runtime_error("fk_device_ptr: unknown array id");
+    }
+    return 0;
+  });
+}
+
+// ---- symbolic phase alone (host) ------------------------------------------------------------------
+int fk_symbolic_create(const double* p, const int* t, int nv, int nt, const fk_create_opts* opts, fk_symbolic* out) {
+  return guard([&]() {
+    need(out && p && t, "fk: NULL argument");
+    fk_create_opts o{};
+    if (opts) o = *opts;
+    std::unique_ptr<fk_symbolic_s> s(new fk_symbolic_s());
+    build_symbolic(p, t, nv, nt, to_symbolic_opts(o), s->S);
+    *out = s.release();
+    return 0;
+  });
+}
+int fk_symbolic_sizes(fk_symbolic s, long long* nnz, int* ntiles, long long* n_tile_elems, long long* nnz_tiles,
+                      long long* n_ents, int* n_blocks) {
+  return guard([&]() {
+    need(s, "fk: NULL argument");
+    if (nnz) *nnz = s->S.nnz;
+    if (ntiles) *ntiles = s->S.ntiles;
+    if (n_tile_elems) *n_tile_elems = (long long)s->S.tile_elems.size();
+    if (nnz_tiles) *nnz_tiles = (long long)s->S.tile_gidx.size();
+    if (n_ents) *n_ents = (long long)s->S.tile_ents.size();
+    if (n_blocks) *n_blocks = (int)s->S.blk_row.size() - 1;
+    return 0;
+  });
+}
+int fk_symbolic_export(fk_symbolic s, int* rowptr, int* colind, int* diag, int* e2nnz, long long* tile_elem_ptr,
+                       unsigned int* tile_elems, long long* tile_nnz_ptr, int* tile_gidx, unsigned short* tile_coff,
+                       long long* tile_ent_ptr, unsigned short* tile_ents, int* blk_row) {
+  return guard([&]() {
+    need(s, "fk: NULL argument");
+    const Symbolic& S = s->S;
+    copy_vec(S.rowptr, rowptr);
+    copy_vec(S.colind, colind);
+    copy_vec(S.diag, diag);
+    copy_vec(S.e2nnz, e2nnz);
+    copy_vec(S.tile_elem_ptr, tile_elem_ptr);
+    copy_vec(S.tile_elems, tile_elems);
+    copy_vec(S.tile_nnz_ptr, tile_nnz_ptr);
+    copy_vec(S.tile_gidx, tile_gidx);
+    copy_vec(S.tile_coff, tile_coff);
+    copy_vec(S.tile_ent_ptr, tile_ent_ptr);
+    copy_vec(S.tile_ents, tile_ents);
+    copy_vec(S.blk_row, blk_row);
+    return 0;
+  });
+}
+int fk_symbolic_destroy(fk_symbolic s) {
+  delete s;
+  return 0;
+}
+
+// ---- assembly -----------------------------------------------------------------------------------
+static void copy_out(fk_handle h, const double* dev, double* host, size_t n) {
+  if (host) FK_CUDA(cudaMemcpyAsync(host, dev, sizeof(double) * n, cudaMemcpyDeviceToHost, h->stream));
+  FK_CUDA(cudaStreamSynchronize(h->stream));
+}
+
+int fk_assemble_stiffness_dev(fk_handle h, int slot, const double* f_dev) {
+  return guard([&]() {
+    need(h, "fk: NULL handle");
+    DeviceGuard dg(h->device);
+    assemble_stiffness_dev(h, slot, f_dev);
+    return 0;
+  });
+}
+int fk_assemble_mass_dev(fk_handle h, int slot, const double* rho_dev) {
+  return guard([&]() {
+    need(h, "fk: NULL handle");
+    DeviceGuard dg(h->device);
+    assemble_mass_dev(h, slot, rho_dev);
+    return 0;
+  });
+}
+int fk_assemble_tangential_dev(fk_handle h, int slot, const double* H_dev, const double* dmu_dev) {
+  return guard([&]() {
+    need(h && H_dev && dmu_dev, "fk: NULL argument");
+    DeviceGuard dg(h->device);
+    assemble_tangential_dev(h, slot, H_dev, dmu_dev);
+    return 0;
+  });
+}
+int fk_assemble_stiffness(fk_handle h, int slot, const double* f, double* vals_out) {
+  return guard([&]() {
+    need(h, "fk: NULL handle");
+    DeviceGuard dg(h->device);
+    if (f) h->st_a.upload(f, (size_t)h->nt, h->stream);
+    assemble_stiffness_dev(h, slot, f ? h->st_a.ptr : nullptr);
+    copy_out(h, h->vals[slot].ptr, vals_out, (size_t)h->nnz);
+    return 0;
+  });
+}
+int fk_assemble_mass(fk_handle h, int slot, const double* rho, double* vals_out) {
+  return guard([&]() {
+    need(h, "fk: NULL handle");
+    DeviceGuard dg(h->device);
+    if (rho) h->st_a.upload(rho, (size_t)h->nt, h->stream);
+    assemble_mass_dev(h, slot, rho ? h->st_a.ptr : nullptr);
+    copy_out(h, h->vals[slot].ptr, vals_out, (size_t)h->nnz);
+    return 0;
+  });
+}
+int fk_assemble_tangential(fk_handle h, int slot, const double* Hfield, const double* dmu, double* vals_out) {
+  return guard([&]() {
+    need(h && Hfield && dmu, "fk: NULL argument");
+    DeviceGuard dg(h->device);
+    h->st_a.upload(dmu, (size_t)h->nt, h->stream);
+    h->st_b.upload(Hfield, (size_t)3 * h->nt, h->stream);
+    assemble_tangential_dev(h, slot, h->st_b.ptr, h->st_a.ptr);
+    copy_out(h, h->vals[slot].ptr, vals_out, (size_t)h->nnz);
+    return 0;
+  });
+}
+int fk_local_stiffness(fk_handle h, const double* f, double* Ak) {
+  return guard([&]() {
+    need(h && Ak, "fk: NULL argument");
+    DeviceGuard dg(h->device);
+    if (f) h->st_a.upload(f, (size_t)h->nt, h->stream);
+    h->st_b.ensure((size_t)16 * h->nt);
+    local_stiffness_kernel<<<cdiv(h->nt, 128), 128, 0, h->stream>>>(h->p4.ptr, h->t4.ptr, h->user_ve ? h->VE.ptr : nullptr,
+                                                                    f ? h->st_a.ptr : nullptr, h->nt, h->st_b.ptr);
+    FK_CUDA(cudaGetLastError());
+    h->launches++;
+    copy_out(h, h->st_b.ptr, Ak, (size_t)16 * h->nt);
+    return 0;
+  });
+}
+
+int fk_matrix_axpby(fk_handle h, int dst, double alpha, int x, double beta, int y) {
+  return guard([&]() {
+    need(h, "fk: NULL handle");
+    check_slot(x);
+    DeviceGuard dg(h->device);
+    need(h->vals[x].ptr != nullptr, "fk_matrix_axpby: slot x is empty");
+    if (beta != 0.0) { check_slot(y); need(h->vals[y].ptr != nullptr, "fk_matrix_axpby: slot y is empty"); }
+    double* d = slot_vals(h, dst);
+    axpby_kernel<<<std::min(cdiv(h->nnz, 256), h->num_sms * 8), 256, 0, h->stream>>>(d, alpha, h->vals[x].ptr, beta,
+                                                                                     beta != 0.0 ? h->vals[y].ptr : nullptr, h->nnz);
+    FK_CUDA(cudaGetLastError());
+    h->launches++;
+    return 0;
+  });
+}
+int fk_matrix_get(fk_handle h, int slot, double* vals_out) {
+  return guard([&]() {
+    need(h && vals_out, "fk: NULL argument");
+    check_slot(slot);
+    need(h->vals[slot].ptr != nullptr, "fk_matrix_get: slot is empty");
+    DeviceGuard dg(h->device);
+    copy_out(h, h->vals[slot].ptr, vals_out, (size_t)h->nnz);
+    return 0;
+  });
+}
+int fk_matrix_set(fk_handle h, int slot, const double* vals_in) {
+  return guard([&]() {
+    need(h && vals_in, "fk: NULL argument");
+    DeviceGuard dg(h->device);
+    double* d = slot_vals(h, slot);
+    FK_CUDA(cudaMemcpyAsync(d, vals_in, sizeof(double) * (size_t)h->nnz, cudaMemcpyHostToDevice, h->stream));
+    FK_CUDA(cudaStreamSynchronize(h->stream));
+    return 0;
+  });
+}
+
+// ---- right-hand sides ---------------------------------------------------------------------------
+int fk_lagrange(fk_handle h, double* C_out) {
+  return guard([&]() {
+    need(h && C_out, "fk: NULL argument");
+    DeviceGuard dg(h->device);
+    // diag-only "matrix" VE/4 per local node, assembled through the same gather plan: the diagonal
+    // then holds sum_k VE[k]/4 in ascending element order = the reference loop (FEM3D.jl:274-281)
+    h->st_b.ensure((size_t)h->nnz);
+    AsmArgs a = base_args(h, h->st_b.ptr);
+    a.VE = h->VE.ptr;
+    launch_assemble<ASM_LAGRANGE>(h, a);
+    h->st_c.ensure((size_t)h->nv);
+    FK_CUDA(cudaMemsetAsync(h->st_c.ptr, 0, sizeof(double) * (size_t)h->nv, h->stream));
+    gather_diag_kernel<<<cdiv(h->n_rows, 256), 256, 0, h->stream>>>(h->st_b.ptr, h->diag.ptr, h->n_rows, h->st_c.ptr);
+    FK_CUDA(cudaGetLastError());
+    h->launches++;
+    copy_out(h, h->st_c.ptr, C_out, (size_t)h->nv);
+    return 0;
+  });
+}
+
+int fk_boundary_integral(fk_handle h, const int* surfaceT, const double* normal, const double* AE, int ns, const double* F,
+                         const int* shell_ids, int nshell, double* RHS_out) {
+  return guard([&]() {
+    need(h && surfaceT && normal && F && RHS_out, "fk: NULL argument");
+    need(ns >= 0 && (nshell == 0 || shell_ids), "fk_boundary_integral: bad shell id list");
+    DeviceGuard dg(h->device);
+    const int nv = h->nv;
+    // integer bookkeeping on the host: node -> selected surface triangles, ascending triangle order
+    std::vector<int> ptr((size_t)nv + 1, 0);
+    std::vector<char> sel((size_t)ns, 0);
+    for (int s = 0; s < ns; s++) {
+      const int id = surfaceT[4 * (size_t)s + 3];
+      for (int m = 0; m < nshell; m++) if (shell_ids[m] == id) sel[s] = 1;   // `in shell_id`, FEM3D.jl:289
+      if (!sel[s]) continue;
+      for (int i = 0; i < 3; i++) {
+        const int n = surfaceT[4 * (size_t)s + i];
+        need(n >= 0 && n < nv, "fk_boundary_integral: surface node out of range");
+        ptr[(size_t)n + 1]++;
+      }
+    }
+    for (int n = 0; n < nv; n++) ptr[n + 1] += ptr[n];
+    std::vector<int> n2s((size_t)ptr[nv] + 1), fill(ptr.begin(), ptr.end() - 1);
+    for (int s = 0; s < ns; s++)
+      if (sel[s])
+        for (int i = 0; i < 3; i++) n2s[fill[surfaceT[4 * (size_t)s + i]]++] = s;
+    cudaStream_t st = h->stream;
+    h->st_i.upload(surfaceT, (size_t)4 * ns, st);
+    h->st_j.upload(ptr, st);
+    h->st_k.upload(n2s, st);
+    h->st_a.upload(normal, (size_t)3 * ns, st);
+    if (AE) h->st_b.upload(AE, (size_t)ns, st);
+    h->st_c.ensure((size_t)nv);
+    boundary_integral_kernel<<<cdiv(nv, 256), 256, 0, st>>>(h->p4.ptr, h->st_i.ptr, h->st_a.ptr, AE ? h->st_b.ptr : nullptr,
+                                                           h->st_j.ptr, h->st_k.ptr, nv, F[0], F[1], F[2], h->st_c.ptr);
+    FK_CUDA(cudaGetLastError());
+    h->launches++;
+    copy_out(h, h->st_c.ptr, RHS_out, (size_t)nv);
+    return 0;
+  });
+}
+
+// ---- SpMV / PCG ---------------------------------------------------------------------------------
+int fk_spmv_dev(fk_handle h, int slot, const double* x_dev, double* y_dev) {
+  return guard([&]() {
+    need(h && x_dev && y_dev, "fk: NULL argument");
+    check_slot(slot);
+    need(h->vals[slot].ptr != nullptr, "fk_spmv: matrix slot has not been assembled");
+    DeviceGuard dg(h->device);
+    launch_spmv(h, h->stream, h->vals[slot].ptr, x_dev, y_dev, false, nullptr, 0);
+    h->launches++;
+    return 0;
+  });
+}
+int fk_spmv(fk_handle h, int slot, const double* x, double* y) {
+  return guard([&]() {
+    need(h && x && y, "fk: NULL argument");
+    check_slot(slot);
+    need(h->vals[slot].ptr != nullptr, "fk_spmv: matrix slot has not been assembled");
+    DeviceGuard dg(h->device);
+    h->st_c.upload(x, (size_t)h->nv, h->stream);
+    h->st_d.ensure((size_t)h->nv);
+    FK_CUDA(cudaMemsetAsync(h->st_d.ptr, 0, sizeof(double) * (size_t)h->nv, h->stream));
+    launch_spmv(h, h->stream, h->vals[slot].ptr, h->st_c.ptr, h->st_d.ptr, false, nullptr, 0);
+    h->launches++;
+    copy_out(h, h->st_d.ptr, y, (size_t)h->nv);
+    return 0;
+  });
+}
+int fk_pcg_dev(fk_handle h, int slot, const double* b_dev, double* x_dev, const fk_pcg_opts* opts, int* iters_out,
+               double* relres_out) {
+  return guard([&]() {
+    need(h && b_dev && x_dev, "fk: NULL argument");
+    DeviceGuard dg(h->device);
+    pcg_dev(h, slot, b_dev, x_dev, opts, iters_out, relres_out);
+    return 0;
+  });
+}
+int fk_pcg(fk_handle h, int slot, const double* b, double* x, const fk_pcg_opts* opts, int* iters_out, double* relres_out) {
+  return guard([&]() {
+    need(h && b && x, "fk: NULL argument");
+    DeviceGuard dg(h->device);
+    ensure_pcg(h);
+    const size_t n = (size_t)h->n_rows;
+    FK_CUDA(cudaMemcpyAsync(h->bvec.ptr, b, sizeof(double) * n, cudaMemcpyHostToDevice, h->stream));
+    h->st_d.ensure((size_t)h->nv);
+    if (opts && opts->warm_start) FK_CUDA(cudaMemcpyAsync(h->st_d.ptr, x, sizeof(double) * n, cudaMemcpyHostToDevice, h->stream));
+    pcg_dev(h, slot, h->bvec.ptr, h->st_d.ptr, opts, iters_out, relres_out);
+    copy_out(h, h->st_d.ptr, x, n);
+    return 0;
+  });
+}
+
+// ---- field recovery / nonlinear step --------------------------------------------------------------
+int fk_recover_field_dev(fk_handle h, const double* u_dev, const double* mu_dev, int compat_bug, double* Hfield_dev,
+                         double* Hnorm_dev, double* B_dev) {
+  return guard([&]() {
+    need(h && u_dev, "fk: NULL argument");
+    need(!B_dev || mu_dev, "fk_recover_field: B requested without mu");
+    DeviceGuard dg(h->device);
+    recover_field_kernel<<<cdiv(h->nt, 256), 256, 0, h->stream>>>(h->p4.ptr, h->t4.ptr, u_dev, mu_dev, h->nt, compat_bug,
+                                                                  Hfield_dev, Hnorm_dev, B_dev);
+    FK_CUDA(cudaGetLastError());
+    h->launches++;
+    return 0;
+  });
+}
+int fk_recover_field(fk_handle h, const double* u, const double* mu, int compat_bug, double* Hfield_out, double* Hnorm_out,
+                     double* B_out) {
+  return guard([&]() {
+    need(h && u, "fk: NULL argument");
+    need(!B_out || mu, "fk_recover_field: B requested without mu");
+    DeviceGuard dg(h->device);
+    const size_t nt = (size_t)h->nt;
+    h->st_c.upload(u, (size_t)h->nv, h->stream);
+    if (mu) h->st_a.upload(mu, nt, h->stream);
+    h->st_b.ensure(5 * nt);
+    double* Hf = h->st_b.ptr;
+    double* Hn = Hf + 3 * nt;
+    double* B = Hn + nt;
+    recover_field_kernel<<<cdiv(h->nt, 256), 256, 0, h->stream>>>(h->p4.ptr, h->t4.ptr, h->st_c.ptr, mu ? h->st_a.ptr : nullptr,
+                                                                  h->nt, compat_bug, Hfield_out ? Hf : nullptr,
+                                                                  Hnorm_out ? Hn : nullptr, B_out ? B : nullptr);
+    FK_CUDA(cudaGetLastError());
+    h->launches++;
+    if (Hfield_out) FK_CUDA(cudaMemcpyAsync(Hfield_out, Hf, sizeof(double) * 3 * nt, cudaMemcpyDeviceToHost, h->stream));
+    if (Hnorm_out) FK_CUDA(cudaMemcpyAsync(Hnorm_out, Hn, sizeof(double) * nt, cudaMemcpyDeviceToHost, h->stream));
+    if (B_out) FK_CUDA(cudaMemcpyAsync(B_out, B, sizeof(double) * nt, cudaMemcpyDeviceToHost, h->stream));
+    FK_CUDA(cudaStreamSynchronize(h->stream));
+    return 0;
+  });
+}
+
+int fk_spline_fit(const double* x, const double* y, int m, double* t_out, double* c_out) {
+  return guard([&]() {
+    need(x && y && t_out && c_out, "fk: NULL argument");
+    need(m >= 4, "fk_spline_fit: a cubic interpolating spline needs at least 4 points");
+    for (int i = 1; i < m; i++) need(x[i] > x[i - 1], "fk_spline_fit: x must be strictly increasing");
+    const int k = 3, n = m + k + 1;
+    for (int i = 0; i <= k; i++) { t_out[i] = x[0]; t_out[n - 1 - i] = x[m - 1]; }
+    for (int i = 0; i < m - k - 1; i++) t_out[k + 1 + i] = x[i + 2];   // interior knots x[3..m-2] (1-based)
+    // collocation N c = y, N[i][j] = B_j(x_i): banded, solved densely with partial pivoting (m is table-sized)
+    std::vector<double> N((size_t)m * m, 0.0), rhs(y, y + m);
+    for (int i = 0; i < m; i++) {
+      const int l = find_interval(t_out, n, k, x[i]);
+      double hb[6];
+      bspline_basis(t_out, k, l, x[i], hb);
+      for (int j = 0; j <= k; j++) N[(size_t)i * m + (l - k + j)] = hb[j];
+    }
+    for (int c = 0; c < m; c++) {
+      int piv = c;
+      for (int r = c + 1; r < m; r++) if (std::fabs(N[(size_t)r * m + c]) > std::fabs(N[(size_t)piv * m + c])) piv = r;
+      need(N[(size_t)piv * m + c] != 0.0, "fk_spline_fit: singular collocation matrix");
+      if (piv != c) {
+        for (int q = 0; q < m; q++) std::swap(N[(size_t)c * m + q], N[(size_t)piv * m + q]);
+        std::swap(rhs[c], rhs[piv]);
+      }
+      for (int r = c + 1; r < m; r++) {
+        const double f = N[(size_t)r * m + c] / N[(size_t)c * m + c];
+        if (f == 0.0) continue;
+        for (int q = c; q < m; q++) N[(size_t)r * m + q] -= f * N[(size_t)c * m + q];
+        rhs[r] -= f * rhs[c];
+      }
+    }
+    for (int r = m - 1; r >= 0; r--) {
+      double s = rhs[r];
+      for (int q = r + 1; q < m; q++) s -= N[(size_t)r * m + q] * c_out[q];
+      c_out[r] = s / N[(size_t)r * m + r];
+    }
+    for (int i = m; i < n; i++) c_out[i] = 0.0;
+    return 0;
+  });
+}
+
+int fk_spline_eval(const double* t, const double* c, int n, int k, int bc, const double* x, int nx, double* y_out) {
+  int status = 0;
+  int rc = guard([&]() {
+    need(t && c && x && y_out, "fk: NULL argument");
+    need(k >= 1 && k <= 5 && n >= 2 * (k + 1), "fk_spline_eval: bad spline");
+    for (int i = 0; i < nx; i++) status |= spline_eval_host(t, c, n, k, bc, x[i], y_out + i);
+    return 0;
+  });
+  if (rc) return rc;
+  if (status) set_error("fk_spline_eval: argument outside the knot range with bc = error");
+  return status;
+}
+
+int fk_set_spline(fk_handle h, int id, const double* t, const double* c, int n, int k, int bc) {
+  return guard([&]() {
+    need(h && t && c, "fk: NULL argument");
+    need(id >= 0 && id < FK_MAX_SPLINES, "fk_set_spline: table id out of range");
+    need(k >= 1 && k <= 5 && n >= 2 * (k + 1), "fk_set_spline: bad spline (need 1 <= k <= 5 and n >= 2k+2)");
+    need(bc >= 0 && bc <= 3, "fk_set_spline: bad bc");
+    DeviceGuard dg(h->device);
+    h->spl_t[id].upload(t, (size_t)n, h->stream);
+    h->spl_c[id].upload(c, (size_t)n, h->stream);
+    FK_CUDA(cudaStreamSynchronize(h->stream));
+    h->spl.s[id] = SplineDev{h->spl_t[id].ptr, h->spl_c[id].ptr, n, k, bc};
+    return 0;
+  });
+}
+
+int fk_set_material(fk_handle h, const unsigned char* matid) {
+  return guard([&]() {
+    need(h && matid, "fk: NULL argument");
+    for (int k = 0; k < h->nt; k++) need(matid[k] <= FK_MAX_SPLINES / 2, "fk_set_material: material id too large");
+    DeviceGuard dg(h->device);
+    ensure_state(h);
+    FK_CUDA(cudaMemcpyAsync(h->matid.ptr, matid, (size_t)h->nt, cudaMemcpyHostToDevice, h->stream));
+    FK_CUDA(cudaStreamSynchronize(h->stream));
+    h->have_material = true;
+    return 0;
+  });
+}
+int fk_set_inside(fk_handle h, const int* ids, int n) {
+  return guard([&]() {
+    need(h && (ids || n == 0), "fk: NULL argument");
+    for (int i = 0; i < n; i++) need(ids[i] >= 0 && ids[i] < h->nt, "fk_set_inside: element id out of range");
+    DeviceGuard dg(h->device);
+    ensure_state(h);
+    FK_CUDA(cudaMemsetAsync(h->matid.ptr, 0, (size_t)h->nt, h->stream));
+    if (n > 0) {
+      h->st_i.upload(ids, (size_t)n, h->stream);
+      set_material_kernel<<<cdiv(n, 256), 256, 0, h->stream>>>(h->matid.ptr, h->st_i.ptr, n);
+      FK_CUDA(cudaGetLastError());
+      h->launches++;
+    }
+    FK_CUDA(cudaStreamSynchronize(h->stream));
+    h->have_material = true;
+    return 0;
+  });
+}
+int fk_set_mu(fk_handle h, const double* mu) {
+  return guard([&]() {
+    need(h && mu, "fk: NULL argument");
+    DeviceGuard dg(h->device);
+    ensure_state(h);
+    FK_CUDA(cudaMemcpyAsync(h->mu.ptr, mu, sizeof(double) * (size_t)h->nt, cudaMemcpyHostToDevice, h->stream));
+    FK_CUDA(cudaStreamSynchronize(h->stream));
+    return 0;
+  });
+}
+int fk_get_mu(fk_handle h, double* mu_out, double* dmu_out) {
+  return guard([&]() {
+    need(h, "fk: NULL handle");
+    DeviceGuard dg(h->device);
+    ensure_state(h);
+    if (mu_out) FK_CUDA(cudaMemcpyAsync(mu_out, h->mu.ptr, sizeof(double) * (size_t)h->nt, cudaMemcpyDeviceToHost, h->stream));
+    if (dmu_out) FK_CUDA(cudaMemcpyAsync(dmu_out, h->dmu.ptr, sizeof(double) * (size_t)h->nt, cudaMemcpyDeviceToHost, h->stream));
+    FK_CUDA(cudaStreamSynchronize(h->stream));
+    return 0;
+  });
+}
+int fk_get_field(fk_handle h, double* Hfield_out, double* Hnorm_out) {
+  return guard([&]() {
+    need(h, "fk: NULL handle");
+    DeviceGuard dg(h->device);
+    ensure_state(h);
+    if (Hfield_out) FK_CUDA(cudaMemcpyAsync(Hfield_out, h->Hfield.ptr, sizeof(double) * 3 * (size_t)h->nt, cudaMemcpyDeviceToHost, h->stream));
+    if (Hnorm_out) FK_CUDA(cudaMemcpyAsync(Hnorm_out, h->Hn.ptr, sizeof(double) * (size_t)h->nt, cudaMemcpyDeviceToHost, h->stream));
+    FK_CUDA(cudaStreamSynchronize(h->stream));
+    return 0;
+  });
+}
+
+static int picard_step_dev(fk_handle h, int slot, const double* u_dev, int compat_bug, double* div_out) {
+  ensure_state(h);
+  AsmArgs a = base_args(h, slot_vals(h, slot));
+  a.u = u_dev;
+  a.mu = h->mu.ptr;
+  a.dmu = h->dmu.ptr;
+  a.Hn = h->Hn.ptr;
+  a.Hfield = h->Hfield.ptr;
+  a.matid = h->have_material ? h->matid.ptr : nullptr;
+  a.tile_max = h->tile_max.ptr;
+  a.errflag = h->errflag.ptr;
+  a.compat = compat_bug;
+  FK_CUDA(cudaMemsetAsync(h->errflag.ptr, 0, sizeof(int), h->stream));
+  launch_assemble<ASM_PICARD>(h, a);
+  max_array_kernel<<<1, 256, 0, h->stream>>>(h->tile_max.ptr, h->sym.ntiles, h->scal.ptr);
+  FK_CUDA(cudaGetLastError());
+  h->launches++;
+  double dmax = 0.0;
+  int err = 0;
+  FK_CUDA(cudaMemcpyAsync(&dmax, h->scal.ptr, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+  FK_CUDA(cudaMemcpyAsync(&err, h->errflag.ptr, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+  FK_CUDA(cudaStreamSynchronize(h->stream));
+  if (div_out) *div_out = (4e-7 * 3.14159265358979323846) * dmax;   // mu0*max|H - Hold| (NewtonRaphson.jl:200)
+  if (err & 1) { set_error("fk_picard_step: |H| outside the spline's knot range with bc = error"); return 2; }
+  if (err & 2) { set_error("fk_picard_step: Nans/Infs in mu"); return 3; }   // NewtonRaphson.jl:210-212
+  return 0;
+}
+int fk_picard_step_dev(fk_handle h, int slot, const double* u_dev, int compat_bug, double* div_out) {
+  return guard([&]() {
+    need(h && u_dev, "fk: NULL argument");
+    DeviceGuard dg(h->device);
+    return picard_step_dev(h, slot, u_dev, compat_bug, div_out);
+  });
+}
+int fk_picard_step(fk_handle h, int slot, const double* u, int compat_bug, double* div_out) {
+  return guard([&]() {
+    need(h && u, "fk: NULL argument");
+    DeviceGuard dg(h->device);
+    h->u.upload(u, (size_t)h->nv, h->stream);
+    return picard_step_dev(h, slot, h->u.ptr, compat_bug, div_out);
+  });
+}
+
+// ---- legacy drop-in -----------------------------------------------------------------------------
+// ABI-identical to the reference's scalarPotential (magnetostatics.cpp:49-95): BoundaryIntegral,
+// stiffnessMatrix(p,t,VE,mu), Jacobi-PCG with Eigen's defaults on -RHS, result copied into u_in.
+// It cannot return a status (void); failures are reported on stderr and u_in is left untouched.
+void scalarPotential(double* u_in, double* p_in, int* t_in, int* surfaceT_in, double* normal_in, int nv, int nt, int ns,
+                     double* VE, double* mu, double* Hext, int shell_id) {
+  fk_handle h = nullptr;
+  int rc = fk_create(p_in, t_in, nv, nt, VE, nullptr, &h);
+  std::vector<double> rhs((size_t)std::max(nv, 1));
+  if (!rc) rc = fk_boundary_integral(h, surfaceT_in, normal_in, nullptr, ns, Hext, &shell_id, 1, rhs.data());
+  if (!rc) rc = fk_assemble_stiffness(h, 0, mu, nullptr);
+  if (!rc) {
+    for (int i = 0; i < nv; i++) rhs[i] = -rhs[i];
+    int iters = 0;
+    double relres = 0.0;
+    rc = fk_pcg(h, 0, rhs.data(), u_in, nullptr, &iters, &relres);
+    if (!rc && !(relres <= DBL_EPSILON))
+      std::fprintf(stderr, "femeko_cuda scalarPotential: PCG stopped after %d iterations at relative residual %.3e "
+                           "(Eigen's default tolerance is machine epsilon; the reference throws here)\n", iters, relres);
+  }
+  if (rc) std::fprintf(stderr, "femeko_cuda scalarPotential failed: %s\n", fk_last_error());
+  if (h) fk_destroy(h);
+}
+
+}  // extern "C"

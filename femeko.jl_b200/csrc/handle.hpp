@@ -1,0 +1,98 @@
+// Internal state behind fk_handle.  One handle = one mesh (or mesh partition) resident on one GPU.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "kernels.cuh"
+#include "symbolic.hpp"
+
+namespace fk {
+
+void set_error(const std::string& s);
+
+#define FK_CUDA(call)                                                                                  \
+  do {                                                                                                 \
+    cudaError_t e_ = (call);                                                                           \
+    if (e_ != cudaSuccess)                                                                             \
+      throw std::runtime_error(std::string("CUDA error: ") + cudaGetErrorString(e_) + " at " + __FILE__ + \
+                               ":" + std::to_string(__LINE__) + " (" #call ")");                       \
+  } while (0)
+
+template <class T>
+struct DevBuf {
+  T* ptr = nullptr;
+  size_t count = 0;
+  void ensure(size_t n) {
+    if (n <= count && ptr) return;
+    release();
+    FK_CUDA(cudaMalloc((void**)&ptr, std::max<size_t>(n, 1) * sizeof(T)));
+    count = n;
+  }
+  void upload(const T* src, size_t n, cudaStream_t s) {
+    ensure(n);
+    if (n) FK_CUDA(cudaMemcpyAsync(ptr, src, n * sizeof(T), cudaMemcpyHostToDevice, s));
+  }
+  void upload(const std::vector<T>& v, cudaStream_t s) { upload(v.data(), v.size(), s); }
+  void release() {
+    if (ptr) cudaFree(ptr);
+    ptr = nullptr;
+    count = 0;
+  }
+  ~DevBuf() { release(); }
+  DevBuf() = default;
+  DevBuf(const DevBuf&) = delete;
+  DevBuf& operator=(const DevBuf&) = delete;
+};
+
+struct Comm;  // multi-GPU state (comm.cu)
+
+}  // namespace fk
+
+struct fk_handle_s {
+  int device = 0;
+  int num_sms = 148;
+  cudaStream_t stream = nullptr;       // all work is issued here (nullptr = legacy default stream)
+  cudaStream_t cap_stream = nullptr;   // private stream used only to capture the PCG chunk graph
+  int nv = 0, nt = 0, n_rows = 0;
+  long long nnz = 0;
+  bool user_ve = false;
+  fk::Symbolic sym;                    // host copy of the symbolic artefacts (pattern, e2nnz)
+
+  // mesh
+  fk::DevBuf<double4> p4;
+  fk::DevBuf<int4> t4;
+  fk::DevBuf<double> VE;
+  // pattern + plans
+  fk::DevBuf<int> rowptr, colind, diag, blk_row, tile_gidx;
+  fk::DevBuf<long long> tile_elem_ptr, tile_nnz_ptr, tile_ent_ptr;
+  fk::DevBuf<uint32_t> tile_elems;
+  fk::DevBuf<uint16_t> tile_coff, tile_ents;
+  int e_pad = 0;
+  size_t asm_smem = 0;
+  // matrices
+  fk::DevBuf<double> vals[FK_NUM_SLOTS];
+  // nonlinear state
+  fk::DevBuf<double> mu, dmu, Hn, Hfield, u, tile_max, scal;
+  fk::DevBuf<unsigned char> matid;
+  fk::DevBuf<int> errflag;
+  fk::DevBuf<double> spl_t[FK_MAX_SPLINES], spl_c[FK_MAX_SPLINES];
+  fk::SplineSet spl{};
+  bool have_material = false;
+  // PCG workspace
+  fk::DevBuf<double> x, r, p, Ap, dinv, part, bvec;
+  fk::DevBuf<fk::PcgCtl> ctl;
+  fk::PcgCtl* ctl_host = nullptr;      // pinned
+  int grid_spmv = 0, grid_vec = 0, spmv_cap = 0;
+  cudaGraphExec_t graph[FK_NUM_SLOTS] = {nullptr, nullptr, nullptr, nullptr};
+  int graph_chunk[FK_NUM_SLOTS] = {0, 0, 0, 0};
+  // generic staging for the host-pointer API
+  fk::DevBuf<double> st_a, st_b, st_c, st_d;
+  fk::DevBuf<int> st_i, st_j, st_k;
+  // multi-GPU
+  fk::Comm* comm = nullptr;
+  // launch counter (kernels of this library launched through this handle)
+  long long launches = 0;
+};

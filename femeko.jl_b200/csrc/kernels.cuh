@@ -1,0 +1,598 @@
+// Hand-written sm_100a fp64 kernels of the Femeko hot path.  All three kernel families are
+// HBM-bound gather / stream kernels (no dense contraction -> no tensor cores):
+//   K1  assemble_kernel<MODE>   P1 tet local matrices -> CSR values, tile-gather, no atomics
+//   K2  spmv_kernel / pcg_*     CSR-stream SpMV fused with p.Ap, fused x/r update + 2 dots, direction update
+//   K3  recover_field_kernel    H = -grad(u), |H|, B = mu |H|
+// Reference math: src/FEM3D.jl:5-17 (abcd), :59-76 (local stiffness), :466-476 (mass), :79-105
+// (tangential), magneticField.jl:111-132 (field), ConjugateGradient.h:29-85 (PCG recurrence).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <float.h>
+
+#include "../../include/femeko_cuda.h"
+
+namespace fk {
+
+constexpr int kAsmThreads = 256;
+constexpr int kSpmvThreads = 256;
+constexpr int kVecThreads = 256;
+
+// ------------------------------------------------------------------------------------------------
+// small helpers
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ double warp_max(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// Deterministic block reduction (fixed shuffle tree, warps folded in index order).  Every thread
+// returns the total.  `scratch` holds >= 33 doubles.  Safe to call repeatedly.
+__device__ __forceinline__ double block_sum(double v, double* scratch) {
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+  v = warp_sum(v);
+  __syncthreads();
+  if (lane == 0) scratch[w] = v;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double s = 0.0;
+    for (int i = 0; i < nw; i++) s += scratch[i];
+    scratch[32] = s;
+  }
+  __syncthreads();
+  return scratch[32];
+}
+__device__ __forceinline__ double block_max(double v, double* scratch) {
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+  v = warp_max(v);
+  __syncthreads();
+  if (lane == 0) scratch[w] = v;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double s = scratch[0];
+    for (int i = 1; i < nw; i++) s = fmax(s, scratch[i]);
+    scratch[32] = s;
+  }
+  __syncthreads();
+  return scratch[32];
+}
+// Sum of a short global array by the whole block in a fixed order (every block gets the same bits).
+__device__ __forceinline__ double block_sum_array(const double* __restrict__ a, int n, double* scratch) {
+  double v = 0.0;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) v += a[i];
+  return block_sum(v, scratch);
+}
+
+// ------------------------------------------------------------------------------------------------
+// P1 geometry: gradients of the barycentric shape functions of one tetrahedron.
+// Replaces the four 4x4 solves of abcd (src/FEM3D.jl:5-17 / FEMc.cpp:18-42): with
+// E = [x1-x0 | x2-x0 | x3-x0], rows of inv(E) are grad(lambda_1..3), grad(lambda_0) = -(sum).
+// Nodes are padded to 32 B (x,y,z,0) so one node = one aligned sector = two 128-bit loads.
+// ------------------------------------------------------------------------------------------------
+struct TetGeom {
+  double g[4][3];  // grad(lambda_i)
+  double vol;      // |det E| / 6  (elementVolume, src/mesh.jl:484-505)
+};
+
+__device__ __forceinline__ void load_node(const double4* __restrict__ p4, int n, double& x, double& y, double& z) {
+  const double2* q = reinterpret_cast<const double2*>(p4 + n);
+  double2 a = __ldg(q), b = __ldg(q + 1);
+  x = a.x; y = a.y; z = b.x;
+}
+
+__device__ __forceinline__ void tet_geometry(const double4* __restrict__ p4, const int4 nd, TetGeom& G) {
+  double x0, y0, z0, x1, y1, z1, x2, y2, z2, x3, y3, z3;
+  load_node(p4, nd.x, x0, y0, z0);
+  load_node(p4, nd.y, x1, y1, z1);
+  load_node(p4, nd.z, x2, y2, z2);
+  load_node(p4, nd.w, x3, y3, z3);
+  const double ax = x1 - x0, ay = y1 - y0, az = z1 - z0;  // AB
+  const double bx = x2 - x0, by = y2 - y0, bz = z2 - z0;  // AC
+  const double cx = x3 - x0, cy = y3 - y0, cz = z3 - z0;  // AD
+  // cofactors
+  const double c1x = by * cz - bz * cy, c1y = bz * cx - bx * cz, c1z = bx * cy - by * cx;  // AC x AD
+  const double c2x = cy * az - cz * ay, c2y = cz * ax - cx * az, c2z = cx * ay - cy * ax;  // AD x AB
+  const double c3x = ay * bz - az * by, c3y = az * bx - ax * bz, c3z = ax * by - ay * bx;  // AB x AC
+  const double det = ax * c1x + ay * c1y + az * c1z;                                      // AB . (AC x AD)
+  const double inv = 1.0 / det;
+  G.g[1][0] = c1x * inv; G.g[1][1] = c1y * inv; G.g[1][2] = c1z * inv;
+  G.g[2][0] = c2x * inv; G.g[2][1] = c2y * inv; G.g[2][2] = c2z * inv;
+  G.g[3][0] = c3x * inv; G.g[3][1] = c3y * inv; G.g[3][2] = c3z * inv;
+  G.g[0][0] = -(G.g[1][0] + G.g[2][0] + G.g[3][0]);
+  G.g[0][1] = -(G.g[1][1] + G.g[2][1] + G.g[3][1]);
+  G.g[0][2] = -(G.g[1][2] + G.g[2][2] + G.g[3][2]);
+  G.vol = fabs(det) / 6.0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// FITPACK splev / fpbspl on the device (the Dierckx Spline1D call of NewtonRaphson.jl:203-207).
+// ------------------------------------------------------------------------------------------------
+struct SplineDev {
+  const double* t;  // n knots
+  const double* c;  // n coefficients (n-k-1 used)
+  int n, k, bc;
+};
+struct SplineSet {
+  SplineDev s[FK_MAX_SPLINES];
+};
+
+__device__ __forceinline__ double splev_dev(const SplineDev& S, double x, int& err) {
+  const double* __restrict__ t = S.t;
+  const int n = S.n, k = S.k;
+  const double tb = __ldg(t + k), te = __ldg(t + n - k - 1);
+  if (x < tb || x > te || !(x == x)) {
+    if (S.bc == FK_BC_ZERO) return 0.0;
+    if (S.bc == FK_BC_ERROR || !(x == x)) { err = 1; return x; }
+    if (S.bc == FK_BC_NEAREST) x = (x < tb) ? tb : te;
+  }
+  // largest l in [k, n-k-2] with t[l] <= x (binary search; FITPACK walks linearly)
+  int lo = k, hi = n - k - 2;
+  while (lo < hi) {
+    int mid = (lo + hi + 1) >> 1;
+    if (__ldg(t + mid) <= x) lo = mid; else hi = mid - 1;
+  }
+  const int l = lo;
+  double h[6], hh[5];
+  h[0] = 1.0;
+  for (int j = 1; j <= k; j++) {
+    for (int i = 0; i < j; i++) hh[i] = h[i];
+    h[0] = 0.0;
+    for (int i = 0; i < j; i++) {
+      const double tli = __ldg(t + l + i + 1), tlj = __ldg(t + l + i + 1 - j);
+      if (tli == tlj) { h[i + 1] = 0.0; continue; }
+      const double f = hh[i] / (tli - tlj);
+      h[i] = h[i] + f * (tli - x);
+      h[i + 1] = f * (x - tlj);
+    }
+  }
+  double sp = 0.0;
+  for (int j = 0; j <= k; j++) sp += __ldg(S.c + l - k + j) * h[j];
+  return sp;
+}
+
+// ------------------------------------------------------------------------------------------------
+// K1: tile-gather assembly.
+// One CTA per tile (symbolic.hpp).  Phase 1: one thread per staged element computes the 10 unique
+// entries of the symmetric 4x4 local matrix into shared memory (SoA: sym-major, conflict-free).
+// Phase 2: one thread per CSR entry owned by the tile sums its contributors (slot, pair) in
+// ascending element order and writes the value once.  No atomics, bitwise run-to-run reproducible.
+// ------------------------------------------------------------------------------------------------
+enum AsmMode { ASM_STIFF = 0, ASM_MASS = 1, ASM_TANGENT = 2, ASM_PICARD = 3, ASM_LAGRANGE = 4 };
+
+struct AsmArgs {
+  const double4* p4;
+  const int4* t4;
+  const double* VE;       // nullable: volume from the determinant
+  const double* coef;     // STIFF: f (nullable = 1) | MASS: rho (nullable) | TANGENT: dmu
+  const double* Hvec;     // TANGENT: 3 x nt
+  // PICARD
+  const double* u;
+  double* mu;             // in (linear elements) / out (material elements)
+  double* dmu;            // nullable
+  double* Hn;             // in: |H| old, out: |H| new
+  double* Hfield;         // nullable, 3 x nt
+  const unsigned char* matid;  // nullable = all linear
+  double* tile_max;       // per tile: max | |H| - |H|old | over owned material elements
+  int* errflag;
+  int compat;
+  SplineSet spl;
+  // plan
+  const long long* tile_elem_ptr;
+  const uint32_t* tile_elems;
+  const long long* tile_nnz_ptr;
+  const int* tile_gidx;
+  const uint16_t* tile_coff;
+  const long long* tile_ent_ptr;
+  const uint16_t* tile_ents;
+  double* vals;
+  int e_pad;  // staging stride (>= max tile elements)
+};
+
+template <int MODE>
+static __global__ void __launch_bounds__(kAsmThreads) assemble_kernel(const AsmArgs a) {
+  extern __shared__ double stage[];  // 10 x e_pad
+  __shared__ double red[33];
+  const int tile = blockIdx.x;
+  const long long e0 = a.tile_elem_ptr[tile];
+  const int ne = (int)(a.tile_elem_ptr[tile + 1] - e0);
+  const int EP = a.e_pad;
+  double dmax = 0.0;
+
+  for (int s = threadIdx.x; s < ne; s += kAsmThreads) {
+    const uint32_t raw = __ldg(a.tile_elems + e0 + s);
+    const int k = (int)(raw & 0x7fffffffu);
+    const bool owner = (raw >> 31) != 0;
+    const int4 nd = __ldg(a.t4 + k);
+    double m[10];
+    if (MODE == ASM_MASS || MODE == ASM_LAGRANGE) {
+      double v;
+      if (a.VE) v = __ldg(a.VE + k);
+      else { TetGeom G; tet_geometry(a.p4, nd, G); v = G.vol; }
+      if (MODE == ASM_MASS) {
+        if (a.coef) v = v * __ldg(a.coef + k);
+        const double d = v * ((1.0 / 20.0) * 2.0), o = v * ((1.0 / 20.0) * 1.0);
+        m[0] = d; m[1] = o; m[2] = o; m[3] = o; m[4] = d; m[5] = o; m[6] = o; m[7] = d; m[8] = o; m[9] = d;
+      } else {
+        const double d = v / 4.0;
+        m[0] = d; m[1] = 0; m[2] = 0; m[3] = 0; m[4] = d; m[5] = 0; m[6] = 0; m[7] = d; m[8] = 0; m[9] = d;
+      }
+    } else {
+      TetGeom G;
+      tet_geometry(a.p4, nd, G);
+      const double V = a.VE ? __ldg(a.VE + k) : G.vol;
+      if (MODE == ASM_TANGENT) {
+        const double hx = __ldg(a.Hvec + 3 * (size_t)k), hy = __ldg(a.Hvec + 3 * (size_t)k + 1),
+                     hz = __ldg(a.Hvec + 3 * (size_t)k + 2);
+        const double H = sqrt(hx * hx + hy * hy + hz * hz);
+        const double s0 = V * __ldg(a.coef + k) / H;
+        double gh[4];
+#pragma unroll
+        for (int i = 0; i < 4; i++) gh[i] = hx * G.g[i][0] + hy * G.g[i][1] + hz * G.g[i][2];
+        int q = 0;
+#pragma unroll
+        for (int i = 0; i < 4; i++)
+#pragma unroll
+          for (int j = i; j < 4; j++) m[q++] = s0 * gh[i] * gh[j];
+      } else {
+        double f;
+        if (MODE == ASM_PICARD) {
+          const double u0 = __ldg(a.u + nd.x), u1 = __ldg(a.u + nd.y), u2 = __ldg(a.u + nd.z), u3 = __ldg(a.u + nd.w);
+          double hx = -(u0 * G.g[0][0]) - u1 * G.g[1][0] - u2 * G.g[2][0] - u3 * G.g[3][0];
+          double hy = -(u0 * G.g[0][1]) - u1 * G.g[1][1] - u2 * G.g[2][1] - u3 * G.g[3][1];
+          double hz = -(u0 * G.g[0][2]) - u1 * G.g[1][2] - u2 * G.g[2][2] - u3 * G.g[3][2];
+          if (a.compat) { hy += hz; hz = 0.0; }  // NewtonRaphson.jl:187-189: d-term lands in row 2
+          const double Hn = sqrt(hx * hx + hy * hy + hz * hz);
+          const int mat = a.matid ? (int)__ldg(a.matid + k) : 0;
+          if (mat > 0) {
+            int err = 0;
+            f = splev_dev(a.spl.s[mat - 1], Hn, err);
+            double df = 0.0;
+            const SplineDev& D = a.spl.s[FK_MAX_SPLINES / 2 + mat - 1];
+            if (a.dmu && D.n > 0) df = splev_dev(D, Hn, err);
+            if (!(f == f) || fabs(f) > DBL_MAX || !(df == df) || fabs(df) > DBL_MAX) err |= 2;  // Nans/Infs in mu
+            if (err) atomicOr(a.errflag, err);
+            if (owner) {
+              dmax = fmax(dmax, fabs(Hn - a.Hn[k]));
+              a.mu[k] = f;
+              if (a.dmu) a.dmu[k] = df;
+            }
+          } else {
+            f = __ldg(a.mu + k);
+          }
+          if (owner) {
+            a.Hn[k] = Hn;
+            if (a.Hfield) { a.Hfield[3 * (size_t)k] = hx; a.Hfield[3 * (size_t)k + 1] = hy; a.Hfield[3 * (size_t)k + 2] = hz; }
+          }
+        } else {
+          f = a.coef ? __ldg(a.coef + k) : 1.0;
+        }
+        const double s0 = V * f;  // VE[k]*f[k]*( b b' + c c' + d d' ), src/FEM3D.jl:71
+        int q = 0;
+#pragma unroll
+        for (int i = 0; i < 4; i++)
+#pragma unroll
+          for (int j = i; j < 4; j++)
+            m[q++] = s0 * ((G.g[i][0] * G.g[j][0] + G.g[i][1] * G.g[j][1]) + G.g[i][2] * G.g[j][2]);
+      }
+    }
+#pragma unroll
+    for (int q = 0; q < 10; q++) stage[q * EP + s] = m[q];
+  }
+  __syncthreads();
+
+  const long long n0 = a.tile_nnz_ptr[tile];
+  const int nn = (int)(a.tile_nnz_ptr[tile + 1] - n0);
+  const uint16_t* __restrict__ coff = a.tile_coff + n0 + tile;
+  const uint16_t* __restrict__ ents = a.tile_ents + a.tile_ent_ptr[tile];
+  for (int q = threadIdx.x; q < nn; q += kAsmThreads) {
+    const int beg = __ldg(coff + q), end = __ldg(coff + q + 1);
+    double acc = 0.0;
+    for (int e = beg; e < end; e++) {
+      const uint32_t en = __ldg(ents + e);
+      acc += stage[(en & 15u) * EP + (en >> 4)];
+    }
+    a.vals[__ldg(a.tile_gidx + n0 + q)] = acc;
+  }
+
+  if (MODE == ASM_PICARD) {
+    dmax = block_max(dmax, red);
+    if (threadIdx.x == 0) a.tile_max[tile] = dmax;
+  }
+}
+
+// dense 16 x nt local stiffness (localStiffnessMatrix, src/FEM3D.jl:59-76) -- API completeness
+static __global__ void local_stiffness_kernel(const double4* __restrict__ p4, const int4* __restrict__ t4,
+                                       const double* __restrict__ VE, const double* __restrict__ f, int nt,
+                                       double* __restrict__ Ak) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= nt) return;
+  TetGeom G;
+  tet_geometry(p4, __ldg(t4 + k), G);
+  const double V = VE ? VE[k] : G.vol;
+  const double s0 = f ? V * f[k] : V;
+  for (int j = 0; j < 4; j++)
+    for (int i = 0; i < 4; i++)
+      Ak[16 * (size_t)k + 4 * j + i] = s0 * ((G.g[i][0] * G.g[j][0] + G.g[i][1] * G.g[j][1]) + G.g[i][2] * G.g[j][2]);
+}
+
+static __global__ void volumes_kernel(const double4* __restrict__ p4, const int4* __restrict__ t4, int nt, double* __restrict__ VE) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= nt) return;
+  TetGeom G;
+  tet_geometry(p4, __ldg(t4 + k), G);
+  VE[k] = G.vol;
+}
+
+// ------------------------------------------------------------------------------------------------
+// K3: field recovery  H_k = -sum_i u[t_i] grad(lambda_i)  (magneticField.jl:111-132)
+// ------------------------------------------------------------------------------------------------
+static __global__ void __launch_bounds__(256) recover_field_kernel(const double4* __restrict__ p4, const int4* __restrict__ t4,
+                                                            const double* __restrict__ u, const double* __restrict__ mu,
+                                                            int nt, int compat, double* __restrict__ Hfield,
+                                                            double* __restrict__ Hn, double* __restrict__ B) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= nt) return;
+  const int4 nd = __ldg(t4 + k);
+  TetGeom G;
+  tet_geometry(p4, nd, G);
+  const double u0 = __ldg(u + nd.x), u1 = __ldg(u + nd.y), u2 = __ldg(u + nd.z), u3 = __ldg(u + nd.w);
+  double hx = -(u0 * G.g[0][0]) - u1 * G.g[1][0] - u2 * G.g[2][0] - u3 * G.g[3][0];
+  double hy = -(u0 * G.g[0][1]) - u1 * G.g[1][1] - u2 * G.g[2][1] - u3 * G.g[3][1];
+  double hz = -(u0 * G.g[0][2]) - u1 * G.g[1][2] - u2 * G.g[2][2] - u3 * G.g[3][2];
+  if (compat) { hy += hz; hz = 0.0; }
+  const double H = sqrt(hx * hx + hy * hy + hz * hz);
+  if (Hfield) { Hfield[3 * (size_t)k] = hx; Hfield[3 * (size_t)k + 1] = hy; Hfield[3 * (size_t)k + 2] = hz; }
+  if (Hn) Hn[k] = H;
+  if (B) B[k] = __ldg(mu + k) * H;
+}
+
+// ------------------------------------------------------------------------------------------------
+// K2: SpMV + Jacobi-PCG
+// ------------------------------------------------------------------------------------------------
+struct PcgCtl {
+  double absNew[2];  // r.z of the current / next iteration (ping-pong by iteration parity)
+  double rhs2, thr, r2;
+  int base_it, max_iter, done, iters;
+};
+
+__device__ __forceinline__ bool pcg_inactive(const PcgCtl* c, int j) {
+  return c != nullptr && (c->done != 0 || c->base_it + j >= c->max_iter);
+}
+
+// CSR-stream SpMV over precomputed row blocks: the block's value/column stream is read fully
+// coalesced (evict-first: it is touched once per product), multiplied with gathered x (L2/L1
+// resident) into shared memory, then one thread per row folds its segment left to right.
+// DOT fuses p.Ap: per-CTA partial sums in fixed order -> part[blockIdx.x].
+template <bool DOT>
+static __global__ void __launch_bounds__(kSpmvThreads) spmv_kernel(const int* __restrict__ rowptr, const int* __restrict__ colind,
+                                                            const double* __restrict__ vals, const double* __restrict__ x,
+                                                            double* __restrict__ y, const int* __restrict__ blk_row, int nblk,
+                                                            int cap, double* __restrict__ part, const PcgCtl* ctl, int j) {
+  extern __shared__ double prod[];
+  __shared__ double red[33];
+  if (pcg_inactive(ctl, j)) return;
+  double acc = 0.0;
+  for (int b = blockIdx.x; b < nblk; b += gridDim.x) {
+    const int r0 = blk_row[b], r1 = blk_row[b + 1];
+    const int q0 = rowptr[r0], q1 = rowptr[r1];
+    if (q1 - q0 <= cap) {
+      for (int q = q0 + threadIdx.x; q < q1; q += kSpmvThreads)
+        prod[q - q0] = __ldcs(vals + q) * __ldg(x + __ldcs(colind + q));
+      __syncthreads();
+      for (int r = r0 + threadIdx.x; r < r1; r += kSpmvThreads) {
+        const int a = rowptr[r] - q0, e = rowptr[r + 1] - q0;
+        double s = 0.0;
+        for (int q = a; q < e; q++) s += prod[q];
+        y[r] = s;
+        if (DOT) acc += s * x[r];
+      }
+      __syncthreads();
+    } else {  // a row block too long to stage (very high-degree node): whole CTA per row
+      for (int r = r0; r < r1; r++) {
+        double s = 0.0;
+        for (int q = rowptr[r] + threadIdx.x; q < rowptr[r + 1]; q += kSpmvThreads) s += vals[q] * __ldg(x + colind[q]);
+        s = block_sum(s, red);
+        if (threadIdx.x == 0) {
+          y[r] = s;
+          if (DOT) acc += s * x[r];
+        }
+      }
+    }
+  }
+  if (DOT) {
+    acc = block_sum(acc, red);
+    if (threadIdx.x == 0) part[blockIdx.x] = acc;
+  }
+}
+
+// dinv = 1/diag(A), 1 where the diagonal is zero or missing (BasicPreconditioners.h:62-75)
+static __global__ void jacobi_kernel(const double* __restrict__ vals, const int* __restrict__ diag, int n, int identity,
+                              double* __restrict__ dinv) {
+  const int r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= n) return;
+  double d = 1.0;
+  if (!identity && diag[r] >= 0) {
+    const double v = vals[diag[r]];
+    if (v != 0.0) d = 1.0 / v;
+  }
+  dinv[r] = d;
+}
+
+// r = b - Ax0 (Ax0 nullable), p = dinv r, partials of b.b, r.r, r.p   (ConjugateGradient.h:38-59)
+static __global__ void __launch_bounds__(kVecThreads) pcg_init_kernel(const double* __restrict__ b, const double* __restrict__ Ax0,
+                                                               const double* __restrict__ dinv, int n, double* __restrict__ r,
+                                                               double* __restrict__ p, double* __restrict__ part3) {
+  __shared__ double red[33];
+  double s_bb = 0.0, s_rr = 0.0, s_rp = 0.0;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const double bi = b[i];
+    const double ri = Ax0 ? bi - Ax0[i] : bi;
+    const double pi = dinv[i] * ri;
+    r[i] = ri;
+    p[i] = pi;
+    s_bb += bi * bi;
+    s_rr += ri * ri;
+    s_rp += ri * pi;
+  }
+  s_bb = block_sum(s_bb, red);
+  s_rr = block_sum(s_rr, red);
+  s_rp = block_sum(s_rp, red);
+  if (threadIdx.x == 0) {
+    part3[blockIdx.x] = s_bb;
+    part3[gridDim.x + blockIdx.x] = s_rr;
+    part3[2 * gridDim.x + blockIdx.x] = s_rp;
+  }
+}
+
+// single block: fold the partials (or take the all-reduced scalars when npart == 1)
+static __global__ void pcg_init_fin_kernel(const double* __restrict__ part3, int npart, int stride, double tol, int max_iter,
+                                    PcgCtl* ctl) {
+  __shared__ double red[33];
+  const double bb = block_sum_array(part3, npart, red);
+  const double rr = block_sum_array(part3 + stride, npart, red);
+  const double rp = block_sum_array(part3 + 2 * stride, npart, red);
+  if (threadIdx.x == 0) {
+    ctl->rhs2 = bb;
+    ctl->thr = fmax(tol * tol * bb, DBL_MIN);
+    ctl->r2 = rr;
+    ctl->absNew[0] = rp;
+    ctl->absNew[1] = 0.0;
+    ctl->base_it = 0;
+    ctl->max_iter = max_iter;
+    ctl->iters = 0;
+    ctl->done = (bb == 0.0 || rr < ctl->thr) ? 1 : 0;   // ConjugateGradient.h:43-56 early exits
+  }
+}
+
+// x += alpha p ; r -= alpha Ap ; partials of r.r and r.(dinv r)        (ConjugateGradient.h:62-76)
+static __global__ void __launch_bounds__(kVecThreads) pcg_update_kernel(double* __restrict__ x, double* __restrict__ r,
+                                                                 const double* __restrict__ p, const double* __restrict__ Ap,
+                                                                 const double* __restrict__ dinv, int n,
+                                                                 const double* __restrict__ part_pAp, int npart,
+                                                                 double* __restrict__ part2, const PcgCtl* ctl, int j) {
+  __shared__ double red[33];
+  if (pcg_inactive(ctl, j)) return;
+  const double pAp = block_sum_array(part_pAp, npart, red);
+  const double alpha = ctl->absNew[j & 1] / pAp;
+  double s_rr = 0.0, s_rz = 0.0;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    x[i] += alpha * p[i];
+    const double ri = r[i] - alpha * Ap[i];
+    r[i] = ri;
+    s_rr += ri * ri;
+    s_rz += ri * (dinv[i] * ri);
+  }
+  s_rr = block_sum(s_rr, red);
+  s_rz = block_sum(s_rz, red);
+  if (threadIdx.x == 0) {
+    part2[blockIdx.x] = s_rr;
+    part2[gridDim.x + blockIdx.x] = s_rz;
+  }
+}
+
+// convergence test, beta, p = dinv r + beta p                           (ConjugateGradient.h:72-81)
+static __global__ void __launch_bounds__(kVecThreads) pcg_direction_kernel(double* __restrict__ p, const double* __restrict__ r,
+                                                                    const double* __restrict__ dinv, int n,
+                                                                    const double* __restrict__ part2, int npart, int stride,
+                                                                    PcgCtl* ctl, int j) {
+  __shared__ double red[33];
+  if (pcg_inactive(ctl, j)) return;
+  const double rr = block_sum_array(part2, npart, red);
+  const double rz = block_sum_array(part2 + stride, npart, red);
+  const double absOld = ctl->absNew[j & 1];
+  const bool conv = rr < ctl->thr;
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    ctl->r2 = rr;
+    if (conv) { ctl->iters = ctl->base_it + j; ctl->done = 1; }
+    else ctl->absNew[(j + 1) & 1] = rz;
+  }
+  if (conv) return;
+  const double beta = rz / absOld;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+    p[i] = dinv[i] * r[i] + beta * p[i];
+}
+
+static __global__ void pcg_advance_kernel(PcgCtl* ctl, int chunk) {
+  if (!ctl->done) ctl->base_it += chunk;
+}
+
+// fold per-CTA partials into scalars (multi-GPU: feeds the NCCL all-reduce)
+static __global__ void fold_partials_kernel(const double* __restrict__ part, int npart, int stride, int nvals, double* __restrict__ out) {
+  __shared__ double red[33];
+  for (int v = 0; v < nvals; v++) {
+    const double s = block_sum_array(part + (size_t)v * stride, npart, red);
+    if (threadIdx.x == 0) out[v] = s;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// small vector / matrix-value kernels
+// ------------------------------------------------------------------------------------------------
+static __global__ void axpby_kernel(double* __restrict__ dst, double alpha, const double* __restrict__ x, double beta,
+                             const double* __restrict__ y, long long n) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    dst[i] = (beta != 0.0) ? alpha * x[i] + beta * y[i] : alpha * x[i];
+}
+static __global__ void fill_kernel(double* __restrict__ dst, double v, long long n) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) dst[i] = v;
+}
+static __global__ void pad_nodes_kernel(const double* __restrict__ p, int nv, double4* __restrict__ p4) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n < nv) p4[n] = make_double4(p[3 * (size_t)n], p[3 * (size_t)n + 1], p[3 * (size_t)n + 2], 0.0);
+}
+static __global__ void gather_diag_kernel(const double* __restrict__ vals, const int* __restrict__ diag, int n, double* __restrict__ out) {
+  const int r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r < n) out[r] = diag[r] >= 0 ? vals[diag[r]] : 0.0;
+}
+static __global__ void max_array_kernel(const double* __restrict__ a, int n, double* __restrict__ out) {
+  __shared__ double red[33];
+  double v = 0.0;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) v = fmax(v, a[i]);
+  v = block_max(v, red);
+  if (threadIdx.x == 0) out[0] = v;
+}
+static __global__ void set_material_kernel(unsigned char* __restrict__ matid, const int* __restrict__ ids, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) matid[ids[i]] = 1;
+}
+// BoundaryIntegral (src/FEM3D.jl:284-297 / FEMc.cpp:170-200) as a per-node gather over the node's
+// surface triangles in ascending triangle order (= the order the reference loop adds them).
+static __global__ void boundary_integral_kernel(const double4* __restrict__ p4, const int* __restrict__ surfaceT,
+                                         const double* __restrict__ normal, const double* __restrict__ AE,
+                                         const int* __restrict__ n2s_ptr, const int* __restrict__ n2s, int nv, double Fx,
+                                         double Fy, double Fz, double* __restrict__ RHS) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= nv) return;
+  double acc = 0.0;
+  for (int q = n2s_ptr[n]; q < n2s_ptr[n + 1]; q++) {
+    const int s = n2s[q];
+    double area;
+    if (AE) area = AE[s];
+    else {  // areaTriangle of FEMc.cpp:45-54
+      double x0, y0, z0, x1, y1, z1, x2, y2, z2;
+      load_node(p4, surfaceT[4 * (size_t)s], x0, y0, z0);
+      load_node(p4, surfaceT[4 * (size_t)s + 1], x1, y1, z1);
+      load_node(p4, surfaceT[4 * (size_t)s + 2], x2, y2, z2);
+      const double ax = x1 - x0, ay = y1 - y0, az = z1 - z0, bx = x2 - x0, by = y2 - y0, bz = z2 - z0;
+      const double cx = ay * bz - az * by, cy = az * bx - ax * bz, cz = ax * by - ay * bx;
+      area = 0.5 * sqrt(cx * cx + cy * cy + cz * cz);
+    }
+    const double dotv = normal[3 * (size_t)s] * Fx + normal[3 * (size_t)s + 1] * Fy + normal[3 * (size_t)s + 2] * Fz;
+    acc += dotv * area / 3;
+  }
+  RHS[n] = acc;
+}
+
+// halo exchange packing: sendbuf[i] = v[idx[i]]
+static __global__ void pack_kernel(const double* __restrict__ v, const int* __restrict__ idx, int n, double* __restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = v[idx[i]];
+}
+
+}  // namespace fk

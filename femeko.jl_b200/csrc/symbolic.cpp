@@ -1,0 +1,296 @@
+// Symbolic phase (host): canonical CSR pattern, element->nnz map, assembly tiles, SpMV row blocks.
+// See symbolic.hpp.  Reference context: the pattern equals what Eigen's setFromTriplets produces for
+// the 16*nt triplets of src/FEMc.cpp:111-129 (every (t[i,k], t[j,k]) pair, columns ascending), and
+// e2nnz is the per-element form of the triplet index lists of NewtonRaphson.jl:114-127.
+#include "symbolic.hpp"
+
+#include <algorithm>
+#include <cmath>
+#include <numeric>
+#include <stdexcept>
+#include <string>
+
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+
+namespace fk {
+
+static inline uint64_t spread21(uint64_t v) {
+  v &= 0x1fffffULL;
+  v = (v | (v << 32)) & 0x1f00000000ffffULL;
+  v = (v | (v << 16)) & 0x1f0000ff0000ffULL;
+  v = (v | (v << 8)) & 0x100f00f00f00f00fULL;
+  v = (v | (v << 4)) & 0x10c30c30c30c30c3ULL;
+  v = (v | (v << 2)) & 0x1249249249249249ULL;
+  return v;
+}
+
+void build_symbolic(const double* p, const int* t, int nv, int nt, const SymbolicOpts& o, Symbolic& S) {
+  if (nv <= 0 || nt <= 0) throw std::runtime_error("fk: empty mesh (nv and nt must be positive)");
+  if (o.tile_max_elems < 1 || o.tile_max_elems > 4096) throw std::runtime_error("fk: tile_max_elems must be in [1, 4096]");
+  if ((int64_t)nt * 4 >= (int64_t)1 << 32) throw std::runtime_error("fk: nt too large for 32-bit incidence ids");
+  S.nv = nv;
+  S.nt = nt;
+  S.n_rows = (o.n_owned < 0 || o.n_owned > nv) ? nv : o.n_owned;
+  const int nr = S.n_rows;
+
+  // ---- node -> element incidences, ascending element order (counting sort) ------------------
+  std::vector<int64_t> n2e_ptr((size_t)nv + 1, 0);
+  for (int64_t q = 0; q < (int64_t)4 * nt; q++) {
+    int n = t[q];
+    if (n < 0 || n >= nv) throw std::runtime_error("fk: connectivity entry out of range (expected 0-based ids < nv)");
+    n2e_ptr[(size_t)n + 1]++;
+  }
+  for (int r = 0; r < nv; r++) n2e_ptr[r + 1] += n2e_ptr[r];
+  std::vector<uint32_t> n2e((size_t)4 * nt);
+  {
+    std::vector<int64_t> fill(n2e_ptr.begin(), n2e_ptr.end() - 1);
+    for (int64_t q = 0; q < (int64_t)4 * nt; q++) n2e[(size_t)fill[t[q]]++] = (uint32_t)q;  // q = 4k + i
+  }
+
+  // ---- row pattern: sorted unique nodes of all incident elements ----------------------------
+  S.rowptr.assign((size_t)nv + 1, 0);
+  std::vector<int> rowlen((size_t)nv, 0);
+#pragma omp parallel
+  {
+    std::vector<int> buf;
+#pragma omp for schedule(dynamic, 1024)
+    for (int r = 0; r < nr; r++) {
+      buf.clear();
+      for (int64_t q = n2e_ptr[r]; q < n2e_ptr[r + 1]; q++) {
+        const int* e = t + 4 * (size_t)(n2e[q] >> 2);
+        buf.push_back(e[0]); buf.push_back(e[1]); buf.push_back(e[2]); buf.push_back(e[3]);
+      }
+      std::sort(buf.begin(), buf.end());
+      rowlen[r] = (int)(std::unique(buf.begin(), buf.end()) - buf.begin());
+    }
+  }
+  int64_t nnz = 0;
+  for (int r = 0; r < nv; r++) {
+    S.rowptr[r] = (int)nnz;
+    nnz += rowlen[r];
+    if (nnz > 0x7fffffffLL) throw std::runtime_error("fk: more than 2^31-1 matrix entries on one GPU; partition the mesh");
+  }
+  S.rowptr[nv] = (int)nnz;
+  S.nnz = nnz;
+  S.colind.resize((size_t)nnz);
+  S.diag.assign((size_t)nr, -1);
+#pragma omp parallel
+  {
+    std::vector<int> buf;
+#pragma omp for schedule(dynamic, 1024)
+    for (int r = 0; r < nr; r++) {
+      buf.clear();
+      for (int64_t q = n2e_ptr[r]; q < n2e_ptr[r + 1]; q++) {
+        const int* e = t + 4 * (size_t)(n2e[q] >> 2);
+        buf.push_back(e[0]); buf.push_back(e[1]); buf.push_back(e[2]); buf.push_back(e[3]);
+      }
+      std::sort(buf.begin(), buf.end());
+      int m = (int)(std::unique(buf.begin(), buf.end()) - buf.begin());
+      int* dst = S.colind.data() + S.rowptr[r];
+      for (int c = 0; c < m; c++) {
+        dst[c] = buf[c];
+        if (buf[c] == r) S.diag[r] = S.rowptr[r] + c;
+      }
+    }
+  }
+
+  // ---- element -> nnz map ---------------------------------------------------------------------
+  S.e2nnz.resize((size_t)16 * nt);
+#pragma omp parallel for schedule(static)
+  for (int k = 0; k < nt; k++) {
+    const int* e = t + 4 * (size_t)k;
+    for (int i = 0; i < 4; i++) {
+      int r = e[i];
+      for (int j = 0; j < 4; j++) {
+        int idx = -1;
+        if (r < nr) {
+          const int* b = S.colind.data() + S.rowptr[r];
+          const int* en = S.colind.data() + S.rowptr[r + 1];
+          idx = (int)(std::lower_bound(b, en, e[j]) - S.colind.data());
+        }
+        S.e2nnz[(size_t)16 * k + 4 * i + j] = idx;
+      }
+    }
+  }
+
+  // ---- tiles: rows grouped along a space-filling curve so each tile is a compact blob ---------
+  std::vector<int> order((size_t)nr);
+  std::iota(order.begin(), order.end(), 0);
+  if (!o.natural_order && p != nullptr) {
+    double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
+    for (int n = 0; n < nv; n++)
+      for (int d = 0; d < 3; d++) {
+        double v = p[3 * (size_t)n + d];
+        if (!std::isfinite(v)) throw std::runtime_error("fk: non-finite node coordinate");
+        lo[d] = std::min(lo[d], v);
+        hi[d] = std::max(hi[d], v);
+      }
+    double ext = std::max({hi[0] - lo[0], hi[1] - lo[1], hi[2] - lo[2], 1e-300});
+    std::vector<uint64_t> key((size_t)nr);
+#pragma omp parallel for schedule(static)
+    for (int r = 0; r < nr; r++) {
+      uint64_t c[3];
+      for (int d = 0; d < 3; d++) {
+        double f = (p[3 * (size_t)r + d] - lo[d]) / ext;
+        c[d] = (uint64_t)std::min(2097151.0, std::max(0.0, f * 2097151.0));
+      }
+      key[r] = (spread21(c[0]) << 2) | (spread21(c[1]) << 1) | spread21(c[2]);
+    }
+    std::sort(order.begin(), order.end(), [&](int a, int b) { return key[a] != key[b] ? key[a] < key[b] : a < b; });
+  }
+
+  std::vector<int> tile_of_row((size_t)nv, -1);
+  std::vector<int64_t> tile_row_ptr;  // -> order positions
+  std::vector<int> tile_nelem;
+  {
+    std::vector<int> marker((size_t)nt, -1);
+    int tile = 0, cur_rows = 0, cur_elems = 0;
+    int64_t cur_ents = 0, cur_nnz = 0;
+    tile_row_ptr.push_back(0);
+    for (int pos = 0; pos < nr; pos++) {
+      int r = order[pos];
+      int64_t deg = n2e_ptr[r + 1] - n2e_ptr[r];
+      if (deg > o.tile_max_elems || 4 * deg > 65535)
+        throw std::runtime_error("fk: node " + std::to_string(r) + " has " + std::to_string(deg) +
+                                 " incident elements, more than one assembly tile can stage");
+      // count-and-mark (a degenerate element listing the node twice is counted once)
+      auto claim = [&](int id) {
+        int c = 0;
+        for (int64_t q = n2e_ptr[r]; q < n2e_ptr[r + 1]; q++) {
+          int& m = marker[n2e[q] >> 2];
+          if (m != id) { m = id; c++; }
+        }
+        return c;
+      };
+      int newel = 0;
+      for (int64_t q = n2e_ptr[r]; q < n2e_ptr[r + 1]; q++) newel += (marker[n2e[q] >> 2] != tile);
+      if (cur_rows > 0 && (cur_elems + newel > o.tile_max_elems || cur_rows + 1 > o.tile_max_rows ||
+                           cur_ents + 4 * deg > 65535 || cur_nnz + rowlen[r] > 65535)) {
+        tile_nelem.push_back(cur_elems);
+        tile_row_ptr.push_back(pos);
+        tile++;
+        cur_rows = cur_elems = 0;
+        cur_ents = cur_nnz = 0;
+      }
+      newel = claim(tile);
+      cur_elems += newel;
+      cur_rows++;
+      cur_ents += 4 * deg;
+      cur_nnz += rowlen[r];
+      tile_of_row[r] = tile;
+    }
+    if (cur_rows > 0) {
+      tile_nelem.push_back(cur_elems);
+      tile_row_ptr.push_back(nr);
+    }
+  }
+  const int T = (int)tile_nelem.size();
+  S.ntiles = T;
+  S.tile_elem_ptr.assign((size_t)T + 1, 0);
+  S.tile_nnz_ptr.assign((size_t)T + 1, 0);
+  S.tile_ent_ptr.assign((size_t)T + 1, 0);
+  for (int tl = 0; tl < T; tl++) {
+    int64_t n_nnz = 0, n_ent = 0;
+    for (int64_t pos = tile_row_ptr[tl]; pos < tile_row_ptr[tl + 1]; pos++) {
+      int r = order[pos];
+      n_nnz += rowlen[r];
+      n_ent += 4 * (n2e_ptr[r + 1] - n2e_ptr[r]);
+    }
+    S.tile_elem_ptr[tl + 1] = S.tile_elem_ptr[tl] + tile_nelem[tl];
+    S.tile_nnz_ptr[tl + 1] = S.tile_nnz_ptr[tl] + n_nnz;
+    S.tile_ent_ptr[tl + 1] = S.tile_ent_ptr[tl] + n_ent;
+    S.max_tile_elems = std::max(S.max_tile_elems, tile_nelem[tl]);
+    S.max_tile_nnz = std::max<int>(S.max_tile_nnz, (int)n_nnz);
+    S.max_tile_ents = std::max<int>(S.max_tile_ents, (int)n_ent);
+  }
+  S.tile_elems.resize((size_t)S.tile_elem_ptr[T]);
+  S.tile_gidx.resize((size_t)S.tile_nnz_ptr[T]);
+  S.tile_coff.resize((size_t)S.tile_nnz_ptr[T] + T);
+  S.tile_ents.resize((size_t)S.tile_ent_ptr[T]);
+
+  int bad = 0;
+#pragma omp parallel
+  {
+    std::vector<int> rows;
+    std::vector<uint32_t> elems;
+    std::vector<int> base, cnt;
+#pragma omp for schedule(dynamic, 16)
+    for (int tl = 0; tl < T; tl++) {
+      rows.assign(order.begin() + tile_row_ptr[tl], order.begin() + tile_row_ptr[tl + 1]);
+      std::sort(rows.begin(), rows.end());
+      elems.clear();
+      for (int r : rows)
+        for (int64_t q = n2e_ptr[r]; q < n2e_ptr[r + 1]; q++) elems.push_back(n2e[q] >> 2);
+      std::sort(elems.begin(), elems.end());
+      elems.erase(std::unique(elems.begin(), elems.end()), elems.end());
+      if ((int)elems.size() != tile_nelem[tl]) {
+#pragma omp atomic write
+        bad = 1;
+        continue;
+      }
+      uint32_t* te = S.tile_elems.data() + S.tile_elem_ptr[tl];
+      for (size_t s = 0; s < elems.size(); s++) {
+        const int* e = t + 4 * (size_t)elems[s];
+        int owner_row = -1;
+        for (int i = 0; i < 4 && owner_row < 0; i++) if (e[i] < nr) owner_row = e[i];
+        uint32_t own = (owner_row >= 0 && tile_of_row[owner_row] == tl) ? 0x80000000u : 0u;
+        te[s] = elems[s] | own;
+      }
+      // tile-local numbering of the entries of the tile's rows
+      int nloc = 0;
+      base.resize(rows.size());
+      for (size_t m = 0; m < rows.size(); m++) { base[m] = nloc; nloc += rowlen[rows[m]]; }
+      int* gidx = S.tile_gidx.data() + S.tile_nnz_ptr[tl];
+      for (size_t m = 0; m < rows.size(); m++)
+        for (int c = 0; c < rowlen[rows[m]]; c++) gidx[base[m] + c] = S.rowptr[rows[m]] + c;
+      cnt.assign((size_t)nloc + 1, 0);
+      for (size_t m = 0; m < rows.size(); m++) {
+        int r = rows[m];
+        for (int64_t q = n2e_ptr[r]; q < n2e_ptr[r + 1]; q++) {
+          uint32_t k = n2e[q] >> 2, i = n2e[q] & 3;
+          for (int j = 0; j < 4; j++) cnt[base[m] + (S.e2nnz[(size_t)16 * k + 4 * i + j] - S.rowptr[r]) + 1]++;
+        }
+      }
+      uint16_t* coff = S.tile_coff.data() + S.tile_nnz_ptr[tl] + tl;
+      for (int q = 0; q < nloc; q++) cnt[q + 1] += cnt[q];
+      for (int q = 0; q <= nloc; q++) coff[q] = (uint16_t)cnt[q];
+      uint16_t* ents = S.tile_ents.data() + S.tile_ent_ptr[tl];
+      for (size_t m = 0; m < rows.size(); m++) {
+        int r = rows[m];
+        for (int64_t q = n2e_ptr[r]; q < n2e_ptr[r + 1]; q++) {  // ascending element order
+          uint32_t k = n2e[q] >> 2, i = n2e[q] & 3;
+          uint32_t slot = (uint32_t)(std::lower_bound(elems.begin(), elems.end(), k) - elems.begin());
+          for (int j = 0; j < 4; j++) {
+            int loc = base[m] + (S.e2nnz[(size_t)16 * k + 4 * i + j] - S.rowptr[r]);
+            ents[cnt[loc]++] = (uint16_t)((slot << 4) | (uint32_t)sym_index((int)i, j));
+          }
+        }
+      }
+    }
+  }
+  if (bad) throw std::runtime_error("fk: internal error building assembly tiles");
+
+  // ---- SpMV row blocks --------------------------------------------------------------------------
+  S.blk_row.clear();
+  S.blk_row.push_back(0);
+  {
+    int rows_in = 0;
+    int64_t nnz_in = 0;
+    for (int r = 0; r < nr; r++) {
+      if (rows_in > 0 && (nnz_in + rowlen[r] > o.spmv_block_nnz || rows_in >= o.spmv_block_rows)) {
+        S.blk_row.push_back(r);
+        S.max_blk_nnz = std::max<int>(S.max_blk_nnz, (int)nnz_in);
+        rows_in = 0;
+        nnz_in = 0;
+      }
+      rows_in++;
+      nnz_in += rowlen[r];
+    }
+    S.blk_row.push_back(nr);
+    S.max_blk_nnz = std::max<int>(S.max_blk_nnz, (int)nnz_in);
+  }
+}
+
+}  // namespace fk

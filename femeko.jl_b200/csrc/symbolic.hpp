@@ -1,0 +1,58 @@
+// Symbolic phase of the assembly / SpMV engine (host side, runs once per mesh).
+//
+// The reference rebuilds its sparsity on every assembly (16 x sparse()+`+=`, src/FEM3D.jl:47-53;
+// setFromTriplets, src/FEMc.cpp:111-129) or keeps a triplet index list (NewtonRaphson.jl:114-127).
+// Here the pattern, the element->nnz map and the gather plan of the atomic-free assembly kernel are
+// computed once and reused by every numeric assembly.
+#pragma once
+#include <cstdint>
+#include <vector>
+
+namespace fk {
+
+struct SymbolicOpts {
+  int tile_max_elems = 1024;  // elements staged per tile (<= 4096: 12-bit slot in a gather entry)
+  int tile_max_rows = 256;
+  bool natural_order = false;
+  int spmv_block_nnz = 2048;
+  int spmv_block_rows = 256;
+  int n_owned = -1;  // rows [0, n_owned) get a pattern (multi-GPU: owned rows first); -1 = all
+};
+
+// Gather plan of one assembly tile = a set of rows whose every incident element is staged once in
+// shared memory; every CSR entry of those rows is then summed by ONE thread from the staged local
+// matrices in ascending element order (deterministic, no atomics).
+struct Symbolic {
+  int nv = 0, nt = 0, n_rows = 0;
+  int64_t nnz = 0;
+  std::vector<int> rowptr;   // nv+1
+  std::vector<int> colind;   // nnz, ascending per row
+  std::vector<int> diag;     // n_rows: CSR index of (r,r)
+  std::vector<int> e2nnz;    // 16*nt: index of (t[i,k], t[j,k]); -1 if the row is not assembled here
+
+  int ntiles = 0;
+  std::vector<int64_t> tile_elem_ptr;  // ntiles+1 -> tile_elems
+  std::vector<uint32_t> tile_elems;    // element id | (owner bit 31): owner = tile holding row t[0,k]
+  std::vector<int64_t> tile_nnz_ptr;   // ntiles+1 -> tile_gidx ; coff index = tile_nnz_ptr[T] + T
+  std::vector<int> tile_gidx;          // global CSR index of each tile-local entry
+  std::vector<uint16_t> tile_coff;     // per tile: (tile nnz + 1) offsets into the tile's entries
+  std::vector<int64_t> tile_ent_ptr;   // ntiles+1 -> tile_ents
+  std::vector<uint16_t> tile_ents;     // (slot << 4) | sym(i,j): staged element slot + local pair
+  int max_tile_elems = 0, max_tile_nnz = 0, max_tile_ents = 0;
+
+  // SpMV row blocks: rows [blk_row[b], blk_row[b+1]) hold <= spmv_block_nnz entries (or one long row)
+  std::vector<int> blk_row;
+  int max_blk_nnz = 0;
+};
+
+// p: 3 x nv (may be null when natural_order), t: 4 x nt 0-based.  Throws std::runtime_error on bad input.
+void build_symbolic(const double* p, const int* t, int nv, int nt, const SymbolicOpts& o, Symbolic& S);
+
+// index of the unordered local pair (i,j) in the 10-entry symmetric staging layout
+inline int sym_index(int i, int j) {
+  if (i > j) { int s = i; i = j; j = s; }
+  static const int base[4] = {0, 4, 7, 9};
+  return base[i] + (j - i);
+}
+
+}  // namespace fk

@@ -1,0 +1,369 @@
+"""Host-side mirror of the reference's FEM operator interface for the P1 tetrahedral hot path.
+
+Same names, argument meaning and error behaviour as the Julia functions (src/FEM3D.jl) so that the
+drivers read like the reference's; every numeric operation is a call into libfemeko_cuda.so:
+
+    stiffnessMatrix(mesh, f)            src/FEM3D.jl:40-56      -> fk_assemble_stiffness
+    localStiffnessMatrix(mesh, f)       src/FEM3D.jl:59-76      -> fk_local_stiffness
+    massMatrix(mesh)                    src/FEM3D.jl:466-492    -> fk_assemble_mass
+    tangentialStiffnessMatrix(...)      src/FEM3D.jl:79-119     -> fk_assemble_tangential
+    lagrange(mesh)                      src/FEM3D.jl:274-281    -> fk_lagrange
+    BoundaryIntegral(mesh, F, shell_id) src/FEM3D.jl:284-297    -> fk_boundary_integral
+    cg(A, b)                            IterativeSolvers.cg call sites (run.jl:141, LL.jl:185) and
+                                        Eigen's Jacobi-PCG (magnetostatics.cpp:26-38) -> fk_pcg
+    lineSearch(u, du, A, RHS)           src/FEM3D.jl:123-152    -> fk_spmv
+    recoverField(mesh, u, mu)           magneticField.jl:111-132 -> fk_recover_field
+    Spline1D(x, y; bc)                  Dierckx.jl (NewtonRaphson.jl:57-63) -> fk_spline_fit/eval
+
+Indices are 0-based (see mesh.py).  Matrices come back as :class:`SparseCSR` on the canonical
+pattern (structural node adjacency, ascending columns; CSR == CSC by symmetry).
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import lib as L
+from .mesh import MESH
+
+
+class Femeko:
+    """Owner of one ``fk_handle``: the mesh resident on the GPU plus its symbolic artefacts."""
+
+    def __init__(self, mesh: MESH, use_mesh_VE: bool = True, device: int | None = None, n_owned: int = 0, **opts):
+        self.lib = L.load()
+        self.mesh = mesh
+        o = L.fk_create_opts()
+        for k, v in opts.items():
+            setattr(o, k, int(v))
+        if device is None:
+            device = -1
+        o.device = int(device)
+        o.n_owned = int(n_owned)
+        p = L.f64(mesh.p)
+        t = L.i32(mesh.t)
+        assert p.shape[0] == 3 and t.shape[0] == 4, "mesh.p must be 3 x nv and mesh.t 4 x nt"
+        p = np.asfortranarray(p)
+        t = np.asfortranarray(t)
+        VE = L.f64(mesh.VE) if (use_mesh_VE and mesh.VE is not None) else None
+        h = C.c_void_p()
+        L.check(self.lib.fk_create(L.dptr(p), L.iptr(t), int(p.shape[1]), int(t.shape[1]), L.dptr(VE), C.byref(o), C.byref(h)))
+        self.h = h
+        nv, nt, nnz, ntl = C.c_int(), C.c_int(), C.c_longlong(), C.c_int()
+        L.check(self.lib.fk_sizes(h, C.byref(nv), C.byref(nt), C.byref(nnz), C.byref(ntl)))
+        self.nv, self.nt, self.nnz, self.ntiles = nv.value, nt.value, nnz.value, ntl.value
+        self.n_rows = n_owned if n_owned > 0 else self.nv
+        self._pattern = None
+
+    # -- lifecycle ------------------------------------------------------------------------------
+    def close(self):
+        if getattr(self, "h", None) is not None and self.h.value:
+            self.lib.fk_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_stream(self, stream_ptr: int):
+        L.check(self.lib.fk_set_stream(self.h, C.c_void_p(stream_ptr)))
+
+    def synchronize(self):
+        L.check(self.lib.fk_synchronize(self.h))
+
+    def launch_count(self) -> int:
+        n = C.c_longlong()
+        L.check(self.lib.fk_launch_count(self.h, C.byref(n)))
+        return n.value
+
+    # -- symbolic artefacts ---------------------------------------------------------------------
+    def pattern(self):
+        if self._pattern is None:
+            rowptr = np.zeros(self.nv + 1, dtype=np.int32)
+            colind = np.zeros(self.nnz, dtype=np.int32)
+            L.check(self.lib.fk_csr_pattern(self.h, L.iptr(rowptr), L.iptr(colind)))
+            self._pattern = (rowptr, colind)
+        return self._pattern
+
+    def elem2nnz(self):
+        m = np.zeros(16 * self.nt, dtype=np.int32)
+        L.check(self.lib.fk_elem2nnz(self.h, L.iptr(m)))
+        return m
+
+    def volumes(self):
+        v = np.zeros(self.nt)
+        L.check(self.lib.fk_volumes(self.h, L.dptr(v)))
+        return v
+
+    def tile_stats(self):
+        st, a, b, c = C.c_longlong(), C.c_int(), C.c_int(), C.c_int()
+        L.check(self.lib.fk_tile_stats(self.h, C.byref(st), C.byref(a), C.byref(b), C.byref(c)))
+        return {"tiles": self.ntiles, "staged_elems": st.value, "recompute_factor": st.value / max(1, self.nt),
+                "max_elems": a.value, "max_nnz": b.value, "max_ents": c.value}
+
+    def device_ptr(self, which: int) -> int:
+        p = C.c_void_p()
+        L.check(self.lib.fk_device_ptr(self.h, which, C.byref(p)))
+        return p.value
+
+    # -- assembly (host pointers: the Julia call shape) -----------------------------------------
+    def _vals(self, want):
+        return np.zeros(self.nnz) if want else None
+
+    def assemble_stiffness(self, f=None, slot=0, want_vals=True):
+        v = self._vals(want_vals)
+        f = self._coef(f)
+        L.check(self.lib.fk_assemble_stiffness(self.h, slot, L.dptr(f), L.dptr(v)))
+        return v
+
+    def assemble_mass(self, rho=None, slot=1, want_vals=True):
+        v = self._vals(want_vals)
+        rho = self._coef(rho)
+        L.check(self.lib.fk_assemble_mass(self.h, slot, L.dptr(rho), L.dptr(v)))
+        return v
+
+    def assemble_tangential(self, Hfield, dmu, slot=2, want_vals=True):
+        v = self._vals(want_vals)
+        Hf = np.asfortranarray(L.f64(Hfield))
+        assert Hf.shape == (3, self.nt), "H_vec must be 3 x nt"
+        L.check(self.lib.fk_assemble_tangential(self.h, slot, L.dptr(Hf), L.dptr(self._coef(dmu)), L.dptr(v)))
+        return v
+
+    def _coef(self, f):
+        if f is None:
+            return None
+        f = np.ascontiguousarray(f, dtype=np.float64)
+        if f.shape != (self.nt,):
+            raise ValueError(f"coefficient vector must have length nt = {self.nt}")
+        return f
+
+    def local_stiffness(self, f=None):
+        Ak = np.zeros((16, self.nt), order="F")
+        L.check(self.lib.fk_local_stiffness(self.h, L.dptr(self._coef(f)), L.dptr(Ak)))
+        return Ak
+
+    def matrix_axpby(self, dst, alpha, x, beta=0.0, y=0):
+        L.check(self.lib.fk_matrix_axpby(self.h, dst, float(alpha), x, float(beta), y))
+
+    def matrix_get(self, slot):
+        v = np.zeros(self.nnz)
+        L.check(self.lib.fk_matrix_get(self.h, slot, L.dptr(v)))
+        return v
+
+    def matrix_set(self, slot, vals):
+        v = np.ascontiguousarray(vals, dtype=np.float64)
+        assert v.shape == (self.nnz,)
+        L.check(self.lib.fk_matrix_set(self.h, slot, L.dptr(v)))
+
+    # -- vectors --------------------------------------------------------------------------------
+    def lagrange(self):
+        Cv = np.zeros(self.nv)
+        L.check(self.lib.fk_lagrange(self.h, L.dptr(Cv)))
+        return Cv
+
+    def boundary_integral(self, surfaceT, normal, AE, F, shell_id):
+        sT = np.asfortranarray(L.i32(surfaceT))
+        nrm = np.asfortranarray(L.f64(normal))
+        ids = np.ascontiguousarray(np.atleast_1d(shell_id), dtype=np.int32)
+        Fv = np.ascontiguousarray(F, dtype=np.float64)
+        assert Fv.shape == (3,)
+        RHS = np.zeros(self.nv)
+        AEv = None if AE is None else np.ascontiguousarray(AE, dtype=np.float64)
+        L.check(self.lib.fk_boundary_integral(self.h, L.iptr(sT), L.dptr(nrm), L.dptr(AEv), int(sT.shape[1]), L.dptr(Fv),
+                                              L.iptr(ids), int(ids.size), L.dptr(RHS)))
+        return RHS
+
+    # -- SpMV / PCG -----------------------------------------------------------------------------
+    def spmv(self, x, slot=0):
+        x = np.ascontiguousarray(x, dtype=np.float64)
+        assert x.shape == (self.nv,)
+        y = np.zeros(self.nv)
+        L.check(self.lib.fk_spmv(self.h, slot, L.dptr(x), L.dptr(y)))
+        return y
+
+    @staticmethod
+    def pcg_opts(tol=0.0, max_iter=0, warm_start=False, check_every=0, tol_disable=False, no_precond=False):
+        return L.fk_pcg_opts(float(tol), int(max_iter), int(warm_start), int(check_every), int(tol_disable), int(no_precond))
+
+    def pcg(self, b, slot=0, x0=None, **kw):
+        """Jacobi-PCG with Eigen's recurrence; returns (x, iterations, relative residual)."""
+        b = np.ascontiguousarray(b, dtype=np.float64)
+        assert b.shape[0] >= self.n_rows
+        x = np.zeros(self.nv)
+        if x0 is not None:
+            x[:] = x0
+            kw["warm_start"] = True
+        o = self.pcg_opts(**kw)
+        it, rr = C.c_int(), C.c_double()
+        L.check(self.lib.fk_pcg(self.h, slot, L.dptr(b), L.dptr(x), C.byref(o), C.byref(it), C.byref(rr)))
+        return x, it.value, rr.value
+
+    # -- field recovery / nonlinear -------------------------------------------------------------
+    def recover_field(self, u, mu=None, compat_bug=False, want_B=True):
+        u = np.ascontiguousarray(u, dtype=np.float64)
+        assert u.shape[0] >= self.nv
+        Hf = np.zeros((3, self.nt), order="F")
+        Hn = np.zeros(self.nt)
+        B = np.zeros(self.nt) if (mu is not None and want_B) else None
+        L.check(self.lib.fk_recover_field(self.h, L.dptr(u), L.dptr(self._coef(mu)), int(compat_bug), L.dptr(Hf), L.dptr(Hn),
+                                          L.dptr(B)))
+        return Hf, Hn, B
+
+    def set_spline(self, table_id, spl: "Spline1D"):
+        L.check(self.lib.fk_set_spline(self.h, table_id, L.dptr(spl.t), L.dptr(spl.c), len(spl.t), spl.k, L.BC[spl.bc]))
+
+    def set_inside(self, ids):
+        ids = np.ascontiguousarray(ids, dtype=np.int32)
+        L.check(self.lib.fk_set_inside(self.h, L.iptr(ids), int(ids.size)))
+
+    def set_material(self, matid):
+        m = np.ascontiguousarray(matid, dtype=np.uint8)
+        assert m.shape == (self.nt,)
+        L.check(self.lib.fk_set_material(self.h, m.ctypes.data_as(L.c_ubyte_p)))
+
+    def set_mu(self, mu):
+        L.check(self.lib.fk_set_mu(self.h, L.dptr(self._coef(mu))))
+
+    def get_mu(self, want_dmu=False):
+        mu = np.zeros(self.nt)
+        dmu = np.zeros(self.nt) if want_dmu else None
+        L.check(self.lib.fk_get_mu(self.h, L.dptr(mu), L.dptr(dmu)))
+        return (mu, dmu) if want_dmu else mu
+
+    def get_field(self):
+        Hf = np.zeros((3, self.nt), order="F")
+        Hn = np.zeros(self.nt)
+        L.check(self.lib.fk_get_field(self.h, L.dptr(Hf), L.dptr(Hn)))
+        return Hf, Hn
+
+    def picard_step(self, u, slot=0, compat_bug=False):
+        """Fused sweep: H from u, div = mu0*max|dH|, mu = spl(|H|), stiffness(mu) -> slot.  Returns div.
+        Raises FemekoError("Nans/Infs in mu") / out-of-range errors like the reference does."""
+        u = np.ascontiguousarray(u, dtype=np.float64)
+        assert u.shape[0] >= self.nv
+        div = C.c_double()
+        L.check(self.lib.fk_picard_step(self.h, slot, L.dptr(u), int(compat_bug), C.byref(div)))
+        return div.value
+
+
+class SparseCSR:
+    """Assembled matrix on the canonical pattern; keeps its handle + slot so solves stay on the GPU."""
+
+    def __init__(self, fk: Femeko, slot: int, vals: np.ndarray):
+        self.fk, self.slot, self.vals = fk, slot, vals
+        self.rowptr, self.colind = fk.pattern()
+        self.shape = (fk.nv, fk.nv)
+
+    def toscipy(self):
+        import scipy.sparse as sp
+
+        return sp.csr_matrix((self.vals, self.colind, self.rowptr), shape=self.shape)
+
+    def _sync(self):
+        """Make the device slot hold this matrix (another assembly may have reused the slot)."""
+        self.fk.matrix_set(self.slot, self.vals)
+
+    def __matmul__(self, x):
+        self._sync()
+        return self.fk.spmv(x, self.slot)
+
+
+def _handle(mesh: MESH) -> Femeko:
+    fk = getattr(mesh, "_fk", None)
+    if fk is None or not fk.h.value:
+        fk = Femeko(mesh)
+        mesh._fk = fk
+    return fk
+
+
+def stiffnessMatrix(mesh: MESH, f=None) -> SparseCSR:
+    fk = _handle(mesh)
+    return SparseCSR(fk, 0, fk.assemble_stiffness(f, slot=0))
+
+
+def massMatrix(mesh: MESH) -> SparseCSR:
+    fk = _handle(mesh)
+    return SparseCSR(fk, 1, fk.assemble_mass(None, slot=1))
+
+
+def tangentialStiffnessMatrix(mesh: MESH, H_vec, dmu) -> SparseCSR:
+    fk = _handle(mesh)
+    return SparseCSR(fk, 2, fk.assemble_tangential(H_vec, dmu, slot=2))
+
+
+def localStiffnessMatrix(mesh: MESH, f=None) -> np.ndarray:
+    return _handle(mesh).local_stiffness(f)
+
+
+def lagrange(mesh: MESH) -> np.ndarray:
+    return _handle(mesh).lagrange()
+
+
+def BoundaryIntegral(mesh: MESH, F, shell_id) -> np.ndarray:
+    return _handle(mesh).boundary_integral(mesh.surfaceT, mesh.normal, mesh.AE, F, shell_id)
+
+
+def cg(A: SparseCSR, b, Pl="jacobi", reltol=None, maxiter=None, x0=None, log=False):
+    """Conjugate gradients on the GPU.  ``Pl="jacobi"`` is Eigen's default solver of the C++ path
+    (tol = eps, 2n iterations); ``Pl=None`` mirrors IterativeSolvers.cg(A, b) (no preconditioner,
+    reltol = sqrt(eps), maxiter = n)."""
+    n = A.shape[0]
+    if Pl is None:
+        reltol = np.sqrt(np.finfo(float).eps) if reltol is None else reltol
+        maxiter = n if maxiter is None else maxiter
+    A._sync()
+    x, it, rr = A.fk.pcg(b, slot=A.slot, x0=x0, tol=reltol or 0.0, max_iter=maxiter or 0, no_precond=Pl is None)
+    return (x, it, rr) if log else x
+
+
+def lineSearch(u, du, A: SparseCSR, RHS, minStep: float = 1e-4):
+    """Backtracking of src/FEM3D.jl:123-152; updates u in place, returns the residual norm."""
+    A._sync()
+    alf = 1.0
+    residual_old = np.linalg.norm(RHS - A.fk.spmv(u, A.slot))
+    u_trial = u + du
+    residue = np.linalg.norm(RHS - A.fk.spmv(u_trial, A.slot))
+    while residue > residual_old and alf > minStep:
+        alf *= 0.9
+        u_trial = u + alf * du
+        residue = np.linalg.norm(RHS - A.fk.spmv(u_trial, A.slot))
+    if alf < minStep:
+        print("Warning: N-R could not decrease the residue further")
+    else:
+        u[:] = u_trial
+    return residue
+
+
+def recoverField(mesh: MESH, u, mu=None, compat_bug: bool = False):
+    """H_vectorField (3 x nt), |H| and B = mu.*H as in magneticField.jl:111-132."""
+    return _handle(mesh).recover_field(u, mu, compat_bug)
+
+
+class Spline1D:
+    """Dierckx.jl ``Spline1D(x, y; k=3, s=0, bc)``: interpolating cubic B-spline with FITPACK's
+    knot choice; fields ``t`` (knots), ``c`` (coefficients), ``k`` like the Julia object."""
+
+    def __init__(self, x, y, bc: str = "nearest"):
+        if bc not in L.BC:
+            raise ValueError("bc must be one of " + ", ".join(L.BC))
+        x = np.ascontiguousarray(x, dtype=np.float64)
+        y = np.ascontiguousarray(y, dtype=np.float64)
+        if x.shape != y.shape:
+            raise ValueError("x and y must have the same length")
+        m = x.size
+        self.k, self.bc = 3, bc
+        self.t = np.zeros(m + 4)
+        self.c = np.zeros(m + 4)
+        L.check(L.load().fk_spline_fit(L.dptr(x), L.dptr(y), m, L.dptr(self.t), L.dptr(self.c)))
+
+    def __call__(self, x):
+        xv = np.ascontiguousarray(np.atleast_1d(x), dtype=np.float64)
+        out = np.zeros(xv.size)
+        rc = L.load().fk_spline_eval(L.dptr(self.t), L.dptr(self.c), len(self.t), self.k, L.BC[self.bc], L.dptr(xv.ravel()),
+                                     int(xv.size), L.dptr(out))
+        L.check(rc)
+        out = out.reshape(xv.shape)
+        return out if np.ndim(x) else float(out[0])

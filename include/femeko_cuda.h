@@ -1,0 +1,185 @@
+/* femeko_cuda.h -- C ABI of libfemeko_cuda.so, the B200 (sm_100a, fp64) hot path of Femeko.jl.
+ *
+ * Boundary convention = the reference's own ccall pattern (Femeko_jl_C++/Magnetostatics/run.jl:50-79,
+ * magnetostatics.cpp:49-95): plain pointers + sizes, caller owns every buffer, matrices are
+ * column-major (Julia), node/element indices are 0-based `int` (the caller shifts, run.jl:50-52),
+ * pointers are only read/written during the call.  Persistent device state lives behind an opaque
+ * handle (the way the reference's C++ LL object copies p,t into owned storage, LL.cpp:10-13).
+ *
+ * Every new entry point returns int (0 = ok, != 0 = error, text via fk_last_error()); nothing throws
+ * across the boundary (the reference throws std::runtime_error through extern "C",
+ * magnetostatics.cpp:29-38, which aborts the Julia process).
+ *
+ * Pointer kinds:  *_h / unsuffixed = HOST memory (pageable is fine);  names ending in _dev and every
+ * pointer argument of an fk_*_dev function = DEVICE memory on the handle's GPU (e.g. a torch
+ * tensor's data_ptr()).  Matrices assembled by the handle live in numbered value slots that share
+ * one CSR pattern (slot 0..FK_NUM_SLOTS-1), so M + dt*A (heat3D.jl:85) or A + At
+ * (NewtonRaphson.jl:171) are value-only operations.
+ */
+#ifndef FEMEKO_CUDA_H
+#define FEMEKO_CUDA_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct fk_handle_s* fk_handle;
+
+#define FK_NUM_SLOTS 4
+#define FK_MAX_SPLINES 8
+
+/* spline boundary behaviour = Dierckx.jl `bc` strings (NewtonRaphson.jl:58, manyBodyIntersecting.jl:191) */
+enum { FK_BC_EXTRAPOLATE = 0, FK_BC_ZERO = 1, FK_BC_ERROR = 2, FK_BC_NEAREST = 3 };
+
+/* Options of the symbolic phase (all 0 = defaults). */
+typedef struct fk_create_opts {
+  int tile_max_elems; /* elements staged per assembly tile (<= 4096); default 1024            */
+  int tile_max_rows;  /* rows per assembly tile; default 256                                  */
+  int natural_order;  /* 1: tile rows in input order instead of Morton order of coordinates   */
+  int spmv_block_nnz; /* nnz staged per SpMV row block; default 2048                          */
+  int device;         /* CUDA device ordinal; -1 = current device                             */
+  int n_owned;        /* multi-GPU partitions: rows [0, n_owned) are owned (assembled, solved),
+                         rows [n_owned, nv) are halo copies; 0 = all rows owned                 */
+} fk_create_opts;
+
+/* PCG options.  Defaults (all 0) reproduce Eigen::ConjugateGradient's: tol = DBL_EPSILON relative
+ * residual, max_iter = 2n (IterativeSolverBase.h:251,368), x0 = 0, Jacobi preconditioner. */
+typedef struct fk_pcg_opts {
+  double tol;           /* relative residual ||r|| / ||b||; <= 0 -> DBL_EPSILON; use tol_disable to run a fixed count */
+  int max_iter;         /* <= 0 -> 2n                                                          */
+  int warm_start;       /* 1: x holds the initial guess (solveWithGuess); 0: x0 = 0            */
+  int check_every;      /* iterations per host convergence poll / CUDA-graph chunk; default 32 */
+  int tol_disable;      /* 1: never stop on the residual, run exactly max_iter iterations      */
+  int no_precond;       /* 1: identity preconditioner (IterativeSolvers.cg call sites, run.jl:141) */
+} fk_pcg_opts;
+
+const char* fk_last_error(void);
+int fk_version(void);
+
+/* ---- lifecycle -------------------------------------------------------------------------------
+ * fk_create copies p (3 x nv) and t (4 x nt, 0-based) to the GPU, runs the symbolic phase
+ * (canonical CSR pattern = structural node adjacency, ascending columns == Eigen setFromTriplets
+ * pattern of FEMc.cpp:111-129; element->nnz map; assembly tiles) and allocates the value slots.
+ * VE may be NULL: volumes are then computed as |AB.(ACxAD)|/6 (src/mesh.jl:484-505).            */
+int fk_create(const double* p, const int* t, int nv, int nt, const double* VE,
+              const fk_create_opts* opts, fk_handle* out);
+int fk_destroy(fk_handle h);
+/* stream: a cudaStream_t passed as void* (NULL = legacy default stream).  All work of the handle is
+ * issued on it.                                                                                  */
+int fk_set_stream(fk_handle h, void* stream);
+int fk_synchronize(fk_handle h);
+/* number of kernels of this library launched through the handle so far (graph nodes included) */
+int fk_launch_count(fk_handle h, long long* n);
+
+/* ---- symbolic artefacts (host copies) ------------------------------------------------------- */
+int fk_sizes(fk_handle h, int* nv, int* nt, long long* nnz, int* ntiles);
+int fk_csr_pattern(fk_handle h, int* rowptr /* nv+1 */, int* colind /* nnz */);
+/* map[16k + 4i + j] = CSR value index of entry (t[i,k], t[j,k]); the deterministic scatter map
+ * (reference analogue: rowIDs/colIDs of NewtonRaphson.jl:115-127).                              */
+int fk_elem2nnz(fk_handle h, int* map /* 16 nt */);
+int fk_volumes(fk_handle h, double* VE /* nt */);
+/* assembly-plan statistics: elements staged over all tiles (>= nt; the excess is halo recompute) */
+int fk_tile_stats(fk_handle h, long long* staged_elems, int* max_elems, int* max_nnz, int* max_ents);
+/* device pointers of handle-owned arrays, for zero-copy interop (torch.from_blob-style):
+ * which: 0 rowptr(int) 1 colind(int) 2 VE(double) 3 mu(double) 4 Hnorm(double) 5 Hfield(double 3 x nt)
+ *        6 u(double nv) 16+s values of slot s                                                   */
+int fk_device_ptr(fk_handle h, int which, void** ptr);
+
+/* ---- symbolic phase alone (host only, needs no GPU): lets the plan be inspected / validated ---
+ * Arrays may be NULL to skip them.  Sizes: tile_*_ptr ntiles+1; tile_elems n_tile_elems (bit 31 =
+ * this tile owns the element's per-element outputs); tile_gidx nnz_tiles; tile_coff nnz_tiles+ntiles
+ * (tile T's offsets start at tile_nnz_ptr[T]+T); tile_ents 16*nt entries (slot<<4 | pair);
+ * blk_row n_blocks+1.                                                                           */
+typedef struct fk_symbolic_s* fk_symbolic;
+int fk_symbolic_create(const double* p, const int* t, int nv, int nt, const fk_create_opts* opts, fk_symbolic* out);
+int fk_symbolic_sizes(fk_symbolic s, long long* nnz, int* ntiles, long long* n_tile_elems, long long* nnz_tiles,
+                      long long* n_ents, int* n_blocks);
+int fk_symbolic_export(fk_symbolic s, int* rowptr, int* colind, int* diag, int* e2nnz, long long* tile_elem_ptr,
+                       unsigned int* tile_elems, long long* tile_nnz_ptr, int* tile_gidx, unsigned short* tile_coff,
+                       long long* tile_ent_ptr, unsigned short* tile_ents, int* blk_row);
+int fk_symbolic_destroy(fk_symbolic s);
+
+/* ---- assembly: stiffnessMatrix / massMatrix / tangentialStiffnessMatrix ----------------------
+ * Host form = the Julia call shape: coefficient vector in, CSR values out (vals_out may be NULL to
+ * keep the matrix on the GPU only).  f == NULL means ones(nt) (src/FEM3D.jl:40).                */
+int fk_assemble_stiffness(fk_handle h, int slot, const double* f, double* vals_out);     /* FEM3D.jl:40-76, FEMc.cpp:102-167 */
+int fk_assemble_mass(fk_handle h, int slot, const double* rho, double* vals_out);       /* FEM3D.jl:466-492 */
+int fk_assemble_tangential(fk_handle h, int slot, const double* Hfield /* 3 x nt */,
+                           const double* dmu, double* vals_out);                        /* FEM3D.jl:79-119 */
+int fk_local_stiffness(fk_handle h, const double* f, double* Ak /* 16 x nt */);          /* FEM3D.jl:59-76 */
+int fk_assemble_stiffness_dev(fk_handle h, int slot, const double* f_dev);
+int fk_assemble_mass_dev(fk_handle h, int slot, const double* rho_dev);
+int fk_assemble_tangential_dev(fk_handle h, int slot, const double* Hfield_dev, const double* dmu_dev);
+
+/* slot algebra on the shared pattern: dst = alpha*X + beta*Y (Y ignored when beta == 0) */
+int fk_matrix_axpby(fk_handle h, int dst, double alpha, int x, double beta, int y);
+int fk_matrix_get(fk_handle h, int slot, double* vals_out);
+int fk_matrix_set(fk_handle h, int slot, const double* vals_in);
+
+/* ---- right-hand sides ----------------------------------------------------------------------- */
+int fk_lagrange(fk_handle h, double* C_out /* nv */);                                    /* FEM3D.jl:274-281 */
+/* BoundaryIntegral (FEM3D.jl:284-297 / FEMc.cpp:170-200).  AE may be NULL: the area is then
+ * recomputed by cross product like the C++ reference does.  shell_ids: list of boundary ids.   */
+int fk_boundary_integral(fk_handle h, const int* surfaceT /* 4 x ns */, const double* normal /* 3 x ns */,
+                         const double* AE, int ns, const double* F /* 3 */, const int* shell_ids,
+                         int nshell, double* RHS_out /* nv */);
+
+/* ---- SpMV and Jacobi-PCG (Eigen recurrence, ConjugateGradient.h:29-85) ---------------------- */
+int fk_spmv(fk_handle h, int slot, const double* x, double* y);
+int fk_spmv_dev(fk_handle h, int slot, const double* x_dev, double* y_dev);
+int fk_pcg(fk_handle h, int slot, const double* b, double* x, const fk_pcg_opts* opts,
+           int* iters_out, double* relres_out);
+int fk_pcg_dev(fk_handle h, int slot, const double* b_dev, double* x_dev, const fk_pcg_opts* opts,
+               int* iters_out, double* relres_out);
+
+/* ---- field recovery and the nonlinear step --------------------------------------------------
+ * H_k = -sum_i u[t_i] grad(lambda_i), |H_k|, B_k = mu_k |H_k| (magneticField.jl:111-132).
+ * compat_bug != 0 reproduces NewtonRaphson.jl:187-189 / run.jl:94-96 (d-term written into row 2).
+ * Output pointers may be NULL.                                                                  */
+int fk_recover_field(fk_handle h, const double* u, const double* mu, int compat_bug,
+                     double* Hfield_out /* 3 x nt */, double* Hnorm_out, double* B_out);
+int fk_recover_field_dev(fk_handle h, const double* u_dev, const double* mu_dev, int compat_bug,
+                         double* Hfield_dev, double* Hnorm_dev, double* B_dev);
+
+/* B-spline table `id` in FITPACK (t, c, k) form = the fields of a Dierckx.jl Spline1D
+ * (NewtonRaphson.jl:57-63).  fk_spline_fit builds the interpolating spline curfit(k=3, s=0) returns:
+ * n = m + 4 knots [x1 x4 | x3..x_{m-2} | xm x4].                                                */
+int fk_spline_fit(const double* x, const double* y, int m, double* t_out /* m+4 */, double* c_out /* m+4 */);
+int fk_spline_eval(const double* t, const double* c, int n, int k, int bc, const double* x, int nx,
+                   double* y_out);   /* host splev (FITPACK fpbspl), returns 2 if bc=error and out of range */
+int fk_set_spline(fk_handle h, int id, const double* t, const double* c, int n, int k, int bc);
+/* material of every element: 0 = linear (mu untouched), m >= 1 = mu from spline table m-1 and
+ * dmu from table FK_MAX_SPLINES/2 + m-1 when set.  fk_set_inside marks ids[] as material 1
+ * (mesh.InsideElements, NewtonRaphson.jl:204) and everything else 0.                            */
+int fk_set_material(fk_handle h, const unsigned char* matid /* nt */);
+int fk_set_inside(fk_handle h, const int* ids, int n);
+int fk_set_mu(fk_handle h, const double* mu /* nt */);
+int fk_get_mu(fk_handle h, double* mu_out, double* dmu_out /* may be NULL */);
+int fk_get_field(fk_handle h, double* Hfield_out, double* Hnorm_out);
+/* One fused nonlinear sweep over the elements (manyBodyIntersecting.jl:156-207 + :147, or
+ * NewtonRaphson.jl:178-207 + :153-161): from the potential u recover H and |H|, div =
+ * mu0*max_{material}| |H| - |H|_old |, mu = spl(|H|) (and dmu) on material elements, and assemble
+ * the stiffness matrix with the new mu into `slot` -- one kernel, the mesh is read once.
+ * Returns status 2 if a spline with bc = error was evaluated out of range.                      */
+int fk_picard_step(fk_handle h, int slot, const double* u, int compat_bug, double* div_out);
+int fk_picard_step_dev(fk_handle h, int slot, const double* u_dev, int compat_bug, double* div_out);
+
+/* ---- multi-GPU (one process per GPU; NCCL over NVLink) --------------------------------------
+ * The handle is built on this rank's partition (owned rows first, then halo rows; ghost elements
+ * duplicated so assembly needs no communication).  fk_comm_* wire the halo exchange of the SpMV and
+ * the dot-product all-reduce of the PCG into the same kernels.                                   */
+int fk_nccl_unique_id(unsigned char* id128);
+int fk_comm_init(fk_handle h, const unsigned char* id128, int rank, int nranks);
+/* n_owned rows are owned; for each neighbour q: send_idx lists local rows to send, recv rows land in
+ * local rows [recv_start[q], recv_start[q]+recv_count[q]).                                       */
+int fk_set_halo(fk_handle h, int n_owned, int nneigh, const int* neigh_rank, const int* send_ptr /* nneigh+1 */,
+                const int* send_idx, const int* recv_start, const int* recv_count);
+
+/* ---- legacy drop-in: ABI-identical to the reference (magnetostatics.cpp:49-60) --------------- */
+void scalarPotential(double* u_in, double* p_in, int* t_in, int* surfaceT_in, double* normal_in,
+                     int nv, int nt, int ns, double* VE, double* mu, double* Hext, int shell_id);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FEMEKO_CUDA_H */

@@ -1,0 +1,324 @@
+"""TEST INFRASTRUCTURE ONLY -- ctypes front end of the CPU oracle.
+
+Two libraries:
+  * ``oracle/_build/liboracle.so``   plain-C restatement (femeko_oracle.c), always buildable (gcc);
+  * ``oracle/_ref/libfemeko_ref.so`` the UNMODIFIED reference C++ (src/FEMc.cpp + Eigen) behind
+    ref_shim.cpp, and ``oracle/_ref/magnetostatics.so`` (the reference's own ccall library,
+    Femeko_jl_C++/Magnetostatics/magnetostatics.cpp:49-95).  Built in the dev container where
+    /root/reference exists; they travel to the GPU box as prebuilt files.
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs import
+this module.  Parity status: pinned against outputs of the compiled reference (no golden vectors
+exist upstream); Julia-only orderings and Dierckx are pinned via scipy's FITPACK.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_dp = C.POINTER(C.c_double)
+_ip = C.POINTER(C.c_int)
+
+
+def build(ref: bool = True) -> None:
+    """Compile the oracle (and, when /root/reference is present, the reference shim)."""
+    subprocess.run(["make", "-s", "-C", _HERE, "_build/liboracle.so"] + (["ref"] if ref else []),
+                   check=True, env={**os.environ, "MAKEFLAGS": ""})
+
+
+def _d(a):
+    return None if a is None else a.ctypes.data_as(_dp)
+
+
+def _i(a):
+    return None if a is None else a.ctypes.data_as(_ip)
+
+
+def _f64(a):
+    return None if a is None else np.ascontiguousarray(np.asarray(a, dtype=np.float64).ravel(order="K"))
+
+
+def _i32(a):
+    return None if a is None else np.ascontiguousarray(np.asarray(a, dtype=np.int32).ravel(order="K"))
+
+
+def _flat(a, dtype):
+    """Column-major flattening of a (possibly F-ordered) matrix: the bytes Julia would pass."""
+    if a is None:
+        return None
+    return np.ascontiguousarray(np.asarray(a, dtype=dtype).ravel(order="F"))
+
+
+_lib = None
+_ref = None
+_mag = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        path = os.path.join(_HERE, "_build", "liboracle.so")
+        if not os.path.exists(path):
+            build(ref=False)
+        _lib = C.CDLL(path)
+        _lib.orc_pattern.restype = C.c_long
+    return _lib
+
+
+def have_ref() -> bool:
+    return os.path.exists(os.path.join(_HERE, "_ref", "libfemeko_ref.so"))
+
+
+def ref():
+    global _ref
+    if _ref is None:
+        _ref = C.CDLL(os.path.join(_HERE, "_ref", "libfemeko_ref.so"))
+        _ref.ref_stiffness_csc.restype = C.c_long
+    return _ref
+
+
+def ref_magnetostatics():
+    global _mag
+    if _mag is None:
+        _mag = C.CDLL(os.path.join(_HERE, "_ref", "magnetostatics.so"))
+    return _mag
+
+
+# ----------------------------------------------------------------------------- restatement
+def abcd(p, nodes, nd):
+    r = np.zeros(4)
+    lib().orc_abcd(_d(_flat(p, np.float64)), _i(_i32(nodes)), C.c_int(int(nd)), _d(r))
+    return r
+
+
+def local_stiffness(p, t, VE, f=None):
+    nt = t.shape[1]
+    Ak = np.zeros(16 * nt)
+    lib().orc_local_stiffness(_d(_flat(p, np.float64)), _i(_flat(t, np.int32)), _d(_f64(VE)), _d(_f64(f)),
+                              C.c_int(nt), _d(Ak))
+    return Ak.reshape(nt, 16).T  # 16 x nt view, Julia layout
+
+
+def local_mass(VE, rho=None):
+    nt = len(VE)
+    Mk = np.zeros(16 * nt)
+    lib().orc_local_mass(_d(_f64(VE)), _d(_f64(rho)), C.c_int(nt), _d(Mk))
+    return Mk.reshape(nt, 16).T
+
+
+def local_tangential(p, t, VE, Hvec, dmu):
+    nt = t.shape[1]
+    Ak = np.zeros(16 * nt)
+    lib().orc_local_tangential(_d(_flat(p, np.float64)), _i(_flat(t, np.int32)), _d(_f64(VE)),
+                               _d(_flat(Hvec, np.float64)), _d(_f64(dmu)), C.c_int(nt), _d(Ak))
+    return Ak.reshape(nt, 16).T
+
+
+def pattern(t, nv):
+    nt = t.shape[1]
+    tf = _flat(t, np.int32)
+    rowptr = np.zeros(nv + 1, dtype=np.int32)
+    nnz = lib().orc_pattern(_i(tf), C.c_int(nv), C.c_int(nt), _i(rowptr), None)
+    colind = np.zeros(nnz, dtype=np.int32)
+    lib().orc_pattern(_i(tf), C.c_int(nv), C.c_int(nt), _i(rowptr), _i(colind))
+    return rowptr, colind
+
+
+def elem2nnz(t, rowptr, colind):
+    nt = t.shape[1]
+    m = np.zeros(16 * nt, dtype=np.int32)
+    lib().orc_elem2nnz(_i(_flat(t, np.int32)), C.c_int(nt), _i(rowptr), _i(colind), _i(m))
+    return m
+
+
+def assemble_julia(e2nnz, nnz, Ak, scale=None, n_major_single=False):
+    nt = Ak.shape[1]
+    vals = np.zeros(nnz)
+    lib().orc_assemble_julia(_i(e2nnz), C.c_int(nt), C.c_long(nnz), _d(_flat(Ak, np.float64)), _d(_f64(scale)),
+                             C.c_int(int(n_major_single)), _d(vals))
+    return vals
+
+
+def assemble_eigen(e2nnz, nnz, Ak, mu=None):
+    nt = Ak.shape[1]
+    vals = np.zeros(nnz)
+    lib().orc_assemble_eigen(_i(e2nnz), C.c_int(nt), C.c_long(nnz), _d(_flat(Ak, np.float64)), _d(_f64(mu)), _d(vals))
+    return vals
+
+
+def stiffness(mesh, f=None, order="julia"):
+    """stiffnessMatrix(mesh, f) -> (rowptr, colind, vals) on the canonical pattern."""
+    rowptr, colind = pattern(mesh.t, mesh.nv)
+    m = elem2nnz(mesh.t, rowptr, colind)
+    if order == "julia":
+        Ak = local_stiffness(mesh.p, mesh.t, mesh.VE, f)
+        vals = assemble_julia(m, len(colind), Ak)
+    else:
+        Ak = local_stiffness(mesh.p, mesh.t, mesh.VE, None)
+        vals = assemble_eigen(m, len(colind), Ak, f)
+    return rowptr, colind, vals
+
+
+def mass(mesh, rho=None):
+    rowptr, colind = pattern(mesh.t, mesh.nv)
+    m = elem2nnz(mesh.t, rowptr, colind)
+    return rowptr, colind, assemble_julia(m, len(colind), local_mass(mesh.VE, rho))
+
+
+def tangential(mesh, Hvec, dmu):
+    rowptr, colind = pattern(mesh.t, mesh.nv)
+    m = elem2nnz(mesh.t, rowptr, colind)
+    return rowptr, colind, assemble_julia(m, len(colind), local_tangential(mesh.p, mesh.t, mesh.VE, Hvec, dmu))
+
+
+def lagrange(mesh):
+    Cv = np.zeros(mesh.nv)
+    lib().orc_lagrange(_i(_flat(mesh.t, np.int32)), _d(_f64(mesh.VE)), C.c_int(mesh.nv), C.c_int(mesh.nt), _d(Cv))
+    return Cv
+
+
+def boundary_integral(mesh, F, shell_id, form="julia"):
+    RHS = np.zeros(mesh.nv)
+    Fv = _f64(F)
+    if form == "julia":
+        ids = _i32(np.atleast_1d(shell_id))
+        lib().orc_boundary_integral_julia(_i(_flat(mesh.surfaceT, np.int32)), _d(_flat(mesh.normal, np.float64)),
+                                          _d(_f64(mesh.AE)), C.c_int(mesh.ns), _d(Fv), _i(ids), C.c_int(len(ids)),
+                                          C.c_int(mesh.nv), _d(RHS))
+    else:
+        lib().orc_boundary_integral_cpp(_d(_flat(mesh.p, np.float64)), _i(_flat(mesh.surfaceT, np.int32)),
+                                        _d(_flat(mesh.normal, np.float64)), C.c_int(mesh.ns), _d(Fv),
+                                        C.c_int(int(np.atleast_1d(shell_id)[0])), C.c_int(mesh.nv), _d(RHS))
+    return RHS
+
+
+def recover_field(mesh, u, compat_bug=False):
+    Hf = np.zeros(3 * mesh.nt)
+    H = np.zeros(mesh.nt)
+    lib().orc_recover_field(_d(_flat(mesh.p, np.float64)), _i(_flat(mesh.t, np.int32)), _d(_f64(u)), C.c_int(mesh.nt),
+                            C.c_int(int(compat_bug)), _d(Hf), _d(H))
+    return np.asfortranarray(Hf.reshape(mesh.nt, 3).T), H
+
+
+def gradient(x, y):
+    z = np.zeros(len(x))
+    lib().orc_gradient(_d(_f64(x)), _d(_f64(y)), C.c_int(len(x)), _d(z))
+    return z
+
+
+def material_permeability(H, B):
+    n = len(H)
+    mu, dmu, nu = np.zeros(n), np.zeros(n), np.zeros(n)
+    lib().orc_material_permeability(_d(_f64(H)), _d(_f64(B)), C.c_int(n), _d(mu), _d(dmu), _d(nu))
+    return mu, dmu, nu
+
+
+BC = {"extrapolate": 0, "zero": 1, "error": 2, "nearest": 3}
+
+
+def splev(tk, c, k, x, bc="nearest"):
+    tk, c = _f64(tk), _f64(c)
+    x = np.atleast_1d(np.asarray(x, dtype=np.float64))
+    out = np.zeros(x.size)
+    err = 0
+    v = C.c_double()
+    for m, xv in enumerate(x.ravel()):
+        err |= lib().orc_splev(_d(tk), C.c_int(len(tk)), _d(c), C.c_int(k), C.c_double(xv), C.c_int(BC[bc]), C.byref(v))
+        out[m] = v.value
+    if err:
+        raise ValueError("spline evaluated outside its knots with bc='error'")
+    return out.reshape(x.shape)
+
+
+def spmv(rowptr, colind, vals, x):
+    n = len(rowptr) - 1
+    y = np.zeros(n)
+    lib().orc_spmv(C.c_int(n), _i(rowptr), _i(colind), _d(_f64(vals)), _d(_f64(x)), _d(y))
+    return y
+
+
+def pcg(rowptr, colind, vals, b, tol=2.220446049250313e-16, max_iter=None):
+    n = len(rowptr) - 1
+    x = np.zeros(n)
+    it, err = C.c_int(), C.c_double()
+    info = lib().orc_pcg(C.c_int(n), _i(rowptr), _i(colind), _d(_f64(vals)), _d(_f64(b)), _d(x), C.c_double(tol),
+                         C.c_int(2 * n if max_iter is None else max_iter), C.byref(it), C.byref(err))
+    return x, it.value, err.value, info
+
+
+# ----------------------------------------------------------------------------- compiled reference
+def ref_abcd(p, nodes, nd):
+    r = np.zeros(4)
+    pf = _flat(p, np.float64)
+    ref().ref_abcd(_d(pf), C.c_int(p.shape[1]), _i(_i32(nodes)), C.c_int(int(nd)), _d(r))
+    return r
+
+
+def ref_local_stiffness(mesh):
+    Ak = np.zeros(16 * mesh.nt)
+    ref().ref_local_stiffness(_d(_flat(mesh.p, np.float64)), _i(_flat(mesh.t, np.int32)), C.c_int(mesh.nv),
+                              C.c_int(mesh.nt), _d(_f64(mesh.VE)), _d(Ak))
+    return Ak.reshape(mesh.nt, 16).T
+
+
+def ref_stiffness(mesh, mu=None, want_time=False):
+    """Reference stiffnessMatrix (FEMc.cpp:102-167) -> CSC (outer, inner, values)."""
+    pf, tf, ve, muv = _flat(mesh.p, np.float64), _flat(mesh.t, np.int32), _f64(mesh.VE), _f64(mu)
+    outer = np.zeros(mesh.nv + 1, dtype=np.int32)
+    secs = C.c_double()
+    # two passes would assemble twice; over-allocate with the structural bound instead
+    rowptr, _ = pattern(mesh.t, mesh.nv)
+    cap = int(rowptr[-1])
+    inner = np.zeros(cap, dtype=np.int32)
+    vals = np.zeros(cap)
+    nnz = ref().ref_stiffness_csc(_d(pf), _i(tf), C.c_int(mesh.nv), C.c_int(mesh.nt), _d(ve), _d(muv), _i(outer),
+                                  _i(inner), _d(vals), C.byref(secs))
+    out = (outer, inner[:nnz], vals[:nnz])
+    return out + (secs.value,) if want_time else out
+
+
+def ref_stiffness_seconds(mesh, mu):
+    """Wall time of the reference assembly only (no copy-out)."""
+    secs = C.c_double()
+    ref().ref_stiffness_csc(_d(_flat(mesh.p, np.float64)), _i(_flat(mesh.t, np.int32)), C.c_int(mesh.nv),
+                            C.c_int(mesh.nt), _d(_f64(mesh.VE)), _d(_f64(mu)), None, None, None, C.byref(secs))
+    return secs.value
+
+
+def ref_lagrange(mesh):
+    Cv = np.zeros(mesh.nv)
+    ref().ref_lagrange(_i(_flat(mesh.t, np.int32)), _d(_f64(mesh.VE)), C.c_int(mesh.nv), C.c_int(mesh.nt), _d(Cv))
+    return Cv
+
+
+def ref_boundary_integral(mesh, F, shell_id):
+    RHS = np.zeros(mesh.nv)
+    ref().ref_boundary_integral(_d(_flat(mesh.p, np.float64)), _i(_flat(mesh.surfaceT, np.int32)),
+                                _d(_flat(mesh.normal, np.float64)), C.c_int(mesh.nv), C.c_int(mesh.ns), _d(_f64(F)),
+                                C.c_int(int(shell_id)), _d(RHS))
+    return RHS
+
+
+def ref_cg(outer, inner, values, b, tol=0.0, max_iter=0):
+    """Eigen ConjugateGradient (Lower, Jacobi) as magnetostatics.cpp:26-38; tol/max_iter <= 0 keep
+    Eigen's defaults.  Returns x, iterations, error estimate, info, seconds."""
+    n = len(outer) - 1
+    x = np.zeros(n)
+    it, err, secs = C.c_int(), C.c_double(), C.c_double()
+    info = ref().ref_cg(C.c_int(n), _i(_i32(outer)), _i(_i32(inner)), _d(_f64(values)), _d(_f64(b)), _d(x),
+                        C.c_double(tol), C.c_int(max_iter), C.byref(it), C.byref(err), C.byref(secs))
+    return x, it.value, err.value, info, secs.value
+
+
+def ref_scalar_potential(mesh, mu, Hext, shell_id):
+    """The reference's own ccall entry point, called exactly as run.jl:66-79 does."""
+    u = np.zeros(mesh.nv)
+    ref_magnetostatics().scalarPotential(
+        _d(u), _d(_flat(mesh.p, np.float64)), _i(_flat(mesh.t, np.int32)), _i(_flat(mesh.surfaceT, np.int32)),
+        _d(_flat(mesh.normal, np.float64)), C.c_int(mesh.nv), C.c_int(mesh.nt), C.c_int(mesh.ns), _d(_f64(mesh.VE)),
+        _d(_f64(mu)), _d(_f64(Hext)), C.c_int(int(shell_id)))
+    return u

@@ -1,0 +1,64 @@
+"""Test helper: export the symbolic phase of libfemeko_cuda.so (host only, no GPU) and execute the
+assembly gather plan in numpy, so the plan itself (tiles, slots, contributor lists) is validated on
+the CPU against the oracle.  Test infrastructure only."""
+import ctypes as C
+
+import numpy as np
+
+from femeko_jl_b200 import lib as L
+
+SYM = np.array([[0, 1, 2, 3], [1, 4, 5, 6], [2, 5, 7, 8], [3, 6, 8, 9]])
+
+
+def export_symbolic(mesh, **opts):
+    lib = L.load()
+    o = L.fk_create_opts()
+    for k, v in opts.items():
+        setattr(o, k, int(v))
+    p = np.asfortranarray(mesh.p, dtype=np.float64)
+    t = np.asfortranarray(mesh.t, dtype=np.int32)
+    s = C.c_void_p()
+    L.check(lib.fk_symbolic_create(L.dptr(p), L.iptr(t), mesh.nv, mesh.nt, C.byref(o), C.byref(s)))
+    nnz, ntiles, nte, nnzt, nent, nblk = C.c_longlong(), C.c_int(), C.c_longlong(), C.c_longlong(), C.c_longlong(), C.c_int()
+    L.check(lib.fk_symbolic_sizes(s, C.byref(nnz), C.byref(ntiles), C.byref(nte), C.byref(nnzt), C.byref(nent), C.byref(nblk)))
+    T = ntiles.value
+    n_rows = o.n_owned if o.n_owned > 0 else mesh.nv
+    out = dict(
+        rowptr=np.zeros(mesh.nv + 1, np.int32), colind=np.zeros(nnz.value, np.int32), diag=np.zeros(n_rows, np.int32),
+        e2nnz=np.zeros(16 * mesh.nt, np.int32), tile_elem_ptr=np.zeros(T + 1, np.int64), tile_elems=np.zeros(nte.value, np.uint32),
+        tile_nnz_ptr=np.zeros(T + 1, np.int64), tile_gidx=np.zeros(nnzt.value, np.int32),
+        tile_coff=np.zeros(nnzt.value + T, np.uint16), tile_ent_ptr=np.zeros(T + 1, np.int64),
+        tile_ents=np.zeros(nent.value, np.uint16), blk_row=np.zeros(nblk.value + 1, np.int32))
+    order = ["rowptr", "colind", "diag", "e2nnz", "tile_elem_ptr", "tile_elems", "tile_nnz_ptr", "tile_gidx", "tile_coff",
+             "tile_ent_ptr", "tile_ents", "blk_row"]
+    L.check(lib.fk_symbolic_export(s, *[C.c_void_p(out[k].ctypes.data) for k in order]))
+    lib.fk_symbolic_destroy(s)
+    out["ntiles"] = T
+    out["nnz"] = nnz.value
+    return out
+
+
+def run_plan(plan, Ak):
+    """Execute the gather plan on dense local matrices Ak (16 x nt, Julia layout): returns CSR values."""
+    nt = Ak.shape[1]
+    A10 = np.zeros((10, nt))
+    for i in range(4):
+        for j in range(i, 4):
+            A10[SYM[i, j]] = Ak[4 * j + i]
+    vals = np.full(plan["nnz"], np.nan)
+    written = np.zeros(plan["nnz"], dtype=np.int32)
+    for T in range(plan["ntiles"]):
+        e0, e1 = plan["tile_elem_ptr"][T], plan["tile_elem_ptr"][T + 1]
+        elems = (plan["tile_elems"][e0:e1] & 0x7FFFFFFF).astype(np.int64)
+        n0, n1 = plan["tile_nnz_ptr"][T], plan["tile_nnz_ptr"][T + 1]
+        coff = plan["tile_coff"][n0 + T: n1 + T + 1].astype(np.int64)
+        ents = plan["tile_ents"][plan["tile_ent_ptr"][T]: plan["tile_ent_ptr"][T + 1]].astype(np.int64)
+        assert coff[0] == 0 and coff[-1] == ents.size
+        contrib = A10[ents & 15, elems[ents >> 4]]
+        csum = np.concatenate([[0.0], np.cumsum(contrib)])
+        # exact sequential sums per segment (cumsum differences would lose bits): loop when small
+        g = plan["tile_gidx"][n0:n1]
+        for q in range(n1 - n0):
+            vals[g[q]] = contrib[coff[q]:coff[q + 1]].sum() if coff[q + 1] - coff[q] > 8 else sum(contrib[coff[q]:coff[q + 1]], 0.0)
+        written[g] += 1
+    return vals, written

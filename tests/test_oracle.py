@@ -1,0 +1,122 @@
+"""CPU: pin the oracle (oracle/femeko_oracle.c) against the reference.
+
+* against the committed golden fixtures = outputs of the compiled, unmodified reference C++
+  (tests/golden/make_golden.py) -- runs everywhere;
+* against the compiled reference itself (oracle/_ref) on fresh meshes -- runs where it was built;
+* against scipy's FITPACK wrapper for the Dierckx spline pieces (Dierckx.jl wraps the same Fortran);
+* analytic known answers: patch test, zero row sums, mass = volume.
+"""
+import numpy as np
+import pytest
+
+import femeko_jl_b200 as fk
+from conftest import abs_sum_scale, load_golden, rel_err_matrix, rel_l2
+from oracle import oracle as orc
+
+GOLD = ["kuhn3", "kuhn6", "delaunay300"]
+
+
+@pytest.mark.parametrize("name", GOLD)
+def test_oracle_matches_golden_reference_outputs(name):
+    m, g = load_golden(name)
+    rp, ci = orc.pattern(m.t, m.nv)
+    assert np.array_equal(rp, g["csc_outer"]) and np.array_equal(ci, g["csc_inner"])  # pattern bit-exact
+    # local matrices (FEMc.cpp:76-99 uses a QR solve, the oracle an LU solve: agreement to rounding)
+    Ak = orc.local_stiffness(m.p, m.t, m.VE, None)
+    assert np.max(np.abs(Ak - g["Ak"])) <= 1e-12 * np.max(np.abs(g["Ak"]))
+    # abcd samples
+    for row, k in zip(g["abcd"], g["abcd_elems"]):
+        for i in range(4):
+            r = orc.abcd(m.p, m.t[:, k], m.t[i, k])
+            assert np.allclose(r, row[i], rtol=1e-11, atol=1e-11 * np.abs(row[i]).max())
+    e2n = orc.elem2nnz(m.t, rp, ci)
+    sc_mu, sc_1 = abs_sum_scale(m, g["Ak"], g["mu"]), abs_sum_scale(m, g["Ak"])
+    v = orc.assemble_eigen(e2n, len(ci), Ak, g["mu"])
+    assert rel_err_matrix(v, g["csc_values_mu"], sc_mu) < 1e-12
+    v = orc.assemble_julia(e2n, len(ci), orc.local_stiffness(m.p, m.t, m.VE, g["mu"]))
+    assert rel_err_matrix(v, g["csc_values_mu"], sc_mu) < 1e-12      # Julia order == C++ order to 1e-12
+    v1 = orc.assemble_eigen(e2n, len(ci), Ak, None)
+    assert rel_err_matrix(v1, g["csc_values_nomu"], sc_1) < 1e-12
+    assert np.array_equal(orc.lagrange(m), g["lagrange"])            # same loop, same order: bit-exact
+    assert np.array_equal(orc.boundary_integral(m, g["F"], 0, "cpp"), g["boundary_integral"])
+    assert rel_l2(orc.boundary_integral(m, g["F"], [0], "julia"), g["boundary_integral"]) < 1e-14
+    x, it, err, info = orc.pcg(rp, ci, g["csc_values_mu"], -g["boundary_integral"], 1e-10)
+    assert info == 0 and abs(it - int(g["cg_iters"])) <= 1
+    assert rel_l2(x, g["cg_u"]) < 1e-8
+
+
+@pytest.mark.skipif(not orc.have_ref(), reason="compiled reference (oracle/_ref) not present")
+@pytest.mark.parametrize("mesh", ["kuhn5", "delaunay"])
+def test_oracle_matches_compiled_reference(mesh):
+    m = fk.kuhn_cube(5) if mesh == "kuhn5" else fk.delaunay_ball(800, seed=3)
+    mu = np.random.default_rng(1).uniform(1.0, 5.0, m.nt) * fk.mu0
+    outer, inner, vals = orc.ref_stiffness(m, mu)
+    rp, ci, v = orc.stiffness(m, mu, order="eigen")
+    assert np.array_equal(outer, rp) and np.array_equal(inner, ci)
+    sc = abs_sum_scale(m, orc.ref_local_stiffness(m), mu)
+    assert rel_err_matrix(v, vals, sc) < 1e-12
+    _, _, vj = orc.stiffness(m, mu, order="julia")
+    assert rel_err_matrix(vj, vals, sc) < 1e-12
+    b = -orc.ref_boundary_integral(m, [0.3, -1.0, 0.5], 0)
+    x1, it1, e1, info, _ = orc.ref_cg(outer, inner, vals, b, 1e-9, 0)
+    x2, it2, e2, _ = orc.pcg(rp, ci, vals, b, 1e-9)
+    assert info == 0 and abs(it1 - it2) <= 1 and rel_l2(x2, x1) < 1e-8
+
+
+def test_patch_test_and_row_sums():
+    """Linear u = g.x: recovered H = -g exactly; A u vanishes at interior nodes; A 1 = 0; sum(M) = volume."""
+    m = fk.delaunay_ball(600, seed=5)
+    g = np.array([0.7, -1.3, 0.4])
+    u = g @ m.p
+    Hf, H = orc.recover_field(m, u)
+    assert np.allclose(Hf, -g[:, None], atol=1e-10)
+    rp, ci, v = orc.stiffness(m, None)
+    interior = np.ones(m.nv, bool)
+    interior[np.unique(m.surfaceT[:3])] = False
+    Au = orc.spmv(rp, ci, v, u)
+    assert np.max(np.abs(Au[interior])) < 1e-9 * np.max(np.abs(v)) * np.max(np.abs(u))
+    assert np.max(np.abs(orc.spmv(rp, ci, v, np.ones(m.nv)))) < 1e-10 * np.max(np.abs(v))
+    _, _, mv = orc.mass(m)
+    assert abs(mv.sum() - m.VE.sum()) < 1e-10 * m.VE.sum()
+    Hb, _ = orc.recover_field(m, u, compat_bug=True)            # NewtonRaphson.jl:187-189
+    assert np.allclose(Hb[0], -g[0]) and np.allclose(Hb[1], -(g[1] + g[2])) and np.all(Hb[2] == 0)
+
+
+def test_tangential_oracle_definition():
+    m = fk.kuhn_cube(3)
+    rng = np.random.default_rng(2)
+    Hv = np.asfortranarray(rng.normal(size=(3, m.nt)))
+    dmu = rng.random(m.nt)
+    Ak = orc.local_tangential(m.p, m.t, m.VE, Hv, dmu)
+    k = 17
+    G = np.array([orc.abcd(m.p, m.t[:, k], m.t[i, k])[1:] for i in range(4)])
+    gh = G @ Hv[:, k]
+    ref = m.VE[k] * dmu[k] / np.linalg.norm(Hv[:, k]) * np.outer(gh, gh)
+    assert np.allclose(Ak[:, k].reshape(4, 4), ref, rtol=1e-12)
+
+
+def test_splev_matches_fitpack():
+    from scipy import interpolate
+
+    x = np.array([0.0, 20, 22.4, 30, 55, 80, 120, 200, 400, 900, 2000, 5000.0])
+    y = 1.0 / (1.0 + x / 300.0) + 0.2
+    tck = interpolate.splrep(x, y, k=3, s=0)
+    xs = np.linspace(-50, 6000, 777)
+    inside = (xs >= x[0]) & (xs <= x[-1])
+    assert np.allclose(orc.splev(tck[0], tck[1], 3, xs[inside], "error"), interpolate.splev(xs[inside], tck, ext=2), rtol=1e-13)
+    assert np.allclose(orc.splev(tck[0], tck[1], 3, xs, "nearest"), interpolate.splev(xs, tck, ext=3), rtol=1e-13)
+    assert np.allclose(orc.splev(tck[0], tck[1], 3, xs, "extrapolate"), interpolate.splev(xs, tck, ext=0), rtol=1e-12)
+    assert np.allclose(orc.splev(tck[0], tck[1], 3, xs, "zero"), interpolate.splev(xs, tck, ext=1), rtol=1e-13)
+    with pytest.raises(ValueError):
+        orc.splev(tck[0], tck[1], 3, xs, "error")
+
+
+def test_material_permeability_rules():
+    """magneticProperties.jl:157-188: mu = B/H with non-finite -> max; dmu central differences."""
+    H = np.array([0.0, 10.0, 20.0, 40.0, 80.0])
+    B = np.array([0.0, 0.5, 0.8, 1.0, 1.1])
+    mu, dmu, nu = orc.material_permeability(H, B)
+    assert mu[0] == np.max(B[1:] / H[1:]) and np.allclose(mu[1:], B[1:] / H[1:])
+    assert np.isclose(dmu[2], (mu[3] - mu[1]) / (H[3] - H[1])) and np.isclose(dmu[0], (mu[1] - mu[0]) / 10.0)
+    assert nu[0] == 0.0 and np.allclose(nu[1:], fk.mu0 * H[1:] / B[1:])
+    assert np.allclose(orc.gradient(H, B)[1:-1], (B[2:] - B[:-2]) / (H[2:] - H[:-2]))
