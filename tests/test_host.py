@@ -1,0 +1,141 @@
+"""CPU: the C-ABI library loads and exports every symbol include/femeko_cuda.h declares; the
+symbolic phase (pattern, element->nnz map, assembly gather plan, SpMV row blocks) is validated
+against the oracle by executing the plan in numpy; host spline fit/eval against scipy FITPACK.
+No compute calls that need a GPU."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+import femeko_jl_b200 as fk
+from conftest import ROOT, load_golden, rel_err_matrix, abs_sum_scale
+from femeko_jl_b200 import lib as L
+from oracle import oracle as orc
+from plan_emulator import export_symbolic, run_plan
+
+
+def test_library_exports_every_declared_symbol():
+    hdr = open(os.path.join(ROOT, "include", "femeko_cuda.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    declared = set(re.findall(r"\b(fk_[a-z0-9_]+|scalarPotential)\s*\(", hdr))
+    assert len(declared) > 40
+    lib = C.CDLL(L.LIB_PATH)
+    missing = [n for n in sorted(declared) if not hasattr(lib, n)]
+    assert not missing, f"declared in the header but not exported: {missing}"
+    # and the Python binding covers the same set
+    assert declared == set(L._SIGS), (declared ^ set(L._SIGS))
+    assert L.load().fk_version() >= 100
+
+
+def test_create_without_gpu_fails_loudly():
+    import torch
+
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    m = fk.kuhn_cube(2)
+    with pytest.raises(L.FemekoError, match="no CUDA device"):
+        fk.Femeko(m)
+
+
+@pytest.mark.parametrize("name", ["kuhn3", "kuhn6", "delaunay300"])
+@pytest.mark.parametrize("opts", [{}, {"natural_order": 1}, {"tile_max_elems": 128, "tile_max_rows": 16}])
+def test_symbolic_pattern_map_and_plan_against_reference(name, opts):
+    m, g = load_golden(name)
+    plan = export_symbolic(m, **opts)
+    # CSR pattern bit-exact with the reference's Eigen pattern (CSC == CSR by symmetry)
+    assert np.array_equal(plan["rowptr"], g["csc_outer"]) and np.array_equal(plan["colind"], g["csc_inner"])
+    rp, ci = plan["rowptr"], plan["colind"]
+    e2n = plan["e2nnz"]
+    assert np.array_equal(e2n, orc.elem2nnz(m.t, rp, ci))
+    # the map really addresses (t[i,k], t[j,k])
+    rows = np.repeat(np.arange(m.nv), np.diff(rp))
+    for i in range(4):
+        for j in range(4):
+            idx = e2n[4 * i + j::16]
+            assert np.array_equal(rows[idx], m.t[i]) and np.array_equal(ci[idx], m.t[j])
+    assert np.array_equal(ci[plan["diag"]], np.arange(m.nv))
+    # executing the gather plan on the REFERENCE's local matrices reproduces the reference's matrix
+    vals, written = run_plan(plan, g["Ak"] * g["mu"][None, :])
+    assert np.all(written == 1)
+    assert rel_err_matrix(vals, g["csc_values_mu"], abs_sum_scale(m, g["Ak"], g["mu"])) < 1e-14
+    # every element owned by exactly one tile; every (k,i,j) contribution listed exactly once
+    assert int((plan["tile_elems"] >> 31).sum()) == m.nt
+    assert plan["tile_ents"].size == 16 * m.nt
+    # SpMV blocks cover the rows contiguously
+    assert plan["blk_row"][0] == 0 and plan["blk_row"][-1] == m.nv and np.all(np.diff(plan["blk_row"]) > 0)
+
+
+def test_symbolic_owned_rows_only():
+    """Multi-GPU partitions: only rows < n_owned get a pattern; halo rows are empty."""
+    m = fk.kuhn_cube(4)
+    n_owned = 60
+    plan = export_symbolic(m, n_owned=n_owned)
+    full = export_symbolic(m)
+    assert np.array_equal(plan["rowptr"][:n_owned + 1], full["rowptr"][:n_owned + 1])
+    assert np.all(plan["rowptr"][n_owned:] == plan["rowptr"][n_owned])
+    assert np.array_equal(plan["colind"], full["colind"][:plan["nnz"]])
+    Ak = orc.local_stiffness(m.p, m.t, m.VE, None)
+    v, w = run_plan(plan, Ak)
+    vf, _ = run_plan(full, Ak)
+    assert np.all(w == 1) and np.allclose(v, vf[:plan["nnz"]], rtol=0, atol=1e-15)
+    rows_of = np.repeat(np.arange(m.nv), np.diff(full["rowptr"]))
+    e = plan["e2nnz"].reshape(m.nt, 4, 4)
+    halo = m.t.T >= n_owned
+    assert np.all(e[halo] == -1) and np.all(e[~halo] >= 0)
+
+
+def test_symbolic_rejects_bad_input():
+    m = fk.kuhn_cube(2)
+    bad = m.t.copy()
+    bad[0, 0] = m.nv
+    m2 = fk.MESH(p=m.p, t=bad, nv=m.nv, nt=m.nt)
+    with pytest.raises(L.FemekoError, match="out of range"):
+        export_symbolic(m2)
+    with pytest.raises(L.FemekoError, match="more than one assembly tile"):
+        export_symbolic(m, tile_max_elems=4)
+
+
+def test_spline1d_matches_fitpack():
+    from scipy import interpolate
+
+    H = np.concatenate([[0.0], np.geomspace(20, 5e5, 60)])
+    mu = fk.mu0 * (1 + 700.0 / (1 + (H / 4000.0) ** 1.2))
+    spl = fk.Spline1D(H, mu, bc="nearest")
+    tck = interpolate.splrep(H, mu, k=3, s=0)
+    assert np.array_equal(spl.t, tck[0])                                      # FITPACK's knot choice
+    assert np.allclose(spl.c, tck[1], rtol=1e-9, atol=1e-12 * np.abs(tck[1]).max())
+    xs = np.concatenate([H, np.linspace(-10, 6e5, 2001)])
+    ref = interpolate.splev(xs, tck, ext=3)
+    assert np.allclose(spl(xs), ref, rtol=1e-10)
+    assert np.allclose(spl(H), mu, rtol=1e-12)                                # interpolates the table
+    with pytest.raises(L.FemekoError, match="outside the knot range"):
+        fk.Spline1D(H, mu, bc="error")(np.array([6e5]))
+    assert np.allclose(fk.Spline1D(H, mu, bc="error")(H[3:9]), mu[3:9], rtol=1e-12)
+    with pytest.raises(L.FemekoError):
+        fk.Spline1D(H[::-1].copy(), mu)
+
+
+def test_material_permeability_matches_oracle():
+    H = np.concatenate([[0.0], np.geomspace(5, 1e5, 40)])
+    B = 1.6 * np.tanh(H / 800.0) + fk.mu0 * H
+    d = fk.DATA()
+    d.HofM, d.B = H.copy(), B.copy()
+    fk.materialPermeability(d)
+    mu, dmu, nu = orc.material_permeability(H, B)
+    assert np.array_equal(d.mu, mu) and np.array_equal(d.dmu, dmu) and np.array_equal(d.nu, nu)
+    assert np.array_equal(fk.gradient(H, B), orc.gradient(H, B))
+
+
+def test_mesh_generators_geometry():
+    m = fk.kuhn_cube(5)
+    assert m.nt == 6 * 125 and m.nv == 216 and m.ns == 12 * 25
+    assert np.isclose(m.VE.sum(), 1.0) and np.isclose(m.AE.sum(), 6.0) and np.all(m.VE > 0)
+    # outward unit normals
+    c = (m.p[:, m.surfaceT[0]] + m.p[:, m.surfaceT[1]] + m.p[:, m.surfaceT[2]]) / 3
+    assert np.all((m.normal * c).sum(0) > 0) and np.allclose(np.linalg.norm(m.normal, axis=0), 1)
+    d = fk.delaunay_ball(500, seed=2)
+    assert np.all(d.VE > 0) and d.nInside > 0 and len(np.unique(d.t)) == d.nv
+    F = np.array([0.3, -0.2, 0.9])          # closed boundary: the Neumann load sums to zero
+    assert abs(orc.boundary_integral(d, F, [0]).sum()) < 1e-9 * d.AE.sum()
