@@ -249,6 +249,34 @@ class Femeko:
         return div.value
 
 
+
+    # -- device-pointer forms (zero-copy: torch tensors' data_ptr(), or fk_device_ptr arrays) ----
+    def assemble_stiffness_dev(self, f_ptr: int | None, slot=0):
+        L.check(self.lib.fk_assemble_stiffness_dev(self.h, slot, C.c_void_p(f_ptr)))
+
+    def assemble_mass_dev(self, rho_ptr: int | None = None, slot=1):
+        L.check(self.lib.fk_assemble_mass_dev(self.h, slot, C.c_void_p(rho_ptr)))
+
+    def spmv_dev(self, x_ptr: int, y_ptr: int, slot=0):
+        L.check(self.lib.fk_spmv_dev(self.h, slot, C.c_void_p(x_ptr), C.c_void_p(y_ptr)))
+
+    def pcg_dev(self, b_ptr: int, x_ptr: int, slot=0, **kw):
+        o = self.pcg_opts(**kw)
+        it, rr = C.c_int(), C.c_double()
+        L.check(self.lib.fk_pcg_dev(self.h, slot, C.c_void_p(b_ptr), C.c_void_p(x_ptr), C.byref(o), C.byref(it), C.byref(rr)))
+        return it.value, rr.value
+
+    def recover_field_dev(self, u_ptr: int, mu_ptr: int | None, Hfield_ptr: int | None, Hn_ptr: int | None,
+                          B_ptr: int | None, compat_bug=False):
+        L.check(self.lib.fk_recover_field_dev(self.h, C.c_void_p(u_ptr), C.c_void_p(mu_ptr), int(compat_bug),
+                                              C.c_void_p(Hfield_ptr), C.c_void_p(Hn_ptr), C.c_void_p(B_ptr)))
+
+    def picard_step_dev(self, u_ptr: int, slot=0, compat_bug=False):
+        div = C.c_double()
+        L.check(self.lib.fk_picard_step_dev(self.h, slot, C.c_void_p(u_ptr), int(compat_bug), C.byref(div)))
+        return div.value
+
+
 class SparseCSR:
     """Assembled matrix on the canonical pattern; keeps its handle + slot so solves stay on the GPU."""
 

@@ -100,17 +100,20 @@ def _finish(mesh: MESH, inside_mask: np.ndarray) -> MESH:
     return mesh
 
 
-def kuhn_cells(N: int, i0: int = 0, i1: int | None = None, stride: tuple | None = None) -> np.ndarray:
-    """Connectivity (4 x 6*ncells, int32, F-order) of the Kuhn subdivision of cells with x-index in
-    [i0, i1).  Node id of lattice point (i, j, k) is ``(i*(N+1) + j)*(N+1) + k`` unless `stride`
-    (si, sj, sk) overrides it.  The six tets of a cell are the six monotone lattice paths from
-    corner (i,j,k) to (i+1,j+1,k+1), one per permutation of the axis order."""
+def kuhn_cells(N: int, i0: int = 0, i1: int | None = None, stride: tuple | None = None, Ny: int | None = None,
+               Nz: int | None = None) -> np.ndarray:
+    """Connectivity (4 x 6*ncells, int32, F-order) of the Kuhn subdivision of the cells with x-index
+    in [i0, i1) of a lattice with N x Ny x Nz cells (Ny, Nz default to N).  Node id of lattice point
+    (i, j, k) is ``(i*(Ny+1) + j)*(Nz+1) + k`` unless `stride` (si, sj, sk) overrides it.  The six
+    tets of a cell are the six monotone lattice paths from corner (i,j,k) to (i+1,j+1,k+1), one per
+    permutation of the axis order."""
     if i1 is None:
         i1 = N
-    n1 = N + 1
-    si, sj, sk = stride if stride is not None else (n1 * n1, n1, 1)
-    ii, jj, kk = np.meshgrid(np.arange(i0, i1, dtype=np.int64), np.arange(N, dtype=np.int64),
-                             np.arange(N, dtype=np.int64), indexing="ij")
+    Ny = N if Ny is None else Ny
+    Nz = N if Nz is None else Nz
+    si, sj, sk = stride if stride is not None else ((Ny + 1) * (Nz + 1), Nz + 1, 1)
+    ii, jj, kk = np.meshgrid(np.arange(i0, i1, dtype=np.int64), np.arange(Ny, dtype=np.int64),
+                             np.arange(Nz, dtype=np.int64), indexing="ij")
     base = (ii * si + jj * sj + kk * sk).ravel()
     steps = (si, sj, sk)
     ncell = base.size
@@ -124,30 +127,42 @@ def kuhn_cells(N: int, i0: int = 0, i1: int | None = None, stride: tuple | None 
     return np.asfortranarray(t.reshape(ncell * 6, 4).T)
 
 
-def _cube_surface(N: int, single_id: bool) -> np.ndarray:
-    """Boundary triangles of the Kuhn cube: every cube-face lattice square is cut along the diagonal
-    from its low corner to its high corner (the trace of the Kuhn subdivision)."""
-    n1 = N + 1
-    a, b = np.meshgrid(np.arange(N, dtype=np.int64), np.arange(N, dtype=np.int64), indexing="ij")
-    a = a.ravel()
-    b = b.ravel()
+def _box_surface(dims, single_id: bool, x_range=None, faces=(0, 1, 2, 3, 4, 5)) -> np.ndarray:
+    """Boundary triangles (global lattice ids) of the Kuhn box with dims = (Nx, Ny, Nz) cells: every
+    face lattice square is cut along the diagonal from its low corner to its high corner (the trace
+    of the Kuhn subdivision).  `x_range` = (c0, c1) restricts the y/z faces to cells c0 <= i < c1;
+    `faces` selects which of the six faces (-x, +x, -y, +y, -z, +z) to emit."""
+    n = [d + 1 for d in dims]
     out = []
     sid = 0
     for axis in range(3):
-        for side in (0, N):
-            def nid(u, v):
-                idx = [None, None, None]
-                idx[axis] = np.full_like(u, side)
-                o = [d for d in range(3) if d != axis]
-                idx[o[0]] = u
-                idx[o[1]] = v
-                return (idx[0] * n1 + idx[1]) * n1 + idx[2]
-            c00, c10, c01, c11 = nid(a, b), nid(a + 1, b), nid(a, b + 1), nid(a + 1, b + 1)
-            ident = np.full_like(c00, 0 if single_id else sid)
-            out.append(np.stack([c00, c10, c11, ident]))
-            out.append(np.stack([c00, c11, c01, ident]))
+        o = [d for d in range(3) if d != axis]
+        r0 = (0, dims[o[0]])
+        if x_range is not None and o[0] == 0:
+            r0 = x_range
+        a, b = np.meshgrid(np.arange(r0[0], r0[1], dtype=np.int64), np.arange(dims[o[1]], dtype=np.int64), indexing="ij")
+        a = a.ravel()
+        b = b.ravel()
+        for side in (0, dims[axis]):
+            if sid in faces:
+                def nid(u, v):
+                    idx = [None, None, None]
+                    idx[axis] = np.full_like(u, side)
+                    idx[o[0]] = u
+                    idx[o[1]] = v
+                    return (idx[0] * n[1] + idx[1]) * n[2] + idx[2]
+                c00, c10, c01, c11 = nid(a, b), nid(a + 1, b), nid(a, b + 1), nid(a + 1, b + 1)
+                ident = np.full_like(c00, 0 if single_id else sid)
+                out.append(np.stack([c00, c10, c11, ident]))
+                out.append(np.stack([c00, c11, c01, ident]))
             sid += 1
+    if not out:
+        return np.zeros((4, 0), dtype=np.int64)
     return np.concatenate(out, axis=1)
+
+
+def _cube_surface(N: int, single_id: bool) -> np.ndarray:
+    return _box_surface((N, N, N), single_id)
 
 
 def _orient_outward(p: np.ndarray, surfaceT: np.ndarray, centre: np.ndarray) -> np.ndarray:
@@ -183,6 +198,36 @@ def kuhn_cube(N: int, L: float = 1.0, inside_edge: float = 0.2, inside_box=None,
     half = np.asarray(inside_box if inside_box is not None else [0.5 * inside_edge * L] * 3)
     inside = np.all(np.abs(cen) <= half[:, None], axis=0)
     return _finish(mesh, inside)
+
+
+def kuhn_box(dims, h: float | None = None, inside_edge: float = 0.2, single_shell_id: bool = True) -> MESH:
+    """Box of dims = (Nx, Ny, Nz) Kuhn cells of edge h (default 1/Ny), centred at the origin: the
+    multi-GPU benchmark domain is `world` unit cubes side by side along x.  Inside region: in every
+    unit-cube period along x, the elements whose centroid lies in the centred cube of edge
+    `inside_edge` (one "magnet" per period, so partitions carry equal nonlinear work)."""
+    Nx, Ny, Nz = (int(d) for d in dims)
+    h = 1.0 / Ny if h is None else h
+    gx = (np.arange(Nx + 1, dtype=np.float64) - Nx / 2.0) * h
+    gy = (np.arange(Ny + 1, dtype=np.float64) - Ny / 2.0) * h
+    gz = (np.arange(Nz + 1, dtype=np.float64) - Nz / 2.0) * h
+    X, Y, Z = np.meshgrid(gx, gy, gz, indexing="ij")
+    mesh = MESH()
+    mesh.p = np.asfortranarray(np.stack([X.ravel(), Y.ravel(), Z.ravel()]))
+    mesh.t = kuhn_cells(Nx, Ny=Ny, Nz=Nz)
+    s = _box_surface((Nx, Ny, Nz), single_shell_id)
+    s = _orient_outward(mesh.p, s, np.zeros(3))
+    mesh.surfaceT = np.asfortranarray(s.astype(np.int32))
+    mesh.shell_id = [0] if single_shell_id else list(range(6))
+    cen = (mesh.p[:, mesh.t[0]] + mesh.p[:, mesh.t[1]] + mesh.p[:, mesh.t[2]] + mesh.p[:, mesh.t[3]]) / 4
+    return _finish(mesh, box_inside_mask(cen, Nx * h, Ny * h, inside_edge))
+
+
+def box_inside_mask(cen: np.ndarray, Lx: float, Ly: float, inside_edge: float) -> np.ndarray:
+    """Periodic magnets along x: period Ly (one per unit cube), centred cube of edge inside_edge*Ly."""
+    xs = cen[0] + Lx / 2.0
+    xr = xs - np.floor(xs / Ly) * Ly - Ly / 2.0
+    half = 0.5 * inside_edge * Ly
+    return (np.abs(xr) <= half) & (np.abs(cen[1]) <= half) & (np.abs(cen[2]) <= half)
 
 
 def delaunay_ball(npts: int = 4000, seed: int = 1234, R: float = 5.0, inside_half: float = 0.5,
