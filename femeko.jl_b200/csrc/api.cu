@@ -50,7 +50,7 @@ static inline int cdiv(long long a, int b) { return (int)((a + b - 1) / b); }
 
 static double* slot_vals(fk_handle h, int slot) {
   check_slot(slot);
-  h->vals[slot].ensure((size_t)h->nnz);
+  h->vals[slot].ensure((size_t)h->nnz + kSlack);
   return h->vals[slot].ptr;
 }
 
@@ -59,26 +59,45 @@ static double* slot_vals(fk_handle h, int slot) {
 // ------------------------------------------------------------------------------------------------
 static AsmArgs base_args(fk_handle h, double* vals) {
   AsmArgs a{};
-  a.p4 = h->p4.ptr;
-  a.t4 = h->t4.ptr;
   a.VE = h->user_ve ? h->VE.ptr : nullptr;
-  a.tile_elem_ptr = h->tile_elem_ptr.ptr;
-  a.tile_elems = h->tile_elems.ptr;
-  a.tile_nnz_ptr = h->tile_nnz_ptr.ptr;
-  a.tile_gidx = h->tile_gidx.ptr;
-  a.tile_coff = h->tile_coff.ptr;
-  a.tile_ent_ptr = h->tile_ent_ptr.ptr;
-  a.tile_ents = h->tile_ents.ptr;
+  a.tile_hdr = reinterpret_cast<const int4*>(h->tile_hdr.ptr);
+  a.tile_blob = reinterpret_cast<const uint4*>(h->tile_blob.ptr);
+  a.ntiles = h->sym.ntiles;
   a.vals = vals;
   a.e_pad = h->e_pad;
+  a.nno_max = h->sym.max_tile_nodes;
+  a.blob_a_max = h->sym.max_blob_a;
+  a.blob_b_max = h->sym.max_blob_b;
   a.spl = h->spl;
   return a;
 }
 
+// launch configurations of the assembly kernel: {threads per CTA, min resident CTAs per SM}
+constexpr int kNumAsmCfg = 6;
+template <int MODE, int THREADS, int MINB>
+static void launch_assemble_cfg(fk_handle h, const AsmArgs& a, bool setup) {
+  if (setup) {  // persistent grid: every resident CTA slot of the device, fixed per configuration
+    FK_CUDA(cudaFuncSetAttribute(assemble_kernel<MODE, THREADS, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->asm_smem));
+    int occ = 1;
+    FK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, assemble_kernel<MODE, THREADS, MINB>, THREADS, h->asm_smem));
+    h->asm_grid[MODE] = std::max(1, std::min(h->sym.ntiles, h->num_sms * std::max(1, occ)));
+    return;
+  }
+  assemble_kernel<MODE, THREADS, MINB><<<h->asm_grid[MODE], THREADS, h->asm_smem, h->stream>>>(a);
+}
 template <int MODE>
-static void launch_assemble(fk_handle h, const AsmArgs& a) {
+static void launch_assemble(fk_handle h, const AsmArgs& a, bool setup = false) {
   if (h->sym.ntiles == 0) return;
-  assemble_kernel<MODE><<<h->sym.ntiles, kAsmThreads, h->asm_smem, h->stream>>>(a);
+  // 0 = measured default: the fused Picard sweep needs > 80 registers (2 CTAs/SM), the others fit 3 CTAs/SM
+  const int cfg = h->asm_cfg > 0 ? h->asm_cfg : (MODE == ASM_PICARD ? 2 : 1);
+  switch (cfg) {
+    case 2: launch_assemble_cfg<MODE, 256, 2>(h, a, setup); break;
+    case 3: launch_assemble_cfg<MODE, 384, 2>(h, a, setup); break;
+    case 4: launch_assemble_cfg<MODE, 512, 2>(h, a, setup); break;
+    case 5: launch_assemble_cfg<MODE, 128, 6>(h, a, setup); break;
+    default: launch_assemble_cfg<MODE, 256, 3>(h, a, setup); break;
+  }
+  if (setup) return;
   FK_CUDA(cudaGetLastError());
   h->launches++;
 }
@@ -123,18 +142,51 @@ static void ensure_state(fk_handle h) {
 // ------------------------------------------------------------------------------------------------
 // SpMV / PCG launchers
 // ------------------------------------------------------------------------------------------------
-static void launch_spmv(fk_handle h, cudaStream_t s, const double* vals, const double* x, double* y, bool dot,
-                        const PcgCtl* ctl, int j) {
+void launch_spmv(fk_handle h, cudaStream_t s, const double* vals, const double* x, double* y, bool dot, const PcgCtl* ctl,
+                 int j) {
   const int nblk = (int)h->sym.blk_row.size() - 1;
   if (nblk <= 0) return;
-  const size_t smem = (size_t)h->spmv_cap * sizeof(double);
-  if (dot)
-    spmv_kernel<true><<<h->grid_spmv, kSpmvThreads, smem, s>>>(h->rowptr.ptr, h->colind.ptr, vals, x, y, h->blk_row.ptr, nblk,
-                                                               h->spmv_cap, h->part.ptr, ctl, j);
-  else
-    spmv_kernel<false><<<h->grid_spmv, kSpmvThreads, smem, s>>>(h->rowptr.ptr, h->colind.ptr, vals, x, y, h->blk_row.ptr, nblk,
-                                                                h->spmv_cap, nullptr, ctl, j);
+  if (h->spmv_variant == 1) {
+    SpmvTmaArgs a{h->rowptr.ptr, h->colind.ptr, vals, x, y, reinterpret_cast<const int4*>(h->blk_info.ptr), nblk, h->spmv_cap,
+                  h->spmv_rows_cap, h->spmv_stages, dot ? h->part.ptr : nullptr, ctl, j};
+    if (dot) spmv_tma_kernel<true><<<h->grid_spmv, kSpmvThreads, h->spmv_smem, s>>>(a);
+    else spmv_tma_kernel<false><<<h->grid_spmv, kSpmvThreads, h->spmv_smem, s>>>(a);
+  } else {
+    if (dot)
+      spmv_kernel<true><<<h->grid_spmv, kSpmvThreads, h->spmv_smem, s>>>(h->rowptr.ptr, h->colind.ptr, vals, x, y, h->blk_row.ptr,
+                                                                         nblk, h->spmv_cap, h->part.ptr, ctl, j);
+    else
+      spmv_kernel<false><<<h->grid_spmv, kSpmvThreads, h->spmv_smem, s>>>(h->rowptr.ptr, h->colind.ptr, vals, x, y, h->blk_row.ptr,
+                                                                          nblk, h->spmv_cap, nullptr, ctl, j);
+  }
   FK_CUDA(cudaGetLastError());
+}
+
+// launch geometry of the persistent SpMV: full residency, fixed per configuration (deterministic p.Ap)
+static void configure_spmv(fk_handle h, int variant, int stages) {
+  cudaDeviceProp prop;
+  FK_CUDA(cudaGetDeviceProperties(&prop, h->device));
+  h->spmv_variant = (variant == 2) ? 0 : 1;   // option value 0/1 = TMA-staged (default), 2 = warp-loaded
+  h->spmv_stages = std::min(8, std::max(2, stages > 0 ? stages : 3));
+  int occ = 1;
+  if (h->spmv_variant == 1) {
+    h->spmv_smem = (size_t)h->spmv_stages * spmv_stage_bytes(h->spmv_cap, h->spmv_rows_cap);
+    need(h->spmv_smem <= (size_t)prop.sharedMemPerBlockOptin, "fk: SpMV stages do not fit in shared memory");
+    FK_CUDA(cudaFuncSetAttribute(spmv_tma_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->spmv_smem));
+    FK_CUDA(cudaFuncSetAttribute(spmv_tma_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->spmv_smem));
+    FK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, spmv_tma_kernel<true>, kSpmvThreads, h->spmv_smem));
+  } else {
+    h->spmv_smem = (size_t)h->spmv_cap * sizeof(double);
+    FK_CUDA(cudaFuncSetAttribute(spmv_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->spmv_smem));
+    FK_CUDA(cudaFuncSetAttribute(spmv_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->spmv_smem));
+    FK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, spmv_kernel<true>, kSpmvThreads, h->spmv_smem));
+  }
+  occ = std::max(1, occ);
+  const int nblk = (int)h->sym.blk_row.size() - 1;
+  h->grid_spmv = std::max(1, std::min(nblk, h->num_sms * occ));
+  for (int s = 0; s < FK_NUM_SLOTS; s++)
+    if (h->graph[s]) { cudaGraphExecDestroy(h->graph[s]); h->graph[s] = nullptr; }
+  if (h->part.ptr) h->part.ensure((size_t)4 * std::max(h->grid_spmv, h->grid_vec) + 16);
 }
 
 static void ensure_pcg(fk_handle h) {
@@ -370,41 +422,36 @@ int fk_create(const double* p, const int* t, int nv, int nt, const double* VE, c
     } else {
       volumes_kernel<<<cdiv(nt, 256), 256, 0, s>>>(h->p4.ptr, h->t4.ptr, nt, h->VE.ptr);
     }
+    h->rowptr.ensure(S.rowptr.size() + kSlack);
     h->rowptr.upload(S.rowptr, s);
+    h->colind.ensure(S.colind.size() + kSlack);
     h->colind.upload(S.colind, s);
+    h->blk_info.upload(S.blk_info, s);
     h->diag.upload(S.diag, s);
     h->blk_row.upload(S.blk_row, s);
-    h->tile_gidx.upload(S.tile_gidx, s);
-    h->tile_elems.upload(S.tile_elems, s);
-    h->tile_coff.upload(S.tile_coff, s);
-    h->tile_ents.upload(S.tile_ents, s);
-    {
-      std::vector<long long> a(S.tile_elem_ptr.begin(), S.tile_elem_ptr.end()), b(S.tile_nnz_ptr.begin(), S.tile_nnz_ptr.end()),
-          c(S.tile_ent_ptr.begin(), S.tile_ent_ptr.end());
-      h->tile_elem_ptr.upload(a, s);
-      h->tile_nnz_ptr.upload(b, s);
-      h->tile_ent_ptr.upload(c, s);
-      FK_CUDA(cudaStreamSynchronize(s));
-    }
-    h->e_pad = (S.max_tile_elems + 31) & ~31;
-    h->asm_smem = (size_t)10 * h->e_pad * sizeof(double);
+    h->tile_hdr.upload(S.tile_hdr, s);
+    h->tile_blob.upload(S.tile_blob, s);
+    FK_CUDA(cudaStreamSynchronize(s));
+    // the device only needs the packed blobs; drop the host copies of the unpacked plan
+    h->sym.tile_blob = std::vector<uint32_t>();
+    h->e_pad = (S.max_tile_elems + 15) & ~15;
+    h->asm_smem = asm_smem_bytes(h->e_pad, S.max_tile_nodes, S.max_blob_a, S.max_blob_b);
     need(h->asm_smem <= (size_t)prop.sharedMemPerBlockOptin, "fk_create: assembly tile does not fit in shared memory");
-    FK_CUDA(cudaFuncSetAttribute(assemble_kernel<ASM_STIFF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->asm_smem));
-    FK_CUDA(cudaFuncSetAttribute(assemble_kernel<ASM_MASS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->asm_smem));
-    FK_CUDA(cudaFuncSetAttribute(assemble_kernel<ASM_TANGENT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->asm_smem));
-    FK_CUDA(cudaFuncSetAttribute(assemble_kernel<ASM_PICARD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->asm_smem));
-    FK_CUDA(cudaFuncSetAttribute(assemble_kernel<ASM_LAGRANGE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->asm_smem));
+    need(o.asm_cfg >= 0 && o.asm_cfg < kNumAsmCfg, "fk_create: asm_cfg out of range");
+    h->asm_cfg = o.asm_cfg;
+    {
+      AsmArgs dummy{};
+      launch_assemble<ASM_STIFF>(h.get(), dummy, true);
+      launch_assemble<ASM_MASS>(h.get(), dummy, true);
+      launch_assemble<ASM_TANGENT>(h.get(), dummy, true);
+      launch_assemble<ASM_PICARD>(h.get(), dummy, true);
+      launch_assemble<ASM_LAGRANGE>(h.get(), dummy, true);
+    }
 
     // launch geometry of the persistent SpMV / vector kernels: full residency, fixed for determinism
     h->spmv_cap = std::max(32, std::min(S.max_blk_nnz, std::max(so.spmv_block_nnz, 2048)));
-    const size_t smem = (size_t)h->spmv_cap * sizeof(double);
-    FK_CUDA(cudaFuncSetAttribute(spmv_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    FK_CUDA(cudaFuncSetAttribute(spmv_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    int occ = 1;
-    FK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, spmv_kernel<true>, kSpmvThreads, smem));
-    occ = std::max(1, occ);
-    const int nblk = (int)S.blk_row.size() - 1;
-    h->grid_spmv = std::max(1, std::min(nblk, h->num_sms * occ));
+    h->spmv_rows_cap = std::max(1, S.max_blk_rows);
+    configure_spmv(h.get(), o.spmv_variant, o.spmv_stages);
     h->grid_vec = std::max(1, std::min(cdiv(std::max(1, h->n_rows), kVecThreads), h->num_sms * 8));
     FK_CUDA(cudaStreamSynchronize(s));
     h->st_a.release();
@@ -433,6 +480,31 @@ int fk_set_stream(fk_handle h, void* stream) {
   return guard([&]() {
     need(h, "fk: NULL handle");
     h->stream = (cudaStream_t)stream;
+    return 0;
+  });
+}
+
+int fk_tune(fk_handle h, int what, int value) {
+  return guard([&]() {
+    need(h, "fk: NULL handle");
+    DeviceGuard dg(h->device);
+    FK_CUDA(cudaStreamSynchronize(h->stream));
+    switch (what) {
+      case 0: {
+        need(value >= 0 && value < kNumAsmCfg, "fk_tune: asm_cfg out of range");
+        h->asm_cfg = value;
+        AsmArgs dummy{};
+        launch_assemble<ASM_STIFF>(h, dummy, true);
+        launch_assemble<ASM_MASS>(h, dummy, true);
+        launch_assemble<ASM_TANGENT>(h, dummy, true);
+        launch_assemble<ASM_PICARD>(h, dummy, true);
+        launch_assemble<ASM_LAGRANGE>(h, dummy, true);
+        break;
+      }
+      case 1: configure_spmv(h, value, h->spmv_stages); break;
+      case 2: configure_spmv(h, h->spmv_variant == 1 ? 1 : 2, value); break;
+      default: throw std::runtime_error("fk_tune: unknown option");
+    }
     return 0;
   });
 }

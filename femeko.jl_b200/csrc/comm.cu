@@ -114,11 +114,8 @@ void comm_issue_iteration(fk_handle_s* h, cudaStream_t s, const double* vals, in
   double* part = h->part.ptr;
   double* scal = h->scal.ptr;
   const int gs = h->grid_spmv, gv = h->grid_vec;
-  const int nblk = (int)h->sym.blk_row.size() - 1;
   comm_halo_exchange(h, s, h->p.ptr);
-  const size_t smem = (size_t)h->spmv_cap * sizeof(double);
-  spmv_kernel<true><<<gs, kSpmvThreads, smem, s>>>(h->rowptr.ptr, h->colind.ptr, vals, h->p.ptr, h->Ap.ptr, h->blk_row.ptr, nblk,
-                                                   h->spmv_cap, part, ctl, j);
+  launch_spmv(h, s, vals, h->p.ptr, h->Ap.ptr, true, ctl, j);
   fold_partials_kernel<<<1, 256, 0, s>>>(part, gs, gs, 1, scal);
   comm_allreduce_sum(h, s, scal, 1);
   pcg_update_kernel<<<gv, kVecThreads, 0, s>>>(h->x.ptr, h->r.ptr, h->p.ptr, h->Ap.ptr, h->dinv.ptr, n, scal, 1, part + gs, ctl, j);

@@ -7,6 +7,9 @@
 struct fk_handle_s;
 
 namespace fk {
+struct PcgCtl;
+void launch_spmv(fk_handle_s* h, cudaStream_t s, const double* vals, const double* x, double* y, bool dot, const PcgCtl* ctl,
+                 int j);
 void comm_destroy(fk_handle_s* h);
 void comm_halo_exchange(fk_handle_s* h, cudaStream_t s, double* v);
 void comm_allreduce_sum(fk_handle_s* h, cudaStream_t s, double* v, int n);

@@ -48,6 +48,7 @@ struct DevBuf {
 };
 
 struct Comm;  // multi-GPU state (comm.cu)
+constexpr size_t kSlack = 8;  // elements of slack after vals / colind / rowptr (aligned bulk copies may over-read)
 
 }  // namespace fk
 
@@ -66,11 +67,11 @@ struct fk_handle_s {
   fk::DevBuf<int4> t4;
   fk::DevBuf<double> VE;
   // pattern + plans
-  fk::DevBuf<int> rowptr, colind, diag, blk_row, tile_gidx;
-  fk::DevBuf<long long> tile_elem_ptr, tile_nnz_ptr, tile_ent_ptr;
-  fk::DevBuf<uint32_t> tile_elems;
-  fk::DevBuf<uint16_t> tile_coff, tile_ents;
-  int e_pad = 0;
+  fk::DevBuf<int> rowptr, colind, diag, blk_row, blk_info;
+  fk::DevBuf<int> tile_hdr;            // int4 per tile
+  fk::DevBuf<uint32_t> tile_blob;      // packed per-tile plan blobs (symbolic.hpp)
+  int e_pad = 0, asm_cfg = 0;
+  int asm_grid[8] = {0, 0, 0, 0, 0, 0, 0, 0};  // persistent grid per assembly mode
   size_t asm_smem = 0;
   // matrices
   fk::DevBuf<double> vals[FK_NUM_SLOTS];
@@ -86,6 +87,9 @@ struct fk_handle_s {
   fk::DevBuf<fk::PcgCtl> ctl;
   fk::PcgCtl* ctl_host = nullptr;      // pinned
   int grid_spmv = 0, grid_vec = 0, spmv_cap = 0;
+  int spmv_variant = 1;                // 0: warp-loaded stream (spmv_kernel), 1: TMA-staged stream (spmv_tma_kernel)
+  int spmv_stages = 3, spmv_rows_cap = 0;
+  size_t spmv_smem = 0;
   cudaGraphExec_t graph[FK_NUM_SLOTS] = {nullptr, nullptr, nullptr, nullptr};
   int graph_chunk[FK_NUM_SLOTS] = {0, 0, 0, 0};
   // generic staging for the host-pointer API

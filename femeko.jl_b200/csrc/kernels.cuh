@@ -11,6 +11,7 @@
 #include <float.h>
 
 #include "../../include/femeko_cuda.h"
+#include "symbolic.hpp"
 
 namespace fk {
 
@@ -86,12 +87,9 @@ __device__ __forceinline__ void load_node(const double4* __restrict__ p4, int n,
   x = a.x; y = a.y; z = b.x;
 }
 
-__device__ __forceinline__ void tet_geometry(const double4* __restrict__ p4, const int4 nd, TetGeom& G) {
-  double x0, y0, z0, x1, y1, z1, x2, y2, z2, x3, y3, z3;
-  load_node(p4, nd.x, x0, y0, z0);
-  load_node(p4, nd.y, x1, y1, z1);
-  load_node(p4, nd.z, x2, y2, z2);
-  load_node(p4, nd.w, x3, y3, z3);
+__device__ __forceinline__ void tet_geometry_xyz(const double x0, const double y0, const double z0, const double x1, const double y1,
+                                                 const double z1, const double x2, const double y2, const double z2, const double x3,
+                                                 const double y3, const double z3, TetGeom& G) {
   const double ax = x1 - x0, ay = y1 - y0, az = z1 - z0;  // AB
   const double bx = x2 - x0, by = y2 - y0, bz = z2 - z0;  // AC
   const double cx = x3 - x0, cy = y3 - y0, cz = z3 - z0;  // AD
@@ -108,6 +106,15 @@ __device__ __forceinline__ void tet_geometry(const double4* __restrict__ p4, con
   G.g[0][1] = -(G.g[1][1] + G.g[2][1] + G.g[3][1]);
   G.g[0][2] = -(G.g[1][2] + G.g[2][2] + G.g[3][2]);
   G.vol = fabs(det) / 6.0;
+}
+
+__device__ __forceinline__ void tet_geometry(const double4* __restrict__ p4, const int4 nd, TetGeom& G) {
+  double x0, y0, z0, x1, y1, z1, x2, y2, z2, x3, y3, z3;
+  load_node(p4, nd.x, x0, y0, z0);
+  load_node(p4, nd.y, x1, y1, z1);
+  load_node(p4, nd.z, x2, y2, z2);
+  load_node(p4, nd.w, x3, y3, z3);
+  tet_geometry_xyz(x0, y0, z0, x1, y1, z1, x2, y2, z2, x3, y3, z3, G);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -156,155 +163,7 @@ __device__ __forceinline__ double splev_dev(const SplineDev& S, double x, int& e
   return sp;
 }
 
-// ------------------------------------------------------------------------------------------------
-// K1: tile-gather assembly.
-// One CTA per tile (symbolic.hpp).  Phase 1: one thread per staged element computes the 10 unique
-// entries of the symmetric 4x4 local matrix into shared memory (SoA: sym-major, conflict-free).
-// Phase 2: one thread per CSR entry owned by the tile sums its contributors (slot, pair) in
-// ascending element order and writes the value once.  No atomics, bitwise run-to-run reproducible.
-// ------------------------------------------------------------------------------------------------
-enum AsmMode { ASM_STIFF = 0, ASM_MASS = 1, ASM_TANGENT = 2, ASM_PICARD = 3, ASM_LAGRANGE = 4 };
-
-struct AsmArgs {
-  const double4* p4;
-  const int4* t4;
-  const double* VE;       // nullable: volume from the determinant
-  const double* coef;     // STIFF: f (nullable = 1) | MASS: rho (nullable) | TANGENT: dmu
-  const double* Hvec;     // TANGENT: 3 x nt
-  // PICARD
-  const double* u;
-  double* mu;             // in (linear elements) / out (material elements)
-  double* dmu;            // nullable
-  double* Hn;             // in: |H| old, out: |H| new
-  double* Hfield;         // nullable, 3 x nt
-  const unsigned char* matid;  // nullable = all linear
-  double* tile_max;       // per tile: max | |H| - |H|old | over owned material elements
-  int* errflag;
-  int compat;
-  SplineSet spl;
-  // plan
-  const long long* tile_elem_ptr;
-  const uint32_t* tile_elems;
-  const long long* tile_nnz_ptr;
-  const int* tile_gidx;
-  const uint16_t* tile_coff;
-  const long long* tile_ent_ptr;
-  const uint16_t* tile_ents;
-  double* vals;
-  int e_pad;  // staging stride (>= max tile elements)
-};
-
-template <int MODE>
-static __global__ void __launch_bounds__(kAsmThreads) assemble_kernel(const AsmArgs a) {
-  extern __shared__ double stage[];  // 10 x e_pad
-  __shared__ double red[33];
-  const int tile = blockIdx.x;
-  const long long e0 = a.tile_elem_ptr[tile];
-  const int ne = (int)(a.tile_elem_ptr[tile + 1] - e0);
-  const int EP = a.e_pad;
-  double dmax = 0.0;
-
-  for (int s = threadIdx.x; s < ne; s += kAsmThreads) {
-    const uint32_t raw = __ldg(a.tile_elems + e0 + s);
-    const int k = (int)(raw & 0x7fffffffu);
-    const bool owner = (raw >> 31) != 0;
-    const int4 nd = __ldg(a.t4 + k);
-    double m[10];
-    if (MODE == ASM_MASS || MODE == ASM_LAGRANGE) {
-      double v;
-      if (a.VE) v = __ldg(a.VE + k);
-      else { TetGeom G; tet_geometry(a.p4, nd, G); v = G.vol; }
-      if (MODE == ASM_MASS) {
-        if (a.coef) v = v * __ldg(a.coef + k);
-        const double d = v * ((1.0 / 20.0) * 2.0), o = v * ((1.0 / 20.0) * 1.0);
-        m[0] = d; m[1] = o; m[2] = o; m[3] = o; m[4] = d; m[5] = o; m[6] = o; m[7] = d; m[8] = o; m[9] = d;
-      } else {
-        const double d = v / 4.0;
-        m[0] = d; m[1] = 0; m[2] = 0; m[3] = 0; m[4] = d; m[5] = 0; m[6] = 0; m[7] = d; m[8] = 0; m[9] = d;
-      }
-    } else {
-      TetGeom G;
-      tet_geometry(a.p4, nd, G);
-      const double V = a.VE ? __ldg(a.VE + k) : G.vol;
-      if (MODE == ASM_TANGENT) {
-        const double hx = __ldg(a.Hvec + 3 * (size_t)k), hy = __ldg(a.Hvec + 3 * (size_t)k + 1),
-                     hz = __ldg(a.Hvec + 3 * (size_t)k + 2);
-        const double H = sqrt(hx * hx + hy * hy + hz * hz);
-        const double s0 = V * __ldg(a.coef + k) / H;
-        double gh[4];
-#pragma unroll
-        for (int i = 0; i < 4; i++) gh[i] = hx * G.g[i][0] + hy * G.g[i][1] + hz * G.g[i][2];
-        int q = 0;
-#pragma unroll
-        for (int i = 0; i < 4; i++)
-#pragma unroll
-          for (int j = i; j < 4; j++) m[q++] = s0 * gh[i] * gh[j];
-      } else {
-        double f;
-        if (MODE == ASM_PICARD) {
-          const double u0 = __ldg(a.u + nd.x), u1 = __ldg(a.u + nd.y), u2 = __ldg(a.u + nd.z), u3 = __ldg(a.u + nd.w);
-          double hx = -(u0 * G.g[0][0]) - u1 * G.g[1][0] - u2 * G.g[2][0] - u3 * G.g[3][0];
-          double hy = -(u0 * G.g[0][1]) - u1 * G.g[1][1] - u2 * G.g[2][1] - u3 * G.g[3][1];
-          double hz = -(u0 * G.g[0][2]) - u1 * G.g[1][2] - u2 * G.g[2][2] - u3 * G.g[3][2];
-          if (a.compat) { hy += hz; hz = 0.0; }  // NewtonRaphson.jl:187-189: d-term lands in row 2
-          const double Hn = sqrt(hx * hx + hy * hy + hz * hz);
-          const int mat = a.matid ? (int)__ldg(a.matid + k) : 0;
-          if (mat > 0) {
-            int err = 0;
-            f = splev_dev(a.spl.s[mat - 1], Hn, err);
-            double df = 0.0;
-            const SplineDev& D = a.spl.s[FK_MAX_SPLINES / 2 + mat - 1];
-            if (a.dmu && D.n > 0) df = splev_dev(D, Hn, err);
-            if (!(f == f) || fabs(f) > DBL_MAX || !(df == df) || fabs(df) > DBL_MAX) err |= 2;  // Nans/Infs in mu
-            if (err) atomicOr(a.errflag, err);
-            if (owner) {
-              dmax = fmax(dmax, fabs(Hn - a.Hn[k]));
-              a.mu[k] = f;
-              if (a.dmu) a.dmu[k] = df;
-            }
-          } else {
-            f = __ldg(a.mu + k);
-          }
-          if (owner) {
-            a.Hn[k] = Hn;
-            if (a.Hfield) { a.Hfield[3 * (size_t)k] = hx; a.Hfield[3 * (size_t)k + 1] = hy; a.Hfield[3 * (size_t)k + 2] = hz; }
-          }
-        } else {
-          f = a.coef ? __ldg(a.coef + k) : 1.0;
-        }
-        const double s0 = V * f;  // VE[k]*f[k]*( b b' + c c' + d d' ), src/FEM3D.jl:71
-        int q = 0;
-#pragma unroll
-        for (int i = 0; i < 4; i++)
-#pragma unroll
-          for (int j = i; j < 4; j++)
-            m[q++] = s0 * ((G.g[i][0] * G.g[j][0] + G.g[i][1] * G.g[j][1]) + G.g[i][2] * G.g[j][2]);
-      }
-    }
-#pragma unroll
-    for (int q = 0; q < 10; q++) stage[q * EP + s] = m[q];
-  }
-  __syncthreads();
-
-  const long long n0 = a.tile_nnz_ptr[tile];
-  const int nn = (int)(a.tile_nnz_ptr[tile + 1] - n0);
-  const uint16_t* __restrict__ coff = a.tile_coff + n0 + tile;
-  const uint16_t* __restrict__ ents = a.tile_ents + a.tile_ent_ptr[tile];
-  for (int q = threadIdx.x; q < nn; q += kAsmThreads) {
-    const int beg = __ldg(coff + q), end = __ldg(coff + q + 1);
-    double acc = 0.0;
-    for (int e = beg; e < end; e++) {
-      const uint32_t en = __ldg(ents + e);
-      acc += stage[(en & 15u) * EP + (en >> 4)];
-    }
-    a.vals[__ldg(a.tile_gidx + n0 + q)] = acc;
-  }
-
-  if (MODE == ASM_PICARD) {
-    dmax = block_max(dmax, red);
-    if (threadIdx.x == 0) a.tile_max[tile] = dmax;
-  }
-}
+#include "assemble.cuh"
 
 // dense 16 x nt local stiffness (localStiffnessMatrix, src/FEM3D.jl:59-76) -- API completeness
 static __global__ void local_stiffness_kernel(const double4* __restrict__ p4, const int4* __restrict__ t4,
@@ -410,6 +269,8 @@ static __global__ void __launch_bounds__(kSpmvThreads) spmv_kernel(const int* __
     if (threadIdx.x == 0) part[blockIdx.x] = acc;
   }
 }
+
+#include "spmv.cuh"
 
 // dinv = 1/diag(A), 1 where the diagonal is zero or missing (BasicPreconditioners.h:62-75)
 static __global__ void jacobi_kernel(const double* __restrict__ vals, const int* __restrict__ diag, int n, int identity,

@@ -6,6 +6,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstring>
 #include <numeric>
 #include <stdexcept>
 #include <string>
@@ -215,7 +216,7 @@ void build_symbolic(const double* p, const int* t, int nv, int nt, const Symboli
   {
     std::vector<int> rows;
     std::vector<uint32_t> elems;
-    std::vector<int> base, cnt;
+    std::vector<int> base, cnt, perm, newpos, fillp;
 #pragma omp for schedule(dynamic, 16)
     for (int tl = 0; tl < T; tl++) {
       rows.assign(order.begin() + tile_row_ptr[tl], order.begin() + tile_row_ptr[tl + 1]);
@@ -242,9 +243,6 @@ void build_symbolic(const double* p, const int* t, int nv, int nt, const Symboli
       int nloc = 0;
       base.resize(rows.size());
       for (size_t m = 0; m < rows.size(); m++) { base[m] = nloc; nloc += rowlen[rows[m]]; }
-      int* gidx = S.tile_gidx.data() + S.tile_nnz_ptr[tl];
-      for (size_t m = 0; m < rows.size(); m++)
-        for (int c = 0; c < rowlen[rows[m]]; c++) gidx[base[m] + c] = S.rowptr[rows[m]] + c;
       cnt.assign((size_t)nloc + 1, 0);
       for (size_t m = 0; m < rows.size(); m++) {
         int r = rows[m];
@@ -253,9 +251,20 @@ void build_symbolic(const double* p, const int* t, int nv, int nt, const Symboli
           for (int j = 0; j < 4; j++) cnt[base[m] + (S.e2nnz[(size_t)16 * k + 4 * i + j] - S.rowptr[r]) + 1]++;
         }
       }
+      // entries are issued longest contributor list first (stable), so the 32 entries a warp sums
+      // together have near-equal trip counts (diagonals ~ node degree, off-diagonals ~ edge degree)
+      perm.resize((size_t)nloc);
+      std::iota(perm.begin(), perm.end(), 0);
+      std::stable_sort(perm.begin(), perm.end(), [&](int a, int b) { return cnt[a + 1] > cnt[b + 1]; });
+      newpos.resize((size_t)nloc);
+      for (int q = 0; q < nloc; q++) newpos[perm[q]] = q;
+      int* gidx = S.tile_gidx.data() + S.tile_nnz_ptr[tl];
+      for (size_t m = 0; m < rows.size(); m++)
+        for (int c = 0; c < rowlen[rows[m]]; c++) gidx[newpos[base[m] + c]] = S.rowptr[rows[m]] + c;
       uint16_t* coff = S.tile_coff.data() + S.tile_nnz_ptr[tl] + tl;
-      for (int q = 0; q < nloc; q++) cnt[q + 1] += cnt[q];
-      for (int q = 0; q <= nloc; q++) coff[q] = (uint16_t)cnt[q];
+      fillp.assign((size_t)nloc + 1, 0);
+      for (int q = 0; q < nloc; q++) fillp[q + 1] = fillp[q] + cnt[perm[q] + 1];
+      for (int q = 0; q <= nloc; q++) coff[q] = (uint16_t)fillp[q];
       uint16_t* ents = S.tile_ents.data() + S.tile_ent_ptr[tl];
       for (size_t m = 0; m < rows.size(); m++) {
         int r = rows[m];
@@ -263,14 +272,95 @@ void build_symbolic(const double* p, const int* t, int nv, int nt, const Symboli
           uint32_t k = n2e[q] >> 2, i = n2e[q] & 3;
           uint32_t slot = (uint32_t)(std::lower_bound(elems.begin(), elems.end(), k) - elems.begin());
           for (int j = 0; j < 4; j++) {
-            int loc = base[m] + (S.e2nnz[(size_t)16 * k + 4 * i + j] - S.rowptr[r]);
-            ents[cnt[loc]++] = (uint16_t)((slot << 4) | (uint32_t)sym_index((int)i, j));
+            int loc = newpos[base[m] + (S.e2nnz[(size_t)16 * k + 4 * i + j] - S.rowptr[r])];
+            ents[fillp[loc]++] = (uint16_t)((slot << 4) | (uint32_t)sym_index((int)i, j));
           }
         }
       }
     }
   }
   if (bad) throw std::runtime_error("fk: internal error building assembly tiles");
+
+  // ---- packed device blobs (see symbolic.hpp) ---------------------------------------------------
+  {
+    // per tile: sorted unique nodes of the staged elements (local numbering of the tile)
+    std::vector<int64_t> node_ptr((size_t)T + 1, 0);
+    std::vector<int> tnodes;
+    {
+      std::vector<std::vector<int>> per((size_t)T);
+#pragma omp parallel for schedule(dynamic, 16)
+      for (int tl = 0; tl < T; tl++) {
+        std::vector<int>& v = per[tl];
+        const uint32_t* te = S.tile_elems.data() + S.tile_elem_ptr[tl];
+        v.reserve((size_t)4 * tile_nelem[tl]);
+        for (int q = 0; q < tile_nelem[tl]; q++) {
+          const int* e = t + 4 * (size_t)(te[q] & 0x7fffffffu);
+          v.push_back(e[0]); v.push_back(e[1]); v.push_back(e[2]); v.push_back(e[3]);
+        }
+        std::sort(v.begin(), v.end());
+        v.erase(std::unique(v.begin(), v.end()), v.end());
+      }
+      for (int tl = 0; tl < T; tl++) {
+        if (per[tl].size() > 65535) throw std::runtime_error("fk: an assembly tile touches more than 65535 nodes");
+        node_ptr[tl + 1] = node_ptr[tl] + (int64_t)per[tl].size();
+      }
+      tnodes.resize((size_t)node_ptr[T]);
+#pragma omp parallel for schedule(static)
+      for (int tl = 0; tl < T; tl++) std::copy(per[tl].begin(), per[tl].end(), tnodes.begin() + node_ptr[tl]);
+    }
+    S.tile_hdr.assign((size_t)4 * T, 0);
+    std::vector<int64_t> off((size_t)T + 1, 0);  // bytes
+    for (int tl = 0; tl < T; tl++) {
+      const int ne = tile_nelem[tl], nn = (int)(S.tile_nnz_ptr[tl + 1] - S.tile_nnz_ptr[tl]),
+                nents = (int)(S.tile_ent_ptr[tl + 1] - S.tile_ent_ptr[tl]), nno = (int)(node_ptr[tl + 1] - node_ptr[tl]);
+      const int a = blob_a_bytes(ne, nno), b = blob_b_bytes(nn, nents);
+      S.max_blob_a = std::max(S.max_blob_a, a);
+      S.max_blob_b = std::max(S.max_blob_b, b);
+      S.max_tile_nodes = std::max(S.max_tile_nodes, nno);
+      off[tl + 1] = off[tl] + a + b;
+      if (off[tl + 1] / 16 > 0x7fffffffLL) throw std::runtime_error("fk: assembly plan too large for one GPU; partition the mesh");
+      S.tile_hdr[4 * (size_t)tl] = (int)(off[tl] / 16);
+      S.tile_hdr[4 * (size_t)tl + 1] = a;
+      S.tile_hdr[4 * (size_t)tl + 2] = b;
+      S.tile_hdr[4 * (size_t)tl + 3] = 0;
+    }
+    S.tile_blob.assign((size_t)(off[T] / 4), 0u);
+#pragma omp parallel for schedule(static)
+    for (int tl = 0; tl < T; tl++) {
+      const int ne = tile_nelem[tl], nn = (int)(S.tile_nnz_ptr[tl + 1] - S.tile_nnz_ptr[tl]),
+                nents = (int)(S.tile_ent_ptr[tl + 1] - S.tile_ent_ptr[tl]), nno = (int)(node_ptr[tl + 1] - node_ptr[tl]);
+      unsigned char* dst = reinterpret_cast<unsigned char*>(S.tile_blob.data()) + off[tl];
+      const int* nodes = tnodes.data() + node_ptr[tl];
+      // section A: sizes, node coordinates (SoA), global node ids, element ids, local connectivity
+      {
+        int* hd = reinterpret_cast<int*>(dst);
+        hd[0] = ne; hd[1] = nno; hd[2] = nn; hd[3] = nents;
+        dst += 16;
+      }
+      for (int d = 0; d < 3; d++) {
+        double* c = reinterpret_cast<double*>(dst);
+        for (int i = 0; i < nno; i++) c[i] = p ? p[3 * (size_t)nodes[i] + d] : 0.0;
+        dst += pad16(8 * nno);
+      }
+      std::memcpy(dst, nodes, sizeof(int) * (size_t)nno);
+      dst += pad16(4 * nno);
+      const uint32_t* te = S.tile_elems.data() + S.tile_elem_ptr[tl];
+      std::memcpy(dst, te, sizeof(uint32_t) * (size_t)ne);
+      dst += pad16(4 * ne);
+      uint16_t* loc = reinterpret_cast<uint16_t*>(dst);
+      for (int q = 0; q < ne; q++) {
+        const int* e = t + 4 * (size_t)(te[q] & 0x7fffffffu);
+        for (int i = 0; i < 4; i++) loc[4 * q + i] = (uint16_t)(std::lower_bound(nodes, nodes + nno, e[i]) - nodes);
+      }
+      dst += pad16(8 * ne);
+      // section B: gather plan
+      std::memcpy(dst, S.tile_gidx.data() + S.tile_nnz_ptr[tl], sizeof(int) * (size_t)nn);
+      dst += pad16(4 * nn);
+      std::memcpy(dst, S.tile_coff.data() + S.tile_nnz_ptr[tl] + tl, sizeof(uint16_t) * ((size_t)nn + 1));
+      dst += pad16(2 * (nn + 1));
+      std::memcpy(dst, S.tile_ents.data() + S.tile_ent_ptr[tl], sizeof(uint16_t) * (size_t)nents);
+    }
+  }
 
   // ---- SpMV row blocks --------------------------------------------------------------------------
   S.blk_row.clear();
@@ -290,6 +380,16 @@ void build_symbolic(const double* p, const int* t, int nv, int nt, const Symboli
     }
     S.blk_row.push_back(nr);
     S.max_blk_nnz = std::max<int>(S.max_blk_nnz, (int)nnz_in);
+    const int nb = (int)S.blk_row.size() - 1;
+    S.blk_info.resize((size_t)4 * nb);
+    for (int b = 0; b < nb; b++) {
+      const int r0 = S.blk_row[b], r1 = S.blk_row[b + 1];
+      S.blk_info[4 * (size_t)b] = r0;
+      S.blk_info[4 * (size_t)b + 1] = r1;
+      S.blk_info[4 * (size_t)b + 2] = S.rowptr[r0];
+      S.blk_info[4 * (size_t)b + 3] = S.rowptr[r1];
+      S.max_blk_rows = std::max(S.max_blk_rows, r1 - r0);
+    }
   }
 }
 

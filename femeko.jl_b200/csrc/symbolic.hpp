@@ -11,7 +11,7 @@
 namespace fk {
 
 struct SymbolicOpts {
-  int tile_max_elems = 1024;  // elements staged per tile (<= 4096: 12-bit slot in a gather entry)
+  int tile_max_elems = 512;   // elements staged per tile (<= 4096: 12-bit slot in a gather entry)
   int tile_max_rows = 256;
   bool natural_order = false;
   int spmv_block_nnz = 2048;
@@ -40,13 +40,38 @@ struct Symbolic {
   std::vector<uint16_t> tile_ents;     // (slot << 4) | sym(i,j): staged element slot + local pair
   int max_tile_elems = 0, max_tile_nnz = 0, max_tile_ents = 0;
 
+  // Device form of the plan: one packed, 16-byte aligned blob per tile so the kernel fetches ALL of a
+  // tile's inputs with two bulk (TMA) copies and phase 1 issues no dependent global gathers.
+  // Section A = {ne, nno, nn, nents} (4 x i32) | x | y | z (f64 x nno each: coordinates of the tile's
+  // nodes, local numbering) |
+  // gnode (i32 x nno: global node ids) | ek (u32 x ne: element id, bit 31 = owner) |
+  // loc (4 x u16 x ne: local node ids of each staged element).
+  // Section B = gidx (i32 x nn) | coff (u16 x (nn+1)) | ents (u16 x nents).
+  // Every sub-section is padded to 16 bytes.
+  // tile_hdr[T] = {offset of A in 16-byte units, bytes of A, bytes of B, 0}; B follows A directly.
+  std::vector<int> tile_hdr;        // 4 * ntiles
+  std::vector<uint32_t> tile_blob;  // packed words
+  int max_blob_a = 0, max_blob_b = 0;  // bytes
+  int max_tile_nodes = 0;
+
   // SpMV row blocks: rows [blk_row[b], blk_row[b+1]) hold <= spmv_block_nnz entries (or one long row)
   std::vector<int> blk_row;
-  int max_blk_nnz = 0;
+  std::vector<int> blk_info;  // 4 per block: {r0, r1, rowptr[r0], rowptr[r1]}
+  int max_blk_nnz = 0, max_blk_rows = 0;
 };
 
 // p: 3 x nv (may be null when natural_order), t: 4 x nt 0-based.  Throws std::runtime_error on bad input.
 void build_symbolic(const double* p, const int* t, int nv, int nt, const SymbolicOpts& o, Symbolic& S);
+
+// byte sizes of the packed blob sections (shared by the host packer and the kernel)
+#ifdef __CUDACC__
+#define FK_HD __host__ __device__
+#else
+#define FK_HD
+#endif
+FK_HD inline int pad16(int bytes) { return (bytes + 15) & ~15; }
+FK_HD inline int blob_a_bytes(int ne, int nno) { return 16 + 3 * pad16(8 * nno) + pad16(4 * nno) + pad16(4 * ne) + pad16(8 * ne); }
+FK_HD inline int blob_b_bytes(int nn, int nents) { return pad16(4 * nn) + pad16(2 * (nn + 1)) + pad16(2 * nents); }
 
 // index of the unordered local pair (i,j) in the 10-entry symmetric staging layout
 inline int sym_index(int i, int j) {

@@ -71,6 +71,10 @@ class Femeko:
     def set_stream(self, stream_ptr: int):
         L.check(self.lib.fk_set_stream(self.h, C.c_void_p(stream_ptr)))
 
+    def tune(self, what: int, value: int):
+        """Launch-shape tuning (fk_tune): what 0 = asm_cfg, 1 = spmv_variant, 2 = spmv_stages."""
+        L.check(self.lib.fk_tune(self.h, int(what), int(value)))
+
     def synchronize(self):
         L.check(self.lib.fk_synchronize(self.h))
 

@@ -31,7 +31,8 @@ class FemekoError(RuntimeError):
 
 class fk_create_opts(C.Structure):
     _fields_ = [("tile_max_elems", C.c_int), ("tile_max_rows", C.c_int), ("natural_order", C.c_int),
-                ("spmv_block_nnz", C.c_int), ("device", C.c_int), ("n_owned", C.c_int)]
+                ("spmv_block_nnz", C.c_int), ("device", C.c_int), ("n_owned", C.c_int), ("asm_cfg", C.c_int),
+                ("spmv_variant", C.c_int), ("spmv_stages", C.c_int)]
 
 
 class fk_pcg_opts(C.Structure):
@@ -59,6 +60,7 @@ _SIGS = {
     "fk_destroy": (C.c_int, [_H]),
     "fk_set_stream": (C.c_int, [_H, C.c_void_p]),
     "fk_synchronize": (C.c_int, [_H]),
+    "fk_tune": (C.c_int, [_H, C.c_int, C.c_int]),
     "fk_launch_count": (C.c_int, [_H, C.POINTER(C.c_longlong)]),
     "fk_sizes": (C.c_int, [_H, c_int_p, c_int_p, C.POINTER(C.c_longlong), c_int_p]),
     "fk_csr_pattern": (C.c_int, [_H, c_int_p, c_int_p]),

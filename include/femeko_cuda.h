@@ -33,13 +33,17 @@ enum { FK_BC_EXTRAPOLATE = 0, FK_BC_ZERO = 1, FK_BC_ERROR = 2, FK_BC_NEAREST = 3
 
 /* Options of the symbolic phase (all 0 = defaults). */
 typedef struct fk_create_opts {
-  int tile_max_elems; /* elements staged per assembly tile (<= 4096); default 1024            */
+  int tile_max_elems; /* elements staged per assembly tile (<= 4096); default 512             */
   int tile_max_rows;  /* rows per assembly tile; default 256                                  */
   int natural_order;  /* 1: tile rows in input order instead of Morton order of coordinates   */
   int spmv_block_nnz; /* nnz staged per SpMV row block; default 2048                          */
   int device;         /* CUDA device ordinal; -1 = current device                             */
   int n_owned;        /* multi-GPU partitions: rows [0, n_owned) are owned (assembled, solved),
                          rows [n_owned, nv) are halo copies; 0 = all rows owned                 */
+  int asm_cfg;        /* assembly launch shape {threads, min CTAs/SM}: 0 = default (Picard sweep {256,2},
+                         others {256,3}); 1 {256,3} 2 {256,2} 3 {384,2} 4 {512,2} 5 {128,6}      */
+  int spmv_variant;   /* 0/1: matrix stream staged by TMA bulk copies (default); 2: loaded by the warps */
+  int spmv_stages;    /* TMA variant: shared-memory stages per CTA (2..8); default 3            */
 } fk_create_opts;
 
 /* PCG options.  Defaults (all 0) reproduce Eigen::ConjugateGradient's: tol = DBL_EPSILON relative
@@ -68,6 +72,9 @@ int fk_destroy(fk_handle h);
  * issued on it.                                                                                  */
 int fk_set_stream(fk_handle h, void* stream);
 int fk_synchronize(fk_handle h);
+/* change a launch-shape option after creation (tuning sweeps): what 0 = asm_cfg, 1 = spmv_variant,
+ * 2 = spmv_stages; values as in fk_create_opts.  Results do not depend on these.                 */
+int fk_tune(fk_handle h, int what, int value);
 /* number of kernels of this library launched through the handle so far (graph nodes included) */
 int fk_launch_count(fk_handle h, long long* n);
 
