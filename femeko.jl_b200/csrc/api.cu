@@ -50,7 +50,10 @@ static inline int cdiv(long long a, int b) { return (int)((a + b - 1) / b); }
 
 static double* slot_vals(fk_handle h, int slot) {
   check_slot(slot);
-  h->vals[slot].ensure((size_t)h->nnz + kSlack);
+  if (!h->vals[slot].ptr) {  // padding entries of the SELL layout must be (and stay) zero
+    h->vals[slot].ensure((size_t)h->nnz_sell + kSlack);
+    FK_CUDA(cudaMemsetAsync(h->vals[slot].ptr, 0, sizeof(double) * ((size_t)h->nnz_sell + kSlack), h->stream));
+  }
   return h->vals[slot].ptr;
 }
 
@@ -144,46 +147,24 @@ static void ensure_state(fk_handle h) {
 // ------------------------------------------------------------------------------------------------
 void launch_spmv(fk_handle h, cudaStream_t s, const double* vals, const double* x, double* y, bool dot, const PcgCtl* ctl,
                  int j) {
-  const int nblk = (int)h->sym.blk_row.size() - 1;
-  if (nblk <= 0) return;
-  if (h->spmv_variant == 1) {
-    SpmvTmaArgs a{h->rowptr.ptr, h->colind.ptr, vals, x, y, reinterpret_cast<const int4*>(h->blk_info.ptr), nblk, h->spmv_cap,
-                  h->spmv_rows_cap, h->spmv_stages, dot ? h->part.ptr : nullptr, ctl, j};
-    if (dot) spmv_tma_kernel<true><<<h->grid_spmv, kSpmvThreads, h->spmv_smem, s>>>(a);
-    else spmv_tma_kernel<false><<<h->grid_spmv, kSpmvThreads, h->spmv_smem, s>>>(a);
-  } else {
-    if (dot)
-      spmv_kernel<true><<<h->grid_spmv, kSpmvThreads, h->spmv_smem, s>>>(h->rowptr.ptr, h->colind.ptr, vals, x, y, h->blk_row.ptr,
-                                                                         nblk, h->spmv_cap, h->part.ptr, ctl, j);
-    else
-      spmv_kernel<false><<<h->grid_spmv, kSpmvThreads, h->spmv_smem, s>>>(h->rowptr.ptr, h->colind.ptr, vals, x, y, h->blk_row.ptr,
-                                                                          nblk, h->spmv_cap, nullptr, ctl, j);
-  }
+  if (h->sym.nslices <= 0) return;
+  if (dot)
+    spmv_sell_kernel<true><<<h->grid_spmv, kSpmvThreads, 0, s>>>(h->slice_ptr.ptr, h->srow.ptr, h->sell_col.ptr, vals, x, y,
+                                                                 h->sym.nslices, h->part.ptr, ctl, j);
+  else
+    spmv_sell_kernel<false><<<h->grid_spmv, kSpmvThreads, 0, s>>>(h->slice_ptr.ptr, h->srow.ptr, h->sell_col.ptr, vals, x, y,
+                                                                  h->sym.nslices, nullptr, ctl, j);
   FK_CUDA(cudaGetLastError());
 }
 
-// launch geometry of the persistent SpMV: full residency, fixed per configuration (deterministic p.Ap)
-static void configure_spmv(fk_handle h, int variant, int stages) {
-  cudaDeviceProp prop;
-  FK_CUDA(cudaGetDeviceProperties(&prop, h->device));
-  h->spmv_variant = (variant == 2) ? 0 : 1;   // option value 0/1 = TMA-staged (default), 2 = warp-loaded
-  h->spmv_stages = std::min(8, std::max(2, stages > 0 ? stages : 3));
+// launch geometry of the persistent SpMV: full residency, fixed per handle (deterministic p.Ap)
+static void configure_spmv(fk_handle h, int ctas_per_sm) {
   int occ = 1;
-  if (h->spmv_variant == 1) {
-    h->spmv_smem = (size_t)h->spmv_stages * spmv_stage_bytes(h->spmv_cap, h->spmv_rows_cap);
-    need(h->spmv_smem <= (size_t)prop.sharedMemPerBlockOptin, "fk: SpMV stages do not fit in shared memory");
-    FK_CUDA(cudaFuncSetAttribute(spmv_tma_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->spmv_smem));
-    FK_CUDA(cudaFuncSetAttribute(spmv_tma_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->spmv_smem));
-    FK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, spmv_tma_kernel<true>, kSpmvThreads, h->spmv_smem));
-  } else {
-    h->spmv_smem = (size_t)h->spmv_cap * sizeof(double);
-    FK_CUDA(cudaFuncSetAttribute(spmv_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->spmv_smem));
-    FK_CUDA(cudaFuncSetAttribute(spmv_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->spmv_smem));
-    FK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, spmv_kernel<true>, kSpmvThreads, h->spmv_smem));
-  }
+  FK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, spmv_sell_kernel<true>, kSpmvThreads, 0));
   occ = std::max(1, occ);
-  const int nblk = (int)h->sym.blk_row.size() - 1;
-  h->grid_spmv = std::max(1, std::min(nblk, h->num_sms * occ));
+  if (ctas_per_sm > 0) occ = std::min(occ, ctas_per_sm);
+  const int groups = (h->sym.nslices + (kSpmvThreads / 32) - 1) / (kSpmvThreads / 32);
+  h->grid_spmv = std::max(1, std::min(groups, h->num_sms * occ));
   for (int s = 0; s < FK_NUM_SLOTS; s++)
     if (h->graph[s]) { cudaGraphExecDestroy(h->graph[s]); h->graph[s] = nullptr; }
   if (h->part.ptr) h->part.ensure((size_t)4 * std::max(h->grid_spmv, h->grid_vec) + 16);
@@ -260,7 +241,7 @@ static void pcg_dev(fk_handle h, int slot, const double* b_dev, double* x_dev, c
   cudaStream_t s = h->stream;
   const int gv = h->grid_vec;
 
-  jacobi_kernel<<<cdiv(n, 256), 256, 0, s>>>(h->vals[slot].ptr, h->diag.ptr, n, opt.no_precond, h->dinv.ptr);
+  jacobi_kernel<<<cdiv(n, 256), 256, 0, s>>>(h->vals[slot].ptr, h->sell_diag.ptr, n, opt.no_precond, h->dinv.ptr);
   const double* Ax0 = nullptr;
   if (opt.warm_start) {
     FK_CUDA(cudaMemcpyAsync(h->x.ptr, x_dev, sizeof(double) * (size_t)n, cudaMemcpyDeviceToDevice, s));
@@ -364,7 +345,7 @@ static SymbolicOpts to_symbolic_opts(const fk_create_opts& o) {
   if (o.tile_max_elems > 0) so.tile_max_elems = o.tile_max_elems;
   if (o.tile_max_rows > 0) so.tile_max_rows = o.tile_max_rows;
   so.natural_order = o.natural_order != 0;
-  if (o.spmv_block_nnz > 0) so.spmv_block_nnz = o.spmv_block_nnz;
+  if (o.sell_sigma > 0) so.sell_sigma = o.sell_sigma;
   if (o.n_owned > 0) so.n_owned = o.n_owned;
   return so;
 }
@@ -407,6 +388,7 @@ int fk_create(const double* p, const int* t, int nv, int nt, const double* VE, c
     const Symbolic& S = h->sym;
     h->n_rows = S.n_rows;
     h->nnz = S.nnz;
+    h->nnz_sell = S.nnz_sell;
 
     cudaStream_t s = h->stream;
     // mesh: nodes padded to 32 B, connectivity as int4
@@ -426,9 +408,12 @@ int fk_create(const double* p, const int* t, int nv, int nt, const double* VE, c
     h->rowptr.upload(S.rowptr, s);
     h->colind.ensure(S.colind.size() + kSlack);
     h->colind.upload(S.colind, s);
-    h->blk_info.upload(S.blk_info, s);
-    h->diag.upload(S.diag, s);
-    h->blk_row.upload(S.blk_row, s);
+    h->slice_ptr.upload(S.slice_ptr, s);
+    h->srow.upload(S.srow, s);
+    h->sell_col.ensure(S.sell_col.size() + kSlack);
+    h->sell_col.upload(S.sell_col, s);
+    h->csr2sell.upload(S.csr2sell, s);
+    h->sell_diag.upload(S.sell_diag, s);
     h->tile_hdr.upload(S.tile_hdr, s);
     h->tile_blob.upload(S.tile_blob, s);
     FK_CUDA(cudaStreamSynchronize(s));
@@ -449,9 +434,7 @@ int fk_create(const double* p, const int* t, int nv, int nt, const double* VE, c
     }
 
     // launch geometry of the persistent SpMV / vector kernels: full residency, fixed for determinism
-    h->spmv_cap = std::max(32, std::min(S.max_blk_nnz, std::max(so.spmv_block_nnz, 2048)));
-    h->spmv_rows_cap = std::max(1, S.max_blk_rows);
-    configure_spmv(h.get(), o.spmv_variant, o.spmv_stages);
+    configure_spmv(h.get(), o.spmv_ctas_per_sm);
     h->grid_vec = std::max(1, std::min(cdiv(std::max(1, h->n_rows), kVecThreads), h->num_sms * 8));
     FK_CUDA(cudaStreamSynchronize(s));
     h->st_a.release();
@@ -501,8 +484,7 @@ int fk_tune(fk_handle h, int what, int value) {
         launch_assemble<ASM_LAGRANGE>(h, dummy, true);
         break;
       }
-      case 1: configure_spmv(h, value, h->spmv_stages); break;
-      case 2: configure_spmv(h, h->spmv_variant == 1 ? 1 : 2, value); break;
+      case 1: configure_spmv(h, value); break;
       default: throw std::runtime_error("fk_tune: unknown option");
     }
     return 0;
@@ -609,7 +591,7 @@ int fk_symbolic_create(const double* p, const int* t, int nv, int nt, const fk_c
   });
 }
 int fk_symbolic_sizes(fk_symbolic s, long long* nnz, int* ntiles, long long* n_tile_elems, long long* nnz_tiles,
-                      long long* n_ents, int* n_blocks) {
+                      long long* n_ents, int* nslices, long long* nnz_sell) {
   return guard([&]() {
     need(s, "fk: NULL argument");
     if (nnz) *nnz = s->S.nnz;
@@ -617,13 +599,15 @@ int fk_symbolic_sizes(fk_symbolic s, long long* nnz, int* ntiles, long long* n_t
     if (n_tile_elems) *n_tile_elems = (long long)s->S.tile_elems.size();
     if (nnz_tiles) *nnz_tiles = (long long)s->S.tile_gidx.size();
     if (n_ents) *n_ents = (long long)s->S.tile_ents.size();
-    if (n_blocks) *n_blocks = (int)s->S.blk_row.size() - 1;
+    if (nslices) *nslices = s->S.nslices;
+    if (nnz_sell) *nnz_sell = s->S.nnz_sell;
     return 0;
   });
 }
 int fk_symbolic_export(fk_symbolic s, int* rowptr, int* colind, int* diag, int* e2nnz, long long* tile_elem_ptr,
                        unsigned int* tile_elems, long long* tile_nnz_ptr, int* tile_gidx, unsigned short* tile_coff,
-                       long long* tile_ent_ptr, unsigned short* tile_ents, int* blk_row) {
+                       long long* tile_ent_ptr, unsigned short* tile_ents, int* slice_ptr, int* srow, int* sell_col,
+                       int* csr2sell) {
   return guard([&]() {
     need(s, "fk: NULL argument");
     const Symbolic& S = s->S;
@@ -638,7 +622,10 @@ int fk_symbolic_export(fk_symbolic s, int* rowptr, int* colind, int* diag, int* 
     copy_vec(S.tile_coff, tile_coff);
     copy_vec(S.tile_ent_ptr, tile_ent_ptr);
     copy_vec(S.tile_ents, tile_ents);
-    copy_vec(S.blk_row, blk_row);
+    copy_vec(S.slice_ptr, slice_ptr);
+    copy_vec(S.srow, srow);
+    copy_vec(S.sell_col, sell_col);
+    copy_vec(S.csr2sell, csr2sell);
     return 0;
   });
 }
@@ -648,6 +635,17 @@ int fk_symbolic_destroy(fk_symbolic s) {
 }
 
 // ---- assembly -----------------------------------------------------------------------------------
+// matrix values leave the device in CSR order (the pattern fk_csr_pattern returns)
+static void copy_out_matrix(fk_handle h, const double* vals, double* host) {
+  if (host) {
+    h->st_m.ensure((size_t)h->nnz);
+    sell_to_csr_kernel<<<std::min(cdiv(h->nnz, 256), h->num_sms * 16), 256, 0, h->stream>>>(vals, h->csr2sell.ptr, h->nnz, h->st_m.ptr);
+    FK_CUDA(cudaGetLastError());
+    h->launches++;
+    FK_CUDA(cudaMemcpyAsync(host, h->st_m.ptr, sizeof(double) * (size_t)h->nnz, cudaMemcpyDeviceToHost, h->stream));
+  }
+  FK_CUDA(cudaStreamSynchronize(h->stream));
+}
 static void copy_out(fk_handle h, const double* dev, double* host, size_t n) {
   if (host) FK_CUDA(cudaMemcpyAsync(host, dev, sizeof(double) * n, cudaMemcpyDeviceToHost, h->stream));
   FK_CUDA(cudaStreamSynchronize(h->stream));
@@ -683,7 +681,7 @@ int fk_assemble_stiffness(fk_handle h, int slot, const double* f, double* vals_o
     DeviceGuard dg(h->device);
     if (f) h->st_a.upload(f, (size_t)h->nt, h->stream);
     assemble_stiffness_dev(h, slot, f ? h->st_a.ptr : nullptr);
-    copy_out(h, h->vals[slot].ptr, vals_out, (size_t)h->nnz);
+    copy_out_matrix(h, h->vals[slot].ptr, vals_out);
     return 0;
   });
 }
@@ -693,7 +691,7 @@ int fk_assemble_mass(fk_handle h, int slot, const double* rho, double* vals_out)
     DeviceGuard dg(h->device);
     if (rho) h->st_a.upload(rho, (size_t)h->nt, h->stream);
     assemble_mass_dev(h, slot, rho ? h->st_a.ptr : nullptr);
-    copy_out(h, h->vals[slot].ptr, vals_out, (size_t)h->nnz);
+    copy_out_matrix(h, h->vals[slot].ptr, vals_out);
     return 0;
   });
 }
@@ -704,7 +702,7 @@ int fk_assemble_tangential(fk_handle h, int slot, const double* Hfield, const do
     h->st_a.upload(dmu, (size_t)h->nt, h->stream);
     h->st_b.upload(Hfield, (size_t)3 * h->nt, h->stream);
     assemble_tangential_dev(h, slot, h->st_b.ptr, h->st_a.ptr);
-    copy_out(h, h->vals[slot].ptr, vals_out, (size_t)h->nnz);
+    copy_out_matrix(h, h->vals[slot].ptr, vals_out);
     return 0;
   });
 }
@@ -731,8 +729,8 @@ int fk_matrix_axpby(fk_handle h, int dst, double alpha, int x, double beta, int 
     need(h->vals[x].ptr != nullptr, "fk_matrix_axpby: slot x is empty");
     if (beta != 0.0) { check_slot(y); need(h->vals[y].ptr != nullptr, "fk_matrix_axpby: slot y is empty"); }
     double* d = slot_vals(h, dst);
-    axpby_kernel<<<std::min(cdiv(h->nnz, 256), h->num_sms * 8), 256, 0, h->stream>>>(d, alpha, h->vals[x].ptr, beta,
-                                                                                     beta != 0.0 ? h->vals[y].ptr : nullptr, h->nnz);
+    axpby_kernel<<<std::min(cdiv(h->nnz_sell, 256), h->num_sms * 8), 256, 0, h->stream>>>(
+        d, alpha, h->vals[x].ptr, beta, beta != 0.0 ? h->vals[y].ptr : nullptr, h->nnz_sell);
     FK_CUDA(cudaGetLastError());
     h->launches++;
     return 0;
@@ -744,7 +742,7 @@ int fk_matrix_get(fk_handle h, int slot, double* vals_out) {
     check_slot(slot);
     need(h->vals[slot].ptr != nullptr, "fk_matrix_get: slot is empty");
     DeviceGuard dg(h->device);
-    copy_out(h, h->vals[slot].ptr, vals_out, (size_t)h->nnz);
+    copy_out_matrix(h, h->vals[slot].ptr, vals_out);
     return 0;
   });
 }
@@ -753,7 +751,10 @@ int fk_matrix_set(fk_handle h, int slot, const double* vals_in) {
     need(h && vals_in, "fk: NULL argument");
     DeviceGuard dg(h->device);
     double* d = slot_vals(h, slot);
-    FK_CUDA(cudaMemcpyAsync(d, vals_in, sizeof(double) * (size_t)h->nnz, cudaMemcpyHostToDevice, h->stream));
+    h->st_m.upload(vals_in, (size_t)h->nnz, h->stream);
+    csr_to_sell_kernel<<<std::min(cdiv(h->nnz, 256), h->num_sms * 16), 256, 0, h->stream>>>(h->st_m.ptr, h->csr2sell.ptr, h->nnz, d);
+    FK_CUDA(cudaGetLastError());
+    h->launches++;
     FK_CUDA(cudaStreamSynchronize(h->stream));
     return 0;
   });
@@ -766,13 +767,13 @@ int fk_lagrange(fk_handle h, double* C_out) {
     DeviceGuard dg(h->device);
     // diag-only "matrix" VE/4 per local node, assembled through the same gather plan: the diagonal
     // then holds sum_k VE[k]/4 in ascending element order = the reference loop (FEM3D.jl:274-281)
-    h->st_b.ensure((size_t)h->nnz);
+    h->st_b.ensure((size_t)h->nnz_sell);
     AsmArgs a = base_args(h, h->st_b.ptr);
     a.VE = h->VE.ptr;
     launch_assemble<ASM_LAGRANGE>(h, a);
     h->st_c.ensure((size_t)h->nv);
     FK_CUDA(cudaMemsetAsync(h->st_c.ptr, 0, sizeof(double) * (size_t)h->nv, h->stream));
-    gather_diag_kernel<<<cdiv(h->n_rows, 256), 256, 0, h->stream>>>(h->st_b.ptr, h->diag.ptr, h->n_rows, h->st_c.ptr);
+    gather_diag_kernel<<<cdiv(h->n_rows, 256), 256, 0, h->stream>>>(h->st_b.ptr, h->sell_diag.ptr, h->n_rows, h->st_c.ptr);
     FK_CUDA(cudaGetLastError());
     h->launches++;
     copy_out(h, h->st_c.ptr, C_out, (size_t)h->nv);

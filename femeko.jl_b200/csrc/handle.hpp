@@ -67,7 +67,9 @@ struct fk_handle_s {
   fk::DevBuf<int4> t4;
   fk::DevBuf<double> VE;
   // pattern + plans
-  fk::DevBuf<int> rowptr, colind, diag, blk_row, blk_info;
+  fk::DevBuf<int> rowptr, colind;                                  // canonical CSR pattern (exports, diagnostics)
+  fk::DevBuf<int> slice_ptr, srow, sell_col, csr2sell, sell_diag;  // SELL-32-sigma device layout (symbolic.hpp)
+  long long nnz_sell = 0;
   fk::DevBuf<int> tile_hdr;            // int4 per tile
   fk::DevBuf<uint32_t> tile_blob;      // packed per-tile plan blobs (symbolic.hpp)
   int e_pad = 0, asm_cfg = 0;
@@ -86,14 +88,11 @@ struct fk_handle_s {
   fk::DevBuf<double> x, r, p, Ap, dinv, part, bvec;
   fk::DevBuf<fk::PcgCtl> ctl;
   fk::PcgCtl* ctl_host = nullptr;      // pinned
-  int grid_spmv = 0, grid_vec = 0, spmv_cap = 0;
-  int spmv_variant = 1;                // 0: warp-loaded stream (spmv_kernel), 1: TMA-staged stream (spmv_tma_kernel)
-  int spmv_stages = 3, spmv_rows_cap = 0;
-  size_t spmv_smem = 0;
+  int grid_spmv = 0, grid_vec = 0;
   cudaGraphExec_t graph[FK_NUM_SLOTS] = {nullptr, nullptr, nullptr, nullptr};
   int graph_chunk[FK_NUM_SLOTS] = {0, 0, 0, 0};
   // generic staging for the host-pointer API
-  fk::DevBuf<double> st_a, st_b, st_c, st_d;
+  fk::DevBuf<double> st_a, st_b, st_c, st_d, st_m;
   fk::DevBuf<int> st_i, st_j, st_k;
   // multi-GPU
   fk::Comm* comm = nullptr;

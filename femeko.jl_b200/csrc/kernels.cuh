@@ -1,7 +1,7 @@
 // Hand-written sm_100a fp64 kernels of the Femeko hot path.  All three kernel families are
 // HBM-bound gather / stream kernels (no dense contraction -> no tensor cores):
 //   K1  assemble_kernel<MODE>   P1 tet local matrices -> CSR values, tile-gather, no atomics
-//   K2  spmv_kernel / pcg_*     CSR-stream SpMV fused with p.Ap, fused x/r update + 2 dots, direction update
+//   K2  spmv_sell_kernel / pcg_*  SELL-32 SpMV fused with p.Ap, fused x/r update + 2 dots, direction update
 //   K3  recover_field_kernel    H = -grad(u), |H|, B = mu |H|
 // Reference math: src/FEM3D.jl:5-17 (abcd), :59-76 (local stiffness), :466-476 (mass), :79-105
 // (tangential), magneticField.jl:111-132 (field), ConjugateGradient.h:29-85 (PCG recurrence).
@@ -222,52 +222,6 @@ struct PcgCtl {
 
 __device__ __forceinline__ bool pcg_inactive(const PcgCtl* c, int j) {
   return c != nullptr && (c->done != 0 || c->base_it + j >= c->max_iter);
-}
-
-// CSR-stream SpMV over precomputed row blocks: the block's value/column stream is read fully
-// coalesced (evict-first: it is touched once per product), multiplied with gathered x (L2/L1
-// resident) into shared memory, then one thread per row folds its segment left to right.
-// DOT fuses p.Ap: per-CTA partial sums in fixed order -> part[blockIdx.x].
-template <bool DOT>
-static __global__ void __launch_bounds__(kSpmvThreads) spmv_kernel(const int* __restrict__ rowptr, const int* __restrict__ colind,
-                                                            const double* __restrict__ vals, const double* __restrict__ x,
-                                                            double* __restrict__ y, const int* __restrict__ blk_row, int nblk,
-                                                            int cap, double* __restrict__ part, const PcgCtl* ctl, int j) {
-  extern __shared__ double prod[];
-  __shared__ double red[33];
-  if (pcg_inactive(ctl, j)) return;
-  double acc = 0.0;
-  for (int b = blockIdx.x; b < nblk; b += gridDim.x) {
-    const int r0 = blk_row[b], r1 = blk_row[b + 1];
-    const int q0 = rowptr[r0], q1 = rowptr[r1];
-    if (q1 - q0 <= cap) {
-      for (int q = q0 + threadIdx.x; q < q1; q += kSpmvThreads)
-        prod[q - q0] = __ldcs(vals + q) * __ldg(x + __ldcs(colind + q));
-      __syncthreads();
-      for (int r = r0 + threadIdx.x; r < r1; r += kSpmvThreads) {
-        const int a = rowptr[r] - q0, e = rowptr[r + 1] - q0;
-        double s = 0.0;
-        for (int q = a; q < e; q++) s += prod[q];
-        y[r] = s;
-        if (DOT) acc += s * x[r];
-      }
-      __syncthreads();
-    } else {  // a row block too long to stage (very high-degree node): whole CTA per row
-      for (int r = r0; r < r1; r++) {
-        double s = 0.0;
-        for (int q = rowptr[r] + threadIdx.x; q < rowptr[r + 1]; q += kSpmvThreads) s += vals[q] * __ldg(x + colind[q]);
-        s = block_sum(s, red);
-        if (threadIdx.x == 0) {
-          y[r] = s;
-          if (DOT) acc += s * x[r];
-        }
-      }
-    }
-  }
-  if (DOT) {
-    acc = block_sum(acc, red);
-    if (threadIdx.x == 0) part[blockIdx.x] = acc;
-  }
 }
 
 #include "spmv.cuh"

@@ -281,6 +281,56 @@ void build_symbolic(const double* p, const int* t, int nv, int nt, const Symboli
   }
   if (bad) throw std::runtime_error("fk: internal error building assembly tiles");
 
+  // ---- SELL-32-sigma layout (see symbolic.hpp) ---------------------------------------------------
+  {
+    const int C = 32;
+    const int sigma = std::max(1, o.sell_sigma);
+    std::vector<int> ord((size_t)nr);
+    std::iota(ord.begin(), ord.end(), 0);
+    if (sigma > 1)
+      for (int w0 = 0; w0 < nr; w0 += sigma)
+        std::stable_sort(ord.begin() + w0, ord.begin() + std::min(nr, w0 + sigma), [&](int a, int b) { return rowlen[a] > rowlen[b]; });
+    S.nslices = (nr + C - 1) / C;
+    S.srow.assign((size_t)S.nslices * C, -1);
+    std::copy(ord.begin(), ord.end(), S.srow.begin());
+    S.slice_ptr.assign((size_t)S.nslices + 1, 0);
+    int64_t tot = 0;
+    for (int sl = 0; sl < S.nslices; sl++) {
+      int w = 0;
+      for (int l = 0; l < C; l++) {
+        const int r = S.srow[(size_t)sl * C + l];
+        if (r >= 0) w = std::max(w, rowlen[r]);
+      }
+      S.slice_ptr[sl] = (int)tot;
+      tot += (int64_t)w * C;
+      if (tot > 0x7fffffffLL) throw std::runtime_error("fk: more than 2^31-1 padded matrix entries on one GPU; partition the mesh");
+    }
+    S.slice_ptr[S.nslices] = (int)tot;
+    S.nnz_sell = tot;
+    S.sell_col.assign((size_t)tot, 0);
+    S.csr2sell.assign((size_t)S.nnz, -1);
+    S.sell_diag.assign((size_t)nr, -1);
+#pragma omp parallel for schedule(static)
+    for (int sl = 0; sl < S.nslices; sl++) {
+      const int base = S.slice_ptr[sl], w = (S.slice_ptr[sl + 1] - base) / C;
+      for (int l = 0; l < C; l++) {
+        const int r = S.srow[(size_t)sl * C + l];
+        const int len = r >= 0 ? rowlen[r] : 0;
+        for (int k = 0; k < w; k++) {
+          const int idx = base + k * C + l;
+          if (k < len) {
+            const int q = S.rowptr[r] + k;
+            S.sell_col[idx] = S.colind[q];
+            S.csr2sell[q] = idx;
+            if (S.colind[q] == r) S.sell_diag[r] = idx;
+          } else {
+            S.sell_col[idx] = r >= 0 ? r : 0;  // padding: value stays 0, column is a valid index
+          }
+        }
+      }
+    }
+  }
+
   // ---- packed device blobs (see symbolic.hpp) ---------------------------------------------------
   {
     // per tile: sorted unique nodes of the staged elements (local numbering of the tile)
@@ -354,7 +404,11 @@ void build_symbolic(const double* p, const int* t, int nv, int nt, const Symboli
       }
       dst += pad16(8 * ne);
       // section B: gather plan
-      std::memcpy(dst, S.tile_gidx.data() + S.tile_nnz_ptr[tl], sizeof(int) * (size_t)nn);
+      {  // value indices in the device (SELL) layout; the host-side plan (tile_gidx) keeps CSR indices
+        int* gd = reinterpret_cast<int*>(dst);
+        const int* gs = S.tile_gidx.data() + S.tile_nnz_ptr[tl];
+        for (int q = 0; q < nn; q++) gd[q] = S.csr2sell[gs[q]];
+      }
       dst += pad16(4 * nn);
       std::memcpy(dst, S.tile_coff.data() + S.tile_nnz_ptr[tl] + tl, sizeof(uint16_t) * ((size_t)nn + 1));
       dst += pad16(2 * (nn + 1));
@@ -362,35 +416,6 @@ void build_symbolic(const double* p, const int* t, int nv, int nt, const Symboli
     }
   }
 
-  // ---- SpMV row blocks --------------------------------------------------------------------------
-  S.blk_row.clear();
-  S.blk_row.push_back(0);
-  {
-    int rows_in = 0;
-    int64_t nnz_in = 0;
-    for (int r = 0; r < nr; r++) {
-      if (rows_in > 0 && (nnz_in + rowlen[r] > o.spmv_block_nnz || rows_in >= o.spmv_block_rows)) {
-        S.blk_row.push_back(r);
-        S.max_blk_nnz = std::max<int>(S.max_blk_nnz, (int)nnz_in);
-        rows_in = 0;
-        nnz_in = 0;
-      }
-      rows_in++;
-      nnz_in += rowlen[r];
-    }
-    S.blk_row.push_back(nr);
-    S.max_blk_nnz = std::max<int>(S.max_blk_nnz, (int)nnz_in);
-    const int nb = (int)S.blk_row.size() - 1;
-    S.blk_info.resize((size_t)4 * nb);
-    for (int b = 0; b < nb; b++) {
-      const int r0 = S.blk_row[b], r1 = S.blk_row[b + 1];
-      S.blk_info[4 * (size_t)b] = r0;
-      S.blk_info[4 * (size_t)b + 1] = r1;
-      S.blk_info[4 * (size_t)b + 2] = S.rowptr[r0];
-      S.blk_info[4 * (size_t)b + 3] = S.rowptr[r1];
-      S.max_blk_rows = std::max(S.max_blk_rows, r1 - r0);
-    }
-  }
 }
 
 }  // namespace fk

@@ -14,8 +14,7 @@ struct SymbolicOpts {
   int tile_max_elems = 512;   // elements staged per tile (<= 4096: 12-bit slot in a gather entry)
   int tile_max_rows = 256;
   bool natural_order = false;
-  int spmv_block_nnz = 2048;
-  int spmv_block_rows = 256;
+  int sell_sigma = 1024;      // SELL-32-sigma: rows are sorted by length inside windows of sigma rows (1 = input order)
   int n_owned = -1;  // rows [0, n_owned) get a pattern (multi-GPU: owned rows first); -1 = all
 };
 
@@ -54,10 +53,19 @@ struct Symbolic {
   int max_blob_a = 0, max_blob_b = 0;  // bytes
   int max_tile_nodes = 0;
 
-  // SpMV row blocks: rows [blk_row[b], blk_row[b+1]) hold <= spmv_block_nnz entries (or one long row)
-  std::vector<int> blk_row;
-  std::vector<int> blk_info;  // 4 per block: {r0, r1, rowptr[r0], rowptr[r1]}
-  int max_blk_nnz = 0, max_blk_rows = 0;
+  // Device storage of every matrix on this pattern: SELL-32-sigma (sliced ELLPACK).  Slice s holds the
+  // 32 rows srow[32s .. 32s+31] (-1 = padding lane); its entries sit column-major from slice_ptr[s]:
+  // entry k of lane l at slice_ptr[s] + 32 k + l, k < width(s) = (slice_ptr[s+1] - slice_ptr[s]) / 32, in
+  // ascending column order per row (the CSR order), short rows padded with (value 0, column = own row).
+  // One thread owns one row: value / column loads are perfectly coalesced and, on meshes whose numbering
+  // has locality, so are the x gathers (neighbouring rows have neighbouring columns).
+  int nslices = 0;
+  int64_t nnz_sell = 0;              // padded entry count = slice_ptr[nslices]
+  std::vector<int> slice_ptr;        // nslices + 1
+  std::vector<int> srow;             // 32 * nslices
+  std::vector<int> sell_col;         // nnz_sell
+  std::vector<int> csr2sell;         // nnz: CSR index -> SELL index
+  std::vector<int> sell_diag;        // n_rows: SELL index of (r,r), -1 if absent
 };
 
 // p: 3 x nv (may be null when natural_order), t: 4 x nt 0-based.  Throws std::runtime_error on bad input.

@@ -36,14 +36,13 @@ typedef struct fk_create_opts {
   int tile_max_elems; /* elements staged per assembly tile (<= 4096); default 512             */
   int tile_max_rows;  /* rows per assembly tile; default 256                                  */
   int natural_order;  /* 1: tile rows in input order instead of Morton order of coordinates   */
-  int spmv_block_nnz; /* nnz staged per SpMV row block; default 2048                          */
+  int sell_sigma;     /* SELL-32-sigma: rows sorted by length inside windows of sigma rows; default 1024 */
   int device;         /* CUDA device ordinal; -1 = current device                             */
   int n_owned;        /* multi-GPU partitions: rows [0, n_owned) are owned (assembled, solved),
                          rows [n_owned, nv) are halo copies; 0 = all rows owned                 */
   int asm_cfg;        /* assembly launch shape {threads, min CTAs/SM}: 0 = default (Picard sweep {256,2},
                          others {256,3}); 1 {256,3} 2 {256,2} 3 {384,2} 4 {512,2} 5 {128,6}      */
-  int spmv_variant;   /* 0/1: matrix stream staged by TMA bulk copies (default); 2: loaded by the warps */
-  int spmv_stages;    /* TMA variant: shared-memory stages per CTA (2..8); default 3            */
+  int spmv_ctas_per_sm; /* cap on resident SpMV CTAs per SM (0 = as many as fit)               */
 } fk_create_opts;
 
 /* PCG options.  Defaults (all 0) reproduce Eigen::ConjugateGradient's: tol = DBL_EPSILON relative
@@ -72,8 +71,8 @@ int fk_destroy(fk_handle h);
  * issued on it.                                                                                  */
 int fk_set_stream(fk_handle h, void* stream);
 int fk_synchronize(fk_handle h);
-/* change a launch-shape option after creation (tuning sweeps): what 0 = asm_cfg, 1 = spmv_variant,
- * 2 = spmv_stages; values as in fk_create_opts.  Results do not depend on these.                 */
+/* change a launch-shape option after creation (tuning sweeps): what 0 = asm_cfg, 1 = spmv_ctas_per_sm;
+ * values as in fk_create_opts.  Matrix values do not depend on these.                            */
 int fk_tune(fk_handle h, int what, int value);
 /* number of kernels of this library launched through the handle so far (graph nodes included) */
 int fk_launch_count(fk_handle h, long long* n);
@@ -89,21 +88,25 @@ int fk_volumes(fk_handle h, double* VE /* nt */);
 int fk_tile_stats(fk_handle h, long long* staged_elems, int* max_elems, int* max_nnz, int* max_ents);
 /* device pointers of handle-owned arrays, for zero-copy interop (torch.from_blob-style):
  * which: 0 rowptr(int) 1 colind(int) 2 VE(double) 3 mu(double) 4 Hnorm(double) 5 Hfield(double 3 x nt)
- *        6 u(double nv) 16+s values of slot s                                                   */
+ *        6 u(double nv) 7 dmu(double) 8 csr2sell(int nnz) 16+s values of slot s.  Matrix values live on
+ *        the device in the SELL-32-sigma layout of the symbolic phase: the CSR entry q of fk_csr_pattern
+ *        is values[csr2sell[q]] (fk_matrix_get / fk_assemble_* return plain CSR order on the host).   */
 int fk_device_ptr(fk_handle h, int which, void** ptr);
 
 /* ---- symbolic phase alone (host only, needs no GPU): lets the plan be inspected / validated ---
  * Arrays may be NULL to skip them.  Sizes: tile_*_ptr ntiles+1; tile_elems n_tile_elems (bit 31 =
- * this tile owns the element's per-element outputs); tile_gidx nnz_tiles; tile_coff nnz_tiles+ntiles
- * (tile T's offsets start at tile_nnz_ptr[T]+T); tile_ents 16*nt entries (slot<<4 | pair);
- * blk_row n_blocks+1.                                                                           */
+ * this tile owns the element's per-element outputs); tile_gidx nnz_tiles (CSR indices); tile_coff
+ * nnz_tiles+ntiles (tile T's offsets start at tile_nnz_ptr[T]+T); tile_ents 16*nt entries (slot<<4 |
+ * pair); SELL-32-sigma device layout: slice_ptr nslices+1, srow 32*nslices (-1 = padding lane),
+ * sell_col nnz_sell, csr2sell nnz.                                                               */
 typedef struct fk_symbolic_s* fk_symbolic;
 int fk_symbolic_create(const double* p, const int* t, int nv, int nt, const fk_create_opts* opts, fk_symbolic* out);
 int fk_symbolic_sizes(fk_symbolic s, long long* nnz, int* ntiles, long long* n_tile_elems, long long* nnz_tiles,
-                      long long* n_ents, int* n_blocks);
+                      long long* n_ents, int* nslices, long long* nnz_sell);
 int fk_symbolic_export(fk_symbolic s, int* rowptr, int* colind, int* diag, int* e2nnz, long long* tile_elem_ptr,
                        unsigned int* tile_elems, long long* tile_nnz_ptr, int* tile_gidx, unsigned short* tile_coff,
-                       long long* tile_ent_ptr, unsigned short* tile_ents, int* blk_row);
+                       long long* tile_ent_ptr, unsigned short* tile_ents, int* slice_ptr, int* srow, int* sell_col,
+                       int* csr2sell);
 int fk_symbolic_destroy(fk_symbolic s);
 
 /* ---- assembly: stiffnessMatrix / massMatrix / tangentialStiffnessMatrix ----------------------

@@ -34,8 +34,8 @@ def main():
     ap.add_argument("--n", type=int, default=119)
     ap.add_argument("--tiles", default="512,1024,2048")
     ap.add_argument("--cfgs", default="0,1,2,3,4")
-    ap.add_argument("--blocks", default="1024,2048,4096")
-    ap.add_argument("--stages", default="2,3,4,6")
+    ap.add_argument("--blocks", default="1,1024", help="SELL sigma values")
+    ap.add_argument("--stages", default="0,4,6", help="SpMV CTAs per SM caps")
     ap.add_argument("--out", default="gpurun_out/sweep.jsonl")
     args = ap.parse_args()
     dev = torch.device("cuda", 0)
@@ -54,11 +54,11 @@ def main():
     u = torch.from_numpy(-(np.array([0.5, 0, 0]) / MU0) @ m.p).to(dev)
     first = True
     for tile in [int(x) for x in args.tiles.split(",")]:
-        blocks = [int(x) for x in args.blocks.split(",")] if first else [2048]
+        blocks = [int(x) for x in args.blocks.split(",")] if first else [1024]
         for blk in blocks:
             t0 = time.time()
             try:
-                h = fk.Femeko(m, use_mesh_VE=False, device=0, tile_max_elems=tile, tile_max_rows=4096, spmv_block_nnz=blk)
+                h = fk.Femeko(m, use_mesh_VE=False, device=0, tile_max_elems=tile, tile_max_rows=4096, sell_sigma=blk)
             except Exception as e:  # noqa: BLE001
                 emit({"tile": tile, "blk": blk, "error": str(e)})
                 continue
@@ -91,25 +91,23 @@ def main():
                 b = torch.from_numpy(np.random.default_rng(0).standard_normal(h.nv)).to(dev)
                 x = torch.zeros(h.nv, dtype=torch.float64, device=dev)
                 y = torch.zeros(h.nv, dtype=torch.float64, device=dev)
-                combos = [(2, 0)] + [(1, s) for s in [int(v) for v in args.stages.split(",")]]
-                xs = {}
-                for variant, stg in combos:
+                y0 = x0 = None
+                for ctas in [int(v) for v in args.stages.split(",")]:
                     try:
-                        h.tune(1, variant)
-                        if stg:
-                            h.tune(2, stg)
+                        h.tune(1, ctas)
                         ms_spmv = timed(stream, lambda: h.spmv_dev(b.data_ptr(), y.data_ptr(), slot=0), 20)
                         yv = y.cpu().numpy().copy()
                         kw = dict(max_iter=100, tol_disable=True, check_every=100)
                         ms_pcg = timed(stream, lambda: h.pcg_dev(b.data_ptr(), x.data_ptr(), slot=0, **kw), 5)
                         xv = x.cpu().numpy().copy()
-                        xs[(variant, stg)] = (yv, xv)
-                        y0, x0 = xs[combos[0]]
-                        emit({"kind": "spmv", "blk": blk, "variant": variant, "stages": stg, "spmv_us": round(ms_spmv * 1e3, 2),
+                        if y0 is None:
+                            y0, x0 = yv, xv
+                        emit({"kind": "spmv", "sigma": blk, "ctas_per_sm": ctas, "spmv_us": round(ms_spmv * 1e3, 2),
                               "pcg_iter_us": round(ms_pcg * 10, 2), "spmv_bitwise_same": bool(np.array_equal(yv, y0)),
-                              "pcg_x_maxrel": float(np.max(np.abs(xv - x0)) / (np.max(np.abs(x0)) + 1e-300))})
+                              "pcg_x_maxrel": float(np.max(np.abs(xv - x0)) / (np.max(np.abs(x0)) + 1e-300)),
+                              "nnz": h.nnz})
                     except Exception as e:  # noqa: BLE001
-                        emit({"kind": "spmv", "blk": blk, "variant": variant, "stages": stg, "error": str(e)})
+                        emit({"kind": "spmv", "sigma": blk, "ctas_per_sm": ctas, "error": str(e)})
             h.close()
         first = False
     out.close()

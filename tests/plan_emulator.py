@@ -19,8 +19,10 @@ def export_symbolic(mesh, **opts):
     t = np.asfortranarray(mesh.t, dtype=np.int32)
     s = C.c_void_p()
     L.check(lib.fk_symbolic_create(L.dptr(p), L.iptr(t), mesh.nv, mesh.nt, C.byref(o), C.byref(s)))
-    nnz, ntiles, nte, nnzt, nent, nblk = C.c_longlong(), C.c_int(), C.c_longlong(), C.c_longlong(), C.c_longlong(), C.c_int()
-    L.check(lib.fk_symbolic_sizes(s, C.byref(nnz), C.byref(ntiles), C.byref(nte), C.byref(nnzt), C.byref(nent), C.byref(nblk)))
+    nnz, ntiles, nte, nnzt, nent, nsl, nsell = (C.c_longlong(), C.c_int(), C.c_longlong(), C.c_longlong(), C.c_longlong(), C.c_int(),
+                                                C.c_longlong())
+    L.check(lib.fk_symbolic_sizes(s, C.byref(nnz), C.byref(ntiles), C.byref(nte), C.byref(nnzt), C.byref(nent), C.byref(nsl),
+                                  C.byref(nsell)))
     T = ntiles.value
     n_rows = o.n_owned if o.n_owned > 0 else mesh.nv
     out = dict(
@@ -28,13 +30,16 @@ def export_symbolic(mesh, **opts):
         e2nnz=np.zeros(16 * mesh.nt, np.int32), tile_elem_ptr=np.zeros(T + 1, np.int64), tile_elems=np.zeros(nte.value, np.uint32),
         tile_nnz_ptr=np.zeros(T + 1, np.int64), tile_gidx=np.zeros(nnzt.value, np.int32),
         tile_coff=np.zeros(nnzt.value + T, np.uint16), tile_ent_ptr=np.zeros(T + 1, np.int64),
-        tile_ents=np.zeros(nent.value, np.uint16), blk_row=np.zeros(nblk.value + 1, np.int32))
+        tile_ents=np.zeros(nent.value, np.uint16), slice_ptr=np.zeros(nsl.value + 1, np.int32),
+        srow=np.zeros(32 * nsl.value, np.int32), sell_col=np.zeros(nsell.value, np.int32), csr2sell=np.zeros(nnz.value, np.int32))
     order = ["rowptr", "colind", "diag", "e2nnz", "tile_elem_ptr", "tile_elems", "tile_nnz_ptr", "tile_gidx", "tile_coff",
-             "tile_ent_ptr", "tile_ents", "blk_row"]
+             "tile_ent_ptr", "tile_ents", "slice_ptr", "srow", "sell_col", "csr2sell"]
     L.check(lib.fk_symbolic_export(s, *[C.c_void_p(out[k].ctypes.data) for k in order]))
     lib.fk_symbolic_destroy(s)
     out["ntiles"] = T
     out["nnz"] = nnz.value
+    out["nslices"] = nsl.value
+    out["nnz_sell"] = nsell.value
     return out
 
 
@@ -62,3 +67,21 @@ def run_plan(plan, Ak):
             vals[g[q]] = contrib[coff[q]:coff[q + 1]].sum() if coff[q + 1] - coff[q] > 8 else sum(contrib[coff[q]:coff[q + 1]], 0.0)
         written[g] += 1
     return vals, written
+
+
+def sell_spmv(plan, vals_csr, x):
+    """Execute the SELL-32-sigma layout in numpy the way spmv_sell_kernel walks it (one lane per row, left to
+    right, separately rounded multiply and add): returns y over the assembled rows."""
+    vs = np.zeros(plan["nnz_sell"])
+    vs[plan["csr2sell"]] = vals_csr
+    y = np.zeros(len(plan["diag"]))
+    sp, srow, col = plan["slice_ptr"], plan["srow"], plan["sell_col"]
+    for s in range(plan["nslices"]):
+        base, w = sp[s], (sp[s + 1] - sp[s]) // 32
+        acc = np.zeros(32)
+        for k in range(w):
+            i = base + 32 * k + np.arange(32)
+            acc = acc + vs[i] * x[col[i]]
+        r = srow[32 * s: 32 * s + 32]
+        y[r[r >= 0]] = acc[r >= 0]
+    return y

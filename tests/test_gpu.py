@@ -43,7 +43,7 @@ def test_stiffness_against_reference_golden(name):
 
 
 @pytest.mark.parametrize("mesh,opts", [("kuhn12", {}), ("kuhn12", {"natural_order": 1}),
-                                       ("kuhn12", {"tile_max_elems": 256, "tile_max_rows": 32, "spmv_block_nnz": 300}),
+                                       ("kuhn12", {"tile_max_elems": 256, "tile_max_rows": 32, "sell_sigma": 64}),
                                        ("delaunay", {}), ("delaunay", {"tile_max_elems": 1024, "tile_max_rows": 4096})])
 def test_assembly_family_against_oracle(mesh, opts):
     m = fk.kuhn_cube(12) if mesh == "kuhn12" else fk.delaunay_ball(3000, seed=11)

@@ -13,7 +13,7 @@ import femeko_jl_b200 as fk
 from conftest import ROOT, load_golden, rel_err_matrix, abs_sum_scale
 from femeko_jl_b200 import lib as L
 from oracle import oracle as orc
-from plan_emulator import export_symbolic, run_plan
+from plan_emulator import export_symbolic, run_plan, sell_spmv
 
 
 def test_library_exports_every_declared_symbol():
@@ -63,8 +63,17 @@ def test_symbolic_pattern_map_and_plan_against_reference(name, opts):
     # every element owned by exactly one tile; every (k,i,j) contribution listed exactly once
     assert int((plan["tile_elems"] >> 31).sum()) == m.nt
     assert plan["tile_ents"].size == 16 * m.nt
-    # SpMV blocks cover the rows contiguously
-    assert plan["blk_row"][0] == 0 and plan["blk_row"][-1] == m.nv and np.all(np.diff(plan["blk_row"]) > 0)
+    # SELL-32-sigma device layout: every row in exactly one lane, csr2sell injective, padding inert, and
+    # walking it the way spmv_sell_kernel does reproduces the CSR product of the reference's matrix
+    sr = plan["srow"]
+    assert np.array_equal(np.sort(sr[sr >= 0]), np.arange(m.nv))
+    assert np.unique(plan["csr2sell"]).size == plan["nnz"] and plan["nnz_sell"] >= plan["nnz"]
+    assert np.array_equal(plan["sell_col"][plan["csr2sell"]], ci)
+    x = np.random.default_rng(3).standard_normal(m.nv)
+    import scipy.sparse as sp
+    A = sp.csr_matrix((g["csc_values_mu"], ci, rp), shape=(m.nv, m.nv))
+    y = sell_spmv(plan, g["csc_values_mu"], x)
+    assert np.max(np.abs(y - A @ x)) <= 1e-14 * np.max(np.abs(A @ x))
 
 
 def test_symbolic_owned_rows_only():
