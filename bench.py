@@ -276,6 +276,7 @@ def run_ours(args):
         with torch.cuda.stream(stream):
             u2 = u_dev.clone()
         h.set_mu(np.full(mesh.nt, MU0))
+        h.reset_field()
         t0 = time.time()
         tot_it, att, div = 0, 0, float("inf")
         while div > 1e-4 and att < 100:                      # NewtonRaphson.jl:37-38,148
@@ -324,7 +325,7 @@ def run_ours(args):
             "e2e": {"value": round(e2e_value, 3), "unit": UNIT, "ms_per_step": round(ms_e2e / K, 4),
                     "h2d_bytes_per_step": 16 * nv, "d2h_bytes_per_step": 8 * n_rows + 8 + 4 + 64},
             "gpu_launches": int(launches),
-            "roofline": {"kernel": "fused Jacobi-PCG iteration (spmv_kernel<DOT> + pcg_update_kernel + pcg_direction_kernel)",
+            "roofline": {"kernel": "fused Jacobi-PCG iteration (spmv_sell_kernel<DOT> + pcg_update_kernel + pcg_direction_kernel)",
                          "bound": "hbm", "achieved": round(pcg_gbs, 1), "peak": peak, "unit": "GB/s",
                          "frac": round(pcg_gbs / peak, 4), "traffic": traffic.get("pcg_iteration_bytes"),
                          "peak_source": peak_src, "algorithmic_bytes_per_launch": it_bytes,

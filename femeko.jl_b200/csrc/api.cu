@@ -170,20 +170,55 @@ static void configure_spmv(fk_handle h, int ctas_per_sm) {
   if (h->part.ptr) h->part.ensure((size_t)4 * std::max(h->grid_spmv, h->grid_vec) + 16);
 }
 
+// B200 has 126 MB of L2: the five PCG vectors of a 10 M-tet problem (69 MB) fit, the matrix stream
+// (307 MB per product) does not.  Pin the vector slab in L2 (persisting access-policy window) and let
+// everything else -- the matrix is read with evict-first loads anyway -- stream past it, so the vector
+// kernels and the x gather / y write of the SpMV run at L2 speed instead of HBM speed.
+static void configure_l2(fk_handle h) {
+  h->l2_window_set = false;
+  if (!h->pcg_slab.ptr) return;
+  int max_persist = 0, max_window = 0;
+  cudaDeviceGetAttribute(&max_persist, cudaDevAttrMaxPersistingL2CacheSize, h->device);
+  cudaDeviceGetAttribute(&max_window, cudaDevAttrMaxAccessPolicyWindowSize, h->device);
+  cudaStreamAttrValue attr{};
+  if (h->l2_persist && max_persist > 0 && max_window > 0) {
+    const size_t bytes = h->pcg_slab.count * sizeof(double);
+    const size_t win = std::min(bytes, (size_t)max_window);
+    const size_t persist = std::min(win, (size_t)max_persist);
+    if (cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, persist) != cudaSuccess) { cudaGetLastError(); return; }
+    attr.accessPolicyWindow.base_ptr = h->pcg_slab.ptr;
+    attr.accessPolicyWindow.num_bytes = win;
+    attr.accessPolicyWindow.hitRatio = (float)std::min(1.0, (double)persist / (double)win);
+    attr.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+    attr.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+    h->l2_window_set = true;
+  } else {
+    attr.accessPolicyWindow.num_bytes = 0;  // disables the window
+    attr.accessPolicyWindow.hitProp = cudaAccessPropertyNormal;
+    attr.accessPolicyWindow.missProp = cudaAccessPropertyNormal;
+  }
+  h->l2_window = attr.accessPolicyWindow;
+  if (h->stream && cudaStreamSetAttribute(h->stream, cudaStreamAttributeAccessPolicyWindow, &attr) != cudaSuccess) cudaGetLastError();
+  for (int s = 0; s < FK_NUM_SLOTS; s++)
+    if (h->graph[s]) { cudaGraphExecDestroy(h->graph[s]); h->graph[s] = nullptr; }
+}
+
 static void ensure_pcg(fk_handle h) {
   if (h->x.ptr) return;
   const size_t nvec = (size_t)h->nv;  // vectors carry halo rows too (SpMV input)
-  h->x.ensure(nvec);
-  h->r.ensure(nvec);
-  h->p.ensure(nvec);
-  h->Ap.ensure(nvec);
-  h->dinv.ensure(nvec);
+  const size_t stride = (nvec + 31) & ~(size_t)31;
+  h->pcg_slab.ensure(5 * stride);
+  h->x.ptr = h->pcg_slab.ptr;
+  h->r.ptr = h->x.ptr + stride;
+  h->p.ptr = h->r.ptr + stride;
+  h->Ap.ptr = h->p.ptr + stride;
+  h->dinv.ptr = h->Ap.ptr + stride;
+  configure_l2(h);
   h->bvec.ensure(nvec);
   h->part.ensure((size_t)4 * std::max(h->grid_spmv, h->grid_vec) + 16);
   h->ctl.ensure(1);
   h->scal.ensure(8);
-  FK_CUDA(cudaMemsetAsync(h->p.ptr, 0, nvec * sizeof(double), h->stream));
-  FK_CUDA(cudaMemsetAsync(h->x.ptr, 0, nvec * sizeof(double), h->stream));
+  FK_CUDA(cudaMemsetAsync(h->pcg_slab.ptr, 0, 5 * stride * sizeof(double), h->stream));
   if (!h->ctl_host) FK_CUDA(cudaMallocHost((void**)&h->ctl_host, sizeof(PcgCtl)));
 }
 
@@ -218,6 +253,19 @@ static void build_graph(fk_handle h, int slot, int chunk) {
     throw;
   }
   FK_CUDA(cudaStreamEndCapture(h->cap_stream, &g));
+  {  // the L2 policy window is a per-launch attribute: put it on every kernel node of the chunk
+    size_t nn = 0;
+    FK_CUDA(cudaGraphGetNodes(g, nullptr, &nn));
+    std::vector<cudaGraphNode_t> nodes(nn);
+    if (nn) FK_CUDA(cudaGraphGetNodes(g, nodes.data(), &nn));
+    cudaLaunchAttributeValue val{};
+    val.accessPolicyWindow = h->l2_window;
+    for (cudaGraphNode_t nd : nodes) {
+      cudaGraphNodeType ty;
+      if (cudaGraphNodeGetType(nd, &ty) == cudaSuccess && ty == cudaGraphNodeTypeKernel)
+        if (cudaGraphKernelNodeSetAttribute(nd, cudaLaunchAttributeAccessPolicyWindow, &val) != cudaSuccess) cudaGetLastError();
+    }
+  }
   cudaError_t e = cudaGraphInstantiate(&h->graph[slot], g, 0);
   cudaGraphDestroy(g);
   FK_CUDA(e);
@@ -453,6 +501,7 @@ int fk_destroy(fk_handle h) {
       if (h->graph[s]) cudaGraphExecDestroy(h->graph[s]);
     if (h->cap_stream) cudaStreamDestroy(h->cap_stream);
     if (h->ctl_host) cudaFreeHost(h->ctl_host);
+    if (h->l2_window_set) cudaCtxResetPersistingL2Cache();
     comm_destroy(h);
     delete h;
     return 0;
@@ -462,7 +511,9 @@ int fk_destroy(fk_handle h) {
 int fk_set_stream(fk_handle h, void* stream) {
   return guard([&]() {
     need(h, "fk: NULL handle");
+    DeviceGuard dg(h->device);
     h->stream = (cudaStream_t)stream;
+    configure_l2(h);
     return 0;
   });
 }
@@ -485,6 +536,7 @@ int fk_tune(fk_handle h, int what, int value) {
         break;
       }
       case 1: configure_spmv(h, value); break;
+      case 2: h->l2_persist = value != 0; configure_l2(h); break;
       default: throw std::runtime_error("fk_tune: unknown option");
     }
     return 0;
@@ -1030,6 +1082,17 @@ int fk_get_mu(fk_handle h, double* mu_out, double* dmu_out) {
     if (mu_out) FK_CUDA(cudaMemcpyAsync(mu_out, h->mu.ptr, sizeof(double) * (size_t)h->nt, cudaMemcpyDeviceToHost, h->stream));
     if (dmu_out) FK_CUDA(cudaMemcpyAsync(dmu_out, h->dmu.ptr, sizeof(double) * (size_t)h->nt, cudaMemcpyDeviceToHost, h->stream));
     FK_CUDA(cudaStreamSynchronize(h->stream));
+    return 0;
+  });
+}
+int fk_reset_field(fk_handle h) {
+  return guard([&]() {
+    need(h, "fk: NULL handle");
+    DeviceGuard dg(h->device);
+    if (!h->mu.ptr) { ensure_state(h); return 0; }
+    FK_CUDA(cudaMemsetAsync(h->dmu.ptr, 0, sizeof(double) * (size_t)h->nt, h->stream));
+    FK_CUDA(cudaMemsetAsync(h->Hn.ptr, 0, sizeof(double) * (size_t)h->nt, h->stream));
+    FK_CUDA(cudaMemsetAsync(h->Hfield.ptr, 0, sizeof(double) * (size_t)3 * h->nt, h->stream));
     return 0;
   });
 }

@@ -85,7 +85,11 @@ struct fk_handle_s {
   fk::SplineSet spl{};
   bool have_material = false;
   // PCG workspace
-  fk::DevBuf<double> x, r, p, Ap, dinv, part, bvec;
+  fk::DevBuf<double> pcg_slab;         // x | r | p | Ap | dinv in ONE allocation: a single L2 access-policy window covers them
+  struct VecView { double* ptr = nullptr; } x, r, p, Ap, dinv;
+  bool l2_persist = true, l2_window_set = false;
+  cudaAccessPolicyWindow l2_window{};
+  fk::DevBuf<double> part, bvec;
   fk::DevBuf<fk::PcgCtl> ctl;
   fk::PcgCtl* ctl_host = nullptr;      // pinned
   int grid_spmv = 0, grid_vec = 0;

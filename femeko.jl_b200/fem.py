@@ -243,6 +243,10 @@ class Femeko:
         L.check(self.lib.fk_get_field(self.h, L.dptr(Hf), L.dptr(Hn)))
         return Hf, Hn
 
+    def reset_field(self):
+        """|H|_old = 0 (the `Hold = zeros(nt)` a nonlinear solve starts from, NewtonRaphson.jl:139-140)."""
+        L.check(self.lib.fk_reset_field(self.h))
+
     def picard_step(self, u, slot=0, compat_bug=False):
         """Fused sweep: H from u, div = mu0*max|dH|, mu = spl(|H|), stiffness(mu) -> slot.  Returns div.
         Raises FemekoError("Nans/Infs in mu") / out-of-range errors like the reference does."""

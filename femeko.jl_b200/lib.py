@@ -99,6 +99,7 @@ _SIGS = {
     "fk_set_mu": (C.c_int, [_H, c_double_p]),
     "fk_get_mu": (C.c_int, [_H, c_double_p, c_double_p]),
     "fk_get_field": (C.c_int, [_H, c_double_p, c_double_p]),
+    "fk_reset_field": (C.c_int, [_H]),
     "fk_picard_step": (C.c_int, [_H, C.c_int, c_double_p, C.c_int, c_double_p]),
     "fk_picard_step_dev": (C.c_int, [_H, C.c_int, C.c_void_p, C.c_int, c_double_p]),
     "fk_nccl_unique_id": (C.c_int, [c_ubyte_p]),

@@ -71,8 +71,9 @@ int fk_destroy(fk_handle h);
  * issued on it.                                                                                  */
 int fk_set_stream(fk_handle h, void* stream);
 int fk_synchronize(fk_handle h);
-/* change a launch-shape option after creation (tuning sweeps): what 0 = asm_cfg, 1 = spmv_ctas_per_sm;
- * values as in fk_create_opts.  Matrix values do not depend on these.                            */
+/* change a launch option after creation (tuning sweeps): what 0 = asm_cfg, 1 = spmv_ctas_per_sm (values
+ * as in fk_create_opts), 2 = pin the PCG vectors in L2 with a persisting access-policy window (1 = on,
+ * the default; 0 = off).  Matrix values do not depend on these.                                    */
 int fk_tune(fk_handle h, int what, int value);
 /* number of kernels of this library launched through the handle so far (graph nodes included) */
 int fk_launch_count(fk_handle h, long long* n);
@@ -166,6 +167,9 @@ int fk_set_inside(fk_handle h, const int* ids, int n);
 int fk_set_mu(fk_handle h, const double* mu /* nt */);
 int fk_get_mu(fk_handle h, double* mu_out, double* dmu_out /* may be NULL */);
 int fk_get_field(fk_handle h, double* Hfield_out, double* Hnorm_out);
+/* forget the stored field (|H|_old = 0, Hfield = 0, dmu = 0): the state a fresh nonlinear solve starts
+ * from (`Hold = zeros(nt)`, NewtonRaphson.jl:139-140); mu is left as set by fk_set_mu.             */
+int fk_reset_field(fk_handle h);
 /* One fused nonlinear sweep over the elements (manyBodyIntersecting.jl:156-207 + :147, or
  * NewtonRaphson.jl:178-207 + :153-161): from the potential u recover H and |H|, div =
  * mu0*max_{material}| |H| - |H|_old |, mu = spl(|H|) (and dmu) on material elements, and assemble

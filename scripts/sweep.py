@@ -92,13 +92,21 @@ def main():
                 x = torch.zeros(h.nv, dtype=torch.float64, device=dev)
                 y = torch.zeros(h.nv, dtype=torch.float64, device=dev)
                 y0 = x0 = None
+                try:
+                    from cuda.bindings import runtime as crt
+                    emit({"kind": "l2", "max_persist": int(crt.cudaDeviceGetAttribute(crt.cudaDeviceAttr.cudaDevAttrMaxPersistingL2CacheSize, 0)[1]),
+                          "max_window": int(crt.cudaDeviceGetAttribute(crt.cudaDeviceAttr.cudaDevAttrMaxAccessPolicyWindowSize, 0)[1]),
+                          "l2": int(crt.cudaDeviceGetAttribute(crt.cudaDeviceAttr.cudaDevAttrL2CacheSize, 0)[1])})
+                except Exception as e:  # noqa: BLE001
+                    emit({"kind": "l2", "error": str(e)})
                 for ctas in [int(v) for v in args.stages.split(",")]:
                     try:
-                        h.tune(1, ctas)
+                        h.tune(1, max(ctas, 0))
+                        h.tune(2, 0 if ctas < 0 else 1)   # ctas = -1: default grid with the L2 window off
                         ms_spmv = timed(stream, lambda: h.spmv_dev(b.data_ptr(), y.data_ptr(), slot=0), 20)
                         yv = y.cpu().numpy().copy()
                         kw = dict(max_iter=100, tol_disable=True, check_every=100)
-                        ms_pcg = timed(stream, lambda: h.pcg_dev(b.data_ptr(), x.data_ptr(), slot=0, **kw), 5)
+                        ms_pcg = timed(stream, lambda: h.pcg_dev(b.data_ptr(), x.data_ptr(), slot=0, **kw), 20)
                         xv = x.cpu().numpy().copy()
                         if y0 is None:
                             y0, x0 = yv, xv
