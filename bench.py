@@ -318,7 +318,9 @@ def run_ours(args):
                                    f"{Piters} Jacobi-PCG iterations per step (fixed count, x0=0)",
                        "tets_total": world_tets, "rows_total": world_rows, "nnz_total": world_nnz, "pcg_iters_per_step": Piters,
                        "l2": "inputs larger than L2 (CSR values+indices %.0f MB per GPU vs 126 MB L2)" % (12 * nnz / 1e6),
-                       "parallelism": "single GPU" if world == 1 else f"node-partitioned slabs x{world}, NCCL halo+allreduce"},
+                       "parallelism": "single GPU" if world == 1 else
+                       f"node-partitioned slabs x{world}, " + ("halo rows + all-reduce over NVLink peer memory inside the PCG kernels"
+                                                                if h.comm_mode() == 2 else "NCCL send/recv halo + ncclAllReduce")},
             "components": {"picard_assembly_ms": round(asm_ms, 4), "picard_assembly_mtets_per_s": round(nt / asm_ms / 1e3, 1),
                            "pcg_ms": round(pcg_ms, 4), "pcg_iters_per_s": round(Piters / (pcg_ms * 1e-3), 1),
                            "setup_s_untimed": round(setup_s, 2), "linear_presolve_iters": it0},

@@ -148,12 +148,14 @@ static void ensure_state(fk_handle h) {
 void launch_spmv(fk_handle h, cudaStream_t s, const double* vals, const double* x, double* y, bool dot, const PcgCtl* ctl,
                  int j) {
   if (h->sym.nslices <= 0) return;
-  if (dot)
+  if (dot) {  // partitioned: p.Ap is finished (and all-reduced over peer memory) inside the kernel -> scal[0]
+    const RedArgs ra = h->comm ? comm_red_args(h, h->tickets.ptr, h->scal.ptr, 0) : RedArgs{};
     spmv_sell_kernel<true><<<h->grid_spmv, kSpmvThreads, 0, s>>>(h->slice_ptr.ptr, h->srow.ptr, h->sell_col.ptr, vals, x, y,
-                                                                 h->sym.nslices, h->part.ptr, ctl, j);
-  else
+                                                                 h->sym.nslices, h->part.ptr, ra, ctl, j);
+  } else {
     spmv_sell_kernel<false><<<h->grid_spmv, kSpmvThreads, 0, s>>>(h->slice_ptr.ptr, h->srow.ptr, h->sell_col.ptr, vals, x, y,
-                                                                  h->sym.nslices, nullptr, ctl, j);
+                                                                  h->sym.nslices, nullptr, RedArgs{}, ctl, j);
+  }
   FK_CUDA(cudaGetLastError());
 }
 
@@ -182,7 +184,7 @@ static void configure_l2(fk_handle h) {
   cudaDeviceGetAttribute(&max_window, cudaDevAttrMaxAccessPolicyWindowSize, h->device);
   cudaStreamAttrValue attr{};
   if (h->l2_persist && max_persist > 0 && max_window > 0) {
-    const size_t bytes = h->pcg_slab.count * sizeof(double);
+    const size_t bytes = 5 * h->slab_stride * sizeof(double);   // x r p Ap dinv (not the Picard staging vector)
     const size_t win = std::min(bytes, (size_t)max_window);
     const size_t persist = std::min(win, (size_t)max_persist);
     if (cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, persist) != cudaSuccess) { cudaGetLastError(); return; }
@@ -203,35 +205,52 @@ static void configure_l2(fk_handle h) {
     if (h->graph[s]) { cudaGraphExecDestroy(h->graph[s]); h->graph[s] = nullptr; }
 }
 
-static void ensure_pcg(fk_handle h) {
+void ensure_pcg(fk_handle h) {
   if (h->x.ptr) return;
   const size_t nvec = (size_t)h->nv;  // vectors carry halo rows too (SpMV input)
   const size_t stride = (nvec + 31) & ~(size_t)31;
-  h->pcg_slab.ensure(5 * stride);
+  h->slab_stride = stride;
+  h->pcg_slab.ensure(6 * stride + 128);   // + the 128-word control block of the peer-memory path (comm.cu)
   h->x.ptr = h->pcg_slab.ptr;
   h->r.ptr = h->x.ptr + stride;
   h->p.ptr = h->r.ptr + stride;
   h->Ap.ptr = h->p.ptr + stride;
   h->dinv.ptr = h->Ap.ptr + stride;
+  h->u.ptr = h->dinv.ptr + stride;
   configure_l2(h);
   h->bvec.ensure(nvec);
   h->part.ensure((size_t)4 * std::max(h->grid_spmv, h->grid_vec) + 16);
   h->ctl.ensure(1);
   h->scal.ensure(8);
-  FK_CUDA(cudaMemsetAsync(h->pcg_slab.ptr, 0, 5 * stride * sizeof(double), h->stream));
+  h->tickets.ensure(8);
+  FK_CUDA(cudaMemsetAsync(h->tickets.ptr, 0, 8 * sizeof(unsigned int), h->stream));
+  FK_CUDA(cudaMemsetAsync(h->pcg_slab.ptr, 0, (6 * stride + 128) * sizeof(double), h->stream));
   if (!h->ctl_host) FK_CUDA(cudaMallocHost((void**)&h->ctl_host, sizeof(PcgCtl)));
 }
 
-// one PCG iteration (index j inside a chunk) issued into stream s; single-GPU form
+// One PCG iteration (index j inside a chunk) issued into stream s.  Three kernels on one GPU; on a partitioned
+// problem the halo rows of p are exchanged first (two more kernels over peer memory) and the dot products
+// are all-reduced inside the SpMV / update kernels.  NCCL fallback: halo by send/recv, all-reduce by NCCL.
 static void issue_iteration(fk_handle h, cudaStream_t s, const double* vals, int j) {
   const int n = h->n_rows;
   PcgCtl* ctl = h->ctl.ptr;
   double* part = h->part.ptr;
+  double* scal = h->scal.ptr;
   const int gs = h->grid_spmv, gv = h->grid_vec;
-  launch_spmv(h, s, vals, h->p.ptr, h->Ap.ptr, true, ctl, j);
-  pcg_update_kernel<<<gv, kVecThreads, 0, s>>>(h->x.ptr, h->r.ptr, h->p.ptr, h->Ap.ptr, h->dinv.ptr, n, part, gs,
-                                               part + gs, ctl, j);
-  pcg_direction_kernel<<<gv, kVecThreads, 0, s>>>(h->p.ptr, h->r.ptr, h->dinv.ptr, n, part + gs, gv, gv, ctl, j);
+  if (h->comm) {
+    comm_halo_exchange(h, s, h->p.ptr);
+    launch_spmv(h, s, vals, h->p.ptr, h->Ap.ptr, true, ctl, j);                    // -> scal[0] = p.Ap (this GPU / all ranks)
+    comm_nccl_allreduce(h, s, scal, 1, 0);
+    pcg_update_kernel<<<gv, kVecThreads, 0, s>>>(h->x.ptr, h->r.ptr, h->p.ptr, h->Ap.ptr, h->dinv.ptr, n, scal, 1, part + gs,
+                                                 comm_red_args(h, h->tickets.ptr + 1, scal + 1, 0), ctl, j);   // -> scal[1..2] = r.r, r.z
+    comm_nccl_allreduce(h, s, scal + 1, 2, 0);
+    pcg_direction_kernel<<<gv, kVecThreads, 0, s>>>(h->p.ptr, h->r.ptr, h->dinv.ptr, n, scal + 1, 1, 1, ctl, j);
+  } else {  // one GPU: the consumers fold the per-CTA partials themselves
+    launch_spmv(h, s, vals, h->p.ptr, h->Ap.ptr, true, ctl, j);
+    pcg_update_kernel<<<gv, kVecThreads, 0, s>>>(h->x.ptr, h->r.ptr, h->p.ptr, h->Ap.ptr, h->dinv.ptr, n, part, gs, part + gs,
+                                                 RedArgs{}, ctl, j);
+    pcg_direction_kernel<<<gv, kVecThreads, 0, s>>>(h->p.ptr, h->r.ptr, h->dinv.ptr, n, part + gs, gv, gv, ctl, j);
+  }
   FK_CUDA(cudaGetLastError());
 }
 
@@ -243,6 +262,7 @@ static void build_graph(fk_handle h, int slot, int chunk) {
   }
   if (!h->cap_stream) FK_CUDA(cudaStreamCreateWithFlags(&h->cap_stream, cudaStreamNonBlocking));
   cudaGraph_t g = nullptr;
+  const long long launches0 = h->launches;   // capturing is not launching
   FK_CUDA(cudaStreamBeginCapture(h->cap_stream, cudaStreamCaptureModeThreadLocal));
   try {
     for (int j = 0; j < chunk; j++) issue_iteration(h, h->cap_stream, h->vals[slot].ptr, j);
@@ -253,6 +273,7 @@ static void build_graph(fk_handle h, int slot, int chunk) {
     throw;
   }
   FK_CUDA(cudaStreamEndCapture(h->cap_stream, &g));
+  h->launches = launches0;
   {  // the L2 policy window is a per-launch attribute: put it on every kernel node of the chunk
     size_t nn = 0;
     FK_CUDA(cudaGraphGetNodes(g, nullptr, &nn));
@@ -300,34 +321,36 @@ static void pcg_dev(fk_handle h, int slot, const double* b_dev, double* x_dev, c
   } else {
     FK_CUDA(cudaMemsetAsync(h->x.ptr, 0, sizeof(double) * (size_t)n, s));
   }
-  pcg_init_kernel<<<gv, kVecThreads, 0, s>>>(b_dev, Ax0, h->dinv.ptr, n, h->r.ptr, h->p.ptr, h->part.ptr);
   if (h->comm) {
-    fold_partials_kernel<<<1, 256, 0, s>>>(h->part.ptr, gv, gv, 3, h->scal.ptr);
-    comm_allreduce_sum(h, s, h->scal.ptr, 3);
-    pcg_init_fin_kernel<<<1, 256, 0, s>>>(h->scal.ptr, 1, 1, tol, max_iter, h->ctl.ptr);
-    h->launches++;
+    pcg_init_kernel<<<gv, kVecThreads, 0, s>>>(b_dev, Ax0, h->dinv.ptr, n, h->r.ptr, h->p.ptr, h->part.ptr,
+                                               comm_red_args(h, h->tickets.ptr + 2, h->scal.ptr + 4, 0));   // -> scal[4..6] = b.b, r.r, r.p
+    comm_nccl_allreduce(h, s, h->scal.ptr + 4, 3, 0);
+    pcg_init_fin_kernel<<<1, 256, 0, s>>>(h->scal.ptr + 4, 1, 1, tol, max_iter, h->ctl.ptr);
   } else {
+    pcg_init_kernel<<<gv, kVecThreads, 0, s>>>(b_dev, Ax0, h->dinv.ptr, n, h->r.ptr, h->p.ptr, h->part.ptr, RedArgs{});
     pcg_init_fin_kernel<<<1, 256, 0, s>>>(h->part.ptr, gv, gv, tol, max_iter, h->ctl.ptr);
   }
   FK_CUDA(cudaGetLastError());
   h->launches += 3;
 
-  if (!h->comm) build_graph(h, slot, chunk);
+  const bool graphed = !h->comm || comm_capturable(h);
+  if (graphed) build_graph(h, slot, chunk);
   int launched = 0;
   while (true) {
-    if (h->comm) {
-      for (int j = 0; j < chunk; j++) comm_issue_iteration(h, s, h->vals[slot].ptr, j);
+    if (!graphed) {
+      for (int j = 0; j < chunk; j++) issue_iteration(h, s, h->vals[slot].ptr, j);
       pcg_advance_kernel<<<1, 1, 0, s>>>(h->ctl.ptr, chunk);
-      h->launches += (long long)chunk * 6 + 1;
+      h->launches += (long long)chunk * 3 + 1;   // the halo pack kernel is counted in comm_halo_exchange
     } else {
       FK_CUDA(cudaGraphLaunch(h->graph[slot], s));
-      h->launches += (long long)chunk * 3 + 1;
+      h->launches += (long long)chunk * (h->comm ? 5 : 3) + 1;
     }
     launched += chunk;
     FK_CUDA(cudaMemcpyAsync(h->ctl_host, h->ctl.ptr, sizeof(PcgCtl), cudaMemcpyDeviceToHost, s));
     FK_CUDA(cudaStreamSynchronize(s));
     if (h->ctl_host->done || launched >= max_iter) break;
   }
+  if (h->comm) comm_check(h);
   const PcgCtl& c = *h->ctl_host;
   const int iters = c.done ? c.iters : max_iter;
   if (c.rhs2 == 0.0) {  // x = 0 (ConjugateGradient.h:43-49)
@@ -622,7 +645,7 @@ int fk_device_ptr(fk_handle h, int which, void** ptr) {
       case 3: *ptr = h->mu.ptr; break;
       case 4: *ptr = h->Hn.ptr; break;
       case 5: *ptr = h->Hfield.ptr; break;
-      case 6: h->u.ensure((size_t)h->nv); *ptr = h->u.ptr; break;
+      case 6: ensure_pcg(h); *ptr = h->u.ptr; break;
       case 7: *ptr = h->dmu.ptr; break;
       default: throw std::runtime_error("fk_device_ptr: unknown array id");
     }
@@ -1112,6 +1135,13 @@ static int picard_step_dev(fk_handle h, int slot, const double* u_dev, int compa
   ensure_state(h);
   AsmArgs a = base_args(h, slot_vals(h, slot));
   a.u = u_dev;
+  if (h->comm) {  // partitions: the sweep reads the potential on halo nodes too -> refresh them from their owners
+    ensure_pcg(h);
+    if (u_dev != h->u.ptr)
+      FK_CUDA(cudaMemcpyAsync(h->u.ptr, u_dev, sizeof(double) * (size_t)h->n_rows, cudaMemcpyDeviceToDevice, h->stream));
+    comm_halo_exchange(h, h->stream, h->u.ptr);
+    a.u = h->u.ptr;
+  }
   a.mu = h->mu.ptr;
   a.dmu = h->dmu.ptr;
   a.Hn = h->Hn.ptr;
@@ -1122,9 +1152,8 @@ static int picard_step_dev(fk_handle h, int slot, const double* u_dev, int compa
   a.compat = compat_bug;
   FK_CUDA(cudaMemsetAsync(h->errflag.ptr, 0, sizeof(int), h->stream));
   launch_assemble<ASM_PICARD>(h, a);
-  max_array_kernel<<<1, 256, 0, h->stream>>>(h->tile_max.ptr, h->sym.ntiles, h->scal.ptr);
-  FK_CUDA(cudaGetLastError());
-  h->launches++;
+  // div = mu0 * max over every rank's material elements (NewtonRaphson.jl:200)
+  comm_allreduce_partials(h, h->stream, h->tile_max.ptr, h->sym.ntiles, h->sym.ntiles, 1, 1, h->scal.ptr, nullptr, 0);
   double dmax = 0.0;
   int err = 0;
   FK_CUDA(cudaMemcpyAsync(&dmax, h->scal.ptr, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
@@ -1146,7 +1175,8 @@ int fk_picard_step(fk_handle h, int slot, const double* u, int compat_bug, doubl
   return guard([&]() {
     need(h && u, "fk: NULL argument");
     DeviceGuard dg(h->device);
-    h->u.upload(u, (size_t)h->nv, h->stream);
+    ensure_pcg(h);
+    FK_CUDA(cudaMemcpyAsync(h->u.ptr, u, sizeof(double) * (size_t)h->nv, cudaMemcpyHostToDevice, h->stream));
     return picard_step_dev(h, slot, h->u.ptr, compat_bug, div_out);
   });
 }

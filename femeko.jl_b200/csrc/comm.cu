@@ -5,6 +5,8 @@
 #include <nccl.h>
 
 #include <algorithm>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 
 #include "comm.hpp"
@@ -57,6 +59,23 @@ static NcclApi& nccl() {
       throw std::runtime_error(std::string("NCCL error: ") + nccl().GetErrorString(r_) + " (" #call ")"); \
   } while (0)
 
+constexpr int kPushCtas = 16;     // CTAs per neighbour of the halo push
+
+// Peer-memory state of the fused path.  Every rank exports (CUDA IPC) its PCG vector slab and a small
+// control block; peers write halo rows straight into the owner's vector and reduction operands straight
+// into the owner's mailbox over NVLink, each followed by a system-scope release of a sequence flag.
+struct P2P {
+  bool on = false;
+  void* peer_slab[kMaxRanks] = {};                 // peer r's pcg_slab (own rank: local pointer)
+  unsigned long long* peer_ctrl[kMaxRanks] = {};   // peer r's control block
+  size_t peer_stride[kMaxRanks] = {};              // doubles between consecutive vectors of peer r's slab
+  bool opened_slab[kMaxRanks] = {};
+  int remote_start[kMaxNeigh] = {};                // where my rows land in neighbour q's vectors
+  int remote_slot[kMaxNeigh] = {};                 // my index in neighbour q's neighbour list (its flag slot for me)
+  unsigned long long* ctrl = nullptr;              // my control block: the kCtrlWords words after the 6 slab vectors
+  DevBuf<unsigned long long*> peer_ctrl_dev;       // device copy of peer_ctrl
+};
+
 struct Comm {
   ncclComm_t comm = nullptr;
   int rank = 0, nranks = 1;
@@ -66,22 +85,113 @@ struct Comm {
   DevBuf<int> send_idx;
   DevBuf<double> sendbuf;
   bool have_halo = false;
+  P2P p2p;
 };
+
+// ---- peer-memory kernels --------------------------------------------------------------------------
+struct HaloPushArgs {
+  const double* v;                       // local vector (owned rows are read)
+  const int* send_idx;
+  int send_ptr[kMaxNeigh + 1];
+  double* dst[kMaxNeigh];                // neighbour q's copy of the vector, at the rows it receives from me
+  unsigned long long* flag[kMaxNeigh];   // neighbour q's halo flag for me
+  unsigned long long* my_ctrl;           // sequence number = my count of executed exchanges + 1 (same on every rank)
+  int nneigh;
+};
+// grid (kPushCtas, nneigh): gather my boundary rows and store them into the neighbour's halo rows over NVLink
+static __global__ void __launch_bounds__(256) halo_push_kernel(const HaloPushArgs a) {
+  const int q = blockIdx.y;
+  const int b = a.send_ptr[q], n = a.send_ptr[q + 1] - b;
+  double* dst = a.dst[q];
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) dst[i] = a.v[__ldg(a.send_idx + b + i)];
+}
+// one warp, stream-ordered after the push: release my rows to every neighbour (the push kernel has completed, so
+// its stores precede this system-scope release), wait for every neighbour's rows, advance the exchange counter
+static __global__ void halo_sync_kernel(const HaloPushArgs a) {
+  const unsigned long long seq = a.my_ctrl[kOffHaloCnt] + 1ULL;
+  __syncwarp();
+  if ((int)threadIdx.x < a.nneigh) {
+    __threadfence_system();
+    st_release_sys(a.flag[threadIdx.x], seq);
+    spin_until(a.my_ctrl + threadIdx.x, seq, a.my_ctrl + kOffErr);
+  }
+  __syncwarp();
+  if (threadIdx.x == 0) a.my_ctrl[kOffHaloCnt] = seq;
+}
+
+// stand-alone all-reduce of folded per-CTA partials (the Picard sweep's max): same protocol as the in-kernel one
+static __global__ void __launch_bounds__(256) allreduce_p2p_kernel(const double* __restrict__ part, int npart, int stride, int nvals,
+                                                             const RedArgs ra) {
+  __shared__ double red[33];
+  __shared__ double val[3];
+  for (int v = 0; v < nvals; v++) {
+    double s = (ra.op == 0) ? 0.0 : -DBL_MAX;
+    for (int i = threadIdx.x; i < npart; i += blockDim.x) {
+      const double x = part[(size_t)v * stride + i];
+      s = (ra.op == 0) ? s + x : fmax(s, x);
+    }
+    s = (ra.op == 0) ? block_sum(s, red) : block_max(s, red);
+    if (threadIdx.x == 0) val[v] = s;
+  }
+  __syncthreads();
+  peer_allreduce(val, nvals, ra);
+  if ((int)threadIdx.x < nvals) ra.out[threadIdx.x] = val[threadIdx.x];
+}
 
 void comm_destroy(fk_handle_s* h) {
   if (!h->comm) return;
+  P2P& P = h->comm->p2p;
+  for (int r = 0; r < kMaxRanks; r++) {
+    if (P.opened_slab[r]) cudaIpcCloseMemHandle(P.peer_slab[r]);
+  }
   if (h->comm->comm) nccl().CommDestroy(h->comm->comm);
   delete h->comm;
   h->comm = nullptr;
 }
 
+static void check_comm_error(fk_handle_s* h) {  // called at host sync points
+  Comm* c = h->comm;
+  if (!c || !c->p2p.on) return;
+  unsigned long long e = 0;
+  FK_CUDA(cudaMemcpyAsync(&e, c->p2p.ctrl + kOffErr, sizeof(e), cudaMemcpyDeviceToHost, h->stream));
+  FK_CUDA(cudaStreamSynchronize(h->stream));
+  if (e) throw std::runtime_error("fk: a peer GPU did not answer within the timeout (halo / all-reduce over NVLink)");
+}
+void comm_check(fk_handle_s* h) { check_comm_error(h); }
+bool comm_capturable(fk_handle_s* h) { return h->comm && h->comm->p2p.on; }
+
+// Fill the halo rows of `v` (a vector inside the PCG slab) from their owners.
 void comm_halo_exchange(fk_handle_s* h, cudaStream_t s, double* v) {
   Comm* c = h->comm;
   if (!c || !c->have_halo || c->nneigh == 0) return;
+  if (c->p2p.on) {
+    P2P& P = c->p2p;
+    const size_t off = (size_t)(v - h->pcg_slab.ptr);
+    const size_t vec = off / h->slab_stride;           // which slab vector (the stride differs from rank to rank)
+    if (v < h->pcg_slab.ptr || vec >= 6 || off != vec * h->slab_stride)
+      throw std::runtime_error("fk: halo exchange of a vector outside the PCG slab");
+    HaloPushArgs a{};
+    a.v = v;
+    a.send_idx = c->send_idx.ptr;
+    a.my_ctrl = P.ctrl;
+    for (int q = 0; q <= c->nneigh; q++) a.send_ptr[q] = c->send_ptr[q];
+    for (int q = 0; q < c->nneigh; q++) {
+      const int nb = c->neigh_rank[q];
+      a.dst[q] = static_cast<double*>(P.peer_slab[nb]) + vec * P.peer_stride[nb] + P.remote_start[q];
+      a.flag[q] = P.peer_ctrl[nb] + P.remote_slot[q];
+    }
+    a.nneigh = c->nneigh;
+    halo_push_kernel<<<dim3(kPushCtas, c->nneigh), 256, 0, s>>>(a);
+    halo_sync_kernel<<<1, 32, 0, s>>>(a);
+    FK_CUDA(cudaGetLastError());
+    h->launches += 2;
+    return;
+  }
   const int nsend = c->send_ptr[c->nneigh];
   if (nsend > 0) {
     pack_kernel<<<(nsend + 255) / 256, 256, 0, s>>>(v, c->send_idx.ptr, nsend, c->sendbuf.ptr);
     FK_CUDA(cudaGetLastError());
+    h->launches++;
   }
   FK_NCCL(nccl().GroupStart());
   for (int q = 0; q < c->nneigh; q++) {
@@ -93,37 +203,45 @@ void comm_halo_exchange(fk_handle_s* h, cudaStream_t s, double* v) {
   FK_NCCL(nccl().GroupEnd());
 }
 
-void comm_allreduce_sum(fk_handle_s* h, cudaStream_t s, double* v, int n) {
+// out[0..nvals) = reduce over ranks of (fold of this rank's per-CTA partials part[v*stride + 0..npart)).
+void comm_allreduce_partials(fk_handle_s* h, cudaStream_t s, const double* part, int npart, int stride, int nvals, int op, double* out,
+                             const PcgCtl* ctl, int j) {
   Comm* c = h->comm;
+  if (c && c->nranks > 1 && c->p2p.on) {
+    P2P& P = c->p2p;
+    RedArgs ra{nullptr, out, op, c->rank, c->nranks, P.peer_ctrl_dev.ptr, P.ctrl};
+    allreduce_p2p_kernel<<<1, 256, 0, s>>>(part, npart, stride, nvals, ra);
+    FK_CUDA(cudaGetLastError());
+    h->launches++;
+    return;
+  }
+  if (op == 0) fold_partials_kernel<<<1, 256, 0, s>>>(part, npart, stride, nvals, out);
+  else max_array_kernel<<<1, 256, 0, s>>>(part, npart, out);
+  FK_CUDA(cudaGetLastError());
+  h->launches++;
   if (!c || c->nranks == 1) return;
-  FK_NCCL(nccl().AllReduce(v, v, (size_t)n, ncclDouble, ncclSum, c->comm, s));
-}
-void comm_allreduce_max(fk_handle_s* h, cudaStream_t s, double* v, int n) {
-  Comm* c = h->comm;
-  if (!c || c->nranks == 1) return;
-  FK_NCCL(nccl().AllReduce(v, v, (size_t)n, ncclDouble, ncclMax, c->comm, s));
+  FK_NCCL(nccl().AllReduce(out, out, (size_t)nvals, ncclDouble, op == 0 ? ncclSum : ncclMax, c->comm, s));
 }
 
-// One PCG iteration with the two exchanges: halo rows of p before the SpMV, and the all-reduce of
-// p.Ap, then of (r.r, r.z).  The per-CTA partial sums are folded on the device first, so each
-// all-reduce carries 1-2 doubles; the update/direction kernels then read the reduced scalars
-// (npart == 1) instead of the partial arrays.
-void comm_issue_iteration(fk_handle_s* h, cudaStream_t s, const double* vals, int j) {
-  const int n = h->n_rows;
-  PcgCtl* ctl = h->ctl.ptr;
-  double* part = h->part.ptr;
-  double* scal = h->scal.ptr;
-  const int gs = h->grid_spmv, gv = h->grid_vec;
-  comm_halo_exchange(h, s, h->p.ptr);
-  launch_spmv(h, s, vals, h->p.ptr, h->Ap.ptr, true, ctl, j);
-  fold_partials_kernel<<<1, 256, 0, s>>>(part, gs, gs, 1, scal);
-  comm_allreduce_sum(h, s, scal, 1);
-  pcg_update_kernel<<<gv, kVecThreads, 0, s>>>(h->x.ptr, h->r.ptr, h->p.ptr, h->Ap.ptr, h->dinv.ptr, n, scal, 1, part + gs, ctl, j);
-  fold_partials_kernel<<<1, 256, 0, s>>>(part + gs, gv, gv, 2, scal + 1);
-  comm_allreduce_sum(h, s, scal + 1, 2);
-  pcg_direction_kernel<<<gv, kVecThreads, 0, s>>>(h->p.ptr, h->r.ptr, h->dinv.ptr, n, scal + 1, 1, 1, ctl, j);
-  FK_CUDA(cudaGetLastError());
+// reduction descriptor of the in-kernel grid reductions (kernels.cuh): peer memory when attached, else local
+RedArgs comm_red_args(fk_handle_s* h, unsigned int* ticket, double* out, int op) {
+  RedArgs ra{ticket, out, op, 0, 1, nullptr, nullptr};
+  Comm* c = h->comm;
+  if (c && c->nranks > 1 && c->p2p.on) {
+    ra.rank = c->rank;
+    ra.nranks = c->nranks;
+    ra.peer_ctrl = c->p2p.peer_ctrl_dev.ptr;
+    ra.my_ctrl = c->p2p.ctrl;
+  }
+  return ra;
 }
+// NCCL fallback: the kernels reduced over this GPU only; finish over the ranks with ncclAllReduce
+void comm_nccl_allreduce(fk_handle_s* h, cudaStream_t s, double* v, int n, int op) {
+  Comm* c = h->comm;
+  if (!c || c->nranks == 1 || c->p2p.on) return;
+  FK_NCCL(nccl().AllReduce(v, v, (size_t)n, ncclDouble, op == 0 ? ncclSum : ncclMax, c->comm, s));
+}
+int comm_kind(fk_handle_s* h) { return !h->comm ? 0 : (h->comm->p2p.on ? 2 : 1); }
 
 }  // namespace fk
 
@@ -199,6 +317,83 @@ int fk_set_halo(fk_handle h, int n_owned, int nneigh, const int* neigh_rank, con
     set_error(e.what());
     return 1;
   }
+}
+
+// ---- peer-memory (CUDA IPC over NVLink) fused path ---------------------------------------------------
+// export (128 bytes): the 64-byte IPC handle of the PCG vector slab -- the control block lives in the same
+// allocation, right after the six vectors, so one mapping per peer suffices -- then the slab stride (u64)
+int fk_comm_p2p_export(fk_handle h, unsigned char* handles128) {
+  try {
+    if (!h || !handles128) throw std::runtime_error("fk: NULL argument");
+    if (!h->comm) throw std::runtime_error("fk_comm_p2p_export: call fk_comm_init first");
+    FK_CUDA(cudaSetDevice(h->device));
+    ensure_pcg(h);
+    P2P& P = h->comm->p2p;
+    P.ctrl = reinterpret_cast<unsigned long long*>(h->pcg_slab.ptr + 6 * h->slab_stride);
+    FK_CUDA(cudaMemset(P.ctrl, 0, kCtrlWords * sizeof(unsigned long long)));
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t is expected to be 64 bytes");
+    cudaIpcMemHandle_t a;
+    FK_CUDA(cudaIpcGetMemHandle(&a, h->pcg_slab.ptr));
+    std::memset(handles128, 0, 128);
+    std::memcpy(handles128, &a, 64);
+    const unsigned long long stride = h->slab_stride;
+    std::memcpy(handles128 + 64, &stride, 8);
+    return 0;
+  } catch (const std::exception& e) {
+    set_error(e.what());
+    return 1;
+  }
+}
+
+// attach: exports of ALL ranks (nranks x 128 bytes, rank order); for each neighbour q of this rank,
+// remote_start[q] = first row of neighbour q's vectors that receives my rows, remote_slot[q] = my index in
+// neighbour q's neighbour list.  From here on the halo exchange and the all-reduces run over peer memory.
+int fk_comm_p2p_attach(fk_handle h, const unsigned char* all_handles, const int* remote_start, const int* remote_slot) {
+  try {
+    if (!h || !all_handles) throw std::runtime_error("fk: NULL argument");
+    Comm* c = h->comm;
+    if (!c || !c->have_halo) throw std::runtime_error("fk_comm_p2p_attach: call fk_comm_init and fk_set_halo first");
+    if (c->nranks > kMaxRanks || c->nneigh > kMaxNeigh) throw std::runtime_error("fk_comm_p2p_attach: too many ranks / neighbours");
+    if (c->nneigh > 0 && !(remote_start && remote_slot)) throw std::runtime_error("fk: NULL argument");
+    FK_CUDA(cudaSetDevice(h->device));
+    P2P& P = c->p2p;
+    if (!P.ctrl) throw std::runtime_error("fk_comm_p2p_attach: call fk_comm_p2p_export first");
+    for (int r = 0; r < c->nranks; r++) {
+      unsigned long long stride = 0;
+      std::memcpy(&stride, all_handles + (size_t)r * 128 + 64, 8);
+      P.peer_stride[r] = (size_t)stride;
+      if (r == c->rank) {
+        P.peer_slab[r] = h->pcg_slab.ptr;
+      } else {
+        cudaIpcMemHandle_t a;
+        std::memcpy(&a, all_handles + (size_t)r * 128, 64);
+        void* pa = nullptr;
+        FK_CUDA(cudaIpcOpenMemHandle(&pa, a, cudaIpcMemLazyEnablePeerAccess));
+        P.peer_slab[r] = pa;
+        P.opened_slab[r] = true;
+      }
+      P.peer_ctrl[r] = reinterpret_cast<unsigned long long*>(static_cast<double*>(P.peer_slab[r]) + 6 * P.peer_stride[r]);
+    }
+    for (int q = 0; q < c->nneigh; q++) {
+      if (remote_start[q] < 0 || remote_slot[q] < 0 || remote_slot[q] >= kMaxNeigh) throw std::runtime_error("fk_comm_p2p_attach: bad remote plan");
+      P.remote_start[q] = remote_start[q];
+      P.remote_slot[q] = remote_slot[q];
+    }
+    std::vector<unsigned long long*> ptrs(P.peer_ctrl, P.peer_ctrl + kMaxRanks);
+    P.peer_ctrl_dev.upload(ptrs, h->stream);
+    FK_CUDA(cudaStreamSynchronize(h->stream));
+    P.on = true;
+    return 0;
+  } catch (const std::exception& e) {
+    set_error(e.what());
+    return 1;
+  }
+}
+
+int fk_comm_mode(fk_handle h, int* mode) {  // 0 = single GPU, 1 = NCCL, 2 = peer memory
+  if (!h || !mode) return 1;
+  *mode = !h->comm ? 0 : (h->comm->p2p.on ? 2 : 1);
+  return 0;
 }
 
 }  // extern "C"

@@ -8,11 +8,19 @@ struct fk_handle_s;
 
 namespace fk {
 struct PcgCtl;
+struct RedArgs;
+RedArgs comm_red_args(fk_handle_s* h, unsigned int* ticket, double* out, int op);
+void comm_nccl_allreduce(fk_handle_s* h, cudaStream_t s, double* v, int n, int op);   // no-op unless on the NCCL path
+int comm_kind(fk_handle_s* h);   // 0 single GPU, 1 NCCL, 2 peer memory
 void launch_spmv(fk_handle_s* h, cudaStream_t s, const double* vals, const double* x, double* y, bool dot, const PcgCtl* ctl,
                  int j);
 void comm_destroy(fk_handle_s* h);
 void comm_halo_exchange(fk_handle_s* h, cudaStream_t s, double* v);
-void comm_allreduce_sum(fk_handle_s* h, cudaStream_t s, double* v, int n);
-void comm_allreduce_max(fk_handle_s* h, cudaStream_t s, double* v, int n);
-void comm_issue_iteration(fk_handle_s* h, cudaStream_t s, const double* vals, int j);
+// out[0..nvals) = reduction over ranks (op 0 sum / 1 max) of the folded per-CTA partials part[v*stride + 0..npart);
+// also the single-GPU fold (no communicator).  One kernel on the peer-memory path, fold + ncclAllReduce otherwise.
+void comm_allreduce_partials(fk_handle_s* h, cudaStream_t s, const double* part, int npart, int stride, int nvals, int op, double* out,
+                             const PcgCtl* ctl, int j);
+void comm_check(fk_handle_s* h);   // throws if a peer timed out
+bool comm_capturable(fk_handle_s* h);   // peer-memory path: the whole iteration is kernels -> CUDA-graph capturable
+void ensure_pcg(fk_handle_s* h);   // api.cu: allocates the PCG vector slab
 }  // namespace fk

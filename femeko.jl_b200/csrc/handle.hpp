@@ -78,18 +78,21 @@ struct fk_handle_s {
   // matrices
   fk::DevBuf<double> vals[FK_NUM_SLOTS];
   // nonlinear state
-  fk::DevBuf<double> mu, dmu, Hn, Hfield, u, tile_max, scal;
+  fk::DevBuf<double> mu, dmu, Hn, Hfield, tile_max, scal;
   fk::DevBuf<unsigned char> matid;
   fk::DevBuf<int> errflag;
   fk::DevBuf<double> spl_t[FK_MAX_SPLINES], spl_c[FK_MAX_SPLINES];
   fk::SplineSet spl{};
   bool have_material = false;
   // PCG workspace
-  fk::DevBuf<double> pcg_slab;         // x | r | p | Ap | dinv in ONE allocation: a single L2 access-policy window covers them
-  struct VecView { double* ptr = nullptr; } x, r, p, Ap, dinv;
+  fk::DevBuf<double> pcg_slab;         // x | r | p | Ap | dinv | u in ONE allocation: one L2 access-policy window covers the first five,
+                                       // and one CUDA-IPC handle exports every vector peers write halo rows into
+  struct VecView { double* ptr = nullptr; } x, r, p, Ap, dinv, u;   // u: potential staged for the Picard sweep (6th slab vector)
+  size_t slab_stride = 0;
   bool l2_persist = true, l2_window_set = false;
   cudaAccessPolicyWindow l2_window{};
   fk::DevBuf<double> part, bvec;
+  fk::DevBuf<unsigned int> tickets;    // last-CTA tickets of the in-kernel grid reductions (zero between kernels)
   fk::DevBuf<fk::PcgCtl> ctl;
   fk::PcgCtl* ctl_host = nullptr;      // pinned
   int grid_spmv = 0, grid_vec = 0;

@@ -71,6 +71,123 @@ __device__ __forceinline__ double block_sum_array(const double* __restrict__ a, 
 }
 
 // ------------------------------------------------------------------------------------------------
+// Grid-wide reductions finished INSIDE the producing kernel, and across GPUs over peer memory.
+// Every CTA publishes its partial sums; the CTA that takes the last ticket folds all partials in index
+// order (so the result does not depend on which CTA was last), and -- on a partitioned problem -- stores
+// the operands into every rank's mailbox over NVLink, waits for every rank's operands in its own mailbox
+// and combines them in rank order: identical bits on every rank, no extra kernel, no NCCL call.
+// Control block layout (64-bit words) of a rank: halo flags | mailbox [2 slots][kMaxRanks][kMailWords] |
+// error | count of executed reductions | count of executed halo exchanges.
+// ------------------------------------------------------------------------------------------------
+constexpr int kMaxRanks = 8;       // one NVSwitch node
+constexpr int kMaxNeigh = 32;
+constexpr int kMailWords = 4;      // per (slot, rank): 3 values + sequence flag
+constexpr int kOffMail = kMaxNeigh;
+constexpr int kOffErr = kOffMail + 2 * kMaxRanks * kMailWords;
+constexpr int kOffCnt = kOffErr + 1;
+constexpr int kOffHaloCnt = kOffCnt + 1;
+constexpr int kCtrlWords = 128;
+
+__device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+// spin until *flag >= seq; gives up after ~2 s (a lost peer must not hang the GPU) and records the failure
+__device__ __forceinline__ bool spin_until(const unsigned long long* flag, unsigned long long seq, unsigned long long* err) {
+  const long long t0 = clock64();
+  while (ld_acquire_sys(flag) < seq) {
+    if (clock64() - t0 > 4000000000LL) {
+      *err = 1ULL;
+      return false;
+    }
+  }
+  return true;
+}
+
+struct RedArgs {
+  unsigned int* ticket;                        // zero between kernels
+  double* out;                                 // reduced scalars
+  int op;                                      // 0 = sum, 1 = max
+  int rank, nranks;                            // nranks <= 1 or my_ctrl == nullptr: this GPU only
+  unsigned long long* const* peer_ctrl;        // control block of every rank (peer memory)
+  unsigned long long* my_ctrl;
+};
+
+// exchange `nvals` (<= 3) scalars held in val[] (shared memory) with every rank; result back in val[].
+// Called by a whole CTA (>= kMaxRanks threads).  The sequence number is a device-side count of EXECUTED
+// reductions (every rank executes the same ones), so consecutive reductions alternate mailbox slots and a
+// rank can run at most one reduction ahead of the slowest reader.
+__device__ __forceinline__ void peer_allreduce(double* val, int nvals, const RedArgs& ra) {
+  const unsigned long long seq = ra.my_ctrl[kOffCnt] + 1ULL;
+  __syncthreads();
+  const int slot = (int)(seq & 1ULL);
+  if ((int)threadIdx.x < ra.nranks) {
+    unsigned long long* box = ra.peer_ctrl[threadIdx.x] + kOffMail + ((size_t)slot * kMaxRanks + ra.rank) * kMailWords;
+    for (int v = 0; v < nvals; v++) reinterpret_cast<double*>(box)[v] = val[v];
+    __threadfence_system();
+    st_release_sys(box + 3, seq);
+    spin_until(ra.my_ctrl + kOffMail + ((size_t)slot * kMaxRanks + threadIdx.x) * kMailWords + 3, seq, ra.my_ctrl + kOffErr);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int v = 0; v < nvals; v++) {
+      double s = 0.0;
+      for (int r = 0; r < ra.nranks; r++) {
+        const double x = reinterpret_cast<volatile double*>(ra.my_ctrl + kOffMail + ((size_t)slot * kMaxRanks + r) * kMailWords)[v];
+        s = (ra.op == 0) ? s + x : fmax(s, x);
+      }
+      val[v] = s;
+    }
+    ra.my_ctrl[kOffCnt] = seq;
+  }
+  __syncthreads();
+}
+
+// v[k] (valid in thread 0): this CTA's partial of value k.  part: NV x stride scratch, stride >= gridDim.x.
+// ra.ticket == nullptr: only publish the partials (measured on one B200: letting every CTA of the consumer
+// fold the ~1200 partials in parallel is 7 us per iteration faster than the serial tail of a last CTA).
+template <int NV>
+__device__ __forceinline__ void grid_reduce_finish(const double (&v)[NV], double* __restrict__ part, int stride, const RedArgs& ra,
+                                                   double* scratch /* >= 33 doubles */) {
+  __shared__ int last_flag;
+  __shared__ double val[3];
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int k = 0; k < NV; k++) part[(size_t)k * stride + blockIdx.x] = v[k];
+    if (ra.ticket == nullptr) {
+      last_flag = 0;   // single GPU: the consuming kernel folds the partials itself (every CTA in parallel, no serial tail)
+    } else {
+      __threadfence();
+      last_flag = (atomicAdd(ra.ticket, 1u) == gridDim.x - 1) ? 1 : 0;
+    }
+  }
+  __syncthreads();
+  if (!last_flag) return;
+  __threadfence();
+#pragma unroll
+  for (int k = 0; k < NV; k++) {
+    double s = (ra.op == 0) ? 0.0 : -DBL_MAX;
+    for (int i = threadIdx.x; i < (int)gridDim.x; i += blockDim.x) {
+      const double x = __ldcg(part + (size_t)k * stride + i);
+      s = (ra.op == 0) ? s + x : fmax(s, x);
+    }
+    s = (ra.op == 0) ? block_sum(s, scratch) : block_max(s, scratch);
+    if (threadIdx.x == 0) val[k] = s;
+  }
+  __syncthreads();
+  if (ra.nranks > 1 && ra.my_ctrl != nullptr) peer_allreduce(val, NV, ra);
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int k = 0; k < NV; k++) ra.out[k] = val[k];
+    *ra.ticket = 0u;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
 // P1 geometry: gradients of the barycentric shape functions of one tetrahedron.
 // Replaces the four 4x4 solves of abcd (src/FEM3D.jl:5-17 / FEMc.cpp:18-42): with
 // E = [x1-x0 | x2-x0 | x3-x0], rows of inv(E) are grad(lambda_1..3), grad(lambda_0) = -(sum).
@@ -242,8 +359,8 @@ static __global__ void jacobi_kernel(const double* __restrict__ vals, const int*
 // r = b - Ax0 (Ax0 nullable), p = dinv r, partials of b.b, r.r, r.p   (ConjugateGradient.h:38-59)
 static __global__ void __launch_bounds__(kVecThreads) pcg_init_kernel(const double* __restrict__ b, const double* __restrict__ Ax0,
                                                                const double* __restrict__ dinv, int n, double* __restrict__ r,
-                                                               double* __restrict__ p, double* __restrict__ part3) {
-  __shared__ double red[33];
+                                                               double* __restrict__ p, double* __restrict__ part3, const RedArgs red) {
+  __shared__ double red_s[33];
   double s_bb = 0.0, s_rr = 0.0, s_rp = 0.0;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
     const double bi = b[i];
@@ -255,17 +372,15 @@ static __global__ void __launch_bounds__(kVecThreads) pcg_init_kernel(const doub
     s_rr += ri * ri;
     s_rp += ri * pi;
   }
-  s_bb = block_sum(s_bb, red);
-  s_rr = block_sum(s_rr, red);
-  s_rp = block_sum(s_rp, red);
-  if (threadIdx.x == 0) {
-    part3[blockIdx.x] = s_bb;
-    part3[gridDim.x + blockIdx.x] = s_rr;
-    part3[2 * gridDim.x + blockIdx.x] = s_rp;
-  }
+  s_bb = block_sum(s_bb, red_s);
+  s_rr = block_sum(s_rr, red_s);
+  s_rp = block_sum(s_rp, red_s);
+  const double v[3] = {s_bb, s_rr, s_rp};
+  grid_reduce_finish<3>(v, part3, gridDim.x, red, red_s);   // -> out[0..2] = (b.b, r.r, r.p) over all ranks
 }
 
-// single block: fold the partials (or take the all-reduced scalars when npart == 1)
+// single block: fold the partials of (b.b, r.r, r.p) (npart == 1: already reduced scalars) -> thresholds and
+// the early exits of ConjugateGradient.h:43-56
 static __global__ void pcg_init_fin_kernel(const double* __restrict__ part3, int npart, int stride, double tol, int max_iter,
                                     PcgCtl* ctl) {
   __shared__ double red[33];
@@ -281,7 +396,7 @@ static __global__ void pcg_init_fin_kernel(const double* __restrict__ part3, int
     ctl->base_it = 0;
     ctl->max_iter = max_iter;
     ctl->iters = 0;
-    ctl->done = (bb == 0.0 || rr < ctl->thr) ? 1 : 0;   // ConjugateGradient.h:43-56 early exits
+    ctl->done = (bb == 0.0 || rr < ctl->thr) ? 1 : 0;
   }
 }
 
@@ -290,10 +405,11 @@ static __global__ void __launch_bounds__(kVecThreads) pcg_update_kernel(double* 
                                                                  const double* __restrict__ p, const double* __restrict__ Ap,
                                                                  const double* __restrict__ dinv, int n,
                                                                  const double* __restrict__ part_pAp, int npart,
-                                                                 double* __restrict__ part2, const PcgCtl* ctl, int j) {
-  __shared__ double red[33];
+                                                                 double* __restrict__ part2, const RedArgs red, const PcgCtl* ctl,
+                                                                 int j) {
+  __shared__ double red_s[33];
   if (pcg_inactive(ctl, j)) return;
-  const double pAp = block_sum_array(part_pAp, npart, red);
+  const double pAp = block_sum_array(part_pAp, npart, red_s);   // npart == 1: the all-reduced scalar
   const double alpha = ctl->absNew[j & 1] / pAp;
   double s_rr = 0.0, s_rz = 0.0;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
@@ -303,12 +419,10 @@ static __global__ void __launch_bounds__(kVecThreads) pcg_update_kernel(double* 
     s_rr += ri * ri;
     s_rz += ri * (dinv[i] * ri);
   }
-  s_rr = block_sum(s_rr, red);
-  s_rz = block_sum(s_rz, red);
-  if (threadIdx.x == 0) {
-    part2[blockIdx.x] = s_rr;
-    part2[gridDim.x + blockIdx.x] = s_rz;
-  }
+  s_rr = block_sum(s_rr, red_s);
+  s_rz = block_sum(s_rz, red_s);
+  const double v[2] = {s_rr, s_rz};
+  grid_reduce_finish<2>(v, part2, gridDim.x, red, red_s);   // -> out[0..1] = (r.r, r.z) over all ranks
 }
 
 // convergence test, beta, p = dinv r + beta p                           (ConjugateGradient.h:72-81)

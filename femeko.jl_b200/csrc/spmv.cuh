@@ -7,7 +7,8 @@
 // neighbouring columns, so the gather of a step touches 2-3 lines instead of 32.  Each row is folded
 // left to right with separately rounded multiply and add: the summation order of Eigen's column-major
 // product on a symmetric pattern (and of the CSR loop), bitwise reproducible, no shared memory, no
-// block-level synchronisation.  DOT fuses p.Ap: per-CTA partial sums in fixed order -> part[blockIdx.x].
+// block-level synchronisation.  DOT fuses p.Ap: per-CTA partial sums, folded in index order by the last
+// CTA to finish (and all-reduced over peer memory on a partitioned problem): grid_reduce_finish.
 //
 // Measured alternatives (profiles/r01b_spmv_variants.md): a CSR-stream kernel staging products in shared
 // memory (85 us at 25.6 M entries) and the same with the stream moved by TMA bulk copies (90-300 us):
@@ -20,8 +21,9 @@ template <bool DOT>
 static __global__ void __launch_bounds__(kSpmvThreads) spmv_sell_kernel(const int* __restrict__ slice_ptr, const int* __restrict__ srow,
                                                                   const int* __restrict__ col, const double* __restrict__ vals,
                                                                   const double* __restrict__ x, double* __restrict__ y, int nslices,
-                                                                  double* __restrict__ part, const PcgCtl* ctl, int j) {
-  __shared__ double red[33];
+                                                                  double* __restrict__ part, const RedArgs red, const PcgCtl* ctl,
+                                                                  int j) {
+  __shared__ double red_s[33];
   if (pcg_inactive(ctl, j)) return;
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   constexpr int WPB = kSpmvThreads / 32;
@@ -54,8 +56,8 @@ static __global__ void __launch_bounds__(kSpmvThreads) spmv_sell_kernel(const in
     }
   }
   if (DOT) {
-    dot = block_sum(dot, red);
-    if (threadIdx.x == 0) part[blockIdx.x] = dot;
+    const double v[1] = {block_sum(dot, red_s)};
+    grid_reduce_finish<1>(v, part, gridDim.x, red, red_s);   // -> out[0] = p.Ap over all ranks
   }
 }
 

@@ -75,6 +75,12 @@ class Femeko:
         """Launch-shape tuning (fk_tune): what 0 = asm_cfg, 1 = spmv_variant, 2 = spmv_stages."""
         L.check(self.lib.fk_tune(self.h, int(what), int(value)))
 
+    def comm_mode(self) -> int:
+        """0 = single GPU, 1 = NCCL send/recv + all-reduce, 2 = peer memory over NVLink (fk_comm_mode)."""
+        m = C.c_int()
+        L.check(self.lib.fk_comm_mode(self.h, C.byref(m)))
+        return m.value
+
     def synchronize(self):
         L.check(self.lib.fk_synchronize(self.h))
 

@@ -105,6 +105,9 @@ _SIGS = {
     "fk_nccl_unique_id": (C.c_int, [c_ubyte_p]),
     "fk_comm_init": (C.c_int, [_H, c_ubyte_p, C.c_int, C.c_int]),
     "fk_set_halo": (C.c_int, [_H, C.c_int, C.c_int, c_int_p, c_int_p, c_int_p, c_int_p, c_int_p]),
+    "fk_comm_p2p_export": (C.c_int, [_H, c_ubyte_p]),
+    "fk_comm_p2p_attach": (C.c_int, [_H, c_ubyte_p, c_int_p, c_int_p]),
+    "fk_comm_mode": (C.c_int, [_H, c_int_p]),
     "scalarPotential": (None, [c_double_p, c_double_p, c_int_p, c_int_p, c_double_p, C.c_int, C.c_int, C.c_int,
                                c_double_p, c_double_p, c_double_p, C.c_int]),
 }

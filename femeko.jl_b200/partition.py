@@ -17,6 +17,8 @@ from __future__ import annotations
 
 from dataclasses import dataclass, field
 
+import os
+
 import numpy as np
 
 from .mesh import MESH, _box_surface, _finish, _orient_outward, box_inside_mask, kuhn_cells
@@ -89,6 +91,39 @@ class Partition:
         rs = np.ascontiguousarray(self.recv_start, dtype=np.int32)
         rc = np.ascontiguousarray(self.recv_count, dtype=np.int32)
         L.check(lib.fk_set_halo(h.h, self.n_owned, len(self.neigh), L.iptr(ne), L.iptr(sp), L.iptr(si), L.iptr(rs), L.iptr(rc)))
+        if self.world > 1 and dist is not None and not os.environ.get("FK_NO_P2P"):
+            self._attach_p2p(h, dist)
+
+    def _attach_p2p(self, h, dist):
+        """Peer-memory path: all-gather the CUDA-IPC handles and every rank's receive plan, then map the
+        peers (fk_comm_p2p_attach).  Set FK_NO_P2P=1 to stay on the NCCL send/recv + all-reduce path."""
+        import ctypes as C
+
+        import torch
+
+        from . import lib as L
+
+        lib = L.load()
+        hb = (C.c_ubyte * 128)()
+        L.check(lib.fk_comm_p2p_export(h.h, hb))
+        mine = torch.tensor(list(hb), dtype=torch.uint8)
+        if dist.get_backend() == "nccl":
+            mine = mine.cuda()
+        allh = [torch.empty_like(mine) for _ in range(self.world)]
+        dist.all_gather(allh, mine)
+        plans = [None] * self.world
+        dist.all_gather_object(plans, {"neigh": [int(v) for v in self.neigh], "recv_start": [int(v) for v in self.recv_start]})
+        rstart, rslot = [], []
+        for nb in self.neigh:
+            qq = plans[int(nb)]["neigh"].index(self.rank)
+            rslot.append(qq)
+            rstart.append(plans[int(nb)]["recv_start"][qq])
+        blob = np.concatenate([t.cpu().numpy() for t in allh]).astype(np.uint8)
+        hs = (C.c_ubyte * blob.size).from_buffer_copy(blob.tobytes())
+        a = np.ascontiguousarray(rstart, dtype=np.int32)
+        b = np.ascontiguousarray(rslot, dtype=np.int32)
+        L.check(lib.fk_comm_p2p_attach(h.h, hs, L.iptr(a), L.iptr(b)))
+        dist.barrier()
 
     # ---- host side (any torch.distributed backend; used for set-up data and the gloo tests) ----
     def exchange_host(self, v: np.ndarray, dist) -> None:

@@ -189,6 +189,18 @@ int fk_comm_init(fk_handle h, const unsigned char* id128, int rank, int nranks);
 int fk_set_halo(fk_handle h, int n_owned, int nneigh, const int* neigh_rank, const int* send_ptr /* nneigh+1 */,
                 const int* send_idx, const int* recv_start, const int* recv_count);
 
+/* Peer-memory path (one NVSwitch node, <= 8 ranks): every rank exports CUDA-IPC handles of its PCG vector
+ * slab, which also holds a small control block (fk_comm_p2p_export: 128 bytes); after an all-gather of those
+ * (any transport) fk_comm_p2p_attach maps the peers.  From then on the halo rows are stored straight into
+ * the owner's vectors over NVLink and the all-reduces are single kernels over peer mailboxes (operands
+ * combined in rank order: identical bits on every rank); NCCL stays as the fallback when attach fails.
+ * remote_start[q] / remote_slot[q]: neighbour q's recv_start for this rank / this rank's index in q's
+ * neighbour list.  fk_comm_mode: 0 = single GPU, 1 = NCCL, 2 = peer memory.                        */
+int fk_comm_p2p_export(fk_handle h, unsigned char* handles128);
+int fk_comm_p2p_attach(fk_handle h, const unsigned char* all_handles /* nranks x 128 */, const int* remote_start,
+                       const int* remote_slot);
+int fk_comm_mode(fk_handle h, int* mode);
+
 /* ---- legacy drop-in: ABI-identical to the reference (magnetostatics.cpp:49-60) --------------- */
 void scalarPotential(double* u_in, double* p_in, int* t_in, int* surfaceT_in, double* normal_in,
                      int nv, int nt, int ns, double* VE, double* mu, double* Hext, int shell_id);
