@@ -71,7 +71,7 @@ static AsmArgs base_args(fk_handle h, double* vals) {
   a.nno_max = h->sym.max_tile_nodes;
   a.blob_a_max = h->sym.max_blob_a;
   a.blob_b_max = h->sym.max_blob_b;
-  a.spl = h->spl;
+  a.dbg = h->asm_dbg;
   return a;
 }
 
@@ -129,7 +129,7 @@ static void ensure_state(fk_handle h) {
   h->Hn.ensure((size_t)h->nt);
   h->Hfield.ensure((size_t)3 * h->nt);
   h->matid.ensure((size_t)h->nt);
-  h->tile_max.ensure((size_t)std::max(1, h->sym.ntiles));
+  h->tile_max.ensure((size_t)std::max(1, 4 * h->num_sms));   // per-CTA maxima of material_update_kernel
   h->errflag.ensure(1);
   h->scal.ensure(8);
   const int g = std::min(cdiv(h->nt, 256), 65535);
@@ -490,7 +490,7 @@ int fk_create(const double* p, const int* t, int nv, int nt, const double* VE, c
     FK_CUDA(cudaStreamSynchronize(s));
     // the device only needs the packed blobs; drop the host copies of the unpacked plan
     h->sym.tile_blob = std::vector<uint32_t>();
-    h->e_pad = (S.max_tile_elems + 15) & ~15;
+    h->e_pad = S.e_pad;
     h->asm_smem = asm_smem_bytes(h->e_pad, S.max_tile_nodes, S.max_blob_a, S.max_blob_b);
     need(h->asm_smem <= (size_t)prop.sharedMemPerBlockOptin, "fk_create: assembly tile does not fit in shared memory");
     need(o.asm_cfg >= 0 && o.asm_cfg < kNumAsmCfg, "fk_create: asm_cfg out of range");
@@ -524,6 +524,7 @@ int fk_destroy(fk_handle h) {
       if (h->graph[s]) cudaGraphExecDestroy(h->graph[s]);
     if (h->cap_stream) cudaStreamDestroy(h->cap_stream);
     if (h->ctl_host) cudaFreeHost(h->ctl_host);
+    if (h->pin8) cudaFreeHost(h->pin8);
     if (h->l2_window_set) cudaCtxResetPersistingL2Cache();
     comm_destroy(h);
     delete h;
@@ -560,6 +561,7 @@ int fk_tune(fk_handle h, int what, int value) {
       }
       case 1: configure_spmv(h, value); break;
       case 2: h->l2_persist = value != 0; configure_l2(h); break;
+      case 3: h->asm_dbg = value; break;   // profiling experiments: skip assembly phases (results are garbage)
       default: throw std::runtime_error("fk_tune: unknown option");
     }
     return 0;
@@ -1064,6 +1066,10 @@ int fk_set_material(fk_handle h, const unsigned char* matid) {
     DeviceGuard dg(h->device);
     ensure_state(h);
     FK_CUDA(cudaMemcpyAsync(h->matid.ptr, matid, (size_t)h->nt, cudaMemcpyHostToDevice, h->stream));
+    std::vector<int> list;
+    for (int k = 0; k < h->nt; k++) if (matid[k] > 0) list.push_back(k);
+    h->n_mat = (int)list.size();
+    if (h->n_mat > 0) h->mat_list.upload(list, h->stream);
     FK_CUDA(cudaStreamSynchronize(h->stream));
     h->have_material = true;
     return 0;
@@ -1076,9 +1082,10 @@ int fk_set_inside(fk_handle h, const int* ids, int n) {
     DeviceGuard dg(h->device);
     ensure_state(h);
     FK_CUDA(cudaMemsetAsync(h->matid.ptr, 0, (size_t)h->nt, h->stream));
+    h->n_mat = n;
     if (n > 0) {
-      h->st_i.upload(ids, (size_t)n, h->stream);
-      set_material_kernel<<<cdiv(n, 256), 256, 0, h->stream>>>(h->matid.ptr, h->st_i.ptr, n);
+      h->mat_list.upload(ids, (size_t)n, h->stream);
+      set_material_kernel<<<cdiv(n, 256), 256, 0, h->stream>>>(h->matid.ptr, h->mat_list.ptr, n);
       FK_CUDA(cudaGetLastError());
       h->launches++;
     }
@@ -1142,23 +1149,35 @@ static int picard_step_dev(fk_handle h, int slot, const double* u_dev, int compa
     comm_halo_exchange(h, h->stream, h->u.ptr);
     a.u = h->u.ptr;
   }
-  a.mu = h->mu.ptr;
-  a.dmu = h->dmu.ptr;
+  a.coef = h->mu.ptr;
   a.Hn = h->Hn.ptr;
   a.Hfield = h->Hfield.ptr;
-  a.matid = h->have_material ? h->matid.ptr : nullptr;
-  a.tile_max = h->tile_max.ptr;
-  a.errflag = h->errflag.ptr;
   a.compat = compat_bug;
-  FK_CUDA(cudaMemsetAsync(h->errflag.ptr, 0, sizeof(int), h->stream));
+  int* errflag = reinterpret_cast<int*>(h->scal.ptr + 7);   // rides in the scalar block: one copy brings back both
+  FK_CUDA(cudaMemsetAsync(errflag, 0, sizeof(double), h->stream));
+  // 1. material elements: mu(|H|), dmu/dH from the spline and the convergence metric (per-CTA maxima)
+  int npart = 1;
+  if (h->have_material && h->n_mat > 0) {
+    npart = std::min(cdiv(h->n_mat, 256), 4 * h->num_sms);
+    h->tile_max.ensure((size_t)npart);
+    material_update_kernel<<<npart, 256, 0, h->stream>>>(h->p4.ptr, h->t4.ptr, h->mat_list.ptr, h->n_mat,
+                                                        h->matid.ptr, a.u, h->spl, compat_bug, h->Hn.ptr, h->mu.ptr, h->dmu.ptr,
+                                                        h->tile_max.ptr, errflag);
+    FK_CUDA(cudaGetLastError());
+    h->launches++;
+  } else {
+    FK_CUDA(cudaMemsetAsync(h->tile_max.ptr, 0, sizeof(double), h->stream));
+  }
+  // 2. the fused sweep: stiffness with the refreshed mu + H, |H| of every element
   launch_assemble<ASM_PICARD>(h, a);
   // div = mu0 * max over every rank's material elements (NewtonRaphson.jl:200)
-  comm_allreduce_partials(h, h->stream, h->tile_max.ptr, h->sym.ntiles, h->sym.ntiles, 1, 1, h->scal.ptr, nullptr, 0);
-  double dmax = 0.0;
-  int err = 0;
-  FK_CUDA(cudaMemcpyAsync(&dmax, h->scal.ptr, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
-  FK_CUDA(cudaMemcpyAsync(&err, h->errflag.ptr, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+  comm_allreduce_partials(h, h->stream, h->tile_max.ptr, npart, npart, 1, 1, h->scal.ptr, nullptr, 0);
+  if (!h->pin8) FK_CUDA(cudaMallocHost((void**)&h->pin8, 8 * sizeof(double)));
+  FK_CUDA(cudaMemcpyAsync(h->pin8, h->scal.ptr, 8 * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
   FK_CUDA(cudaStreamSynchronize(h->stream));
+  const double dmax = h->pin8[0];
+  int err = 0;
+  std::memcpy(&err, h->pin8 + 7, sizeof(int));
   if (div_out) *div_out = (4e-7 * 3.14159265358979323846) * dmax;   // mu0*max|H - Hold| (NewtonRaphson.jl:200)
   if (err & 1) { set_error("fk_picard_step: |H| outside the spline's knot range with bc = error"); return 2; }
   if (err & 2) { set_error("fk_picard_step: Nans/Infs in mu"); return 3; }   // NewtonRaphson.jl:210-212

@@ -18,19 +18,13 @@ enum AsmMode { ASM_STIFF = 0, ASM_MASS = 1, ASM_TANGENT = 2, ASM_PICARD = 3, ASM
 
 struct AsmArgs {
   const double* VE;       // nullable: volume from the determinant
-  const double* coef;     // STIFF: f (nullable = 1) | MASS: rho (nullable) | TANGENT: dmu
+  const double* coef;     // STIFF: f (nullable = 1) | MASS: rho (nullable) | TANGENT: dmu | PICARD: mu (already updated)
   const double* Hvec;     // TANGENT: 3 x nt
-  // PICARD
+  // PICARD: the element's owner tile also stores H = -grad(u) and |H| (field recovery fused into the sweep)
   const double* u;
-  double* mu;             // in (linear elements) / out (material elements)
-  double* dmu;            // nullable
-  double* Hn;             // in: |H| old, out: |H| new
+  double* Hn;
   double* Hfield;         // nullable, 3 x nt
-  const unsigned char* matid;  // nullable = all linear
-  double* tile_max;       // per tile: max | |H| - |H|old | over owned material elements
-  int* errflag;
   int compat;
-  SplineSet spl;
   // plan
   const int4* tile_hdr;   // {blob offset / 16, ne | nno << 16, nn, nents}
   const uint4* tile_blob; // 16-byte units
@@ -40,6 +34,7 @@ struct AsmArgs {
   int nno_max;            // max nodes per tile (u staging)
   int blob_a_max;         // bytes reserved in shared memory for section A / B (per buffer)
   int blob_b_max;
+  int dbg;                // profiling experiments only (fk_tune 3): bit 0 skips phase 1, bit 1 skips phase 2
 };
 
 // ---- mbarrier + bulk-copy primitives (PTX ISA: mbarrier, cp.async.bulk; sm_90+) -----------------
@@ -80,7 +75,7 @@ template <int MODE>
 __device__ __forceinline__ void element_local(const AsmArgs& a, const int k, const bool owner, const double* __restrict__ xs,
                                               const double* __restrict__ ys, const double* __restrict__ zs,
                                               const double* __restrict__ us, const uint2 l, const double fpre, const double vpre,
-                                              double (&m)[10], double& dmax) {
+                                              double (&m)[10]) {
   const int l0 = l.x & 0xffff, l1 = l.x >> 16, l2 = l.y & 0xffff, l3 = l.y >> 16;
   TetGeom G;
   if (MODE == ASM_MASS || MODE == ASM_LAGRANGE) {
@@ -116,37 +111,20 @@ __device__ __forceinline__ void element_local(const AsmArgs& a, const int k, con
       for (int j = i; j < 4; j++) m[q++] = s0 * gh[i] * gh[j];
     return;
   }
-  double f;
+  const double f = fpre;  // 1.0 when the coefficient vector is absent (fetch_coef)
   if (MODE == ASM_PICARD) {
-    const double u0 = us[l0], u1 = us[l1], u2 = us[l2], u3 = us[l3];
-    double hx = -(u0 * G.g[0][0]) - u1 * G.g[1][0] - u2 * G.g[2][0] - u3 * G.g[3][0];
-    double hy = -(u0 * G.g[0][1]) - u1 * G.g[1][1] - u2 * G.g[2][1] - u3 * G.g[3][1];
-    double hz = -(u0 * G.g[0][2]) - u1 * G.g[1][2] - u2 * G.g[2][2] - u3 * G.g[3][2];
-    if (a.compat) { hy += hz; hz = 0.0; }  // NewtonRaphson.jl:187-189: d-term lands in row 2
-    const double Hn = sqrt(hx * hx + hy * hy + hz * hz);
-    const int mat = a.matid ? (int)__ldg(a.matid + k) : 0;
-    if (mat > 0) {
-      int err = 0;
-      f = splev_dev(a.spl.s[mat - 1], Hn, err);
-      double df = 0.0;
-      const SplineDev& D = a.spl.s[FK_MAX_SPLINES / 2 + mat - 1];
-      if (a.dmu && D.n > 0) df = splev_dev(D, Hn, err);
-      if (!(f == f) || fabs(f) > DBL_MAX || !(df == df) || fabs(df) > DBL_MAX) err |= 2;  // Nans/Infs in mu
-      if (err) atomicOr(a.errflag, err);
-      if (owner) {
-        dmax = fmax(dmax, fabs(Hn - a.Hn[k]));
-        a.mu[k] = f;
-        if (a.dmu) a.dmu[k] = df;
-      }
-    } else {
-      f = fpre;
-    }
+    // field recovery rides along: the tile that owns the element stores H and |H| (NewtonRaphson.jl:178-197);
+    // the recomputed copies -- about half of the staged elements, grouped after the owned ones by the plan -- skip
+    // it.  mu(|H|) of the material elements was refreshed by material_update_kernel just before this sweep.
     if (owner) {
-      a.Hn[k] = Hn;
+      const double u0 = us[l0], u1 = us[l1], u2 = us[l2], u3 = us[l3];
+      double hx = -(u0 * G.g[0][0]) - u1 * G.g[1][0] - u2 * G.g[2][0] - u3 * G.g[3][0];
+      double hy = -(u0 * G.g[0][1]) - u1 * G.g[1][1] - u2 * G.g[2][1] - u3 * G.g[3][1];
+      double hz = -(u0 * G.g[0][2]) - u1 * G.g[1][2] - u2 * G.g[2][2] - u3 * G.g[3][2];
+      if (a.compat) { hy += hz; hz = 0.0; }  // NewtonRaphson.jl:187-189: d-term lands in row 2
+      a.Hn[k] = sqrt(hx * hx + hy * hy + hz * hz);
       if (a.Hfield) { a.Hfield[3 * (size_t)k] = hx; a.Hfield[3 * (size_t)k + 1] = hy; a.Hfield[3 * (size_t)k + 2] = hz; }
     }
-  } else {
-    f = fpre;  // 1.0 when the coefficient vector is absent (fetch_coef)
   }
   const double s0 = V * f;  // VE[k]*f[k]*( b b' + c c' + d d' ), src/FEM3D.jl:71
   int q = 0;
@@ -160,15 +138,14 @@ __device__ __forceinline__ void element_local(const AsmArgs& a, const int k, con
 // per-element coefficient gathers (the only global gathers left in phase 1): issued one tile ahead
 template <int MODE>
 __device__ __forceinline__ void fetch_coef(const AsmArgs& a, const int k, double& f, double& v) {
-  const double* cp = (MODE == ASM_PICARD) ? a.mu : a.coef;
-  f = (MODE != ASM_LAGRANGE && cp) ? __ldg(cp + k) : 1.0;
+  f = (MODE != ASM_LAGRANGE && a.coef) ? __ldg(a.coef + k) : 1.0;
   v = a.VE ? __ldg(a.VE + k) : 0.0;
 }
 
 // ---- the kernel ----------------------------------------------------------------------------------
-// Shared memory: [ stage 10 x e_pad f64 | us nno_max f64 | (A | B) buffer 0 | (A | B) buffer 1 ].
+// Shared memory: [ stage 10 x e_pad f64 | us 2 x nno_max f64 | (A | B) buffer 0 | (A | B) buffer 1 ].
 __host__ __device__ inline size_t asm_smem_bytes(int e_pad, int nno_max, int blob_a_max, int blob_b_max) {
-  return (size_t)80 * e_pad + (size_t)pad16(8 * nno_max) + 2 * ((size_t)blob_a_max + blob_b_max);
+  return (size_t)80 * e_pad + 2 * (size_t)pad16(8 * nno_max) + 2 * ((size_t)blob_a_max + blob_b_max);
 }
 
 struct TileView {  // pointers into one shared-memory copy of section A
@@ -192,16 +169,18 @@ struct TileView {  // pointers into one shared-memory copy of section A
 
 constexpr int kAsmPre = 2;  // per-thread register prefetch depth (elements / nodes of the NEXT tile)
 
+// Two CTA-wide barriers per tile: one between the phases, one at the end of the tile (which also publishes the
+// next tile's potential values and releases the staging array and the blob buffer).
 template <int MODE, int THREADS, int MINB>
-static __global__ void __launch_bounds__(THREADS, MINB) assemble_kernel(const AsmArgs a) {
+static __global__ void __launch_bounds__(THREADS, MINB) assemble_kernel(const __grid_constant__ AsmArgs a) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   __shared__ __align__(8) uint64_t barA[2], barB[2];
-  __shared__ double red[33];
   const int tid = threadIdx.x;
   const int EP = a.e_pad;
   double* stage = reinterpret_cast<double*>(smem_raw);
-  double* us = stage + (size_t)10 * EP;
-  unsigned char* buf0 = reinterpret_cast<unsigned char*>(us) + pad16(8 * a.nno_max);
+  double* us0 = stage + (size_t)10 * EP;
+  const int us_stride = pad16(8 * a.nno_max) / 8;
+  unsigned char* buf0 = reinterpret_cast<unsigned char*>(us0 + 2 * (size_t)us_stride);
   const size_t bufsz = (size_t)a.blob_a_max + a.blob_b_max;
 
   const int mine = (a.ntiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;  // tiles of this CTA
@@ -226,6 +205,12 @@ static __global__ void __launch_bounds__(THREADS, MINB) assemble_kernel(const As
       if (MODE == ASM_PICARD && s < T.nno) upre[j] = __ldg(a.u + T.gnode[s]);
     }
   };
+  auto stage_u = [&](const TileView& T, double* us) {  // potential at a tile's nodes: one gather per node
+#pragma unroll
+    for (int j = 0; j < kAsmPre; j++)
+      if (tid + j * THREADS < T.nno) us[tid + j * THREADS] = upre[j];
+    for (int n = tid + kAsmPre * THREADS; n < T.nno; n += THREADS) us[n] = __ldg(a.u + T.gnode[n]);
+  };
 
   int4 hnext = make_int4(0, 0, 0, 0);  // thread 0: header of tile i + 1, loaded one tile ahead
   if (tid == 0) {
@@ -238,6 +223,10 @@ static __global__ void __launch_bounds__(THREADS, MINB) assemble_kernel(const As
   __syncthreads();  // barrier init visible to every waiter
   mbar_wait(&barA[0], 0);
   prefetch(TileView(buf0));
+  if (MODE == ASM_PICARD) {
+    stage_u(TileView(buf0), us0);
+    __syncthreads();
+  }
 
   for (int i = 0; i < mine; i++) {
     if (tid == 0 && i + 1 < mine) {  // buffer (i+1)&1 was released by the barrier that ended tile i-1
@@ -248,23 +237,17 @@ static __global__ void __launch_bounds__(THREADS, MINB) assemble_kernel(const As
     const unsigned char* sB = sA + a.blob_a_max;
     const TileView T(sA);  // section A of tile i was awaited before its prefetch
     const int ne = T.ne, nn = T.nn;
+    const double* us = us0 + (size_t)(i & 1) * us_stride;
 
-    if (MODE == ASM_PICARD) {  // potential at the tile's nodes: one gather per node, not one per element corner
-#pragma unroll
-      for (int j = 0; j < kAsmPre; j++)
-        if (tid + j * THREADS < T.nno) us[tid + j * THREADS] = upre[j];
-      for (int n = tid + kAsmPre * THREADS; n < T.nno; n += THREADS) us[n] = __ldg(a.u + T.gnode[n]);
-      __syncthreads();
-    }
     // ---- phase 1 ------------------------------------------------------------------------------
-    double dmax = 0.0;
+    if (!(a.dbg & 1)) {
 #pragma unroll
     for (int j = 0; j < kAsmPre; j++) {
       const int s = tid + j * THREADS;
       if (s < ne) {
         const uint32_t raw = T.ek[s];
         double m[10];
-        element_local<MODE>(a, (int)(raw & 0x7fffffffu), (raw >> 31) != 0, T.xs, T.ys, T.zs, us, T.loc[s], fpre[j], vpre[j], m, dmax);
+        element_local<MODE>(a, (int)(raw & 0x7fffffffu), (raw >> 31) != 0, T.xs, T.ys, T.zs, us, T.loc[s], fpre[j], vpre[j], m);
 #pragma unroll
         for (int q = 0; q < 10; q++) stage[q * EP + s] = m[q];
       }
@@ -273,9 +256,10 @@ static __global__ void __launch_bounds__(THREADS, MINB) assemble_kernel(const As
       const uint32_t raw = T.ek[s];
       double f, v, m[10];
       fetch_coef<MODE>(a, (int)(raw & 0x7fffffffu), f, v);
-      element_local<MODE>(a, (int)(raw & 0x7fffffffu), (raw >> 31) != 0, T.xs, T.ys, T.zs, us, T.loc[s], f, v, m, dmax);
+      element_local<MODE>(a, (int)(raw & 0x7fffffffu), (raw >> 31) != 0, T.xs, T.ys, T.zs, us, T.loc[s], f, v, m);
 #pragma unroll
       for (int q = 0; q < 10; q++) stage[q * EP + s] = m[q];
+    }
     }
     if (i + 1 < mine) {  // next tile's gathers fly during this tile's phase 2
       mbar_wait(&barA[(i + 1) & 1], (uint32_t)(((i + 1) >> 1) & 1));
@@ -288,20 +272,15 @@ static __global__ void __launch_bounds__(THREADS, MINB) assemble_kernel(const As
     const int* gidx = reinterpret_cast<const int*>(sB);
     const uint16_t* coff = reinterpret_cast<const uint16_t*>(sB + pad16(4 * nn));
     const uint16_t* ents = reinterpret_cast<const uint16_t*>(sB + pad16(4 * nn) + pad16(2 * (nn + 1)));
+    if (!(a.dbg & 2))
     for (int q = tid; q < nn; q += THREADS) {
       const int beg = coff[q], end = coff[q + 1];
       double acc = 0.0;
-      for (int e = beg; e < end; e++) {
-        const uint32_t en = ents[e];
-        acc += stage[(en & 15u) * EP + (en >> 4)];
-      }
+      for (int e = beg; e < end; e++) acc += stage[ents[e]];  // ents: pair * e_pad + slot, ascending element order
       a.vals[gidx[q]] = acc;
     }
-    if (MODE == ASM_PICARD) {
-      dmax = block_max(dmax, red);  // contains the barriers that release stage / us / this buffer
-      if (tid == 0) a.tile_max[tile_of(i)] = dmax;
-    } else {
-      __syncthreads();  // stage and this tile's buffers may be overwritten from here on
-    }
+    if (MODE == ASM_PICARD && i + 1 < mine)
+      stage_u(TileView(buf0 + (size_t)((i + 1) & 1) * bufsz), us0 + (size_t)((i + 1) & 1) * us_stride);
+    __syncthreads();  // stage, this tile's blob buffer and us[i & 1] may be overwritten from here on
   }
 }

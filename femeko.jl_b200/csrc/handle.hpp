@@ -72,7 +72,8 @@ struct fk_handle_s {
   long long nnz_sell = 0;
   fk::DevBuf<int> tile_hdr;            // int4 per tile
   fk::DevBuf<uint32_t> tile_blob;      // packed per-tile plan blobs (symbolic.hpp)
-  int e_pad = 0, asm_cfg = 0;
+  int e_pad = 0, asm_cfg = 0, asm_dbg = 0;
+  double* pin8 = nullptr;              // pinned host landing zone of the 8-double scalar block
   int asm_grid[8] = {0, 0, 0, 0, 0, 0, 0, 0};  // persistent grid per assembly mode
   size_t asm_smem = 0;
   // matrices
@@ -80,6 +81,8 @@ struct fk_handle_s {
   // nonlinear state
   fk::DevBuf<double> mu, dmu, Hn, Hfield, tile_max, scal;
   fk::DevBuf<unsigned char> matid;
+  fk::DevBuf<int> mat_list;            // ids of the elements with a B-H curve (matid > 0), ascending
+  int n_mat = 0;
   fk::DevBuf<int> errflag;
   fk::DevBuf<double> spl_t[FK_MAX_SPLINES], spl_c[FK_MAX_SPLINES];
   fk::SplineSet spl{};

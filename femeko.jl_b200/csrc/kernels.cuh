@@ -282,6 +282,48 @@ __device__ __forceinline__ double splev_dev(const SplineDev& S, double x, int& e
 
 #include "assemble.cuh"
 
+// mu(|H|), dmu/dH of the material elements from the B-H spline (NewtonRaphson.jl:178-207; manyBodyIntersecting.jl:189-197),
+// run just before the fused sweep of a Picard step: one thread per listed element recomputes H from the potential,
+// evaluates the spline(s), stores mu / dmu and folds |  |H| - |H|old  | into a per-CTA maximum (the convergence
+// metric of NewtonRaphson.jl:200).  |H|old is read here, before the sweep overwrites it.  Linear elements are never
+// touched, so the sweep itself carries no spline code.
+static __global__ void __launch_bounds__(256) material_update_kernel(const double4* __restrict__ p4, const int4* __restrict__ t4,
+                                                              const int* __restrict__ list, int n,
+                                                              const unsigned char* __restrict__ matid,
+                                                              const double* __restrict__ u, const SplineSet spl, int compat,
+                                                              const double* __restrict__ Hn_old, double* __restrict__ mu,
+                                                              double* __restrict__ dmu, double* __restrict__ part_max,
+                                                              int* __restrict__ errflag) {
+  __shared__ double red[33];
+  double dmax = 0.0;
+  int err = 0;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const int k = __ldg(list + i);
+    const int mat = (int)__ldg(matid + k);
+    if (mat <= 0) continue;
+    const int4 nd = __ldg(t4 + k);
+    TetGeom G;
+    tet_geometry(p4, nd, G);
+    const double u0 = __ldg(u + nd.x), u1 = __ldg(u + nd.y), u2 = __ldg(u + nd.z), u3 = __ldg(u + nd.w);
+    double hx = -(u0 * G.g[0][0]) - u1 * G.g[1][0] - u2 * G.g[2][0] - u3 * G.g[3][0];
+    double hy = -(u0 * G.g[0][1]) - u1 * G.g[1][1] - u2 * G.g[2][1] - u3 * G.g[3][1];
+    double hz = -(u0 * G.g[0][2]) - u1 * G.g[1][2] - u2 * G.g[2][2] - u3 * G.g[3][2];
+    if (compat) { hy += hz; hz = 0.0; }  // NewtonRaphson.jl:187-189: d-term lands in row 2
+    const double Hn = sqrt(hx * hx + hy * hy + hz * hz);
+    const double f = splev_dev(spl.s[mat - 1], Hn, err);
+    double df = 0.0;
+    const SplineDev& D = spl.s[FK_MAX_SPLINES / 2 + mat - 1];
+    if (dmu && D.n > 0) df = splev_dev(D, Hn, err);
+    if (!(f == f) || fabs(f) > DBL_MAX || !(df == df) || fabs(df) > DBL_MAX) err |= 2;  // Nans/Infs in mu
+    dmax = fmax(dmax, fabs(Hn - Hn_old[k]));
+    mu[k] = f;
+    if (dmu) dmu[k] = df;
+  }
+  if (err) atomicOr(errflag, err);
+  dmax = block_max(dmax, red);
+  if (threadIdx.x == 0) part_max[blockIdx.x] = dmax;
+}
+
 // dense 16 x nt local stiffness (localStiffnessMatrix, src/FEM3D.jl:59-76) -- API completeness
 static __global__ void local_stiffness_kernel(const double4* __restrict__ p4, const int4* __restrict__ t4,
                                        const double* __restrict__ VE, const double* __restrict__ f, int nt,

@@ -216,7 +216,7 @@ void build_symbolic(const double* p, const int* t, int nv, int nt, const Symboli
   {
     std::vector<int> rows;
     std::vector<uint32_t> elems;
-    std::vector<int> base, cnt, perm, newpos, fillp;
+    std::vector<int> base, cnt, perm, newpos, fillp, slot_of;
 #pragma omp for schedule(dynamic, 16)
     for (int tl = 0; tl < T; tl++) {
       rows.assign(order.begin() + tile_row_ptr[tl], order.begin() + tile_row_ptr[tl + 1]);
@@ -231,13 +231,27 @@ void build_symbolic(const double* p, const int* t, int nv, int nt, const Symboli
         bad = 1;
         continue;
       }
+      // staging slots: the elements this tile OWNS first (ascending id), then the ones it only recomputes
+      // (ascending id) -- whole warps of the fused sweep can then skip the per-owner work
       uint32_t* te = S.tile_elems.data() + S.tile_elem_ptr[tl];
-      for (size_t s = 0; s < elems.size(); s++) {
-        const int* e = t + 4 * (size_t)elems[s];
-        int owner_row = -1;
-        for (int i = 0; i < 4 && owner_row < 0; i++) if (e[i] < nr) owner_row = e[i];
-        uint32_t own = (owner_row >= 0 && tile_of_row[owner_row] == tl) ? 0x80000000u : 0u;
-        te[s] = elems[s] | own;
+      slot_of.resize(elems.size());
+      {
+        int n_own = 0;
+        for (size_t s = 0; s < elems.size(); s++) {
+          const int* e = t + 4 * (size_t)elems[s];
+          int owner_row = -1;
+          for (int i = 0; i < 4 && owner_row < 0; i++) if (e[i] < nr) owner_row = e[i];
+          const bool own = owner_row >= 0 && tile_of_row[owner_row] == tl;
+          slot_of[s] = own ? 1 : 0;
+          n_own += own;
+        }
+        int a = 0, b = n_own;
+        for (size_t s = 0; s < elems.size(); s++) {
+          const bool own = slot_of[s] != 0;
+          const int slot = own ? a++ : b++;
+          slot_of[s] = slot;
+          te[slot] = elems[s] | (own ? 0x80000000u : 0u);
+        }
       }
       // tile-local numbering of the entries of the tile's rows
       int nloc = 0;
@@ -270,7 +284,7 @@ void build_symbolic(const double* p, const int* t, int nv, int nt, const Symboli
         int r = rows[m];
         for (int64_t q = n2e_ptr[r]; q < n2e_ptr[r + 1]; q++) {  // ascending element order
           uint32_t k = n2e[q] >> 2, i = n2e[q] & 3;
-          uint32_t slot = (uint32_t)(std::lower_bound(elems.begin(), elems.end(), k) - elems.begin());
+          uint32_t slot = (uint32_t)slot_of[std::lower_bound(elems.begin(), elems.end(), k) - elems.begin()];
           for (int j = 0; j < 4; j++) {
             int loc = newpos[base[m] + (S.e2nnz[(size_t)16 * k + 4 * i + j] - S.rowptr[r])];
             ents[fillp[loc]++] = (uint16_t)((slot << 4) | (uint32_t)sym_index((int)i, j));
@@ -358,6 +372,8 @@ void build_symbolic(const double* p, const int* t, int nv, int nt, const Symboli
 #pragma omp parallel for schedule(static)
       for (int tl = 0; tl < T; tl++) std::copy(per[tl].begin(), per[tl].end(), tnodes.begin() + node_ptr[tl]);
     }
+    S.e_pad = (S.max_tile_elems + 15) & ~15;
+    if (10 * (int64_t)S.e_pad > 65535) throw std::runtime_error("fk: tile_max_elems too large for 16-bit staging indices");
     S.tile_hdr.assign((size_t)4 * T, 0);
     std::vector<int64_t> off((size_t)T + 1, 0);  // bytes
     for (int tl = 0; tl < T; tl++) {
@@ -412,7 +428,11 @@ void build_symbolic(const double* p, const int* t, int nv, int nt, const Symboli
       dst += pad16(4 * nn);
       std::memcpy(dst, S.tile_coff.data() + S.tile_nnz_ptr[tl] + tl, sizeof(uint16_t) * ((size_t)nn + 1));
       dst += pad16(2 * (nn + 1));
-      std::memcpy(dst, S.tile_ents.data() + S.tile_ent_ptr[tl], sizeof(uint16_t) * (size_t)nents);
+      {  // contributor lists as direct indices into the staging array: pair * e_pad + slot (< 10 * e_pad <= 65535)
+        const uint16_t* es = S.tile_ents.data() + S.tile_ent_ptr[tl];
+        uint16_t* ed = reinterpret_cast<uint16_t*>(dst);
+        for (int q = 0; q < nents; q++) ed[q] = (uint16_t)((es[q] & 15u) * (uint32_t)S.e_pad + (es[q] >> 4));
+      }
     }
   }
 

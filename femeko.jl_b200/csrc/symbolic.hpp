@@ -52,6 +52,7 @@ struct Symbolic {
   std::vector<uint32_t> tile_blob;  // packed words
   int max_blob_a = 0, max_blob_b = 0;  // bytes
   int max_tile_nodes = 0;
+  int e_pad = 16;                      // staging stride of the assembly kernel: max_tile_elems rounded up to 16
 
   // Device storage of every matrix on this pattern: SELL-32-sigma (sliced ELLPACK).  Slice s holds the
   // 32 rows srow[32s .. 32s+31] (-1 = padding lane); its entries sit column-major from slice_ptr[s]:

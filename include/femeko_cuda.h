@@ -73,7 +73,8 @@ int fk_set_stream(fk_handle h, void* stream);
 int fk_synchronize(fk_handle h);
 /* change a launch option after creation (tuning sweeps): what 0 = asm_cfg, 1 = spmv_ctas_per_sm (values
  * as in fk_create_opts), 2 = pin the PCG vectors in L2 with a persisting access-policy window (1 = on,
- * the default; 0 = off).  Matrix values do not depend on these.                                    */
+ * the default; 0 = off).  Matrix values do not depend on these.  3 = profiling experiments only: bit 0 / 1
+ * skip phase 1 / 2 of the assembly kernel (matrix values are then garbage).                        */
 int fk_tune(fk_handle h, int what, int value);
 /* number of kernels of this library launched through the handle so far (graph nodes included) */
 int fk_launch_count(fk_handle h, long long* n);

@@ -37,6 +37,7 @@ def main():
     ap.add_argument("--blocks", default="1,1024", help="SELL sigma values")
     ap.add_argument("--stages", default="0,4,6", help="SpMV CTAs per SM caps")
     ap.add_argument("--out", default="gpurun_out/sweep.jsonl")
+    ap.add_argument("--no-spmv", action="store_true")
     args = ap.parse_args()
     dev = torch.device("cuda", 0)
     torch.cuda.set_device(0)
@@ -86,7 +87,7 @@ def main():
                     except Exception as e:  # noqa: BLE001
                         emit({"kind": "asm", "tile": tile, "cfg": cfg, "error": str(e)})
                 h.tune(0, 0)
-            if first:
+            if first and not args.no_spmv:
                 h.assemble_stiffness_dev(h.device_ptr(3), slot=0)
                 b = torch.from_numpy(np.random.default_rng(0).standard_normal(h.nv)).to(dev)
                 x = torch.zeros(h.nv, dtype=torch.float64, device=dev)
