@@ -69,14 +69,15 @@ static AsmArgs base_args(fk_handle h, double* vals) {
   a.vals = vals;
   a.e_pad = h->e_pad;
   a.nno_max = h->sym.max_tile_nodes;
-  a.blob_a_max = h->sym.max_blob_a;
+  a.blob_i_max = h->sym.max_blob_i;
+  a.blob_g_max = h->sym.max_blob_g;
   a.blob_b_max = h->sym.max_blob_b;
   a.dbg = h->asm_dbg;
   return a;
 }
 
 // launch configurations of the assembly kernel: {threads per CTA, min resident CTAs per SM}
-constexpr int kNumAsmCfg = 6;
+constexpr int kNumAsmCfg = 8;
 template <int MODE, int THREADS, int MINB>
 static void launch_assemble_cfg(fk_handle h, const AsmArgs& a, bool setup) {
   if (setup) {  // persistent grid: every resident CTA slot of the device, fixed per configuration
@@ -91,13 +92,16 @@ static void launch_assemble_cfg(fk_handle h, const AsmArgs& a, bool setup) {
 template <int MODE>
 static void launch_assemble(fk_handle h, const AsmArgs& a, bool setup = false) {
   if (h->sym.ntiles == 0) return;
-  // 0 = measured default: the fused Picard sweep needs > 80 registers (2 CTAs/SM), the others fit 3 CTAs/SM
-  const int cfg = h->asm_cfg > 0 ? h->asm_cfg : (MODE == ASM_PICARD ? 2 : 1);
+  // 0 = measured default: {256, 2} for every mode (two CTAs per SM is what shared memory allows; the 128-register
+  // budget keeps phase 1 free of spills)
+  const int cfg = h->asm_cfg > 0 ? h->asm_cfg : 2;
   switch (cfg) {
     case 2: launch_assemble_cfg<MODE, 256, 2>(h, a, setup); break;
     case 3: launch_assemble_cfg<MODE, 384, 2>(h, a, setup); break;
     case 4: launch_assemble_cfg<MODE, 512, 2>(h, a, setup); break;
     case 5: launch_assemble_cfg<MODE, 128, 6>(h, a, setup); break;
+    case 6: launch_assemble_cfg<MODE, 512, 1>(h, a, setup); break;
+    case 7: launch_assemble_cfg<MODE, 768, 1>(h, a, setup); break;
     default: launch_assemble_cfg<MODE, 256, 3>(h, a, setup); break;
   }
   if (setup) return;
@@ -491,10 +495,10 @@ int fk_create(const double* p, const int* t, int nv, int nt, const double* VE, c
     // the device only needs the packed blobs; drop the host copies of the unpacked plan
     h->sym.tile_blob = std::vector<uint32_t>();
     h->e_pad = S.e_pad;
-    h->asm_smem = asm_smem_bytes(h->e_pad, S.max_tile_nodes, S.max_blob_a, S.max_blob_b);
-    need(h->asm_smem <= (size_t)prop.sharedMemPerBlockOptin, "fk_create: assembly tile does not fit in shared memory");
     need(o.asm_cfg >= 0 && o.asm_cfg < kNumAsmCfg, "fk_create: asm_cfg out of range");
     h->asm_cfg = o.asm_cfg;
+    h->asm_smem = asm_smem_bytes(h->e_pad, S.max_tile_nodes, S.max_blob_i, S.max_blob_g, S.max_blob_b);
+    need(h->asm_smem <= (size_t)prop.sharedMemPerBlockOptin, "fk_create: assembly tile does not fit in shared memory");
     {
       AsmArgs dummy{};
       launch_assemble<ASM_STIFF>(h.get(), dummy, true);

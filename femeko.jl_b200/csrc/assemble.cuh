@@ -1,18 +1,21 @@
 // K1: tile-gather assembly (included inside namespace fk by kernels.cuh).
 //
 // Persistent CTAs walk the tiles of the symbolic phase (symbolic.hpp).  Everything a tile needs is ONE
-// packed blob in HBM -- node coordinates, local connectivity, element ids, and the gather plan -- that
-// thread 0 fetches with two bulk (TMA, cp.async.bulk) copies completing on mbarriers, one tile AHEAD of
-// the compute (double-buffered), so the warps never wait on a dependent chain of global gathers:
-//   copy A  x|y|z of the tile's nodes, global node ids, element ids, local connectivity  -> phase 1
-//   copy B  gidx | coff | contributor lists                                              -> phase 2
+// packed blob in HBM, fetched by thread 0 with three bulk (TMA, cp.async.bulk) copies completing on
+// mbarriers, ahead of the compute, so the warps never wait on a dependent chain of global gathers:
+//   section I  sizes, global node ids, element ids (two tiles ahead: feeds the next tile's gathers)
+//   section G  x|y|z of the tile's nodes, local connectivity (one tile ahead)               -> phase 1
+//   section B  gidx | coff | contributor lists (one tile ahead)                             -> phase 2
 // Phase 1: one thread per staged element computes the 10 unique entries of the symmetric 4x4 local
-// matrix into shared memory (SoA: pair-major) from shared-memory coordinates.
-// Phase 2: one thread per CSR entry owned by the tile sums its contributors (slot, pair) in
-// ascending element order out of shared memory and writes the value once.  Entries are issued
-// longest list first so a warp's 32 lists have near-equal length.  No atomics; bitwise reproducible.
+// matrix into shared memory (SoA: pair-major) from shared-memory coordinates.  The elements a tile owns
+// come first in the staging order; in the fused Picard sweep only those also store H and |H|.
+// Phase 2: one thread per CSR entry owned by the tile sums its contributors (staging index = pair *
+// e_pad + slot) in ascending element order out of shared memory and writes the value once.  Entries are
+// issued longest list first so a warp's 32 lists have near-equal length.  No atomics; bitwise reproducible.
+// mu(|H|) of the material elements is refreshed by material_update_kernel (kernels.cuh) before the sweep,
+// so this kernel carries no spline code.
 // Reference math: src/FEM3D.jl:59-76 (stiffness), :466-476 (mass), :79-105 (tangential),
-// :274-281 (lagrange), NewtonRaphson.jl:178-207 (Picard: H recovery + spline + rescale).
+// :274-281 (lagrange), NewtonRaphson.jl:178-197 (Picard: H recovery + rescale by mu).
 
 enum AsmMode { ASM_STIFF = 0, ASM_MASS = 1, ASM_TANGENT = 2, ASM_PICARD = 3, ASM_LAGRANGE = 4 };
 
@@ -26,13 +29,14 @@ struct AsmArgs {
   double* Hfield;         // nullable, 3 x nt
   int compat;
   // plan
-  const int4* tile_hdr;   // {blob offset / 16, ne | nno << 16, nn, nents}
+  const int4* tile_hdr;   // {blob offset / 16, bytes of I, bytes of G, bytes of B}
   const uint4* tile_blob; // 16-byte units
   int ntiles;
   double* vals;
   int e_pad;              // staging stride (>= max tile elements)
   int nno_max;            // max nodes per tile (u staging)
-  int blob_a_max;         // bytes reserved in shared memory for section A / B (per buffer)
+  int blob_i_max;         // bytes reserved in shared memory for sections I / G / B (per buffer)
+  int blob_g_max;
   int blob_b_max;
   int dbg;                // profiling experiments only (fk_tune 3): bit 0 skips phase 1, bit 1 skips phase 2
 };
@@ -122,7 +126,7 @@ __device__ __forceinline__ void element_local(const AsmArgs& a, const int k, con
       double hy = -(u0 * G.g[0][1]) - u1 * G.g[1][1] - u2 * G.g[2][1] - u3 * G.g[3][1];
       double hz = -(u0 * G.g[0][2]) - u1 * G.g[1][2] - u2 * G.g[2][2] - u3 * G.g[3][2];
       if (a.compat) { hy += hz; hz = 0.0; }  // NewtonRaphson.jl:187-189: d-term lands in row 2
-      a.Hn[k] = sqrt(hx * hx + hy * hy + hz * hz);
+      a.Hn[k] = norm3(hx, hy, hz);
       if (a.Hfield) { a.Hfield[3 * (size_t)k] = hx; a.Hfield[3 * (size_t)k + 1] = hy; a.Hfield[3 * (size_t)k + 2] = hz; }
     }
   }
@@ -143,60 +147,78 @@ __device__ __forceinline__ void fetch_coef(const AsmArgs& a, const int k, double
 }
 
 // ---- the kernel ----------------------------------------------------------------------------------
-// Shared memory: [ stage 10 x e_pad f64 | us 2 x nno_max f64 | (A | B) buffer 0 | (A | B) buffer 1 ].
-__host__ __device__ inline size_t asm_smem_bytes(int e_pad, int nno_max, int blob_a_max, int blob_b_max) {
-  return (size_t)80 * e_pad + 2 * (size_t)pad16(8 * nno_max) + 2 * ((size_t)blob_a_max + blob_b_max);
+// Shared memory: [ stage 10 x e_pad f64 | us 2 x nno_max f64 | I x (depth + 1) | (G | B) x depth ].
+constexpr int kAsmDepth = 2;  // ring depth of the geometry / gather-plan sections (ids: one more); deeper rings measured slower
+__host__ __device__ inline size_t asm_smem_bytes(int e_pad, int nno_max, int blob_i_max, int blob_g_max, int blob_b_max) {
+  return (size_t)80 * e_pad + 2 * (size_t)pad16(8 * nno_max) + (size_t)(kAsmDepth + 1) * blob_i_max +
+         (size_t)kAsmDepth * ((size_t)blob_g_max + blob_b_max);
 }
 
-struct TileView {  // pointers into one shared-memory copy of section A
+struct TileView {  // pointers into the shared-memory copies of sections I and G of one tile
   int ne, nno, nn;
-  const double *xs, *ys, *zs;
   const int* gnode;
   const uint32_t* ek;
+  const double *xs, *ys, *zs;
   const uint2* loc;
-  __device__ __forceinline__ explicit TileView(const unsigned char* sA) {
-    const int4 h = *reinterpret_cast<const int4*>(sA);
+  __device__ __forceinline__ TileView(const unsigned char* sI, const unsigned char* sG) {
+    const int4 h = *reinterpret_cast<const int4*>(sI);
     ne = h.x; nno = h.y; nn = h.z;
-    const unsigned char* q = sA + 16;
+    const unsigned char* q = sI + 32;
+    gnode = reinterpret_cast<const int*>(q); q += pad16(4 * nno);
+    ek = reinterpret_cast<const uint32_t*>(q);
+    q = sG;
     xs = reinterpret_cast<const double*>(q); q += pad16(8 * nno);
     ys = reinterpret_cast<const double*>(q); q += pad16(8 * nno);
     zs = reinterpret_cast<const double*>(q); q += pad16(8 * nno);
-    gnode = reinterpret_cast<const int*>(q); q += pad16(4 * nno);
-    ek = reinterpret_cast<const uint32_t*>(q); q += pad16(4 * ne);
     loc = reinterpret_cast<const uint2*>(q);
   }
 };
 
 constexpr int kAsmPre = 2;  // per-thread register prefetch depth (elements / nodes of the NEXT tile)
 
-// Two CTA-wide barriers per tile: one between the phases, one at the end of the tile (which also publishes the
-// next tile's potential values and releases the staging array and the blob buffer).
+// Pipeline (per persistent CTA, ring depth D = kAsmDepth): while tile i computes, the ids of tiles i+1 .. i+D and the
+// geometry + gather plans of tiles i+1 .. i+D-1 are resident or in flight, so HBM always has this CTA's requests
+// queued whatever phase the SM is in; the coefficient / potential gathers of tile i+1 are issued (from ids that
+// landed at least a tile ago) before phase 2 of tile i.  Two CTA-wide barriers per tile: one between the phases,
+// one at the end of the tile (which also publishes the next tile's potential values and releases the staging array
+// and the ring slots of tile i).
 template <int MODE, int THREADS, int MINB>
 static __global__ void __launch_bounds__(THREADS, MINB) assemble_kernel(const __grid_constant__ AsmArgs a) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
-  __shared__ __align__(8) uint64_t barA[2], barB[2];
+  __shared__ __align__(8) uint64_t barI[kAsmDepth + 1], barG[kAsmDepth], barB[kAsmDepth];
   const int tid = threadIdx.x;
   const int EP = a.e_pad;
+  constexpr int D = kAsmDepth, DI = kAsmDepth + 1;
   double* stage = reinterpret_cast<double*>(smem_raw);
   double* us0 = stage + (size_t)10 * EP;
   const int us_stride = pad16(8 * a.nno_max) / 8;
-  unsigned char* buf0 = reinterpret_cast<unsigned char*>(us0 + 2 * (size_t)us_stride);
-  const size_t bufsz = (size_t)a.blob_a_max + a.blob_b_max;
+  unsigned char* bufI = reinterpret_cast<unsigned char*>(us0 + 2 * (size_t)us_stride);
+  unsigned char* bufG = bufI + (size_t)DI * a.blob_i_max;
+  const size_t gbsz = (size_t)a.blob_g_max + a.blob_b_max;
 
   const int mine = (a.ntiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;  // tiles of this CTA
   if (mine <= 0) return;
   auto tile_of = [&](int i) { return (int)blockIdx.x + i * (int)gridDim.x; };
-  auto issue = [&](int i, const int4 hdr) {  // thread 0: fetch tile i's blob into buffer i & 1
-    unsigned char* dst = buf0 + (size_t)(i & 1) * bufsz;
-    const uint4* src = a.tile_blob + (size_t)hdr.x;
-    mbar_expect_tx(&barA[i & 1], (uint32_t)hdr.y);
-    bulk_g2s(dst, src, (uint32_t)hdr.y, &barA[i & 1]);
-    mbar_expect_tx(&barB[i & 1], (uint32_t)hdr.z);
-    bulk_g2s(dst + a.blob_a_max, src + (hdr.y >> 4), (uint32_t)hdr.z, &barB[i & 1]);
+  auto ids_of = [&](int i) { return bufI + (size_t)(i % DI) * a.blob_i_max; };
+  auto gb_of = [&](int i) { return bufG + (size_t)(i % D) * gbsz; };
+  auto issue_ids = [&](int i, const int2 hdr) {  // thread 0: ids of tile i -> ring slot i % (D + 1)
+    mbar_expect_tx(&barI[i % DI], (uint32_t)hdr.y);
+    bulk_g2s(ids_of(i), a.tile_blob + (size_t)hdr.x, (uint32_t)hdr.y, &barI[i % DI]);
   };
+  auto issue_gb = [&](int i) {  // thread 0: geometry + gather plan of tile i -> ring slot i % D; sizes come from its ids
+    mbar_wait(&barI[i % DI], (uint32_t)((i / DI) & 1));  // requested at least a tile ago
+    const int4 h = *reinterpret_cast<const int4*>(ids_of(i) + 16);  // {G offset / 16, bytes I, bytes G, bytes B}
+    unsigned char* dst = gb_of(i);
+    const uint4* src = a.tile_blob + (size_t)h.x;
+    mbar_expect_tx(&barG[i % D], (uint32_t)h.z);
+    bulk_g2s(dst, src, (uint32_t)h.z, &barG[i % D]);
+    mbar_expect_tx(&barB[i % D], (uint32_t)h.w);
+    bulk_g2s(dst + a.blob_g_max, src + (h.z >> 4), (uint32_t)h.w, &barB[i % D]);
+  };
+  const int2* hdr2 = reinterpret_cast<const int2*>(a.tile_hdr);  // first half of each int4 header: {offset / 16, bytes of I}
 
   double fpre[kAsmPre], vpre[kAsmPre], upre[kAsmPre];
-  auto prefetch = [&](const TileView& T) {  // coefficient / potential gathers of a tile whose section A has landed
+  auto prefetch = [&](const TileView& T) {  // coefficient / potential gathers of a tile whose ids have landed
 #pragma unroll
     for (int j = 0; j < kAsmPre; j++) {
       const int s = tid + j * THREADS;
@@ -212,30 +234,34 @@ static __global__ void __launch_bounds__(THREADS, MINB) assemble_kernel(const __
     for (int n = tid + kAsmPre * THREADS; n < T.nno; n += THREADS) us[n] = __ldg(a.u + T.gnode[n]);
   };
 
-  int4 hnext = make_int4(0, 0, 0, 0);  // thread 0: header of tile i + 1, loaded one tile ahead
+  int2 hnext = make_int2(0, 0);  // thread 0: header of the next tile whose ids will be requested
   if (tid == 0) {
-    mbar_init(&barA[0], 1); mbar_init(&barA[1], 1);
-    mbar_init(&barB[0], 1); mbar_init(&barB[1], 1);
+    for (int b = 0; b < DI; b++) mbar_init(&barI[b], 1);
+    for (int b = 0; b < D; b++) { mbar_init(&barG[b], 1); mbar_init(&barB[b], 1); }
     mbar_init_fence();
-    issue(0, __ldg(a.tile_hdr + tile_of(0)));
-    if (mine > 1) hnext = __ldg(a.tile_hdr + tile_of(1));
+    for (int j = 0; j < D && j < mine; j++) issue_ids(j, __ldg(hdr2 + 2 * (size_t)tile_of(j)));
+    for (int j = 0; j < D - 1 && j < mine; j++) issue_gb(j);
+    if (D < mine) hnext = __ldg(hdr2 + 2 * (size_t)tile_of(D));
   }
   __syncthreads();  // barrier init visible to every waiter
-  mbar_wait(&barA[0], 0);
-  prefetch(TileView(buf0));
+  mbar_wait(&barI[0], 0);
+  prefetch(TileView(ids_of(0), bufG));
   if (MODE == ASM_PICARD) {
-    stage_u(TileView(buf0), us0);
+    stage_u(TileView(ids_of(0), bufG), us0);
     __syncthreads();
   }
 
   for (int i = 0; i < mine; i++) {
-    if (tid == 0 && i + 1 < mine) {  // buffer (i+1)&1 was released by the barrier that ended tile i-1
-      issue(i + 1, hnext);
-      if (i + 2 < mine) hnext = __ldg(a.tile_hdr + tile_of(i + 2));
+    if (tid == 0) {  // the ring slots written here were released by the barrier that ended tile i-1
+      if (i + D - 1 < mine) issue_gb(i + D - 1);
+      if (i + D < mine) {
+        issue_ids(i + D, hnext);
+        if (i + D + 1 < mine) hnext = __ldg(hdr2 + 2 * (size_t)tile_of(i + D + 1));
+      }
     }
-    const unsigned char* sA = buf0 + (size_t)(i & 1) * bufsz;
-    const unsigned char* sB = sA + a.blob_a_max;
-    const TileView T(sA);  // section A of tile i was awaited before its prefetch
+    mbar_wait(&barG[i % D], (uint32_t)((i / D) & 1));
+    const TileView T(ids_of(i), gb_of(i));  // the ids of tile i were awaited before its prefetch
+    const unsigned char* sB = gb_of(i) + a.blob_g_max;
     const int ne = T.ne, nn = T.nn;
     const double* us = us0 + (size_t)(i & 1) * us_stride;
 
@@ -261,26 +287,36 @@ static __global__ void __launch_bounds__(THREADS, MINB) assemble_kernel(const __
       for (int q = 0; q < 10; q++) stage[q * EP + s] = m[q];
     }
     }
-    if (i + 1 < mine) {  // next tile's gathers fly during this tile's phase 2
-      mbar_wait(&barA[(i + 1) & 1], (uint32_t)(((i + 1) >> 1) & 1));
-      prefetch(TileView(buf0 + (size_t)((i + 1) & 1) * bufsz));
+    if (i + 1 < mine) {  // next tile's gathers fly during this tile's phase 2; its ids were requested >= a tile ago
+      mbar_wait(&barI[(i + 1) % DI], (uint32_t)(((i + 1) / DI) & 1));
+      prefetch(TileView(ids_of(i + 1), bufG));   // ids only: the geometry pointers are not used
     }
     __syncthreads();
-    mbar_wait(&barB[i & 1], (uint32_t)((i >> 1) & 1));
+    mbar_wait(&barB[i % D], (uint32_t)((i / D) & 1));
 
     // ---- phase 2 ------------------------------------------------------------------------------
     const int* gidx = reinterpret_cast<const int*>(sB);
     const uint16_t* coff = reinterpret_cast<const uint16_t*>(sB + pad16(4 * nn));
     const uint16_t* ents = reinterpret_cast<const uint16_t*>(sB + pad16(4 * nn) + pad16(2 * (nn + 1)));
+    // two entries per thread at a time (independent load -> add chains); entries are sorted longest list first, so
+    // the second entry's list is never the longer one.  ents: pair * e_pad + slot, in ascending element order.
     if (!(a.dbg & 2))
-    for (int q = tid; q < nn; q += THREADS) {
-      const int beg = coff[q], end = coff[q + 1];
-      double acc = 0.0;
-      for (int e = beg; e < end; e++) acc += stage[ents[e]];  // ents: pair * e_pad + slot, ascending element order
-      a.vals[gidx[q]] = acc;
+    for (int q = tid; q < nn; q += 2 * THREADS) {
+      const int q2 = q + THREADS;
+      const bool two = q2 < nn;
+      const int b1 = coff[q], n1 = coff[q + 1] - b1;
+      const int b2 = two ? coff[q2] : 0, n2 = two ? coff[q2 + 1] - b2 : 0;
+      double acc1 = 0.0, acc2 = 0.0;
+      int e = 0;
+      for (; e < n2; e++) {
+        acc1 += stage[ents[b1 + e]];
+        acc2 += stage[ents[b2 + e]];
+      }
+      for (; e < n1; e++) acc1 += stage[ents[b1 + e]];
+      a.vals[gidx[q]] = acc1;
+      if (two) a.vals[gidx[q2]] = acc2;
     }
-    if (MODE == ASM_PICARD && i + 1 < mine)
-      stage_u(TileView(buf0 + (size_t)((i + 1) & 1) * bufsz), us0 + (size_t)((i + 1) & 1) * us_stride);
-    __syncthreads();  // stage, this tile's blob buffer and us[i & 1] may be overwritten from here on
+    if (MODE == ASM_PICARD && i + 1 < mine) stage_u(TileView(ids_of(i + 1), bufG), us0 + (size_t)((i + 1) & 1) * us_stride);
+    __syncthreads();  // stage, this tile's ring slots and us[i & 1] may be overwritten from here on
   }
 }

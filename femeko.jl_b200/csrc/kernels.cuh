@@ -193,6 +193,13 @@ __device__ __forceinline__ void grid_reduce_finish(const double (&v)[NV], double
 // E = [x1-x0 | x2-x0 | x3-x0], rows of inv(E) are grad(lambda_1..3), grad(lambda_0) = -(sum).
 // Nodes are padded to 32 B (x,y,z,0) so one node = one aligned sector = two 128-bit loads.
 // ------------------------------------------------------------------------------------------------
+// |h|: exact zeros (potential still flat, e.g. the first Picard step) skip the fp64 sqrt, whose zero / denormal
+// inputs take the slow path of the software sequence; sqrt(0) = 0, so the value is the same bit for bit
+__device__ __forceinline__ double norm3(double hx, double hy, double hz) {
+  const double h2 = hx * hx + hy * hy + hz * hz;
+  return h2 > 0.0 ? sqrt(h2) : h2;
+}
+
 struct TetGeom {
   double g[4][3];  // grad(lambda_i)
   double vol;      // |det E| / 6  (elementVolume, src/mesh.jl:484-505)
@@ -309,7 +316,7 @@ static __global__ void __launch_bounds__(256) material_update_kernel(const doubl
     double hy = -(u0 * G.g[0][1]) - u1 * G.g[1][1] - u2 * G.g[2][1] - u3 * G.g[3][1];
     double hz = -(u0 * G.g[0][2]) - u1 * G.g[1][2] - u2 * G.g[2][2] - u3 * G.g[3][2];
     if (compat) { hy += hz; hz = 0.0; }  // NewtonRaphson.jl:187-189: d-term lands in row 2
-    const double Hn = sqrt(hx * hx + hy * hy + hz * hz);
+    const double Hn = norm3(hx, hy, hz);
     const double f = splev_dev(spl.s[mat - 1], Hn, err);
     double df = 0.0;
     const SplineDev& D = spl.s[FK_MAX_SPLINES / 2 + mat - 1];
@@ -364,7 +371,7 @@ static __global__ void __launch_bounds__(256) recover_field_kernel(const double4
   double hy = -(u0 * G.g[0][1]) - u1 * G.g[1][1] - u2 * G.g[2][1] - u3 * G.g[3][1];
   double hz = -(u0 * G.g[0][2]) - u1 * G.g[1][2] - u2 * G.g[2][2] - u3 * G.g[3][2];
   if (compat) { hy += hz; hz = 0.0; }
-  const double H = sqrt(hx * hx + hy * hy + hz * hz);
+  const double H = norm3(hx, hy, hz);
   if (Hfield) { Hfield[3 * (size_t)k] = hx; Hfield[3 * (size_t)k + 1] = hy; Hfield[3 * (size_t)k + 2] = hz; }
   if (Hn) Hn[k] = H;
   if (B) B[k] = __ldg(mu + k) * H;

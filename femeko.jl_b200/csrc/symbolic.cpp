@@ -379,16 +379,17 @@ void build_symbolic(const double* p, const int* t, int nv, int nt, const Symboli
     for (int tl = 0; tl < T; tl++) {
       const int ne = tile_nelem[tl], nn = (int)(S.tile_nnz_ptr[tl + 1] - S.tile_nnz_ptr[tl]),
                 nents = (int)(S.tile_ent_ptr[tl + 1] - S.tile_ent_ptr[tl]), nno = (int)(node_ptr[tl + 1] - node_ptr[tl]);
-      const int a = blob_a_bytes(ne, nno), b = blob_b_bytes(nn, nents);
-      S.max_blob_a = std::max(S.max_blob_a, a);
+      const int bi = blob_i_bytes(ne, nno), bg = blob_g_bytes(ne, nno), b = blob_b_bytes(nn, nents);
+      S.max_blob_i = std::max(S.max_blob_i, bi);
+      S.max_blob_g = std::max(S.max_blob_g, bg);
       S.max_blob_b = std::max(S.max_blob_b, b);
       S.max_tile_nodes = std::max(S.max_tile_nodes, nno);
-      off[tl + 1] = off[tl] + a + b;
+      off[tl + 1] = off[tl] + bi + bg + b;
       if (off[tl + 1] / 16 > 0x7fffffffLL) throw std::runtime_error("fk: assembly plan too large for one GPU; partition the mesh");
       S.tile_hdr[4 * (size_t)tl] = (int)(off[tl] / 16);
-      S.tile_hdr[4 * (size_t)tl + 1] = a;
-      S.tile_hdr[4 * (size_t)tl + 2] = b;
-      S.tile_hdr[4 * (size_t)tl + 3] = 0;
+      S.tile_hdr[4 * (size_t)tl + 1] = bi;
+      S.tile_hdr[4 * (size_t)tl + 2] = bg;
+      S.tile_hdr[4 * (size_t)tl + 3] = b;
     }
     S.tile_blob.assign((size_t)(off[T] / 4), 0u);
 #pragma omp parallel for schedule(static)
@@ -397,22 +398,25 @@ void build_symbolic(const double* p, const int* t, int nv, int nt, const Symboli
                 nents = (int)(S.tile_ent_ptr[tl + 1] - S.tile_ent_ptr[tl]), nno = (int)(node_ptr[tl + 1] - node_ptr[tl]);
       unsigned char* dst = reinterpret_cast<unsigned char*>(S.tile_blob.data()) + off[tl];
       const int* nodes = tnodes.data() + node_ptr[tl];
-      // section A: sizes, node coordinates (SoA), global node ids, element ids, local connectivity
+      // section I: sizes, global node ids, element ids
       {
         int* hd = reinterpret_cast<int*>(dst);
         hd[0] = ne; hd[1] = nno; hd[2] = nn; hd[3] = nents;
-        dst += 16;
-      }
-      for (int d = 0; d < 3; d++) {
-        double* c = reinterpret_cast<double*>(dst);
-        for (int i = 0; i < nno; i++) c[i] = p ? p[3 * (size_t)nodes[i] + d] : 0.0;
-        dst += pad16(8 * nno);
+        hd[4] = S.tile_hdr[4 * (size_t)tl] + S.tile_hdr[4 * (size_t)tl + 1] / 16;
+        hd[5] = S.tile_hdr[4 * (size_t)tl + 1]; hd[6] = S.tile_hdr[4 * (size_t)tl + 2]; hd[7] = S.tile_hdr[4 * (size_t)tl + 3];
+        dst += 32;
       }
       std::memcpy(dst, nodes, sizeof(int) * (size_t)nno);
       dst += pad16(4 * nno);
       const uint32_t* te = S.tile_elems.data() + S.tile_elem_ptr[tl];
       std::memcpy(dst, te, sizeof(uint32_t) * (size_t)ne);
       dst += pad16(4 * ne);
+      // section G: node coordinates (SoA), local connectivity
+      for (int d = 0; d < 3; d++) {
+        double* c = reinterpret_cast<double*>(dst);
+        for (int i = 0; i < nno; i++) c[i] = p ? p[3 * (size_t)nodes[i] + d] : 0.0;
+        dst += pad16(8 * nno);
+      }
       uint16_t* loc = reinterpret_cast<uint16_t*>(dst);
       for (int q = 0; q < ne; q++) {
         const int* e = t + 4 * (size_t)(te[q] & 0x7fffffffu);

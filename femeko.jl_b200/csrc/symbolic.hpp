@@ -39,18 +39,19 @@ struct Symbolic {
   std::vector<uint16_t> tile_ents;     // (slot << 4) | sym(i,j): staged element slot + local pair
   int max_tile_elems = 0, max_tile_nnz = 0, max_tile_ents = 0;
 
-  // Device form of the plan: one packed, 16-byte aligned blob per tile so the kernel fetches ALL of a
-  // tile's inputs with two bulk (TMA) copies and phase 1 issues no dependent global gathers.
-  // Section A = {ne, nno, nn, nents} (4 x i32) | x | y | z (f64 x nno each: coordinates of the tile's
-  // nodes, local numbering) |
-  // gnode (i32 x nno: global node ids) | ek (u32 x ne: element id, bit 31 = owner) |
-  // loc (4 x u16 x ne: local node ids of each staged element).
-  // Section B = gidx (i32 x nn) | coff (u16 x (nn+1)) | ents (u16 x nents).
+  // Device form of the plan: one packed, 16-byte aligned blob per tile in three sections, so the kernel fetches ALL
+  // of a tile's inputs with three bulk (TMA) copies and phase 1 issues no dependent global gathers.
+  // Section I (ids, fetched two tiles ahead: it feeds the coefficient / potential gathers of the next tile) =
+  //   {ne, nno, nn, nents, offset of G in 16-byte units, bytes of I, bytes of G, bytes of B} (8 x i32) | gnode (i32 x nno: global node ids) | ek (u32 x ne: element id, bit 31 = owner).
+  // Section G (geometry, one tile ahead) = x | y | z (f64 x nno each: coordinates of the tile's nodes, local
+  //   numbering) | loc (4 x u16 x ne: local node ids of each staged element).
+  // Section B (gather plan, one tile ahead) = gidx (i32 x nn) | coff (u16 x (nn+1)) | ents (u16 x nents, as
+  //   pair * e_pad + slot).
   // Every sub-section is padded to 16 bytes.
-  // tile_hdr[T] = {offset of A in 16-byte units, bytes of A, bytes of B, 0}; B follows A directly.
+  // tile_hdr[T] = {offset of I in 16-byte units, bytes of I, bytes of G, bytes of B}; G follows I, B follows G.
   std::vector<int> tile_hdr;        // 4 * ntiles
   std::vector<uint32_t> tile_blob;  // packed words
-  int max_blob_a = 0, max_blob_b = 0;  // bytes
+  int max_blob_i = 0, max_blob_g = 0, max_blob_b = 0;  // bytes
   int max_tile_nodes = 0;
   int e_pad = 16;                      // staging stride of the assembly kernel: max_tile_elems rounded up to 16
 
@@ -79,7 +80,8 @@ void build_symbolic(const double* p, const int* t, int nv, int nt, const Symboli
 #define FK_HD
 #endif
 FK_HD inline int pad16(int bytes) { return (bytes + 15) & ~15; }
-FK_HD inline int blob_a_bytes(int ne, int nno) { return 16 + 3 * pad16(8 * nno) + pad16(4 * nno) + pad16(4 * ne) + pad16(8 * ne); }
+FK_HD inline int blob_i_bytes(int ne, int nno) { return 32 + pad16(4 * nno) + pad16(4 * ne); }
+FK_HD inline int blob_g_bytes(int ne, int nno) { return 3 * pad16(8 * nno) + pad16(8 * ne); }
 FK_HD inline int blob_b_bytes(int nn, int nents) { return pad16(4 * nn) + pad16(2 * (nn + 1)) + pad16(2 * nents); }
 
 // index of the unordered local pair (i,j) in the 10-entry symmetric staging layout

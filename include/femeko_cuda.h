@@ -40,8 +40,7 @@ typedef struct fk_create_opts {
   int device;         /* CUDA device ordinal; -1 = current device                             */
   int n_owned;        /* multi-GPU partitions: rows [0, n_owned) are owned (assembled, solved),
                          rows [n_owned, nv) are halo copies; 0 = all rows owned                 */
-  int asm_cfg;        /* assembly launch shape {threads, min CTAs/SM}: 0 = default (Picard sweep {256,2},
-                         others {256,3}); 1 {256,3} 2 {256,2} 3 {384,2} 4 {512,2} 5 {128,6}      */
+  int asm_cfg;        /* assembly launch shape {threads, min CTAs/SM}: 0 = default ({256,2}); 1 {256,3} 2 {256,2} 3 {384,2} 4 {512,2} 5 {128,6} 6 {512,1} 7 {768,1} */
   int spmv_ctas_per_sm; /* cap on resident SpMV CTAs per SM (0 = as many as fit)               */
 } fk_create_opts;
 
@@ -74,7 +73,7 @@ int fk_synchronize(fk_handle h);
 /* change a launch option after creation (tuning sweeps): what 0 = asm_cfg, 1 = spmv_ctas_per_sm (values
  * as in fk_create_opts), 2 = pin the PCG vectors in L2 with a persisting access-policy window (1 = on,
  * the default; 0 = off).  Matrix values do not depend on these.  3 = profiling experiments only: bit 0 / 1
- * skip phase 1 / 2 of the assembly kernel (matrix values are then garbage).                        */
+ * skip phase 1 / 2 of the assembly kernel (matrix values are then garbage).                            */
 int fk_tune(fk_handle h, int what, int value);
 /* number of kernels of this library launched through the handle so far (graph nodes included) */
 int fk_launch_count(fk_handle h, long long* n);

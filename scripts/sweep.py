@@ -38,6 +38,7 @@ def main():
     ap.add_argument("--stages", default="0,4,6", help="SpMV CTAs per SM caps")
     ap.add_argument("--out", default="gpurun_out/sweep.jsonl")
     ap.add_argument("--no-spmv", action="store_true")
+    ap.add_argument("--depths", default="2", help="assembly ring depths")
     args = ap.parse_args()
     dev = torch.device("cuda", 0)
     torch.cuda.set_device(0)
@@ -71,7 +72,7 @@ def main():
             h.set_mu(np.full(m.nt, MU0))
             st = h.tile_stats()
             if blk == blocks[0] or not first:
-                for cfg in [int(x) for x in args.cfgs.split(",")]:
+                for depth, cfg in [(d, c) for d in [int(x) for x in args.depths.split(",")] for c in [int(x) for x in args.cfgs.split(",")]]:
                     try:
                         h.tune(0, cfg)
                         ms_p = timed(stream, lambda: h.picard_step_dev(u.data_ptr(), slot=0), 10)
@@ -81,11 +82,11 @@ def main():
                         if ref_vals is None:
                             ref_vals = v
                         same = bool(np.array_equal(v, ref_vals))
-                        emit({"kind": "asm", "tile": tile, "cfg": cfg, "picard_ms": round(ms_p, 4), "stiff_ms": round(ms_s, 4),
+                        emit({"kind": "asm", "tile": tile, "cfg": cfg, "depth": depth, "picard_ms": round(ms_p, 4), "stiff_ms": round(ms_s, 4),
                               "mass_ms": round(ms_m, 4), "staged_ratio": round(st["staged_elems"] / m.nt, 3), "ntiles": h.ntiles,
                               "bitwise_same_as_first": same, "setup_s": round(setup, 2)})
                     except Exception as e:  # noqa: BLE001
-                        emit({"kind": "asm", "tile": tile, "cfg": cfg, "error": str(e)})
+                        emit({"kind": "asm", "tile": tile, "cfg": cfg, "depth": depth, "error": str(e)})
                 h.tune(0, 0)
             if first and not args.no_spmv:
                 h.assemble_stiffness_dev(h.device_ptr(3), slot=0)
