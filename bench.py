@@ -332,7 +332,7 @@ def run_ours(args):
                          "frac": round(pcg_gbs / peak, 4), "traffic": traffic.get("pcg_iteration_bytes"),
                          "peak_source": peak_src, "algorithmic_bytes_per_launch": it_bytes,
                          "avg_launch_ms": round(pcg_ms / Piters, 5)},
-            "roofline_assembly": {"kernel": "assemble_kernel<ASM_PICARD>", "bound": "hbm", "achieved": round(asm_gbs, 1),
+            "roofline_assembly": {"kernel": "Picard sweep: material_update_kernel + assemble_kernel<ASM_PICARD> + max fold (fk_picard_step_dev, one host poll)", "bound": "hbm", "achieved": round(asm_gbs, 1),
                                   "peak": peak, "unit": "GB/s", "frac": round(asm_gbs / peak, 4),
                                   "traffic": traffic.get("picard_assembly_bytes"), "algorithmic_bytes_per_launch": asm_bytes,
                                   "avg_launch_ms": round(asm_ms, 5)},
