@@ -1204,6 +1204,99 @@ int fk_picard_step(fk_handle h, int slot, const double* u, int compat_bug, doubl
   });
 }
 
+// ---- micromagnetics demagnetising field -----------------------------------------------
+// LL::LL + LL::magnetostaticField of Femeko_jl_C++/Micromagnetics/LL.cpp: the constructor's work (node volumes
+// :29-36, stiffnessMatrix(p,t,VE) :40) is fk_demag_setup; each fk_demag_field call is one magnetostaticField()
+// (:287-348): load vector from M, Jacobi-PCG on the persistent matrix, element field, box method to the nodes.
+int fk_demag_setup(fk_handle h, int slot, const int* inside_elements, int n_inside, double* volumes_out) {
+  return guard([&]() {
+    need(h && (inside_elements || n_inside == 0), "fk: NULL argument");
+    need(n_inside >= 0, "fk_demag_setup: negative element count");
+    need(h->comm == nullptr, "fk_demag_setup: partitioned handles are not supported");
+    DeviceGuard dg(h->device);
+    cudaStream_t s = h->stream;
+    const int nv = h->nv, nt = h->nt;
+    // node -> (4 * list position + local index), ascending list position = the reference's scatter order
+    std::vector<int> t((size_t)4 * nt);
+    FK_CUDA(cudaMemcpyAsync(t.data(), h->t4.ptr, sizeof(int) * 4 * (size_t)nt, cudaMemcpyDeviceToHost, s));
+    FK_CUDA(cudaStreamSynchronize(s));
+    std::vector<int> ptr((size_t)nv + 1, 0);
+    for (int ik = 0; ik < n_inside; ik++) {
+      const int k = inside_elements[ik];
+      need(k >= 0 && k < nt, "fk_demag_setup: element id out of range (ids are 0-based, permalloy.jl:70-72)");
+      for (int i = 0; i < 4; i++) ptr[(size_t)t[4 * (size_t)k + i] + 1]++;
+    }
+    for (int n = 0; n < nv; n++) ptr[n + 1] += ptr[n];
+    std::vector<int> lst((size_t)4 * n_inside), fill(ptr.begin(), ptr.end() - 1);
+    for (int ik = 0; ik < n_inside; ik++) {
+      const int k = inside_elements[ik];
+      for (int i = 0; i < 4; i++) lst[fill[t[4 * (size_t)k + i]]++] = 4 * ik + i;
+    }
+    h->dm_inside.upload(inside_elements, (size_t)n_inside, s);
+    h->dm_n2i_ptr.upload(ptr, s);
+    h->dm_n2i.upload(lst, s);
+    h->dm_vol.ensure((size_t)nv);
+    h->dm_w.ensure((size_t)4 * std::max(n_inside, 1));
+    h->dm_M.ensure((size_t)3 * nv);
+    h->dm_Hd.ensure((size_t)3 * nv);
+    h->dm_n_inside = n_inside;
+    demag_node_gather_kernel<0><<<cdiv(std::max(nv, 1), 256), 256, 0, s>>>(h->dm_n2i_ptr.ptr, h->dm_n2i.ptr, nv, h->VE.ptr,
+                                                                          h->dm_inside.ptr, nullptr, 0, h->dm_vol.ptr);
+    FK_CUDA(cudaGetLastError());
+    h->launches++;
+    assemble_stiffness_dev(h, slot, nullptr);   // A = stiffnessMatrix(p, t, VE), LL.cpp:40
+    if (volumes_out) copy_out(h, h->dm_vol.ptr, volumes_out, (size_t)nv);
+    else FK_CUDA(cudaStreamSynchronize(s));     // ptr / lst are read by the pending uploads
+    return 0;
+  });
+}
+
+static void demag_field_dev(fk_handle h, int slot, const double* M_dev, const fk_pcg_opts* opts, int nan_outside,
+                            double* Hd_dev, double* u_dev, int* iters_out, double* relres_out) {
+  need(h->dm_n_inside >= 0, "fk_demag_field: call fk_demag_setup first");
+  ensure_pcg(h);
+  cudaStream_t s = h->stream;
+  const int nv = h->nv, ni = h->dm_n_inside;
+  // load vector, LL.cpp:292-312
+  if (ni) demag_elem_rhs_kernel<<<cdiv(ni, 256), 256, 0, s>>>(h->p4.ptr, h->t4.ptr, h->VE.ptr, h->dm_inside.ptr, ni, M_dev, h->dm_w.ptr);
+  demag_node_gather_kernel<1><<<cdiv(nv, 256), 256, 0, s>>>(h->dm_n2i_ptr.ptr, h->dm_n2i.ptr, nv, h->dm_w.ptr, nullptr, nullptr, 0,
+                                                            h->bvec.ptr);
+  FK_CUDA(cudaGetLastError());
+  h->launches += ni ? 2 : 1;
+  // u = CG.solve(RHS), LL.cpp:315 (warm_start: from the potential of the previous call, kept in the handle)
+  pcg_dev(h, slot, h->bvec.ptr, h->u.ptr, opts, iters_out, relres_out);
+  // element field + box method, LL.cpp:317-346
+  if (ni) demag_elem_field_kernel<<<cdiv(ni, 256), 256, 0, s>>>(h->p4.ptr, h->t4.ptr, h->VE.ptr, h->dm_inside.ptr, ni, h->u.ptr, h->dm_w.ptr);
+  demag_node_gather_kernel<2><<<cdiv(nv, 256), 256, 0, s>>>(h->dm_n2i_ptr.ptr, h->dm_n2i.ptr, nv, h->dm_w.ptr, nullptr, h->dm_vol.ptr,
+                                                            nan_outside, Hd_dev);
+  FK_CUDA(cudaGetLastError());
+  h->launches += ni ? 2 : 1;
+  if (u_dev) FK_CUDA(cudaMemcpyAsync(u_dev, h->u.ptr, sizeof(double) * (size_t)nv, cudaMemcpyDeviceToDevice, s));
+}
+int fk_demag_field_dev(fk_handle h, int slot, const double* M_dev, const fk_pcg_opts* opts, int nan_outside, double* Hd_dev,
+                       double* u_dev, int* iters_out, double* relres_out) {
+  return guard([&]() {
+    need(h && M_dev && Hd_dev, "fk: NULL argument");
+    DeviceGuard dg(h->device);
+    demag_field_dev(h, slot, M_dev, opts, nan_outside, Hd_dev, u_dev, iters_out, relres_out);
+    return 0;
+  });
+}
+int fk_demag_field(fk_handle h, int slot, const double* M, const fk_pcg_opts* opts, int nan_outside, double* Hd_out,
+                   double* u_out, int* iters_out, double* relres_out) {
+  return guard([&]() {
+    need(h && M && Hd_out, "fk: NULL argument");
+    need(h->dm_n_inside >= 0, "fk_demag_field: call fk_demag_setup first");
+    DeviceGuard dg(h->device);
+    const size_t nv = (size_t)h->nv;
+    FK_CUDA(cudaMemcpyAsync(h->dm_M.ptr, M, sizeof(double) * 3 * nv, cudaMemcpyHostToDevice, h->stream));
+    demag_field_dev(h, slot, h->dm_M.ptr, opts, nan_outside, h->dm_Hd.ptr, nullptr, iters_out, relres_out);
+    if (u_out) FK_CUDA(cudaMemcpyAsync(u_out, h->u.ptr, sizeof(double) * nv, cudaMemcpyDeviceToHost, h->stream));
+    copy_out(h, h->dm_Hd.ptr, Hd_out, 3 * nv);
+    return 0;
+  });
+}
+
 // ---- legacy drop-in -----------------------------------------------------------------------------
 // ABI-identical to the reference's scalarPotential (magnetostatics.cpp:49-95): BoundaryIntegral,
 // stiffnessMatrix(p,t,VE,mu), Jacobi-PCG with Eigen's defaults on -RHS, result copied into u_in.

@@ -81,6 +81,10 @@ struct fk_handle_s {
   // nonlinear state
   fk::DevBuf<double> mu, dmu, Hn, Hfield, tile_max, scal;
   fk::DevBuf<unsigned char> matid;
+  // micromagnetics demag field (fk_demag_*): magnetic elements, node -> (list position, local index) lists, node volumes
+  fk::DevBuf<int> dm_inside, dm_n2i_ptr, dm_n2i;
+  fk::DevBuf<double> dm_vol, dm_w, dm_M, dm_Hd;
+  int dm_n_inside = -1;
   fk::DevBuf<int> mat_list;            // ids of the elements with a B-H curve (matid > 0), ascending
   int n_mat = 0;
   fk::DevBuf<int> errflag;

@@ -288,6 +288,7 @@ __device__ __forceinline__ double splev_dev(const SplineDev& S, double x, int& e
 }
 
 #include "assemble.cuh"
+#include "demag.cuh"
 
 // mu(|H|), dmu/dH of the material elements from the B-H spline (NewtonRaphson.jl:178-207; manyBodyIntersecting.jl:189-197),
 // run just before the fused sweep of a Picard step: one thread per listed element recomputes H from the potential,

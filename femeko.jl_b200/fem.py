@@ -262,7 +262,33 @@ class Femeko:
         L.check(self.lib.fk_picard_step(self.h, slot, L.dptr(u), int(compat_bug), C.byref(div)))
         return div.value
 
+    # -- micromagnetics demagnetising field (LL.cpp:287-348) -------------------------------------
+    def demag_setup(self, inside_elements, slot=0):
+        """LL constructor work: box-method node volumes + stiffnessMatrix(p, t, VE) resident in `slot`."""
+        ids = np.ascontiguousarray(inside_elements, dtype=np.int32)
+        vol = np.zeros(self.nv)
+        L.check(self.lib.fk_demag_setup(self.h, slot, L.iptr(ids), int(ids.size), L.dptr(vol)))
+        self._demag_slot = slot
+        return vol
 
+    def demag_field(self, M, nan_outside=True, want_u=False, **kw):
+        """One LL::magnetostaticField(): returns (Hd 3 x nv, iterations[, u])."""
+        M = np.asfortranarray(M, dtype=np.float64)
+        assert M.shape == (3, self.nv)
+        Hd = np.zeros((3, self.nv), order="F")
+        u = np.zeros(self.nv) if want_u else None
+        o = self.pcg_opts(**kw)
+        it, rr = C.c_int(), C.c_double()
+        L.check(self.lib.fk_demag_field(self.h, self._demag_slot, L.dptr(M), C.byref(o), int(nan_outside), L.dptr(Hd), L.dptr(u),
+                                        C.byref(it), C.byref(rr)))
+        return (Hd, it.value, u) if want_u else (Hd, it.value)
+
+    def demag_field_dev(self, M_ptr: int, Hd_ptr: int, u_ptr: int | None = None, nan_outside=True, **kw):
+        o = self.pcg_opts(**kw)
+        it, rr = C.c_int(), C.c_double()
+        L.check(self.lib.fk_demag_field_dev(self.h, self._demag_slot, C.c_void_p(M_ptr), C.byref(o), int(nan_outside),
+                                            C.c_void_p(Hd_ptr), C.c_void_p(u_ptr), C.byref(it), C.byref(rr)))
+        return it.value, rr.value
 
     # -- device-pointer forms (zero-copy: torch tensors' data_ptr(), or fk_device_ptr arrays) ----
     def assemble_stiffness_dev(self, f_ptr: int | None, slot=0):

@@ -178,6 +178,25 @@ int fk_reset_field(fk_handle h);
 int fk_picard_step(fk_handle h, int slot, const double* u, int compat_bug, double* div_out);
 int fk_picard_step_dev(fk_handle h, int slot, const double* u_dev, int compat_bug, double* div_out);
 
+/* ---- micromagnetics demagnetising field: the repeated solve of the LL time loop ---------------
+ * Replaces LL::LL (constructor work) + LL::magnetostaticField of Femeko_jl_C++/Micromagnetics/LL.cpp
+ * (:4-66, :287-348; Julia twin Micromagnetics/LL.jl:162-211), reached in the reference through
+ * LandauLifshitz(...) (micromagnetics.cpp:6-29, permalloy.jl:75-86).
+ * fk_demag_setup: inside_elements = mesh.InsideElements (0-based, permalloy.jl:70-72); computes the
+ *   box-method node volumes (LL.cpp:29-36; volumes_out nv, may be NULL) and assembles
+ *   stiffnessMatrix(p, t, VE) (LL.cpp:40) into `slot`, which stays resident for every later call.
+ * fk_demag_field: one magnetostaticField(): RHS[nd] += VE_k (grad lambda_i . <M>_k) over the magnetic
+ *   elements (:292-312), u = Jacobi-PCG(A, RHS) (:315; opts->warm_start = 1 starts from the previous
+ *   call's potential), H_k = -sum u grad lambda (:317-326), box method to the nodes (:328-346).
+ *   M, Hd are 3 x nv column-major.  Nodes outside the magnetic region have zero node volume: the
+ *   reference divides 0/0 there (NaN); nan_outside != 0 reproduces that, 0 writes 0.
+ *   u_out (nv) may be NULL.  Single-GPU handles only.                                            */
+int fk_demag_setup(fk_handle h, int slot, const int* inside_elements, int n_inside, double* volumes_out);
+int fk_demag_field(fk_handle h, int slot, const double* M, const fk_pcg_opts* opts, int nan_outside,
+                   double* Hd_out, double* u_out, int* iters_out, double* relres_out);
+int fk_demag_field_dev(fk_handle h, int slot, const double* M_dev, const fk_pcg_opts* opts, int nan_outside,
+                       double* Hd_dev, double* u_dev, int* iters_out, double* relres_out);
+
 /* ---- multi-GPU (one process per GPU; NCCL over NVLink) --------------------------------------
  * The handle is built on this rank's partition (owned rows first, then halo rows; ghost elements
  * duplicated so assembly needs no communication).  fk_comm_* wire the halo exchange of the SpMV and

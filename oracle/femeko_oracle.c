@@ -395,3 +395,57 @@ done:
   free(r); free(p); free(z); free(tmp); free(dinv);
   return (it >= max_iter) ? 1 : 0;
 }
+
+/* ---------------------------------------------------------------- micromagnetics demag ------ */
+/* Femeko_jl_C++/Micromagnetics/LL.cpp.  Box-method node volumes, constructor :29-36:
+   volumes[t(i,k)] += VE[k] over the magnetic elements, in list order. */
+void orc_node_volumes(const int* t, const double* VE, const int* inside, int n_inside, int nv, double* vol) {
+  for (int n = 0; n < nv; n++) vol[n] = 0.0;
+  for (int ik = 0; ik < n_inside; ik++) {
+    int k = inside[ik];
+    for (int i = 0; i < 4; i++) vol[t[4 * k + i]] += VE[k];
+  }
+}
+
+/* Load vector of magnetostaticField, LL.cpp:292-312: m_avg += M(:,nd)/4 over the element's nodes, then
+   RHS(nd) += VE[k]*( b*mx + c*my + d*mz ) with (b,c,d) from abcd (linearBasis :139-160). M is 3 x nv. */
+void orc_demag_rhs(const double* p, const int* t, const double* VE, const int* inside, int n_inside, int nv,
+                   const double* M, double* rhs) {
+  for (int n = 0; n < nv; n++) rhs[n] = 0.0;
+  for (int ik = 0; ik < n_inside; ik++) {
+    int k = inside[ik];
+    double m[3] = {0.0, 0.0, 0.0};
+    for (int i = 0; i < 4; i++) {
+      int nd = t[4 * k + i];
+      m[0] += M[3 * nd] / 4.0; m[1] += M[3 * nd + 1] / 4.0; m[2] += M[3 * nd + 2] / 4.0;
+    }
+    for (int i = 0; i < 4; i++) {
+      int nd = t[4 * k + i];
+      double r[4];
+      orc_abcd(p, t + 4 * k, nd, r);
+      rhs[nd] += VE[k] * (r[1] * m[0] + r[2] * m[1] + r[3] * m[2]);
+    }
+  }
+}
+
+/* Field on the nodes, LL.cpp:317-346: Hdk = -sum_i (b,c,d)_i u(t_i) per element, Hd(nd) += VE[k]*Hdk over the
+   magnetic elements, Hd(nd) /= volumes(nd) for EVERY node (0/0 = NaN outside the magnetic region). Hd is 3 x nv. */
+void orc_demag_box(const double* p, const int* t, const double* VE, const int* inside, int n_inside, int nv,
+                   const double* u, const double* vol, double* Hd) {
+  for (int n = 0; n < 3 * nv; n++) Hd[n] = 0.0;
+  for (int ik = 0; ik < n_inside; ik++) {
+    int k = inside[ik];
+    double h[3] = {0.0, 0.0, 0.0};
+    for (int i = 0; i < 4; i++) {
+      int nd = t[4 * k + i];
+      double r[4];
+      orc_abcd(p, t + 4 * k, nd, r);
+      h[0] -= r[1] * u[nd]; h[1] -= r[2] * u[nd]; h[2] -= r[3] * u[nd];
+    }
+    for (int i = 0; i < 4; i++) {
+      int nd = t[4 * k + i];
+      Hd[3 * nd] += VE[k] * h[0]; Hd[3 * nd + 1] += VE[k] * h[1]; Hd[3 * nd + 2] += VE[k] * h[2];
+    }
+  }
+  for (int n = 0; n < nv; n++) { Hd[3 * n] /= vol[n]; Hd[3 * n + 1] /= vol[n]; Hd[3 * n + 2] /= vol[n]; }
+}

@@ -322,3 +322,63 @@ def ref_scalar_potential(mesh, mu, Hext, shell_id):
         _d(_flat(mesh.normal, np.float64)), C.c_int(mesh.nv), C.c_int(mesh.nt), C.c_int(mesh.ns), _d(_f64(mesh.VE)),
         _d(_f64(mu)), _d(_f64(Hext)), C.c_int(int(shell_id)))
     return u
+
+
+# ----------------------------------------------------------------------------- micromagnetics demag field
+def node_volumes(mesh, inside):
+    """Box-method node volumes, LL.cpp:29-36."""
+    vol = np.zeros(mesh.nv)
+    ins = _i32(inside)
+    lib().orc_node_volumes(_i(_flat(mesh.t, np.int32)), _d(_f64(mesh.VE)), _i(ins), C.c_int(len(ins)), C.c_int(mesh.nv), _d(vol))
+    return vol
+
+
+def demag_rhs(mesh, inside, M):
+    """Load vector of LL::magnetostaticField, LL.cpp:292-312.  M is 3 x nv."""
+    rhs = np.zeros(mesh.nv)
+    ins = _i32(inside)
+    lib().orc_demag_rhs(_d(_flat(mesh.p, np.float64)), _i(_flat(mesh.t, np.int32)), _d(_f64(mesh.VE)), _i(ins), C.c_int(len(ins)),
+                        C.c_int(mesh.nv), _d(_flat(M, np.float64)), _d(rhs))
+    return rhs
+
+
+def demag_box(mesh, inside, u, vol):
+    """Element field -> nodes by the box method, LL.cpp:317-346 (NaN where vol == 0, like the reference)."""
+    Hd = np.zeros(3 * mesh.nv)
+    ins = _i32(inside)
+    with np.errstate(all="ignore"):
+        lib().orc_demag_box(_d(_flat(mesh.p, np.float64)), _i(_flat(mesh.t, np.int32)), _d(_f64(mesh.VE)), _i(ins), C.c_int(len(ins)),
+                            C.c_int(mesh.nv), _d(_f64(u)), _d(_f64(vol)), _d(Hd))
+    return np.asfortranarray(Hd.reshape(mesh.nv, 3).T)
+
+
+def demag_field(mesh, inside, M, tol=2.220446049250313e-16):
+    """LL::magnetostaticField restated end to end: RHS, Jacobi-PCG (Eigen defaults) on stiffnessMatrix(p,t,VE), box method."""
+    rowptr, colind, vals = stiffness(mesh, None, order="eigen")
+    rhs = demag_rhs(mesh, inside, M)
+    u, it, _, _ = pcg(rowptr, colind, vals, rhs, tol)
+    vol = node_volumes(mesh, inside)
+    return demag_box(mesh, inside, u, vol), u, it, rhs, vol
+
+
+_ref_ll = None
+
+
+def have_ref_ll() -> bool:
+    return os.path.exists(os.path.join(_HERE, "_ref", "libfemeko_ref_ll.so"))
+
+
+def ref_demag_field(mesh, inside, inside_nodes, M):
+    """The UNMODIFIED reference class LL (ref_ll_shim.cpp): returns (Hd 3 x nv, volumes)."""
+    global _ref_ll
+    if _ref_ll is None:
+        _ref_ll = C.CDLL(os.path.join(_HERE, "_ref", "libfemeko_ref_ll.so"))
+    Hd = np.zeros(3 * mesh.nv)
+    vol = np.zeros(mesh.nv)
+    pf, tf = _flat(mesh.p, np.float64), _flat(mesh.t, np.int32)
+    ins, insn = _i32(inside), _i32(inside_nodes)
+    Mf = _flat(M, np.float64).copy()
+    VE = _f64(mesh.VE).copy()
+    _ref_ll.ref_demag_field(_d(pf), _i(tf), _d(VE), _i(ins), _i(insn), C.c_int(mesh.nv), C.c_int(mesh.nt), C.c_int(len(ins)),
+                            C.c_int(len(insn)), _d(Mf), _d(Hd), _d(vol))
+    return np.asfortranarray(Hd.reshape(mesh.nv, 3).T), vol

@@ -259,3 +259,64 @@ def _neighbours(m):
     mark = np.zeros(m.nv, bool)
     mark[m.InsideNodes] = True
     return np.flatnonzero(mark[m.t].any(axis=0)).astype(np.int32)
+
+
+@pytest.mark.parametrize("name", ["kuhn6", "delaunay300"])
+def test_demag_field_against_reference_golden(name):
+    """fk_demag_setup / fk_demag_field vs the compiled reference class LL (golden) and the oracle."""
+    import os
+    from conftest import GOLDEN
+    m, g = load_golden(name)
+    d = dict(np.load(os.path.join(GOLDEN, "demag_" + name + ".npz")))
+    ins = np.asarray(g["InsideElements"], dtype=np.int32)
+    h = fk.Femeko(m)
+    vol = h.demag_setup(ins, slot=0)
+    assert np.array_equal(vol, d["volumes"])                                          # gathered in list order: bit-exact
+    Hd, it, u = h.demag_field(d["M"], want_u=True)                                    # Eigen defaults, like CG.solve(RHS)
+    fin = np.isfinite(d["Hd"])
+    assert np.array_equal(fin, np.isfinite(Hd))
+    assert rel_l2(Hd[fin], d["Hd"][fin]) < 1e-8
+    Ho, uo, ito, rhs, _ = orc.demag_field(m, ins, d["M"])
+    assert abs(it - ito) <= 1 and rel_l2(u - u.mean(), uo - uo.mean()) < 1e-8
+    Hz, _ = h.demag_field(d["M"], nan_outside=False)
+    assert np.all(Hz[~fin] == 0.0) and np.array_equal(Hz[fin], Hd[fin])
+    # warm start from the converged potential: nothing left to do
+    _, it2 = h.demag_field(d["M"], warm_start=True, tol=1e-10)
+    assert it2 <= 1
+    h.close()
+
+
+def test_demag_field_oracle_and_properties_at_size():
+    """Load vector + box method bit-for-bit against the oracle on a seeded mesh (same summation order), linearity in M,
+    and the repeated-solve loop through device pointers."""
+    import torch
+    m = fk.kuhn_cube(24, inside_edge=0.5)
+    ins = m.InsideElements.astype(np.int32)
+    insn = np.unique(m.t[:, ins])
+    rng = np.random.default_rng(9)
+    M = np.zeros((3, m.nv), order="F")
+    M[:, insn] = rng.normal(size=(3, len(insn)))
+    h = fk.Femeko(m)
+    vol = h.demag_setup(ins)
+    assert np.array_equal(vol, orc.node_volumes(m, ins))
+    Hd, it, u = h.demag_field(M, want_u=True, tol=1e-12)
+    rhs = orc.demag_rhs(m, ins, M)
+    rp, ci = h.pattern()
+    A = h.matrix_get(0)
+    import scipy.sparse as sp
+    r = rhs - sp.csr_matrix((A, ci, rp), shape=(m.nv, m.nv)) @ u
+    assert np.linalg.norm(r) <= 2e-12 * np.linalg.norm(rhs)                            # u solves A u = RHS(oracle)
+    Hb = orc.demag_box(m, ins, u, vol)
+    fin = np.isfinite(Hb)
+    assert np.array_equal(fin, np.isfinite(Hd)) and rel_l2(Hd[fin], Hb[fin]) < 1e-13  # box method on the same u
+    H2, _ = h.demag_field(2.5 * M, tol=1e-12)
+    assert rel_l2(H2[fin], 2.5 * Hd[fin]) < 1e-9                                       # linear in M
+    # device-pointer form, repeated solves with warm start (the LL time loop's call pattern)
+    Md = torch.from_numpy(np.ascontiguousarray(M.T)).cuda()                            # 3 x nv column-major == nv x 3 row-major
+    Hdd = torch.empty_like(Md)
+    it0, _ = h.demag_field_dev(Md.data_ptr(), Hdd.data_ptr(), tol=1e-12)
+    it1, _ = h.demag_field_dev(Md.data_ptr(), Hdd.data_ptr(), tol=1e-12, warm_start=True)
+    torch.cuda.synchronize()
+    assert it0 == it and it1 <= 1
+    assert np.array_equal(np.isfinite(Hdd.cpu().numpy().T), fin) and rel_l2(Hdd.cpu().numpy().T[fin], Hd[fin]) < 1e-9
+    h.close()

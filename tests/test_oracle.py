@@ -120,3 +120,18 @@ def test_material_permeability_rules():
     assert np.isclose(dmu[2], (mu[3] - mu[1]) / (H[3] - H[1])) and np.isclose(dmu[0], (mu[1] - mu[0]) / 10.0)
     assert nu[0] == 0.0 and np.allclose(nu[1:], fk.mu0 * H[1:] / B[1:])
     assert np.allclose(orc.gradient(H, B)[1:-1], (B[2:] - B[:-2]) / (H[2:] - H[:-2]))
+
+
+@pytest.mark.parametrize("name", ["kuhn6", "delaunay300"])
+def test_oracle_demag_field_matches_golden_reference(name):
+    """SURVEY 8f-1: oracle restatement of LL::magnetostaticField vs the compiled reference class (golden)."""
+    m, g = load_golden(name)
+    d = dict(np.load(__import__("os").path.join(__import__("conftest").GOLDEN, "demag_" + name + ".npz")))
+    ins = np.asarray(g["InsideElements"], dtype=np.int32)
+    Hd, u, it, rhs, vol = orc.demag_field(m, ins, d["M"])
+    assert np.array_equal(vol, d["volumes"])                      # same loop order: bit-exact
+    fin = np.isfinite(d["Hd"])
+    assert np.array_equal(fin, np.isfinite(Hd))                   # NaN exactly where the node volume is 0
+    assert np.array_equal(np.flatnonzero(fin[0]), d["InsideNodes"])
+    assert rel_l2(Hd[fin], d["Hd"][fin]) < 1e-10
+    assert abs(rhs.sum()) < 1e-12 * np.abs(rhs).sum()              # sum_i grad(lambda_i) = 0: the load vector has zero mean
