@@ -152,21 +152,26 @@ static void ensure_state(fk_handle h) {
 void launch_spmv(fk_handle h, cudaStream_t s, const double* vals, const double* x, double* y, bool dot, const PcgCtl* ctl,
                  int j) {
   if (h->sym.nslices <= 0) return;
-  if (dot) {  // partitioned: p.Ap is finished (and all-reduced over peer memory) inside the kernel -> scal[0]
-    const RedArgs ra = h->comm ? comm_red_args(h, h->tickets.ptr, h->scal.ptr, 0) : RedArgs{};
-    spmv_sell_kernel<true><<<h->grid_spmv, kSpmvThreads, 0, s>>>(h->slice_ptr.ptr, h->srow.ptr, h->sell_col.ptr, vals, x, y,
-                                                                 h->sym.nslices, h->part.ptr, ra, ctl, j);
-  } else {
-    spmv_sell_kernel<false><<<h->grid_spmv, kSpmvThreads, 0, s>>>(h->slice_ptr.ptr, h->srow.ptr, h->sell_col.ptr, vals, x, y,
-                                                                  h->sym.nslices, nullptr, RedArgs{}, ctl, j);
-  }
+  const int4* meta = reinterpret_cast<const int4*>(h->slice_meta.ptr);
+  // partitioned: p.Ap is finished (and all-reduced over peer memory) inside the kernel -> scal[0]
+  const RedArgs ra = (dot && h->comm) ? comm_red_args(h, h->tickets.ptr, h->scal.ptr, 0) : RedArgs{};
+  spmv_variant_dispatch(h->spmv_variant, [&](auto G, auto MINB) {
+    if (dot)
+      spmv_sell_kernel<true, G(), MINB()><<<h->grid_spmv, kSpmvThreads, 0, s>>>(meta, h->srow.ptr, h->sell_colz.ptr, vals, x, y,
+                                                                              h->sym.nslices, h->part.ptr, ra, ctl, j);
+    else
+      spmv_sell_kernel<false, G(), MINB()><<<h->grid_spmv, kSpmvThreads, 0, s>>>(meta, h->srow.ptr, h->sell_colz.ptr, vals, x, y,
+                                                                               h->sym.nslices, nullptr, RedArgs{}, ctl, j);
+  });
   FK_CUDA(cudaGetLastError());
 }
 
 // launch geometry of the persistent SpMV: full residency, fixed per handle (deterministic p.Ap)
 static void configure_spmv(fk_handle h, int ctas_per_sm) {
   int occ = 1;
-  FK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, spmv_sell_kernel<true>, kSpmvThreads, 0));
+  spmv_variant_dispatch(h->spmv_variant, [&](auto G, auto MINB) {
+    FK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, spmv_sell_kernel<true, G(), MINB()>, kSpmvThreads, 0));
+  });
   occ = std::max(1, occ);
   if (ctas_per_sm > 0) occ = std::min(occ, ctas_per_sm);
   const int groups = (h->sym.nslices + (kSpmvThreads / 32) - 1) / (kSpmvThreads / 32);
@@ -422,6 +427,7 @@ static SymbolicOpts to_symbolic_opts(const fk_create_opts& o) {
   so.natural_order = o.natural_order != 0;
   if (o.sell_sigma > 0) so.sell_sigma = o.sell_sigma;
   if (o.n_owned > 0) so.n_owned = o.n_owned;
+  so.wide_cols = o.sell_wide_cols != 0;
   return so;
 }
 
@@ -485,8 +491,9 @@ int fk_create(const double* p, const int* t, int nv, int nt, const double* VE, c
     h->colind.upload(S.colind, s);
     h->slice_ptr.upload(S.slice_ptr, s);
     h->srow.upload(S.srow, s);
-    h->sell_col.ensure(S.sell_col.size() + kSlack);
-    h->sell_col.upload(S.sell_col, s);
+    h->slice_meta.upload(S.slice_meta, s);
+    h->sell_colz.ensure(S.sell_colz.size() + 2 * kSlack);
+    h->sell_colz.upload(S.sell_colz, s);
     h->csr2sell.upload(S.csr2sell, s);
     h->sell_diag.upload(S.sell_diag, s);
     h->tile_hdr.upload(S.tile_hdr, s);
@@ -509,6 +516,7 @@ int fk_create(const double* p, const int* t, int nv, int nt, const double* VE, c
     }
 
     // launch geometry of the persistent SpMV / vector kernels: full residency, fixed for determinism
+    h->spmv_ctas = o.spmv_ctas_per_sm;
     configure_spmv(h.get(), o.spmv_ctas_per_sm);
     h->grid_vec = std::max(1, std::min(cdiv(std::max(1, h->n_rows), kVecThreads), h->num_sms * 8));
     FK_CUDA(cudaStreamSynchronize(s));
@@ -563,9 +571,14 @@ int fk_tune(fk_handle h, int what, int value) {
         launch_assemble<ASM_LAGRANGE>(h, dummy, true);
         break;
       }
-      case 1: configure_spmv(h, value); break;
+      case 1: h->spmv_ctas = value; configure_spmv(h, value); break;
       case 2: h->l2_persist = value != 0; configure_l2(h); break;
       case 3: h->asm_dbg = value; break;   // profiling experiments: skip assembly phases (results are garbage)
+      case 4:
+        need(value >= 0 && value < kNumSpmvVariants, "fk_tune: spmv variant out of range");
+        h->spmv_variant = value;
+        configure_spmv(h, h->spmv_ctas);
+        break;
       default: throw std::runtime_error("fk_tune: unknown option");
     }
     return 0;
@@ -617,6 +630,16 @@ int fk_elem2nnz(fk_handle h, int* map) {
   });
 }
 
+int fk_sell_stats(fk_handle h, long long* nnz_sell, long long* n_slices, long long* n_slices16, long long* col_bytes) {
+  return guard([&]() {
+    need(h, "fk: NULL argument");
+    if (nnz_sell) *nnz_sell = h->sym.nnz_sell;
+    if (n_slices) *n_slices = h->sym.nslices;
+    if (n_slices16) *n_slices16 = h->sym.n_slices16;
+    if (col_bytes) *col_bytes = 2 * (long long)h->sym.sell_colz.size();
+    return 0;
+  });
+}
 int fk_tile_stats(fk_handle h, long long* staged_elems, int* max_elems, int* max_nnz, int* max_ents) {
   return guard([&]() {
     need(h, "fk: NULL handle");
@@ -707,6 +730,17 @@ int fk_symbolic_export(fk_symbolic s, int* rowptr, int* colind, int* diag, int* 
     copy_vec(S.srow, srow);
     copy_vec(S.sell_col, sell_col);
     copy_vec(S.csr2sell, csr2sell);
+    return 0;
+  });
+}
+int fk_symbolic_colz(fk_symbolic s, long long* n_colz, long long* n_slices16, int* slice_meta, unsigned short* colz) {
+  return guard([&]() {
+    need(s, "fk: NULL argument");
+    const Symbolic& S = s->S;
+    if (n_colz) *n_colz = (long long)S.sell_colz.size();
+    if (n_slices16) *n_slices16 = S.n_slices16;
+    if (slice_meta) copy_vec(S.slice_meta, slice_meta);
+    if (colz) copy_vec(S.sell_colz, colz);
     return 0;
   });
 }

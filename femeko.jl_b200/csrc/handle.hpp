@@ -68,7 +68,8 @@ struct fk_handle_s {
   fk::DevBuf<double> VE;
   // pattern + plans
   fk::DevBuf<int> rowptr, colind;                                  // canonical CSR pattern (exports, diagnostics)
-  fk::DevBuf<int> slice_ptr, srow, sell_col, csr2sell, sell_diag;  // SELL-32-sigma device layout (symbolic.hpp)
+  fk::DevBuf<int> slice_ptr, slice_meta, srow, csr2sell, sell_diag;
+  fk::DevBuf<unsigned short> sell_colz;  // packed column stream  // SELL-32-sigma device layout (symbolic.hpp)
   long long nnz_sell = 0;
   fk::DevBuf<int> tile_hdr;            // int4 per tile
   fk::DevBuf<uint32_t> tile_blob;      // packed per-tile plan blobs (symbolic.hpp)
@@ -103,6 +104,7 @@ struct fk_handle_s {
   fk::DevBuf<fk::PcgCtl> ctl;
   fk::PcgCtl* ctl_host = nullptr;      // pinned
   int grid_spmv = 0, grid_vec = 0;
+  int spmv_variant = 3, spmv_ctas = 0;   // SpMV launch shape (spmv.cuh: spmv_variant_dispatch), cap on CTAs per SM
   cudaGraphExec_t graph[FK_NUM_SLOTS] = {nullptr, nullptr, nullptr, nullptr};
   int graph_chunk[FK_NUM_SLOTS] = {0, 0, 0, 0};
   // generic staging for the host-pointer API

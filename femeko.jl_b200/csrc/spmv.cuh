@@ -1,8 +1,9 @@
 // K2a: SpMV on the SELL-32-sigma layout (included inside namespace fk; layout in symbolic.hpp).
 //
 // One thread owns one row, one warp one slice.  In step k the warp reads 32 consecutive values (256 B)
-// and 32 consecutive columns (128 B) -- the matrix stream, 12 B per entry, is read exactly once and
-// fully coalesced with streaming (evict-first) loads so it does not displace the PCG vectors from L2 --
+// and its columns (16-bit offsets from the slice's smallest column, four steps per 8-byte word, 256 B per warp
+// load; 32-bit columns in a slice whose columns span >= 65536: packed stream, symbolic.hpp) -- the matrix stream, 10 B per entry on a mesh numbered
+// with locality, is read exactly once and fully coalesced with streaming (evict-first) loads so it does not displace the PCG vectors from L2 --
 // and gathers x through the read-only path; on meshes numbered with locality neighbouring rows have
 // neighbouring columns, so the gather of a step touches 2-3 lines instead of 32.  Each row is folded
 // left to right with separately rounded multiply and add: the summation order of Eigen's column-major
@@ -15,41 +16,62 @@
 // both were bound by the per-entry x gather in L1 (32 distinct lines per warp request), not by HBM.
 
 constexpr int kSellC = 32;
-constexpr int kSellUnroll = 5;
 
-template <bool DOT>
-static __global__ void __launch_bounds__(kSpmvThreads) spmv_sell_kernel(const int* __restrict__ slice_ptr, const int* __restrict__ srow,
-                                                                  const int* __restrict__ col, const double* __restrict__ vals,
-                                                                  const double* __restrict__ x, double* __restrict__ y, int nslices,
-                                                                  double* __restrict__ part, const RedArgs red, const PcgCtl* ctl,
-                                                                  int j) {
+// a slice with 32-bit columns (columns span >= 65536: rare; halo columns of a partition, unordered meshes)
+static __device__ __forceinline__ double sell_slice_row32(const double* __restrict__ v, const int* __restrict__ c, int w,
+                                                          const double* __restrict__ x) {
+  double acc = 0.0;
+#pragma unroll 4
+  for (int k = 0; k < w; k++) acc = __dadd_rn(acc, __dmul_rn(__ldcs(v + k * kSellC), __ldg(x + __ldcs(c + k * kSellC))));
+  return acc;
+}
+
+// a slice with 16-bit column offsets: one 8-byte word per lane holds the columns of four consecutive steps, so
+// a batch of 4 G entries issues G column loads + 4 G value loads, then 4 G independent gathers of x, and only
+// then folds them left to right -- the memory-level parallelism comes from the batch, not from occupancy alone.
+template <int G>
+static __device__ __forceinline__ double sell_slice_row16(const double* __restrict__ v, const uint2* __restrict__ c, int cbase, int w,
+                                                          const double* __restrict__ x) {
+  double acc = 0.0;
+  const double* __restrict__ xb = x + cbase;
+  for (int k = 0; k < w; k += 4 * G) {
+    uint2 cw[G];
+    double vv[4 * G], xx[4 * G];
+#pragma unroll
+    for (int g = 0; g < G; g++) cw[g] = (k + 4 * g < w) ? __ldcs(c + ((k >> 2) + g) * kSellC) : make_uint2(0u, 0u);
+#pragma unroll
+    for (int u = 0; u < 4 * G; u++) vv[u] = (k + u < w) ? __ldcs(v + (k + u) * kSellC) : 0.0;
+#pragma unroll
+    for (int u = 0; u < 4 * G; u++) {
+      const unsigned word = (u & 2) ? cw[u >> 2].y : cw[u >> 2].x;
+      const unsigned off = (u & 1) ? (word >> 16) : (word & 0xffffu);
+      xx[u] = (k + u < w) ? __ldg(xb + off) : 0.0;
+    }
+#pragma unroll
+    for (int u = 0; u < 4 * G; u++)
+      if (k + u < w) acc = __dadd_rn(acc, __dmul_rn(vv[u], xx[u]));
+  }
+  return acc;
+}
+
+template <bool DOT, int G, int MINB>
+static __global__ void __launch_bounds__(kSpmvThreads, MINB) spmv_sell_kernel(const int4* __restrict__ slice_meta, const int* __restrict__ srow,
+                                                                  const unsigned short* __restrict__ colz,
+                                                                  const double* __restrict__ vals, const double* __restrict__ x,
+                                                                  double* __restrict__ y, int nslices, double* __restrict__ part,
+                                                                  const RedArgs red, const PcgCtl* ctl, int j) {
   __shared__ double red_s[33];
   if (pcg_inactive(ctl, j)) return;
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   constexpr int WPB = kSpmvThreads / 32;
   double dot = 0.0;
   for (int sl = blockIdx.x * WPB + wib; sl < nslices; sl += gridDim.x * WPB) {
-    const int base = __ldg(slice_ptr + sl), w = (__ldg(slice_ptr + sl + 1) - base) >> 5;
+    const int4 m = __ldg(slice_meta + sl);   // {value base, width, column offset in 64-byte units, column base | -1}
     const int r = __ldg(srow + sl * kSellC + lane);
-    const double* __restrict__ v = vals + base + lane;
-    const int* __restrict__ c = col + base + lane;
-    double acc = 0.0;
-    int k = 0;
-    for (; k + kSellUnroll <= w; k += kSellUnroll) {
-      double vv[kSellUnroll];
-      int cc[kSellUnroll];
-#pragma unroll
-      for (int u = 0; u < kSellUnroll; u++) {
-        cc[u] = __ldcs(c + (k + u) * kSellC);
-        vv[u] = __ldcs(v + (k + u) * kSellC);
-      }
-      double xx[kSellUnroll];
-#pragma unroll
-      for (int u = 0; u < kSellUnroll; u++) xx[u] = __ldg(x + cc[u]);
-#pragma unroll
-      for (int u = 0; u < kSellUnroll; u++) acc = __dadd_rn(acc, __dmul_rn(vv[u], xx[u]));
-    }
-    for (; k < w; k++) acc = __dadd_rn(acc, __dmul_rn(__ldcs(v + k * kSellC), __ldg(x + __ldcs(c + k * kSellC))));
+    const double* __restrict__ v = vals + m.x + lane;
+    const unsigned short* __restrict__ cz = colz + (size_t)m.z * kSellC;
+    const double acc = m.w >= 0 ? sell_slice_row16<G>(v, reinterpret_cast<const uint2*>(cz) + lane, m.w, m.y, x)
+                                : sell_slice_row32(v, reinterpret_cast<const int*>(cz) + lane, m.y, x);
     if (r >= 0) {
       y[r] = acc;
       if (DOT) dot += acc * x[r];
@@ -58,6 +80,20 @@ static __global__ void __launch_bounds__(kSpmvThreads) spmv_sell_kernel(const in
   if (DOT) {
     const double v[1] = {block_sum(dot, red_s)};
     grid_reduce_finish<1>(v, part, gridDim.x, red, red_s);   // -> out[0] = p.Ap over all ranks
+  }
+}
+
+// launch shapes {entries per batch = 4 G, min CTAs per SM}; selected with fk_tune(h, 4, variant)
+constexpr int kNumSpmvVariants = 6;
+template <typename F>
+static void spmv_variant_dispatch(int variant, F&& f) {
+  switch (variant) {
+    case 0: f(std::integral_constant<int, 1>{}, std::integral_constant<int, 8>{}); break;
+    case 1: f(std::integral_constant<int, 1>{}, std::integral_constant<int, 6>{}); break;
+    case 2: f(std::integral_constant<int, 2>{}, std::integral_constant<int, 5>{}); break;
+    case 3: f(std::integral_constant<int, 2>{}, std::integral_constant<int, 4>{}); break;
+    case 4: f(std::integral_constant<int, 4>{}, std::integral_constant<int, 3>{}); break;
+    default: f(std::integral_constant<int, 4>{}, std::integral_constant<int, 2>{}); break;
   }
 }
 

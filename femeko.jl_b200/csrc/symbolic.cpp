@@ -5,6 +5,7 @@
 #include "symbolic.hpp"
 
 #include <algorithm>
+#include <climits>
 #include <cmath>
 #include <cstring>
 #include <numeric>
@@ -341,6 +342,49 @@ void build_symbolic(const double* p, const int* t, int nv, int nt, const Symboli
             S.sell_col[idx] = r >= 0 ? r : 0;  // padding: value stays 0, column is a valid index
           }
         }
+      }
+    }
+    // packed column stream (symbolic.hpp): 16-bit offsets where a slice's columns span < 65536
+    S.slice_meta.assign((size_t)4 * S.nslices, 0);
+    std::vector<int> cmin((size_t)S.nslices, 0);
+    int64_t units = 0, n16 = 0;
+    for (int sl = 0; sl < S.nslices; sl++) {
+      const int base = S.slice_ptr[sl], w = (S.slice_ptr[sl + 1] - base) / C;
+      int lo = INT_MAX, hi = -1;
+      for (int l = 0; l < C; l++) {
+        const int r = S.srow[(size_t)sl * C + l];
+        if (r < 0) continue;
+        lo = std::min(lo, std::min(r, S.colind[S.rowptr[r]]));   // columns ascend in a row; padding uses r itself
+        hi = std::max(hi, std::max(r, S.colind[S.rowptr[r] + std::max(rowlen[r], 1) - 1]));
+      }
+      if (hi < 0) lo = hi = 0;
+      const bool narrow = !o.wide_cols && (int64_t)hi - lo < 65536;
+      if (units > 0x7fffffffLL - 2 * w - 4) throw std::runtime_error("fk: column stream too large for one GPU; partition the mesh");
+      S.slice_meta[4 * (size_t)sl + 0] = base;
+      S.slice_meta[4 * (size_t)sl + 1] = w;
+      S.slice_meta[4 * (size_t)sl + 2] = (int)units;
+      S.slice_meta[4 * (size_t)sl + 3] = narrow ? lo : -1;
+      cmin[sl] = lo;
+      units += narrow ? 4 * ((w + 3) / 4) : 2 * w;
+      n16 += narrow;
+    }
+    S.n_slices16 = n16;
+    S.sell_colz.assign((size_t)units * C, 0);
+#pragma omp parallel for schedule(static)
+    for (int sl = 0; sl < S.nslices; sl++) {
+      const int* m = &S.slice_meta[4 * (size_t)sl];
+      const int* src = &S.sell_col[(size_t)m[0]];
+      uint16_t* dst = &S.sell_colz[(size_t)m[2] * C];
+      const int n = m[1] * C;
+      if (m[3] >= 0) {   // step k of lane l -> 16-bit word ((k / 4) * 32 + l) * 4 + k % 4 (steps k >= w of the last group: 0)
+        for (int e = 0; e < n; e++) {
+          const int k = e / C, l = e % C;
+          int c = src[e];
+          if (c < m[3] || c - m[3] > 65535) c = m[3];   // padding of an unused lane (value 0): any valid column
+          dst[((size_t)(k / 4) * C + l) * 4 + (k % 4)] = (uint16_t)(c - m[3]);
+        }
+      } else {
+        std::memcpy(dst, src, sizeof(int) * (size_t)n);
       }
     }
   }

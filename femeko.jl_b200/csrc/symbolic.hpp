@@ -16,6 +16,7 @@ struct SymbolicOpts {
   bool natural_order = false;
   int sell_sigma = 1024;      // SELL-32-sigma: rows are sorted by length inside windows of sigma rows (1 = input order)
   int n_owned = -1;  // rows [0, n_owned) get a pattern (multi-GPU: owned rows first); -1 = all
+  bool wide_cols = false;  // true: every slice keeps 32-bit columns in the packed column stream (A/B measurements)
 };
 
 // Gather plan of one assembly tile = a set of rows whose every incident element is staged once in
@@ -65,7 +66,19 @@ struct Symbolic {
   int64_t nnz_sell = 0;              // padded entry count = slice_ptr[nslices]
   std::vector<int> slice_ptr;        // nslices + 1
   std::vector<int> srow;             // 32 * nslices
-  std::vector<int> sell_col;         // nnz_sell
+  std::vector<int> sell_col;         // nnz_sell (host copy, 32-bit; the device reads the packed stream below)
+  // Packed column stream of the device SpMV.  A slice whose columns span < 65536 (every slice of a mesh numbered
+  // with locality) stores them as 16-bit offsets from the slice's smallest column: 10 instead of 12 bytes per
+  // entry on the matrix stream that bounds a PCG iteration.  Any other slice keeps 32-bit columns; the choice is
+  // per slice = per warp, so it costs no divergence.  The stream is addressed in 64-byte units.  A 16-bit slice of
+  // width w is stored in groups of four steps: lane l reads the offsets of steps 4 g .. 4 g + 3 of its row as ONE
+  // 8-byte word at 16-bit index ((g * 32 + l) * 4) (a warp reads a group with one coalesced 256-byte load and has
+  // four gathers to issue at once); it takes 4 ceil(w / 4) units, steps >= w of the last group are 0.  A 32-bit slice
+  // keeps the plain SELL order (step k of lane l at 32-bit index 32 k + l) and takes 2 w units.
+  // slice_meta[4 sl ..] = {slice_ptr[sl], w, offset in 64-byte units, column base (-1: 32-bit columns)}.
+  std::vector<int> slice_meta;       // 4 * nslices
+  std::vector<uint16_t> sell_colz;   // 32 * (units of all slices)
+  int64_t n_slices16 = 0;            // slices stored with 16-bit columns
   std::vector<int> csr2sell;         // nnz: CSR index -> SELL index
   std::vector<int> sell_diag;        // n_rows: SELL index of (r,r), -1 if absent
 };

@@ -114,6 +114,12 @@ class Femeko:
         return {"tiles": self.ntiles, "staged_elems": st.value, "recompute_factor": st.value / max(1, self.nt),
                 "max_elems": a.value, "max_nnz": b.value, "max_ents": c.value}
 
+    def sell_stats(self):
+        """(padded entries, slices, slices with 16-bit columns, bytes of the packed column stream)"""
+        v = [C.c_longlong() for _ in range(4)]
+        L.check(self.lib.fk_sell_stats(self.h, *[C.byref(x) for x in v]))
+        return tuple(x.value for x in v)
+
     def device_ptr(self, which: int) -> int:
         p = C.c_void_p()
         L.check(self.lib.fk_device_ptr(self.h, which, C.byref(p)))

@@ -32,7 +32,7 @@ class FemekoError(RuntimeError):
 class fk_create_opts(C.Structure):
     _fields_ = [("tile_max_elems", C.c_int), ("tile_max_rows", C.c_int), ("natural_order", C.c_int),
                 ("sell_sigma", C.c_int), ("device", C.c_int), ("n_owned", C.c_int), ("asm_cfg", C.c_int),
-                ("spmv_ctas_per_sm", C.c_int)]
+                ("spmv_ctas_per_sm", C.c_int), ("sell_wide_cols", C.c_int)]
 
 
 class fk_pcg_opts(C.Structure):
@@ -67,11 +67,13 @@ _SIGS = {
     "fk_elem2nnz": (C.c_int, [_H, c_int_p]),
     "fk_volumes": (C.c_int, [_H, c_double_p]),
     "fk_tile_stats": (C.c_int, [_H, C.POINTER(C.c_longlong), c_int_p, c_int_p, c_int_p]),
+    "fk_sell_stats": (C.c_int, [_H] + [C.POINTER(C.c_longlong)] * 4),
     "fk_device_ptr": (C.c_int, [_H, C.c_int, C.POINTER(C.c_void_p)]),
     "fk_symbolic_create": (C.c_int, [c_double_p, c_int_p, C.c_int, C.c_int, C.POINTER(fk_create_opts), C.POINTER(_H)]),
     "fk_symbolic_sizes": (C.c_int, [_H, C.POINTER(C.c_longlong), c_int_p, C.POINTER(C.c_longlong), C.POINTER(C.c_longlong),
                                     C.POINTER(C.c_longlong), c_int_p, C.POINTER(C.c_longlong)]),
     "fk_symbolic_export": (C.c_int, [_H] + [C.c_void_p] * 15),
+    "fk_symbolic_colz": (C.c_int, [_H, C.POINTER(C.c_longlong), C.POINTER(C.c_longlong), C.c_void_p, C.c_void_p]),
     "fk_symbolic_destroy": (C.c_int, [_H]),
     "fk_assemble_stiffness": (C.c_int, [_H, C.c_int, c_double_p, c_double_p]),
     "fk_assemble_mass": (C.c_int, [_H, C.c_int, c_double_p, c_double_p]),

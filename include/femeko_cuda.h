@@ -42,6 +42,8 @@ typedef struct fk_create_opts {
                          rows [n_owned, nv) are halo copies; 0 = all rows owned                 */
   int asm_cfg;        /* assembly launch shape {threads, min CTAs/SM}: 0 = default ({256,2}); 1 {256,3} 2 {256,2} 3 {384,2} 4 {512,2} 5 {128,6} 6 {512,1} 7 {768,1} */
   int spmv_ctas_per_sm; /* cap on resident SpMV CTAs per SM (0 = as many as fit)               */
+  int sell_wide_cols; /* 1: keep 32-bit columns in every SELL slice (default 0: slices whose columns span
+                         < 65536 store 16-bit offsets, ~10 instead of 12 bytes per matrix entry)  */
 } fk_create_opts;
 
 /* PCG options.  Defaults (all 0) reproduce Eigen::ConjugateGradient's: tol = DBL_EPSILON relative
@@ -73,7 +75,9 @@ int fk_synchronize(fk_handle h);
 /* change a launch option after creation (tuning sweeps): what 0 = asm_cfg, 1 = spmv_ctas_per_sm (values
  * as in fk_create_opts), 2 = pin the PCG vectors in L2 with a persisting access-policy window (1 = on,
  * the default; 0 = off).  Matrix values do not depend on these.  3 = profiling experiments only: bit 0 / 1
- * skip phase 1 / 2 of the assembly kernel (matrix values are then garbage).                            */
+ * skip phase 1 / 2 of the assembly kernel (matrix values are then garbage).  4 = SpMV launch shape
+ * {entries per batch, min CTAs per SM}: 0 {4,8} 1 {4,6} 2 {8,5} 3 {8,4} (default) 4 {16,3} 5 {16,2}; results do
+ * not depend on it.                            */
 int fk_tune(fk_handle h, int what, int value);
 /* number of kernels of this library launched through the handle so far (graph nodes included) */
 int fk_launch_count(fk_handle h, long long* n);
@@ -87,6 +91,9 @@ int fk_elem2nnz(fk_handle h, int* map /* 16 nt */);
 int fk_volumes(fk_handle h, double* VE /* nt */);
 /* assembly-plan statistics: elements staged over all tiles (>= nt; the excess is halo recompute) */
 int fk_tile_stats(fk_handle h, long long* staged_elems, int* max_elems, int* max_nnz, int* max_ents);
+/* device matrix layout (SELL-32-sigma): padded entries, slices, slices stored with 16-bit column offsets, and the
+ * bytes of the packed column stream one SpMV reads                                                          */
+int fk_sell_stats(fk_handle h, long long* nnz_sell, long long* n_slices, long long* n_slices16, long long* col_bytes);
 /* device pointers of handle-owned arrays, for zero-copy interop (torch.from_blob-style):
  * which: 0 rowptr(int) 1 colind(int) 2 VE(double) 3 mu(double) 4 Hnorm(double) 5 Hfield(double 3 x nt)
  *        6 u(double nv) 7 dmu(double) 8 csr2sell(int nnz) 16+s values of slot s.  Matrix values live on
@@ -108,6 +115,13 @@ int fk_symbolic_export(fk_symbolic s, int* rowptr, int* colind, int* diag, int* 
                        unsigned int* tile_elems, long long* tile_nnz_ptr, int* tile_gidx, unsigned short* tile_coff,
                        long long* tile_ent_ptr, unsigned short* tile_ents, int* slice_ptr, int* srow, int* sell_col,
                        int* csr2sell);
+/* packed column stream read by the device SpMV (two calls: sizes with NULL arrays, then the arrays):
+ * slice_meta[4 sl ..] = {value base, width, offset in 64-byte units, column base (-1: 32-bit columns)},
+ * colz = 16-bit words; a slice with column base >= 0 stores offsets from it in groups of four steps
+ * (step k of lane l at ((k / 4) * 32 + l) * 4 + k % 4, 4 ceil(width / 4) units), any other slice 32 x width
+ * 32-bit columns (2 width units).  n_slices16 = slices stored with 16-bit columns.                          */
+int fk_symbolic_colz(fk_symbolic s, long long* n_colz, long long* n_slices16, int* slice_meta /* 4 x nslices */,
+                     unsigned short* colz /* n_colz */);
 int fk_symbolic_destroy(fk_symbolic s);
 
 /* ---- assembly: stiffnessMatrix / massMatrix / tangentialStiffnessMatrix ----------------------

@@ -35,6 +35,12 @@ def export_symbolic(mesh, **opts):
     order = ["rowptr", "colind", "diag", "e2nnz", "tile_elem_ptr", "tile_elems", "tile_nnz_ptr", "tile_gidx", "tile_coff",
              "tile_ent_ptr", "tile_ents", "slice_ptr", "srow", "sell_col", "csr2sell"]
     L.check(lib.fk_symbolic_export(s, *[C.c_void_p(out[k].ctypes.data) for k in order]))
+    ncz, n16 = C.c_longlong(), C.c_longlong()
+    L.check(lib.fk_symbolic_colz(s, C.byref(ncz), C.byref(n16), None, None))
+    out["slice_meta"] = np.zeros(4 * nsl.value, np.int32)
+    out["colz"] = np.zeros(ncz.value, np.uint16)
+    L.check(lib.fk_symbolic_colz(s, None, None, C.c_void_p(out["slice_meta"].ctypes.data), C.c_void_p(out["colz"].ctypes.data)))
+    out["n_slices16"] = n16.value
     lib.fk_symbolic_destroy(s)
     out["ntiles"] = T
     out["nnz"] = nnz.value
@@ -71,17 +77,32 @@ def run_plan(plan, Ak):
 
 def sell_spmv(plan, vals_csr, x):
     """Execute the SELL-32-sigma layout in numpy the way spmv_sell_kernel walks it (one lane per row, left to
-    right, separately rounded multiply and add): returns y over the assembled rows."""
+    right, separately rounded multiply and add; columns from the packed stream: 16-bit offsets from the slice's
+    column base, or 32-bit columns where the base is -1): returns y over the assembled rows."""
     vs = np.zeros(plan["nnz_sell"])
     vs[plan["csr2sell"]] = vals_csr
     y = np.zeros(len(plan["diag"]))
-    sp, srow, col = plan["slice_ptr"], plan["srow"], plan["sell_col"]
+    srow, meta, colz = plan["srow"], plan["slice_meta"].reshape(-1, 4), plan["colz"]
+    assert np.array_equal(meta[:, 0], plan["slice_ptr"][:-1])
+    live_all = np.zeros(plan["nnz_sell"], bool)
+    live_all[plan["csr2sell"]] = True
     for s in range(plan["nslices"]):
-        base, w = sp[s], (sp[s + 1] - sp[s]) // 32
+        base, w, off, cbase = (int(v) for v in meta[s])
+        assert w == (plan["slice_ptr"][s + 1] - base) // 32
+        if cbase >= 0:   # groups of four steps per lane: word ((k // 4) * 32 + l) * 4 + k % 4
+            g4 = (w + 3) // 4
+            z = colz[32 * off: 32 * (off + 4 * g4)].astype(np.int64).reshape(g4, 32, 4)
+            col = cbase + z.transpose(0, 2, 1).reshape(4 * g4, 32)[:w].reshape(-1)
+        else:
+            col = colz[32 * off: 32 * (off + 2 * w)].view(np.int32).astype(np.int64)
+        r = srow[32 * s: 32 * s + 32]
+        # the packed columns are the plain SELL columns wherever a value can be non-zero
+        ref = plan["sell_col"][base: base + 32 * w]
+        live = live_all[base: base + 32 * w]
+        assert np.array_equal(col[live], ref[live])
         acc = np.zeros(32)
         for k in range(w):
-            i = base + 32 * k + np.arange(32)
-            acc = acc + vs[i] * x[col[i]]
-        r = srow[32 * s: 32 * s + 32]
+            i = 32 * k + np.arange(32)
+            acc = acc + vs[base + i] * x[col[i]]
         y[r[r >= 0]] = acc[r >= 0]
     return y

@@ -251,7 +251,19 @@ def test_full_size_properties():
     inside_nodes[np.unique(m.t[:, np.concatenate([m.InsideElements, _neighbours(m)])])] = True
     far = interior & ~inside_nodes
     assert np.max(np.abs(Au[far])) < 1e-9 * diag.max() * np.abs(u).max()        # linear fields are discretely harmonic
+    # packed column stream: every slice of the lattice numbering is 16-bit; 32-bit columns give the same bits
+    nsell, nsl, n16, cb = h.sell_stats()
+    assert n16 == nsl and 2 * nsell <= cb <= 2 * nsell + 2 * 96 * nsl
+    b = np.random.default_rng(5).standard_normal(m.nv)
+    b -= b.mean()
+    xs, its, _ = h.pcg(b, max_iter=20, tol_disable=True)
     h.close()
+    hw = fk.Femeko(m, use_mesh_VE=False, sell_wide_cols=1)
+    assert hw.sell_stats()[2] == 0
+    hw.assemble_stiffness(mu, want_vals=False)
+    assert np.array_equal(hw.spmv(u, slot=0), Au)
+    assert np.array_equal(hw.pcg(b, max_iter=20, tol_disable=True)[0], xs)
+    hw.close()
 
 
 def _neighbours(m):

@@ -76,6 +76,38 @@ def test_symbolic_pattern_map_and_plan_against_reference(name, opts):
     assert np.max(np.abs(y - A @ x)) <= 1e-14 * np.max(np.abs(A @ x))
 
 
+def test_sell_packed_columns_mixed_widths():
+    """Packed column stream of the SpMV: slices whose columns span < 65536 store 16-bit offsets, the others 32-bit
+    columns.  A 74 k-node Kuhn cube in lattice order is all-narrow; swapping two far-apart nodes makes a few slices
+    wide; sell_wide_cols=1 forces every slice wide.  All three walk to the same product."""
+    import scipy.sparse as sp
+    m = fk.kuhn_cube(41)
+    assert m.nv > 65536
+    rng = np.random.default_rng(11)
+    x = rng.standard_normal(m.nv)
+    for case in ("lattice", "swapped", "forced"):
+        t = m.t.copy()
+        p = m.p.copy()
+        if case == "swapped":
+            a, b = 5, m.nv - 7
+            t[m.t == a], t[m.t == b] = b, a
+            p[:, [a, b]] = p[:, [b, a]]
+        mm = fk.MESH(p=p, t=t, surfaceT=m.surfaceT, nv=m.nv, nt=m.nt) if case == "swapped" else m
+        plan = export_symbolic(mm, natural_order=1, **({"sell_wide_cols": 1} if case == "forced" else {}))
+        n16, nsl = plan["n_slices16"], plan["nslices"]
+        if case == "lattice":
+            assert n16 == nsl
+        elif case == "swapped":
+            assert 0 < nsl - n16 < 64
+        else:
+            assert n16 == 0 and plan["colz"].size == 2 * plan["nnz_sell"]
+        vals = rng.standard_normal(plan["nnz"])
+        A = sp.csr_matrix((vals, plan["colind"], plan["rowptr"]), shape=(m.nv, m.nv))
+        y = sell_spmv(plan, vals, x)
+        ref = A @ x
+        assert np.max(np.abs(y - ref)) <= 1e-13 * np.max(np.abs(ref))
+
+
 def test_symbolic_owned_rows_only():
     """Multi-GPU partitions: only rows < n_owned get a pattern; halo rows are empty."""
     m = fk.kuhn_cube(4)
