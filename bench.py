@@ -230,8 +230,8 @@ def run_ours(args):
     it_c, rr_c, div_c = C.c_int(), C.c_double(), C.c_double()
 
     def step_e2e():
-        L.check(h.lib.fk_picard_step(h.h, 0, host_ptr(u_host), 0, C.byref(div_c)))
-        L.check(h.lib.fk_pcg(h.h, 0, host_ptr(b_host), host_ptr(x_host), C.byref(o), C.byref(it_c), C.byref(rr_c)))
+        L.check(h.lib.fk_picard_pcg(h.h, 0, host_ptr(u_host), 0, host_ptr(b_host), host_ptr(x_host), C.byref(o), C.byref(div_c),
+                                    C.byref(it_c), C.byref(rr_c)))
         return div_c.value
 
     def barrier():

@@ -537,6 +537,8 @@ int fk_destroy(fk_handle h) {
     if (h->cap_stream) cudaStreamDestroy(h->cap_stream);
     if (h->ctl_host) cudaFreeHost(h->ctl_host);
     if (h->pin8) cudaFreeHost(h->pin8);
+    if (h->copy_ev) cudaEventDestroy(h->copy_ev);
+    if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
     if (h->l2_window_set) cudaCtxResetPersistingL2Cache();
     comm_destroy(h);
     delete h;
@@ -1235,6 +1237,37 @@ int fk_picard_step(fk_handle h, int slot, const double* u, int compat_bug, doubl
     ensure_pcg(h);
     FK_CUDA(cudaMemcpyAsync(h->u.ptr, u, sizeof(double) * (size_t)h->nv, cudaMemcpyHostToDevice, h->stream));
     return picard_step_dev(h, slot, h->u.ptr, compat_bug, div_out);
+  });
+}
+
+// One nonlinear (Picard) iteration from host buffers: fk_picard_step(u) followed by fk_pcg(b -> x) -- the body of
+// the reference loop (NewtonRaphson.jl:148-214, manyBodyIntersecting.jl:141-210).  Same kernels, same results;
+// the right-hand side rides up on a second stream while the sweep runs, so the step pays for one upload, not two.
+int fk_picard_pcg(fk_handle h, int slot, const double* u, int compat_bug, const double* b, double* x, const fk_pcg_opts* opts,
+                  double* div_out, int* iters_out, double* relres_out) {
+  return guard([&]() {
+    need(h && u && b && x, "fk: NULL argument");
+    DeviceGuard dg(h->device);
+    ensure_pcg(h);
+    const size_t n = (size_t)h->n_rows;
+    if (!h->copy_stream) {
+      FK_CUDA(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+      FK_CUDA(cudaEventCreateWithFlags(&h->copy_ev, cudaEventDisableTiming));
+    }
+    h->st_d.ensure((size_t)h->nv);
+    FK_CUDA(cudaMemcpyAsync(h->u.ptr, u, sizeof(double) * (size_t)h->nv, cudaMemcpyHostToDevice, h->stream));
+    // bvec / st_d were last touched by work on h->stream: order the side copies after it
+    FK_CUDA(cudaEventRecord(h->copy_ev, h->stream));
+    FK_CUDA(cudaStreamWaitEvent(h->copy_stream, h->copy_ev, 0));
+    FK_CUDA(cudaMemcpyAsync(h->bvec.ptr, b, sizeof(double) * n, cudaMemcpyHostToDevice, h->copy_stream));
+    if (opts && opts->warm_start) FK_CUDA(cudaMemcpyAsync(h->st_d.ptr, x, sizeof(double) * n, cudaMemcpyHostToDevice, h->copy_stream));
+    FK_CUDA(cudaEventRecord(h->copy_ev, h->copy_stream));
+    const int rc = picard_step_dev(h, slot, h->u.ptr, compat_bug, div_out);
+    FK_CUDA(cudaStreamWaitEvent(h->stream, h->copy_ev, 0));
+    if (rc != 0) { FK_CUDA(cudaStreamSynchronize(h->stream)); return rc; }
+    pcg_dev(h, slot, h->bvec.ptr, h->st_d.ptr, opts, iters_out, relres_out);
+    copy_out(h, h->st_d.ptr, x, n);
+    return 0;
   });
 }
 

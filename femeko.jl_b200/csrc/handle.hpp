@@ -74,6 +74,8 @@ struct fk_handle_s {
   fk::DevBuf<int> tile_hdr;            // int4 per tile
   fk::DevBuf<uint32_t> tile_blob;      // packed per-tile plan blobs (symbolic.hpp)
   int e_pad = 0, asm_cfg = 0, asm_dbg = 0;
+  cudaStream_t copy_stream = nullptr;  // fk_picard_pcg: uploads that overlap the sweep
+  cudaEvent_t copy_ev = nullptr;
   double* pin8 = nullptr;              // pinned host landing zone of the 8-double scalar block
   int asm_grid[8] = {0, 0, 0, 0, 0, 0, 0, 0};  // persistent grid per assembly mode
   size_t asm_smem = 0;

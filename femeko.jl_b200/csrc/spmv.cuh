@@ -17,12 +17,25 @@
 
 constexpr int kSellC = 32;
 
-// a slice with 32-bit columns (columns span >= 65536: rare; halo columns of a partition, unordered meshes)
+// a slice with 32-bit columns (columns span >= 65536: halo columns of a partition, meshes numbered without
+// locality): same batches, one column load per entry
+template <int G>
 static __device__ __forceinline__ double sell_slice_row32(const double* __restrict__ v, const int* __restrict__ c, int w,
                                                           const double* __restrict__ x) {
   double acc = 0.0;
-#pragma unroll 4
-  for (int k = 0; k < w; k++) acc = __dadd_rn(acc, __dmul_rn(__ldcs(v + k * kSellC), __ldg(x + __ldcs(c + k * kSellC))));
+  for (int k = 0; k < w; k += 4 * G) {
+    int cc[4 * G];
+    double vv[4 * G], xx[4 * G];
+#pragma unroll
+    for (int u = 0; u < 4 * G; u++) cc[u] = (k + u < w) ? __ldcs(c + (k + u) * kSellC) : 0;
+#pragma unroll
+    for (int u = 0; u < 4 * G; u++) vv[u] = (k + u < w) ? __ldcs(v + (k + u) * kSellC) : 0.0;
+#pragma unroll
+    for (int u = 0; u < 4 * G; u++) xx[u] = (k + u < w) ? __ldg(x + cc[u]) : 0.0;
+#pragma unroll
+    for (int u = 0; u < 4 * G; u++)
+      if (k + u < w) acc = __dadd_rn(acc, __dmul_rn(vv[u], xx[u]));
+  }
   return acc;
 }
 
@@ -71,7 +84,7 @@ static __global__ void __launch_bounds__(kSpmvThreads, MINB) spmv_sell_kernel(co
     const double* __restrict__ v = vals + m.x + lane;
     const unsigned short* __restrict__ cz = colz + (size_t)m.z * kSellC;
     const double acc = m.w >= 0 ? sell_slice_row16<G>(v, reinterpret_cast<const uint2*>(cz) + lane, m.w, m.y, x)
-                                : sell_slice_row32(v, reinterpret_cast<const int*>(cz) + lane, m.y, x);
+                                : sell_slice_row32<(G > 2 ? 2 : G)>(v, reinterpret_cast<const int*>(cz) + lane, m.y, x);
     if (r >= 0) {
       y[r] = acc;
       if (DOT) dot += acc * x[r];

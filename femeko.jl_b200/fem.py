@@ -268,6 +268,22 @@ class Femeko:
         L.check(self.lib.fk_picard_step(self.h, slot, L.dptr(u), int(compat_bug), C.byref(div)))
         return div.value
 
+    def picard_pcg(self, u, b, slot=0, x0=None, compat_bug=False, **kw):
+        """One nonlinear iteration of the reference loop (NewtonRaphson.jl:148-214): picard_step(u) then pcg(b);
+        one C call, the upload of b overlaps the sweep.  Returns (x, div, iterations, relative residual)."""
+        u = np.ascontiguousarray(u, dtype=np.float64)
+        b = np.ascontiguousarray(b, dtype=np.float64)
+        assert u.shape[0] >= self.nv and b.shape[0] >= self.n_rows
+        x = np.zeros(self.nv)
+        if x0 is not None:
+            x[:] = x0
+            kw["warm_start"] = True
+        o = self.pcg_opts(**kw)
+        div, it, rr = C.c_double(), C.c_int(), C.c_double()
+        L.check(self.lib.fk_picard_pcg(self.h, slot, L.dptr(u), int(compat_bug), L.dptr(b), L.dptr(x), C.byref(o), C.byref(div),
+                                       C.byref(it), C.byref(rr)))
+        return x, div.value, it.value, rr.value
+
     # -- micromagnetics demagnetising field (LL.cpp:287-348) -------------------------------------
     def demag_setup(self, inside_elements, slot=0):
         """LL constructor work: box-method node volumes + stiffnessMatrix(p, t, VE) resident in `slot`."""

@@ -104,6 +104,8 @@ _SIGS = {
     "fk_reset_field": (C.c_int, [_H]),
     "fk_picard_step": (C.c_int, [_H, C.c_int, c_double_p, C.c_int, c_double_p]),
     "fk_picard_step_dev": (C.c_int, [_H, C.c_int, C.c_void_p, C.c_int, c_double_p]),
+    "fk_picard_pcg": (C.c_int, [_H, C.c_int, c_double_p, C.c_int, c_double_p, c_double_p, C.POINTER(fk_pcg_opts), c_double_p,
+                                c_int_p, c_double_p]),
     "fk_demag_setup": (C.c_int, [_H, C.c_int, c_int_p, C.c_int, c_double_p]),
     "fk_demag_field": (C.c_int, [_H, C.c_int, c_double_p, C.POINTER(fk_pcg_opts), C.c_int, c_double_p, c_double_p, c_int_p,
                                  c_double_p]),

@@ -191,6 +191,11 @@ int fk_reset_field(fk_handle h);
  * Returns status 2 if a spline with bc = error was evaluated out of range.                      */
 int fk_picard_step(fk_handle h, int slot, const double* u, int compat_bug, double* div_out);
 int fk_picard_step_dev(fk_handle h, int slot, const double* u_dev, int compat_bug, double* div_out);
+/* One nonlinear iteration from host buffers = fk_picard_step(u) then fk_pcg(b -> x): the body of the reference
+ * loop (NewtonRaphson.jl:148-214, manyBodyIntersecting.jl:141-210).  Identical results; the upload of b (and of
+ * the warm-start x) overlaps the sweep on a second stream.                                                  */
+int fk_picard_pcg(fk_handle h, int slot, const double* u, int compat_bug, const double* b, double* x,
+                  const fk_pcg_opts* opts, double* div_out, int* iters_out, double* relres_out);
 
 /* ---- micromagnetics demagnetising field: the repeated solve of the LL time loop ---------------
  * Replaces LL::LL (constructor work) + LL::magnetostaticField of Femeko_jl_C++/Micromagnetics/LL.cpp

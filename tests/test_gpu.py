@@ -188,6 +188,19 @@ def test_fused_picard_step_against_oracle(mesh):
     div2 = h.picard_step(u2)
     _, Hn2 = orc.recover_field(m, u2)
     assert np.isclose(div2, fk.mu0 * np.max(np.abs(Hn2[m.InsideElements] - Hn[m.InsideElements])), rtol=1e-9)
+    # one-call nonlinear iteration (fk_picard_pcg) = picard_step + pcg, bit for bit (b rides up on a second stream)
+    b = rng.normal(size=m.nv)
+    b -= b.mean()
+    h.set_mu(mu0v)
+    h.reset_field()
+    d_a = h.picard_step(u)
+    x_a, it_a, rr_a = h.pcg(b, tol=1e-9)
+    h.set_mu(mu0v)
+    h.reset_field()
+    x_b, d_b, it_b, rr_b = h.picard_pcg(u, b, tol=1e-9)
+    assert d_a == d_b and it_a == it_b and rr_a == rr_b and np.array_equal(x_a, x_b)
+    x_c, _, it_c, _ = h.picard_pcg(u, b, x0=x_b, tol=1e-8)
+    assert it_c <= 1 and rel_l2(x_c, x_b) < 1e-7
     # bc = "error" semantics (NewtonRaphson.jl:58): |H| beyond the table raises
     h.set_spline(0, fk.Spline1D(data.HofM, data.mu, bc="error"))
     with pytest.raises(L.FemekoError, match="outside the spline"):
