@@ -245,7 +245,7 @@ static void issue_iteration(fk_handle h, cudaStream_t s, const double* vals, int
   PcgCtl* ctl = h->ctl.ptr;
   double* part = h->part.ptr;
   double* scal = h->scal.ptr;
-  const int gs = h->grid_spmv, gv = h->grid_vec;
+  const int gs = h->grid_spmv, gv = h->grid_pcg;
   if (h->comm) {
     comm_halo_exchange(h, s, h->p.ptr);
     launch_spmv(h, s, vals, h->p.ptr, h->Ap.ptr, true, ctl, j);                    // -> scal[0] = p.Ap (this GPU / all ranks)
@@ -519,6 +519,7 @@ int fk_create(const double* p, const int* t, int nv, int nt, const double* VE, c
     h->spmv_ctas = o.spmv_ctas_per_sm;
     configure_spmv(h.get(), o.spmv_ctas_per_sm);
     h->grid_vec = std::max(1, std::min(cdiv(std::max(1, h->n_rows), kVecThreads), h->num_sms * 8));
+    h->grid_pcg = std::max(1, std::min(cdiv(std::max(1, h->n_rows), 2 * kVecUnroll * kVecThreads), h->num_sms * kPcgVecCtas));
     FK_CUDA(cudaStreamSynchronize(s));
     h->st_a.release();
     h->launches += 2;

@@ -105,7 +105,7 @@ struct fk_handle_s {
   fk::DevBuf<unsigned int> tickets;    // last-CTA tickets of the in-kernel grid reductions (zero between kernels)
   fk::DevBuf<fk::PcgCtl> ctl;
   fk::PcgCtl* ctl_host = nullptr;      // pinned
-  int grid_spmv = 0, grid_vec = 0;
+  int grid_spmv = 0, grid_vec = 0, grid_pcg = 0;   // grid_pcg: the update / direction kernels of an iteration
   int spmv_variant = 3, spmv_ctas = 0;   // SpMV launch shape (spmv.cuh: spmv_variant_dispatch), cap on CTAs per SM
   cudaGraphExec_t graph[FK_NUM_SLOTS] = {nullptr, nullptr, nullptr, nullptr};
   int graph_chunk[FK_NUM_SLOTS] = {0, 0, 0, 0};

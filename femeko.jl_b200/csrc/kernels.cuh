@@ -450,8 +450,15 @@ static __global__ void pcg_init_fin_kernel(const double* __restrict__ part3, int
   }
 }
 
+// The two vector kernels of an iteration work on pairs of rows (128-bit loads; every vector of the PCG slab is
+// 256-byte aligned) and keep kVecUnroll pairs per thread in flight: all loads of a pass are issued before the first
+// use.  Launched with kPcgVecCtas CTAs per SM (fk_handle_s::grid_pcg) so the whole grid is resident and the fold
+// of the producer's partial sums in the prologue runs once per CTA, not once per wave.
+constexpr int kVecUnroll = 2;
+constexpr int kPcgVecCtas = 4;
+
 // x += alpha p ; r -= alpha Ap ; partials of r.r and r.(dinv r)        (ConjugateGradient.h:62-76)
-static __global__ void __launch_bounds__(kVecThreads) pcg_update_kernel(double* __restrict__ x, double* __restrict__ r,
+static __global__ void __launch_bounds__(kVecThreads, kPcgVecCtas) pcg_update_kernel(double* __restrict__ x, double* __restrict__ r,
                                                                  const double* __restrict__ p, const double* __restrict__ Ap,
                                                                  const double* __restrict__ dinv, int n,
                                                                  const double* __restrict__ part_pAp, int npart,
@@ -462,7 +469,38 @@ static __global__ void __launch_bounds__(kVecThreads) pcg_update_kernel(double* 
   const double pAp = block_sum_array(part_pAp, npart, red_s);   // npart == 1: the all-reduced scalar
   const double alpha = ctl->absNew[j & 1] / pAp;
   double s_rr = 0.0, s_rz = 0.0;
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+  const int n2 = n >> 1, T = gridDim.x * blockDim.x;
+  double2* __restrict__ x2 = reinterpret_cast<double2*>(x);
+  double2* __restrict__ r2 = reinterpret_cast<double2*>(r);
+  const double2* __restrict__ p2 = reinterpret_cast<const double2*>(p);
+  const double2* __restrict__ A2 = reinterpret_cast<const double2*>(Ap);
+  const double2* __restrict__ d2 = reinterpret_cast<const double2*>(dinv);
+  for (int i0 = blockIdx.x * blockDim.x + threadIdx.x; i0 < n2; i0 += kVecUnroll * T) {
+    double2 xv[kVecUnroll], rv[kVecUnroll], pv[kVecUnroll], av[kVecUnroll], dv[kVecUnroll];
+#pragma unroll
+    for (int u = 0; u < kVecUnroll; u++) {
+      const int i = i0 + u * T;
+      if (i < n2) { pv[u] = p2[i]; av[u] = A2[i]; rv[u] = r2[i]; xv[u] = x2[i]; dv[u] = d2[i]; }
+    }
+#pragma unroll
+    for (int u = 0; u < kVecUnroll; u++) {
+      const int i = i0 + u * T;
+      if (i < n2) {
+        xv[u].x += alpha * pv[u].x;
+        xv[u].y += alpha * pv[u].y;
+        rv[u].x -= alpha * av[u].x;
+        rv[u].y -= alpha * av[u].y;
+        x2[i] = xv[u];
+        r2[i] = rv[u];
+        s_rr += rv[u].x * rv[u].x;
+        s_rz += rv[u].x * (dv[u].x * rv[u].x);
+        s_rr += rv[u].y * rv[u].y;
+        s_rz += rv[u].y * (dv[u].y * rv[u].y);
+      }
+    }
+  }
+  if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) {   // odd row count: the last row
+    const int i = n - 1;
     x[i] += alpha * p[i];
     const double ri = r[i] - alpha * Ap[i];
     r[i] = ri;
@@ -476,7 +514,7 @@ static __global__ void __launch_bounds__(kVecThreads) pcg_update_kernel(double* 
 }
 
 // convergence test, beta, p = dinv r + beta p                           (ConjugateGradient.h:72-81)
-static __global__ void __launch_bounds__(kVecThreads) pcg_direction_kernel(double* __restrict__ p, const double* __restrict__ r,
+static __global__ void __launch_bounds__(kVecThreads, kPcgVecCtas) pcg_direction_kernel(double* __restrict__ p, const double* __restrict__ r,
                                                                     const double* __restrict__ dinv, int n,
                                                                     const double* __restrict__ part2, int npart, int stride,
                                                                     PcgCtl* ctl, int j) {
@@ -493,8 +531,28 @@ static __global__ void __launch_bounds__(kVecThreads) pcg_direction_kernel(doubl
   }
   if (conv) return;
   const double beta = rz / absOld;
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
-    p[i] = dinv[i] * r[i] + beta * p[i];
+  const int n2 = n >> 1, T = gridDim.x * blockDim.x;
+  double2* __restrict__ p2 = reinterpret_cast<double2*>(p);
+  const double2* __restrict__ r2 = reinterpret_cast<const double2*>(r);
+  const double2* __restrict__ d2 = reinterpret_cast<const double2*>(dinv);
+  for (int i0 = blockIdx.x * blockDim.x + threadIdx.x; i0 < n2; i0 += kVecUnroll * T) {
+    double2 rv[kVecUnroll], pv[kVecUnroll], dv[kVecUnroll];
+#pragma unroll
+    for (int u = 0; u < kVecUnroll; u++) {
+      const int i = i0 + u * T;
+      if (i < n2) { dv[u] = d2[i]; rv[u] = r2[i]; pv[u] = p2[i]; }
+    }
+#pragma unroll
+    for (int u = 0; u < kVecUnroll; u++) {
+      const int i = i0 + u * T;
+      if (i < n2) {
+        pv[u].x = dv[u].x * rv[u].x + beta * pv[u].x;
+        pv[u].y = dv[u].y * rv[u].y + beta * pv[u].y;
+        p2[i] = pv[u];
+      }
+    }
+  }
+  if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) p[n - 1] = dinv[n - 1] * r[n - 1] + beta * p[n - 1];
 }
 
 static __global__ void pcg_advance_kernel(PcgCtl* ctl, int chunk) {

@@ -132,7 +132,24 @@ def test_scalar_potential_dropin(name):
     L.load().scalarPotential(L.dptr(u), L.dptr(p), L.iptr(t), L.iptr(sT), L.dptr(nrm), m.nv, m.nt, m.ns, L.dptr(m.VE),
                              L.dptr(g["mu"]), L.dptr(g["F"]), 0)
     ref = g["cg_u"]
-    assert rel_l2(u - u.mean(), ref - ref.mean()) < 1e-8
+    # The golden potential is Eigen's CG stopped at a relative residual of 1e-10 (cg_err in the fixture).  The drop-in
+    # runs to Eigen's default tolerance like magnetostatics.cpp:26-38: machine epsilon, which the singular Neumann
+    # system never reaches within 2n iterations -- the reference throws there (:36-38), the drop-in warns and returns
+    # the last iterate.  Past convergence the recursion wanders (true residual between 1e-16 and 1e-7 depending on
+    # the rounding of the dot products, scripts/dbg_dropin.py shows it for every version of the kernels), so this
+    # entry point is pinned at 1e-6 on both the solution and its true residual against the reference's own matrix;
+    # the solver itself is pinned at equal tolerance in test_pcg_against_oracle_and_eigen_semantics and below.
+    import scipy.sparse as sp
+    A = sp.csc_matrix((g["csc_values_mu"], g["csc_inner"], g["csc_outer"]), shape=(m.nv, m.nv))
+    b = -g["boundary_integral"]
+    assert np.linalg.norm(b - A @ u) / np.linalg.norm(b) < 1e-6
+    assert rel_l2(u - u.mean(), ref - ref.mean()) < 1e-6
+    # same matrix, same right-hand side, the golden's tolerance: iteration count and potential of Eigen itself
+    h = fk.Femeko(m)
+    h.assemble_stiffness(g["mu"], want_vals=False)
+    x, it, rr = h.pcg(b, tol=1e-10)
+    assert abs(it - int(g["cg_iters"])) <= 1 and rel_l2(x - x.mean(), ref - ref.mean()) < 1e-8
+    h.close()
 
 
 def test_field_recovery_and_patch_test():
