@@ -170,6 +170,8 @@ def run_ours(args):
     mesh, part = build_problem(N, rank, world)
     n_owned = part.n_owned if part is not None else 0
     h = fk.Femeko(mesh, use_mesh_VE=False, device=local, n_owned=n_owned)
+    for kv in [t for t in args.tune.split(",") if t]:
+        h.tune(int(kv.split("=")[0]), int(kv.split("=")[1]))
     stream = torch.cuda.Stream(device=dev)
     h.set_stream(stream.cuda_stream)
     if part is not None:
@@ -453,6 +455,7 @@ def main():
     ap.add_argument("--cpu-n", type=int, default=48, help="Kuhn cells per edge of the bounded CPU sample")
     ap.add_argument("--cpu-budget", type=float, default=20.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--tune", default="", help="experiments: comma-separated what=value pairs for fk_tune (e.g. 6=0)")
     ap.add_argument("--presolve", type=int, default=1, help="0: skip the untimed linear presolve (profiling runs)")
     ap.add_argument("--full-solve", type=int, default=1, help="also record one complete nonlinear solve (untimed)")
     args = ap.parse_args()

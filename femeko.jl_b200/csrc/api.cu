@@ -149,21 +149,26 @@ static void ensure_state(fk_handle h) {
 // ------------------------------------------------------------------------------------------------
 // SpMV / PCG launchers
 // ------------------------------------------------------------------------------------------------
-void launch_spmv(fk_handle h, cudaStream_t s, const double* vals, const double* x, double* y, bool dot, const PcgCtl* ctl,
-                 int j) {
-  if (h->sym.nslices <= 0) return;
+// list == nullptr: every slice.  Otherwise the `nlist` slices named by `list`, partial p.Ap sums at part[0 .. grid).
+static void launch_spmv_list(fk_handle h, cudaStream_t s, const double* vals, const double* x, double* y, bool dot, const PcgCtl* ctl,
+                             int j, const RedArgs& ra, const int* list, int nlist, int grid, double* part) {
+  if (nlist <= 0) return;
   const int4* meta = reinterpret_cast<const int4*>(h->slice_meta.ptr);
-  // partitioned: p.Ap is finished (and all-reduced over peer memory) inside the kernel -> scal[0]
-  const RedArgs ra = (dot && h->comm) ? comm_red_args(h, h->tickets.ptr, h->scal.ptr, 0) : RedArgs{};
   spmv_variant_dispatch(h->spmv_variant, [&](auto G, auto MINB) {
     if (dot)
-      spmv_sell_kernel<true, G(), MINB()><<<h->grid_spmv, kSpmvThreads, 0, s>>>(meta, h->srow.ptr, h->sell_colz.ptr, vals, x, y,
-                                                                              h->sym.nslices, h->part.ptr, ra, ctl, j);
+      spmv_sell_kernel<true, G(), MINB()><<<grid, kSpmvThreads, 0, s>>>(meta, h->srow.ptr, h->sell_colz.ptr, vals, x, y, nlist, part,
+                                                                        ra, ctl, j, list);
     else
-      spmv_sell_kernel<false, G(), MINB()><<<h->grid_spmv, kSpmvThreads, 0, s>>>(meta, h->srow.ptr, h->sell_colz.ptr, vals, x, y,
-                                                                               h->sym.nslices, nullptr, RedArgs{}, ctl, j);
+      spmv_sell_kernel<false, G(), MINB()><<<grid, kSpmvThreads, 0, s>>>(meta, h->srow.ptr, h->sell_colz.ptr, vals, x, y, nlist,
+                                                                         nullptr, RedArgs{}, ctl, j, list);
   });
   FK_CUDA(cudaGetLastError());
+}
+void launch_spmv(fk_handle h, cudaStream_t s, const double* vals, const double* x, double* y, bool dot, const PcgCtl* ctl,
+                 int j, bool publish_only) {
+  // partitioned: p.Ap is finished (and all-reduced over peer memory) inside the kernel -> scal[0]
+  const RedArgs ra = (dot && h->comm && !publish_only) ? comm_red_args(h, h->tickets.ptr, h->scal.ptr, 0) : RedArgs{};
+  launch_spmv_list(h, s, vals, x, y, dot, ctl, j, ra, nullptr, h->sym.nslices, h->grid_spmv, h->part.ptr);
 }
 
 // launch geometry of the persistent SpMV: full residency, fixed per handle (deterministic p.Ap)
@@ -176,6 +181,11 @@ static void configure_spmv(fk_handle h, int ctas_per_sm) {
   if (ctas_per_sm > 0) occ = std::min(occ, ctas_per_sm);
   const int groups = (h->sym.nslices + (kSpmvThreads / 32) - 1) / (kSpmvThreads / 32);
   h->grid_spmv = std::max(1, std::min(groups, h->num_sms * occ));
+  const int wpb = kSpmvThreads / 32;
+  // the interior rows leave `spmv_int_reserve` CTA slots per SM free, so the halo branch (push, wait, halo-coupled
+  // rows) is scheduled beside them instead of behind a full persistent grid
+  h->grid_spmv_int = std::max(1, std::min((h->n_slices_int + wpb - 1) / wpb, h->num_sms * std::max(1, occ - h->spmv_int_reserve)));
+  h->grid_spmv_bnd = std::max(1, std::min((h->n_slices_bnd + wpb - 1) / wpb, h->num_sms * occ));
   for (int s = 0; s < FK_NUM_SLOTS; s++)
     if (h->graph[s]) { cudaGraphExecDestroy(h->graph[s]); h->graph[s] = nullptr; }
   if (h->part.ptr) h->part.ensure((size_t)4 * std::max(h->grid_spmv, h->grid_vec) + 16);
@@ -219,7 +229,7 @@ void ensure_pcg(fk_handle h) {
   const size_t nvec = (size_t)h->nv;  // vectors carry halo rows too (SpMV input)
   const size_t stride = (nvec + 31) & ~(size_t)31;
   h->slab_stride = stride;
-  h->pcg_slab.ensure(6 * stride + 128);   // + the 128-word control block of the peer-memory path (comm.cu)
+  h->pcg_slab.ensure(6 * stride + kCtrlWords);   // + the control block of the peer-memory path (comm.cu)
   h->x.ptr = h->pcg_slab.ptr;
   h->r.ptr = h->x.ptr + stride;
   h->p.ptr = h->r.ptr + stride;
@@ -233,7 +243,7 @@ void ensure_pcg(fk_handle h) {
   h->scal.ensure(8);
   h->tickets.ensure(8);
   FK_CUDA(cudaMemsetAsync(h->tickets.ptr, 0, 8 * sizeof(unsigned int), h->stream));
-  FK_CUDA(cudaMemsetAsync(h->pcg_slab.ptr, 0, (6 * stride + 128) * sizeof(double), h->stream));
+  FK_CUDA(cudaMemsetAsync(h->pcg_slab.ptr, 0, (6 * stride + kCtrlWords) * sizeof(double), h->stream));
   if (!h->ctl_host) FK_CUDA(cudaMallocHost((void**)&h->ctl_host, sizeof(PcgCtl)));
 }
 
@@ -246,19 +256,45 @@ static void issue_iteration(fk_handle h, cudaStream_t s, const double* vals, int
   double* part = h->part.ptr;
   double* scal = h->scal.ptr;
   const int gs = h->grid_spmv, gv = h->grid_pcg;
-  if (h->comm) {
+  if (h->comm && comm_capturable(h)) {
+    // peer memory: the producers publish per-CTA partials like on one GPU; each consumer folds them and exchanges
+    // this GPU's sums with the peers in its prologue (peer_fold) -- no last-CTA tail, no extra kernel
+    const PeerRed pr = comm_peer_red(h);
+    int npart = gs;
+    if (h->n_slices_bnd > 0 && h->n_slices_int > 0 && h->overlap_halo && h->halo_stream) {
+      // the rows that read no halo column start at once; the halo exchange and the rows that need it run beside
+      // them on a second stream (a fork / join inside the captured graph)
+      const int gi = h->grid_spmv_int, gb = h->grid_spmv_bnd;
+      FK_CUDA(cudaEventRecord(h->ev_fork, s));
+      FK_CUDA(cudaStreamWaitEvent(h->halo_stream, h->ev_fork, 0));
+      comm_halo_exchange(h, h->halo_stream, h->p.ptr);
+      launch_spmv_list(h, h->halo_stream, vals, h->p.ptr, h->Ap.ptr, true, ctl, j, RedArgs{}, h->slices_bnd.ptr, h->n_slices_bnd, gb,
+                       part + gi);
+      FK_CUDA(cudaEventRecord(h->ev_join, h->halo_stream));
+      launch_spmv_list(h, s, vals, h->p.ptr, h->Ap.ptr, true, ctl, j, RedArgs{}, h->slices_int.ptr, h->n_slices_int, gi, part);
+      FK_CUDA(cudaStreamWaitEvent(s, h->ev_join, 0));
+      npart = gi + gb;
+    } else {
+      comm_halo_exchange(h, s, h->p.ptr);
+      launch_spmv(h, s, vals, h->p.ptr, h->Ap.ptr, true, ctl, j, /*publish_only=*/true);
+    }
+    double* part2 = part + 2 * gs;   // >= npart: both split grids are capped like the full one
+    pcg_update_kernel<<<gv, kVecThreads, 0, s>>>(h->x.ptr, h->r.ptr, h->p.ptr, h->Ap.ptr, h->dinv.ptr, n, part, npart, part2,
+                                                 RedArgs{}, ctl, j, pr);
+    pcg_direction_kernel<<<gv, kVecThreads, 0, s>>>(h->p.ptr, h->r.ptr, h->dinv.ptr, n, part2, gv, gv, ctl, j, pr);
+  } else if (h->comm) {   // NCCL fallback: reduce over this GPU inside the kernels, then ncclAllReduce
     comm_halo_exchange(h, s, h->p.ptr);
-    launch_spmv(h, s, vals, h->p.ptr, h->Ap.ptr, true, ctl, j);                    // -> scal[0] = p.Ap (this GPU / all ranks)
+    launch_spmv(h, s, vals, h->p.ptr, h->Ap.ptr, true, ctl, j);                    // -> scal[0] = p.Ap (this GPU)
     comm_nccl_allreduce(h, s, scal, 1, 0);
     pcg_update_kernel<<<gv, kVecThreads, 0, s>>>(h->x.ptr, h->r.ptr, h->p.ptr, h->Ap.ptr, h->dinv.ptr, n, scal, 1, part + gs,
-                                                 comm_red_args(h, h->tickets.ptr + 1, scal + 1, 0), ctl, j);   // -> scal[1..2] = r.r, r.z
+                                                 comm_red_args(h, h->tickets.ptr + 1, scal + 1, 0), ctl, j, PeerRed{});   // -> scal[1..2] = r.r, r.z
     comm_nccl_allreduce(h, s, scal + 1, 2, 0);
-    pcg_direction_kernel<<<gv, kVecThreads, 0, s>>>(h->p.ptr, h->r.ptr, h->dinv.ptr, n, scal + 1, 1, 1, ctl, j);
+    pcg_direction_kernel<<<gv, kVecThreads, 0, s>>>(h->p.ptr, h->r.ptr, h->dinv.ptr, n, scal + 1, 1, 1, ctl, j, PeerRed{});
   } else {  // one GPU: the consumers fold the per-CTA partials themselves
     launch_spmv(h, s, vals, h->p.ptr, h->Ap.ptr, true, ctl, j);
     pcg_update_kernel<<<gv, kVecThreads, 0, s>>>(h->x.ptr, h->r.ptr, h->p.ptr, h->Ap.ptr, h->dinv.ptr, n, part, gs, part + gs,
-                                                 RedArgs{}, ctl, j);
-    pcg_direction_kernel<<<gv, kVecThreads, 0, s>>>(h->p.ptr, h->r.ptr, h->dinv.ptr, n, part + gs, gv, gv, ctl, j);
+                                                 RedArgs{}, ctl, j, PeerRed{});
+    pcg_direction_kernel<<<gv, kVecThreads, 0, s>>>(h->p.ptr, h->r.ptr, h->dinv.ptr, n, part + gs, gv, gv, ctl, j, PeerRed{});
   }
   FK_CUDA(cudaGetLastError());
 }
@@ -334,14 +370,24 @@ static void pcg_dev(fk_handle h, int slot, const double* b_dev, double* x_dev, c
     pcg_init_kernel<<<gv, kVecThreads, 0, s>>>(b_dev, Ax0, h->dinv.ptr, n, h->r.ptr, h->p.ptr, h->part.ptr,
                                                comm_red_args(h, h->tickets.ptr + 2, h->scal.ptr + 4, 0));   // -> scal[4..6] = b.b, r.r, r.p
     comm_nccl_allreduce(h, s, h->scal.ptr + 4, 3, 0);
-    pcg_init_fin_kernel<<<1, 256, 0, s>>>(h->scal.ptr + 4, 1, 1, tol, max_iter, h->ctl.ptr);
+    pcg_init_fin_kernel<<<1, 256, 0, s>>>(h->scal.ptr + 4, 1, 1, tol, max_iter, ++h->pcg_epoch, h->ctl.ptr);
   } else {
     pcg_init_kernel<<<gv, kVecThreads, 0, s>>>(b_dev, Ax0, h->dinv.ptr, n, h->r.ptr, h->p.ptr, h->part.ptr, RedArgs{});
-    pcg_init_fin_kernel<<<1, 256, 0, s>>>(h->part.ptr, gv, gv, tol, max_iter, h->ctl.ptr);
+    pcg_init_fin_kernel<<<1, 256, 0, s>>>(h->part.ptr, gv, gv, tol, max_iter, ++h->pcg_epoch, h->ctl.ptr);
   }
   FK_CUDA(cudaGetLastError());
   h->launches += 3;
 
+  if (h->comm && comm_capturable(h) && !h->halo_stream) {   // second stream of the split SpMV (created outside any capture)
+    FK_CUDA(cudaStreamCreateWithFlags(&h->halo_stream, cudaStreamNonBlocking));
+    FK_CUDA(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
+    FK_CUDA(cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming));
+    if (h->l2_window_set) {
+      cudaStreamAttrValue attr{};
+      attr.accessPolicyWindow = h->l2_window;
+      if (cudaStreamSetAttribute(h->halo_stream, cudaStreamAttributeAccessPolicyWindow, &attr) != cudaSuccess) cudaGetLastError();
+    }
+  }
   const bool graphed = !h->comm || comm_capturable(h);
   if (graphed) build_graph(h, slot, chunk);
   int launched = 0;
@@ -352,7 +398,8 @@ static void pcg_dev(fk_handle h, int slot, const double* b_dev, double* x_dev, c
       h->launches += (long long)chunk * 3 + 1;   // the halo pack kernel is counted in comm_halo_exchange
     } else {
       FK_CUDA(cudaGraphLaunch(h->graph[slot], s));
-      h->launches += (long long)chunk * (h->comm ? 5 : 3) + 1;
+      const bool split = h->comm && h->halo_stream && h->overlap_halo && h->n_slices_bnd > 0 && h->n_slices_int > 0;
+      h->launches += (long long)chunk * (h->comm ? (split ? 6 : 5) : 3) + 1;
     }
     launched += chunk;
     FK_CUDA(cudaMemcpyAsync(h->ctl_host, h->ctl.ptr, sizeof(PcgCtl), cudaMemcpyDeviceToHost, s));
@@ -492,6 +539,18 @@ int fk_create(const double* p, const int* t, int nv, int nt, const double* VE, c
     h->slice_ptr.upload(S.slice_ptr, s);
     h->srow.upload(S.srow, s);
     h->slice_meta.upload(S.slice_meta, s);
+    if (o.n_owned > 0 && o.n_owned < nv) {   // partition: slices that read halo columns vs slices that do not
+      std::vector<int> li, lb;
+      for (int sl = 0; sl < S.nslices; sl++) {
+        bool halo = false;
+        for (int e = S.slice_ptr[sl]; e < S.slice_ptr[sl + 1] && !halo; e++) halo = S.sell_col[(size_t)e] >= o.n_owned;
+        (halo ? lb : li).push_back(sl);
+      }
+      h->n_slices_int = (int)li.size();
+      h->n_slices_bnd = (int)lb.size();
+      h->slices_int.upload(li, s);
+      h->slices_bnd.upload(lb, s);
+    }
     h->sell_colz.ensure(S.sell_colz.size() + 2 * kSlack);
     h->sell_colz.upload(S.sell_colz, s);
     h->csr2sell.upload(S.csr2sell, s);
@@ -538,6 +597,9 @@ int fk_destroy(fk_handle h) {
     if (h->cap_stream) cudaStreamDestroy(h->cap_stream);
     if (h->ctl_host) cudaFreeHost(h->ctl_host);
     if (h->pin8) cudaFreeHost(h->pin8);
+    if (h->ev_fork) cudaEventDestroy(h->ev_fork);
+    if (h->ev_join) cudaEventDestroy(h->ev_join);
+    if (h->halo_stream) cudaStreamDestroy(h->halo_stream);
     if (h->copy_ev) cudaEventDestroy(h->copy_ev);
     if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
     if (h->l2_window_set) cudaCtxResetPersistingL2Cache();
@@ -581,6 +643,16 @@ int fk_tune(fk_handle h, int what, int value) {
         need(value >= 0 && value < kNumSpmvVariants, "fk_tune: spmv variant out of range");
         h->spmv_variant = value;
         configure_spmv(h, h->spmv_ctas);
+        break;
+      case 6:
+        need(value >= 0 && value < 8, "fk_tune: reserve out of range");
+        h->spmv_int_reserve = value;
+        configure_spmv(h, h->spmv_ctas);
+        break;
+      case 5:   // partitions: 1 (default) = halo exchange + halo-coupled rows beside the interior rows of the SpMV
+        h->overlap_halo = value != 0;
+        for (int sl = 0; sl < FK_NUM_SLOTS; sl++)
+          if (h->graph[sl]) { cudaGraphExecDestroy(h->graph[sl]); h->graph[sl] = nullptr; }
         break;
       default: throw std::runtime_error("fk_tune: unknown option");
     }

@@ -235,6 +235,12 @@ RedArgs comm_red_args(fk_handle_s* h, unsigned int* ticket, double* out, int op)
   }
   return ra;
 }
+PeerRed comm_peer_red(fk_handle_s* h) {
+  PeerRed pr{0, 1, nullptr, nullptr};
+  Comm* c = h->comm;
+  if (c && c->nranks > 1 && c->p2p.on) pr = PeerRed{c->rank, c->nranks, c->p2p.peer_ctrl_dev.ptr, c->p2p.ctrl};
+  return pr;
+}
 // NCCL fallback: the kernels reduced over this GPU only; finish over the ranks with ncclAllReduce
 void comm_nccl_allreduce(fk_handle_s* h, cudaStream_t s, double* v, int n, int op) {
   Comm* c = h->comm;

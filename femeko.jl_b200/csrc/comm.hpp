@@ -9,11 +9,13 @@ struct fk_handle_s;
 namespace fk {
 struct PcgCtl;
 struct RedArgs;
+struct PeerRed;
+PeerRed comm_peer_red(fk_handle_s* h);   // peer-memory descriptor of the consumer-side fold (kernels.cuh: peer_fold)
 RedArgs comm_red_args(fk_handle_s* h, unsigned int* ticket, double* out, int op);
 void comm_nccl_allreduce(fk_handle_s* h, cudaStream_t s, double* v, int n, int op);   // no-op unless on the NCCL path
 int comm_kind(fk_handle_s* h);   // 0 single GPU, 1 NCCL, 2 peer memory
 void launch_spmv(fk_handle_s* h, cudaStream_t s, const double* vals, const double* x, double* y, bool dot, const PcgCtl* ctl,
-                 int j);
+                 int j, bool publish_only = false);
 void comm_destroy(fk_handle_s* h);
 void comm_halo_exchange(fk_handle_s* h, cudaStream_t s, double* v);
 // out[0..nvals) = reduction over ranks (op 0 sum / 1 max) of the folded per-CTA partials part[v*stride + 0..npart);

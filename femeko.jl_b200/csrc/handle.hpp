@@ -74,6 +74,13 @@ struct fk_handle_s {
   fk::DevBuf<int> tile_hdr;            // int4 per tile
   fk::DevBuf<uint32_t> tile_blob;      // packed per-tile plan blobs (symbolic.hpp)
   int e_pad = 0, asm_cfg = 0, asm_dbg = 0;
+  // partitions: SELL slices that read no halo column / at least one (spmv split, api.cu: issue_iteration)
+  fk::DevBuf<int> slices_int, slices_bnd;
+  int n_slices_int = 0, n_slices_bnd = 0, grid_spmv_int = 1, grid_spmv_bnd = 1;
+  bool overlap_halo = true;
+  int spmv_int_reserve = 0;   // CTA slots per SM the interior SpMV leaves to the halo branch (measured: 0 best)
+  cudaStream_t halo_stream = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   cudaStream_t copy_stream = nullptr;  // fk_picard_pcg: uploads that overlap the sweep
   cudaEvent_t copy_ev = nullptr;
   double* pin8 = nullptr;              // pinned host landing zone of the 8-double scalar block
@@ -105,6 +112,7 @@ struct fk_handle_s {
   fk::DevBuf<unsigned int> tickets;    // last-CTA tickets of the in-kernel grid reductions (zero between kernels)
   fk::DevBuf<fk::PcgCtl> ctl;
   fk::PcgCtl* ctl_host = nullptr;      // pinned
+  unsigned long long pcg_epoch = 0;   // solves started on this handle (identical on every rank of a partitioned problem)
   int grid_spmv = 0, grid_vec = 0, grid_pcg = 0;   // grid_pcg: the update / direction kernels of an iteration
   int spmv_variant = 3, spmv_ctas = 0;   // SpMV launch shape (spmv.cuh: spmv_variant_dispatch), cap on CTAs per SM
   cudaGraphExec_t graph[FK_NUM_SLOTS] = {nullptr, nullptr, nullptr, nullptr};

@@ -86,7 +86,10 @@ constexpr int kOffMail = kMaxNeigh;
 constexpr int kOffErr = kOffMail + 2 * kMaxRanks * kMailWords;
 constexpr int kOffCnt = kOffErr + 1;
 constexpr int kOffHaloCnt = kOffCnt + 1;
-constexpr int kCtrlWords = 128;
+constexpr int kMail2Words = 3;     // consumer-side fold of the PCG iteration: 2 values + sequence flag per (slot, rank)
+constexpr int kOffMail2 = kOffHaloCnt + 1;
+constexpr int kCtrlWords = 256;
+static_assert(kOffMail2 + 2 * kMaxRanks * kMail2Words <= kCtrlWords, "control block too small");
 
 __device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
   asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
@@ -185,6 +188,52 @@ __device__ __forceinline__ void grid_reduce_finish(const double (&v)[NV], double
     for (int k = 0; k < NV; k++) ra.out[k] = val[k];
     *ra.ticket = 0u;
   }
+}
+
+// Dot products of a PCG iteration on a partitioned problem, folded on the CONSUMER side: the producing kernel only
+// publishes its per-CTA partials (no last-CTA tail); every CTA of the consuming kernel folds them (identical bits
+// in every CTA), CTA 0 stores this GPU's sums into every peer's mailbox over NVLink, and every CTA waits for the
+// peers' sums in its own GPU's mailbox and adds them in rank order -> identical bits on every rank.  seq = a number
+// every rank derives identically from (solve epoch, iteration, which reduction); consecutive reductions alternate
+// mailbox slots, and a rank can only reach the next use of a slot after the peer's previous readers of it have
+// finished (it needs the peer's contribution to the reduction in between, sent by a later kernel of the peer).
+struct PeerRed {
+  int rank, nranks;                            // nranks <= 1: this GPU only
+  unsigned long long* const* peer_ctrl;
+  unsigned long long* my_ctrl;
+};
+template <int NV>
+__device__ __forceinline__ void peer_fold(double (&v)[NV], const PeerRed& pr, unsigned long long seq) {
+  static_assert(NV <= kMail2Words - 1, "mailbox holds 2 values");
+  if (pr.nranks <= 1) return;
+  __shared__ double sh[NV * kMaxRanks];
+  const int slot = (int)(seq & 1ULL), t = threadIdx.x;
+  if (t < pr.nranks) {
+    if (t == pr.rank) {
+#pragma unroll
+      for (int k = 0; k < NV; k++) sh[k * kMaxRanks + t] = v[k];
+    } else {
+      if (blockIdx.x == 0) {
+        unsigned long long* box = pr.peer_ctrl[t] + kOffMail2 + ((size_t)slot * kMaxRanks + pr.rank) * kMail2Words;
+#pragma unroll
+        for (int k = 0; k < NV; k++) reinterpret_cast<double*>(box)[k] = v[k];
+        __threadfence_system();
+        st_release_sys(box + kMail2Words - 1, seq);
+      }
+      const unsigned long long* box = pr.my_ctrl + kOffMail2 + ((size_t)slot * kMaxRanks + t) * kMail2Words;
+      spin_until(box + kMail2Words - 1, seq, pr.my_ctrl + kOffErr);
+#pragma unroll
+      for (int k = 0; k < NV; k++) sh[k * kMaxRanks + t] = reinterpret_cast<const volatile double*>(box)[k];
+    }
+  }
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < NV; k++) {
+    double s = 0.0;
+    for (int r = 0; r < pr.nranks; r++) s += sh[k * kMaxRanks + r];
+    v[k] = s;
+  }
+  __syncthreads();
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -385,7 +434,12 @@ struct PcgCtl {
   double absNew[2];  // r.z of the current / next iteration (ping-pong by iteration parity)
   double rhs2, thr, r2;
   int base_it, max_iter, done, iters;
+  unsigned long long epoch;   // solve counter (same on every rank): high half of the peer_fold sequence numbers
 };
+
+__device__ __forceinline__ unsigned long long pcg_seq(const PcgCtl* c, int j, int which) {
+  return (c->epoch << 32) + 2ULL * (unsigned long long)(c->base_it + j) + (unsigned long long)which + 1ULL;
+}
 
 __device__ __forceinline__ bool pcg_inactive(const PcgCtl* c, int j) {
   return c != nullptr && (c->done != 0 || c->base_it + j >= c->max_iter);
@@ -432,7 +486,7 @@ static __global__ void __launch_bounds__(kVecThreads) pcg_init_kernel(const doub
 // single block: fold the partials of (b.b, r.r, r.p) (npart == 1: already reduced scalars) -> thresholds and
 // the early exits of ConjugateGradient.h:43-56
 static __global__ void pcg_init_fin_kernel(const double* __restrict__ part3, int npart, int stride, double tol, int max_iter,
-                                    PcgCtl* ctl) {
+                                    unsigned long long epoch, PcgCtl* ctl) {
   __shared__ double red[33];
   const double bb = block_sum_array(part3, npart, red);
   const double rr = block_sum_array(part3 + stride, npart, red);
@@ -446,6 +500,7 @@ static __global__ void pcg_init_fin_kernel(const double* __restrict__ part3, int
     ctl->base_it = 0;
     ctl->max_iter = max_iter;
     ctl->iters = 0;
+    ctl->epoch = epoch;
     ctl->done = (bb == 0.0 || rr < ctl->thr) ? 1 : 0;
   }
 }
@@ -463,11 +518,12 @@ static __global__ void __launch_bounds__(kVecThreads, kPcgVecCtas) pcg_update_ke
                                                                  const double* __restrict__ dinv, int n,
                                                                  const double* __restrict__ part_pAp, int npart,
                                                                  double* __restrict__ part2, const RedArgs red, const PcgCtl* ctl,
-                                                                 int j) {
+                                                                 int j, const PeerRed pr) {
   __shared__ double red_s[33];
   if (pcg_inactive(ctl, j)) return;
-  const double pAp = block_sum_array(part_pAp, npart, red_s);   // npart == 1: the all-reduced scalar
-  const double alpha = ctl->absNew[j & 1] / pAp;
+  double pAp_v[1] = {block_sum_array(part_pAp, npart, red_s)};   // npart == 1: the all-reduced scalar (NCCL path)
+  peer_fold<1>(pAp_v, pr, pcg_seq(ctl, j, 0));
+  const double alpha = ctl->absNew[j & 1] / pAp_v[0];
   double s_rr = 0.0, s_rz = 0.0;
   const int n2 = n >> 1, T = gridDim.x * blockDim.x;
   double2* __restrict__ x2 = reinterpret_cast<double2*>(x);
@@ -517,11 +573,12 @@ static __global__ void __launch_bounds__(kVecThreads, kPcgVecCtas) pcg_update_ke
 static __global__ void __launch_bounds__(kVecThreads, kPcgVecCtas) pcg_direction_kernel(double* __restrict__ p, const double* __restrict__ r,
                                                                     const double* __restrict__ dinv, int n,
                                                                     const double* __restrict__ part2, int npart, int stride,
-                                                                    PcgCtl* ctl, int j) {
+                                                                    PcgCtl* ctl, int j, const PeerRed pr) {
   __shared__ double red[33];
   if (pcg_inactive(ctl, j)) return;
-  const double rr = block_sum_array(part2, npart, red);
-  const double rz = block_sum_array(part2 + stride, npart, red);
+  double d2v[2] = {block_sum_array(part2, npart, red), block_sum_array(part2 + stride, npart, red)};
+  peer_fold<2>(d2v, pr, pcg_seq(ctl, j, 1));
+  const double rr = d2v[0], rz = d2v[1];
   const double absOld = ctl->absNew[j & 1];
   const bool conv = rr < ctl->thr;
   if (blockIdx.x == 0 && threadIdx.x == 0) {

@@ -72,13 +72,16 @@ static __global__ void __launch_bounds__(kSpmvThreads, MINB) spmv_sell_kernel(co
                                                                   const unsigned short* __restrict__ colz,
                                                                   const double* __restrict__ vals, const double* __restrict__ x,
                                                                   double* __restrict__ y, int nslices, double* __restrict__ part,
-                                                                  const RedArgs red, const PcgCtl* ctl, int j) {
+                                                                  const RedArgs red, const PcgCtl* ctl, int j,
+                                                                  const int* __restrict__ slice_list) {
   __shared__ double red_s[33];
   if (pcg_inactive(ctl, j)) return;
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   constexpr int WPB = kSpmvThreads / 32;
   double dot = 0.0;
-  for (int sl = blockIdx.x * WPB + wib; sl < nslices; sl += gridDim.x * WPB) {
+  // slice_list != nullptr: the kernel covers the nslices slices it names (partitions: interior / halo-coupled rows)
+  for (int q = blockIdx.x * WPB + wib; q < nslices; q += gridDim.x * WPB) {
+    const int sl = slice_list ? __ldg(slice_list + q) : q;
     const int4 m = __ldg(slice_meta + sl);   // {value base, width, column offset in 64-byte units, column base | -1}
     const int r = __ldg(srow + sl * kSellC + lane);
     const double* __restrict__ v = vals + m.x + lane;
