@@ -149,6 +149,22 @@ static void ensure_state(fk_handle h) {
 // ------------------------------------------------------------------------------------------------
 // SpMV / PCG launchers
 // ------------------------------------------------------------------------------------------------
+// launch with (pdl) or without the programmatic-stream-serialization attribute (kernels.cuh: griddep_wait)
+template <typename... KArgs, typename... Args>
+static void launch_k(bool pdl, void (*k)(KArgs...), int grid, int block, cudaStream_t s, Args&&... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3((unsigned)grid);
+  cfg.blockDim = dim3((unsigned)block);
+  cfg.dynamicSmemBytes = 0;
+  cfg.stream = s;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = pdl ? 1 : 0;
+  FK_CUDA(cudaLaunchKernelEx(&cfg, k, KArgs(std::forward<Args>(args))...));
+}
+
 // list == nullptr: every slice.  Otherwise the `nlist` slices named by `list`, partial p.Ap sums at part[0 .. grid).
 static void launch_spmv_list(fk_handle h, cudaStream_t s, const double* vals, const double* x, double* y, bool dot, const PcgCtl* ctl,
                              int j, const RedArgs& ra, const int* list, int nlist, int grid, double* part) {
@@ -156,8 +172,8 @@ static void launch_spmv_list(fk_handle h, cudaStream_t s, const double* vals, co
   const int4* meta = reinterpret_cast<const int4*>(h->slice_meta.ptr);
   spmv_variant_dispatch(h->spmv_variant, [&](auto G, auto MINB) {
     if (dot)
-      spmv_sell_kernel<true, G(), MINB()><<<grid, kSpmvThreads, 0, s>>>(meta, h->srow.ptr, h->sell_colz.ptr, vals, x, y, nlist, part,
-                                                                        ra, ctl, j, list);
+      launch_k(h->pdl && !h->comm, spmv_sell_kernel<true, G(), MINB()>, grid, kSpmvThreads, s, meta, h->srow.ptr, h->sell_colz.ptr, vals,
+               x, y, nlist, part, ra, ctl, j, list);
     else
       spmv_sell_kernel<false, G(), MINB()><<<grid, kSpmvThreads, 0, s>>>(meta, h->srow.ptr, h->sell_colz.ptr, vals, x, y, nlist,
                                                                          nullptr, RedArgs{}, ctl, j, list);
@@ -292,9 +308,9 @@ static void issue_iteration(fk_handle h, cudaStream_t s, const double* vals, int
     pcg_direction_kernel<<<gv, kVecThreads, 0, s>>>(h->p.ptr, h->r.ptr, h->dinv.ptr, n, scal + 1, 1, 1, ctl, j, PeerRed{});
   } else {  // one GPU: the consumers fold the per-CTA partials themselves
     launch_spmv(h, s, vals, h->p.ptr, h->Ap.ptr, true, ctl, j);
-    pcg_update_kernel<<<gv, kVecThreads, 0, s>>>(h->x.ptr, h->r.ptr, h->p.ptr, h->Ap.ptr, h->dinv.ptr, n, part, gs, part + gs,
-                                                 RedArgs{}, ctl, j, PeerRed{});
-    pcg_direction_kernel<<<gv, kVecThreads, 0, s>>>(h->p.ptr, h->r.ptr, h->dinv.ptr, n, part + gs, gv, gv, ctl, j, PeerRed{});
+    launch_k(h->pdl, pcg_update_kernel, gv, kVecThreads, s, h->x.ptr, h->r.ptr, h->p.ptr, h->Ap.ptr, h->dinv.ptr, n, part, gs, part + gs,
+             RedArgs{}, ctl, j, PeerRed{});
+    launch_k(h->pdl, pcg_direction_kernel, gv, kVecThreads, s, h->p.ptr, h->r.ptr, h->dinv.ptr, n, part + gs, gv, gv, ctl, j, PeerRed{});
   }
   FK_CUDA(cudaGetLastError());
 }
@@ -643,6 +659,11 @@ int fk_tune(fk_handle h, int what, int value) {
         need(value >= 0 && value < kNumSpmvVariants, "fk_tune: spmv variant out of range");
         h->spmv_variant = value;
         configure_spmv(h, h->spmv_ctas);
+        break;
+      case 7:   // single GPU: programmatic dependent launch between the kernels of a PCG iteration (1 = on; default off)
+        h->pdl = value != 0;
+        for (int sl = 0; sl < FK_NUM_SLOTS; sl++)
+          if (h->graph[sl]) { cudaGraphExecDestroy(h->graph[sl]); h->graph[sl] = nullptr; }
         break;
       case 6:
         need(value >= 0 && value < 8, "fk_tune: reserve out of range");

@@ -77,6 +77,7 @@ struct fk_handle_s {
   // partitions: SELL slices that read no halo column / at least one (spmv split, api.cu: issue_iteration)
   fk::DevBuf<int> slices_int, slices_bnd;
   int n_slices_int = 0, n_slices_bnd = 0, grid_spmv_int = 1, grid_spmv_bnd = 1;
+  bool pdl = false;           // programmatic dependent launch inside the single-GPU PCG iteration (measured: 63.8 vs 62.6 us -> off)
   bool overlap_halo = true;
   int spmv_int_reserve = 0;   // CTA slots per SM the interior SpMV leaves to the halo branch (measured: 0 best)
   cudaStream_t halo_stream = nullptr;

@@ -33,6 +33,13 @@ __device__ __forceinline__ double warp_max(double v) {
   return v;
 }
 
+// Programmatic dependent launch (the PCG iteration of one GPU): a kernel launched with the programmatic-serialization
+// attribute may become resident while its predecessor still runs; it must not touch the predecessor's results before
+// griddep_wait() (which returns once the predecessor has completed and its writes are visible; a no-op for a plain
+// launch).  griddep_launch() lets the successor's CTAs take SM slots as soon as this kernel's CTAs free them.
+__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void griddep_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 // Deterministic block reduction (fixed shuffle tree, warps folded in index order).  Every thread
 // returns the total.  `scratch` holds >= 33 doubles.  Safe to call repeatedly.
 __device__ __forceinline__ double block_sum(double v, double* scratch) {
@@ -520,6 +527,8 @@ static __global__ void __launch_bounds__(kVecThreads, kPcgVecCtas) pcg_update_ke
                                                                  double* __restrict__ part2, const RedArgs red, const PcgCtl* ctl,
                                                                  int j, const PeerRed pr) {
   __shared__ double red_s[33];
+  griddep_wait();
+  griddep_launch();
   if (pcg_inactive(ctl, j)) return;
   double pAp_v[1] = {block_sum_array(part_pAp, npart, red_s)};   // npart == 1: the all-reduced scalar (NCCL path)
   peer_fold<1>(pAp_v, pr, pcg_seq(ctl, j, 0));
@@ -575,6 +584,8 @@ static __global__ void __launch_bounds__(kVecThreads, kPcgVecCtas) pcg_direction
                                                                     const double* __restrict__ part2, int npart, int stride,
                                                                     PcgCtl* ctl, int j, const PeerRed pr) {
   __shared__ double red[33];
+  griddep_wait();
+  griddep_launch();
   if (pcg_inactive(ctl, j)) return;
   double d2v[2] = {block_sum_array(part2, npart, red), block_sum_array(part2 + stride, npart, red)};
   peer_fold<2>(d2v, pr, pcg_seq(ctl, j, 1));

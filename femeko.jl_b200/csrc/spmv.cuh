@@ -17,6 +17,8 @@
 
 constexpr int kSellC = 32;
 
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+
 // a slice with 32-bit columns (columns span >= 65536: halo columns of a partition, meshes numbered without
 // locality): same batches, one column load per entry
 template <int G>
@@ -75,6 +77,19 @@ static __global__ void __launch_bounds__(kSpmvThreads, MINB) spmv_sell_kernel(co
                                                                   const RedArgs red, const PcgCtl* ctl, int j,
                                                                   const int* __restrict__ slice_list) {
   __shared__ double red_s[33];
+  // the matrix stream does not depend on the previous kernel: pull the head of this warp's first slice towards L2
+  // while the predecessor drains, then wait for its results (x, the control block)
+  {
+    const int q0 = blockIdx.x * (kSpmvThreads / 32) + (threadIdx.x >> 5);
+    if (q0 < nslices) {
+      const int sl0 = slice_list ? __ldg(slice_list + q0) : q0;
+      const int4 m0 = __ldg(slice_meta + sl0);
+      prefetch_l2(vals + m0.x + (threadIdx.x & 31));
+      prefetch_l2(colz + (size_t)m0.z * kSellC + 4 * (threadIdx.x & 31));
+    }
+  }
+  griddep_wait();
+  griddep_launch();
   if (pcg_inactive(ctl, j)) return;
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   constexpr int WPB = kSpmvThreads / 32;

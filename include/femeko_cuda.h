@@ -78,7 +78,8 @@ int fk_synchronize(fk_handle h);
  * skip phase 1 / 2 of the assembly kernel (matrix values are then garbage).  4 = SpMV launch shape
  * {entries per batch, min CTAs per SM}: 0 {4,8} 1 {4,6} 2 {8,5} 3 {8,4} (default) 4 {16,3} 5 {16,2}; results do
  * not depend on it.  5 = partitioned handles: 1 (default) overlaps the halo exchange with the SpMV of the rows that
- * read no halo column, 0 serialises them; 6 = CTA slots per SM that SpMV leaves free for the halo branch (default 0).                            */
+ * read no halo column, 0 serialises them; 6 = CTA slots per SM that SpMV leaves free for the halo branch (default 0); 7 = programmatic dependent launch between the kernels of a single-GPU
+ * PCG iteration (default 0: measured 2 % slower on B200).                            */
 int fk_tune(fk_handle h, int what, int value);
 /* number of kernels of this library launched through the handle so far (graph nodes included) */
 int fk_launch_count(fk_handle h, long long* n);
