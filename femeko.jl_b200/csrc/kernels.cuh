@@ -77,6 +77,31 @@ __device__ __forceinline__ double block_sum_array(const double* __restrict__ a, 
   return block_sum(v, scratch);
 }
 
+// two sums in one pass (same tree and fold order as block_sum for each); scratch holds >= 66 doubles
+__device__ __forceinline__ void block_sum2(double& a, double& b, double* scratch) {
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+  a = warp_sum(a);
+  b = warp_sum(b);
+  __syncthreads();
+  if (lane == 0) { scratch[w] = a; scratch[33 + w] = b; }
+  __syncthreads();
+  if (threadIdx.x < 2) {
+    double s = 0.0;
+    for (int i = 0; i < nw; i++) s += scratch[33 * threadIdx.x + i];
+    scratch[33 * threadIdx.x + 32] = s;
+  }
+  __syncthreads();
+  a = scratch[32];
+  b = scratch[65];
+}
+__device__ __forceinline__ void block_sum2_array(const double* __restrict__ pa, const double* __restrict__ pb, int n, double* scratch,
+                                                 double& a, double& b) {
+  a = 0.0;
+  b = 0.0;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) { a += pa[i]; b += pb[i]; }
+  block_sum2(a, b, scratch);
+}
+
 // ------------------------------------------------------------------------------------------------
 // Grid-wide reductions finished INSIDE the producing kernel, and across GPUs over peer memory.
 // Every CTA publishes its partial sums; the CTA that takes the last ticket folds all partials in index
@@ -526,27 +551,31 @@ static __global__ void __launch_bounds__(kVecThreads, kPcgVecCtas) pcg_update_ke
                                                                  const double* __restrict__ part_pAp, int npart,
                                                                  double* __restrict__ part2, const RedArgs red, const PcgCtl* ctl,
                                                                  int j, const PeerRed pr) {
-  __shared__ double red_s[33];
+  __shared__ double red_s[66];
   griddep_wait();
   griddep_launch();
   if (pcg_inactive(ctl, j)) return;
-  double pAp_v[1] = {block_sum_array(part_pAp, npart, red_s)};   // npart == 1: the all-reduced scalar (NCCL path)
-  peer_fold<1>(pAp_v, pr, pcg_seq(ctl, j, 0));
-  const double alpha = ctl->absNew[j & 1] / pAp_v[0];
-  double s_rr = 0.0, s_rz = 0.0;
   const int n2 = n >> 1, T = gridDim.x * blockDim.x;
   double2* __restrict__ x2 = reinterpret_cast<double2*>(x);
   double2* __restrict__ r2 = reinterpret_cast<double2*>(r);
   const double2* __restrict__ p2 = reinterpret_cast<const double2*>(p);
   const double2* __restrict__ A2 = reinterpret_cast<const double2*>(Ap);
   const double2* __restrict__ d2 = reinterpret_cast<const double2*>(dinv);
-  for (int i0 = blockIdx.x * blockDim.x + threadIdx.x; i0 < n2; i0 += kVecUnroll * T) {
-    double2 xv[kVecUnroll], rv[kVecUnroll], pv[kVecUnroll], av[kVecUnroll], dv[kVecUnroll];
+  double2 xv[kVecUnroll], rv[kVecUnroll], pv[kVecUnroll], av[kVecUnroll], dv[kVecUnroll];
+  auto load = [&](int i0) {
 #pragma unroll
     for (int u = 0; u < kVecUnroll; u++) {
       const int i = i0 + u * T;
       if (i < n2) { pv[u] = p2[i]; av[u] = A2[i]; rv[u] = r2[i]; xv[u] = x2[i]; dv[u] = d2[i]; }
     }
+  };
+  int i0 = blockIdx.x * blockDim.x + threadIdx.x;
+  load(i0);   // the first batch is in flight while the producer's partial sums are folded
+  double pAp_v[1] = {block_sum_array(part_pAp, npart, red_s)};   // npart == 1: the all-reduced scalar (NCCL path)
+  peer_fold<1>(pAp_v, pr, pcg_seq(ctl, j, 0));
+  const double alpha = ctl->absNew[j & 1] / pAp_v[0];
+  double s_rr = 0.0, s_rz = 0.0;
+  while (i0 < n2) {
 #pragma unroll
     for (int u = 0; u < kVecUnroll; u++) {
       const int i = i0 + u * T;
@@ -563,6 +592,8 @@ static __global__ void __launch_bounds__(kVecThreads, kPcgVecCtas) pcg_update_ke
         s_rz += rv[u].y * (dv[u].y * rv[u].y);
       }
     }
+    i0 += kVecUnroll * T;
+    if (i0 < n2) load(i0);
   }
   if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) {   // odd row count: the last row
     const int i = n - 1;
@@ -572,8 +603,7 @@ static __global__ void __launch_bounds__(kVecThreads, kPcgVecCtas) pcg_update_ke
     s_rr += ri * ri;
     s_rz += ri * (dinv[i] * ri);
   }
-  s_rr = block_sum(s_rr, red_s);
-  s_rz = block_sum(s_rz, red_s);
+  block_sum2(s_rr, s_rz, red_s);
   const double v[2] = {s_rr, s_rz};
   grid_reduce_finish<2>(v, part2, gridDim.x, red, red_s);   // -> out[0..1] = (r.r, r.z) over all ranks
 }
@@ -583,11 +613,26 @@ static __global__ void __launch_bounds__(kVecThreads, kPcgVecCtas) pcg_direction
                                                                     const double* __restrict__ dinv, int n,
                                                                     const double* __restrict__ part2, int npart, int stride,
                                                                     PcgCtl* ctl, int j, const PeerRed pr) {
-  __shared__ double red[33];
+  __shared__ double red[66];
   griddep_wait();
   griddep_launch();
   if (pcg_inactive(ctl, j)) return;
-  double d2v[2] = {block_sum_array(part2, npart, red), block_sum_array(part2 + stride, npart, red)};
+  const int n2 = n >> 1, T = gridDim.x * blockDim.x;
+  double2* __restrict__ p2 = reinterpret_cast<double2*>(p);
+  const double2* __restrict__ r2 = reinterpret_cast<const double2*>(r);
+  const double2* __restrict__ d2 = reinterpret_cast<const double2*>(dinv);
+  double2 rv[kVecUnroll], pv[kVecUnroll], dv[kVecUnroll];
+  auto load = [&](int i0) {
+#pragma unroll
+    for (int u = 0; u < kVecUnroll; u++) {
+      const int i = i0 + u * T;
+      if (i < n2) { dv[u] = d2[i]; rv[u] = r2[i]; pv[u] = p2[i]; }
+    }
+  };
+  int i0 = blockIdx.x * blockDim.x + threadIdx.x;
+  load(i0);   // in flight during the fold of (r.r, r.z)
+  double d2v[2];
+  block_sum2_array(part2, part2 + stride, npart, red, d2v[0], d2v[1]);
   peer_fold<2>(d2v, pr, pcg_seq(ctl, j, 1));
   const double rr = d2v[0], rz = d2v[1];
   const double absOld = ctl->absNew[j & 1];
@@ -599,17 +644,7 @@ static __global__ void __launch_bounds__(kVecThreads, kPcgVecCtas) pcg_direction
   }
   if (conv) return;
   const double beta = rz / absOld;
-  const int n2 = n >> 1, T = gridDim.x * blockDim.x;
-  double2* __restrict__ p2 = reinterpret_cast<double2*>(p);
-  const double2* __restrict__ r2 = reinterpret_cast<const double2*>(r);
-  const double2* __restrict__ d2 = reinterpret_cast<const double2*>(dinv);
-  for (int i0 = blockIdx.x * blockDim.x + threadIdx.x; i0 < n2; i0 += kVecUnroll * T) {
-    double2 rv[kVecUnroll], pv[kVecUnroll], dv[kVecUnroll];
-#pragma unroll
-    for (int u = 0; u < kVecUnroll; u++) {
-      const int i = i0 + u * T;
-      if (i < n2) { dv[u] = d2[i]; rv[u] = r2[i]; pv[u] = p2[i]; }
-    }
+  while (i0 < n2) {
 #pragma unroll
     for (int u = 0; u < kVecUnroll; u++) {
       const int i = i0 + u * T;
@@ -619,6 +654,8 @@ static __global__ void __launch_bounds__(kVecThreads, kPcgVecCtas) pcg_direction
         p2[i] = pv[u];
       }
     }
+    i0 += kVecUnroll * T;
+    if (i0 < n2) load(i0);
   }
   if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) p[n - 1] = dinv[n - 1] * r[n - 1] + beta * p[n - 1];
 }
