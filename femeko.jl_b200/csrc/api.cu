@@ -219,13 +219,25 @@ static void configure_l2(fk_handle h) {
   cudaDeviceGetAttribute(&max_window, cudaDevAttrMaxAccessPolicyWindowSize, h->device);
   cudaStreamAttrValue attr{};
   if (h->l2_persist && max_persist > 0 && max_window > 0) {
-    const size_t bytes = 5 * h->slab_stride * sizeof(double);   // x r p Ap dinv (not the Picard staging vector)
-    const size_t win = std::min(bytes, (size_t)max_window);
-    const size_t persist = std::min(win, (size_t)max_persist);
+    // x r p Ap dinv (not the Picard staging vector).  When the five vectors exceed what may persist, pin whole
+    // vectors only, always including p (the SpMV's gather source): [r p Ap dinv], [r p Ap], [p Ap], [p] -- a
+    // partially persisting window (hit ratio < 1) turns the rest of the vectors into evict-first lines and
+    // was measured far slower than no window at 20 M tets (profiles/r03r_*).
+    const size_t vec = h->slab_stride * sizeof(double), cap = std::min((size_t)max_persist, (size_t)max_window);
+    int first = 0, count = 5;
+    if (5 * vec > cap) {
+      const int opts[4][2] = {{1, 4}, {1, 3}, {2, 2}, {2, 1}};
+      count = 0;
+      for (const auto& o : opts)
+        if ((size_t)o[1] * vec <= cap) { first = o[0]; count = o[1]; break; }
+    }
+    if (count == 0) { cudaGetLastError(); return; }   // not even one vector fits: leave the cache alone
+    const size_t win = (size_t)count * vec;
+    const size_t persist = win;
     if (cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, persist) != cudaSuccess) { cudaGetLastError(); return; }
-    attr.accessPolicyWindow.base_ptr = h->pcg_slab.ptr;
+    attr.accessPolicyWindow.base_ptr = h->pcg_slab.ptr + (size_t)first * h->slab_stride;
     attr.accessPolicyWindow.num_bytes = win;
-    attr.accessPolicyWindow.hitRatio = (float)std::min(1.0, (double)persist / (double)win);
+    attr.accessPolicyWindow.hitRatio = 1.0f;
     attr.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
     attr.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
     h->l2_window_set = true;
