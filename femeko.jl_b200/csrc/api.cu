@@ -2,6 +2,7 @@
 // floating-point operation of the hot path runs in the kernels of kernels.cuh on the GPU; there is
 // no CPU fallback (fk_create fails when no CUDA device is present).
 #include <algorithm>
+#include <atomic>
 #include <cfloat>
 #include <cmath>
 #include <cstdio>
@@ -135,7 +136,7 @@ static void ensure_state(fk_handle h) {
   h->matid.ensure((size_t)h->nt);
   h->tile_max.ensure((size_t)std::max(1, 4 * h->num_sms));   // per-CTA maxima of material_update_kernel
   h->errflag.ensure(1);
-  h->scal.ensure(8);
+  h->scal.ensure(16);
   const int g = std::min(cdiv(h->nt, 256), 65535);
   fill_kernel<<<g, 256, 0, h->stream>>>(h->mu.ptr, 4e-7 * 3.14159265358979323846, h->nt);  // mu0 (magneticField.jl:38)
   FK_CUDA(cudaMemsetAsync(h->dmu.ptr, 0, sizeof(double) * (size_t)h->nt, h->stream));
@@ -187,6 +188,16 @@ void launch_spmv(fk_handle h, cudaStream_t s, const double* vals, const double* 
   launch_spmv_list(h, s, vals, x, y, dot, ctl, j, ra, nullptr, h->sym.nslices, h->grid_spmv, h->part.ptr);
 }
 
+// every cached PCG chunk graph bakes in launch shapes, the L2 window and (on partitions) peer pointers: drop them
+// whenever any of those changes
+void invalidate_graphs(fk_handle h) {
+  for (int s = 0; s < FK_NUM_SLOTS; s++)
+    for (int r = 0; r < 2; r++)
+      if (h->graph[s][r]) { cudaGraphExecDestroy(h->graph[s][r]); h->graph[s][r] = nullptr; }
+}
+
+static size_t part_words(fk_handle h) { return (size_t)8 * std::max(std::max(h->grid_spmv, h->grid_vec), h->grid_pcg) + 16; }
+
 // launch geometry of the persistent SpMV: full residency, fixed per handle (deterministic p.Ap)
 static void configure_spmv(fk_handle h, int ctas_per_sm) {
   int occ = 1;
@@ -202,54 +213,69 @@ static void configure_spmv(fk_handle h, int ctas_per_sm) {
   // rows) is scheduled beside them instead of behind a full persistent grid
   h->grid_spmv_int = std::max(1, std::min((h->n_slices_int + wpb - 1) / wpb, h->num_sms * std::max(1, occ - h->spmv_int_reserve)));
   h->grid_spmv_bnd = std::max(1, std::min((h->n_slices_bnd + wpb - 1) / wpb, h->num_sms * occ));
-  for (int s = 0; s < FK_NUM_SLOTS; s++)
-    if (h->graph[s]) { cudaGraphExecDestroy(h->graph[s]); h->graph[s] = nullptr; }
-  if (h->part.ptr) h->part.ensure((size_t)4 * std::max(h->grid_spmv, h->grid_vec) + 16);
+  invalidate_graphs(h);
+  if (h->part.ptr) h->part.ensure(part_words(h));
 }
 
-// B200 has 126 MB of L2: the five PCG vectors of a 10 M-tet problem (69 MB) fit, the matrix stream
-// (307 MB per product) does not.  Pin the vector slab in L2 (persisting access-policy window) and let
-// everything else -- the matrix is read with evict-first loads anyway -- stream past it, so the vector
-// kernels and the x gather / y write of the SpMV run at L2 speed instead of HBM speed.
-static void configure_l2(fk_handle h) {
+// B200 has 126 MB of L2: the PCG vectors of a 10 M-tet problem (14 MB each) fit, the matrix stream (307 MB per
+// product) does not.  Pin the vectors an iteration streams in L2 (persisting access-policy window) and let everything
+// else -- the matrix is read with evict-first loads anyway -- stream past them, so the vector kernels and the x gather /
+// y write of the SpMV run at L2 speed instead of HBM speed.  Slab order: x | r | p | Ap | dinv | s | z | u.
+//   recurrence 0 (Eigen):            x r p Ap dinv; when they exceed what may persist, whole vectors only, always p
+//   recurrence 1 (single reduction): (x) r p Ap dinv s z; shrinking windows always end at z (the SpMV's gather source)
+// A partially persisting window (hit ratio < 1) turns the rest of the vectors into evict-first lines and was measured
+// far slower than no window at 20 M tets (profiles/r03r_*).
+static std::atomic<int> g_l2_users{0};
+static void configure_l2(fk_handle h, int recurrence) {
+  const bool was_set = h->l2_window_set;
   h->l2_window_set = false;
+  h->l2_recurrence = recurrence;
   if (!h->pcg_slab.ptr) return;
   int max_persist = 0, max_window = 0;
   cudaDeviceGetAttribute(&max_persist, cudaDevAttrMaxPersistingL2CacheSize, h->device);
   cudaDeviceGetAttribute(&max_window, cudaDevAttrMaxAccessPolicyWindowSize, h->device);
   cudaStreamAttrValue attr{};
+  attr.accessPolicyWindow.num_bytes = 0;  // disables the window
+  attr.accessPolicyWindow.hitProp = cudaAccessPropertyNormal;
+  attr.accessPolicyWindow.missProp = cudaAccessPropertyNormal;
   if (h->l2_persist && max_persist > 0 && max_window > 0) {
-    // x r p Ap dinv (not the Picard staging vector).  When the five vectors exceed what may persist, pin whole
-    // vectors only, always including p (the SpMV's gather source): [r p Ap dinv], [r p Ap], [p Ap], [p] -- a
-    // partially persisting window (hit ratio < 1) turns the rest of the vectors into evict-first lines and
-    // was measured far slower than no window at 20 M tets (profiles/r03r_*).
     const size_t vec = h->slab_stride * sizeof(double), cap = std::min((size_t)max_persist, (size_t)max_window);
-    int first = 0, count = 5;
-    if (5 * vec > cap) {
-      const int opts[4][2] = {{1, 4}, {1, 3}, {2, 2}, {2, 1}};
-      count = 0;
+    int first = 0, count = 0;
+    if (recurrence == 0) {
+      const int opts[5][2] = {{0, 5}, {1, 4}, {1, 3}, {2, 2}, {2, 1}};
       for (const auto& o : opts)
         if ((size_t)o[1] * vec <= cap) { first = o[0]; count = o[1]; break; }
+    } else {
+      for (int c = 7; c >= 1 && count == 0; c--)
+        if ((size_t)c * vec <= cap) { first = 7 - c; count = c; }
     }
-    if (count == 0) { cudaGetLastError(); return; }   // not even one vector fits: leave the cache alone
-    const size_t win = (size_t)count * vec;
-    const size_t persist = win;
-    if (cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, persist) != cudaSuccess) { cudaGetLastError(); return; }
-    attr.accessPolicyWindow.base_ptr = h->pcg_slab.ptr + (size_t)first * h->slab_stride;
-    attr.accessPolicyWindow.num_bytes = win;
-    attr.accessPolicyWindow.hitRatio = 1.0f;
-    attr.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
-    attr.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
-    h->l2_window_set = true;
-  } else {
-    attr.accessPolicyWindow.num_bytes = 0;  // disables the window
-    attr.accessPolicyWindow.hitProp = cudaAccessPropertyNormal;
-    attr.accessPolicyWindow.missProp = cudaAccessPropertyNormal;
+    if (count > 0) {
+      const size_t win = (size_t)count * vec;
+      if (!h->l2_limit_changed) {   // remember the application's limit: fk_destroy puts it back
+        size_t cur = 0;
+        if (cudaDeviceGetLimit(&cur, cudaLimitPersistingL2CacheSize) == cudaSuccess) h->l2_limit_saved = cur;
+      }
+      size_t cur = 0;
+      cudaDeviceGetLimit(&cur, cudaLimitPersistingL2CacheSize);
+      if (cur >= win || cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, win) == cudaSuccess) {   // only ever raise it
+        if (cur < win) h->l2_limit_changed = true;
+        attr.accessPolicyWindow.base_ptr = h->pcg_slab.ptr + (size_t)first * h->slab_stride;
+        attr.accessPolicyWindow.num_bytes = win;
+        attr.accessPolicyWindow.hitRatio = 1.0f;
+        attr.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+        attr.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+        h->l2_window_set = true;
+      } else {
+        cudaGetLastError();
+      }
+    }
   }
+  if (h->l2_window_set && !was_set) g_l2_users++;
+  if (!h->l2_window_set && was_set) g_l2_users--;
   h->l2_window = attr.accessPolicyWindow;
   if (h->stream && cudaStreamSetAttribute(h->stream, cudaStreamAttributeAccessPolicyWindow, &attr) != cudaSuccess) cudaGetLastError();
-  for (int s = 0; s < FK_NUM_SLOTS; s++)
-    if (h->graph[s]) { cudaGraphExecDestroy(h->graph[s]); h->graph[s] = nullptr; }
+  if (h->halo_stream && cudaStreamSetAttribute(h->halo_stream, cudaStreamAttributeAccessPolicyWindow, &attr) != cudaSuccess) cudaGetLastError();
+  invalidate_graphs(h);
 }
 
 void ensure_pcg(fk_handle h) {
@@ -257,21 +283,23 @@ void ensure_pcg(fk_handle h) {
   const size_t nvec = (size_t)h->nv;  // vectors carry halo rows too (SpMV input)
   const size_t stride = (nvec + 31) & ~(size_t)31;
   h->slab_stride = stride;
-  h->pcg_slab.ensure(6 * stride + kCtrlWords);   // + the control block of the peer-memory path (comm.cu)
+  h->pcg_slab.ensure(kSlabVecs * stride + kCtrlWords);   // + the control block of the peer-memory path (comm.cu)
   h->x.ptr = h->pcg_slab.ptr;
   h->r.ptr = h->x.ptr + stride;
   h->p.ptr = h->r.ptr + stride;
   h->Ap.ptr = h->p.ptr + stride;
   h->dinv.ptr = h->Ap.ptr + stride;
-  h->u.ptr = h->dinv.ptr + stride;
-  configure_l2(h);
+  h->s.ptr = h->dinv.ptr + stride;
+  h->z.ptr = h->s.ptr + stride;
+  h->u.ptr = h->z.ptr + stride;
+  configure_l2(h, 0);
   h->bvec.ensure(nvec);
-  h->part.ensure((size_t)4 * std::max(h->grid_spmv, h->grid_vec) + 16);
+  h->part.ensure(part_words(h));
   h->ctl.ensure(1);
-  h->scal.ensure(8);
+  h->scal.ensure(16);
   h->tickets.ensure(8);
   FK_CUDA(cudaMemsetAsync(h->tickets.ptr, 0, 8 * sizeof(unsigned int), h->stream));
-  FK_CUDA(cudaMemsetAsync(h->pcg_slab.ptr, 0, (6 * stride + kCtrlWords) * sizeof(double), h->stream));
+  FK_CUDA(cudaMemsetAsync(h->pcg_slab.ptr, 0, (kSlabVecs * stride + kCtrlWords) * sizeof(double), h->stream));
   if (!h->ctl_host) FK_CUDA(cudaMallocHost((void**)&h->ctl_host, sizeof(PcgCtl)));
 }
 
@@ -327,19 +355,65 @@ static void issue_iteration(fk_handle h, cudaStream_t s, const double* vals, int
   FK_CUDA(cudaGetLastError());
 }
 
-static void build_graph(fk_handle h, int slot, int chunk) {
-  if (h->graph[slot] && h->graph_chunk[slot] == chunk) return;
-  if (h->graph[slot]) {
-    cudaGraphExecDestroy(h->graph[slot]);
-    h->graph[slot] = nullptr;
+// Partial-sum layout of the single-reduction recurrence inside h->part (M = stride = max grid): delta partials of the
+// SpMV at [0, M), buffer A = (gamma | r.r | b.b) at [M, 4M), buffer B = (gamma | r.r) at [4M, 6M).
+struct CgParts {
+  int M;
+  double *ps, *A, *B;
+};
+static CgParts cg_parts(fk_handle h) {
+  const int M = std::max(std::max(h->grid_spmv, h->grid_vec), h->grid_pcg);
+  return CgParts{M, h->part.ptr, h->part.ptr + M, h->part.ptr + 4 * (size_t)M};
+}
+
+// S kernel of the single-reduction recurrence: w = A z fused with (w, z); on a partition also the halo exchange of z.
+// jS: iteration index the kernel's activity test and exchange sequence number are derived from.
+static void launch_cg_spmv(fk_handle h, cudaStream_t s, const double* vals, const PcgCtl* ctl, int jS) {
+  const CgParts cp = cg_parts(h);
+  if (h->comm) {
+    const HaloFused hf = comm_halo_fused(h, h->z.ptr, h->tickets.ptr + 4);
+    const int4* meta = reinterpret_cast<const int4*>(h->slice_meta.ptr);
+    spmv_variant_dispatch(h->spmv_variant, [&](auto G, auto MINB) {
+      spmv_sell_fused_kernel<G(), MINB()><<<h->grid_spmv, kSpmvThreads, 0, s>>>(meta, h->srow.ptr, h->sell_colz.ptr, vals, h->z.ptr,
+                                                                                h->Ap.ptr, h->sym.nslices, cp.ps, ctl, jS,
+                                                                                h->slices_all.ptr, hf);
+    });
+    FK_CUDA(cudaGetLastError());
+  } else {
+    launch_spmv(h, s, vals, h->z.ptr, h->Ap.ptr, true, ctl, jS);
+  }
+}
+
+// One iteration of the single-reduction recurrence (kernels.cuh: cg_update_kernel): V_j then S_j.
+static void issue_iteration_cg(fk_handle h, cudaStream_t s, const double* vals, int j) {
+  const CgParts cp = cg_parts(h);
+  const PeerRed pr = h->comm ? comm_peer_red(h) : PeerRed{0, 1, nullptr, nullptr};
+  cg_update_kernel<<<h->grid_pcg, kVecThreads, 0, s>>>(h->x.ptr, h->r.ptr, h->p.ptr, h->s.ptr, h->Ap.ptr, h->dinv.ptr, h->z.ptr, h->n_rows,
+                                                       cp.A, cp.B, h->grid_pcg, cp.M, cp.ps, h->grid_spmv, h->ctl.ptr, j, pr);
+  launch_cg_spmv(h, s, vals, h->ctl.ptr, j + 1);
+  FK_CUDA(cudaGetLastError());
+}
+
+static void build_graph(fk_handle h, int slot, int chunk, int rec) {
+  if (h->graph[slot][rec] && h->graph_chunk[slot][rec] == chunk) return;
+  if (h->graph[slot][rec]) {
+    cudaGraphExecDestroy(h->graph[slot][rec]);
+    h->graph[slot][rec] = nullptr;
   }
   if (!h->cap_stream) FK_CUDA(cudaStreamCreateWithFlags(&h->cap_stream, cudaStreamNonBlocking));
   cudaGraph_t g = nullptr;
   const long long launches0 = h->launches;   // capturing is not launching
   FK_CUDA(cudaStreamBeginCapture(h->cap_stream, cudaStreamCaptureModeThreadLocal));
   try {
-    for (int j = 0; j < chunk; j++) issue_iteration(h, h->cap_stream, h->vals[slot].ptr, j);
-    pcg_advance_kernel<<<1, 1, 0, h->cap_stream>>>(h->ctl.ptr, chunk);
+    if (rec == 0) {
+      for (int j = 0; j < chunk; j++) issue_iteration(h, h->cap_stream, h->vals[slot].ptr, j);
+      pcg_advance_kernel<<<1, 1, 0, h->cap_stream>>>(h->ctl.ptr, chunk);
+    } else {
+      for (int j = 0; j < chunk; j++) issue_iteration_cg(h, h->cap_stream, h->vals[slot].ptr, j);
+      const CgParts cp = cg_parts(h);
+      cg_chunk_end_kernel<<<1, 256, 0, h->cap_stream>>>(cp.A, cp.B, h->grid_pcg, cp.M, h->ctl.ptr, chunk,
+                                                        h->comm ? comm_peer_red(h) : PeerRed{0, 1, nullptr, nullptr});
+    }
   } catch (...) {
     cudaStreamEndCapture(h->cap_stream, &g);
     if (g) cudaGraphDestroy(g);
@@ -360,10 +434,19 @@ static void build_graph(fk_handle h, int slot, int chunk) {
         if (cudaGraphKernelNodeSetAttribute(nd, cudaLaunchAttributeAccessPolicyWindow, &val) != cudaSuccess) cudaGetLastError();
     }
   }
-  cudaError_t e = cudaGraphInstantiate(&h->graph[slot], g, 0);
+  cudaError_t e = cudaGraphInstantiate(&h->graph[slot][rec], g, 0);
   cudaGraphDestroy(g);
   FK_CUDA(e);
-  h->graph_chunk[slot] = chunk;
+  h->graph_chunk[slot][rec] = chunk;
+}
+
+// sums (a | a.w, w) -> out[0..1] over every rank (w == nullptr: ones)
+static void ns_sums(fk_handle h, cudaStream_t s, const double* a, const double* w, int mode, double* out) {
+  const int g = h->grid_vec;
+  ns_partials_kernel<<<g, kVecThreads, 0, s>>>(a, w, h->n_rows, mode, h->part.ptr, g);
+  FK_CUDA(cudaGetLastError());
+  h->launches++;
+  comm_allreduce_partials(h, s, h->part.ptr, g, g, 2, 0, out, nullptr, 0);
 }
 
 static void pcg_dev(fk_handle h, int slot, const double* b_dev, double* x_dev, const fk_pcg_opts* o, int* iters_out,
@@ -376,12 +459,30 @@ static void pcg_dev(fk_handle h, int slot, const double* b_dev, double* x_dev, c
   if (o) opt = *o;
   // tol_disable: tol = 0 -> threshold = DBL_MIN, never undercut by a non-zero residual
   const double tol = opt.tol_disable ? 0.0 : (opt.tol > 0 ? opt.tol : DBL_EPSILON);
-  const int max_iter = opt.max_iter > 0 ? opt.max_iter : 2 * n;
+  // Eigen's default 2n (IterativeSolverBase.h:251) counts the rows of the WHOLE system: on a partition every rank
+  // must use the same limit, or the ranks fall out of step in the exchanges
+  const long long n_glob = h->comm ? comm_global_rows(h) : (long long)n;
+  const int max_iter = opt.max_iter > 0 ? opt.max_iter : (int)std::min<long long>(2 * n_glob, 0x7fffffff);
   int chunk = opt.check_every > 0 ? opt.check_every : 32;
   chunk = std::min(chunk, std::max(2, max_iter));
   if (chunk & 1) chunk++;  // scalar ping-pong parity must line up across chunks
+  // single-reduction recurrence: one GPU, or partitions on the peer-memory path (the NCCL fallback keeps Eigen's)
+  const int rec = (opt.recurrence == 1 && (!h->comm || comm_capturable(h))) ? 1 : 0;
+  need(opt.recurrence == 0 || opt.recurrence == 1, "fk_pcg: unknown recurrence");
+  if (rec != h->l2_recurrence) configure_l2(h, rec);
   cudaStream_t s = h->stream;
   const int gv = h->grid_vec;
+
+  // singular Neumann systems: b <- b - (sum b / sum w) w (fk_pcg_opts.project_nullspace)
+  const double* w_ns = (h->ns_user && h->ns_w.ptr) ? h->ns_w.ptr : nullptr;
+  if (opt.project_nullspace) {
+    h->bproj.ensure((size_t)h->nv);
+    ns_sums(h, s, b_dev, w_ns, 0, h->scal.ptr + 8);
+    ns_apply_kernel<<<gv, kVecThreads, 0, s>>>(b_dev, w_ns, n, 0, h->scal.ptr + 8, h->bproj.ptr);
+    FK_CUDA(cudaGetLastError());
+    h->launches++;
+    b_dev = h->bproj.ptr;
+  }
 
   jacobi_kernel<<<cdiv(n, 256), 256, 0, s>>>(h->vals[slot].ptr, h->sell_diag.ptr, n, opt.no_precond, h->dinv.ptr);
   const double* Ax0 = nullptr;
@@ -394,19 +495,32 @@ static void pcg_dev(fk_handle h, int slot, const double* b_dev, double* x_dev, c
   } else {
     FK_CUDA(cudaMemsetAsync(h->x.ptr, 0, sizeof(double) * (size_t)n, s));
   }
-  if (h->comm) {
+  const unsigned long long epoch = ++h->pcg_epoch;
+  if (rec == 1) {
+    const CgParts cp = cg_parts(h);
+    const int g2 = h->grid_pcg;
+    cg_init_kernel<<<g2, kVecThreads, 0, s>>>(b_dev, Ax0, h->dinv.ptr, n, h->r.ptr, h->z.ptr, cp.A, cp.M);   // partials of (r.z, r.r, b.b)
+    if (h->comm) {
+      comm_allreduce_partials(h, s, cp.A, g2, cp.M, 3, 0, h->scal.ptr + 4, nullptr, 0);   // -> scal[4..6] over every rank
+      pcg_init_fin_kernel<<<1, 256, 0, s>>>(h->scal.ptr + 6, h->scal.ptr + 5, h->scal.ptr + 4, 1, tol, max_iter, epoch, h->ctl.ptr);
+    } else {
+      pcg_init_fin_kernel<<<1, 256, 0, s>>>(cp.A + 2 * (size_t)cp.M, cp.A + cp.M, cp.A, g2, tol, max_iter, epoch, h->ctl.ptr);
+    }
+    launch_cg_spmv(h, s, h->vals[slot].ptr, h->ctl.ptr, 0);   // w0 = A z0, delta partials (and the first halo exchange)
+    h->launches++;
+  } else if (h->comm) {
     pcg_init_kernel<<<gv, kVecThreads, 0, s>>>(b_dev, Ax0, h->dinv.ptr, n, h->r.ptr, h->p.ptr, h->part.ptr,
                                                comm_red_args(h, h->tickets.ptr + 2, h->scal.ptr + 4, 0));   // -> scal[4..6] = b.b, r.r, r.p
     comm_nccl_allreduce(h, s, h->scal.ptr + 4, 3, 0);
-    pcg_init_fin_kernel<<<1, 256, 0, s>>>(h->scal.ptr + 4, 1, 1, tol, max_iter, ++h->pcg_epoch, h->ctl.ptr);
+    pcg_init_fin_kernel<<<1, 256, 0, s>>>(h->scal.ptr + 4, h->scal.ptr + 5, h->scal.ptr + 6, 1, tol, max_iter, epoch, h->ctl.ptr);
   } else {
     pcg_init_kernel<<<gv, kVecThreads, 0, s>>>(b_dev, Ax0, h->dinv.ptr, n, h->r.ptr, h->p.ptr, h->part.ptr, RedArgs{});
-    pcg_init_fin_kernel<<<1, 256, 0, s>>>(h->part.ptr, gv, gv, tol, max_iter, ++h->pcg_epoch, h->ctl.ptr);
+    pcg_init_fin_kernel<<<1, 256, 0, s>>>(h->part.ptr, h->part.ptr + gv, h->part.ptr + 2 * (size_t)gv, gv, tol, max_iter, epoch, h->ctl.ptr);
   }
   FK_CUDA(cudaGetLastError());
   h->launches += 3;
 
-  if (h->comm && comm_capturable(h) && !h->halo_stream) {   // second stream of the split SpMV (created outside any capture)
+  if (rec == 0 && h->comm && comm_capturable(h) && !h->halo_stream) {   // second stream of the split SpMV (created outside any capture)
     FK_CUDA(cudaStreamCreateWithFlags(&h->halo_stream, cudaStreamNonBlocking));
     FK_CUDA(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
     FK_CUDA(cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming));
@@ -417,7 +531,7 @@ static void pcg_dev(fk_handle h, int slot, const double* b_dev, double* x_dev, c
     }
   }
   const bool graphed = !h->comm || comm_capturable(h);
-  if (graphed) build_graph(h, slot, chunk);
+  if (graphed) build_graph(h, slot, chunk, rec);
   int launched = 0;
   while (true) {
     if (!graphed) {
@@ -425,20 +539,26 @@ static void pcg_dev(fk_handle h, int slot, const double* b_dev, double* x_dev, c
       pcg_advance_kernel<<<1, 1, 0, s>>>(h->ctl.ptr, chunk);
       h->launches += (long long)chunk * 3 + 1;   // the halo pack kernel is counted in comm_halo_exchange
     } else {
-      FK_CUDA(cudaGraphLaunch(h->graph[slot], s));
+      FK_CUDA(cudaGraphLaunch(h->graph[slot][rec], s));
       const bool split = h->comm && h->halo_stream && h->overlap_halo && h->n_slices_bnd > 0 && h->n_slices_int > 0;
-      h->launches += (long long)chunk * (h->comm ? (split ? 6 : 5) : 3) + 1;
+      h->launches += rec == 1 ? (long long)chunk * 2 + 1 : (long long)chunk * (h->comm ? (split ? 6 : 5) : 3) + 1;
     }
     launched += chunk;
     FK_CUDA(cudaMemcpyAsync(h->ctl_host, h->ctl.ptr, sizeof(PcgCtl), cudaMemcpyDeviceToHost, s));
     FK_CUDA(cudaStreamSynchronize(s));
     if (h->ctl_host->done || launched >= max_iter) break;
+    if (!(h->ctl_host->r2 == h->ctl_host->r2)) break;   // NaN residual (e.g. non-finite matrix values): it would never pass the test
   }
   if (h->comm) comm_check(h);
   const PcgCtl& c = *h->ctl_host;
   const int iters = c.done ? c.iters : max_iter;
   if (c.rhs2 == 0.0) {  // x = 0 (ConjugateGradient.h:43-49)
     FK_CUDA(cudaMemsetAsync(x_dev, 0, sizeof(double) * (size_t)n, s));
+  } else if (opt.project_nullspace) {   // x <- x - (w.x / sum w)
+    ns_sums(h, s, h->x.ptr, w_ns, 1, h->scal.ptr + 8);
+    ns_apply_kernel<<<gv, kVecThreads, 0, s>>>(h->x.ptr, nullptr, n, 1, h->scal.ptr + 8, x_dev);
+    FK_CUDA(cudaGetLastError());
+    h->launches++;
   } else {
     FK_CUDA(cudaMemcpyAsync(x_dev, h->x.ptr, sizeof(double) * (size_t)n, cudaMemcpyDeviceToDevice, s));
   }
@@ -576,8 +696,12 @@ int fk_create(const double* p, const int* t, int nv, int nt, const double* VE, c
       }
       h->n_slices_int = (int)li.size();
       h->n_slices_bnd = (int)lb.size();
+      std::vector<int> la(li);
+      la.insert(la.end(), lb.begin(), lb.end());
       h->slices_int.upload(li, s);
       h->slices_bnd.upload(lb, s);
+      h->slices_all.upload(la, s);
+      FK_CUDA(cudaStreamSynchronize(s));
     }
     h->sell_colz.ensure(S.sell_colz.size() + 2 * kSlack);
     h->sell_colz.upload(S.sell_colz, s);
@@ -620,8 +744,7 @@ int fk_destroy(fk_handle h) {
     if (!h) return 0;
     DeviceGuard dg(h->device);
     cudaDeviceSynchronize();
-    for (int s = 0; s < FK_NUM_SLOTS; s++)
-      if (h->graph[s]) cudaGraphExecDestroy(h->graph[s]);
+    invalidate_graphs(h);
     if (h->cap_stream) cudaStreamDestroy(h->cap_stream);
     if (h->ctl_host) cudaFreeHost(h->ctl_host);
     if (h->pin8) cudaFreeHost(h->pin8);
@@ -630,7 +753,10 @@ int fk_destroy(fk_handle h) {
     if (h->halo_stream) cudaStreamDestroy(h->halo_stream);
     if (h->copy_ev) cudaEventDestroy(h->copy_ev);
     if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
-    if (h->l2_window_set) cudaCtxResetPersistingL2Cache();
+    // leave the device as the host application had it: the persisting lines are released when the last handle with a
+    // window goes away, and the persisting-L2 limit this handle raised is put back
+    if (h->l2_window_set && --g_l2_users <= 0) { cudaCtxResetPersistingL2Cache(); g_l2_users = 0; }
+    if (h->l2_limit_changed && g_l2_users <= 0) cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, h->l2_limit_saved);
     comm_destroy(h);
     delete h;
     return 0;
@@ -642,7 +768,7 @@ int fk_set_stream(fk_handle h, void* stream) {
     need(h, "fk: NULL handle");
     DeviceGuard dg(h->device);
     h->stream = (cudaStream_t)stream;
-    configure_l2(h);
+    configure_l2(h, h->l2_recurrence);
     return 0;
   });
 }
@@ -665,7 +791,7 @@ int fk_tune(fk_handle h, int what, int value) {
         break;
       }
       case 1: h->spmv_ctas = value; configure_spmv(h, value); break;
-      case 2: h->l2_persist = value != 0; configure_l2(h); break;
+      case 2: h->l2_persist = value != 0; configure_l2(h, h->l2_recurrence); break;
       case 3: h->asm_dbg = value; break;   // profiling experiments: skip assembly phases (results are garbage)
       case 4:
         need(value >= 0 && value < kNumSpmvVariants, "fk_tune: spmv variant out of range");
@@ -674,8 +800,7 @@ int fk_tune(fk_handle h, int what, int value) {
         break;
       case 7:   // single GPU: programmatic dependent launch between the kernels of a PCG iteration (1 = on; default off)
         h->pdl = value != 0;
-        for (int sl = 0; sl < FK_NUM_SLOTS; sl++)
-          if (h->graph[sl]) { cudaGraphExecDestroy(h->graph[sl]); h->graph[sl] = nullptr; }
+        invalidate_graphs(h);
         break;
       case 6:
         need(value >= 0 && value < 8, "fk_tune: reserve out of range");
@@ -684,8 +809,7 @@ int fk_tune(fk_handle h, int what, int value) {
         break;
       case 5:   // partitions: 1 (default) = halo exchange + halo-coupled rows beside the interior rows of the SpMV
         h->overlap_halo = value != 0;
-        for (int sl = 0; sl < FK_NUM_SLOTS; sl++)
-          if (h->graph[sl]) { cudaGraphExecDestroy(h->graph[sl]); h->graph[sl] = nullptr; }
+        invalidate_graphs(h);
         break;
       default: throw std::runtime_error("fk_tune: unknown option");
     }
@@ -1213,7 +1337,8 @@ int fk_set_material(fk_handle h, const unsigned char* matid) {
     ensure_state(h);
     FK_CUDA(cudaMemcpyAsync(h->matid.ptr, matid, (size_t)h->nt, cudaMemcpyHostToDevice, h->stream));
     std::vector<int> list;
-    for (int k = 0; k < h->nt; k++) if (matid[k] > 0) list.push_back(k);
+    h->mat_used = 0;
+    for (int k = 0; k < h->nt; k++) if (matid[k] > 0) { list.push_back(k); h->mat_used |= 1u << (matid[k] - 1); }
     h->n_mat = (int)list.size();
     if (h->n_mat > 0) h->mat_list.upload(list, h->stream);
     FK_CUDA(cudaStreamSynchronize(h->stream));
@@ -1229,6 +1354,7 @@ int fk_set_inside(fk_handle h, const int* ids, int n) {
     ensure_state(h);
     FK_CUDA(cudaMemsetAsync(h->matid.ptr, 0, (size_t)h->nt, h->stream));
     h->n_mat = n;
+    h->mat_used = n > 0 ? 1u : 0u;
     if (n > 0) {
       h->mat_list.upload(ids, (size_t)n, h->stream);
       set_material_kernel<<<cdiv(n, 256), 256, 0, h->stream>>>(h->matid.ptr, h->mat_list.ptr, n);
@@ -1284,7 +1410,24 @@ int fk_get_field(fk_handle h, double* Hfield_out, double* Hnorm_out) {
   });
 }
 
-static int picard_step_dev(fk_handle h, int slot, const double* u_dev, int compat_bug, double* div_out) {
+// scalars of the last enqueued sweep -> host (one 128-byte copy + one synchronisation); status as fk_picard_step
+static int picard_collect(fk_handle h, double* div_out) {
+  if (!h->pin8) FK_CUDA(cudaMallocHost((void**)&h->pin8, 16 * sizeof(double)));
+  FK_CUDA(cudaMemcpyAsync(h->pin8, h->scal.ptr, 8 * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+  FK_CUDA(cudaStreamSynchronize(h->stream));
+  h->picard_pending = false;
+  if (h->comm) comm_check(h);
+  const double dmax = h->pin8[0];
+  int err = 0;
+  std::memcpy(&err, h->pin8 + 7, sizeof(int));
+  if (div_out) *div_out = (4e-7 * 3.14159265358979323846) * dmax;   // mu0*max|H - Hold| (NewtonRaphson.jl:200)
+  if (err & 1) { set_error("fk_picard_step: |H| outside the spline's knot range with bc = error"); return 2; }
+  if (err & 2) { set_error("fk_picard_step: Nans/Infs in mu"); return 3; }   // NewtonRaphson.jl:210-212
+  return 0;
+}
+
+// sync = false: only enqueue (the scalars stay on the device until picard_collect)
+static int picard_step_dev(fk_handle h, int slot, const double* u_dev, int compat_bug, double* div_out, bool sync = true) {
   ensure_state(h);
   AsmArgs a = base_args(h, slot_vals(h, slot));
   a.u = u_dev;
@@ -1304,6 +1447,9 @@ static int picard_step_dev(fk_handle h, int slot, const double* u_dev, int compa
   // 1. material elements: mu(|H|), dmu/dH from the spline and the convergence metric (per-CTA maxima)
   int npart = 1;
   if (h->have_material && h->n_mat > 0) {
+    // every material id in use needs its table (a missing one would dereference NULL on the device)
+    for (int m = 0; m < FK_MAX_SPLINES / 2; m++)
+      need(!(h->mat_used & (1u << m)) || h->spl.s[m].n > 0, "fk_picard_step: a material id in use has no spline (fk_set_spline)");
     npart = std::min(cdiv(h->n_mat, 256), 4 * h->num_sms);
     h->tile_max.ensure((size_t)npart);
     material_update_kernel<<<npart, 256, 0, h->stream>>>(h->p4.ptr, h->t4.ptr, h->mat_list.ptr, h->n_mat,
@@ -1318,22 +1464,23 @@ static int picard_step_dev(fk_handle h, int slot, const double* u_dev, int compa
   launch_assemble<ASM_PICARD>(h, a);
   // div = mu0 * max over every rank's material elements (NewtonRaphson.jl:200)
   comm_allreduce_partials(h, h->stream, h->tile_max.ptr, npart, npart, 1, 1, h->scal.ptr, nullptr, 0);
-  if (!h->pin8) FK_CUDA(cudaMallocHost((void**)&h->pin8, 8 * sizeof(double)));
-  FK_CUDA(cudaMemcpyAsync(h->pin8, h->scal.ptr, 8 * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
-  FK_CUDA(cudaStreamSynchronize(h->stream));
-  const double dmax = h->pin8[0];
-  int err = 0;
-  std::memcpy(&err, h->pin8 + 7, sizeof(int));
-  if (div_out) *div_out = (4e-7 * 3.14159265358979323846) * dmax;   // mu0*max|H - Hold| (NewtonRaphson.jl:200)
-  if (err & 1) { set_error("fk_picard_step: |H| outside the spline's knot range with bc = error"); return 2; }
-  if (err & 2) { set_error("fk_picard_step: Nans/Infs in mu"); return 3; }   // NewtonRaphson.jl:210-212
-  return 0;
+  h->picard_pending = true;
+  if (!sync) return 0;
+  return picard_collect(h, div_out);
 }
 int fk_picard_step_dev(fk_handle h, int slot, const double* u_dev, int compat_bug, double* div_out) {
   return guard([&]() {
     need(h && u_dev, "fk: NULL argument");
     DeviceGuard dg(h->device);
-    return picard_step_dev(h, slot, u_dev, compat_bug, div_out);
+    return picard_step_dev(h, slot, u_dev, compat_bug, div_out, div_out != nullptr);
+  });
+}
+int fk_picard_result(fk_handle h, double* div_out) {
+  return guard([&]() {
+    need(h, "fk: NULL handle");
+    DeviceGuard dg(h->device);
+    need(h->scal.ptr != nullptr, "fk_picard_result: no sweep has been run");
+    return picard_collect(h, div_out);
   });
 }
 int fk_picard_step(fk_handle h, int slot, const double* u, int compat_bug, double* div_out) {
@@ -1343,6 +1490,80 @@ int fk_picard_step(fk_handle h, int slot, const double* u, int compat_bug, doubl
     ensure_pcg(h);
     FK_CUDA(cudaMemcpyAsync(h->u.ptr, u, sizeof(double) * (size_t)h->nv, cudaMemcpyHostToDevice, h->stream));
     return picard_step_dev(h, slot, h->u.ptr, compat_bug, div_out);
+  });
+}
+
+// ---- constraints ------------------------------------------------------------------------------------
+int fk_set_dirichlet(fk_handle h, const int* fixed_ids, int n_fixed, const double* gD) {
+  return guard([&]() {
+    need(h && (fixed_ids || n_fixed == 0) && n_fixed >= 0, "fk_set_dirichlet: bad argument");
+    for (int i = 0; i < n_fixed; i++) need(fixed_ids[i] >= 0 && fixed_ids[i] < h->nv, "fk_set_dirichlet: DOF id out of range (ids are 0-based)");
+    DeviceGuard dg(h->device);
+    cudaStream_t s = h->stream;
+    h->n_fixed = n_fixed;
+    h->dir_mask.ensure((size_t)h->nv);
+    h->dir_g.ensure((size_t)h->nv);
+    FK_CUDA(cudaMemsetAsync(h->dir_mask.ptr, 0, (size_t)h->nv, s));
+    FK_CUDA(cudaMemsetAsync(h->dir_g.ptr, 0, sizeof(double) * (size_t)h->nv, s));
+    if (n_fixed > 0) {
+      h->dir_ids.upload(fixed_ids, (size_t)n_fixed, s);
+      if (gD) h->dir_val.upload(gD, (size_t)n_fixed, s);
+      scatter_flag_kernel<<<cdiv(n_fixed, 256), 256, 0, s>>>(h->dir_mask.ptr, h->dir_ids.ptr, n_fixed);
+      scatter_kernel<<<cdiv(n_fixed, 256), 256, 0, s>>>(h->dir_g.ptr, h->dir_ids.ptr, gD ? h->dir_val.ptr : nullptr, n_fixed);
+      FK_CUDA(cudaGetLastError());
+      h->launches += 2;
+    }
+    FK_CUDA(cudaStreamSynchronize(s));
+    return 0;
+  });
+}
+static void apply_dirichlet_dev(fk_handle h, int slot, double* b_dev) {
+  check_slot(slot);
+  need(h->vals[slot].ptr != nullptr, "fk_apply_dirichlet: matrix slot has not been assembled");
+  need(h->dir_mask.ptr != nullptr, "fk_apply_dirichlet: call fk_set_dirichlet first");
+  if (h->n_fixed == 0) return;
+  cudaStream_t s = h->stream;
+  if (b_dev) {   // lift with the unconstrained matrix: b[free] -= A[free,fixed] gD, b[fixed] = gD
+    h->st_d.ensure((size_t)h->nv);
+    FK_CUDA(cudaMemsetAsync(h->st_d.ptr, 0, sizeof(double) * (size_t)h->nv, s));
+    launch_spmv(h, s, h->vals[slot].ptr, h->dir_g.ptr, h->st_d.ptr, false, nullptr, 0);
+    dirichlet_lift_kernel<<<cdiv(h->n_rows, 256), 256, 0, s>>>(b_dev, h->st_d.ptr, h->dir_g.ptr, h->dir_mask.ptr, h->n_rows);
+    h->launches += 2;
+  }
+  const int4* meta = reinterpret_cast<const int4*>(h->slice_meta.ptr);
+  dirichlet_mask_kernel<<<cdiv(h->sym.nslices, 8), 256, 0, s>>>(meta, h->srow.ptr, h->sell_colz.ptr, h->sell_diag.ptr, h->dir_mask.ptr,
+                                                               h->sym.nslices, h->n_rows, h->vals[slot].ptr);
+  FK_CUDA(cudaGetLastError());
+  h->launches++;
+}
+int fk_apply_dirichlet_dev(fk_handle h, int slot, double* b_dev) {
+  return guard([&]() {
+    need(h, "fk: NULL handle");
+    DeviceGuard dg(h->device);
+    apply_dirichlet_dev(h, slot, b_dev);
+    return 0;
+  });
+}
+int fk_apply_dirichlet(fk_handle h, int slot, double* b) {
+  return guard([&]() {
+    need(h, "fk: NULL handle");
+    DeviceGuard dg(h->device);
+    if (b) h->st_c.upload(b, (size_t)h->nv, h->stream);
+    apply_dirichlet_dev(h, slot, b ? h->st_c.ptr : nullptr);
+    copy_out(h, h->st_c.ptr, b, (size_t)h->nv);
+    return 0;
+  });
+}
+int fk_set_nullspace(fk_handle h, const double* w) {
+  return guard([&]() {
+    need(h, "fk: NULL handle");
+    DeviceGuard dg(h->device);
+    h->ns_user = w != nullptr;
+    if (w) {
+      h->ns_w.upload(w, (size_t)h->nv, h->stream);
+      FK_CUDA(cudaStreamSynchronize(h->stream));
+    }
+    return 0;
   });
 }
 
@@ -1368,12 +1589,17 @@ int fk_picard_pcg(fk_handle h, int slot, const double* u, int compat_bug, const 
     FK_CUDA(cudaMemcpyAsync(h->bvec.ptr, b, sizeof(double) * n, cudaMemcpyHostToDevice, h->copy_stream));
     if (opts && opts->warm_start) FK_CUDA(cudaMemcpyAsync(h->st_d.ptr, x, sizeof(double) * n, cudaMemcpyHostToDevice, h->copy_stream));
     FK_CUDA(cudaEventRecord(h->copy_ev, h->copy_stream));
-    const int rc = picard_step_dev(h, slot, h->u.ptr, compat_bug, div_out);
+    // the sweep is only enqueued: its scalars (div, error flags) are parked in a second block so the PCG can reuse the
+    // first, and come back with the solve's own synchronisation -- one host round trip less per nonlinear iteration
+    picard_step_dev(h, slot, h->u.ptr, compat_bug, nullptr, false);
+    FK_CUDA(cudaMemcpyAsync(h->scal.ptr + 12, h->scal.ptr, sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+    FK_CUDA(cudaMemcpyAsync(h->scal.ptr + 13, h->scal.ptr + 7, sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
     FK_CUDA(cudaStreamWaitEvent(h->stream, h->copy_ev, 0));
-    if (rc != 0) { FK_CUDA(cudaStreamSynchronize(h->stream)); return rc; }
     pcg_dev(h, slot, h->bvec.ptr, h->st_d.ptr, opts, iters_out, relres_out);
-    copy_out(h, h->st_d.ptr, x, n);
-    return 0;
+    FK_CUDA(cudaMemcpyAsync(h->scal.ptr, h->scal.ptr + 12, sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+    FK_CUDA(cudaMemcpyAsync(h->scal.ptr + 7, h->scal.ptr + 13, sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+    FK_CUDA(cudaMemcpyAsync(x, h->st_d.ptr, sizeof(double) * n, cudaMemcpyDeviceToHost, h->stream));
+    return picard_collect(h, div_out);
   });
 }
 

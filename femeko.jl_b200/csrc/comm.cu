@@ -72,7 +72,7 @@ struct P2P {
   bool opened_slab[kMaxRanks] = {};
   int remote_start[kMaxNeigh] = {};                // where my rows land in neighbour q's vectors
   int remote_slot[kMaxNeigh] = {};                 // my index in neighbour q's neighbour list (its flag slot for me)
-  unsigned long long* ctrl = nullptr;              // my control block: the kCtrlWords words after the 6 slab vectors
+  unsigned long long* ctrl = nullptr;              // my control block: the kCtrlWords words after the kSlabVecs slab vectors
   DevBuf<unsigned long long*> peer_ctrl_dev;       // device copy of peer_ctrl
 };
 
@@ -85,6 +85,7 @@ struct Comm {
   DevBuf<int> send_idx;
   DevBuf<double> sendbuf;
   bool have_halo = false;
+  long long n_global = 0;   // owned rows of all ranks (Eigen's default iteration limit is 2 n of the WHOLE system)
   P2P p2p;
 };
 
@@ -140,6 +141,12 @@ static __global__ void __launch_bounds__(256) allreduce_p2p_kernel(const double*
 
 void comm_destroy(fk_handle_s* h) {
   if (!h->comm) return;
+  cudaDeviceSynchronize();
+  invalidate_graphs(h);   // they hold peer pointers that die with the mappings below
+  if (h->halo_stream) {   // carries the L2 window of the old slab: recreated on demand
+    cudaStreamDestroy(h->halo_stream);
+    h->halo_stream = nullptr;
+  }
   P2P& P = h->comm->p2p;
   for (int r = 0; r < kMaxRanks; r++) {
     if (P.opened_slab[r]) cudaIpcCloseMemHandle(P.peer_slab[r]);
@@ -168,7 +175,7 @@ void comm_halo_exchange(fk_handle_s* h, cudaStream_t s, double* v) {
     P2P& P = c->p2p;
     const size_t off = (size_t)(v - h->pcg_slab.ptr);
     const size_t vec = off / h->slab_stride;           // which slab vector (the stride differs from rank to rank)
-    if (v < h->pcg_slab.ptr || vec >= 6 || off != vec * h->slab_stride)
+    if (v < h->pcg_slab.ptr || vec >= (size_t)kSlabVecs || off != vec * h->slab_stride)
       throw std::runtime_error("fk: halo exchange of a vector outside the PCG slab");
     HaloPushArgs a{};
     a.v = v;
@@ -248,6 +255,33 @@ void comm_nccl_allreduce(fk_handle_s* h, cudaStream_t s, double* v, int n, int o
   FK_NCCL(nccl().AllReduce(v, v, (size_t)n, ncclDouble, op == 0 ? ncclSum : ncclMax, c->comm, s));
 }
 int comm_kind(fk_handle_s* h) { return !h->comm ? 0 : (h->comm->p2p.on ? 2 : 1); }
+long long comm_global_rows(fk_handle_s* h) { return (h->comm && h->comm->n_global > 0) ? h->comm->n_global : (long long)h->n_rows; }
+
+// descriptor of the exchange fused into the SpMV of the single-reduction recurrence (spmv.cuh: spmv_sell_fused_kernel)
+HaloFused comm_halo_fused(fk_handle_s* h, double* v, unsigned int* ticket) {
+  Comm* c = h->comm;
+  if (!c || !c->p2p.on) throw std::runtime_error("fk: fused halo exchange needs the peer-memory path");
+  P2P& P = c->p2p;
+  const size_t off = (size_t)(v - h->pcg_slab.ptr);
+  const size_t vec = off / h->slab_stride;
+  if (v < h->pcg_slab.ptr || vec >= (size_t)kSlabVecs || off != vec * h->slab_stride)
+    throw std::runtime_error("fk: halo exchange of a vector outside the PCG slab");
+  HaloFused a{};
+  a.send_idx = c->send_idx.ptr;
+  a.my_ctrl = P.ctrl;
+  a.ticket = ticket;
+  for (int q = 0; q <= c->nneigh; q++) a.send_ptr[q] = c->send_ptr[q];
+  for (int q = 0; q < c->nneigh; q++) {
+    const int nb = c->neigh_rank[q];
+    a.dst[q] = static_cast<double*>(P.peer_slab[nb]) + vec * P.peer_stride[nb] + P.remote_start[q];
+    a.flag[q] = P.peer_ctrl[nb] + kOffHalo2 + P.remote_slot[q];
+  }
+  a.nneigh = c->nneigh;
+  const int nsend = c->send_ptr[c->nneigh];
+  a.npush = std::max(1, std::min(std::min(32, h->grid_spmv), (nsend + 2 * kSpmvThreads - 1) / (2 * kSpmvThreads)));
+  a.n_int = h->n_slices_int;
+  return a;
+}
 
 }  // namespace fk
 
@@ -281,7 +315,18 @@ int fk_comm_init(fk_handle h, const unsigned char* id128, int rank, int nranks) 
     ncclUniqueId id;
     std::memcpy(&id, id128, 128);
     FK_NCCL(nccl().CommInitRank(&h->comm->comm, nranks, id, rank));
-    h->scal.ensure(8);
+    h->scal.ensure(16);
+    {   // owned rows of the whole system (default max_iter = 2 n must be the same on every rank)
+      long long* d = nullptr;
+      FK_CUDA(cudaMalloc((void**)&d, sizeof(long long)));
+      long long mine = h->n_rows;
+      FK_CUDA(cudaMemcpy(d, &mine, sizeof(mine), cudaMemcpyHostToDevice));
+      FK_NCCL(nccl().AllReduce(d, d, 1, ncclInt64, ncclSum, h->comm->comm, h->stream));
+      FK_CUDA(cudaStreamSynchronize(h->stream));
+      FK_CUDA(cudaMemcpy(&mine, d, sizeof(mine), cudaMemcpyDeviceToHost));
+      cudaFree(d);
+      h->comm->n_global = mine;
+    }
     return 0;
   } catch (const std::exception& e) {
     set_error(e.what());
@@ -318,6 +363,7 @@ int fk_set_halo(fk_handle h, int n_owned, int nneigh, const int* neigh_rank, con
     c->sendbuf.ensure((size_t)std::max(nsend, 1));
     FK_CUDA(cudaStreamSynchronize(h->stream));
     c->have_halo = true;
+    invalidate_graphs(h);
     return 0;
   } catch (const std::exception& e) {
     set_error(e.what());
@@ -335,7 +381,7 @@ int fk_comm_p2p_export(fk_handle h, unsigned char* handles128) {
     FK_CUDA(cudaSetDevice(h->device));
     ensure_pcg(h);
     P2P& P = h->comm->p2p;
-    P.ctrl = reinterpret_cast<unsigned long long*>(h->pcg_slab.ptr + 6 * h->slab_stride);
+    P.ctrl = reinterpret_cast<unsigned long long*>(h->pcg_slab.ptr + (size_t)kSlabVecs * h->slab_stride);
     FK_CUDA(cudaMemset(P.ctrl, 0, kCtrlWords * sizeof(unsigned long long)));
     static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t is expected to be 64 bytes");
     cudaIpcMemHandle_t a;
@@ -378,7 +424,7 @@ int fk_comm_p2p_attach(fk_handle h, const unsigned char* all_handles, const int*
         P.peer_slab[r] = pa;
         P.opened_slab[r] = true;
       }
-      P.peer_ctrl[r] = reinterpret_cast<unsigned long long*>(static_cast<double*>(P.peer_slab[r]) + 6 * P.peer_stride[r]);
+      P.peer_ctrl[r] = reinterpret_cast<unsigned long long*>(static_cast<double*>(P.peer_slab[r]) + (size_t)kSlabVecs * P.peer_stride[r]);
     }
     for (int q = 0; q < c->nneigh; q++) {
       if (remote_start[q] < 0 || remote_slot[q] < 0 || remote_slot[q] >= kMaxNeigh) throw std::runtime_error("fk_comm_p2p_attach: bad remote plan");
@@ -389,6 +435,7 @@ int fk_comm_p2p_attach(fk_handle h, const unsigned char* all_handles, const int*
     P.peer_ctrl_dev.upload(ptrs, h->stream);
     FK_CUDA(cudaStreamSynchronize(h->stream));
     P.on = true;
+    invalidate_graphs(h);
     return 0;
   } catch (const std::exception& e) {
     set_error(e.what());

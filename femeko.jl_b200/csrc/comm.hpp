@@ -25,4 +25,8 @@ void comm_allreduce_partials(fk_handle_s* h, cudaStream_t s, const double* part,
 void comm_check(fk_handle_s* h);   // throws if a peer timed out
 bool comm_capturable(fk_handle_s* h);   // peer-memory path: the whole iteration is kernels -> CUDA-graph capturable
 void ensure_pcg(fk_handle_s* h);   // api.cu: allocates the PCG vector slab
+void invalidate_graphs(fk_handle_s* h);   // api.cu: cached chunk graphs bake in peer pointers and launch shapes
+struct HaloFused;
+HaloFused comm_halo_fused(fk_handle_s* h, double* v, unsigned int* ticket);   // descriptor of the in-kernel exchange (spmv.cuh)
+long long comm_global_rows(fk_handle_s* h);   // rows owned by all ranks together
 }  // namespace fk

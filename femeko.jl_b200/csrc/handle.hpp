@@ -102,13 +102,18 @@ struct fk_handle_s {
   fk::DevBuf<double> spl_t[FK_MAX_SPLINES], spl_c[FK_MAX_SPLINES];
   fk::SplineSet spl{};
   bool have_material = false;
+  unsigned mat_used = 0;               // bit m-1: material id m occurs in matid
   // PCG workspace
-  fk::DevBuf<double> pcg_slab;         // x | r | p | Ap | dinv | u in ONE allocation: one L2 access-policy window covers the first five,
-                                       // and one CUDA-IPC handle exports every vector peers write halo rows into
-  struct VecView { double* ptr = nullptr; } x, r, p, Ap, dinv, u;   // u: potential staged for the Picard sweep (6th slab vector)
+  fk::DevBuf<double> pcg_slab;         // x | r | p | Ap | dinv | s | z | u in ONE allocation (kSlabVecs vectors + control block): one L2
+                                       // access-policy window covers the vectors a recurrence streams every iteration, and one
+                                       // CUDA-IPC handle exports every vector peers write halo rows into
+  struct VecView { double* ptr = nullptr; } x, r, p, Ap, dinv, s, z, u;   // s, z: single-reduction recurrence; u: potential staged for the Picard sweep
   size_t slab_stride = 0;
   bool l2_persist = true, l2_window_set = false;
   cudaAccessPolicyWindow l2_window{};
+  int l2_recurrence = 0;               // which recurrence the current window was laid out for
+  size_t l2_limit_saved = 0;           // the device's persisting-L2 limit before this handle changed it (restored by fk_destroy)
+  bool l2_limit_changed = false;
   fk::DevBuf<double> part, bvec;
   fk::DevBuf<unsigned int> tickets;    // last-CTA tickets of the in-kernel grid reductions (zero between kernels)
   fk::DevBuf<fk::PcgCtl> ctl;
@@ -116,8 +121,18 @@ struct fk_handle_s {
   unsigned long long pcg_epoch = 0;   // solves started on this handle (identical on every rank of a partitioned problem)
   int grid_spmv = 0, grid_vec = 0, grid_pcg = 0;   // grid_pcg: the update / direction kernels of an iteration
   int spmv_variant = 3, spmv_ctas = 0;   // SpMV launch shape (spmv.cuh: spmv_variant_dispatch), cap on CTAs per SM
-  cudaGraphExec_t graph[FK_NUM_SLOTS] = {nullptr, nullptr, nullptr, nullptr};
-  int graph_chunk[FK_NUM_SLOTS] = {0, 0, 0, 0};
+  cudaGraphExec_t graph[FK_NUM_SLOTS][2] = {};   // [slot][recurrence]
+  int graph_chunk[FK_NUM_SLOTS][2] = {};
+  fk::DevBuf<int> slices_all;          // partitions: slices_int followed by slices_bnd (fused SpMV + halo exchange)
+  // constraints
+  fk::DevBuf<int> dir_ids;             // fixed DOFs (fk_set_dirichlet)
+  fk::DevBuf<double> dir_val, dir_g;   // their values; g = gD scattered over nv (0 on free rows)
+  fk::DevBuf<unsigned char> dir_mask;  // nv: 1 = fixed
+  int n_fixed = 0;
+  fk::DevBuf<double> ns_w, bproj;      // null-space weights (fk_set_nullspace), projected right-hand side
+  bool ns_user = false;
+  // deferred result of an enqueued Picard sweep (fk_picard_step_dev with div_out == NULL)
+  bool picard_pending = false;
   // generic staging for the host-pointer API
   fk::DevBuf<double> st_a, st_b, st_c, st_d, st_m;
   fk::DevBuf<int> st_i, st_j, st_k;

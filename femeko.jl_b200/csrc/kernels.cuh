@@ -120,8 +120,14 @@ constexpr int kOffCnt = kOffErr + 1;
 constexpr int kOffHaloCnt = kOffCnt + 1;
 constexpr int kMail2Words = 3;     // consumer-side fold of the PCG iteration: 2 values + sequence flag per (slot, rank)
 constexpr int kOffMail2 = kOffHaloCnt + 1;
-constexpr int kCtrlWords = 256;
-static_assert(kOffMail2 + 2 * kMaxRanks * kMail2Words <= kCtrlWords, "control block too small");
+// single-reduction recurrence (cg_update_kernel / fused SpMV): halo flags of the in-kernel exchange and a mailbox of
+// 3 values + sequence flag per (slot, rank)
+constexpr int kOffHalo2 = kOffMail2 + 2 * kMaxRanks * kMail2Words;
+constexpr int kMail3Words = 4;
+constexpr int kOffMail3 = kOffHalo2 + kMaxNeigh;
+constexpr int kCtrlWords = 512;
+static_assert(kOffMail3 + 4 * kMaxRanks * kMail3Words <= kCtrlWords, "control block too small");
+constexpr int kSlabVecs = 8;       // x | r | p | Ap (w) | dinv | s | z | potential staging -- then the control block
 
 __device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
   asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
@@ -130,6 +136,27 @@ __device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long
   unsigned long long v;
   asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
   return v;
+}
+__device__ __forceinline__ unsigned long long ld_relaxed_sys(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void fence_acq_rel_sys() { asm volatile("fence.acq_rel.sys;" ::: "memory"); }
+// same contract as spin_until, polling with relaxed loads and ONE acquire fence after success (the polls of ~600
+// CTAs then cost an L2 read each instead of an acquire)
+__device__ __forceinline__ bool spin_until_relaxed(const unsigned long long* flag, unsigned long long seq, unsigned long long* err) {
+  const long long t0 = clock64();
+  bool ok = true;
+  while (ld_relaxed_sys(flag) < seq) {
+    if (clock64() - t0 > 4000000000LL) {
+      *err = 1ULL;
+      ok = false;
+      break;
+    }
+  }
+  fence_acq_rel_sys();
+  return ok;
 }
 // spin until *flag >= seq; gives up after ~2 s (a lost peer must not hang the GPU) and records the failure
 __device__ __forceinline__ bool spin_until(const unsigned long long* flag, unsigned long long seq, unsigned long long* err) {
@@ -263,6 +290,41 @@ __device__ __forceinline__ void peer_fold(double (&v)[NV], const PeerRed& pr, un
   for (int k = 0; k < NV; k++) {
     double s = 0.0;
     for (int r = 0; r < pr.nranks; r++) s += sh[k * kMaxRanks + r];
+    v[k] = s;
+  }
+  __syncthreads();
+}
+
+// Three values (the single fused reduction of the single-reduction recurrence), same protocol as peer_fold on its own
+// mailbox; consecutive reductions alternate slots by the parity of seq, consecutive solves by the parity of the epoch
+// (a rank two hops away may start its next solve while a slow CTA here still reads the last reduction of this one).
+__device__ __forceinline__ void peer_fold3(double (&v)[3], const PeerRed& pr, unsigned long long seq, int epoch_parity) {
+  if (pr.nranks <= 1) return;
+  __shared__ double sh3[3 * kMaxRanks];
+  const int slot = (int)(seq & 1ULL) + 2 * epoch_parity, t = threadIdx.x;   // four slots: a solve never reuses its predecessor's
+  if (t < pr.nranks) {
+    if (t == pr.rank) {
+#pragma unroll
+      for (int k = 0; k < 3; k++) sh3[k * kMaxRanks + t] = v[k];
+    } else {
+      if (blockIdx.x == 0) {
+        unsigned long long* box = pr.peer_ctrl[t] + kOffMail3 + ((size_t)slot * kMaxRanks + pr.rank) * kMail3Words;
+#pragma unroll
+        for (int k = 0; k < 3; k++) reinterpret_cast<double*>(box)[k] = v[k];
+        __threadfence_system();
+        st_release_sys(box + kMail3Words - 1, seq);
+      }
+      const unsigned long long* box = pr.my_ctrl + kOffMail3 + ((size_t)slot * kMaxRanks + t) * kMail3Words;
+      spin_until_relaxed(box + kMail3Words - 1, seq, pr.my_ctrl + kOffErr);
+#pragma unroll
+      for (int k = 0; k < 3; k++) sh3[k * kMaxRanks + t] = reinterpret_cast<const volatile double*>(box)[k];
+    }
+  }
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < 3; k++) {
+    double s = 0.0;
+    for (int r = 0; r < pr.nranks; r++) s += sh3[k * kMaxRanks + r];
     v[k] = s;
   }
   __syncthreads();
@@ -467,10 +529,16 @@ struct PcgCtl {
   double rhs2, thr, r2;
   int base_it, max_iter, done, iters;
   unsigned long long epoch;   // solve counter (same on every rank): high half of the peer_fold sequence numbers
+  double gamma[2], alpha[2];  // single-reduction recurrence: (r,u) and alpha of the previous / current iteration (ping-pong)
 };
 
 __device__ __forceinline__ unsigned long long pcg_seq(const PcgCtl* c, int j, int which) {
   return (c->epoch << 32) + 2ULL * (unsigned long long)(c->base_it + j) + (unsigned long long)which + 1ULL;
+}
+
+// sequence numbers of the single-reduction recurrence: one reduction (V_it) and one halo exchange (S_it) per iteration
+__device__ __forceinline__ unsigned long long cg_seq(const PcgCtl* c, int it) {
+  return (c->epoch << 32) + (unsigned long long)it + 1ULL;
 }
 
 __device__ __forceinline__ bool pcg_inactive(const PcgCtl* c, int j) {
@@ -517,12 +585,12 @@ static __global__ void __launch_bounds__(kVecThreads) pcg_init_kernel(const doub
 
 // single block: fold the partials of (b.b, r.r, r.p) (npart == 1: already reduced scalars) -> thresholds and
 // the early exits of ConjugateGradient.h:43-56
-static __global__ void pcg_init_fin_kernel(const double* __restrict__ part3, int npart, int stride, double tol, int max_iter,
-                                    unsigned long long epoch, PcgCtl* ctl) {
+static __global__ void pcg_init_fin_kernel(const double* __restrict__ pbb, const double* __restrict__ prr, const double* __restrict__ prp,
+                                    int npart, double tol, int max_iter, unsigned long long epoch, PcgCtl* ctl) {
   __shared__ double red[33];
-  const double bb = block_sum_array(part3, npart, red);
-  const double rr = block_sum_array(part3 + stride, npart, red);
-  const double rp = block_sum_array(part3 + 2 * stride, npart, red);
+  const double bb = block_sum_array(pbb, npart, red);
+  const double rr = block_sum_array(prr, npart, red);
+  const double rp = block_sum_array(prp, npart, red);
   if (threadIdx.x == 0) {
     ctl->rhs2 = bb;
     ctl->thr = fmax(tol * tol * bb, DBL_MIN);
@@ -660,6 +728,153 @@ static __global__ void __launch_bounds__(kVecThreads, kPcgVecCtas) pcg_direction
   if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) p[n - 1] = dinv[n - 1] * r[n - 1] + beta * p[n - 1];
 }
 
+
+// ------------------------------------------------------------------------------------------------
+// Single-reduction (Chronopoulos-Gear) Jacobi-PCG: fk_pcg_opts.recurrence = 1.
+//   u = M^-1 r, w = A u, gamma = (r,u), delta = (w,u), beta = gamma/gamma_old,
+//   alpha = gamma / (delta - beta gamma / alpha_old);  p = u + beta p;  s = w + beta s;  x += alpha p;  r -= alpha s.
+// Same iterates as Eigen's loop (ConjugateGradient.h:59-82) in exact arithmetic, but all three dot products of an
+// iteration are consumed at ONE point (the prologue of the vector kernel), so an iteration is two kernels --
+// S_it: w = A z fused with (w,z) [spmv_sell_kernel<DOT>]; V_it: everything else -- and, on a partitioned problem, one
+// cross-GPU reduction instead of two.  V_it folds (gamma, r.r, delta) of the CURRENT residual, tests convergence
+// (Eigen's test: ||r||^2 < tol^2 ||b||^2, iterations reported as Eigen counts them), then makes update it+1.
+// ------------------------------------------------------------------------------------------------
+// r = b - A x0 (Ax0 nullable), z = dinv r; per-CTA partials of (r.z, r.r, b.b) at part[0 | stride | 2 stride]
+static __global__ void __launch_bounds__(kVecThreads) cg_init_kernel(const double* __restrict__ b, const double* __restrict__ Ax0,
+                                                              const double* __restrict__ dinv, int n, double* __restrict__ r,
+                                                              double* __restrict__ z, double* __restrict__ part, int stride) {
+  __shared__ double red_s[33];
+  double s_bb = 0.0, s_rr = 0.0, s_rz = 0.0;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const double bi = b[i];
+    const double ri = Ax0 ? bi - Ax0[i] : bi;
+    const double zi = dinv[i] * ri;
+    r[i] = ri;
+    z[i] = zi;
+    s_bb += bi * bi;
+    s_rr += ri * ri;
+    s_rz += ri * zi;
+  }
+  s_bb = block_sum(s_bb, red_s);
+  s_rr = block_sum(s_rr, red_s);
+  s_rz = block_sum(s_rz, red_s);
+  if (threadIdx.x == 0) {
+    part[blockIdx.x] = s_rz;
+    part[stride + blockIdx.x] = s_rr;
+    part[2 * stride + blockIdx.x] = s_bb;
+  }
+}
+
+// V_it.  partA / partB: (gamma, r.r) partials, rows `stride` apart; V_it reads the buffer of parity it & 1 (written by
+// V_it-1, or by cg_init_kernel for it = 0) and writes the other one -- a CTA may finish its pass while another still
+// folds the old partials.  part_s: delta partials of the SpMV, nps.
+static __global__ void __launch_bounds__(kVecThreads, kPcgVecCtas) cg_update_kernel(double* __restrict__ x, double* __restrict__ r,
+                                                                double* __restrict__ p, double* __restrict__ sv,
+                                                                const double* __restrict__ w, const double* __restrict__ dinv,
+                                                                double* __restrict__ z, int n, double* __restrict__ partA,
+                                                                double* __restrict__ partB, int npv, int stride,
+                                                                const double* __restrict__ part_s, int nps, PcgCtl* ctl, int j,
+                                                                const PeerRed pr) {
+  __shared__ double red_s[66];
+  if (pcg_inactive(ctl, j)) return;
+  const int it = ctl->base_it + j;
+  const double* __restrict__ part_in = (it & 1) ? partB : partA;
+  double* __restrict__ part_out = (it & 1) ? partA : partB;
+  const int n2 = n >> 1, T = gridDim.x * blockDim.x;
+  double2* __restrict__ x2 = reinterpret_cast<double2*>(x);
+  double2* __restrict__ r2 = reinterpret_cast<double2*>(r);
+  double2* __restrict__ p2 = reinterpret_cast<double2*>(p);
+  double2* __restrict__ s2 = reinterpret_cast<double2*>(sv);
+  double2* __restrict__ z2 = reinterpret_cast<double2*>(z);
+  const double2* __restrict__ w2 = reinterpret_cast<const double2*>(w);
+  const double2* __restrict__ d2 = reinterpret_cast<const double2*>(dinv);
+  const bool first = it == 0;   // p and s hold nothing yet: p = u, s = w
+  double2 xv = make_double2(0, 0), rv = xv, pv = xv, sv2 = xv, wv = xv, dv = xv;
+  auto load = [&](int i) {
+    if (i < n2) {
+      rv = r2[i]; wv = w2[i]; dv = d2[i]; xv = x2[i];
+      if (!first) { pv = p2[i]; sv2 = s2[i]; }
+    }
+  };
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  load(i);   // in flight during the fold
+  double v3[3];
+  block_sum2_array(part_in, part_in + stride, npv, red_s, v3[0], v3[1]);
+  v3[2] = block_sum_array(part_s, nps, red_s);
+  peer_fold3(v3, pr, cg_seq(ctl, it), (int)(ctl->epoch & 1ULL));
+  const double gamma = v3[0], rr = v3[1], delta = v3[2];
+  const bool conv = rr < ctl->thr;
+  double alpha, beta = 0.0;
+  if (first) alpha = gamma / delta;
+  else {
+    beta = gamma / ctl->gamma[(it - 1) & 1];
+    alpha = gamma / (delta - beta * gamma / ctl->alpha[(it - 1) & 1]);
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    ctl->r2 = rr;
+    if (conv) { ctl->iters = it > 0 ? it - 1 : 0; ctl->done = 1; }
+    else { ctl->gamma[it & 1] = gamma; ctl->alpha[it & 1] = alpha; }
+  }
+  if (conv) return;
+  double s_rr = 0.0, s_rz = 0.0;
+  while (i < n2) {
+    const double zx = dv.x * rv.x, zy = dv.y * rv.y;   // u = M^-1 r of the current residual (== z[i])
+    if (first) { pv.x = zx; pv.y = zy; sv2 = wv; }
+    else {
+      pv.x = zx + beta * pv.x; pv.y = zy + beta * pv.y;
+      sv2.x = wv.x + beta * sv2.x; sv2.y = wv.y + beta * sv2.y;
+    }
+    xv.x += alpha * pv.x; xv.y += alpha * pv.y;
+    rv.x -= alpha * sv2.x; rv.y -= alpha * sv2.y;
+    const double2 zn = make_double2(dv.x * rv.x, dv.y * rv.y);
+    p2[i] = pv; s2[i] = sv2; x2[i] = xv; r2[i] = rv; z2[i] = zn;
+    s_rr += rv.x * rv.x; s_rz += rv.x * zn.x;
+    s_rr += rv.y * rv.y; s_rz += rv.y * zn.y;
+    i += T;
+    load(i);
+  }
+  if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) {   // odd row count: the last row
+    const int q = n - 1;
+    const double zq = dinv[q] * r[q];
+    const double pq = first ? zq : zq + beta * p[q];
+    const double sq = first ? w[q] : w[q] + beta * sv[q];
+    p[q] = pq; sv[q] = sq;
+    x[q] += alpha * pq;
+    const double rq = r[q] - alpha * sq;
+    r[q] = rq;
+    const double zn = dinv[q] * rq;
+    z[q] = zn;
+    s_rr += rq * rq; s_rz += rq * zn;
+  }
+  block_sum2(s_rz, s_rr, red_s);
+  if (threadIdx.x == 0) { part_out[blockIdx.x] = s_rz; part_out[stride + blockIdx.x] = s_rr; }
+}
+
+// End of a chunk.  If no further V kernel will run (max_iter reached), fold and test the residual of the last update
+// here (Eigen's last loop trip, ConjugateGradient.h:72-73).  On a partitioned problem that reduction is also what keeps
+// a rank from starting its next solve (and pushing new halo rows) while a peer's last SpMV still reads the old ones.
+static __global__ void __launch_bounds__(256) cg_chunk_end_kernel(const double* __restrict__ partA, const double* __restrict__ partB,
+                                                            int npv, int stride, PcgCtl* ctl, int chunk, const PeerRed pr) {
+  __shared__ double red_s[66];
+  const bool done = ctl->done != 0;
+  const bool tail = !done && ctl->base_it + chunk >= ctl->max_iter;
+  __syncthreads();
+  if (tail) {
+    const int itd = ctl->max_iter;   // updates made
+    const double* part_in = (itd & 1) ? partB : partA;
+    double v3[3];
+    block_sum2_array(part_in, part_in + stride, npv, red_s, v3[0], v3[1]);
+    v3[2] = 0.0;
+    peer_fold3(v3, pr, cg_seq(ctl, itd), (int)(ctl->epoch & 1ULL));   // V_itd never runs: the sequence number is free
+    if (threadIdx.x == 0) {
+      ctl->r2 = v3[1];
+      if (v3[1] < ctl->thr) { ctl->iters = itd - 1; ctl->done = 1; }
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0 && !ctl->done) ctl->base_it += chunk;
+}
+
 static __global__ void pcg_advance_kernel(PcgCtl* ctl, int chunk) {
   if (!ctl->done) ctl->base_it += chunk;
 }
@@ -671,6 +886,69 @@ static __global__ void fold_partials_kernel(const double* __restrict__ part, int
     const double s = block_sum_array(part + (size_t)v * stride, npart, red);
     if (threadIdx.x == 0) out[v] = s;
   }
+}
+
+// ------------------------------------------------------------------------------------------------
+// constraints: null-space projection (fk_pcg_opts.project_nullspace) and Dirichlet elimination
+// ------------------------------------------------------------------------------------------------
+// per-CTA partials of (sum a [mode 0] | sum a w [mode 1],  sum w) at part[0 | stride]; w == nullptr: ones
+static __global__ void __launch_bounds__(kVecThreads) ns_partials_kernel(const double* __restrict__ a, const double* __restrict__ w, int n,
+                                                                  int mode, double* __restrict__ part, int stride) {
+  __shared__ double red_s[66];
+  double s0 = 0.0, s1 = 0.0;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const double wi = w ? w[i] : 1.0;
+    s0 += mode ? a[i] * wi : a[i];
+    s1 += wi;
+  }
+  block_sum2(s0, s1, red_s);
+  if (threadIdx.x == 0) { part[blockIdx.x] = s0; part[stride + blockIdx.x] = s1; }
+}
+// mode 0: out = a - (S0 / S1) w   (right-hand side made consistent: the multiplier term of the bordered system)
+// mode 1: out = a - (S0 / S1)     (solution shifted so that w . x = 0)
+static __global__ void __launch_bounds__(kVecThreads) ns_apply_kernel(const double* __restrict__ a, const double* __restrict__ w, int n,
+                                                               int mode, const double* __restrict__ S, double* __restrict__ out) {
+  const double c = S[1] != 0.0 ? S[0] / S[1] : 0.0;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+    out[i] = a[i] - (mode ? c : c * (w ? w[i] : 1.0));
+}
+
+// Dirichlet lift (Fluids/fluids3D.jl:164-169): b[free] -= (A g)[free], b[fixed] = g, g = gD on the fixed rows, 0 elsewhere
+static __global__ void dirichlet_lift_kernel(double* __restrict__ b, const double* __restrict__ Ag, const double* __restrict__ g,
+                                      const unsigned char* __restrict__ mask, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) b[i] = mask[i] ? g[i] : b[i] - Ag[i];
+}
+// fixed rows and columns of a matrix in the SELL layout -> identity: one lane per row, like the SpMV
+static __global__ void __launch_bounds__(256) dirichlet_mask_kernel(const int4* __restrict__ slice_meta, const int* __restrict__ srow,
+                                                              const unsigned short* __restrict__ colz, const int* __restrict__ sell_diag,
+                                                              const unsigned char* __restrict__ mask, int nslices, int n_rows,
+                                                              double* __restrict__ vals) {
+  const int lane = threadIdx.x & 31;
+  const int sl = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (sl >= nslices) return;
+  const int4 m = slice_meta[sl];
+  const int r = srow[sl * 32 + lane];
+  if (r < 0 || r >= n_rows) return;
+  const bool rfix = mask[r] != 0;
+  const int dg = sell_diag[r];
+  const unsigned short* cz = colz + (size_t)m.z * 32;
+  for (int k = 0; k < m.y; k++) {
+    int c;
+    if (m.w >= 0) c = m.w + (int)cz[((size_t)(k >> 2) * 32 + lane) * 4 + (k & 3)];
+    else c = reinterpret_cast<const int*>(cz)[(size_t)k * 32 + lane];
+    const int idx = m.x + k * 32 + lane;
+    if (rfix) vals[idx] = (idx == dg) ? 1.0 : 0.0;
+    else if (mask[c]) vals[idx] = 0.0;
+  }
+}
+static __global__ void scatter_kernel(double* __restrict__ dst, const int* __restrict__ ids, const double* __restrict__ v, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) dst[ids[i]] = v ? v[i] : 0.0;
+}
+static __global__ void scatter_flag_kernel(unsigned char* __restrict__ dst, const int* __restrict__ ids, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) dst[ids[i]] = 1;
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -21,7 +21,13 @@ __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefe
 
 // a slice with 32-bit columns (columns span >= 65536: halo columns of a partition, meshes numbered without
 // locality): same batches, one column load per entry
-template <int G>
+// COH: gather x with ld.global.cg (L2 only).  Used for the slices that read halo columns when the halo rows are
+// written by peer GPUs while this kernel runs (fused exchange): the non-coherent path (ld.global.nc / L1) could serve
+// a line fetched before the peer's store landed.
+template <bool COH>
+static __device__ __forceinline__ double gather_x(const double* p) { return COH ? __ldcg(p) : __ldg(p); }
+
+template <int G, bool COH = false>
 static __device__ __forceinline__ double sell_slice_row32(const double* __restrict__ v, const int* __restrict__ c, int w,
                                                           const double* __restrict__ x) {
   double acc = 0.0;
@@ -33,7 +39,7 @@ static __device__ __forceinline__ double sell_slice_row32(const double* __restri
 #pragma unroll
     for (int u = 0; u < 4 * G; u++) vv[u] = (k + u < w) ? __ldcs(v + (k + u) * kSellC) : 0.0;
 #pragma unroll
-    for (int u = 0; u < 4 * G; u++) xx[u] = (k + u < w) ? __ldg(x + cc[u]) : 0.0;
+    for (int u = 0; u < 4 * G; u++) xx[u] = (k + u < w) ? gather_x<COH>(x + cc[u]) : 0.0;
 #pragma unroll
     for (int u = 0; u < 4 * G; u++)
       if (k + u < w) acc = __dadd_rn(acc, __dmul_rn(vv[u], xx[u]));
@@ -44,7 +50,7 @@ static __device__ __forceinline__ double sell_slice_row32(const double* __restri
 // a slice with 16-bit column offsets: one 8-byte word per lane holds the columns of four consecutive steps, so
 // a batch of 4 G entries issues G column loads + 4 G value loads, then 4 G independent gathers of x, and only
 // then folds them left to right -- the memory-level parallelism comes from the batch, not from occupancy alone.
-template <int G>
+template <int G, bool COH = false>
 static __device__ __forceinline__ double sell_slice_row16(const double* __restrict__ v, const uint2* __restrict__ c, int cbase, int w,
                                                           const double* __restrict__ x) {
   double acc = 0.0;
@@ -60,7 +66,7 @@ static __device__ __forceinline__ double sell_slice_row16(const double* __restri
     for (int u = 0; u < 4 * G; u++) {
       const unsigned word = (u & 2) ? cw[u >> 2].y : cw[u >> 2].x;
       const unsigned off = (u & 1) ? (word >> 16) : (word & 0xffffu);
-      xx[u] = (k + u < w) ? __ldg(xb + off) : 0.0;
+      xx[u] = (k + u < w) ? gather_x<COH>(xb + off) : 0.0;
     }
 #pragma unroll
     for (int u = 0; u < 4 * G; u++)
@@ -112,6 +118,89 @@ static __global__ void __launch_bounds__(kSpmvThreads, MINB) spmv_sell_kernel(co
     const double v[1] = {block_sum(dot, red_s)};
     grid_reduce_finish<1>(v, part, gridDim.x, red, red_s);   // -> out[0] = p.Ap over all ranks
   }
+}
+
+
+// ------------------------------------------------------------------------------------------------
+// Partitioned problems, single-reduction recurrence: SpMV fused with the halo exchange of its input over NVLink
+// peer memory -- ONE kernel, no separate push / wait launches, no second stream.
+//   * the first hf.npush CTAs first store this rank's boundary rows of x straight into the neighbours' halo rows
+//     (x was completed by the previous kernel); the last pusher to finish releases a system-scope sequence flag
+//     to every neighbour;
+//   * every CTA then walks slice_list: the slices that read no halo column first (the bulk: the peers' rows arrive
+//     while they stream), then the halo-coupled ones, each warp waiting once for the neighbours' flags and gathering
+//     x through L2 (ld.global.cg) there.
+// The whole grid is resident (persistent launch), so the pushers always run; a rank only ever waits for stores that
+// its peers issue at the START of the matching kernel, so there is no cyclic wait.
+struct HaloFused {
+  const int* send_idx;
+  int send_ptr[kMaxNeigh + 1];
+  double* dst[kMaxNeigh];                // neighbour q's copy of x at the rows it receives from me
+  unsigned long long* flag[kMaxNeigh];   // neighbour q's flag word for me (its control block, kOffHalo2 + my slot there)
+  unsigned long long* my_ctrl;
+  unsigned int* ticket;                  // zero between kernels
+  int nneigh, npush, n_int;              // slices [0, n_int) of slice_list read no halo column
+};
+
+template <int G, int MINB>
+static __global__ void __launch_bounds__(kSpmvThreads, MINB) spmv_sell_fused_kernel(const int4* __restrict__ slice_meta, const int* __restrict__ srow,
+                                                                        const unsigned short* __restrict__ colz,
+                                                                        const double* __restrict__ vals, const double* __restrict__ x,
+                                                                        double* __restrict__ y, int nslices, double* __restrict__ part,
+                                                                        const PcgCtl* ctl, int j, const int* __restrict__ slice_list,
+                                                                        const __grid_constant__ HaloFused hf) {
+  __shared__ double red_s[33];
+  __shared__ int last_pusher;
+  if (pcg_inactive(ctl, j)) return;
+  const unsigned long long seq = cg_seq(ctl, ctl->base_it + j);
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  constexpr int WPB = kSpmvThreads / 32;
+  if ((int)blockIdx.x < hf.npush) {
+    for (int q = 0; q < hf.nneigh; q++) {
+      const int b = hf.send_ptr[q], n = hf.send_ptr[q + 1] - b;
+      double* __restrict__ dst = hf.dst[q];
+      for (int i = blockIdx.x * kSpmvThreads + threadIdx.x; i < n; i += hf.npush * kSpmvThreads) dst[i] = x[__ldg(hf.send_idx + b + i)];
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) last_pusher = (atomicAdd(hf.ticket, 1u) == (unsigned)hf.npush - 1u) ? 1 : 0;
+    __syncthreads();
+    if (last_pusher) {
+      if ((int)threadIdx.x < hf.nneigh) {
+        __threadfence_system();
+        st_release_sys(hf.flag[threadIdx.x], seq);
+      }
+      if (threadIdx.x == 0) *hf.ticket = 0u;
+    }
+  }
+  double dot = 0.0;
+  bool waited = false;
+  for (int q = blockIdx.x * WPB + wib; q < nslices; q += gridDim.x * WPB) {
+    const int sl = __ldg(slice_list + q);
+    const int4 m = __ldg(slice_meta + sl);
+    const int r = __ldg(srow + sl * kSellC + lane);
+    const double* __restrict__ v = vals + m.x + lane;
+    const unsigned short* __restrict__ cz = colz + (size_t)m.z * kSellC;
+    double acc;
+    if (q < hf.n_int) {
+      acc = m.w >= 0 ? sell_slice_row16<G>(v, reinterpret_cast<const uint2*>(cz) + lane, m.w, m.y, x)
+                     : sell_slice_row32<(G > 2 ? 2 : G)>(v, reinterpret_cast<const int*>(cz) + lane, m.y, x);
+    } else {
+      if (!waited) {   // once per warp: the neighbours' rows of this exchange have landed
+        if (lane < hf.nneigh) spin_until_relaxed(hf.my_ctrl + kOffHalo2 + lane, seq, hf.my_ctrl + kOffErr);
+        __syncwarp();
+        waited = true;
+      }
+      acc = m.w >= 0 ? sell_slice_row16<G, true>(v, reinterpret_cast<const uint2*>(cz) + lane, m.w, m.y, x)
+                     : sell_slice_row32<(G > 2 ? 2 : G), true>(v, reinterpret_cast<const int*>(cz) + lane, m.y, x);
+    }
+    if (r >= 0) {
+      y[r] = acc;
+      dot += acc * x[r];
+    }
+  }
+  const double bs = block_sum(dot, red_s);
+  if (threadIdx.x == 0) part[blockIdx.x] = bs;
 }
 
 // launch shapes {entries per batch = 4 G, min CTAs per SM}; selected with fk_tune(h, 4, variant)

@@ -201,8 +201,29 @@ class Femeko:
         return y
 
     @staticmethod
-    def pcg_opts(tol=0.0, max_iter=0, warm_start=False, check_every=0, tol_disable=False, no_precond=False):
-        return L.fk_pcg_opts(float(tol), int(max_iter), int(warm_start), int(check_every), int(tol_disable), int(no_precond))
+    def pcg_opts(tol=0.0, max_iter=0, warm_start=False, check_every=0, tol_disable=False, no_precond=False, recurrence=0,
+                 project_nullspace=False):
+        return L.fk_pcg_opts(float(tol), int(max_iter), int(warm_start), int(check_every), int(tol_disable), int(no_precond),
+                             int(recurrence), int(project_nullspace))
+
+    # -- constraints ----------------------------------------------------------------------------
+    def set_dirichlet(self, fixed, gD=None):
+        """Fixed DOFs (0-based) and their values (Fluids/fluids3D.jl:142-162); an empty list clears the set."""
+        ids = np.ascontiguousarray(fixed, dtype=np.int32)
+        g = None if gD is None else np.ascontiguousarray(np.broadcast_to(np.asarray(gD, dtype=np.float64), ids.shape))
+        L.check(self.lib.fk_set_dirichlet(self.h, L.iptr(ids), int(ids.size), L.dptr(g)))
+
+    def apply_dirichlet(self, slot=0, b=None):
+        """RHS lift + identity rows / columns on `slot` (fluids3D.jl:164-169); returns the lifted right-hand side."""
+        bb = None if b is None else np.array(b, dtype=np.float64, copy=True)
+        L.check(self.lib.fk_apply_dirichlet(self.h, slot, L.dptr(bb)))
+        return bb
+
+    def set_nullspace(self, w=None):
+        """Weights of fk_pcg_opts.project_nullspace; lagrange(mesh) gives the bordered-system solution
+        (magneticField.jl:99-107)."""
+        wv = None if w is None else np.ascontiguousarray(w, dtype=np.float64)
+        L.check(self.lib.fk_set_nullspace(self.h, L.dptr(wv)))
 
     def pcg(self, b, slot=0, x0=None, **kw):
         """Jacobi-PCG with Eigen's recurrence; returns (x, iterations, relative residual)."""
@@ -333,9 +354,15 @@ class Femeko:
         L.check(self.lib.fk_recover_field_dev(self.h, C.c_void_p(u_ptr), C.c_void_p(mu_ptr), int(compat_bug),
                                               C.c_void_p(Hfield_ptr), C.c_void_p(Hn_ptr), C.c_void_p(B_ptr)))
 
-    def picard_step_dev(self, u_ptr: int, slot=0, compat_bug=False):
+    def picard_step_dev(self, u_ptr: int, slot=0, compat_bug=False, sync=True):
+        """sync=False only enqueues the sweep (no host round trip); fetch div later with picard_result()."""
         div = C.c_double()
-        L.check(self.lib.fk_picard_step_dev(self.h, slot, C.c_void_p(u_ptr), int(compat_bug), C.byref(div)))
+        L.check(self.lib.fk_picard_step_dev(self.h, slot, C.c_void_p(u_ptr), int(compat_bug), C.byref(div) if sync else None))
+        return div.value if sync else None
+
+    def picard_result(self):
+        div = C.c_double()
+        L.check(self.lib.fk_picard_result(self.h, C.byref(div)))
         return div.value
 
 

@@ -37,7 +37,7 @@ class fk_create_opts(C.Structure):
 
 class fk_pcg_opts(C.Structure):
     _fields_ = [("tol", C.c_double), ("max_iter", C.c_int), ("warm_start", C.c_int), ("check_every", C.c_int),
-                ("tol_disable", C.c_int), ("no_precond", C.c_int)]
+                ("tol_disable", C.c_int), ("no_precond", C.c_int), ("recurrence", C.c_int), ("project_nullspace", C.c_int)]
 
 
 def build(verbose: bool = False) -> str:
@@ -104,6 +104,11 @@ _SIGS = {
     "fk_reset_field": (C.c_int, [_H]),
     "fk_picard_step": (C.c_int, [_H, C.c_int, c_double_p, C.c_int, c_double_p]),
     "fk_picard_step_dev": (C.c_int, [_H, C.c_int, C.c_void_p, C.c_int, c_double_p]),
+    "fk_picard_result": (C.c_int, [_H, c_double_p]),
+    "fk_set_dirichlet": (C.c_int, [_H, c_int_p, C.c_int, c_double_p]),
+    "fk_apply_dirichlet": (C.c_int, [_H, C.c_int, c_double_p]),
+    "fk_apply_dirichlet_dev": (C.c_int, [_H, C.c_int, C.c_void_p]),
+    "fk_set_nullspace": (C.c_int, [_H, c_double_p]),
     "fk_picard_pcg": (C.c_int, [_H, C.c_int, c_double_p, C.c_int, c_double_p, c_double_p, C.POINTER(fk_pcg_opts), c_double_p,
                                 c_int_p, c_double_p]),
     "fk_demag_setup": (C.c_int, [_H, C.c_int, c_int_p, C.c_int, c_double_p]),

@@ -37,7 +37,8 @@ typedef struct fk_create_opts {
   int tile_max_rows;  /* rows per assembly tile; default 256                                  */
   int natural_order;  /* 1: tile rows in input order instead of Morton order of coordinates   */
   int sell_sigma;     /* SELL-32-sigma: rows sorted by length inside windows of sigma rows; default 1024 */
-  int device;         /* CUDA device ordinal; -1 = current device                             */
+  int device;         /* CUDA device ordinal (0 = the first device, also what an all-zero struct selects); -1 = the
+                         calling thread's current device (what opts == NULL selects)            */
   int n_owned;        /* multi-GPU partitions: rows [0, n_owned) are owned (assembled, solved),
                          rows [n_owned, nv) are halo copies; 0 = all rows owned                 */
   int asm_cfg;        /* assembly launch shape {threads, min CTAs/SM}: 0 = default ({256,2}); 1 {256,3} 2 {256,2} 3 {384,2} 4 {512,2} 5 {128,6} 6 {512,1} 7 {768,1} */
@@ -55,6 +56,14 @@ typedef struct fk_pcg_opts {
   int check_every;      /* iterations per host convergence poll / CUDA-graph chunk; default 32 */
   int tol_disable;      /* 1: never stop on the residual, run exactly max_iter iterations      */
   int no_precond;       /* 1: identity preconditioner (IterativeSolvers.cg call sites, run.jl:141) */
+  int recurrence;       /* 0: Eigen's two-reduction recurrence (ConjugateGradient.h:59-82), three kernels per iteration;
+                           1: single-reduction (Chronopoulos-Gear) recurrence -- same Krylov iterates in exact arithmetic,
+                           ONE fused reduction and two kernels per iteration (w = A M^-1 r with (w,u) fused; then p, s, x, r,
+                           u in one pass); on partitions the halo push and the wait ride inside the same two kernels      */
+  int project_nullspace;/* 1: singular Neumann systems (constants in the null space): b <- b - (sum b / sum w) w before the
+                           solve and x <- x - (w.x / sum w) after it, w = fk_set_nullspace weights (default ones) -- with
+                           w = lagrange(mesh) this is the solution of the reference's bordered system [A C; C' 0]
+                           (magneticField.jl:99-107, NewtonRaphson.jl:166)                                                */
 } fk_pcg_opts;
 
 const char* fk_last_error(void);
@@ -159,6 +168,20 @@ int fk_pcg(fk_handle h, int slot, const double* b, double* x, const fk_pcg_opts*
 int fk_pcg_dev(fk_handle h, int slot, const double* b_dev, double* x_dev, const fk_pcg_opts* opts,
                int* iters_out, double* relres_out);
 
+/* ---- constraints ------------------------------------------------------------------------------
+ * Dirichlet elimination as the reference drivers do it on the assembled system (Fluids/fluids3D.jl:142-174:
+ * `RHS = -LHS[free,fixed]*gD[fixed]; UP[fixed] = gD[fixed]; UP[free] = LHS[free,free] \ RHS`), kept on the full
+ * pattern: fk_set_dirichlet stores the fixed DOFs and their values (gD == NULL: zeros); fk_apply_dirichlet lifts the
+ * right-hand side (b[free] -= A[free,fixed] gD, b[fixed] = gD) and turns the fixed rows and columns of `slot` into
+ * identity rows / columns, so every later fk_pcg / fk_spmv on that slot solves LHS[free,free] exactly and returns
+ * x[fixed] = gD.  A re-assembly of the slot needs a new fk_apply_dirichlet.  n_fixed = 0 clears the set.
+ * fk_set_nullspace: weights w (nv, NULL = ones) of fk_pcg_opts.project_nullspace; lagrange(mesh) gives the
+ * bordered-system solution of magneticField.jl:107.                                                             */
+int fk_set_dirichlet(fk_handle h, const int* fixed_ids, int n_fixed, const double* gD /* n_fixed or NULL */);
+int fk_apply_dirichlet(fk_handle h, int slot, double* b /* nv, in/out; may be NULL: matrix only */);
+int fk_apply_dirichlet_dev(fk_handle h, int slot, double* b_dev);
+int fk_set_nullspace(fk_handle h, const double* w /* nv or NULL */);
+
 /* ---- field recovery and the nonlinear step --------------------------------------------------
  * H_k = -sum_i u[t_i] grad(lambda_i), |H_k|, B_k = mu_k |H_k| (magneticField.jl:111-132).
  * compat_bug != 0 reproduces NewtonRaphson.jl:187-189 / run.jl:94-96 (d-term written into row 2).
@@ -192,7 +215,10 @@ int fk_reset_field(fk_handle h);
  * the stiffness matrix with the new mu into `slot` -- one kernel, the mesh is read once.
  * Returns status 2 if a spline with bc = error was evaluated out of range.                      */
 int fk_picard_step(fk_handle h, int slot, const double* u, int compat_bug, double* div_out);
+/* div_out == NULL: the sweep is only enqueued (no host synchronisation); div and the error status are then
+ * delivered by the next fk_picard_result / fk_picard_step* / fk_picard_pcg call on the handle.               */
 int fk_picard_step_dev(fk_handle h, int slot, const double* u_dev, int compat_bug, double* div_out);
+int fk_picard_result(fk_handle h, double* div_out);
 /* One nonlinear iteration from host buffers = fk_picard_step(u) then fk_pcg(b -> x): the body of the reference
  * loop (NewtonRaphson.jl:148-214, manyBodyIntersecting.jl:141-210).  Identical results; the upload of b (and of
  * the warm-start x) overlaps the sweep on a second stream.                                                  */
