@@ -59,6 +59,18 @@ def measured_peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def mesh_module():
+    """femeko.jl_b200/mesh.py (pure numpy generators) loaded on its own: the CPU arm must not import the product
+    package, so that the only native code it maps is oracle/."""
+    import importlib.util
+
+    spec = importlib.util.spec_from_file_location("_fk_mesh_standalone", os.path.join(ROOT, "femeko.jl_b200", "mesh.py"))
+    mod = importlib.util.module_from_spec(spec)
+    sys.modules[spec.name] = mod
+    spec.loader.exec_module(mod)
+    return mod
+
+
 def gd_table():
     g = np.load(os.path.join(ROOT, "tests", "golden", "gd_270K.npz"))
     return g["HofM"], g["mu"], g["dmu"]
@@ -215,18 +227,18 @@ def run_ours(args):
     def host_ptr(tn):
         return C.cast(tn.data_ptr(), L.c_double_p)
 
-    opts = dict(max_iter=Piters, tol_disable=True, check_every=Piters + (Piters & 1))
+    opts = dict(max_iter=Piters, tol_disable=True, check_every=Piters + (Piters & 1), recurrence=args.recurrence)
 
     def step_dev(ev=None):
         if ev:
             ev[0].record(stream)
-        div = h.picard_step_dev(u_dev.data_ptr(), slot=0)
+        h.picard_step_dev(u_dev.data_ptr(), slot=0, sync=False)      # enqueued; div comes back with the solve's poll
         if ev:
             ev[1].record(stream)
         h.pcg_dev(b_dev.data_ptr(), x_dev.data_ptr(), slot=0, **opts)
         if ev:
             ev[2].record(stream)
-        return div
+        return h.picard_result()
 
     o = h.pcg_opts(**opts)
     it_c, rr_c, div_c = C.c_int(), C.c_double(), C.c_double()
@@ -267,28 +279,54 @@ def run_ours(args):
         sampler.start()
     ms_dev, launches, evs = timed(step_dev, K, W, True)
     ms_e2e, _, _ = timed(step_e2e, K, W, False)
+    # the same call with PAGEABLE host buffers (what a Julia Array is)
+    u_pg, b_pg, x_pg = u_host.numpy().copy(), b_host.numpy().copy(), np.zeros(nv)
+
+    def step_e2e_pageable():
+        L.check(h.lib.fk_picard_pcg(h.h, 0, L.dptr(u_pg), 0, L.dptr(b_pg), L.dptr(x_pg), C.byref(o), C.byref(div_c),
+                                    C.byref(it_c), C.byref(rr_c)))
+
+    ms_e2e_pg, _, _ = timed(step_e2e_pageable, max(2, K // 2), 2, False)
+    ms_e2e_pg *= K / max(2, K // 2)
     clocks = sampler.stop() if rank == 0 else {}
 
     asm_ms = statistics.mean(e[0].elapsed_time(e[1]) for e in evs)
     pcg_ms = statistics.mean(e[1].elapsed_time(e[2]) for e in evs)
 
-    # untimed record: a complete nonlinear solve (Picard to mu0*max|dH| < 1e-4, PCG to 1e-10 each step)
+    # outside the timed region: a complete nonlinear solve at the bench size (Picard to mu0*max|dH| < 1e-4,
+    # NewtonRaphson.jl:37-38,148; PCG to 1e-10 each pass, warm-started), checked by the true residual of the last pass
     nonlin = None
     if args.full_solve:
         with torch.cuda.stream(stream):
             u2 = u_dev.clone()
+            r2 = torch.empty_like(u2)
         h.set_mu(np.full(mesh.nt, MU0))
         h.reset_field()
+        h.assemble_stiffness_dev(h.device_ptr(3), slot=0)
+        barrier()
         t0 = time.time()
-        tot_it, att, div = 0, 0, float("inf")
-        while div > 1e-4 and att < 100:                      # NewtonRaphson.jl:37-38,148
+        tot_it, att, div, rr = 0, 0, float("inf"), 0.0
+        while div > 1e-4 and att < 100:
+            it, rr = h.pcg_dev(b_dev.data_ptr(), u2.data_ptr(), slot=0, tol=1e-10, max_iter=20000, warm_start=att > 0,
+                               recurrence=args.recurrence)
             div = h.picard_step_dev(u2.data_ptr(), slot=0)
-            it, rr = h.pcg_dev(b_dev.data_ptr(), u2.data_ptr(), slot=0, tol=1e-10, max_iter=20000, warm_start=True)
             tot_it += it
             att += 1
         h.synchronize()
-        nonlin = {"picard_iters": att, "pcg_iters_total": tot_it, "seconds": round(time.time() - t0, 4), "div": div,
-                  "last_relres": rr}
+        secs = time.time() - t0
+        nr = C.c_double()
+        L.check(h.lib.fk_residual_dev(h.h, 0, C.c_void_p(u2.data_ptr()), C.c_void_p(b_dev.data_ptr()), C.c_void_p(r2.data_ptr()),
+                                      C.byref(nr)))
+        with torch.cuda.stream(stream):
+            bn = float(torch.linalg.vector_norm(b_dev[:n_rows]).item())
+        if dist is not None:
+            tb = torch.tensor([bn * bn], dtype=torch.float64, device=dev)
+            dist.all_reduce(tb)
+            bn = float(tb.sqrt().item())
+        nonlin = {"picard_iters": att, "pcg_iters_total": tot_it, "seconds": round(secs, 4), "div": div, "last_relres": rr,
+                  "converged": bool(div <= 1e-4),
+                  "check": {"what": "||b - A(mu(H(u))) u|| / ||b|| with the matrix of the converged state (one more sweep)",
+                            "value": nr.value / max(bn, 1e-300)}}
 
     world_tets = nt_owned
     world_rows = n_rows
@@ -310,15 +348,21 @@ def run_ours(args):
         asm_gbs = asm_bytes / (asm_ms * 1e-3) / 1e9
         traffic = {}
         tpath = os.path.join(ROOT, "profiles", "traffic.json")
-        if os.path.exists(tpath):
-            traffic = json.load(open(tpath))
+        if os.path.exists(tpath):   # ncu captures are per configuration: only a matching one is quoted, else null
+            key = f"n{N}_gpus{world}_rec{args.recurrence}"
+            traffic = json.load(open(tpath)).get(key, {})
+        # what cannot live in L2: the matrix stream (values + packed columns + slice metadata); the vectors are pinned
+        floor_bytes = int(8 * sell[0] + sell[3] + 144 * sell[1])
+        rec_name = ("single-reduction recurrence: spmv_sell_kernel<DOT> + cg_update_kernel, 2 kernels"
+                    if args.recurrence == 1 else "Eigen recurrence: spmv_sell_kernel<DOT> + pcg_update_kernel + pcg_direction_kernel")
         line = {
             "metric": METRIC, "value": round(value, 3), "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": round(ms_step, 4), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic",
             "config": {"workload": f"configs[1]: nonlinear magnetostatics Picard step, Kuhn cube N={N} per GPU "
                                    f"({nt_owned} tets, {n_rows} rows, {nnz} nnz per GPU), Gd mu(H) table @270K, "
-                                   f"{Piters} Jacobi-PCG iterations per step (fixed count, x0=0)",
+                                   f"{Piters} Jacobi-PCG iterations per step (fixed count, x0=0, "
+                                   f"{'single-reduction' if args.recurrence == 1 else 'Eigen'} recurrence)",
                        "tets_total": world_tets, "rows_total": world_rows, "nnz_total": world_nnz, "pcg_iters_per_step": Piters,
                        "l2": "inputs larger than L2 (CSR values+indices %.0f MB per GPU vs 126 MB L2)" % (12 * nnz / 1e6),
                        "parallelism": "single GPU" if world == 1 else
@@ -328,28 +372,38 @@ def run_ours(args):
                            "pcg_ms": round(pcg_ms, 4), "pcg_iters_per_s": round(Piters / (pcg_ms * 1e-3), 1),
                            "setup_s_untimed": round(setup_s, 2), "linear_presolve_iters": it0},
             "e2e": {"value": round(e2e_value, 3), "unit": UNIT, "ms_per_step": round(ms_e2e / K, 4),
-                    "h2d_bytes_per_step": 16 * nv, "d2h_bytes_per_step": 8 * n_rows + 8 + 4 + 64},
+                    "h2d_bytes_per_step": 16 * nv, "d2h_bytes_per_step": 8 * n_rows + 8 + 4 + 64,
+                    "host_buffers": "pinned",
+                    "pageable": {"value": round(world_tets / (ms_e2e_pg / K * 1e-3) / 1e6, 3), "ms_per_step": round(ms_e2e_pg / K, 4),
+                                 "note": "same call with pageable host arrays (a Julia Array)"}},
             "gpu_launches": int(launches),
-            "roofline": {"kernel": "fused Jacobi-PCG iteration (spmv_sell_kernel<DOT> + pcg_update_kernel + pcg_direction_kernel)",
+            "roofline": {"kernel": "fused Jacobi-PCG iteration (" + rec_name + ")",
                          "bound": "hbm", "achieved": round(pcg_gbs, 1), "peak": peak, "unit": "GB/s",
-                         "frac": round(pcg_gbs / peak, 4), "traffic": traffic.get("pcg_iteration_bytes"),
+                         "frac": round(pcg_gbs / peak, 4), "traffic": traffic.get("pcg_iteration_bytes"), "traffic_source": traffic.get("source"),
                          "peak_source": peak_src, "algorithmic_bytes_per_launch": it_bytes,
                          "avg_launch_ms": round(pcg_ms / Piters, 5),
                          "note": "achieved uses SURVEY 8d's common denominator (12 B per CSR entry + 108 B per row); the "
                                  "SpMV actually streams %.2f B per entry (packed 16-bit column offsets, %d of %d slices) and "
                                  "the PCG vectors are pinned in L2, so frac can exceed 1" % (
                                      8 + sell[3] / max(sell[0], 1), sell[2], sell[1]),
-                         "layout_bytes_per_launch": int(8 * sell[0] + sell[3] + 144 * sell[1] + 108 * n_rows)},
-            "roofline_assembly": {"kernel": "Picard sweep: material_update_kernel + assemble_kernel<ASM_PICARD> + max fold (fk_picard_step_dev, one host poll)", "bound": "hbm", "achieved": round(asm_gbs, 1),
+                         "layout_bytes_per_launch": int(8 * sell[0] + sell[3] + 144 * sell[1] + 108 * n_rows),
+                         "floor_bytes": floor_bytes,
+                         "frac_of_floor": round(floor_bytes / (pcg_ms / Piters * 1e-3) / 1e9 / peak, 4),
+                         "floor_note": "L2-aware floor: only the matrix stream (values, packed columns, slice metadata) must "
+                                       "come from HBM each iteration; frac_of_floor = floor_bytes / t / peak"},
+            "roofline_assembly": {"kernel": "Picard sweep: material_update_kernel + assemble_kernel<ASM_PICARD> + max fold (device time of the enqueued sweep; its scalars return with the solve's poll)", "bound": "hbm", "achieved": round(asm_gbs, 1),
                                   "peak": peak, "unit": "GB/s", "frac": round(asm_gbs / peak, 4),
                                   "traffic": traffic.get("picard_assembly_bytes"), "algorithmic_bytes_per_launch": asm_bytes,
                                   "avg_launch_ms": round(asm_ms, 5)},
             "clocks": clocks,
         }
         if nonlin:
-            line["nonlinear_solve_untimed"] = nonlin
+            line["nonlinear_solve"] = nonlin
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(args, budget_s=args.cpu_budget)
+            line["parity"] = parity_block(args, local)
+            if args.solve_n > 0:
+                line["solve"] = solve_block(args, local)
         print(json.dumps(line), flush=True)
     h.close()
     if dist is not None:
@@ -360,22 +414,30 @@ def run_ours(args):
 # --------------------------------------------------------------------------------------------------
 # CPU arm: the compiled reference (oracle/_ref) -- or the C port when it is absent
 # --------------------------------------------------------------------------------------------------
+def scipy_spline(x, y):
+    """FITPACK curfit(k=3, s=0) through scipy (the Fortran Dierckx.jl wraps): (t, c) of Spline1D(x, y)."""
+    from scipy.interpolate import splrep
+
+    t, c, _ = splrep(x, y, k=3, s=0)
+    return np.ascontiguousarray(t), np.ascontiguousarray(c)
+
+
 class CpuStep:
     """One Picard step on the host with the reference's own code where it exists:
     field recovery + spline (C port of magneticField.jl:111-132 / FITPACK splev: the reference has
     them only in Julia), stiffnessMatrix (src/FEMc.cpp:102-133, compiled unchanged) and Eigen's
-    Jacobi-PCG (magnetostatics.cpp:26-38) for a fixed iteration count."""
+    Jacobi-PCG (magnetostatics.cpp:26-38) for a fixed iteration count.  Imports nothing from the product package
+    (the mesh generator is loaded as a stand-alone numpy module, the spline is fitted by scipy)."""
 
     def __init__(self, N, piters):
-        import femeko_jl_b200 as fk
         from oracle import oracle as orc
 
-        self.orc, self.fk = orc, fk
+        self.orc = orc
         self.kind = "reference" if orc.have_ref() else "port"
-        self.m = fk.kuhn_cube(N, inside_edge=0.2)
+        self.m = mesh_module().kuhn_cube(N, inside_edge=0.2)
         self.piters = piters
         Hk, muk, _ = gd_table()
-        self.spl = fk.Spline1D(Hk, muk, bc="nearest")
+        self.spl_t, self.spl_c = scipy_spline(Hk, muk)
         m = self.m
         self.rp, self.ci = orc.pattern(m.t, m.nv)
         self.b = -orc.boundary_integral(m, [0.5, 0.0, 0.0], [0], "julia")
@@ -387,18 +449,101 @@ class CpuStep:
             _, _, v = orc.stiffness(m, mu, order="eigen")
             self.u = orc.pcg(self.rp, self.ci, v, self.b, 1e-8)[0]
         self.mu = mu
+        self.out = None
 
     def step(self):
         orc, m = self.orc, self.m
         _, Hn = orc.recover_field(m, self.u)
         mu = self.mu.copy()
-        mu[m.InsideElements] = orc.splev(self.spl.t, self.spl.c, 3, Hn[m.InsideElements], "nearest")
+        mu[m.InsideElements] = orc.splev(self.spl_t, self.spl_c, 3, Hn[m.InsideElements], "nearest")
         if self.kind == "reference":
             outer, inner, v = orc.ref_stiffness(m, mu)
-            orc.ref_cg(outer, inner, v, self.b, 1e-300, self.piters)
+            x = orc.ref_cg(outer, inner, v, self.b, 1e-300, self.piters)[0]
         else:
             _, _, v = orc.stiffness(m, mu, order="eigen")
-            orc.pcg(self.rp, self.ci, v, self.b, 0.0, self.piters)
+            x = orc.pcg(self.rp, self.ci, v, self.b, 0.0, self.piters)[0]
+        self.out = {"Hn": Hn, "mu": mu, "vals": v, "x": x}
+
+
+def parity_block(args, device):
+    """Outside every timed region: the step bench.py times (sweep with the Gd table + fixed-count PCG) run by the GPU
+    path and by the CPU arm on the SAME mesh and potential (Kuhn N = --cpu-n), outputs compared."""
+    import femeko_jl_b200 as fk
+
+    cs = CpuStep(args.cpu_n, args.pcg_iters)
+    cs.step()
+    m = cs.m
+    Hk, muk, _ = gd_table()
+    h = fk.Femeko(m, use_mesh_VE=cs.kind == "reference", device=device)   # the reference takes VE from its caller
+    h.set_spline(0, fk.Spline1D(Hk, muk, bc="nearest"))
+    h.set_inside(m.InsideElements)
+    h.set_mu(np.full(m.nt, MU0))
+    rp, ci = h.pattern()
+    same_pattern = bool(np.array_equal(rp, cs.rp) and np.array_equal(ci, cs.ci))
+    div = h.picard_step(cs.u, slot=0)
+    v = h.matrix_get(0)
+    x, it, _ = h.pcg(cs.b, slot=0, max_iter=args.pcg_iters, tol_disable=True, recurrence=args.recurrence)
+    _, Hn = h.get_field()
+    mu = h.get_mu()
+    rows = np.repeat(np.arange(m.nv, dtype=np.int64), np.diff(rp))
+    diag = np.zeros(m.nv)
+    on = ci == rows
+    diag[rows[on]] = np.abs(cs.out["vals"][on])
+
+    def rl2(a, b):
+        return float(np.linalg.norm(a - b) / max(np.linalg.norm(b), 1e-300))
+
+    out = {"against": f"CPU arm ({cs.kind}: FEMc.cpp stiffnessMatrix + Eigen Jacobi-CG x{args.pcg_iters}; C port of field recovery + splev) "
+                      f"on Kuhn N={args.cpu_n}, same potential",
+           "pattern_bit_exact": same_pattern,
+           "matrix_max_abs_err_over_diag": float(np.max(np.abs(v - cs.out["vals"]) / diag[rows])),
+           "mu_max_rel_err": float(np.max(np.abs(mu - cs.out["mu"]) / cs.out["mu"])),
+           "Hnorm_rel_l2": rl2(Hn, cs.out["Hn"]),
+           "x_rel_l2_after_fixed_iters": rl2(x, cs.out["x"]),
+           "div": div}
+    out["ok"] = bool(same_pattern and out["matrix_max_abs_err_over_diag"] < 1e-12 and out["mu_max_rel_err"] < 1e-12
+                     and out["x_rel_l2_after_fixed_iters"] < 1e-8)
+    h.close()
+    return out
+
+
+def cpu_solve(args):
+    """The full nonlinear solve on the host: Picard loop of manyBodyIntersecting.jl:141-210 with the compiled reference
+    stiffnessMatrix + Eigen Jacobi-CG (tol 1e-10, x0 = 0) inside, Kuhn N = --solve-n."""
+    from oracle import oracle as orc
+
+    m = mesh_module().kuhn_cube(args.solve_n, inside_edge=0.2)
+    Hk, muk, _ = gd_table()
+    tck = scipy_spline(Hk, muk)
+    t0 = time.time()
+    r = orc.picard_loop(m, [0.5, 0.0, 0.0], tck, tol=1e-4, solver="ref" if orc.have_ref() else "pcg", cg_tol=1e-10)
+    return m, r, time.time() - t0
+
+
+def solve_block(args, device, cpu=None):
+    """Time to solution of the whole nonlinear problem, both arms on the SAME problem (same mesh, table, tolerances,
+    x0 = 0 for every linear solve); the GPU arm runs through the host-pointer API like a Julia driver would."""
+    import femeko_jl_b200 as fk
+
+    m, r, cpu_s = cpu if cpu is not None else cpu_solve(args)
+    Hk, muk, _ = gd_table()
+    spl = fk.Spline1D(Hk, muk, bc="nearest")
+    h = fk.Femeko(m, device=device)
+    fk.picard(m, [0.5, 0.0, 0.0], spl, fk=h, tol=1e-10, recurrence=args.recurrence)      # warm-up (graphs, allocations)
+    t0 = time.time()
+    out = fk.picard(m, [0.5, 0.0, 0.0], spl, fk=h, tol=1e-10, recurrence=args.recurrence)
+    gpu_s = time.time() - t0
+    h.close()
+
+    def rl2(a, b):
+        return float(np.linalg.norm(a - b) / max(np.linalg.norm(b), 1e-300))
+
+    return {"workload": f"nonlinear magnetostatics to mu0*max|dH| < 1e-4 (Picard, manyBodyIntersecting.jl:141-210), Kuhn N={args.solve_n} "
+                        f"({m.nt} tets), Gd table @270K, Jacobi-CG tol 1e-10, x0 = 0",
+            "same_config": True, "gpu_seconds": round(gpu_s, 4), "cpu_seconds": round(cpu_s, 3), "cpu_cores": 1,
+            "picard_passes": [out.att, r["att"]], "cg_iterations": [out.pcg_iters, r["cg_iters"]],
+            "Hfield_rel_l2": rl2(out.Hfield, r["Hfield"]), "mu_rel_l2": rl2(out.mu, r["mu"]),
+            "note": "gpu_seconds is wall clock through the host-pointer C ABI (vectors cross PCIe every call)"}
 
 
 def cpu_baseline(args, budget_s=20.0):
@@ -441,6 +586,11 @@ def run_reference(args):
                                    f"Gd mu(H) table @270K, {args.pcg_iters} Jacobi-PCG iterations per step (fixed count, x0=0)"},
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": 1, "host_cores": os.cpu_count(), "kind": cs.kind, "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    if args.solve_n > 0:
+        m, r, secs = cpu_solve(args)
+        line["solve"] = {"workload": f"nonlinear magnetostatics to mu0*max|dH| < 1e-4, Kuhn N={args.solve_n} ({m.nt} tets), Gd table "
+                                     f"@270K, Jacobi-CG tol 1e-10, x0 = 0", "cpu_seconds": round(secs, 3), "cpu_cores": 1,
+                         "picard_passes": r["att"], "cg_iterations": r["cg_iters"], "div": r["div"]}
     print(json.dumps(line), flush=True)
 
 
@@ -454,6 +604,9 @@ def main():
     ap.add_argument("--pcg-iters", type=int, default=100)
     ap.add_argument("--cpu-n", type=int, default=48, help="Kuhn cells per edge of the bounded CPU sample")
     ap.add_argument("--cpu-budget", type=float, default=20.0)
+    ap.add_argument("--solve-n", type=int, default=32, help="Kuhn cells per edge of the full nonlinear solve timed on both arms (0: skip)")
+    ap.add_argument("--recurrence", type=int, default=1, choices=[0, 1],
+                    help="PCG recurrence: 1 = single reduction (2 kernels / iteration), 0 = Eigen's (3 kernels)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--tune", default="", help="experiments: comma-separated what=value pairs for fk_tune (e.g. 6=0)")
     ap.add_argument("--presolve", type=int, default=1, help="0: skip the untimed linear presolve (profiling runs)")

@@ -10,3 +10,4 @@ from .fem import (Femeko, SparseCSR, stiffnessMatrix, massMatrix, tangentialStif
                   localStiffnessMatrix, lagrange, BoundaryIntegral, cg, lineSearch, recoverField, Spline1D)
 from .materials import (DATA, gradient, materialPermeability, loadMaterial, synthetic_gd_like,  # noqa: F401
                         synthetic_iron_like)
+from .magnetostatics import picard, newton_raphson, NonlinearResult  # noqa: F401

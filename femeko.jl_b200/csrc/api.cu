@@ -496,15 +496,19 @@ static void pcg_dev(fk_handle h, int slot, const double* b_dev, double* x_dev, c
     FK_CUDA(cudaMemsetAsync(h->x.ptr, 0, sizeof(double) * (size_t)n, s));
   }
   const unsigned long long epoch = ++h->pcg_epoch;
+  // in-iteration projection of the residual's mean: one GPU (either recurrence) or the single-reduction recurrence on
+  // partitions (its fused reduction carries the fourth value); the two-reduction partitioned path only projects b and x
+  const int proj = (opt.project_nullspace && (!h->comm || rec == 1)) ? 1 : 0;
+  const double inv_n = 1.0 / (double)n_glob;
   if (rec == 1) {
     const CgParts cp = cg_parts(h);
     const int g2 = h->grid_pcg;
     cg_init_kernel<<<g2, kVecThreads, 0, s>>>(b_dev, Ax0, h->dinv.ptr, n, h->r.ptr, h->z.ptr, cp.A, cp.M);   // partials of (r.z, r.r, b.b)
     if (h->comm) {
       comm_allreduce_partials(h, s, cp.A, g2, cp.M, 3, 0, h->scal.ptr + 4, nullptr, 0);   // -> scal[4..6] over every rank
-      pcg_init_fin_kernel<<<1, 256, 0, s>>>(h->scal.ptr + 6, h->scal.ptr + 5, h->scal.ptr + 4, 1, tol, max_iter, epoch, h->ctl.ptr);
+      pcg_init_fin_kernel<<<1, 256, 0, s>>>(h->scal.ptr + 6, h->scal.ptr + 5, h->scal.ptr + 4, 1, tol, max_iter, epoch, proj, inv_n, h->ctl.ptr);
     } else {
-      pcg_init_fin_kernel<<<1, 256, 0, s>>>(cp.A + 2 * (size_t)cp.M, cp.A + cp.M, cp.A, g2, tol, max_iter, epoch, h->ctl.ptr);
+      pcg_init_fin_kernel<<<1, 256, 0, s>>>(cp.A + 2 * (size_t)cp.M, cp.A + cp.M, cp.A, g2, tol, max_iter, epoch, proj, inv_n, h->ctl.ptr);
     }
     launch_cg_spmv(h, s, h->vals[slot].ptr, h->ctl.ptr, 0);   // w0 = A z0, delta partials (and the first halo exchange)
     h->launches++;
@@ -512,10 +516,10 @@ static void pcg_dev(fk_handle h, int slot, const double* b_dev, double* x_dev, c
     pcg_init_kernel<<<gv, kVecThreads, 0, s>>>(b_dev, Ax0, h->dinv.ptr, n, h->r.ptr, h->p.ptr, h->part.ptr,
                                                comm_red_args(h, h->tickets.ptr + 2, h->scal.ptr + 4, 0));   // -> scal[4..6] = b.b, r.r, r.p
     comm_nccl_allreduce(h, s, h->scal.ptr + 4, 3, 0);
-    pcg_init_fin_kernel<<<1, 256, 0, s>>>(h->scal.ptr + 4, h->scal.ptr + 5, h->scal.ptr + 6, 1, tol, max_iter, epoch, h->ctl.ptr);
+    pcg_init_fin_kernel<<<1, 256, 0, s>>>(h->scal.ptr + 4, h->scal.ptr + 5, h->scal.ptr + 6, 1, tol, max_iter, epoch, 0, 0.0, h->ctl.ptr);
   } else {
     pcg_init_kernel<<<gv, kVecThreads, 0, s>>>(b_dev, Ax0, h->dinv.ptr, n, h->r.ptr, h->p.ptr, h->part.ptr, RedArgs{});
-    pcg_init_fin_kernel<<<1, 256, 0, s>>>(h->part.ptr, h->part.ptr + gv, h->part.ptr + 2 * (size_t)gv, gv, tol, max_iter, epoch, h->ctl.ptr);
+    pcg_init_fin_kernel<<<1, 256, 0, s>>>(h->part.ptr, h->part.ptr + gv, h->part.ptr + 2 * (size_t)gv, gv, tol, max_iter, epoch, proj, inv_n, h->ctl.ptr);
   }
   FK_CUDA(cudaGetLastError());
   h->launches += 3;
@@ -554,7 +558,7 @@ static void pcg_dev(fk_handle h, int slot, const double* b_dev, double* x_dev, c
   const int iters = c.done ? c.iters : max_iter;
   if (c.rhs2 == 0.0) {  // x = 0 (ConjugateGradient.h:43-49)
     FK_CUDA(cudaMemsetAsync(x_dev, 0, sizeof(double) * (size_t)n, s));
-  } else if (opt.project_nullspace) {   // x <- x - (w.x / sum w)
+  } else if (opt.project_nullspace == 1) {   // x <- x - (w.x / sum w)
     ns_sums(h, s, h->x.ptr, w_ns, 1, h->scal.ptr + 8);
     ns_apply_kernel<<<gv, kVecThreads, 0, s>>>(h->x.ptr, nullptr, n, 1, h->scal.ptr + 8, x_dev);
     FK_CUDA(cudaGetLastError());
@@ -1220,6 +1224,103 @@ int fk_pcg(fk_handle h, int slot, const double* b, double* x, const fk_pcg_opts*
   });
 }
 
+// ||b - A x|| (and the residual itself) over every rank; x_dev must be a vector of nv entries (halo rows are refreshed)
+static double residual_dev(fk_handle h, int slot, const double* x_dev, const double* b_dev, double* r_dev) {
+  check_slot(slot);
+  need(h->vals[slot].ptr != nullptr, "fk_residual: matrix slot has not been assembled");
+  ensure_pcg(h);
+  cudaStream_t s = h->stream;
+  const double* xin = x_dev;
+  if (h->comm) {   // the product reads halo rows: stage x in a slab vector and exchange
+    FK_CUDA(cudaMemcpyAsync(h->z.ptr, x_dev, sizeof(double) * (size_t)h->n_rows, cudaMemcpyDeviceToDevice, s));
+    comm_halo_exchange(h, s, h->z.ptr);
+    xin = h->z.ptr;
+  }
+  launch_spmv(h, s, h->vals[slot].ptr, xin, h->Ap.ptr, false, nullptr, 0);
+  const int g = h->grid_vec;
+  residual_kernel<<<g, kVecThreads, 0, s>>>(b_dev, h->Ap.ptr, h->n_rows, r_dev, h->part.ptr);
+  FK_CUDA(cudaGetLastError());
+  h->launches += 2;
+  comm_allreduce_partials(h, s, h->part.ptr, g, g, 1, 0, h->scal.ptr + 10, nullptr, 0);
+  if (!h->pin8) FK_CUDA(cudaMallocHost((void**)&h->pin8, 16 * sizeof(double)));
+  FK_CUDA(cudaMemcpyAsync(h->pin8 + 10, h->scal.ptr + 10, sizeof(double), cudaMemcpyDeviceToHost, s));
+  FK_CUDA(cudaStreamSynchronize(s));
+  return std::sqrt(h->pin8[10]);
+}
+int fk_residual_dev(fk_handle h, int slot, const double* x_dev, const double* b_dev, double* r_dev, double* norm_out) {
+  return guard([&]() {
+    need(h && x_dev && b_dev, "fk: NULL argument");
+    DeviceGuard dg(h->device);
+    const double nr = residual_dev(h, slot, x_dev, b_dev, r_dev);
+    if (norm_out) *norm_out = nr;
+    return 0;
+  });
+}
+int fk_residual(fk_handle h, int slot, const double* x, const double* b, double* r, double* norm_out) {
+  return guard([&]() {
+    need(h && x && b, "fk: NULL argument");
+    DeviceGuard dg(h->device);
+    h->st_c.upload(x, (size_t)h->nv, h->stream);
+    h->st_a.upload(b, (size_t)h->n_rows, h->stream);
+    h->st_d.ensure((size_t)h->nv);
+    const double nr = residual_dev(h, slot, h->st_c.ptr, h->st_a.ptr, r ? h->st_d.ptr : nullptr);
+    if (norm_out) *norm_out = nr;
+    if (r) copy_out(h, h->st_d.ptr, r, (size_t)h->n_rows);
+    return 0;
+  });
+}
+
+// lineSearch of src/FEM3D.jl:123-152 (same trial sequence, same acceptance rule); every vector stays on the device
+static void line_search_dev(fk_handle h, int slot, double* u_dev, const double* du_dev, const double* rhs_dev, double min_step,
+                            double* residue_out, double* alpha_out) {
+  if (!(min_step > 0.0)) min_step = 1e-4;
+  cudaStream_t s = h->stream;
+  const int n = h->n_rows;
+  const int g = std::min(cdiv(std::max(n, 1), 256), h->num_sms * 8);
+  h->bproj.ensure((size_t)h->nv);   // trial vector
+  double* trial = h->bproj.ptr;
+  const double residual_old = residual_dev(h, slot, u_dev, rhs_dev, nullptr);
+  double alf = 1.0;
+  axpby_kernel<<<g, 256, 0, s>>>(trial, 1.0, u_dev, alf, du_dev, n);
+  double residue = residual_dev(h, slot, trial, rhs_dev, nullptr);
+  while (residue > residual_old && alf > min_step) {
+    alf *= 0.9;
+    axpby_kernel<<<g, 256, 0, s>>>(trial, 1.0, u_dev, alf, du_dev, n);
+    h->launches++;
+    residue = residual_dev(h, slot, trial, rhs_dev, nullptr);
+  }
+  h->launches++;
+  if (alf < min_step) {
+    alf = 0.0;   // "N-R could not decrease the residue further": u is left as it was
+  } else {
+    FK_CUDA(cudaMemcpyAsync(u_dev, trial, sizeof(double) * (size_t)n, cudaMemcpyDeviceToDevice, s));
+  }
+  if (residue_out) *residue_out = residue;
+  if (alpha_out) *alpha_out = alf;
+}
+int fk_line_search_dev(fk_handle h, int slot, double* u_dev, const double* du_dev, const double* rhs_dev, double min_step,
+                       double* residue_out, double* alpha_out) {
+  return guard([&]() {
+    need(h && u_dev && du_dev && rhs_dev, "fk: NULL argument");
+    DeviceGuard dg(h->device);
+    line_search_dev(h, slot, u_dev, du_dev, rhs_dev, min_step, residue_out, alpha_out);
+    return 0;
+  });
+}
+int fk_line_search(fk_handle h, int slot, double* u, const double* du, const double* rhs, double min_step, double* residue_out,
+                   double* alpha_out) {
+  return guard([&]() {
+    need(h && u && du && rhs, "fk: NULL argument");
+    DeviceGuard dg(h->device);
+    h->st_c.upload(u, (size_t)h->nv, h->stream);
+    h->st_a.upload(rhs, (size_t)h->n_rows, h->stream);
+    h->st_b.upload(du, (size_t)h->n_rows, h->stream);
+    line_search_dev(h, slot, h->st_c.ptr, h->st_b.ptr, h->st_a.ptr, min_step, residue_out, alpha_out);
+    copy_out(h, h->st_c.ptr, u, (size_t)h->n_rows);
+    return 0;
+  });
+}
+
 // ---- field recovery / nonlinear step --------------------------------------------------------------
 int fk_recover_field_dev(fk_handle h, const double* u_dev, const double* mu_dev, int compat_bug, double* Hfield_dev,
                          double* Hnorm_dev, double* B_dev) {
@@ -1326,6 +1427,39 @@ int fk_set_spline(fk_handle h, int id, const double* t, const double* c, int n, 
     FK_CUDA(cudaStreamSynchronize(h->stream));
     h->spl.s[id] = SplineDev{h->spl_t[id].ptr, h->spl_c[id].ptr, n, k, bc};
     return 0;
+  });
+}
+
+static int spline_apply_dev(fk_handle h, int id, const double* x_dev, int nx, double* y_dev) {
+  need(id >= 0 && id < FK_MAX_SPLINES && h->spl.s[id].n > 0, "fk_spline_apply: table has not been set (fk_set_spline)");
+  if (nx <= 0) return 0;
+  h->errflag.ensure(1);
+  FK_CUDA(cudaMemsetAsync(h->errflag.ptr, 0, sizeof(int), h->stream));
+  splev_kernel<<<cdiv(nx, 256), 256, 0, h->stream>>>(h->spl.s[id], x_dev, nx, y_dev, h->errflag.ptr);
+  FK_CUDA(cudaGetLastError());
+  h->launches++;
+  int err = 0;
+  FK_CUDA(cudaMemcpyAsync(&err, h->errflag.ptr, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+  FK_CUDA(cudaStreamSynchronize(h->stream));
+  if (err) { set_error("fk_spline_apply: argument outside the knot range with bc = error"); return 2; }
+  return 0;
+}
+int fk_spline_apply_dev(fk_handle h, int id, const double* x_dev, int nx, double* y_dev) {
+  return guard([&]() {
+    need(h && x_dev && y_dev, "fk: NULL argument");
+    DeviceGuard dg(h->device);
+    return spline_apply_dev(h, id, x_dev, nx, y_dev);
+  });
+}
+int fk_spline_apply(fk_handle h, int id, const double* x, int nx, double* y_out) {
+  return guard([&]() {
+    need(h && x && y_out && nx >= 0, "fk: NULL argument");
+    DeviceGuard dg(h->device);
+    h->st_a.upload(x, (size_t)nx, h->stream);
+    h->st_b.ensure((size_t)std::max(nx, 1));
+    const int rc = spline_apply_dev(h, id, h->st_a.ptr, nx, h->st_b.ptr);
+    copy_out(h, h->st_b.ptr, y_out, (size_t)nx);
+    return rc;
   });
 }
 
@@ -1711,7 +1845,12 @@ void scalarPotential(double* u_in, double* p_in, int* t_in, int* surfaceT_in, do
     for (int i = 0; i < nv; i++) rhs[i] = -rhs[i];
     int iters = 0;
     double relres = 0.0;
-    rc = fk_pcg(h, 0, rhs.data(), u_in, nullptr, &iters, &relres);
+    // Eigen's defaults (tol = machine epsilon, 2n iterations, x0 = 0) like magnetostatics.cpp:26-38.  The system is
+    // the singular pure-Neumann one: the residual's null-space component (rounding of sum(b) and of every A p) is
+    // projected out so the recursion can actually reach epsilon; the iterate itself is not shifted.
+    fk_pcg_opts po{};
+    po.project_nullspace = 2;
+    rc = fk_pcg(h, 0, rhs.data(), u_in, &po, &iters, &relres);
     if (!rc && !(relres <= DBL_EPSILON))
       std::fprintf(stderr, "femeko_cuda scalarPotential: PCG stopped after %d iterations at relative residual %.3e "
                            "(Eigen's default tolerance is machine epsilon; the reference throws here)\n", iters, relres);

@@ -123,7 +123,7 @@ constexpr int kOffMail2 = kOffHaloCnt + 1;
 // single-reduction recurrence (cg_update_kernel / fused SpMV): halo flags of the in-kernel exchange and a mailbox of
 // 3 values + sequence flag per (slot, rank)
 constexpr int kOffHalo2 = kOffMail2 + 2 * kMaxRanks * kMail2Words;
-constexpr int kMail3Words = 4;
+constexpr int kMail3Words = 5;   // 4 values + sequence flag
 constexpr int kOffMail3 = kOffHalo2 + kMaxNeigh;
 constexpr int kCtrlWords = 512;
 static_assert(kOffMail3 + 4 * kMaxRanks * kMail3Words <= kCtrlWords, "control block too small");
@@ -295,34 +295,34 @@ __device__ __forceinline__ void peer_fold(double (&v)[NV], const PeerRed& pr, un
   __syncthreads();
 }
 
-// Three values (the single fused reduction of the single-reduction recurrence), same protocol as peer_fold on its own
+// Four values (gamma, r.r, delta, sum r: the single fused reduction of the single-reduction recurrence), same protocol as peer_fold on its own
 // mailbox; consecutive reductions alternate slots by the parity of seq, consecutive solves by the parity of the epoch
 // (a rank two hops away may start its next solve while a slow CTA here still reads the last reduction of this one).
-__device__ __forceinline__ void peer_fold3(double (&v)[3], const PeerRed& pr, unsigned long long seq, int epoch_parity) {
+__device__ __forceinline__ void peer_fold3(double (&v)[4], const PeerRed& pr, unsigned long long seq, int epoch_parity) {
   if (pr.nranks <= 1) return;
-  __shared__ double sh3[3 * kMaxRanks];
+  __shared__ double sh3[4 * kMaxRanks];
   const int slot = (int)(seq & 1ULL) + 2 * epoch_parity, t = threadIdx.x;   // four slots: a solve never reuses its predecessor's
   if (t < pr.nranks) {
     if (t == pr.rank) {
 #pragma unroll
-      for (int k = 0; k < 3; k++) sh3[k * kMaxRanks + t] = v[k];
+      for (int k = 0; k < 4; k++) sh3[k * kMaxRanks + t] = v[k];
     } else {
       if (blockIdx.x == 0) {
         unsigned long long* box = pr.peer_ctrl[t] + kOffMail3 + ((size_t)slot * kMaxRanks + pr.rank) * kMail3Words;
 #pragma unroll
-        for (int k = 0; k < 3; k++) reinterpret_cast<double*>(box)[k] = v[k];
+        for (int k = 0; k < 4; k++) reinterpret_cast<double*>(box)[k] = v[k];
         __threadfence_system();
         st_release_sys(box + kMail3Words - 1, seq);
       }
       const unsigned long long* box = pr.my_ctrl + kOffMail3 + ((size_t)slot * kMaxRanks + t) * kMail3Words;
       spin_until_relaxed(box + kMail3Words - 1, seq, pr.my_ctrl + kOffErr);
 #pragma unroll
-      for (int k = 0; k < 3; k++) sh3[k * kMaxRanks + t] = reinterpret_cast<const volatile double*>(box)[k];
+      for (int k = 0; k < 4; k++) sh3[k * kMaxRanks + t] = reinterpret_cast<const volatile double*>(box)[k];
     }
   }
   __syncthreads();
 #pragma unroll
-  for (int k = 0; k < 3; k++) {
+  for (int k = 0; k < 4; k++) {
     double s = 0.0;
     for (int r = 0; r < pr.nranks; r++) s += sh3[k * kMaxRanks + r];
     v[k] = s;
@@ -475,6 +475,15 @@ static __global__ void __launch_bounds__(256) material_update_kernel(const doubl
   if (threadIdx.x == 0) part_max[blockIdx.x] = dmax;
 }
 
+// y = spl(x) on the device (fk_spline_apply): the same splev_dev the Picard pre-pass calls
+static __global__ void splev_kernel(const SplineDev S, const double* __restrict__ x, int n, double* __restrict__ y, int* __restrict__ errflag) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  int err = 0;
+  y[i] = splev_dev(S, x[i], err);
+  if (err) atomicOr(errflag, err);
+}
+
 // dense 16 x nt local stiffness (localStiffnessMatrix, src/FEM3D.jl:59-76) -- API completeness
 static __global__ void local_stiffness_kernel(const double4* __restrict__ p4, const int4* __restrict__ t4,
                                        const double* __restrict__ VE, const double* __restrict__ f, int nt,
@@ -530,6 +539,10 @@ struct PcgCtl {
   int base_it, max_iter, done, iters;
   unsigned long long epoch;   // solve counter (same on every rank): high half of the peer_fold sequence numbers
   double gamma[2], alpha[2];  // single-reduction recurrence: (r,u) and alpha of the previous / current iteration (ping-pong)
+  // fk_pcg_opts.project_nullspace: the mean of r (rounding drift out of range(A) on a singular Neumann system) measured by
+  // one iteration is subtracted by the next one, so the recursive residual can fall to the requested tolerance
+  double rmean[2], inv_n;
+  int proj;
 };
 
 __device__ __forceinline__ unsigned long long pcg_seq(const PcgCtl* c, int j, int which) {
@@ -586,7 +599,8 @@ static __global__ void __launch_bounds__(kVecThreads) pcg_init_kernel(const doub
 // single block: fold the partials of (b.b, r.r, r.p) (npart == 1: already reduced scalars) -> thresholds and
 // the early exits of ConjugateGradient.h:43-56
 static __global__ void pcg_init_fin_kernel(const double* __restrict__ pbb, const double* __restrict__ prr, const double* __restrict__ prp,
-                                    int npart, double tol, int max_iter, unsigned long long epoch, PcgCtl* ctl) {
+                                    int npart, double tol, int max_iter, unsigned long long epoch, int proj, double inv_n,
+                                    PcgCtl* ctl) {
   __shared__ double red[33];
   const double bb = block_sum_array(pbb, npart, red);
   const double rr = block_sum_array(prr, npart, red);
@@ -601,6 +615,9 @@ static __global__ void pcg_init_fin_kernel(const double* __restrict__ pbb, const
     ctl->max_iter = max_iter;
     ctl->iters = 0;
     ctl->epoch = epoch;
+    ctl->proj = proj;
+    ctl->inv_n = inv_n;
+    ctl->rmean[0] = ctl->rmean[1] = 0.0;
     ctl->done = (bb == 0.0 || rr < ctl->thr) ? 1 : 0;
   }
 }
@@ -642,7 +659,9 @@ static __global__ void __launch_bounds__(kVecThreads, kPcgVecCtas) pcg_update_ke
   double pAp_v[1] = {block_sum_array(part_pAp, npart, red_s)};   // npart == 1: the all-reduced scalar (NCCL path)
   peer_fold<1>(pAp_v, pr, pcg_seq(ctl, j, 0));
   const double alpha = ctl->absNew[j & 1] / pAp_v[0];
-  double s_rr = 0.0, s_rz = 0.0;
+  const bool proj = ctl->proj != 0;
+  const double m_prev = proj ? ctl->rmean[j & 1] : 0.0;   // mean of r after the previous update
+  double s_rr = 0.0, s_rz = 0.0, s_r = 0.0;
   while (i0 < n2) {
 #pragma unroll
     for (int u = 0; u < kVecUnroll; u++) {
@@ -652,6 +671,7 @@ static __global__ void __launch_bounds__(kVecThreads, kPcgVecCtas) pcg_update_ke
         xv[u].y += alpha * pv[u].y;
         rv[u].x -= alpha * av[u].x;
         rv[u].y -= alpha * av[u].y;
+        if (proj) { rv[u].x -= m_prev; rv[u].y -= m_prev; s_r += rv[u].x + rv[u].y; }
         x2[i] = xv[u];
         r2[i] = rv[u];
         s_rr += rv[u].x * rv[u].x;
@@ -666,10 +686,15 @@ static __global__ void __launch_bounds__(kVecThreads, kPcgVecCtas) pcg_update_ke
   if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) {   // odd row count: the last row
     const int i = n - 1;
     x[i] += alpha * p[i];
-    const double ri = r[i] - alpha * Ap[i];
+    const double ri = r[i] - alpha * Ap[i] - m_prev;
     r[i] = ri;
     s_rr += ri * ri;
     s_rz += ri * (dinv[i] * ri);
+    s_r += ri;
+  }
+  if (proj) {   // third partial: sum r (single GPU / publish-only layouts: row 2 of part2)
+    s_r = block_sum(s_r, red_s);
+    if (threadIdx.x == 0) part2[2 * (size_t)gridDim.x + blockIdx.x] = s_r;
   }
   block_sum2(s_rr, s_rz, red_s);
   const double v[2] = {s_rr, s_rz};
@@ -705,6 +730,10 @@ static __global__ void __launch_bounds__(kVecThreads, kPcgVecCtas) pcg_direction
   const double rr = d2v[0], rz = d2v[1];
   const double absOld = ctl->absNew[j & 1];
   const bool conv = rr < ctl->thr;
+  if (ctl->proj) {   // uniform: every CTA takes the same branch
+    const double sr = block_sum_array(part2 + 2 * (size_t)stride, npart, red);
+    if (blockIdx.x == 0 && threadIdx.x == 0) ctl->rmean[(j + 1) & 1] = sr * ctl->inv_n;
+  }
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     ctl->r2 = rr;
     if (conv) { ctl->iters = ctl->base_it + j; ctl->done = 1; }
@@ -798,11 +827,14 @@ static __global__ void __launch_bounds__(kVecThreads, kPcgVecCtas) cg_update_ker
   };
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   load(i);   // in flight during the fold
-  double v3[3];
+  const bool proj = ctl->proj != 0;
+  double v3[4];
   block_sum2_array(part_in, part_in + stride, npv, red_s, v3[0], v3[1]);
   v3[2] = block_sum_array(part_s, nps, red_s);
+  v3[3] = (proj && !first) ? block_sum_array(part_in + 2 * (size_t)stride, npv, red_s) : 0.0;   // sum r of the current residual
   peer_fold3(v3, pr, cg_seq(ctl, it), (int)(ctl->epoch & 1ULL));
   const double gamma = v3[0], rr = v3[1], delta = v3[2];
+  const double m_prev = v3[3] * ctl->inv_n;   // mean of the current r: taken out by this update
   const bool conv = rr < ctl->thr;
   double alpha, beta = 0.0;
   if (first) alpha = gamma / delta;
@@ -816,7 +848,7 @@ static __global__ void __launch_bounds__(kVecThreads, kPcgVecCtas) cg_update_ker
     else { ctl->gamma[it & 1] = gamma; ctl->alpha[it & 1] = alpha; }
   }
   if (conv) return;
-  double s_rr = 0.0, s_rz = 0.0;
+  double s_rr = 0.0, s_rz = 0.0, s_r = 0.0;
   while (i < n2) {
     const double zx = dv.x * rv.x, zy = dv.y * rv.y;   // u = M^-1 r of the current residual (== z[i])
     if (first) { pv.x = zx; pv.y = zy; sv2 = wv; }
@@ -826,6 +858,7 @@ static __global__ void __launch_bounds__(kVecThreads, kPcgVecCtas) cg_update_ker
     }
     xv.x += alpha * pv.x; xv.y += alpha * pv.y;
     rv.x -= alpha * sv2.x; rv.y -= alpha * sv2.y;
+    if (proj) { rv.x -= m_prev; rv.y -= m_prev; s_r += rv.x + rv.y; }
     const double2 zn = make_double2(dv.x * rv.x, dv.y * rv.y);
     p2[i] = pv; s2[i] = sv2; x2[i] = xv; r2[i] = rv; z2[i] = zn;
     s_rr += rv.x * rv.x; s_rz += rv.x * zn.x;
@@ -840,11 +873,16 @@ static __global__ void __launch_bounds__(kVecThreads, kPcgVecCtas) cg_update_ker
     const double sq = first ? w[q] : w[q] + beta * sv[q];
     p[q] = pq; sv[q] = sq;
     x[q] += alpha * pq;
-    const double rq = r[q] - alpha * sq;
+    const double rq = r[q] - alpha * sq - (proj ? m_prev : 0.0);
     r[q] = rq;
     const double zn = dinv[q] * rq;
     z[q] = zn;
     s_rr += rq * rq; s_rz += rq * zn;
+    s_r += rq;
+  }
+  if (proj) {
+    s_r = block_sum(s_r, red_s);
+    if (threadIdx.x == 0) part_out[2 * (size_t)stride + blockIdx.x] = s_r;
   }
   block_sum2(s_rz, s_rr, red_s);
   if (threadIdx.x == 0) { part_out[blockIdx.x] = s_rz; part_out[stride + blockIdx.x] = s_rr; }
@@ -862,9 +900,10 @@ static __global__ void __launch_bounds__(256) cg_chunk_end_kernel(const double* 
   if (tail) {
     const int itd = ctl->max_iter;   // updates made
     const double* part_in = (itd & 1) ? partB : partA;
-    double v3[3];
+    double v3[4];
     block_sum2_array(part_in, part_in + stride, npv, red_s, v3[0], v3[1]);
     v3[2] = 0.0;
+    v3[3] = 0.0;
     peer_fold3(v3, pr, cg_seq(ctl, itd), (int)(ctl->epoch & 1ULL));   // V_itd never runs: the sequence number is free
     if (threadIdx.x == 0) {
       ctl->r2 = v3[1];
@@ -886,6 +925,20 @@ static __global__ void fold_partials_kernel(const double* __restrict__ part, int
     const double s = block_sum_array(part + (size_t)v * stride, npart, red);
     if (threadIdx.x == 0) out[v] = s;
   }
+}
+
+// r = b - Ax (r nullable), per-CTA partials of ||b - Ax||^2  (lineSearch / Newton right-hand side, src/FEM3D.jl:128-139)
+static __global__ void __launch_bounds__(kVecThreads) residual_kernel(const double* __restrict__ b, const double* __restrict__ Ax, int n,
+                                                               double* __restrict__ r, double* __restrict__ part) {
+  __shared__ double red_s[33];
+  double s = 0.0;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const double v = b[i] - Ax[i];
+    if (r) r[i] = v;
+    s += v * v;
+  }
+  s = block_sum(s, red_s);
+  if (threadIdx.x == 0) part[blockIdx.x] = s;
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -238,6 +238,26 @@ class Femeko:
         L.check(self.lib.fk_pcg(self.h, slot, L.dptr(b), L.dptr(x), C.byref(o), C.byref(it), C.byref(rr)))
         return x, it.value, rr.value
 
+    def residual(self, x, b, slot=0, want_r=True):
+        """r = b - A x and its 2-norm (the `RHS - A*u` of NewtonRaphson.jl:166)."""
+        x = np.ascontiguousarray(x, dtype=np.float64)
+        b = np.ascontiguousarray(b, dtype=np.float64)
+        assert x.shape[0] >= self.nv and b.shape[0] >= self.n_rows
+        r = np.zeros(self.nv) if want_r else None
+        nr = C.c_double()
+        L.check(self.lib.fk_residual(self.h, slot, L.dptr(x), L.dptr(b), L.dptr(r), C.byref(nr)))
+        return (r, nr.value) if want_r else nr.value
+
+    def line_search(self, u, du, rhs, slot=0, min_step=1e-4):
+        """lineSearch(u, du, A, RHS) of src/FEM3D.jl:123-152 on the device; updates u in place.
+        Returns (residue, accepted step; 0 = u unchanged)."""
+        assert u.dtype == np.float64 and u.flags.c_contiguous and u.shape[0] >= self.nv
+        du = np.ascontiguousarray(du, dtype=np.float64)
+        rhs = np.ascontiguousarray(rhs, dtype=np.float64)
+        res, alf = C.c_double(), C.c_double()
+        L.check(self.lib.fk_line_search(self.h, slot, L.dptr(u), L.dptr(du), L.dptr(rhs), float(min_step), C.byref(res), C.byref(alf)))
+        return res.value, alf.value
+
     # -- field recovery / nonlinear -------------------------------------------------------------
     def recover_field(self, u, mu=None, compat_bug=False, want_B=True):
         u = np.ascontiguousarray(u, dtype=np.float64)
@@ -251,6 +271,13 @@ class Femeko:
 
     def set_spline(self, table_id, spl: "Spline1D"):
         L.check(self.lib.fk_set_spline(self.h, table_id, L.dptr(spl.t), L.dptr(spl.c), len(spl.t), spl.k, L.BC[spl.bc]))
+
+    def spline_apply(self, table_id, x):
+        """spl(x) evaluated by the device splev (what the Picard pre-pass evaluates per element)."""
+        xv = np.ascontiguousarray(x, dtype=np.float64).ravel()
+        y = np.zeros(xv.size)
+        L.check(self.lib.fk_spline_apply(self.h, int(table_id), L.dptr(xv), int(xv.size), L.dptr(y)))
+        return y.reshape(np.shape(x))
 
     def set_inside(self, ids):
         ids = np.ascontiguousarray(ids, dtype=np.int32)
@@ -437,20 +464,12 @@ def cg(A: SparseCSR, b, Pl="jacobi", reltol=None, maxiter=None, x0=None, log=Fal
 
 
 def lineSearch(u, du, A: SparseCSR, RHS, minStep: float = 1e-4):
-    """Backtracking of src/FEM3D.jl:123-152; updates u in place, returns the residual norm."""
+    """Backtracking of src/FEM3D.jl:123-152 (fk_line_search: trial vectors, products and norms stay on the GPU);
+    updates u in place, returns the residual norm."""
     A._sync()
-    alf = 1.0
-    residual_old = np.linalg.norm(RHS - A.fk.spmv(u, A.slot))
-    u_trial = u + du
-    residue = np.linalg.norm(RHS - A.fk.spmv(u_trial, A.slot))
-    while residue > residual_old and alf > minStep:
-        alf *= 0.9
-        u_trial = u + alf * du
-        residue = np.linalg.norm(RHS - A.fk.spmv(u_trial, A.slot))
-    if alf < minStep:
+    residue, alf = A.fk.line_search(u, du, RHS, slot=A.slot, min_step=minStep)
+    if alf == 0.0:
         print("Warning: N-R could not decrease the residue further")
-    else:
-        u[:] = u_trial
     return residue
 
 

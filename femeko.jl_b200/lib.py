@@ -96,6 +96,8 @@ _SIGS = {
     "fk_spline_fit": (C.c_int, [c_double_p, c_double_p, C.c_int, c_double_p, c_double_p]),
     "fk_spline_eval": (C.c_int, [c_double_p, c_double_p, C.c_int, C.c_int, C.c_int, c_double_p, C.c_int, c_double_p]),
     "fk_set_spline": (C.c_int, [_H, C.c_int, c_double_p, c_double_p, C.c_int, C.c_int, C.c_int]),
+    "fk_spline_apply": (C.c_int, [_H, C.c_int, c_double_p, C.c_int, c_double_p]),
+    "fk_spline_apply_dev": (C.c_int, [_H, C.c_int, C.c_void_p, C.c_int, C.c_void_p]),
     "fk_set_material": (C.c_int, [_H, c_ubyte_p]),
     "fk_set_inside": (C.c_int, [_H, c_int_p, C.c_int]),
     "fk_set_mu": (C.c_int, [_H, c_double_p]),
@@ -104,6 +106,10 @@ _SIGS = {
     "fk_reset_field": (C.c_int, [_H]),
     "fk_picard_step": (C.c_int, [_H, C.c_int, c_double_p, C.c_int, c_double_p]),
     "fk_picard_step_dev": (C.c_int, [_H, C.c_int, C.c_void_p, C.c_int, c_double_p]),
+    "fk_residual": (C.c_int, [_H, C.c_int, c_double_p, c_double_p, c_double_p, c_double_p]),
+    "fk_residual_dev": (C.c_int, [_H, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, c_double_p]),
+    "fk_line_search": (C.c_int, [_H, C.c_int, c_double_p, c_double_p, c_double_p, C.c_double, c_double_p, c_double_p]),
+    "fk_line_search_dev": (C.c_int, [_H, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_double, c_double_p, c_double_p]),
     "fk_picard_result": (C.c_int, [_H, c_double_p]),
     "fk_set_dirichlet": (C.c_int, [_H, c_int_p, C.c_int, c_double_p]),
     "fk_apply_dirichlet": (C.c_int, [_H, C.c_int, c_double_p]),

@@ -63,7 +63,9 @@ typedef struct fk_pcg_opts {
   int project_nullspace;/* 1: singular Neumann systems (constants in the null space): b <- b - (sum b / sum w) w before the
                            solve and x <- x - (w.x / sum w) after it, w = fk_set_nullspace weights (default ones) -- with
                            w = lagrange(mesh) this is the solution of the reference's bordered system [A C; C' 0]
-                           (magneticField.jl:99-107, NewtonRaphson.jl:166)                                                */
+                           (magneticField.jl:99-107, NewtonRaphson.jl:166).  During the iteration the mean of r (rounding
+                           drift out of range(A)) is removed one iteration late, so the recursive residual can reach tol.
+                           2: the same without the final shift of x (the iterate Eigen's loop would return)               */
 } fk_pcg_opts;
 
 const char* fk_last_error(void);
@@ -168,6 +170,18 @@ int fk_pcg(fk_handle h, int slot, const double* b, double* x, const fk_pcg_opts*
 int fk_pcg_dev(fk_handle h, int slot, const double* b_dev, double* x_dev, const fk_pcg_opts* opts,
                int* iters_out, double* relres_out);
 
+/* r = b - A x (NewtonRaphson.jl:166 `RHS-A*u`); r may be NULL; norm_out (may be NULL) = ||b - A x||_2 over the owned rows */
+int fk_residual(fk_handle h, int slot, const double* x, const double* b, double* r, double* norm_out);
+int fk_residual_dev(fk_handle h, int slot, const double* x_dev, const double* b_dev, double* r_dev, double* norm_out);
+/* lineSearch(u, du, A, RHS, minStep) of src/FEM3D.jl:123-152, entirely on the device: alpha = 1, then alpha *= 0.9
+ * while ||RHS - A (u + alpha du)|| > ||RHS - A u|| and alpha > min_step (<= 0: the reference's 1e-4); u is updated in
+ * place unless alpha fell below min_step (the reference's "could not decrease the residue" branch).  Returns the residue
+ * of the last trial and the accepted step (0 = u left unchanged).                                                     */
+int fk_line_search(fk_handle h, int slot, double* u, const double* du, const double* rhs, double min_step,
+                   double* residue_out, double* alpha_out);
+int fk_line_search_dev(fk_handle h, int slot, double* u_dev, const double* du_dev, const double* rhs_dev, double min_step,
+                       double* residue_out, double* alpha_out);
+
 /* ---- constraints ------------------------------------------------------------------------------
  * Dirichlet elimination as the reference drivers do it on the assembled system (Fluids/fluids3D.jl:142-174:
  * `RHS = -LHS[free,fixed]*gD[fixed]; UP[fixed] = gD[fixed]; UP[free] = LHS[free,free] \ RHS`), kept on the full
@@ -198,6 +212,10 @@ int fk_spline_fit(const double* x, const double* y, int m, double* t_out /* m+4 
 int fk_spline_eval(const double* t, const double* c, int n, int k, int bc, const double* x, int nx,
                    double* y_out);   /* host splev (FITPACK fpbspl), returns 2 if bc=error and out of range */
 int fk_set_spline(fk_handle h, int id, const double* t, const double* c, int n, int k, int bc);
+/* y = spl_id(x) evaluated by the DEVICE splev (the call `spl(H[mesh.InsideElements])` of NewtonRaphson.jl:203); returns 2
+ * if bc = error and an argument lies outside the knots.  x, y: host (fk_spline_apply) or device (fk_spline_apply_dev).  */
+int fk_spline_apply(fk_handle h, int id, const double* x, int nx, double* y_out);
+int fk_spline_apply_dev(fk_handle h, int id, const double* x_dev, int nx, double* y_dev);
 /* material of every element: 0 = linear (mu untouched), m >= 1 = mu from spline table m-1 and
  * dmu from table FK_MAX_SPLINES/2 + m-1 when set.  fk_set_inside marks ids[] as material 1
  * (mesh.InsideElements, NewtonRaphson.jl:204) and everything else 0.                            */

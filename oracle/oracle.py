@@ -382,3 +382,110 @@ def ref_demag_field(mesh, inside, inside_nodes, M):
     _ref_ll.ref_demag_field(_d(pf), _i(tf), _d(VE), _i(ins), _i(insn), C.c_int(mesh.nv), C.c_int(mesh.nt), C.c_int(len(ins)),
                             C.c_int(len(insn)), _d(Mf), _d(Hd), _d(vol))
     return np.asfortranarray(Hd.reshape(mesh.nv, 3).T), vol
+
+
+# ----------------------------------------------------------------------------- nonlinear drivers (restated loops)
+MU0 = 4e-7 * np.pi
+
+
+def _csr(rowptr, colind, vals, n):
+    import scipy.sparse as sp
+
+    return sp.csr_matrix((vals, colind, rowptr), shape=(n, n))
+
+
+def bordered_solve(A, Lag, b):
+    """u = ([A Lag; Lag' 0] \\ [b; 0])[1:nv]  (magneticField.jl:107, manyBodyIntersecting.jl:155, NewtonRaphson.jl:166)."""
+    import scipy.sparse as sp
+    import scipy.sparse.linalg as spla
+
+    n = A.shape[0]
+    K = sp.bmat([[A, sp.csr_matrix(Lag.reshape(n, 1))], [sp.csr_matrix(Lag.reshape(1, n)), None]], format="csc")
+    return spla.spsolve(K, np.concatenate([b, [0.0]]))[:n]
+
+
+def line_search(u, du, A, RHS, min_step=1e-4):
+    """lineSearch of src/FEM3D.jl:123-152 restated; updates u in place, returns (residue, accepted alpha or 0)."""
+    alf = 1.0
+    residual_old = np.linalg.norm(RHS - A @ u)
+    u_trial = u + du
+    residue = np.linalg.norm(RHS - A @ u_trial)
+    while residue > residual_old and alf > min_step:
+        alf *= 0.9
+        u_trial = u + alf * du
+        residue = np.linalg.norm(RHS - A @ u_trial)
+    if alf < min_step:
+        return residue, 0.0
+    u[:] = u_trial
+    return residue, alf
+
+
+def _solve(mesh, mu, b, Lag, solver, tol, extra_vals=None):
+    """One linear solve of a nonlinear pass: 'direct' = the reference Julia's bordered sparse solve; 'pcg' = the C port
+    of Eigen's Jacobi-CG on the oracle matrix; 'ref' = compiled reference stiffnessMatrix + Eigen ConjugateGradient
+    (magnetostatics.cpp:26-38).  Returns (u, iterations)."""
+    if solver == "ref":
+        outer, inner, v = ref_stiffness(mesh, mu)
+        x, it, _, _, _ = ref_cg(outer, inner, v, b, tol, 0)
+        return x, it
+    rp, ci, v = stiffness(mesh, mu, order="julia")
+    if extra_vals is not None:
+        v = v + extra_vals
+    if solver == "direct":
+        return bordered_solve(_csr(rp, ci, v, mesh.nv), Lag, b), 0
+    x, it, _, _ = pcg(rp, ci, v, b, tol)
+    return x, it
+
+
+def picard_loop(mesh, Bext, tck, tol=1e-4, max_att=100, shell_id=0, solver="direct", cg_tol=1e-12, bc="nearest"):
+    """Picard loop of Magnetostatics/manyBodyIntersecting.jl:141-210 restated (one material = the inside elements).
+    Returns dict(u, Hfield, H, mu, att, div, history, cg_iters)."""
+    RHS = boundary_integral(mesh, Bext, [shell_id], "julia")
+    Lag = lagrange(mesh)
+    mu = np.full(mesh.nt, MU0)
+    H = np.zeros(mesh.nt)
+    ins = np.asarray(mesh.InsideElements)
+    att, div, hist, cg_it = 0, 1.0, [], 0
+    u = np.zeros(mesh.nv)
+    Hf = np.zeros((3, mesh.nt))
+    while div > tol and att < max_att:
+        att += 1
+        Hold = H.copy()
+        u, it = _solve(mesh, mu, -RHS, Lag, solver, cg_tol)
+        cg_it += it
+        Hf, H = recover_field(mesh, u)
+        mu[ins] = splev(tck[0], tck[1], 3, H[ins], bc)
+        if not np.all(np.isfinite(mu)):
+            raise FloatingPointError("Nans/Infs in mu")
+        div = MU0 * np.max(np.abs(H[ins] - Hold[ins]))
+        hist.append((att, div, it))
+    return dict(u=u, Hfield=Hf, H=H, mu=mu, att=att, div=div, history=hist, cg_iters=cg_it)
+
+
+def newton_loop(mesh, Bext, tck, tck_dmu, tol=1e-4, max_att=100, shell_id=0, compat_bug=True, bc="nearest"):
+    """Newton-Raphson loop of Magnetostatics/NewtonRaphson.jl:148-214 restated (bordered direct solves)."""
+    RHS = -boundary_integral(mesh, Bext, [shell_id], "julia")
+    Lag = lagrange(mesh)
+    mu = np.full(mesh.nt, MU0)
+    dmu = np.zeros(mesh.nt)
+    H = np.zeros(mesh.nt)
+    Hf = np.zeros((3, mesh.nt))
+    u = np.zeros(mesh.nv)
+    ins = np.asarray(mesh.InsideElements)
+    att, div, hist = 0, np.inf, []
+    while div > tol and att < max_att:
+        att += 1
+        Hold = H.copy()
+        rp, ci, v = stiffness(mesh, mu, order="julia")
+        A = _csr(rp, ci, v, mesh.nv)
+        vt = tangential(mesh, Hf, dmu)[2] if att > 1 else np.zeros_like(v)
+        du = bordered_solve(_csr(rp, ci, v + vt, mesh.nv), Lag, RHS - A @ u)
+        residue, alf = line_search(u, du, A, RHS)
+        Hf, H = recover_field(mesh, u, compat_bug=compat_bug)
+        div = MU0 * np.max(np.abs(H[ins] - Hold[ins]))
+        mu[ins] = splev(tck[0], tck[1], 3, H[ins], bc)
+        dmu[ins] = splev(tck_dmu[0], tck_dmu[1], 3, H[ins], bc)
+        if not (np.all(np.isfinite(mu)) and np.all(np.isfinite(dmu))):
+            raise FloatingPointError("Nans/Infs in mu")
+        hist.append((att, div, residue, alf))
+    return dict(u=u, Hfield=Hf, H=H, mu=mu, dmu=dmu, att=att, div=div, history=hist)

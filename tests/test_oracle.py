@@ -135,3 +135,39 @@ def test_oracle_demag_field_matches_golden_reference(name):
     assert np.array_equal(np.flatnonzero(fin[0]), d["InsideNodes"])
     assert rel_l2(Hd[fin], d["Hd"][fin]) < 1e-10
     assert abs(rhs.sum()) < 1e-12 * np.abs(rhs).sum()              # sum_i grad(lambda_i) = 0: the load vector has zero mean
+
+
+def test_nonlinear_loop_restatements():
+    """The restated Picard loop (manyBodyIntersecting.jl:141-210) gives the same converged state whichever linear solve
+    runs inside it -- the bordered sparse direct solve the Julia driver uses, the C port of Eigen's Jacobi-CG, or the
+    compiled reference (FEMc.cpp stiffnessMatrix + Eigen ConjugateGradient) -- and the restated Newton loop
+    (NewtonRaphson.jl:148-214) converges to the same fixed point in fewer passes."""
+    import os
+    from scipy.interpolate import splrep
+    import femeko_jl_b200 as fk
+    from conftest import GOLDEN, rel_l2
+
+    g = np.load(os.path.join(GOLDEN, "gd_270K.npz"))
+    tck = splrep(g["HofM"], g["mu"], k=3, s=0)
+    tckd = splrep(g["HofM"], g["dmu"], k=3, s=0)
+    m = fk.kuhn_cube(8, inside_edge=0.5)
+    a = orc.picard_loop(m, [0.5, 0, 0], (tck[0], tck[1]), solver="direct")
+    b = orc.picard_loop(m, [0.5, 0, 0], (tck[0], tck[1]), solver="pcg")
+    assert a["att"] == b["att"] and rel_l2(a["Hfield"], b["Hfield"]) < 1e-9 and rel_l2(a["mu"], b["mu"]) < 1e-9
+    if orc.have_ref():
+        c = orc.picard_loop(m, [0.5, 0, 0], (tck[0], tck[1]), solver="ref", cg_tol=1e-12)
+        assert a["att"] == c["att"] and rel_l2(a["Hfield"], c["Hfield"]) < 1e-9
+    assert a["div"] < 1e-4 and a["history"][0][1] > 0.1           # starts far from the fixed point, ends converged
+    n = orc.newton_loop(m, [0.5, 0, 0], (tck[0], tck[1]), (tckd[0], tckd[1]), compat_bug=False)
+    assert n["att"] < a["att"] and rel_l2(n["Hfield"], a["Hfield"]) < 2e-3
+    # line search: a full step that lands on the solution is accepted, an overshoot backtracks by powers of 0.9
+    rp, ci, v = orc.stiffness(m, None)
+    A = orc._csr(rp, ci, v, m.nv)
+    xs = np.random.default_rng(0).normal(size=m.nv)
+    RHS = A @ xs
+    u = np.zeros(m.nv)
+    res, alf = orc.line_search(u, xs, A, RHS)
+    assert alf == 1.0 and res < 1e-10 * np.linalg.norm(RHS)
+    u = np.zeros(m.nv)
+    res, alf = orc.line_search(u, 2.5 * xs, A, RHS)
+    assert 0 < alf < 1.0 and np.isclose(np.log(alf) / np.log(0.9), round(np.log(alf) / np.log(0.9)))
