@@ -325,7 +325,7 @@ def run_ours(args):
             bn = float(tb.sqrt().item())
         nonlin = {"picard_iters": att, "pcg_iters_total": tot_it, "seconds": round(secs, 4), "div": div, "last_relres": rr,
                   "converged": bool(div <= 1e-4),
-                  "check": {"what": "||b - A(mu(H(u))) u|| / ||b|| with the matrix of the converged state (one more sweep)",
+                  "check": {"what": "nonlinear residual ||b - A(mu(H(u))) u|| / ||b|| of the returned potential (matrix re-assembled from it)",
                             "value": nr.value / max(bn, 1e-300)}}
 
     world_tets = nt_owned

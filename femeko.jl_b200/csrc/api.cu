@@ -6,6 +6,7 @@
 #include <cfloat>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <memory>
 
@@ -220,9 +221,9 @@ static void configure_spmv(fk_handle h, int ctas_per_sm) {
 // B200 has 126 MB of L2: the PCG vectors of a 10 M-tet problem (14 MB each) fit, the matrix stream (307 MB per
 // product) does not.  Pin the vectors an iteration streams in L2 (persisting access-policy window) and let everything
 // else -- the matrix is read with evict-first loads anyway -- stream past them, so the vector kernels and the x gather /
-// y write of the SpMV run at L2 speed instead of HBM speed.  Slab order: x | r | p | Ap | dinv | s | z | u.
-//   recurrence 0 (Eigen):            x r p Ap dinv; when they exceed what may persist, whole vectors only, always p
-//   recurrence 1 (single reduction): (x) r p Ap dinv s z; shrinking windows always end at z (the SpMV's gather source)
+// y write of the SpMV run at L2 speed instead of HBM speed.  Slab order: dinv | x | r | p | Ap | s | z | u.
+//   recurrence 0 (Eigen):            dinv x r p Ap; when they exceed what may persist, whole vectors only, always p
+//   recurrence 1 (single reduction): (dinv x) r p Ap s z; shrinking windows always end at z (the SpMV's gather source)
 // A partially persisting window (hit ratio < 1) turns the rest of the vectors into evict-first lines and was measured
 // far slower than no window at 20 M tets (profiles/r03r_*).
 static std::atomic<int> g_l2_users{0};
@@ -234,20 +235,25 @@ static void configure_l2(fk_handle h, int recurrence) {
   int max_persist = 0, max_window = 0;
   cudaDeviceGetAttribute(&max_persist, cudaDevAttrMaxPersistingL2CacheSize, h->device);
   cudaDeviceGetAttribute(&max_window, cudaDevAttrMaxAccessPolicyWindowSize, h->device);
+  if (std::getenv("FK_DEBUG"))
+    std::fprintf(stderr, "fk: L2 max persisting %d B, max window %d B, vector %zu B, recurrence %d\n", max_persist, max_window,
+                 h->slab_stride * sizeof(double), recurrence);
   cudaStreamAttrValue attr{};
   attr.accessPolicyWindow.num_bytes = 0;  // disables the window
   attr.accessPolicyWindow.hitProp = cudaAccessPropertyNormal;
   attr.accessPolicyWindow.missProp = cudaAccessPropertyNormal;
   if (h->l2_persist && max_persist > 0 && max_window > 0) {
     const size_t vec = h->slab_stride * sizeof(double), cap = std::min((size_t)max_persist, (size_t)max_window);
+    // slab order: dinv | x | r | p | Ap | s | z | u
+    const size_t lim = h->l2_max_vecs > 0 ? (size_t)h->l2_max_vecs : 7;
     int first = 0, count = 0;
-    if (recurrence == 0) {
-      const int opts[5][2] = {{0, 5}, {1, 4}, {1, 3}, {2, 2}, {2, 1}};
+    if (recurrence == 0) {   // dinv x r p Ap, then whole vectors only, always p
+      const int opts[5][2] = {{0, 5}, {1, 4}, {2, 3}, {3, 2}, {3, 1}};
       for (const auto& o : opts)
-        if ((size_t)o[1] * vec <= cap) { first = o[0]; count = o[1]; break; }
-    } else {
+        if ((size_t)o[1] * vec <= cap && (size_t)o[1] <= lim) { first = o[0]; count = o[1]; break; }
+    } else {                 // windows that end at z: with five, dinv (one pass) and x (two) are the ones left to stream
       for (int c = 7; c >= 1 && count == 0; c--)
-        if ((size_t)c * vec <= cap) { first = 7 - c; count = c; }
+        if ((size_t)c * vec <= cap && (size_t)c <= lim) { first = 7 - c; count = c; }
     }
     if (count > 0) {
       const size_t win = (size_t)count * vec;
@@ -263,7 +269,7 @@ static void configure_l2(fk_handle h, int recurrence) {
         attr.accessPolicyWindow.num_bytes = win;
         attr.accessPolicyWindow.hitRatio = 1.0f;
         attr.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
-        attr.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+        attr.accessPolicyWindow.missProp = h->l2_miss_normal ? cudaAccessPropertyNormal : cudaAccessPropertyStreaming;
         h->l2_window_set = true;
       } else {
         cudaGetLastError();
@@ -284,12 +290,12 @@ void ensure_pcg(fk_handle h) {
   const size_t stride = (nvec + 31) & ~(size_t)31;
   h->slab_stride = stride;
   h->pcg_slab.ensure(kSlabVecs * stride + kCtrlWords);   // + the control block of the peer-memory path (comm.cu)
-  h->x.ptr = h->pcg_slab.ptr;
+  h->dinv.ptr = h->pcg_slab.ptr;
+  h->x.ptr = h->dinv.ptr + stride;
   h->r.ptr = h->x.ptr + stride;
   h->p.ptr = h->r.ptr + stride;
   h->Ap.ptr = h->p.ptr + stride;
-  h->dinv.ptr = h->Ap.ptr + stride;
-  h->s.ptr = h->dinv.ptr + stride;
+  h->s.ptr = h->Ap.ptr + stride;
   h->z.ptr = h->s.ptr + stride;
   h->u.ptr = h->z.ptr + stride;
   configure_l2(h, 0);
@@ -317,7 +323,15 @@ static void issue_iteration(fk_handle h, cudaStream_t s, const double* vals, int
     // this GPU's sums with the peers in its prologue (peer_fold) -- no last-CTA tail, no extra kernel
     const PeerRed pr = comm_peer_red(h);
     int npart = gs;
-    if (h->n_slices_bnd > 0 && h->n_slices_int > 0 && h->overlap_halo && h->halo_stream) {
+    if (h->halo_mode == 2) {
+      // the exchange rides inside the SpMV (spmv.cuh: spmv_sell_fused_kernel): no push / wait launches, no second stream
+      const HaloFused hf = comm_halo_fused(h, h->p.ptr, h->tickets.ptr + 4);
+      const int4* meta = reinterpret_cast<const int4*>(h->slice_meta.ptr);
+      spmv_variant_dispatch(h->spmv_variant, [&](auto G, auto MINB) {
+        spmv_sell_fused_kernel<G(), MINB()><<<gs, kSpmvThreads, 0, s>>>(meta, h->srow.ptr, h->sell_colz.ptr, vals, h->p.ptr, h->Ap.ptr,
+                                                                         h->sym.nslices, part, ctl, j, h->slices_all.ptr, hf);
+      });
+    } else if (h->n_slices_bnd > 0 && h->n_slices_int > 0 && h->overlap_halo && h->halo_stream) {
       // the rows that read no halo column start at once; the halo exchange and the rows that need it run beside
       // them on a second stream (a fork / join inside the captured graph)
       const int gi = h->grid_spmv_int, gb = h->grid_spmv_bnd;
@@ -524,7 +538,7 @@ static void pcg_dev(fk_handle h, int slot, const double* b_dev, double* x_dev, c
   FK_CUDA(cudaGetLastError());
   h->launches += 3;
 
-  if (rec == 0 && h->comm && comm_capturable(h) && !h->halo_stream) {   // second stream of the split SpMV (created outside any capture)
+  if (rec == 0 && h->halo_mode != 2 && h->comm && comm_capturable(h) && !h->halo_stream) {   // second stream of the split SpMV (created outside any capture)
     FK_CUDA(cudaStreamCreateWithFlags(&h->halo_stream, cudaStreamNonBlocking));
     FK_CUDA(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
     FK_CUDA(cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming));
@@ -545,7 +559,8 @@ static void pcg_dev(fk_handle h, int slot, const double* b_dev, double* x_dev, c
     } else {
       FK_CUDA(cudaGraphLaunch(h->graph[slot][rec], s));
       const bool split = h->comm && h->halo_stream && h->overlap_halo && h->n_slices_bnd > 0 && h->n_slices_int > 0;
-      h->launches += rec == 1 ? (long long)chunk * 2 + 1 : (long long)chunk * (h->comm ? (split ? 6 : 5) : 3) + 1;
+      const int per_it = rec == 1 ? 2 : (!h->comm || h->halo_mode == 2) ? 3 : (split ? 6 : 5);
+      h->launches += (long long)chunk * per_it + 1;
     }
     launched += chunk;
     FK_CUDA(cudaMemcpyAsync(h->ctl_host, h->ctl.ptr, sizeof(PcgCtl), cudaMemcpyDeviceToHost, s));
@@ -811,9 +826,21 @@ int fk_tune(fk_handle h, int what, int value) {
         h->spmv_int_reserve = value;
         configure_spmv(h, h->spmv_ctas);
         break;
-      case 5:   // partitions: 1 (default) = halo exchange + halo-coupled rows beside the interior rows of the SpMV
+      case 5:   // partitions, Eigen recurrence: 2 (default) = exchange fused into the SpMV kernel; 1 = halo exchange + halo-coupled
+                // rows on a second stream beside the interior rows; 0 = serial
+        need(value >= 0 && value <= 2, "fk_tune: halo mode out of range");
+        h->halo_mode = value;
         h->overlap_halo = value != 0;
         invalidate_graphs(h);
+        break;
+      case 8:   // L2 policy of everything outside the persisting window: 0 = streaming (default), 1 = normal
+        h->l2_miss_normal = value != 0;
+        configure_l2(h, h->l2_recurrence);
+        break;
+      case 9:   // cap on the number of PCG vectors pinned in L2 (0 = as many as may persist)
+        need(value >= 0 && value <= 7, "fk_tune: vector count out of range");
+        h->l2_max_vecs = value;
+        configure_l2(h, h->l2_recurrence);
         break;
       default: throw std::runtime_error("fk_tune: unknown option");
     }

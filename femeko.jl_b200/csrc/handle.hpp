@@ -79,6 +79,9 @@ struct fk_handle_s {
   int n_slices_int = 0, n_slices_bnd = 0, grid_spmv_int = 1, grid_spmv_bnd = 1;
   bool pdl = false;           // programmatic dependent launch inside the single-GPU PCG iteration (measured: 63.8 vs 62.6 us -> off)
   bool overlap_halo = true;
+  int halo_mode = 2;          // partitions, Eigen recurrence: 2 = exchange fused into the SpMV kernel, 1 = second stream, 0 = serial
+  bool l2_miss_normal = false; // fk_tune 8
+  int l2_max_vecs = 0;         // fk_tune 9
   int spmv_int_reserve = 0;   // CTA slots per SM the interior SpMV leaves to the halo branch (measured: 0 best)
   cudaStream_t halo_stream = nullptr;
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
@@ -104,7 +107,7 @@ struct fk_handle_s {
   bool have_material = false;
   unsigned mat_used = 0;               // bit m-1: material id m occurs in matid
   // PCG workspace
-  fk::DevBuf<double> pcg_slab;         // x | r | p | Ap | dinv | s | z | u in ONE allocation (kSlabVecs vectors + control block): one L2
+  fk::DevBuf<double> pcg_slab;         // dinv | x | r | p | Ap | s | z | u in ONE allocation (kSlabVecs vectors + control block): one L2
                                        // access-policy window covers the vectors a recurrence streams every iteration, and one
                                        // CUDA-IPC handle exports every vector peers write halo rows into
   struct VecView { double* ptr = nullptr; } x, r, p, Ap, dinv, s, z, u;   // s, z: single-reduction recurrence; u: potential staged for the Picard sweep

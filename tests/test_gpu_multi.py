@@ -28,15 +28,17 @@ def _port():
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("no_p2p", ["", "1"])
-def test_partitioned_solve_matches_single_gpu(no_p2p):
+@pytest.mark.parametrize("no_p2p,rec,halo", [("", 0, "2"), ("", 0, "1"), ("", 1, ""), ("1", 0, "")])
+def test_partitioned_solve_matches_single_gpu(no_p2p, rec, halo):
     n = _ngpu()
     if n < 2:
         pytest.skip("needs at least 2 GPUs")
     world = 2 if n < 4 else 4
-    env = dict(os.environ, FK_NO_P2P=no_p2p)
+    env = dict(os.environ, FK_NO_P2P=no_p2p, FK_RECURRENCE=str(rec), FK_HALO_MODE=halo)
     if not no_p2p:
         env.pop("FK_NO_P2P")
+    if not halo:
+        env.pop("FK_HALO_MODE")
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}", "--master-addr", "127.0.0.1",
            "--master-port", str(_port()), os.path.join(ROOT, "scripts", "mgpu_check.py"), "16"]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env, cwd=ROOT)
