@@ -158,6 +158,32 @@ def build_problem(N, rank, world):
     return P.kuhn_slab(N, rank, world, inside_edge=0.2)
 
 
+def kernel_split(tr):
+    """Per-kernel device time inside the replayed PCG graph from the %globaltimer records of fk_trace_read:
+    span = latest CTA end - earliest CTA start of a launch; gap = start of the next kernel - end of this one."""
+    names = {0: "spmv", 1: "update", 2: "direction"}
+    tr = tr.astype(np.int64)
+    used = tr[:, :, 0] >= 0          # unused records carry start = 2^64 - 1 (-1 as int64)
+    out = {}
+    for k, nm in names.items():
+        sel = used[:, k] & (tr[:, k, 1] > 0)
+        if sel.sum() < 4:
+            continue
+        out[nm + "_us"] = round(float(np.median(tr[sel, k, 1] - tr[sel, k, 0])) / 1e3, 3)
+        out[nm + "_wait_us"] = round(float(np.median(tr[sel, k, 2])) / 1e3, 3)
+    ks = [k for k in names if names[k] + "_us" in out]
+    its = np.where(np.all(used[:, ks] & (tr[:, ks, 1] > 0), axis=1))[0]
+    if len(its) > 4 and len(ks) >= 2:
+        gaps = []
+        for a, b in zip(ks[:-1], ks[1:]):
+            gaps.append(tr[its, b, 0] - tr[its, a, 1])
+        out["gap_us"] = round(float(np.median(np.sum(gaps, axis=0))) / 1e3, 3)
+        starts = np.sort(tr[its, ks[0], 0])
+        d = np.diff(starts)
+        out["iteration_us"] = round(float(np.median(d[d < 10 * np.median(d)])) / 1e3, 3) if len(d) else None
+    return out
+
+
 def run_ours(args):
     import torch
 
@@ -293,6 +319,20 @@ def run_ours(args):
     asm_ms = statistics.mean(e[0].elapsed_time(e[1]) for e in evs)
     pcg_ms = statistics.mean(e[1].elapsed_time(e[2]) for e in evs)
 
+    # outside the timed region: device-side timeline of one more solve (per-kernel spans inside the replayed graph)
+    split = None
+    if args.trace:
+        h.tune(11, Piters)
+        step_dev(None)
+        h.synchronize()
+        split = kernel_split(h.trace_read())
+        h.tune(11, 0)
+        if dist is not None:   # the slowest rank's view of every figure
+            keys = sorted(split)
+            tt = torch.tensor([split[k] for k in keys], dtype=torch.float64, device=dev)
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            split = {k: round(float(v), 3) for k, v in zip(keys, tt.tolist())}
+
     # outside the timed region: a complete nonlinear solve at the bench size (Picard to mu0*max|dH| < 1e-4,
     # NewtonRaphson.jl:37-38,148; PCG to 1e-10 each pass, warm-started), checked by the true residual of the last pass
     nonlin = None
@@ -397,6 +437,10 @@ def run_ours(args):
                                   "avg_launch_ms": round(asm_ms, 5)},
             "clocks": clocks,
         }
+        if split:
+            line["roofline"]["kernel_split_us"] = split
+            line["roofline"]["kernel_split_note"] = ("device-side %globaltimer records inside the replayed graph (fk_tune 11), median over the "
+                                                     "iterations of one extra untimed solve; wait = longest cross-GPU spin of any CTA")
         if nonlin:
             line["nonlinear_solve"] = nonlin
         if world == 1 and not args.no_cpu_baseline:
@@ -605,7 +649,8 @@ def main():
     ap.add_argument("--cpu-n", type=int, default=48, help="Kuhn cells per edge of the bounded CPU sample")
     ap.add_argument("--cpu-budget", type=float, default=20.0)
     ap.add_argument("--solve-n", type=int, default=32, help="Kuhn cells per edge of the full nonlinear solve timed on both arms (0: skip)")
-    ap.add_argument("--recurrence", type=int, default=1, choices=[0, 1],
+    ap.add_argument("--trace", type=int, default=1, help="1: add the per-kernel split of the PCG iteration (one extra untimed solve)")
+    ap.add_argument("--recurrence", type=int, default=0, choices=[0, 1],
                     help="PCG recurrence: 1 = single reduction (2 kernels / iteration), 0 = Eigen's (3 kernels)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--tune", default="", help="experiments: comma-separated what=value pairs for fk_tune (e.g. 6=0)")

@@ -112,16 +112,19 @@ static void launch_assemble(fk_handle h, const AsmArgs& a, bool setup = false) {
 }
 
 static void assemble_stiffness_dev(fk_handle h, int slot, const double* f_dev) {
+  h->dir_applied &= ~(1u << slot);
   AsmArgs a = base_args(h, slot_vals(h, slot));
   a.coef = f_dev;
   launch_assemble<ASM_STIFF>(h, a);
 }
 static void assemble_mass_dev(fk_handle h, int slot, const double* rho_dev) {
+  h->dir_applied &= ~(1u << slot);
   AsmArgs a = base_args(h, slot_vals(h, slot));
   a.coef = rho_dev;
   launch_assemble<ASM_MASS>(h, a);
 }
 static void assemble_tangential_dev(fk_handle h, int slot, const double* H_dev, const double* dmu_dev) {
+  h->dir_applied &= ~(1u << slot);
   AsmArgs a = base_args(h, slot_vals(h, slot));
   a.coef = dmu_dev;
   a.Hvec = H_dev;
@@ -499,13 +502,25 @@ static void pcg_dev(fk_handle h, int slot, const double* b_dev, double* x_dev, c
   }
 
   jacobi_kernel<<<cdiv(n, 256), 256, 0, s>>>(h->vals[slot].ptr, h->sell_diag.ptr, n, opt.no_precond, h->dinv.ptr);
+  if (h->trace_cap > 0) trace_reset_kernel<<<cdiv((long long)h->trace_cap * kTraceKernels, 256), 256, 0, s>>>(h->trace.ptr, h->trace_cap * kTraceKernels);
   const double* Ax0 = nullptr;
+  // constrained slot (fk_apply_dirichlet): rows and columns of the fixed DOFs are identity, so with x0[fixed] = gD the
+  // residual, the direction and A p vanish on them EXACTLY in every iteration and x[fixed] == gD bit for bit on return
+  // (Fluids/fluids3D.jl:173 writes UP[fixed] = gD after the solve).  x0 = g needs no product: A g == g on such a matrix.
+  const bool constrained = ((h->dir_applied >> slot) & 1u) != 0 && h->n_fixed > 0 && h->dir_g.ptr != nullptr;
   if (opt.warm_start) {
     FK_CUDA(cudaMemcpyAsync(h->x.ptr, x_dev, sizeof(double) * (size_t)n, cudaMemcpyDeviceToDevice, s));
+    if (constrained) {
+      copy_rows_kernel<<<cdiv(h->n_fixed, 256), 256, 0, s>>>(h->x.ptr, h->dir_ids.ptr, h->dir_g.ptr, h->n_fixed);
+      h->launches++;
+    }
     if (h->comm) comm_halo_exchange(h, s, h->x.ptr);
     launch_spmv(h, s, h->vals[slot].ptr, h->x.ptr, h->Ap.ptr, false, nullptr, 0);
     Ax0 = h->Ap.ptr;
     h->launches++;
+  } else if (constrained) {
+    FK_CUDA(cudaMemcpyAsync(h->x.ptr, h->dir_g.ptr, sizeof(double) * (size_t)n, cudaMemcpyDeviceToDevice, s));
+    Ax0 = h->dir_g.ptr;
   } else {
     FK_CUDA(cudaMemsetAsync(h->x.ptr, 0, sizeof(double) * (size_t)n, s));
   }
@@ -520,9 +535,9 @@ static void pcg_dev(fk_handle h, int slot, const double* b_dev, double* x_dev, c
     cg_init_kernel<<<g2, kVecThreads, 0, s>>>(b_dev, Ax0, h->dinv.ptr, n, h->r.ptr, h->z.ptr, cp.A, cp.M);   // partials of (r.z, r.r, b.b)
     if (h->comm) {
       comm_allreduce_partials(h, s, cp.A, g2, cp.M, 3, 0, h->scal.ptr + 4, nullptr, 0);   // -> scal[4..6] over every rank
-      pcg_init_fin_kernel<<<1, 256, 0, s>>>(h->scal.ptr + 6, h->scal.ptr + 5, h->scal.ptr + 4, 1, tol, max_iter, epoch, proj, inv_n, h->ctl.ptr);
+      pcg_init_fin_kernel<<<1, 256, 0, s>>>(h->scal.ptr + 6, h->scal.ptr + 5, h->scal.ptr + 4, 1, tol, max_iter, epoch, proj, inv_n, h->ctl.ptr, h->trace.ptr, h->trace_cap);
     } else {
-      pcg_init_fin_kernel<<<1, 256, 0, s>>>(cp.A + 2 * (size_t)cp.M, cp.A + cp.M, cp.A, g2, tol, max_iter, epoch, proj, inv_n, h->ctl.ptr);
+      pcg_init_fin_kernel<<<1, 256, 0, s>>>(cp.A + 2 * (size_t)cp.M, cp.A + cp.M, cp.A, g2, tol, max_iter, epoch, proj, inv_n, h->ctl.ptr, h->trace.ptr, h->trace_cap);
     }
     launch_cg_spmv(h, s, h->vals[slot].ptr, h->ctl.ptr, 0);   // w0 = A z0, delta partials (and the first halo exchange)
     h->launches++;
@@ -530,10 +545,10 @@ static void pcg_dev(fk_handle h, int slot, const double* b_dev, double* x_dev, c
     pcg_init_kernel<<<gv, kVecThreads, 0, s>>>(b_dev, Ax0, h->dinv.ptr, n, h->r.ptr, h->p.ptr, h->part.ptr,
                                                comm_red_args(h, h->tickets.ptr + 2, h->scal.ptr + 4, 0));   // -> scal[4..6] = b.b, r.r, r.p
     comm_nccl_allreduce(h, s, h->scal.ptr + 4, 3, 0);
-    pcg_init_fin_kernel<<<1, 256, 0, s>>>(h->scal.ptr + 4, h->scal.ptr + 5, h->scal.ptr + 6, 1, tol, max_iter, epoch, 0, 0.0, h->ctl.ptr);
+    pcg_init_fin_kernel<<<1, 256, 0, s>>>(h->scal.ptr + 4, h->scal.ptr + 5, h->scal.ptr + 6, 1, tol, max_iter, epoch, 0, 0.0, h->ctl.ptr, h->trace.ptr, h->trace_cap);
   } else {
     pcg_init_kernel<<<gv, kVecThreads, 0, s>>>(b_dev, Ax0, h->dinv.ptr, n, h->r.ptr, h->p.ptr, h->part.ptr, RedArgs{});
-    pcg_init_fin_kernel<<<1, 256, 0, s>>>(h->part.ptr, h->part.ptr + gv, h->part.ptr + 2 * (size_t)gv, gv, tol, max_iter, epoch, proj, inv_n, h->ctl.ptr);
+    pcg_init_fin_kernel<<<1, 256, 0, s>>>(h->part.ptr, h->part.ptr + gv, h->part.ptr + 2 * (size_t)gv, gv, tol, max_iter, epoch, proj, inv_n, h->ctl.ptr, h->trace.ptr, h->trace_cap);
   }
   FK_CUDA(cudaGetLastError());
   h->launches += 3;
@@ -767,9 +782,9 @@ int fk_destroy(fk_handle h) {
     if (h->cap_stream) cudaStreamDestroy(h->cap_stream);
     if (h->ctl_host) cudaFreeHost(h->ctl_host);
     if (h->pin8) cudaFreeHost(h->pin8);
-    if (h->ev_fork) cudaEventDestroy(h->ev_fork);
-    if (h->ev_join) cudaEventDestroy(h->ev_join);
-    if (h->halo_stream) cudaStreamDestroy(h->halo_stream);
+    if (h->ev_fork) { cudaEventDestroy(h->ev_fork); h->ev_fork = nullptr; }
+    if (h->ev_join) { cudaEventDestroy(h->ev_join); h->ev_join = nullptr; }
+    if (h->halo_stream) { cudaStreamDestroy(h->halo_stream); h->halo_stream = nullptr; }   // comm_destroy below must not destroy it again
     if (h->copy_ev) cudaEventDestroy(h->copy_ev);
     if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
     // leave the device as the host application had it: the persisting lines are released when the last handle with a
@@ -837,12 +852,31 @@ int fk_tune(fk_handle h, int what, int value) {
         h->l2_miss_normal = value != 0;
         configure_l2(h, h->l2_recurrence);
         break;
+      case 11:  // device-side timeline of the PCG kernels: record the last `value` iterations of every solve (0 = off)
+        need(value >= 0 && value <= 1 << 20, "fk_tune: trace length out of range");
+        h->trace_cap = value;
+        if (value > 0) h->trace.ensure((size_t)value * kTraceKernels * 4);
+        break;
       case 9:   // cap on the number of PCG vectors pinned in L2 (0 = as many as may persist)
         need(value >= 0 && value <= 7, "fk_tune: vector count out of range");
         h->l2_max_vecs = value;
         configure_l2(h, h->l2_recurrence);
         break;
       default: throw std::runtime_error("fk_tune: unknown option");
+    }
+    return 0;
+  });
+}
+
+int fk_trace_read(fk_handle h, unsigned long long* out, int max_records, int* n_records) {
+  return guard([&]() {
+    need(h && out && n_records, "fk: NULL argument");
+    DeviceGuard dg(h->device);
+    const int n = std::min(max_records, h->trace_cap * kTraceKernels);
+    *n_records = n;
+    if (n > 0) {
+      FK_CUDA(cudaMemcpyAsync(out, h->trace.ptr, sizeof(unsigned long long) * 4 * (size_t)n, cudaMemcpyDeviceToHost, h->stream));
+      FK_CUDA(cudaStreamSynchronize(h->stream));
     }
     return 0;
   });
@@ -1107,6 +1141,7 @@ int fk_matrix_axpby(fk_handle h, int dst, double alpha, int x, double beta, int 
     need(h->vals[x].ptr != nullptr, "fk_matrix_axpby: slot x is empty");
     if (beta != 0.0) { check_slot(y); need(h->vals[y].ptr != nullptr, "fk_matrix_axpby: slot y is empty"); }
     double* d = slot_vals(h, dst);
+    h->dir_applied &= ~(1u << dst);
     axpby_kernel<<<std::min(cdiv(h->nnz_sell, 256), h->num_sms * 8), 256, 0, h->stream>>>(
         d, alpha, h->vals[x].ptr, beta, beta != 0.0 ? h->vals[y].ptr : nullptr, h->nnz_sell);
     FK_CUDA(cudaGetLastError());
@@ -1129,6 +1164,7 @@ int fk_matrix_set(fk_handle h, int slot, const double* vals_in) {
     need(h && vals_in, "fk: NULL argument");
     DeviceGuard dg(h->device);
     double* d = slot_vals(h, slot);
+    h->dir_applied &= ~(1u << slot);
     h->st_m.upload(vals_in, (size_t)h->nnz, h->stream);
     csr_to_sell_kernel<<<std::min(cdiv(h->nnz, 256), h->num_sms * 16), 256, 0, h->stream>>>(h->st_m.ptr, h->csr2sell.ptr, h->nnz, d);
     FK_CUDA(cudaGetLastError());
@@ -1591,6 +1627,7 @@ static int picard_collect(fk_handle h, double* div_out) {
 static int picard_step_dev(fk_handle h, int slot, const double* u_dev, int compat_bug, double* div_out, bool sync = true) {
   ensure_state(h);
   AsmArgs a = base_args(h, slot_vals(h, slot));
+  h->dir_applied &= ~(1u << slot);
   a.u = u_dev;
   if (h->comm) {  // partitions: the sweep reads the potential on halo nodes too -> refresh them from their owners
     ensure_pcg(h);
@@ -1696,6 +1733,7 @@ static void apply_dirichlet_dev(fk_handle h, int slot, double* b_dev) {
                                                                h->sym.nslices, h->n_rows, h->vals[slot].ptr);
   FK_CUDA(cudaGetLastError());
   h->launches++;
+  h->dir_applied |= 1u << slot;   // fk_pcg on this slot starts from x0[fixed] = gD: the fixed rows then stay exact
 }
 int fk_apply_dirichlet_dev(fk_handle h, int slot, double* b_dev) {
   return guard([&]() {

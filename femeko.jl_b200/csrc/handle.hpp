@@ -131,6 +131,7 @@ struct fk_handle_s {
   fk::DevBuf<int> dir_ids;             // fixed DOFs (fk_set_dirichlet)
   fk::DevBuf<double> dir_val, dir_g;   // their values; g = gD scattered over nv (0 on free rows)
   fk::DevBuf<unsigned char> dir_mask;  // nv: 1 = fixed
+  unsigned dir_applied = 0;            // bit s: slot s carries the identity rows / columns of fk_apply_dirichlet
   int n_fixed = 0;
   fk::DevBuf<double> ns_w, bproj;      // null-space weights (fk_set_nullspace), projected right-hand side
   bool ns_user = false;
@@ -141,6 +142,9 @@ struct fk_handle_s {
   fk::DevBuf<int> st_i, st_j, st_k;
   // multi-GPU
   fk::Comm* comm = nullptr;
+  // fk_tune(h, 11, n): device-side timeline of the PCG kernels (kernels.cuh: trace_rec)
+  fk::DevBuf<unsigned long long> trace;
+  int trace_cap = 0;
   // launch counter (kernels of this library launched through this handle)
   long long launches = 0;
 };

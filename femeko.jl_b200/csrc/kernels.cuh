@@ -543,7 +543,36 @@ struct PcgCtl {
   // one iteration is subtracted by the next one, so the recursive residual can fall to the requested tolerance
   double rmean[2], inv_n;
   int proj;
+  // fk_tune(h, 11, iterations): device-side timeline of the iteration's kernels (nullptr = off).  Record of iteration it, kernel k
+  // at trace[((it % trace_cap) * kTraceKernels + k) * 4 ..]: {min CTA start, max CTA end, longest cross-GPU wait, waits of CTA 0} in
+  // ns of %globaltimer
+  unsigned long long* trace;
+  int trace_cap;
 };
+constexpr int kTraceKernels = 4;   // 0 SpMV, 1 update (cg_update), 2 direction, 3 halo push / wait kernels
+
+__device__ __forceinline__ unsigned long long gtime_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+__device__ __forceinline__ unsigned long long* trace_rec(const PcgCtl* c, int j, int kernel) {
+  if (c == nullptr || c->trace == nullptr) return nullptr;
+  return c->trace + ((size_t)((c->base_it + j) % c->trace_cap) * kTraceKernels + kernel) * 4;
+}
+__device__ __forceinline__ void trace_begin(unsigned long long* tr) {
+  if (tr != nullptr && threadIdx.x == 0) atomicMin(tr, gtime_ns());
+}
+__device__ __forceinline__ void trace_end(unsigned long long* tr) {
+  if (tr != nullptr && threadIdx.x == 0) atomicMax(tr + 1, gtime_ns());
+}
+__device__ __forceinline__ void trace_wait(unsigned long long* tr, unsigned long long t0) {
+  if (tr != nullptr && threadIdx.x == 0) {
+    const unsigned long long dt = gtime_ns() - t0;
+    atomicMax(tr + 2, dt);
+    if (blockIdx.x == 0) tr[3] = dt;
+  }
+}
 
 __device__ __forceinline__ unsigned long long pcg_seq(const PcgCtl* c, int j, int which) {
   return (c->epoch << 32) + 2ULL * (unsigned long long)(c->base_it + j) + (unsigned long long)which + 1ULL;
@@ -600,7 +629,7 @@ static __global__ void __launch_bounds__(kVecThreads) pcg_init_kernel(const doub
 // the early exits of ConjugateGradient.h:43-56
 static __global__ void pcg_init_fin_kernel(const double* __restrict__ pbb, const double* __restrict__ prr, const double* __restrict__ prp,
                                     int npart, double tol, int max_iter, unsigned long long epoch, int proj, double inv_n,
-                                    PcgCtl* ctl) {
+                                    PcgCtl* ctl, unsigned long long* trace = nullptr, int trace_cap = 0) {
   __shared__ double red[33];
   const double bb = block_sum_array(pbb, npart, red);
   const double rr = block_sum_array(prr, npart, red);
@@ -618,6 +647,8 @@ static __global__ void pcg_init_fin_kernel(const double* __restrict__ pbb, const
     ctl->proj = proj;
     ctl->inv_n = inv_n;
     ctl->rmean[0] = ctl->rmean[1] = 0.0;
+    ctl->trace = trace_cap > 0 ? trace : nullptr;
+    ctl->trace_cap = trace_cap;
     ctl->done = (bb == 0.0 || rr < ctl->thr) ? 1 : 0;
   }
 }
@@ -640,6 +671,8 @@ static __global__ void __launch_bounds__(kVecThreads, kPcgVecCtas) pcg_update_ke
   griddep_wait();
   griddep_launch();
   if (pcg_inactive(ctl, j)) return;
+  unsigned long long* const tr = trace_rec(ctl, j, 1);
+  trace_begin(tr);
   const int n2 = n >> 1, T = gridDim.x * blockDim.x;
   double2* __restrict__ x2 = reinterpret_cast<double2*>(x);
   double2* __restrict__ r2 = reinterpret_cast<double2*>(r);
@@ -657,7 +690,9 @@ static __global__ void __launch_bounds__(kVecThreads, kPcgVecCtas) pcg_update_ke
   int i0 = blockIdx.x * blockDim.x + threadIdx.x;
   load(i0);   // the first batch is in flight while the producer's partial sums are folded
   double pAp_v[1] = {block_sum_array(part_pAp, npart, red_s)};   // npart == 1: the all-reduced scalar (NCCL path)
+  const unsigned long long tw0 = tr ? gtime_ns() : 0ULL;
   peer_fold<1>(pAp_v, pr, pcg_seq(ctl, j, 0));
+  trace_wait(tr, tw0);
   const double alpha = ctl->absNew[j & 1] / pAp_v[0];
   const bool proj = ctl->proj != 0;
   const double m_prev = proj ? ctl->rmean[j & 1] : 0.0;   // mean of r after the previous update
@@ -699,6 +734,7 @@ static __global__ void __launch_bounds__(kVecThreads, kPcgVecCtas) pcg_update_ke
   block_sum2(s_rr, s_rz, red_s);
   const double v[2] = {s_rr, s_rz};
   grid_reduce_finish<2>(v, part2, gridDim.x, red, red_s);   // -> out[0..1] = (r.r, r.z) over all ranks
+  trace_end(tr);
 }
 
 // convergence test, beta, p = dinv r + beta p                           (ConjugateGradient.h:72-81)
@@ -710,6 +746,8 @@ static __global__ void __launch_bounds__(kVecThreads, kPcgVecCtas) pcg_direction
   griddep_wait();
   griddep_launch();
   if (pcg_inactive(ctl, j)) return;
+  unsigned long long* const tr = trace_rec(ctl, j, 2);
+  trace_begin(tr);
   const int n2 = n >> 1, T = gridDim.x * blockDim.x;
   double2* __restrict__ p2 = reinterpret_cast<double2*>(p);
   const double2* __restrict__ r2 = reinterpret_cast<const double2*>(r);
@@ -726,7 +764,9 @@ static __global__ void __launch_bounds__(kVecThreads, kPcgVecCtas) pcg_direction
   load(i0);   // in flight during the fold of (r.r, r.z)
   double d2v[2];
   block_sum2_array(part2, part2 + stride, npart, red, d2v[0], d2v[1]);
+  const unsigned long long tw0 = tr ? gtime_ns() : 0ULL;
   peer_fold<2>(d2v, pr, pcg_seq(ctl, j, 1));
+  trace_wait(tr, tw0);
   const double rr = d2v[0], rz = d2v[1];
   const double absOld = ctl->absNew[j & 1];
   const bool conv = rr < ctl->thr;
@@ -739,7 +779,7 @@ static __global__ void __launch_bounds__(kVecThreads, kPcgVecCtas) pcg_direction
     if (conv) { ctl->iters = ctl->base_it + j; ctl->done = 1; }
     else ctl->absNew[(j + 1) & 1] = rz;
   }
-  if (conv) return;
+  if (conv) { trace_end(tr); return; }
   const double beta = rz / absOld;
   while (i0 < n2) {
 #pragma unroll
@@ -755,6 +795,7 @@ static __global__ void __launch_bounds__(kVecThreads, kPcgVecCtas) pcg_direction
     if (i0 < n2) load(i0);
   }
   if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) p[n - 1] = dinv[n - 1] * r[n - 1] + beta * p[n - 1];
+  trace_end(tr);
 }
 
 
@@ -806,6 +847,8 @@ static __global__ void __launch_bounds__(kVecThreads, kPcgVecCtas) cg_update_ker
                                                                 const PeerRed pr) {
   __shared__ double red_s[66];
   if (pcg_inactive(ctl, j)) return;
+  unsigned long long* const tr = trace_rec(ctl, j, 1);
+  trace_begin(tr);
   const int it = ctl->base_it + j;
   const double* __restrict__ part_in = (it & 1) ? partB : partA;
   double* __restrict__ part_out = (it & 1) ? partA : partB;
@@ -832,7 +875,9 @@ static __global__ void __launch_bounds__(kVecThreads, kPcgVecCtas) cg_update_ker
   block_sum2_array(part_in, part_in + stride, npv, red_s, v3[0], v3[1]);
   v3[2] = block_sum_array(part_s, nps, red_s);
   v3[3] = (proj && !first) ? block_sum_array(part_in + 2 * (size_t)stride, npv, red_s) : 0.0;   // sum r of the current residual
+  const unsigned long long tw0 = tr ? gtime_ns() : 0ULL;
   peer_fold3(v3, pr, cg_seq(ctl, it), (int)(ctl->epoch & 1ULL));
+  trace_wait(tr, tw0);
   const double gamma = v3[0], rr = v3[1], delta = v3[2];
   const double m_prev = v3[3] * ctl->inv_n;   // mean of the current r: taken out by this update
   const bool conv = rr < ctl->thr;
@@ -847,7 +892,7 @@ static __global__ void __launch_bounds__(kVecThreads, kPcgVecCtas) cg_update_ker
     if (conv) { ctl->iters = it > 0 ? it - 1 : 0; ctl->done = 1; }
     else { ctl->gamma[it & 1] = gamma; ctl->alpha[it & 1] = alpha; }
   }
-  if (conv) return;
+  if (conv) { trace_end(tr); return; }
   double s_rr = 0.0, s_rz = 0.0, s_r = 0.0;
   while (i < n2) {
     const double zx = dv.x * rv.x, zy = dv.y * rv.y;   // u = M^-1 r of the current residual (== z[i])
@@ -886,6 +931,7 @@ static __global__ void __launch_bounds__(kVecThreads, kPcgVecCtas) cg_update_ker
   }
   block_sum2(s_rz, s_rr, red_s);
   if (threadIdx.x == 0) { part_out[blockIdx.x] = s_rz; part_out[stride + blockIdx.x] = s_rr; }
+  trace_end(tr);
 }
 
 // End of a chunk.  If no further V kernel will run (max_iter reached), fold and test the residual of the last update
@@ -912,6 +958,12 @@ static __global__ void __launch_bounds__(256) cg_chunk_end_kernel(const double* 
   }
   __syncthreads();
   if (threadIdx.x == 0 && !ctl->done) ctl->base_it += chunk;
+}
+
+// records of the device-side timeline: {min start = max u64, max end = 0, longest wait = 0, wait of CTA 0 = 0}
+static __global__ void trace_reset_kernel(unsigned long long* tr, int nrec) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < nrec) { tr[4 * i] = ~0ULL; tr[4 * i + 1] = 0ULL; tr[4 * i + 2] = 0ULL; tr[4 * i + 3] = 0ULL; }
 }
 
 static __global__ void pcg_advance_kernel(PcgCtl* ctl, int chunk) {
@@ -998,6 +1050,11 @@ static __global__ void __launch_bounds__(256) dirichlet_mask_kernel(const int4* 
 static __global__ void scatter_kernel(double* __restrict__ dst, const int* __restrict__ ids, const double* __restrict__ v, int n) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) dst[ids[i]] = v ? v[i] : 0.0;
+}
+// dst[ids[i]] = full[ids[i]] (fixed DOFs of an initial guess <- the scattered Dirichlet values)
+static __global__ void copy_rows_kernel(double* __restrict__ dst, const int* __restrict__ ids, const double* __restrict__ full, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) dst[ids[i]] = full[ids[i]];
 }
 static __global__ void scatter_flag_kernel(unsigned char* __restrict__ dst, const int* __restrict__ ids, int n) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;

@@ -97,6 +97,8 @@ static __global__ void __launch_bounds__(kSpmvThreads, MINB) spmv_sell_kernel(co
   griddep_wait();
   griddep_launch();
   if (pcg_inactive(ctl, j)) return;
+  unsigned long long* const tr = trace_rec(ctl, j, 0);
+  trace_begin(tr);
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   constexpr int WPB = kSpmvThreads / 32;
   double dot = 0.0;
@@ -118,6 +120,7 @@ static __global__ void __launch_bounds__(kSpmvThreads, MINB) spmv_sell_kernel(co
     const double v[1] = {block_sum(dot, red_s)};
     grid_reduce_finish<1>(v, part, gridDim.x, red, red_s);   // -> out[0] = p.Ap over all ranks
   }
+  trace_end(tr);
 }
 
 
@@ -152,6 +155,8 @@ static __global__ void __launch_bounds__(kSpmvThreads, MINB) spmv_sell_fused_ker
   __shared__ double red_s[33];
   __shared__ int last_pusher;
   if (pcg_inactive(ctl, j)) return;
+  unsigned long long* const tr = trace_rec(ctl, j, 0);
+  trace_begin(tr);
   const unsigned long long seq = cg_seq(ctl, ctl->base_it + j);
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   constexpr int WPB = kSpmvThreads / 32;
@@ -187,9 +192,11 @@ static __global__ void __launch_bounds__(kSpmvThreads, MINB) spmv_sell_fused_ker
                      : sell_slice_row32<(G > 2 ? 2 : G)>(v, reinterpret_cast<const int*>(cz) + lane, m.y, x);
     } else {
       if (!waited) {   // once per warp: the neighbours' rows of this exchange have landed
+        const unsigned long long tw0 = (tr && wib == 0) ? gtime_ns() : 0ULL;
         if (lane < hf.nneigh) spin_until_relaxed(hf.my_ctrl + kOffHalo2 + lane, seq, hf.my_ctrl + kOffErr);
         __syncwarp();
         waited = true;
+        if (wib == 0) trace_wait(tr, tw0);
       }
       acc = m.w >= 0 ? sell_slice_row16<G, true>(v, reinterpret_cast<const uint2*>(cz) + lane, m.w, m.y, x)
                      : sell_slice_row32<(G > 2 ? 2 : G), true>(v, reinterpret_cast<const int*>(cz) + lane, m.y, x);
@@ -201,6 +208,7 @@ static __global__ void __launch_bounds__(kSpmvThreads, MINB) spmv_sell_fused_ker
   }
   const double bs = block_sum(dot, red_s);
   if (threadIdx.x == 0) part[blockIdx.x] = bs;
+  trace_end(tr);
 }
 
 // launch shapes {entries per batch = 4 G, min CTAs per SM}; selected with fk_tune(h, 4, variant)

@@ -84,6 +84,15 @@ class Femeko:
     def synchronize(self):
         L.check(self.lib.fk_synchronize(self.h))
 
+    def trace_read(self):
+        """Timeline of the last solve (after tune(11, n)): array [iteration slot, kernel (0 SpMV, 1 update, 2 direction, 3),
+        {start, end, longest cross-GPU wait, wait of CTA 0}] in ns; unused records have start = 2^64 - 1."""
+        cap = 1 << 16
+        buf = np.zeros(4 * cap, dtype=np.uint64)
+        n = C.c_int()
+        L.check(self.lib.fk_trace_read(self.h, buf.ctypes.data_as(C.POINTER(C.c_ulonglong)), cap, C.byref(n)))
+        return buf[:4 * n.value].reshape(-1, 4, 4)
+
     def launch_count(self) -> int:
         n = C.c_longlong()
         L.check(self.lib.fk_launch_count(self.h, C.byref(n)))

@@ -62,6 +62,7 @@ _SIGS = {
     "fk_synchronize": (C.c_int, [_H]),
     "fk_tune": (C.c_int, [_H, C.c_int, C.c_int]),
     "fk_launch_count": (C.c_int, [_H, C.POINTER(C.c_longlong)]),
+    "fk_trace_read": (C.c_int, [_H, C.POINTER(C.c_ulonglong), C.c_int, C.POINTER(C.c_int)]),
     "fk_sizes": (C.c_int, [_H, c_int_p, c_int_p, C.POINTER(C.c_longlong), c_int_p]),
     "fk_csr_pattern": (C.c_int, [_H, c_int_p, c_int_p]),
     "fk_elem2nnz": (C.c_int, [_H, c_int_p]),

@@ -90,8 +90,14 @@ int fk_synchronize(fk_handle h);
  * {entries per batch, min CTAs per SM}: 0 {4,8} 1 {4,6} 2 {8,5} 3 {8,4} (default) 4 {16,3} 5 {16,2}; results do
  * not depend on it.  5 = partitioned handles: 1 (default) overlaps the halo exchange with the SpMV of the rows that
  * read no halo column, 0 serialises them; 6 = CTA slots per SM that SpMV leaves free for the halo branch (default 0); 7 = programmatic dependent launch between the kernels of a single-GPU
- * PCG iteration (default 0: measured 2 % slower on B200).                            */
+ * PCG iteration (default 0: measured 2 % slower on B200).  8 = L2 policy of lines outside the persisting window (0 streaming,
+ * 1 normal); 9 = cap on the PCG vectors pinned in L2 (0 = as many as may persist); 11 = device-side timeline of the
+ * PCG kernels: keep the records of the last `value` iterations of every solve (0 = off), read with fk_trace_read.   */
 int fk_tune(fk_handle h, int what, int value);
+/* Timeline records of the last solve (fk_tune 11): record (it % cap) * 4 + k of kernel k (0 SpMV, 1 update, 2 direction)
+ * is four 64-bit words {earliest CTA start, latest CTA end, longest cross-GPU wait, wait of CTA 0}, ns of the GPU's
+ * %globaltimer; an unused record has start = 2^64 - 1.  Copies min(max_records, 4 cap) records.                    */
+int fk_trace_read(fk_handle h, unsigned long long* out, int max_records, int* n_records);
 /* number of kernels of this library launched through the handle so far (graph nodes included) */
 int fk_launch_count(fk_handle h, long long* n);
 
@@ -188,7 +194,9 @@ int fk_line_search_dev(fk_handle h, int slot, double* u_dev, const double* du_de
  * pattern: fk_set_dirichlet stores the fixed DOFs and their values (gD == NULL: zeros); fk_apply_dirichlet lifts the
  * right-hand side (b[free] -= A[free,fixed] gD, b[fixed] = gD) and turns the fixed rows and columns of `slot` into
  * identity rows / columns, so every later fk_pcg / fk_spmv on that slot solves LHS[free,free] exactly and returns
- * x[fixed] = gD.  A re-assembly of the slot needs a new fk_apply_dirichlet.  n_fixed = 0 clears the set.
+ * x[fixed] = gD bit for bit (fk_pcg starts a constrained slot from x0[fixed] = gD, so residual, direction and A p are
+ * exactly zero on those rows in every iteration).  A re-assembly of the slot needs a new fk_apply_dirichlet.
+ * n_fixed = 0 clears the set.
  * fk_set_nullspace: weights w (nv, NULL = ones) of fk_pcg_opts.project_nullspace; lagrange(mesh) gives the
  * bordered-system solution of magneticField.jl:107.                                                             */
 int fk_set_dirichlet(fk_handle h, const int* fixed_ids, int n_fixed, const double* gD /* n_fixed or NULL */);

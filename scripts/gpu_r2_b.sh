@@ -1,6 +1,7 @@
 #!/bin/bash
 # round 2, call b (2 GPUs): partitioned parity in every mode + 2-GPU bench lines: Eigen fused / Eigen split / single-reduction
 mkdir -p gpurun_out
+timeout 300 python -m pytest tests/test_gpu_round2.py -m gpu -q -k "dirichlet" > gpurun_out/r2b_pytest_dir.log 2>&1; tail -3 gpurun_out/r2b_pytest_dir.log
 timeout 900 python -m pytest tests/test_gpu_multi.py -m gpu -q -s > gpurun_out/r2b_pytest.log 2>&1; echo "pytest rc=$?" >> gpurun_out/r2b_pytest.log
 run() { # name, args...
   local name=$1; shift
