@@ -184,33 +184,75 @@ def kernel_split(tr):
     return out
 
 
-def run_ours(args):
+class Ctx:
+    """Process-wide state of one rank."""
+
+    def __init__(self, args):
+        import torch
+
+        self.rank, self.world, self.local = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
+        if self.world != args.gpus and self.world == 1 and args.gpus > 1:
+            raise SystemExit("bench.py --gpus N>1 must be launched with torch.distributed.run (one rank per GPU)")
+        if not torch.cuda.is_available():
+            raise SystemExit("bench.py: no CUDA device -- this framework has no CPU path (use --impl reference for the CPU arm)")
+        torch.cuda.set_device(self.local)
+        self.dev = torch.device("cuda", self.local)
+        self.dist = None
+        if self.world > 1:
+            import torch.distributed as dist
+
+            dist.init_process_group("nccl", device_id=self.dev)
+            self.dist = dist
+        self.stream = torch.cuda.Stream(device=self.dev)
+        # torch.distributed.run pins OMP_NUM_THREADS = 1: give every rank its share of the host cores for the symbolic phase
+        from femeko_jl_b200 import lib as L
+
+        self.host_threads = L.load().fk_set_host_threads(max(1, (os.cpu_count() or 1) // max(1, self.world)))
+
+    def barrier(self):
+        import torch
+
+        if self.dist is not None:
+            self.dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(self, v):
+        import torch
+
+        if self.dist is None:
+            return float(v)
+        tt = torch.tensor([v], dtype=torch.float64, device=self.dev)
+        self.dist.all_reduce(tt, op=self.dist.ReduceOp.MAX)
+        return float(tt.item())
+
+    def sum_over_ranks(self, vals):
+        import torch
+
+        if self.dist is None:
+            return [int(v) for v in vals]
+        tt = torch.tensor(list(vals), dtype=torch.float64, device=self.dev)
+        self.dist.all_reduce(tt)
+        return [int(v) for v in tt.tolist()]
+
+
+def bench_problem(args, ctx, mesh, part, full):
+    """Set one problem up on this rank's GPU and time the step on it.  full: also the end-to-end legs through the
+    host-pointer C ABI and the untimed nonlinear solve (the headline workload); otherwise device-resident timing only
+    (the strong-scaling block).  Returns a dict of raw figures (max over ranks where it is a time)."""
+    import ctypes as C
+
     import torch
 
     import femeko_jl_b200 as fk
+    from femeko_jl_b200 import lib as L
 
-    rank, world, local = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
-    if world != args.gpus:
-        if world == 1 and args.gpus > 1:
-            raise SystemExit("bench.py --gpus N>1 must be launched with torch.distributed.run (one rank per GPU)")
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py: no CUDA device -- this framework has no CPU path (use --impl reference for the CPU arm)")
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    dist = None
-    if world > 1:
-        import torch.distributed as dist
-
-        dist.init_process_group("nccl", device_id=dev)
-
-    N, Piters = args.n, args.pcg_iters
+    rank, world, local, dist, dev, stream = ctx.rank, ctx.world, ctx.local, ctx.dist, ctx.dev, ctx.stream
+    Piters = args.pcg_iters
     t_setup = time.time()
-    mesh, part = build_problem(N, rank, world)
     n_owned = part.n_owned if part is not None else 0
     h = fk.Femeko(mesh, use_mesh_VE=False, device=local, n_owned=n_owned)
     for kv in [t for t in args.tune.split(",") if t]:
         h.tune(int(kv.split("=")[0]), int(kv.split("=")[1]))
-    stream = torch.cuda.Stream(device=dev)
     h.set_stream(stream.cuda_stream)
     if part is not None:
         part.attach(h, dist)
@@ -232,26 +274,13 @@ def run_ours(args):
     stream.synchronize()
     # untimed: linear solve (mu = mu0 everywhere) for a physical potential to linearise about
     it0 = 0
-    if args.presolve:
+    if args.presolve and full:
         h.assemble_stiffness_dev(h.device_ptr(3), slot=0)
         it0, rr0 = h.pcg_dev(b_dev.data_ptr(), u_dev.data_ptr(), slot=0, tol=1e-8, max_iter=20000)
-    else:   # profiling runs: the uniform applied field H = B_ext/mu0, u = -H.x
+    else:   # profiling runs / the strong-scaling block: the uniform applied field H = B_ext/mu0, u = -H.x
         with torch.cuda.stream(stream):
             u_dev.copy_(torch.from_numpy(-(Bext / MU0) @ mesh.p))
         stream.synchronize()
-
-    # pinned host mirrors for the e2e leg (what a Julia driver would own)
-    u_host = torch.empty(nv, dtype=torch.float64).pin_memory()
-    b_host = torch.empty(nv, dtype=torch.float64).pin_memory()
-    x_host = torch.empty(nv, dtype=torch.float64).pin_memory()
-    u_host.copy_(u_dev.cpu())
-    b_host.copy_(torch.from_numpy(rhs))
-    import ctypes as C
-
-    from femeko_jl_b200 import lib as L
-
-    def host_ptr(tn):
-        return C.cast(tn.data_ptr(), L.c_double_p)
 
     opts = dict(max_iter=Piters, tol_disable=True, check_every=Piters + (Piters & 1), recurrence=args.recurrence)
 
@@ -266,61 +295,63 @@ def run_ours(args):
             ev[2].record(stream)
         return h.picard_result()
 
-    o = h.pcg_opts(**opts)
-    it_c, rr_c, div_c = C.c_int(), C.c_double(), C.c_double()
-
-    def step_e2e():
-        L.check(h.lib.fk_picard_pcg(h.h, 0, host_ptr(u_host), 0, host_ptr(b_host), host_ptr(x_host), C.byref(o), C.byref(div_c),
-                                    C.byref(it_c), C.byref(rr_c)))
-        return div_c.value
-
-    def barrier():
-        if dist is not None:
-            dist.barrier()
-        torch.cuda.synchronize()
-
     def timed(fn, steps, warmup, with_events):
         for _ in range(warmup):
             fn() if not with_events else fn(None)
         evs = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(steps)] if with_events else None
-        barrier()
+        ctx.barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         l0 = h.launch_count()
         e0.record(stream)
         for s in range(steps):
             fn(evs[s]) if with_events else fn()
         e1.record(stream)
-        barrier()
-        ms = e0.elapsed_time(e1)
-        launches = h.launch_count() - l0
-        if dist is not None:
-            tt = torch.tensor([ms], dtype=torch.float64, device=dev)
-            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-            ms = float(tt.item())
-        return ms, launches, evs
+        ctx.barrier()
+        ms = ctx.max_over_ranks(e0.elapsed_time(e1))
+        return ms, h.launch_count() - l0, evs
 
     W, K = max(3, args.warmup), args.steps
+    out = {"h": h, "mesh": mesh, "n_rows": n_rows, "nv": nv, "nt": nt, "nnz": nnz, "nt_owned": nt_owned, "setup_s": setup_s, "it0": it0,
+           "b_dev": b_dev, "u_dev": u_dev}
     sampler = ClockSampler(local)
-    if rank == 0:
+    if rank == 0 and full:
         sampler.start()
-    ms_dev, launches, evs = timed(step_dev, K, W, True)
-    ms_e2e, _, _ = timed(step_e2e, K, W, False)
-    # the same call with PAGEABLE host buffers (what a Julia Array is)
-    u_pg, b_pg, x_pg = u_host.numpy().copy(), b_host.numpy().copy(), np.zeros(nv)
+    out["ms_dev"], out["launches"], evs = timed(step_dev, K, W, True)
+    out["asm_ms"] = ctx.max_over_ranks(statistics.mean(e[0].elapsed_time(e[1]) for e in evs))
+    out["pcg_ms"] = ctx.max_over_ranks(statistics.mean(e[1].elapsed_time(e[2]) for e in evs))
+    if full:
+        # pinned host mirrors for the e2e leg (what a Julia driver would own)
+        u_host = torch.empty(nv, dtype=torch.float64).pin_memory()
+        b_host = torch.empty(nv, dtype=torch.float64).pin_memory()
+        x_host = torch.empty(nv, dtype=torch.float64).pin_memory()
+        u_host.copy_(u_dev.cpu())
+        b_host.copy_(torch.from_numpy(rhs))
 
-    def step_e2e_pageable():
-        L.check(h.lib.fk_picard_pcg(h.h, 0, L.dptr(u_pg), 0, L.dptr(b_pg), L.dptr(x_pg), C.byref(o), C.byref(div_c),
-                                    C.byref(it_c), C.byref(rr_c)))
+        def host_ptr(tn):
+            return C.cast(tn.data_ptr(), L.c_double_p)
 
-    ms_e2e_pg, _, _ = timed(step_e2e_pageable, max(2, K // 2), 2, False)
-    ms_e2e_pg *= K / max(2, K // 2)
-    clocks = sampler.stop() if rank == 0 else {}
+        o = h.pcg_opts(**opts)
+        it_c, rr_c, div_c = C.c_int(), C.c_double(), C.c_double()
 
-    asm_ms = statistics.mean(e[0].elapsed_time(e[1]) for e in evs)
-    pcg_ms = statistics.mean(e[1].elapsed_time(e[2]) for e in evs)
+        def step_e2e():
+            L.check(h.lib.fk_picard_pcg(h.h, 0, host_ptr(u_host), 0, host_ptr(b_host), host_ptr(x_host), C.byref(o), C.byref(div_c),
+                                        C.byref(it_c), C.byref(rr_c)))
+
+        out["ms_e2e"], _, _ = timed(step_e2e, K, W, False)
+        # the same call with PAGEABLE host buffers (what a Julia Array is)
+        u_pg, b_pg, x_pg = u_host.numpy().copy(), b_host.numpy().copy(), np.zeros(nv)
+
+        def step_e2e_pageable():
+            L.check(h.lib.fk_picard_pcg(h.h, 0, L.dptr(u_pg), 0, L.dptr(b_pg), L.dptr(x_pg), C.byref(o), C.byref(div_c),
+                                        C.byref(it_c), C.byref(rr_c)))
+
+        kp = max(2, K // 2)
+        ms_pg, _, _ = timed(step_e2e_pageable, kp, 2, False)
+        out["ms_e2e_pg"] = ms_pg * K / kp
+        out["clocks"] = sampler.stop() if rank == 0 else {}
 
     # outside the timed region: device-side timeline of one more solve (per-kernel spans inside the replayed graph)
-    split = None
+    out["split"] = None
     if args.trace:
         h.tune(11, Piters)
         step_dev(None)
@@ -328,60 +359,174 @@ def run_ours(args):
         split = kernel_split(h.trace_read())
         h.tune(11, 0)
         if dist is not None:   # the slowest rank's view of every figure
-            keys = sorted(split)
+            keys = sorted(k for k in split if split[k] is not None)
             tt = torch.tensor([split[k] for k in keys], dtype=torch.float64, device=dev)
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
             split = {k: round(float(v), 3) for k, v in zip(keys, tt.tolist())}
+        out["split"] = split
+    out["step_dev"] = step_dev
+    return out
 
-    # outside the timed region: a complete nonlinear solve at the bench size (Picard to mu0*max|dH| < 1e-4,
-    # NewtonRaphson.jl:37-38,148; PCG to 1e-10 each pass, warm-started), checked by the true residual of the last pass
-    nonlin = None
-    if args.full_solve:
-        with torch.cuda.stream(stream):
-            u2 = u_dev.clone()
-            r2 = torch.empty_like(u2)
-        h.set_mu(np.full(mesh.nt, MU0))
-        h.reset_field()
-        h.assemble_stiffness_dev(h.device_ptr(3), slot=0)
-        barrier()
-        t0 = time.time()
-        tot_it, att, div, rr = 0, 0, float("inf"), 0.0
-        while div > 1e-4 and att < 100:
-            it, rr = h.pcg_dev(b_dev.data_ptr(), u2.data_ptr(), slot=0, tol=1e-10, max_iter=20000, warm_start=att > 0,
-                               recurrence=args.recurrence)
-            div = h.picard_step_dev(u2.data_ptr(), slot=0)
-            tot_it += it
-            att += 1
-        h.synchronize()
-        secs = time.time() - t0
-        nr = C.c_double()
-        L.check(h.lib.fk_residual_dev(h.h, 0, C.c_void_p(u2.data_ptr()), C.c_void_p(b_dev.data_ptr()), C.c_void_p(r2.data_ptr()),
-                                      C.byref(nr)))
-        with torch.cuda.stream(stream):
-            bn = float(torch.linalg.vector_norm(b_dev[:n_rows]).item())
-        if dist is not None:
-            tb = torch.tensor([bn * bn], dtype=torch.float64, device=dev)
-            dist.all_reduce(tb)
-            bn = float(tb.sqrt().item())
-        nonlin = {"picard_iters": att, "pcg_iters_total": tot_it, "seconds": round(secs, 4), "div": div, "last_relres": rr,
-                  "converged": bool(div <= 1e-4),
-                  "check": {"what": "nonlinear residual ||b - A(mu(H(u))) u|| / ||b|| of the returned potential (matrix re-assembled from it)",
-                            "value": nr.value / max(bn, 1e-300)}}
 
-    world_tets = nt_owned
-    world_rows = n_rows
-    world_nnz = nnz
+def nonlinear_solve_block(args, ctx, P):
+    """Outside the timed region: a complete nonlinear solve at the bench size (Picard to mu0*max|dH| < 1e-4,
+    NewtonRaphson.jl:37-38,148; PCG to 1e-10 each pass, warm-started), checked by the true residual of the last pass."""
+    import ctypes as C
+
+    import torch
+
+    from femeko_jl_b200 import lib as L
+
+    h, mesh, dist, dev, stream = P["h"], P["mesh"], ctx.dist, ctx.dev, ctx.stream
+    b_dev, n_rows = P["b_dev"], P["n_rows"]
+    with torch.cuda.stream(stream):
+        u2 = P["u_dev"].clone()
+        r2 = torch.empty_like(u2)
+    h.set_mu(np.full(mesh.nt, MU0))
+    h.reset_field()
+    h.assemble_stiffness_dev(h.device_ptr(3), slot=0)
+    ctx.barrier()
+    t0 = time.time()
+    tot_it, att, div, rr = 0, 0, float("inf"), 0.0
+    while div > 1e-4 and att < 100:
+        it, rr = h.pcg_dev(b_dev.data_ptr(), u2.data_ptr(), slot=0, tol=1e-10, max_iter=20000, warm_start=att > 0,
+                           recurrence=args.recurrence)
+        div = h.picard_step_dev(u2.data_ptr(), slot=0)
+        tot_it += it
+        att += 1
+    h.synchronize()
+    secs = time.time() - t0
+    nr = C.c_double()
+    L.check(h.lib.fk_residual_dev(h.h, 0, C.c_void_p(u2.data_ptr()), C.c_void_p(b_dev.data_ptr()), C.c_void_p(r2.data_ptr()),
+                                  C.byref(nr)))
+    with torch.cuda.stream(stream):
+        bn = float(torch.linalg.vector_norm(b_dev[:n_rows]).item())
     if dist is not None:
-        tt = torch.tensor([nt_owned, n_rows, nnz], dtype=torch.float64, device=dev)
-        dist.all_reduce(tt)
-        world_tets, world_rows, world_nnz = (int(v) for v in tt.tolist())
+        tb = torch.tensor([bn * bn], dtype=torch.float64, device=dev)
+        dist.all_reduce(tb)
+        bn = float(tb.sqrt().item())
+    return {"picard_iters": att, "pcg_iters_total": tot_it, "seconds": round(secs, 4), "div": div, "last_relres": rr,
+            "converged": bool(div <= 1e-4),
+            "check": {"what": "nonlinear residual ||b - A(mu(H(u))) u|| / ||b|| of the returned potential (matrix re-assembled from it)",
+                      "value": nr.value / max(bn, 1e-300)}}
+
+
+def multi_parity_block(args, ctx):
+    """N > 1, outside every timed region: the partitioned path against a single-GPU solve of the same global problem
+    (rank 0), on a small box cut into x-slabs (the weak-scaling layout) and on a cube cut into px x py x pz blocks (the
+    strong-scaling layout, up to 7 neighbours): linear solve, one Picard sweep with the Gd table, second solve."""
+    import torch
+
+    import femeko_jl_b200 as fk
+    from femeko_jl_b200 import partition as PT
+    from femeko_jl_b200.mesh import kuhn_box
+
+    rank, world, local, dist, dev = ctx.rank, ctx.world, ctx.local, ctx.dist, ctx.dev
+    Hk, muk, _ = gd_table()
+    spl = fk.Spline1D(Hk, muk, bc="nearest")
+    F = np.array([0.5, 0.1, -0.2])
+    out = {}
+    for layout in ("slabs", "blocks"):
+        N = args.parity_n
+        if layout == "slabs":
+            lm, pr = PT.kuhn_slab(N, rank, world, inside_edge=0.4)
+        else:
+            lm, pr = PT.kuhn_block(2 * N, rank, PT.GRIDS[world], inside_edge=0.4)
+
+        def solve(mesh, n_owned, attach):
+            h = fk.Femeko(mesh, use_mesh_VE=False, device=local, n_owned=n_owned)
+            if attach is not None:
+                attach.attach(h, dist)
+            h.set_spline(0, spl)
+            h.set_inside(mesh.InsideElements)
+            mu = np.full(mesh.nt, MU0)
+            mu[mesh.InsideElements] = 3 * MU0
+            h.set_mu(mu)
+            h.assemble_stiffness(mu, slot=0, want_vals=False)
+            b = -h.boundary_integral(mesh.surfaceT, mesh.normal, mesh.AE, F, 0)
+            x, it, _ = h.pcg(b, slot=0, tol=1e-10, max_iter=5000, recurrence=args.recurrence)
+            div = h.picard_step(x * 2e5, slot=1)          # scaled so |H| sits on the nonlinear part of the table
+            x2, it2, _ = h.pcg(b, slot=1, tol=1e-10, max_iter=5000, x0=x, recurrence=args.recurrence)
+            mode = h.comm_mode()
+            h.close()
+            return x, it, x2, it2, div, mode
+
+        x, it, x2, it2, div, mode = solve(lm, pr.n_owned, pr)
+        res = torch.zeros((2, pr.nv_global), dtype=torch.float64, device=dev)
+        idx = torch.from_numpy(pr.l2g[:pr.n_owned]).to(dev)
+        res[0, idx] = torch.from_numpy(x[:pr.n_owned]).to(dev)
+        res[1, idx] = torch.from_numpy(x2[:pr.n_owned]).to(dev)
+        dist.all_reduce(res)
+        if rank == 0:
+            gm = kuhn_box((world * N, N, N), inside_edge=0.4) if layout == "slabs" else fk.kuhn_cube(2 * N, inside_edge=0.4)
+            xs, its, xs2, its2, divs, _ = solve(gm, 0, None)
+            r = res.cpu().numpy()
+            e1 = float(np.linalg.norm(r[0] - xs) / np.linalg.norm(xs))
+            e2 = float(np.linalg.norm(r[1] - xs2) / np.linalg.norm(xs2))
+            out[layout] = {"global_tets": int(gm.nt), "neighbours_rank0": len(pr.neigh), "comm_mode": mode, "relerr_x": e1,
+                           "relerr_x_after_sweep": e2, "iters": [it, its], "iters_after_sweep": [it2, its2],
+                           "div_rel_diff": abs(div - divs) / max(abs(divs), 1e-300),
+                           "ok": bool(e1 < 1e-8 and e2 < 1e-8 and abs(it - its) <= 2 and abs(it2 - its2) <= 2)}
+        dist.barrier()
+    if rank == 0:
+        out["relerr_x"] = max(out[k]["relerr_x_after_sweep"] for k in ("slabs", "blocks"))
+        out["ok"] = bool(all(out[k]["ok"] for k in ("slabs", "blocks")))
+        out["against"] = "single-GPU solve of the same global mesh on rank 0 (tol 1e-10): x-slabs (weak layout) and node blocks (strong layout)"
+    return out
+
+
+def run_ours(args):
+    import femeko_jl_b200 as fk
+
+    ctx = Ctx(args)
+    rank, world = ctx.rank, ctx.world
+    N, Piters = args.n, args.pcg_iters
+    mesh, part = build_problem(N, rank, world)
+    P = bench_problem(args, ctx, mesh, part, full=True)
+    h = P["h"]
+    K, W = args.steps, max(3, args.warmup)
+    n_rows, nv, nt, nnz, nt_owned = P["n_rows"], P["nv"], P["nt"], P["nnz"], P["nt_owned"]
+    ms_dev, asm_ms, pcg_ms, ms_e2e, ms_e2e_pg = P["ms_dev"], P["asm_ms"], P["pcg_ms"], P["ms_e2e"], P["ms_e2e_pg"]
+    nonlin = nonlinear_solve_block(args, ctx, P) if args.full_solve else None
+    world_tets, world_rows, world_nnz = ctx.sum_over_ranks([nt_owned, n_rows, nnz])
+    sell = h.sell_stats()
+    comm_mode = h.comm_mode()
+    geo = h.geo_stats() if "10=0" not in args.tune else None
+    h.close()
+    del P["h"], P["step_dev"], P["b_dev"], P["u_dev"]
+
+    # N > 1: parity of the partitioned path and the strong-scaling workload, each outside the headline's timed region
+    multi_parity = multi_parity_block(args, ctx) if world > 1 and args.parity_n > 0 else None
+    strong = None
+    if args.strong_n > 0 and (world > 1 or args.strong_single):
+        from femeko_jl_b200 import partition as PT
+
+        t0 = time.time()
+        if world > 1:
+            sm, sp = PT.kuhn_block(args.strong_n, rank, PT.GRIDS[world], inside_edge=0.2)
+        else:
+            sm, sp = fk.kuhn_cube(args.strong_n, inside_edge=0.2), None
+        gen_s = time.time() - t0
+        S = bench_problem(args, ctx, sm, sp, full=False)
+        s_tets, s_rows, s_nnz = ctx.sum_over_ranks([S["nt_owned"], S["n_rows"], S["nnz"]])
+        s_halo = ctx.sum_over_ranks([S["nv"] - S["n_rows"]])[0]
+        ms = S["ms_dev"] / K
+        strong = {"workload": f"configs[3]: ONE Kuhn cube N={args.strong_n} ({s_tets} tets, {s_rows} rows) cut into "
+                              f"{'x'.join(str(g) for g in PT.GRIDS[world])} node blocks, same step as the headline "
+                              f"(Picard sweep + {Piters} Jacobi-PCG iterations), device-resident",
+                  "scaling": "strong", "grid": list(PT.GRIDS[world]), "tets_total": s_tets, "rows_total": s_rows, "halo_rows_total": s_halo,
+                  "ms_per_step": round(ms, 4), "mtets_per_s": round(s_tets / (ms * 1e-3) / 1e6, 1),
+                  "pcg_iteration_us": round(S["pcg_ms"] / Piters * 1e3, 2), "picard_assembly_ms": round(S["asm_ms"], 4),
+                  "kernel_split_us": S["split"], "mesh_generation_s": round(gen_s, 1), "setup_s_untimed": round(S["setup_s"], 1),
+                  "host_threads_per_rank": ctx.host_threads,
+                  "note": "efficiency is for the driver to compute from the per-N lines: time per step should fall as 1/N"}
+        S["h"].close()
 
     if rank == 0:
         peak, peak_src = measured_peaks()
         ms_step = ms_dev / K
         value = world_tets / (ms_step * 1e-3) / 1e6
         e2e_value = world_tets / (ms_e2e / K * 1e-3) / 1e6
-        sell = h.sell_stats()
         it_bytes = pcg_bytes(n_rows, nnz)                        # this rank's share, per iteration
         pcg_gbs = it_bytes * Piters / (pcg_ms * 1e-3) / 1e9
         asm_bytes = picard_bytes(nt, nv, nnz)
@@ -395,6 +540,8 @@ def run_ours(args):
         floor_bytes = int(8 * sell[0] + sell[3] + 144 * sell[1])
         rec_name = ("single-reduction recurrence: spmv_sell_kernel<DOT> + cg_update_kernel, 2 kernels"
                     if args.recurrence == 1 else "Eigen recurrence: spmv_sell_kernel<DOT> + pcg_update_kernel + pcg_direction_kernel")
+        sweep_name = ("Picard sweep, rescale path: material_update_kernel + picard_element_kernel + geo_rescale_kernel + max fold"
+                      if geo else "Picard sweep: material_update_kernel + assemble_kernel<ASM_PICARD> + max fold")
         line = {
             "metric": METRIC, "value": round(value, 3), "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": round(ms_step, 4), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -407,16 +554,16 @@ def run_ours(args):
                        "l2": "inputs larger than L2 (CSR values+indices %.0f MB per GPU vs 126 MB L2)" % (12 * nnz / 1e6),
                        "parallelism": "single GPU" if world == 1 else
                        f"node-partitioned slabs x{world}, " + ("halo rows + all-reduce over NVLink peer memory inside the PCG kernels"
-                                                                if h.comm_mode() == 2 else "NCCL send/recv halo + ncclAllReduce")},
+                                                                if comm_mode == 2 else "NCCL send/recv halo + ncclAllReduce")},
             "components": {"picard_assembly_ms": round(asm_ms, 4), "picard_assembly_mtets_per_s": round(nt / asm_ms / 1e3, 1),
                            "pcg_ms": round(pcg_ms, 4), "pcg_iters_per_s": round(Piters / (pcg_ms * 1e-3), 1),
-                           "setup_s_untimed": round(setup_s, 2), "linear_presolve_iters": it0},
+                           "setup_s_untimed": round(P["setup_s"], 2), "linear_presolve_iters": P["it0"]},
             "e2e": {"value": round(e2e_value, 3), "unit": UNIT, "ms_per_step": round(ms_e2e / K, 4),
                     "h2d_bytes_per_step": 16 * nv, "d2h_bytes_per_step": 8 * n_rows + 8 + 4 + 64,
                     "host_buffers": "pinned",
                     "pageable": {"value": round(world_tets / (ms_e2e_pg / K * 1e-3) / 1e6, 3), "ms_per_step": round(ms_e2e_pg / K, 4),
                                  "note": "same call with pageable host arrays (a Julia Array)"}},
-            "gpu_launches": int(launches),
+            "gpu_launches": int(P["launches"]),
             "roofline": {"kernel": "fused Jacobi-PCG iteration (" + rec_name + ")",
                          "bound": "hbm", "achieved": round(pcg_gbs, 1), "peak": peak, "unit": "GB/s",
                          "frac": round(pcg_gbs / peak, 4), "traffic": traffic.get("pcg_iteration_bytes"), "traffic_source": traffic.get("source"),
@@ -431,28 +578,41 @@ def run_ours(args):
                          "frac_of_floor": round(floor_bytes / (pcg_ms / Piters * 1e-3) / 1e9 / peak, 4),
                          "floor_note": "L2-aware floor: only the matrix stream (values, packed columns, slice metadata) must "
                                        "come from HBM each iteration; frac_of_floor = floor_bytes / t / peak"},
-            "roofline_assembly": {"kernel": "Picard sweep: material_update_kernel + assemble_kernel<ASM_PICARD> + max fold (device time of the enqueued sweep; its scalars return with the solve's poll)", "bound": "hbm", "achieved": round(asm_gbs, 1),
+            "roofline_assembly": {"kernel": sweep_name + " (device time of the enqueued sweep; its scalars return with the solve's poll)",
+                                  "bound": "hbm", "achieved": round(asm_gbs, 1),
                                   "peak": peak, "unit": "GB/s", "frac": round(asm_gbs / peak, 4),
                                   "traffic": traffic.get("picard_assembly_bytes"), "algorithmic_bytes_per_launch": asm_bytes,
                                   "avg_launch_ms": round(asm_ms, 5)},
-            "clocks": clocks,
+            "clocks": P["clocks"],
         }
-        if split:
-            line["roofline"]["kernel_split_us"] = split
+        if geo:
+            line["roofline_assembly"]["layout_bytes_per_launch"] = int(geo[3] + 8 * h_nnz_sell(sell) + 72 * nt)
+            line["roofline_assembly"]["layout_note"] = ("what the rescale path streams per sweep: 12 B per contribution slot (%d slots for %d "
+                                                        "contributions), 8 B per entry pair, the values written once, ~72 B per element in "
+                                                        "the element kernel" % (geo[2], geo[1]))
+        if P["split"]:
+            line["roofline"]["kernel_split_us"] = P["split"]
             line["roofline"]["kernel_split_note"] = ("device-side %globaltimer records inside the replayed graph (fk_tune 11), median over the "
                                                      "iterations of one extra untimed solve; wait = longest cross-GPU spin of any CTA")
         if nonlin:
             line["nonlinear_solve"] = nonlin
+        if multi_parity:
+            line["multi_parity"] = multi_parity
+        if strong:
+            line["strong"] = strong
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(args, budget_s=args.cpu_budget)
-            line["parity"] = parity_block(args, local)
+            line["parity"] = parity_block(args, ctx.local)
             if args.solve_n > 0:
-                line["solve"] = solve_block(args, local)
+                line["solve"] = solve_block(args, ctx.local)
         print(json.dumps(line), flush=True)
-    h.close()
-    if dist is not None:
-        dist.barrier()
-        dist.destroy_process_group()
+    if ctx.dist is not None:
+        ctx.dist.barrier()
+        ctx.dist.destroy_process_group()
+
+
+def h_nnz_sell(sell):
+    return int(sell[0])
 
 
 # --------------------------------------------------------------------------------------------------
@@ -649,6 +809,10 @@ def main():
     ap.add_argument("--cpu-n", type=int, default=48, help="Kuhn cells per edge of the bounded CPU sample")
     ap.add_argument("--cpu-budget", type=float, default=20.0)
     ap.add_argument("--solve-n", type=int, default=32, help="Kuhn cells per edge of the full nonlinear solve timed on both arms (0: skip)")
+    ap.add_argument("--strong-n", type=int, default=256,
+                    help="N > 1: also time the step on ONE global Kuhn cube of this many cells per edge cut into blocks (0: skip)")
+    ap.add_argument("--strong-single", action="store_true", help="run the --strong-n cube on one GPU too (the 1-GPU point of the strong curve)")
+    ap.add_argument("--parity-n", type=int, default=12, help="N > 1: cells per edge and rank of the multi-GPU parity check (0: skip)")
     ap.add_argument("--trace", type=int, default=1, help="1: add the per-kernel split of the PCG iteration (one extra untimed solve)")
     ap.add_argument("--recurrence", type=int, default=0, choices=[0, 1],
                     help="PCG recurrence: 1 = single reduction (2 kernels / iteration), 0 = Eigen's (3 kernels)")

@@ -13,6 +13,10 @@
 #include "comm.hpp"
 #include "handle.hpp"
 
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+
 namespace fk {
 
 static thread_local std::string g_err;
@@ -111,9 +115,19 @@ static void launch_assemble(fk_handle h, const AsmArgs& a, bool setup = false) {
   h->launches++;
 }
 
+static void ensure_geo(fk_handle h);
+static void launch_geo_rescale(fk_handle h, double* vals);
 static void assemble_stiffness_dev(fk_handle h, int slot, const double* f_dev) {
   h->dir_applied &= ~(1u << slot);
-  AsmArgs a = base_args(h, slot_vals(h, slot));
+  double* vals = slot_vals(h, slot);
+  if (h->geo_mode == 2 || (h->geo_mode == 1 && h->geo_ready)) {   // rescale path: s = VE f, then the streamed sums
+    ensure_geo(h);
+    geo_scale_kernel<<<cdiv(h->nt, 256), 256, 0, h->stream>>>(h->VE.ptr, f_dev, h->nt, h->geo_s0.ptr);
+    h->launches++;
+    launch_geo_rescale(h, vals);
+    return;
+  }
+  AsmArgs a = base_args(h, vals);
   a.coef = f_dev;
   launch_assemble<ASM_STIFF>(h, a);
 }
@@ -129,6 +143,63 @@ static void assemble_tangential_dev(fk_handle h, int slot, const double* H_dev, 
   a.coef = dmu_dev;
   a.Hvec = H_dev;
   launch_assemble<ASM_TANGENT>(h, a);
+}
+
+// ---- rescale assembly (rescale.cuh) ------------------------------------------------------------------
+constexpr int kNumGeoVariants = 4;
+template <typename F>
+static void geo_variant_dispatch(int variant, F&& f) {   // {contributions per batch, min CTAs per SM}
+  switch (variant) {
+    case 1: f(std::integral_constant<int, 4>{}, std::integral_constant<int, 6>{}); break;
+    case 2: f(std::integral_constant<int, 8>{}, std::integral_constant<int, 3>{}); break;
+    case 3: f(std::integral_constant<int, 6>{}, std::integral_constant<int, 5>{}); break;
+    default: f(std::integral_constant<int, 8>{}, std::integral_constant<int, 4>{}); break;
+  }
+}
+static void configure_geo(fk_handle h) {
+  int occ = 1;
+  geo_variant_dispatch(h->geo_variant, [&](auto B, auto MINB) {
+    FK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, geo_rescale_kernel<B(), MINB()>, kGeoThreads, 0));
+  });
+  const int groups = (h->geo_nslices + kGeoThreads / 32 - 1) / (kGeoThreads / 32);
+  h->geo_grid = std::max(1, std::min(groups, h->num_sms * std::max(1, occ)));
+}
+// the one-off part: plan on the host (symbolic.cpp: build_rescale_plan), factors on the device
+static void ensure_geo(fk_handle h) {
+  if (h->geo_ready) return;
+  RescalePlan R;
+  build_rescale_plan(h->sym, 4096, R);
+  cudaStream_t s = h->stream;
+  h->geo_nslices = R.nslices;
+  h->geo_slots = R.n_slots;
+  h->geo_items = R.n_items;
+  h->geo_contrib = R.n_contrib;
+  h->geo_slice_ptr.upload(R.slice_ptr, s);
+  h->geo_dst1.upload(R.dst1, s);
+  h->geo_dst2.upload(R.dst2, s);
+  h->geo_ref.upload(R.cref, s);
+  h->geo_g.ensure((size_t)std::max<long long>(R.n_slots, 1));
+  h->geo_s0.ensure((size_t)h->nt);
+  if (R.n_slots > 0) {
+    geo_build_kernel<<<std::min(cdiv(R.n_slots, 256), h->num_sms * 16), 256, 0, s>>>(h->p4.ptr, h->t4.ptr, h->geo_ref.ptr, R.n_slots,
+                                                                                     h->geo_g.ptr);
+    FK_CUDA(cudaGetLastError());
+    h->launches++;
+  }
+  FK_CUDA(cudaStreamSynchronize(s));   // the host plan dies with this scope
+  configure_geo(h);
+  h->geo_ready = true;
+}
+// vals = sum_k s0[k] G_k on the plan's items (every stored entry is an item or the mirror of one)
+static void launch_geo_rescale(fk_handle h, double* vals) {
+  if (h->geo_nslices == 0) return;
+  geo_variant_dispatch(h->geo_variant, [&](auto B, auto MINB) {
+    geo_rescale_kernel<B(), MINB()><<<h->geo_grid, kGeoThreads, 0, h->stream>>>(h->geo_slice_ptr.ptr, h->geo_dst1.ptr, h->geo_dst2.ptr,
+                                                                               h->geo_ref.ptr, h->geo_g.ptr, h->geo_s0.ptr,
+                                                                               h->geo_nslices, vals);
+  });
+  FK_CUDA(cudaGetLastError());
+  h->launches++;
 }
 
 static void ensure_state(fk_handle h) {
@@ -525,6 +596,9 @@ static void pcg_dev(fk_handle h, int slot, const double* b_dev, double* x_dev, c
     FK_CUDA(cudaMemsetAsync(h->x.ptr, 0, sizeof(double) * (size_t)n, s));
   }
   const unsigned long long epoch = ++h->pcg_epoch;
+  // LL mailbox tags (kernels.cuh: peer_fold): this solve owns [tag_base, tag_base + 2 max_iter + 8); every rank advances alike
+  need(max_iter < (1 << 29), "fk_pcg: max_iter too large");
+  const unsigned long long tag_base_next = h->tag_base + 2ULL * (unsigned long long)max_iter + 8ULL;
   // in-iteration projection of the residual's mean: one GPU (either recurrence) or the single-reduction recurrence on
   // partitions (its fused reduction carries the fourth value); the two-reduction partitioned path only projects b and x
   const int proj = (opt.project_nullspace && (!h->comm || rec == 1)) ? 1 : 0;
@@ -535,9 +609,9 @@ static void pcg_dev(fk_handle h, int slot, const double* b_dev, double* x_dev, c
     cg_init_kernel<<<g2, kVecThreads, 0, s>>>(b_dev, Ax0, h->dinv.ptr, n, h->r.ptr, h->z.ptr, cp.A, cp.M);   // partials of (r.z, r.r, b.b)
     if (h->comm) {
       comm_allreduce_partials(h, s, cp.A, g2, cp.M, 3, 0, h->scal.ptr + 4, nullptr, 0);   // -> scal[4..6] over every rank
-      pcg_init_fin_kernel<<<1, 256, 0, s>>>(h->scal.ptr + 6, h->scal.ptr + 5, h->scal.ptr + 4, 1, tol, max_iter, epoch, proj, inv_n, h->ctl.ptr, h->trace.ptr, h->trace_cap);
+      pcg_init_fin_kernel<<<1, 256, 0, s>>>(h->scal.ptr + 6, h->scal.ptr + 5, h->scal.ptr + 4, 1, tol, max_iter, epoch, proj, inv_n, h->ctl.ptr, h->trace.ptr, h->trace_cap, (unsigned)h->tag_base);
     } else {
-      pcg_init_fin_kernel<<<1, 256, 0, s>>>(cp.A + 2 * (size_t)cp.M, cp.A + cp.M, cp.A, g2, tol, max_iter, epoch, proj, inv_n, h->ctl.ptr, h->trace.ptr, h->trace_cap);
+      pcg_init_fin_kernel<<<1, 256, 0, s>>>(cp.A + 2 * (size_t)cp.M, cp.A + cp.M, cp.A, g2, tol, max_iter, epoch, proj, inv_n, h->ctl.ptr, h->trace.ptr, h->trace_cap, (unsigned)h->tag_base);
     }
     launch_cg_spmv(h, s, h->vals[slot].ptr, h->ctl.ptr, 0);   // w0 = A z0, delta partials (and the first halo exchange)
     h->launches++;
@@ -545,10 +619,10 @@ static void pcg_dev(fk_handle h, int slot, const double* b_dev, double* x_dev, c
     pcg_init_kernel<<<gv, kVecThreads, 0, s>>>(b_dev, Ax0, h->dinv.ptr, n, h->r.ptr, h->p.ptr, h->part.ptr,
                                                comm_red_args(h, h->tickets.ptr + 2, h->scal.ptr + 4, 0));   // -> scal[4..6] = b.b, r.r, r.p
     comm_nccl_allreduce(h, s, h->scal.ptr + 4, 3, 0);
-    pcg_init_fin_kernel<<<1, 256, 0, s>>>(h->scal.ptr + 4, h->scal.ptr + 5, h->scal.ptr + 6, 1, tol, max_iter, epoch, 0, 0.0, h->ctl.ptr, h->trace.ptr, h->trace_cap);
+    pcg_init_fin_kernel<<<1, 256, 0, s>>>(h->scal.ptr + 4, h->scal.ptr + 5, h->scal.ptr + 6, 1, tol, max_iter, epoch, 0, 0.0, h->ctl.ptr, h->trace.ptr, h->trace_cap, (unsigned)h->tag_base);
   } else {
     pcg_init_kernel<<<gv, kVecThreads, 0, s>>>(b_dev, Ax0, h->dinv.ptr, n, h->r.ptr, h->p.ptr, h->part.ptr, RedArgs{});
-    pcg_init_fin_kernel<<<1, 256, 0, s>>>(h->part.ptr, h->part.ptr + gv, h->part.ptr + 2 * (size_t)gv, gv, tol, max_iter, epoch, proj, inv_n, h->ctl.ptr, h->trace.ptr, h->trace_cap);
+    pcg_init_fin_kernel<<<1, 256, 0, s>>>(h->part.ptr, h->part.ptr + gv, h->part.ptr + 2 * (size_t)gv, gv, tol, max_iter, epoch, proj, inv_n, h->ctl.ptr, h->trace.ptr, h->trace_cap, (unsigned)h->tag_base);
   }
   FK_CUDA(cudaGetLastError());
   h->launches += 3;
@@ -583,6 +657,7 @@ static void pcg_dev(fk_handle h, int slot, const double* b_dev, double* x_dev, c
     if (h->ctl_host->done || launched >= max_iter) break;
     if (!(h->ctl_host->r2 == h->ctl_host->r2)) break;   // NaN residual (e.g. non-finite matrix values): it would never pass the test
   }
+  h->tag_base = tag_base_next;
   if (h->comm) comm_check(h);
   const PcgCtl& c = *h->ctl_host;
   const int iters = c.done ? c.iters : max_iter;
@@ -669,6 +744,15 @@ static void copy_vec(const std::vector<T>& v, U* dst) {
 extern "C" {
 
 const char* fk_last_error(void) { return fk::g_err.c_str(); }
+int fk_set_host_threads(int n) {
+#ifdef _OPENMP
+  if (n > 0) omp_set_num_threads(n);
+  return omp_get_max_threads();
+#else
+  (void)n;
+  return 1;
+#endif
+}
 int fk_version(void) { return 100; }
 
 int fk_create(const double* p, const int* t, int nv, int nt, const double* VE, const fk_create_opts* opts, fk_handle* out) {
@@ -852,6 +936,15 @@ int fk_tune(fk_handle h, int what, int value) {
         h->l2_miss_normal = value != 0;
         configure_l2(h, h->l2_recurrence);
         break;
+      case 10:  // rescale assembly: 0 = never (tile kernel only), 1 = from the second Picard sweep on (default), 2 = at once
+        need(value >= 0 && value <= 2, "fk_tune: geo mode out of range");
+        h->geo_mode = value;
+        break;
+      case 12:  // launch shape of geo_rescale_kernel {batch, min CTAs per SM}: 0 {8,4} (default) 1 {4,6} 2 {8,3} 3 {6,5}
+        need(value >= 0 && value < kNumGeoVariants, "fk_tune: geo variant out of range");
+        h->geo_variant = value;
+        if (h->geo_ready) configure_geo(h);
+        break;
       case 11:  // device-side timeline of the PCG kernels: record the last `value` iterations of every solve (0 = off)
         need(value >= 0 && value <= 1 << 20, "fk_tune: trace length out of range");
         h->trace_cap = value;
@@ -934,6 +1027,18 @@ int fk_sell_stats(fk_handle h, long long* nnz_sell, long long* n_slices, long lo
     if (n_slices) *n_slices = h->sym.nslices;
     if (n_slices16) *n_slices16 = h->sym.n_slices16;
     if (col_bytes) *col_bytes = 2 * (long long)h->sym.sell_colz.size();
+    return 0;
+  });
+}
+int fk_geo_stats(fk_handle h, long long* items, long long* contributions, long long* slots, long long* bytes) {
+  return guard([&]() {
+    need(h, "fk: NULL handle");
+    DeviceGuard dg(h->device);
+    ensure_geo(h);
+    if (items) *items = h->geo_items;
+    if (contributions) *contributions = h->geo_contrib;
+    if (slots) *slots = h->geo_slots;
+    if (bytes) *bytes = 12 * h->geo_slots + 8LL * 32 * h->geo_nslices + 4LL * (h->geo_nslices + 1) + 8LL * h->nt;
     return 0;
   });
 }
@@ -1038,6 +1143,23 @@ int fk_symbolic_colz(fk_symbolic s, long long* n_colz, long long* n_slices16, in
     if (n_slices16) *n_slices16 = S.n_slices16;
     if (slice_meta) copy_vec(S.slice_meta, slice_meta);
     if (colz) copy_vec(S.sell_colz, colz);
+    return 0;
+  });
+}
+// rescale plan of a host-side symbolic object (tests): sizes with every pointer NULL-able, then the arrays
+int fk_symbolic_rescale(fk_symbolic s, long long* n_items, int* n_slices, long long* n_slots, unsigned int* slice_ptr, int* dst1,
+                        int* dst2, unsigned int* cref) {
+  return guard([&]() {
+    need(s, "fk: NULL argument");
+    RescalePlan R;
+    build_rescale_plan(s->S, 4096, R);
+    if (n_items) *n_items = R.n_items;
+    if (n_slices) *n_slices = R.nslices;
+    if (n_slots) *n_slots = R.n_slots;
+    copy_vec(R.slice_ptr, slice_ptr);
+    copy_vec(R.dst1, dst1);
+    copy_vec(R.dst2, dst2);
+    copy_vec(R.cref, cref);
     return 0;
   });
 }
@@ -1658,8 +1780,19 @@ static int picard_step_dev(fk_handle h, int slot, const double* u_dev, int compa
   } else {
     FK_CUDA(cudaMemsetAsync(h->tile_max.ptr, 0, sizeof(double), h->stream));
   }
-  // 2. the fused sweep: stiffness with the refreshed mu + H, |H| of every element
-  launch_assemble<ASM_PICARD>(h, a);
+  // 2. the sweep: stiffness with the refreshed mu + H, |H| of every element.  A handle that sweeps repeatedly (a Picard
+  //    loop) switches to the rescale path (rescale.cuh): same bits, streamed instead of recomputed.
+  h->geo_sweeps++;
+  if (h->geo_mode == 2 || (h->geo_mode == 1 && (h->geo_ready || h->geo_sweeps >= 2))) {
+    ensure_geo(h);
+    picard_element_kernel<<<cdiv(h->nt, 256), 256, 0, h->stream>>>(h->p4.ptr, h->t4.ptr, a.u, h->mu.ptr, a.VE, h->nt, compat_bug,
+                                                                   h->Hn.ptr, h->Hfield.ptr, h->geo_s0.ptr);
+    FK_CUDA(cudaGetLastError());
+    h->launches++;
+    launch_geo_rescale(h, a.vals);
+  } else {
+    launch_assemble<ASM_PICARD>(h, a);
+  }
   // div = mu0 * max over every rank's material elements (NewtonRaphson.jl:200)
   comm_allreduce_partials(h, h->stream, h->tile_max.ptr, npart, npart, 1, 1, h->scal.ptr, nullptr, 0);
   h->picard_pending = true;

@@ -136,7 +136,7 @@ __device__ __forceinline__ void element_local(const AsmArgs& a, const int k, con
   for (int i = 0; i < 4; i++)
 #pragma unroll
     for (int j = i; j < 4; j++)
-      m[q++] = s0 * ((G.g[i][0] * G.g[j][0] + G.g[i][1] * G.g[j][1]) + G.g[i][2] * G.g[j][2]);
+      m[q++] = __dmul_rn(s0, grad_dot3(G.g[i][0], G.g[i][1], G.g[i][2], G.g[j][0], G.g[j][1], G.g[j][2]));
 }
 
 // per-element coefficient gathers (the only global gathers left in phase 1): issued one tile ahead

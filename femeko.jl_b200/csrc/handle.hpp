@@ -121,6 +121,7 @@ struct fk_handle_s {
   fk::DevBuf<unsigned int> tickets;    // last-CTA tickets of the in-kernel grid reductions (zero between kernels)
   fk::DevBuf<fk::PcgCtl> ctl;
   fk::PcgCtl* ctl_host = nullptr;      // pinned
+  unsigned long long tag_base = 16;    // LL mailbox tags handed out so far (kernels.cuh: peer_fold)
   unsigned long long pcg_epoch = 0;   // solves started on this handle (identical on every rank of a partitioned problem)
   int grid_spmv = 0, grid_vec = 0, grid_pcg = 0;   // grid_pcg: the update / direction kernels of an iteration
   int spmv_variant = 3, spmv_ctas = 0;   // SpMV launch shape (spmv.cuh: spmv_variant_dispatch), cap on CTAs per SM
@@ -142,6 +143,14 @@ struct fk_handle_s {
   fk::DevBuf<int> st_i, st_j, st_k;
   // multi-GPU
   fk::Comm* comm = nullptr;
+  // rescale assembly (rescale.cuh): geometric factors of every contribution, built on demand
+  //   geo_mode 0: never; 1 (default): from the second Picard sweep of a handle on; 2: from the first sweep / assembly on
+  int geo_mode = 1, geo_sweeps = 0, geo_nslices = 0, geo_grid = 0, geo_variant = 0;
+  bool geo_ready = false;
+  long long geo_slots = 0, geo_items = 0, geo_contrib = 0;
+  fk::DevBuf<double> geo_g, geo_s0;
+  fk::DevBuf<uint32_t> geo_ref, geo_slice_ptr;
+  fk::DevBuf<int> geo_dst1, geo_dst2;
   // fk_tune(h, 11, n): device-side timeline of the PCG kernels (kernels.cuh: trace_rec)
   fk::DevBuf<unsigned long long> trace;
   int trace_cap = 0;

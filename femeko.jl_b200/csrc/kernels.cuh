@@ -118,12 +118,12 @@ constexpr int kOffMail = kMaxNeigh;
 constexpr int kOffErr = kOffMail + 2 * kMaxRanks * kMailWords;
 constexpr int kOffCnt = kOffErr + 1;
 constexpr int kOffHaloCnt = kOffCnt + 1;
-constexpr int kMail2Words = 3;     // consumer-side fold of the PCG iteration: 2 values + sequence flag per (slot, rank)
+constexpr int kMail2Words = 4;     // consumer-side fold of the PCG iteration: 2 values x 2 LL words per (slot, rank)
 constexpr int kOffMail2 = kOffHaloCnt + 1;
 // single-reduction recurrence (cg_update_kernel / fused SpMV): halo flags of the in-kernel exchange and a mailbox of
 // 3 values + sequence flag per (slot, rank)
 constexpr int kOffHalo2 = kOffMail2 + 2 * kMaxRanks * kMail2Words;
-constexpr int kMail3Words = 5;   // 4 values + sequence flag
+constexpr int kMail3Words = 8;   // 4 values x 2 LL words
 constexpr int kOffMail3 = kOffHalo2 + kMaxNeigh;
 constexpr int kCtrlWords = 512;
 static_assert(kOffMail3 + 4 * kMaxRanks * kMail3Words <= kCtrlWords, "control block too small");
@@ -252,37 +252,76 @@ __device__ __forceinline__ void grid_reduce_finish(const double (&v)[NV], double
 // Dot products of a PCG iteration on a partitioned problem, folded on the CONSUMER side: the producing kernel only
 // publishes its per-CTA partials (no last-CTA tail); every CTA of the consuming kernel folds them (identical bits
 // in every CTA), CTA 0 stores this GPU's sums into every peer's mailbox over NVLink, and every CTA waits for the
-// peers' sums in its own GPU's mailbox and adds them in rank order -> identical bits on every rank.  seq = a number
-// every rank derives identically from (solve epoch, iteration, which reduction); consecutive reductions alternate
-// mailbox slots, and a rank can only reach the next use of a slot after the peer's previous readers of it have
-// finished (it needs the peer's contribution to the reduction in between, sent by a later kernel of the peer).
+// peers' sums in its own GPU's mailbox and adds them in rank order -> identical bits on every rank.
+// The mailbox speaks NCCL's low-latency (LL) protocol: a double travels as two 8-byte words, each {32 data bits | 32-bit
+// tag}; an aligned 8-byte store is single-copy atomic, so a word whose tag matches carries its data -- no fence on
+// either side, one NVLink crossing per reduction (measured with fk_tune 11: the release / acquire version with two
+// system fences on the sender cost 8.8 us per reduction on two B200s).  Tags count the reductions of a handle
+// (PcgCtl::tag_base + position inside the solve, identical on every rank), so a slot never sees the same tag twice in
+// a row; consecutive reductions alternate slots, and a rank can only reach the next use of a slot after the peer's
+// previous readers of it have finished (it needs the peer's contribution to the reduction in between).
 struct PeerRed {
   int rank, nranks;                            // nranks <= 1: this GPU only
   unsigned long long* const* peer_ctrl;
   unsigned long long* my_ctrl;
 };
+__device__ __forceinline__ void st_relaxed_sys(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ void ll_send(unsigned long long* box, const double v, const unsigned tag) {
+  const unsigned long long b = (unsigned long long)__double_as_longlong(v);
+  st_relaxed_sys(box, (b << 32) | (unsigned long long)tag);
+  st_relaxed_sys(box + 1, (b & 0xffffffff00000000ULL) | (unsigned long long)tag);
+}
+__device__ __forceinline__ double ll_recv(const unsigned long long* box, const unsigned tag, unsigned long long* err) {
+  const long long t0 = clock64();
+  unsigned long long w0, w1;
+  while (true) {
+    w0 = ld_relaxed_sys(box);
+    w1 = ld_relaxed_sys(box + 1);
+    if ((unsigned)w0 == tag && (unsigned)w1 == tag) break;
+    if (clock64() - t0 > 4000000000LL) { *err = 1ULL; break; }   // a lost peer must not hang the GPU
+  }
+  return __longlong_as_double((long long)((w0 >> 32) | (w1 & 0xffffffff00000000ULL)));
+}
+// NV values per (slot, rank), two words each, at ctrl[base + (slot * kMaxRanks + rank) * 2 NV]
 template <int NV>
-__device__ __forceinline__ void peer_fold(double (&v)[NV], const PeerRed& pr, unsigned long long seq) {
-  static_assert(NV <= kMail2Words - 1, "mailbox holds 2 values");
+__device__ __forceinline__ void peer_fold_ll(double (&v)[NV], const PeerRed& pr, const unsigned tag, const int slot, const int base) {
   if (pr.nranks <= 1) return;
   __shared__ double sh[NV * kMaxRanks];
-  const int slot = (int)(seq & 1ULL), t = threadIdx.x;
-  if (t < pr.nranks) {
-    if (t == pr.rank) {
+  const int t = threadIdx.x;
+  if (t < pr.nranks * NV) {   // one thread per (rank, value): the stores and the polls of a reduction run side by side
+    const int r = t / NV, k = t - r * NV;
+    if (r == pr.rank) sh[k * kMaxRanks + r] = v[k];
+    else {
+      if (blockIdx.x == 0) ll_send(pr.peer_ctrl[r] + base + ((size_t)slot * kMaxRanks + pr.rank) * (2 * NV) + 2 * k, v[k], tag);
+      sh[k * kMaxRanks + r] = ll_recv(pr.my_ctrl + base + ((size_t)slot * kMaxRanks + r) * (2 * NV) + 2 * k, tag, pr.my_ctrl + kOffErr);
+    }
+  }
+  __syncthreads();
 #pragma unroll
-      for (int k = 0; k < NV; k++) sh[k * kMaxRanks + t] = v[k];
-    } else {
-      if (blockIdx.x == 0) {
-        unsigned long long* box = pr.peer_ctrl[t] + kOffMail2 + ((size_t)slot * kMaxRanks + pr.rank) * kMail2Words;
-#pragma unroll
-        for (int k = 0; k < NV; k++) reinterpret_cast<double*>(box)[k] = v[k];
-        __threadfence_system();
-        st_release_sys(box + kMail2Words - 1, seq);
-      }
-      const unsigned long long* box = pr.my_ctrl + kOffMail2 + ((size_t)slot * kMaxRanks + t) * kMail2Words;
-      spin_until(box + kMail2Words - 1, seq, pr.my_ctrl + kOffErr);
-#pragma unroll
-      for (int k = 0; k < NV; k++) sh[k * kMaxRanks + t] = reinterpret_cast<const volatile double*>(box)[k];
+  for (int k = 0; k < NV; k++) {
+    double s = 0.0;
+    for (int r = 0; r < pr.nranks; r++) s += sh[k * kMaxRanks + r];
+    v[k] = s;
+  }
+  __syncthreads();
+}
+// the two reductions of Eigen's recurrence (p.Ap | r.r, r.z): slots alternate with the parity of seq
+template <int NV>
+__device__ __forceinline__ void peer_fold(double (&v)[NV], const PeerRed& pr, unsigned long long seq, unsigned tag_base) {
+  static_assert(2 * NV <= kMail2Words, "mailbox holds 2 values");
+  // both reductions share the slots (one 4-word record per rank): a 1-value reduction uses the first two words
+  if (pr.nranks <= 1) return;
+  __shared__ double sh[NV * kMaxRanks];
+  const int t = threadIdx.x, slot = (int)(seq & 1ULL);
+  const unsigned tag = tag_base + (unsigned)seq;
+  if (t < pr.nranks * NV) {
+    const int r = t / NV, k = t - r * NV;
+    if (r == pr.rank) sh[k * kMaxRanks + r] = v[k];
+    else {
+      if (blockIdx.x == 0) ll_send(pr.peer_ctrl[r] + kOffMail2 + ((size_t)slot * kMaxRanks + pr.rank) * kMail2Words + 2 * k, v[k], tag);
+      sh[k * kMaxRanks + r] = ll_recv(pr.my_ctrl + kOffMail2 + ((size_t)slot * kMaxRanks + r) * kMail2Words + 2 * k, tag, pr.my_ctrl + kOffErr);
     }
   }
   __syncthreads();
@@ -295,39 +334,11 @@ __device__ __forceinline__ void peer_fold(double (&v)[NV], const PeerRed& pr, un
   __syncthreads();
 }
 
-// Four values (gamma, r.r, delta, sum r: the single fused reduction of the single-reduction recurrence), same protocol as peer_fold on its own
-// mailbox; consecutive reductions alternate slots by the parity of seq, consecutive solves by the parity of the epoch
-// (a rank two hops away may start its next solve while a slow CTA here still reads the last reduction of this one).
-__device__ __forceinline__ void peer_fold3(double (&v)[4], const PeerRed& pr, unsigned long long seq, int epoch_parity) {
-  if (pr.nranks <= 1) return;
-  __shared__ double sh3[4 * kMaxRanks];
-  const int slot = (int)(seq & 1ULL) + 2 * epoch_parity, t = threadIdx.x;   // four slots: a solve never reuses its predecessor's
-  if (t < pr.nranks) {
-    if (t == pr.rank) {
-#pragma unroll
-      for (int k = 0; k < 4; k++) sh3[k * kMaxRanks + t] = v[k];
-    } else {
-      if (blockIdx.x == 0) {
-        unsigned long long* box = pr.peer_ctrl[t] + kOffMail3 + ((size_t)slot * kMaxRanks + pr.rank) * kMail3Words;
-#pragma unroll
-        for (int k = 0; k < 4; k++) reinterpret_cast<double*>(box)[k] = v[k];
-        __threadfence_system();
-        st_release_sys(box + kMail3Words - 1, seq);
-      }
-      const unsigned long long* box = pr.my_ctrl + kOffMail3 + ((size_t)slot * kMaxRanks + t) * kMail3Words;
-      spin_until_relaxed(box + kMail3Words - 1, seq, pr.my_ctrl + kOffErr);
-#pragma unroll
-      for (int k = 0; k < 4; k++) sh3[k * kMaxRanks + t] = reinterpret_cast<const volatile double*>(box)[k];
-    }
-  }
-  __syncthreads();
-#pragma unroll
-  for (int k = 0; k < 4; k++) {
-    double s = 0.0;
-    for (int r = 0; r < pr.nranks; r++) s += sh3[k * kMaxRanks + r];
-    v[k] = s;
-  }
-  __syncthreads();
+// Four values (gamma, r.r, delta, sum r: the single fused reduction of the single-reduction recurrence), same protocol on
+// its own mailbox; consecutive reductions alternate slots by the parity of seq, consecutive solves by the parity of the
+// epoch (a rank two hops away may start its next solve while a slow CTA here still reads the last reduction of this one).
+__device__ __forceinline__ void peer_fold3(double (&v)[4], const PeerRed& pr, unsigned long long seq, int epoch_parity, unsigned tag_base) {
+  peer_fold_ll<4>(v, pr, tag_base + (unsigned)seq, (int)(seq & 1ULL) + 2 * epoch_parity, kOffMail3);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -373,6 +384,14 @@ __device__ __forceinline__ void tet_geometry_xyz(const double x0, const double y
   G.g[0][1] = -(G.g[1][1] + G.g[2][1] + G.g[3][1]);
   G.g[0][2] = -(G.g[1][2] + G.g[2][2] + G.g[3][2]);
   G.vol = fabs(det) / 6.0;
+}
+
+// grad(lambda_i) . grad(lambda_j) with the roundings spelled out (one product, two fused multiply-adds), so that every
+// kernel that forms it -- the tile kernel, the dense local matrices, the one-off factors of the rescale path -- gets
+// the same bits whatever the compiler would contract
+__device__ __forceinline__ double grad_dot3(const double a0, const double a1, const double a2, const double b0, const double b1,
+                                            const double b2) {
+  return __fma_rn(a2, b2, __fma_rn(a1, b1, __dmul_rn(a0, b0)));
 }
 
 __device__ __forceinline__ void tet_geometry(const double4* __restrict__ p4, const int4 nd, TetGeom& G) {
@@ -431,6 +450,7 @@ __device__ __forceinline__ double splev_dev(const SplineDev& S, double x, int& e
 }
 
 #include "assemble.cuh"
+#include "rescale.cuh"
 #include "demag.cuh"
 
 // mu(|H|), dmu/dH of the material elements from the B-H spline (NewtonRaphson.jl:178-207; manyBodyIntersecting.jl:189-197),
@@ -496,7 +516,7 @@ static __global__ void local_stiffness_kernel(const double4* __restrict__ p4, co
   const double s0 = f ? V * f[k] : V;
   for (int j = 0; j < 4; j++)
     for (int i = 0; i < 4; i++)
-      Ak[16 * (size_t)k + 4 * j + i] = s0 * ((G.g[i][0] * G.g[j][0] + G.g[i][1] * G.g[j][1]) + G.g[i][2] * G.g[j][2]);
+      Ak[16 * (size_t)k + 4 * j + i] = __dmul_rn(s0, grad_dot3(G.g[i][0], G.g[i][1], G.g[i][2], G.g[j][0], G.g[j][1], G.g[j][2]));
 }
 
 static __global__ void volumes_kernel(const double4* __restrict__ p4, const int4* __restrict__ t4, int nt, double* __restrict__ VE) {
@@ -548,6 +568,7 @@ struct PcgCtl {
   // ns of %globaltimer
   unsigned long long* trace;
   int trace_cap;
+  unsigned tag_base;   // LL mailbox tags of this solve start here (host: running bound on the reductions of earlier solves)
 };
 constexpr int kTraceKernels = 4;   // 0 SpMV, 1 update (cg_update), 2 direction, 3 halo push / wait kernels
 
@@ -629,7 +650,7 @@ static __global__ void __launch_bounds__(kVecThreads) pcg_init_kernel(const doub
 // the early exits of ConjugateGradient.h:43-56
 static __global__ void pcg_init_fin_kernel(const double* __restrict__ pbb, const double* __restrict__ prr, const double* __restrict__ prp,
                                     int npart, double tol, int max_iter, unsigned long long epoch, int proj, double inv_n,
-                                    PcgCtl* ctl, unsigned long long* trace = nullptr, int trace_cap = 0) {
+                                    PcgCtl* ctl, unsigned long long* trace = nullptr, int trace_cap = 0, unsigned tag_base = 0u) {
   __shared__ double red[33];
   const double bb = block_sum_array(pbb, npart, red);
   const double rr = block_sum_array(prr, npart, red);
@@ -649,6 +670,7 @@ static __global__ void pcg_init_fin_kernel(const double* __restrict__ pbb, const
     ctl->rmean[0] = ctl->rmean[1] = 0.0;
     ctl->trace = trace_cap > 0 ? trace : nullptr;
     ctl->trace_cap = trace_cap;
+    ctl->tag_base = tag_base;
     ctl->done = (bb == 0.0 || rr < ctl->thr) ? 1 : 0;
   }
 }
@@ -691,7 +713,7 @@ static __global__ void __launch_bounds__(kVecThreads, kPcgVecCtas) pcg_update_ke
   load(i0);   // the first batch is in flight while the producer's partial sums are folded
   double pAp_v[1] = {block_sum_array(part_pAp, npart, red_s)};   // npart == 1: the all-reduced scalar (NCCL path)
   const unsigned long long tw0 = tr ? gtime_ns() : 0ULL;
-  peer_fold<1>(pAp_v, pr, pcg_seq(ctl, j, 0));
+  peer_fold<1>(pAp_v, pr, pcg_seq(ctl, j, 0), ctl->tag_base);
   trace_wait(tr, tw0);
   const double alpha = ctl->absNew[j & 1] / pAp_v[0];
   const bool proj = ctl->proj != 0;
@@ -765,7 +787,7 @@ static __global__ void __launch_bounds__(kVecThreads, kPcgVecCtas) pcg_direction
   double d2v[2];
   block_sum2_array(part2, part2 + stride, npart, red, d2v[0], d2v[1]);
   const unsigned long long tw0 = tr ? gtime_ns() : 0ULL;
-  peer_fold<2>(d2v, pr, pcg_seq(ctl, j, 1));
+  peer_fold<2>(d2v, pr, pcg_seq(ctl, j, 1), ctl->tag_base);
   trace_wait(tr, tw0);
   const double rr = d2v[0], rz = d2v[1];
   const double absOld = ctl->absNew[j & 1];
@@ -876,7 +898,7 @@ static __global__ void __launch_bounds__(kVecThreads, kPcgVecCtas) cg_update_ker
   v3[2] = block_sum_array(part_s, nps, red_s);
   v3[3] = (proj && !first) ? block_sum_array(part_in + 2 * (size_t)stride, npv, red_s) : 0.0;   // sum r of the current residual
   const unsigned long long tw0 = tr ? gtime_ns() : 0ULL;
-  peer_fold3(v3, pr, cg_seq(ctl, it), (int)(ctl->epoch & 1ULL));
+  peer_fold3(v3, pr, cg_seq(ctl, it), (int)(ctl->epoch & 1ULL), ctl->tag_base);
   trace_wait(tr, tw0);
   const double gamma = v3[0], rr = v3[1], delta = v3[2];
   const double m_prev = v3[3] * ctl->inv_n;   // mean of the current r: taken out by this update
@@ -950,7 +972,7 @@ static __global__ void __launch_bounds__(256) cg_chunk_end_kernel(const double* 
     block_sum2_array(part_in, part_in + stride, npv, red_s, v3[0], v3[1]);
     v3[2] = 0.0;
     v3[3] = 0.0;
-    peer_fold3(v3, pr, cg_seq(ctl, itd), (int)(ctl->epoch & 1ULL));   // V_itd never runs: the sequence number is free
+    peer_fold3(v3, pr, cg_seq(ctl, itd), (int)(ctl->epoch & 1ULL), ctl->tag_base);   // V_itd never runs: the sequence number is free
     if (threadIdx.x == 0) {
       ctl->r2 = v3[1];
       if (v3[1] < ctl->thr) { ctl->iters = itd - 1; ctl->done = 1; }

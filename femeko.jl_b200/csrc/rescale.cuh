@@ -1,0 +1,118 @@
+// K1r: RESCALE assembly (included inside namespace fk by kernels.cuh; plan in symbolic.hpp: RescalePlan).
+//
+// Between two Picard steps only the element coefficient s_k = VE[k] mu[k] changes: A = sum_k s_k G_k, G_k the
+// geometric part (grad lambda_i . grad lambda_j) of the local matrix.  The reference's nonlinear loop keeps the local
+// matrices and rescales them by mu every iteration for exactly that reason (NewtonRaphson.jl:114-127,153-161).
+// Here the geometric factors are computed ONCE per handle (geo_build_kernel), stored in the order the sums consume
+// them, and a sweep is three streaming kernels with no shared memory and no block-level synchronisation:
+//   material_update_kernel   mu(|H|) of the elements that carry a B-H curve (kernels.cuh, unchanged)
+//   picard_element_kernel    H = -grad u, |H| of every element, s_k = VE[k] mu[k]
+//   geo_rescale_kernel       one lane per stored entry PAIR {(r,c), (c,r)}: sum of s_k g in ascending element order
+//                            (the order of the tile kernel and of Eigen's setFromTriplets), written to both entries
+// Every product is rounded as the tile kernel rounds it (s_k first: VE[k]*f[k]*(...), src/FEM3D.jl:71), so the two
+// paths agree bit for bit; the tile kernel (assemble.cuh) stays the from-scratch path.
+// Bytes per sweep and tet on a Kuhn mesh: factors 8 + element id 4 per contribution (10.4 incl. padding), 8 per pair
+// for the two value indices, 20 for the values -> ~165 B; element kernel ~70 B.
+
+// the ten local pairs in sym_index order (symbolic.hpp)
+__device__ __forceinline__ void pair_ij(const int q, int& i, int& j) {
+  i = q < 4 ? 0 : (q < 7 ? 1 : (q < 9 ? 2 : 3));
+  j = q - (i == 0 ? 0 : (i == 1 ? 3 : (i == 2 ? 5 : 6)));
+}
+
+// geometric factor of every contribution slot; strips the pair bits of the slot's element reference
+static __global__ void __launch_bounds__(256) geo_build_kernel(const double4* __restrict__ p4, const int4* __restrict__ t4,
+                                                               uint32_t* __restrict__ cref, long long nslots,
+                                                               double* __restrict__ g) {
+  for (long long s = blockIdx.x * (long long)blockDim.x + threadIdx.x; s < nslots; s += (long long)gridDim.x * blockDim.x) {
+    const uint32_t c = cref[s];
+    if (c == 0xffffffffu) { g[s] = 0.0; continue; }
+    const int k = (int)(c & 0x0fffffffu);
+    int pi, pj;
+    pair_ij((int)(c >> 28), pi, pj);
+    TetGeom G;
+    tet_geometry(p4, __ldg(t4 + k), G);
+    double a0 = 0, a1 = 0, a2 = 0, b0 = 0, b1 = 0, b2 = 0;
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+      if (q == pi) { a0 = G.g[q][0]; a1 = G.g[q][1]; a2 = G.g[q][2]; }
+      if (q == pj) { b0 = G.g[q][0]; b1 = G.g[q][1]; b2 = G.g[q][2]; }
+    }
+    g[s] = grad_dot3(a0, a1, a2, b0, b1, b2);
+    cref[s] = (uint32_t)k;
+  }
+}
+
+// s_k = VE[k] f[k] of a plain stiffness assembly (f nullable = 1)
+static __global__ void __launch_bounds__(256) geo_scale_kernel(const double* __restrict__ VE, const double* __restrict__ f, int nt,
+                                                               double* __restrict__ s0) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= nt) return;
+  s0[k] = f ? __dmul_rn(VE[k], f[k]) : __dmul_rn(VE[k], 1.0);
+}
+
+// Picard sweep, element part: field recovery of EVERY element (NewtonRaphson.jl:178-197) and its scale s_k = VE[k] mu[k];
+// mu of the material elements was refreshed by material_update_kernel just before.  VE == nullptr: |det| / 6.
+static __global__ void __launch_bounds__(256) picard_element_kernel(const double4* __restrict__ p4, const int4* __restrict__ t4,
+                                                                    const double* __restrict__ u, const double* __restrict__ mu,
+                                                                    const double* __restrict__ VE, int nt, int compat,
+                                                                    double* __restrict__ Hn, double* __restrict__ Hfield,
+                                                                    double* __restrict__ s0) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= nt) return;
+  const int4 nd = __ldg(t4 + k);
+  const double f = __ldcs(mu + k);
+  const double u0 = __ldg(u + nd.x), u1 = __ldg(u + nd.y), u2 = __ldg(u + nd.z), u3 = __ldg(u + nd.w);
+  TetGeom G;
+  tet_geometry(p4, nd, G);
+  double hx = -(u0 * G.g[0][0]) - u1 * G.g[1][0] - u2 * G.g[2][0] - u3 * G.g[3][0];
+  double hy = -(u0 * G.g[0][1]) - u1 * G.g[1][1] - u2 * G.g[2][1] - u3 * G.g[3][1];
+  double hz = -(u0 * G.g[0][2]) - u1 * G.g[1][2] - u2 * G.g[2][2] - u3 * G.g[3][2];
+  if (compat) { hy += hz; hz = 0.0; }  // NewtonRaphson.jl:187-189: d-term lands in row 2
+  __stcs(Hn + k, norm3(hx, hy, hz));
+  if (Hfield) {
+    __stcs(Hfield + 3 * (size_t)k, hx);
+    __stcs(Hfield + 3 * (size_t)k + 1, hy);
+    __stcs(Hfield + 3 * (size_t)k + 2, hz);
+  }
+  const double V = VE ? __ldcs(VE + k) : G.vol;
+  s0[k] = __dmul_rn(V, f);
+}
+
+// One warp per slice of 32 items; a lane works through its item's contributions in batches of B: the B element ids and
+// factors (coalesced, streaming) and then B independent gathers of s are in flight before the ordered fold starts.
+constexpr int kGeoThreads = 256;
+template <int B, int MINB>
+static __global__ void __launch_bounds__(kGeoThreads, MINB) geo_rescale_kernel(const uint32_t* __restrict__ slice_ptr,
+                                                                               const int* __restrict__ dst1, const int* __restrict__ dst2,
+                                                                               const uint32_t* __restrict__ cref, const double* __restrict__ g,
+                                                                               const double* __restrict__ s0, int nslices,
+                                                                               double* __restrict__ vals) {
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  constexpr int WPB = kGeoThreads / 32;
+  for (int s = blockIdx.x * WPB + wib; s < nslices; s += gridDim.x * WPB) {
+    const uint32_t b0 = __ldg(slice_ptr + s);
+    const int w = (int)(__ldg(slice_ptr + s + 1) - b0);
+    const int d1 = __ldcs(dst1 + (size_t)s * 32 + lane), d2 = __ldcs(dst2 + (size_t)s * 32 + lane);
+    const uint32_t* __restrict__ rp = cref + (size_t)b0 * 32 + lane;
+    const double* __restrict__ gp = g + (size_t)b0 * 32 + lane;
+    double acc = 0.0;
+    for (int k = 0; k < w; k += B) {
+      uint32_t rr[B];
+      double gg[B], ss[B];
+#pragma unroll
+      for (int q = 0; q < B; q++) rr[q] = (k + q < w) ? __ldcs(rp + (size_t)(k + q) * 32) : 0xffffffffu;
+#pragma unroll
+      for (int q = 0; q < B; q++) gg[q] = (k + q < w) ? __ldcs(gp + (size_t)(k + q) * 32) : 0.0;
+#pragma unroll
+      for (int q = 0; q < B; q++) ss[q] = rr[q] != 0xffffffffu ? __ldg(s0 + rr[q]) : 0.0;
+#pragma unroll
+      for (int q = 0; q < B; q++)
+        if (rr[q] != 0xffffffffu) acc = __dadd_rn(acc, __dmul_rn(ss[q], gg[q]));
+    }
+    if (d1 >= 0) {
+      vals[d1] = acc;
+      if (d2 >= 0) vals[d2] = acc;
+    }
+  }
+}

@@ -160,15 +160,21 @@ static __global__ void __launch_bounds__(kSpmvThreads, MINB) spmv_sell_fused_ker
   const unsigned long long seq = cg_seq(ctl, ctl->base_it + j);
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   constexpr int WPB = kSpmvThreads / 32;
-  if ((int)blockIdx.x < hf.npush) {
+  // the LAST hf.npush CTAs push: the slice schedule below gives them one slice per warp less than the others, which pays
+  // for the push (stores over NVLink, one system fence, the ticket), so they do not end the kernel late
+  const int first_pusher = (int)gridDim.x - hf.npush;
+  if ((int)blockIdx.x >= first_pusher) {
+    const int pidx = (int)blockIdx.x - first_pusher;
     for (int q = 0; q < hf.nneigh; q++) {
       const int b = hf.send_ptr[q], n = hf.send_ptr[q + 1] - b;
       double* __restrict__ dst = hf.dst[q];
-      for (int i = blockIdx.x * kSpmvThreads + threadIdx.x; i < n; i += hf.npush * kSpmvThreads) dst[i] = x[__ldg(hf.send_idx + b + i)];
+      for (int i = pidx * kSpmvThreads + threadIdx.x; i < n; i += hf.npush * kSpmvThreads) dst[i] = x[__ldg(hf.send_idx + b + i)];
     }
-    __threadfence_system();
     __syncthreads();
-    if (threadIdx.x == 0) last_pusher = (atomicAdd(hf.ticket, 1u) == (unsigned)hf.npush - 1u) ? 1 : 0;
+    if (threadIdx.x == 0) {   // one fence per CTA: the barrier orders every thread's stores before it
+      __threadfence_system();
+      last_pusher = (atomicAdd(hf.ticket, 1u) == (unsigned)hf.npush - 1u) ? 1 : 0;
+    }
     __syncthreads();
     if (last_pusher) {
       if ((int)threadIdx.x < hf.nneigh) {
@@ -180,7 +186,10 @@ static __global__ void __launch_bounds__(kSpmvThreads, MINB) spmv_sell_fused_ker
   }
   double dot = 0.0;
   bool waited = false;
-  for (int q = blockIdx.x * WPB + wib; q < nslices; q += gridDim.x * WPB) {
+  // static schedule: pass 0 covers the first Wn slices with the non-pushing warps only; every later pass is a stride of
+  // all W warps.  Fixed per launch shape, so the per-CTA partial sums are reproducible.
+  const int W = (int)gridDim.x * WPB, Wn = first_pusher * WPB, wid = (int)blockIdx.x * WPB + wib;
+  for (int q = wid < Wn ? wid : Wn + wid; q < nslices; q = q < Wn ? Wn + wid : q + W) {
     const int sl = __ldg(slice_list + q);
     const int4 m = __ldg(slice_meta + sl);
     const int r = __ldg(srow + sl * kSellC + lane);

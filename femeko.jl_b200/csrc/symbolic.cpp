@@ -486,4 +486,120 @@ void build_symbolic(const double* p, const int* t, int nv, int nt, const Symboli
 
 }
 
+// ------------------------------------------------------------------------------------------------
+// rescale plan (symbolic.hpp: RescalePlan)
+// ------------------------------------------------------------------------------------------------
+void build_rescale_plan(const Symbolic& S, int window, RescalePlan& R) {
+  const int nt = S.nt;
+  const int64_t nnz = S.nnz;
+  if ((int64_t)nt >= ((int64_t)1 << 28)) throw std::runtime_error("fk: too many elements on one GPU for the rescale plan (28-bit ids)");
+  if (window < 32) window = 32;
+  window = (window + 31) & ~31;
+  const int* e2 = S.e2nnz.data();
+  // canonical entry of local pair (a, b), a <= b, of element k; other = its mirror (or -1)
+  auto canon = [&](int64_t k, int a, int b, int& other) -> int {
+    const int e1 = e2[16 * k + 4 * a + b], eb = e2[16 * k + 4 * b + a];
+    if (a == b || e1 == eb) { other = -1; return e1; }
+    if (e1 >= 0 && eb >= 0) { other = std::max(e1, eb); return std::min(e1, eb); }
+    other = -1;
+    return e1 >= 0 ? e1 : eb;
+  };
+  // ---- contributions per canonical entry ----------------------------------------------------------
+  std::vector<int> cnt((size_t)nnz, 0), mirror((size_t)nnz, -1);
+#pragma omp parallel for schedule(static)
+  for (int64_t k = 0; k < nt; k++)
+    for (int a = 0; a < 4; a++)
+      for (int b = a; b < 4; b++) {
+        int other;
+        const int c = canon(k, a, b, other);
+        if (c < 0) continue;
+#pragma omp atomic
+        cnt[c]++;
+        if (other >= 0) {
+#pragma omp atomic write
+          mirror[c] = other;
+        }
+      }
+  // ---- items in SELL order of their canonical entry ------------------------------------------------
+  std::vector<int> at((size_t)S.nnz_sell, -1);   // SELL index -> canonical CSR index
+#pragma omp parallel for schedule(static)
+  for (int64_t e = 0; e < nnz; e++)
+    if (cnt[e] > 0) at[S.csr2sell[e]] = (int)e;
+  std::vector<int> items;
+  items.reserve((size_t)(nnz / 2 + S.n_rows + 64));
+  for (int64_t q = 0; q < S.nnz_sell; q++)
+    if (at[q] >= 0) items.push_back(at[q]);
+  std::vector<int>().swap(at);
+  const int64_t ni = (int64_t)items.size();
+  R.n_items = ni;
+  R.nslices = (int)((ni + 31) / 32);
+  // ---- windows sorted by list length, longest first (stable) ---------------------------------------
+  const int64_t nwin = (ni + window - 1) / window;
+#pragma omp parallel for schedule(dynamic, 16)
+  for (int64_t w = 0; w < nwin; w++) {
+    const int64_t b = w * window, e = std::min(ni, b + window);
+    std::stable_sort(items.begin() + b, items.begin() + e, [&](int x, int y) { return cnt[x] > cnt[y]; });
+  }
+  // ---- slices ----------------------------------------------------------------------------------------
+  R.slice_ptr.assign((size_t)R.nslices + 1, 0u);
+  R.max_width = 0;
+  uint64_t run = 0;
+  for (int s = 0; s < R.nslices; s++) {
+    int w = 0;
+    for (int64_t i = 32 * (int64_t)s; i < std::min(ni, 32 * (int64_t)s + 32); i++) w = std::max(w, cnt[items[i]]);
+    R.max_width = std::max(R.max_width, w);
+    R.slice_ptr[s] = (uint32_t)run;
+    run += (uint64_t)w;
+    if (run > 0xffffffffULL) throw std::runtime_error("fk: rescale plan too large for one GPU; partition the mesh");
+  }
+  R.slice_ptr[R.nslices] = (uint32_t)run;
+  R.n_slots = 32 * (int64_t)run;
+  R.dst1.assign((size_t)32 * R.nslices, -1);
+  R.dst2.assign((size_t)32 * R.nslices, -1);
+  std::vector<int64_t> slot_of((size_t)nnz, -1);   // canonical CSR index -> first slot (32 slice_ptr + lane)
+#pragma omp parallel for schedule(static)
+  for (int64_t i = 0; i < ni; i++) {
+    const int c = items[i];
+    R.dst1[i] = S.csr2sell[c];
+    R.dst2[i] = mirror[c] >= 0 ? S.csr2sell[mirror[c]] : -1;
+    slot_of[c] = 32 * (int64_t)R.slice_ptr[i >> 5] + (i & 31);
+  }
+  // ---- contribution lists ------------------------------------------------------------------------------
+  R.cref.assign((size_t)R.n_slots, 0xffffffffu);
+  std::vector<int> fill((size_t)nnz, 0);
+  int64_t total = 0;
+#pragma omp parallel for schedule(static) reduction(+ : total)
+  for (int64_t k = 0; k < nt; k++)
+    for (int a = 0; a < 4; a++)
+      for (int b = a; b < 4; b++) {
+        int other;
+        const int c = canon(k, a, b, other);
+        if (c < 0) continue;
+        int f;
+#pragma omp atomic capture
+        f = fill[c]++;
+        R.cref[(size_t)(slot_of[c] + 32 * (int64_t)f)] = (uint32_t)k | ((uint32_t)sym_index(a, b) << 28);
+        total++;
+      }
+  R.n_contrib = total;
+  // ascending element order inside every list (the fill order above depends on the thread schedule)
+#pragma omp parallel
+  {
+    std::vector<uint32_t> buf;
+#pragma omp for schedule(static)
+    for (int64_t i = 0; i < ni; i++) {
+      const int c = items[i], n = cnt[c];
+      if (n < 2) continue;
+      const int64_t s0 = slot_of[c];
+      buf.resize((size_t)n);
+      for (int e = 0; e < n; e++) buf[e] = R.cref[(size_t)(s0 + 32 * (int64_t)e)];
+      std::sort(buf.begin(), buf.end(), [](uint32_t x, uint32_t y) {
+        const uint32_t kx = x & 0x0fffffffu, ky = y & 0x0fffffffu;
+        return kx != ky ? kx < ky : x < y;
+      });
+      for (int e = 0; e < n; e++) R.cref[(size_t)(s0 + 32 * (int64_t)e)] = buf[e];
+    }
+  }
+}
+
 }  // namespace fk

@@ -83,6 +83,26 @@ struct Symbolic {
   std::vector<int> sell_diag;        // n_rows: SELL index of (r,r), -1 if absent
 };
 
+// Plan of the RESCALE assembly (api.cu: ensure_geo): the stiffness matrix of a Picard step is A = sum_k s_k G_k with
+// s_k = VE[k] f[k] the only thing that changes between steps (NewtonRaphson.jl:114-127,153-161 keeps the local
+// matrices Ak and rescales them by mu every iteration).  The plan lists, for every stored entry pair {(r,c), (c,r)},
+// its contributions (element, local pair) in ascending element order -- the summation order of the tile kernel and of
+// Eigen's setFromTriplets.  An item = one canonical entry (the smaller CSR index of the pair, or the only one stored on
+// this partition); items follow the SELL order of their canonical entry, are sorted by list length inside windows
+// (longest first) and are cut into slices of 32: lane l of slice s owns item 32 s + l, its e-th contribution sits at
+// 32 (slice_ptr[s] + e) + l, so a warp reads 32 consecutive geometric factors / element ids per step.
+struct RescalePlan {
+  int64_t n_items = 0;             // canonical entries
+  int nslices = 0;
+  int64_t n_contrib = 0;           // contributions listed (10 per element on an unpartitioned mesh)
+  int64_t n_slots = 0;             // padded contribution slots = 32 * slice_ptr[nslices]
+  int max_width = 0;
+  std::vector<uint32_t> slice_ptr; // nslices + 1, in units of 32 slots
+  std::vector<int> dst1, dst2;     // 32 * nslices: SELL index of the item's entry / of its mirror (-1: none; dst1 -1: padding lane)
+  std::vector<uint32_t> cref;      // n_slots: element id | local pair (sym_index) << 28; 0xffffffff = padding
+};
+void build_rescale_plan(const Symbolic& S, int window, RescalePlan& R);
+
 // p: 3 x nv (may be null when natural_order), t: 4 x nt 0-based.  Throws std::runtime_error on bad input.
 void build_symbolic(const double* p, const int* t, int nv, int nt, const SymbolicOpts& o, Symbolic& S);
 

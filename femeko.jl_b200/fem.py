@@ -84,6 +84,12 @@ class Femeko:
     def synchronize(self):
         L.check(self.lib.fk_synchronize(self.h))
 
+    def geo_stats(self):
+        """(entry pairs, contributions, padded slots, device bytes) of the rescale-assembly plan (built if needed)."""
+        v = [C.c_longlong() for _ in range(4)]
+        L.check(self.lib.fk_geo_stats(self.h, *[C.byref(x) for x in v]))
+        return tuple(x.value for x in v)
+
     def trace_read(self):
         """Timeline of the last solve (after tune(11, n)): array [iteration slot, kernel (0 SpMV, 1 update, 2 direction, 3),
         {start, end, longest cross-GPU wait, wait of CTA 0}] in ns; unused records have start = 2^64 - 1."""

@@ -62,6 +62,7 @@ _SIGS = {
     "fk_synchronize": (C.c_int, [_H]),
     "fk_tune": (C.c_int, [_H, C.c_int, C.c_int]),
     "fk_launch_count": (C.c_int, [_H, C.POINTER(C.c_longlong)]),
+    "fk_geo_stats": (C.c_int, [_H] + [C.POINTER(C.c_longlong)] * 4),
     "fk_trace_read": (C.c_int, [_H, C.POINTER(C.c_ulonglong), C.c_int, C.POINTER(C.c_int)]),
     "fk_sizes": (C.c_int, [_H, c_int_p, c_int_p, C.POINTER(C.c_longlong), c_int_p]),
     "fk_csr_pattern": (C.c_int, [_H, c_int_p, c_int_p]),
@@ -75,6 +76,9 @@ _SIGS = {
                                     C.POINTER(C.c_longlong), c_int_p, C.POINTER(C.c_longlong)]),
     "fk_symbolic_export": (C.c_int, [_H] + [C.c_void_p] * 15),
     "fk_symbolic_colz": (C.c_int, [_H, C.POINTER(C.c_longlong), C.POINTER(C.c_longlong), C.c_void_p, C.c_void_p]),
+    "fk_set_host_threads": (C.c_int, [C.c_int]),
+    "fk_symbolic_rescale": (C.c_int, [_H, C.POINTER(C.c_longlong), c_int_p, C.POINTER(C.c_longlong), C.c_void_p, C.c_void_p, C.c_void_p,
+                                      C.c_void_p]),
     "fk_symbolic_destroy": (C.c_int, [_H]),
     "fk_assemble_stiffness": (C.c_int, [_H, C.c_int, c_double_p, c_double_p]),
     "fk_assemble_mass": (C.c_int, [_H, C.c_int, c_double_p, c_double_p]),

@@ -287,3 +287,99 @@ def kuhn_slab(N: int, rank: int, world: int, inside_edge: float = 0.2):
         owner[n_owned + (pl if has_l else 0):] = rank + 1
     P.neigh, P.send_ptr, P.send_idx, P.recv_start, P.recv_count = _halo_plan(owner, l2g, loc.t, rank, P.n_owned)
     return loc, P
+
+
+# --------------------------------------------------------------------------------------------------
+# strong scaling: ONE global Kuhn cube cut into px x py x pz blocks of nodes (what RCB yields for a cube),
+# every rank's share generated directly -- the global mesh (100 M tets at N = 256) is never materialised
+# --------------------------------------------------------------------------------------------------
+GRIDS = {1: (1, 1, 1), 2: (2, 1, 1), 4: (2, 2, 1), 8: (2, 2, 2)}
+
+
+def block_bounds(N: int, parts: int):
+    """Node planes [a_r, a_{r+1}) of the N + 1 planes along one axis owned by block r."""
+    return [(r * (N + 1)) // parts for r in range(parts + 1)]
+
+
+def block_part(N: int, grid) -> np.ndarray:
+    """Node partition of kuhn_cube(N) into grid = (px, py, pz) blocks; rank = (bx * py + by) * pz + bz."""
+    n1 = N + 1
+    b = [np.searchsorted(np.asarray(block_bounds(N, g)[1:]), np.arange(n1), side="right") for g in grid]
+    part = (b[0][:, None, None] * grid[1] + b[1][None, :, None]) * grid[2] + b[2][None, None, :]
+    return part.ravel().astype(np.int32)
+
+
+def kuhn_block(N: int, rank: int, grid, inside_edge: float = 0.2):
+    """Rank `rank`'s share of kuhn_cube(N) partitioned by block_part(N, grid), generated directly: identical (node
+    order, element order, surface triangles, halo plan) to partition_mesh(kuhn_cube(N), block_part(N, grid), rank)
+    -- tests/test_partition.py checks that at small N.  Work and memory are proportional to the rank's share."""
+    from itertools import permutations
+
+    px, py, pz = (int(g) for g in grid)
+    world = px * py * pz
+    n1 = N + 1
+    bidx = (rank // (py * pz), (rank // pz) % py, rank % pz)
+    bounds = [block_bounds(N, g) for g in (px, py, pz)]
+    a0 = [bounds[d][bidx[d]] for d in range(3)]
+    a1 = [bounds[d][bidx[d] + 1] for d in range(3)]
+    c0 = [max(a0[d] - 1, 0) for d in range(3)]            # cells with a corner on an owned plane, per axis
+    c1 = [min(a1[d], N) for d in range(3)]
+    E = [c1[d] - c0[d] + 1 for d in range(3)]             # node box spanned by those cells
+    ii, jj, kk = np.meshgrid(*[np.arange(c0[d], c1[d], dtype=np.int64) for d in range(3)], indexing="ij")
+    ii, jj, kk = ii.ravel(), jj.ravel(), kk.ravel()
+    ncell = ii.size
+    # six tets per cell as (i, j, k) lattice paths, in the element order of kuhn_cells (cells lexicographic, 6 per cell)
+    box = np.empty((ncell, 6, 4), dtype=np.int64)         # flat index inside the node box
+    own = np.zeros((ncell, 6), dtype=bool)
+    step = np.eye(3, dtype=np.int64)
+    for q, perm in enumerate(permutations(range(3))):
+        v = [ii.copy(), jj.copy(), kk.copy()]
+        for m in range(4):
+            if m > 0:
+                ax = perm[m - 1]
+                v[ax] = v[ax] + step[ax, ax]
+            box[:, q, m] = ((v[0] - c0[0]) * E[1] + (v[1] - c0[1])) * E[2] + (v[2] - c0[2])
+            own[:, q] |= ((v[0] >= a0[0]) & (v[0] < a1[0]) & (v[1] >= a0[1]) & (v[1] < a1[1]) & (v[2] >= a0[2]) & (v[2] < a1[2]))
+    del ii, jj, kk
+    box = box.reshape(ncell * 6, 4)[own.ravel()]          # elements touching an owned node, ascending global id
+    nbox = E[0] * E[1] * E[2]
+    used = np.zeros(nbox, dtype=bool)
+    used[box.ravel()] = True
+    bi, bj, bk = np.unravel_index(np.arange(nbox, dtype=np.int64), E)
+    gi, gj, gk = bi + c0[0], bj + c0[1], bk + c0[2]
+    owned_box = (gi >= a0[0]) & (gi < a1[0]) & (gj >= a0[1]) & (gj < a1[1]) & (gk >= a0[2]) & (gk < a1[2])
+    assert used[owned_box].all()
+    gid = (gi * n1 + gj) * n1 + gk
+    blk = [np.searchsorted(np.asarray(bounds[d][1:]), g, side="right") for d, g in enumerate((gi, gj, gk))]
+    owner_box = ((blk[0] * py + blk[1]) * pz + blk[2]).astype(np.int32)
+    owned_idx = np.flatnonzero(owned_box)                  # box order == ascending global id
+    halo_idx = np.flatnonzero(used & ~owned_box)
+    halo_idx = halo_idx[np.lexsort((gid[halo_idx], owner_box[halo_idx]))]
+    order = np.concatenate([owned_idx, halo_idx])
+    lid = -np.ones(nbox, dtype=np.int64)
+    lid[order] = np.arange(order.size)
+    n_owned = int(owned_idx.size)
+    l2g = gid[order]
+    loc = MESH()
+    loc.t = np.asfortranarray(lid[box].T.astype(np.int32))
+    del box
+    g = (np.arange(n1, dtype=np.float64) / N - 0.5) * 1.0
+    loc.p = np.asfortranarray(np.stack([g[gi[order]], g[gj[order]], g[gk[order]]]))
+    # outer surface: the global triangles (restricted to this rank's x range of cells) that hold an owned node
+    sg = _box_surface((N, N, N), True, x_range=(c0[0], c1[0]))
+    si, sj, sk = sg[:3] // (n1 * n1), (sg[:3] // n1) % n1, sg[:3] % n1
+    s_own = ((si >= a0[0]) & (si < a1[0]) & (sj >= a0[1]) & (sj < a1[1]) & (sk >= a0[2]) & (sk < a1[2])).any(axis=0)
+    sg, si, sj, sk = sg[:, s_own], si[:, s_own], sj[:, s_own], sk[:, s_own]
+    sl = sg.copy()
+    sl[:3] = lid[((si - c0[0]) * E[1] + (sj - c0[1])) * E[2] + (sk - c0[2])]
+    assert (sl[:3] >= 0).all()
+    sl = _orient_outward(loc.p, sl, np.zeros(3))
+    loc.surfaceT = np.asfortranarray(sl.astype(np.int32))
+    loc.shell_id = [0]
+    cen = (loc.p[:, loc.t[0]] + loc.p[:, loc.t[1]] + loc.p[:, loc.t[2]] + loc.p[:, loc.t[3]]) / 4
+    half = 0.5 * inside_edge
+    _finish(loc, np.all(np.abs(cen) <= half, axis=0))
+    P = Partition(rank=rank, world=world, n_owned=n_owned, l2g=l2g, nv_global=n1 ** 3)
+    P.nt_owned = int((loc.t[0] < n_owned).sum())
+    P.neigh, P.send_ptr, P.send_idx, P.recv_start, P.recv_count = _halo_plan(owner_box[order], l2g, loc.t, rank, n_owned)
+    return loc, P

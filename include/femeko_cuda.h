@@ -69,6 +69,10 @@ typedef struct fk_pcg_opts {
 } fk_pcg_opts;
 
 const char* fk_last_error(void);
+/* Host threads (OpenMP) of the symbolic phase (fk_create, the rescale plan); n <= 0 only queries.  Returns the count in
+ * effect.  Launchers that pin OMP_NUM_THREADS = 1 per process (torch.distributed.run) make fk_create of a 50 M-tet
+ * partition take minutes; a driver with one process per GPU gives each process its share of the cores here.        */
+int fk_set_host_threads(int n);
 int fk_version(void);
 
 /* ---- lifecycle -------------------------------------------------------------------------------
@@ -97,6 +101,12 @@ int fk_tune(fk_handle h, int what, int value);
 /* Timeline records of the last solve (fk_tune 11): record (it % cap) * 4 + k of kernel k (0 SpMV, 1 update, 2 direction)
  * is four 64-bit words {earliest CTA start, latest CTA end, longest cross-GPU wait, wait of CTA 0}, ns of the GPU's
  * %globaltimer; an unused record has start = 2^64 - 1.  Copies min(max_records, 4 cap) records.                    */
+/* Rescale assembly (fk_tune 10: 0 never, 1 = from the second Picard sweep of the handle on (default), 2 = at once; fk_tune 12: its
+ * launch shape): the geometric factors grad(lambda_i).grad(lambda_j) of every contribution are computed once and every
+ * later stiffness assembly / Picard sweep streams sum_k VE[k] f[k] g, bit-identical to the tile kernel, the way
+ * NewtonRaphson.jl:114-127,153-161 keeps Ak and rescales it by mu.  fk_geo_stats builds the plan if needed and reports
+ * its size: entry pairs, contributions, padded slots, device bytes (12 B per slot + 8 B per pair + 8 B per element).   */
+int fk_geo_stats(fk_handle h, long long* items, long long* contributions, long long* slots, long long* bytes);
 int fk_trace_read(fk_handle h, unsigned long long* out, int max_records, int* n_records);
 /* number of kernels of this library launched through the handle so far (graph nodes included) */
 int fk_launch_count(fk_handle h, long long* n);
@@ -141,6 +151,11 @@ int fk_symbolic_export(fk_symbolic s, int* rowptr, int* colind, int* diag, int* 
  * 32-bit columns (2 width units).  n_slices16 = slices stored with 16-bit columns.                          */
 int fk_symbolic_colz(fk_symbolic s, long long* n_colz, long long* n_slices16, int* slice_meta /* 4 x nslices */,
                      unsigned short* colz /* n_colz */);
+/* plan of the rescale assembly (symbolic.hpp: RescalePlan): item 32 s + l = lane l of slice s, its e-th contribution at
+ * cref[32 (slice_ptr[s] + e) + l] = element | local pair << 28 (0xffffffff: padding); dst1 / dst2 = SELL index of the
+ * item's entry and of its mirror (-1: none).  Call with NULL arrays for the sizes first.                            */
+int fk_symbolic_rescale(fk_symbolic s, long long* n_items, int* n_slices, long long* n_slots, unsigned int* slice_ptr /* n_slices+1 */,
+                        int* dst1 /* 32 n_slices */, int* dst2, unsigned int* cref /* n_slots */);
 int fk_symbolic_destroy(fk_symbolic s);
 
 /* ---- assembly: stiffnessMatrix / massMatrix / tangentialStiffnessMatrix ----------------------

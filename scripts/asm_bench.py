@@ -1,0 +1,71 @@
+#!/usr/bin/env python
+"""Assembly micro-benchmark (B200): CUDA-event times of the Picard sweep and of a plain stiffness assembly through the
+tile kernel and through the rescale path (every launch shape of fk_tune 12), at one Kuhn size.  One JSON line per case.
+    python scripts/asm_bench.py [N=119] [reps=20] [short]       short: two launches per path only (for ncu)"""
+import json
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import femeko_jl_b200 as fk  # noqa: E402
+
+MU0 = 4e-7 * np.pi
+n = int(sys.argv[1]) if len(sys.argv) > 1 else 119
+reps = int(sys.argv[2]) if len(sys.argv) > 2 else 20
+short = len(sys.argv) > 3
+m = fk.kuhn_cube(n, inside_edge=0.2)
+g = np.load(os.path.join(ROOT, "tests", "golden", "gd_270K.npz"))
+h = fk.Femeko(m, use_mesh_VE=False, device=0)
+h.set_spline(0, fk.Spline1D(g["HofM"], g["mu"], bc="nearest"))
+h.set_spline(fk.lib.FK_MAX_SPLINES // 2, fk.Spline1D(g["HofM"], g["dmu"], bc="nearest"))
+h.set_inside(m.InsideElements)
+h.set_mu(np.full(m.nt, MU0))
+u = torch.from_numpy(-(np.array([0.5, 0, 0]) / MU0) @ m.p).cuda()
+big = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")     # L2 flush between timed launches
+nt, nv, nnz = h.nt, h.nv, h.nnz
+picard_bytes = (16 + 8 + 64 + 24 + 8 + 8) * nt + (24 + 8) * nv + 8 * nnz
+stiff_bytes = 88 * nt + 24 * nv + 8 * nnz
+
+
+def timed(fn, reps):
+    ts = []
+    for _ in range(reps):
+        big.zero_()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        fn()
+        e1.record()
+        torch.cuda.synchronize()
+        ts.append(e0.elapsed_time(e1))
+    ts.sort()
+    return ts[len(ts) // 2], ts[0]
+
+
+def report(name, t, nbytes):
+    med, best = t
+    print(json.dumps({"case": name, "N": n, "ms_median": round(med, 4), "ms_best": round(best, 4),
+                      "algorithmic_GBps": round(nbytes / med / 1e6, 1), "frac_of_6550": round(nbytes / med / 1e6 / 6550.7, 3),
+                      "gtets_per_s": round(nt / med / 1e6, 2)}), flush=True)
+
+
+sweep = lambda: h.picard_step_dev(u.data_ptr(), slot=0, sync=False)   # noqa: E731
+stiff = lambda: h.assemble_stiffness_dev(h.device_ptr(3), slot=1)      # noqa: E731
+r = 2 if short else reps
+h.tune(10, 0)
+sweep(); stiff(); h.synchronize()
+report("picard_sweep_tile", timed(sweep, r), picard_bytes)
+report("stiffness_tile", timed(stiff, r), stiff_bytes)
+h.tune(10, 2)
+sweep(); stiff(); h.synchronize()
+print(json.dumps({"geo_stats(items, contributions, slots, bytes)": h.geo_stats()}), flush=True)
+for v in ([0] if short else [0, 1, 2, 3]):
+    h.tune(12, v)
+    sweep(); stiff(); h.synchronize()
+    report(f"picard_sweep_rescale_v{v}", timed(sweep, r), picard_bytes)
+    report(f"stiffness_rescale_v{v}", timed(stiff, r), stiff_bytes)
+h.picard_result()
+h.close()

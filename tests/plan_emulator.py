@@ -13,6 +13,7 @@ SYM = np.array([[0, 1, 2, 3], [1, 4, 5, 6], [2, 5, 7, 8], [3, 6, 8, 9]])
 def export_symbolic(mesh, **opts):
     lib = L.load()
     o = L.fk_create_opts()
+    want_rescale = opts.pop("_rescale", True)
     for k, v in opts.items():
         setattr(o, k, int(v))
     p = np.asfortranarray(mesh.p, dtype=np.float64)
@@ -41,6 +42,15 @@ def export_symbolic(mesh, **opts):
     out["colz"] = np.zeros(ncz.value, np.uint16)
     L.check(lib.fk_symbolic_colz(s, None, None, C.c_void_p(out["slice_meta"].ctypes.data), C.c_void_p(out["colz"].ctypes.data)))
     out["n_slices16"] = n16.value
+    if want_rescale:
+        ni, nsr, nslots = C.c_longlong(), C.c_int(), C.c_longlong()
+        L.check(lib.fk_symbolic_rescale(s, C.byref(ni), C.byref(nsr), C.byref(nslots), None, None, None, None))
+        out["r_slice_ptr"] = np.zeros(nsr.value + 1, np.uint32)
+        out["r_dst1"] = np.zeros(32 * nsr.value, np.int32)
+        out["r_dst2"] = np.zeros(32 * nsr.value, np.int32)
+        out["r_cref"] = np.zeros(nslots.value, np.uint32)
+        L.check(lib.fk_symbolic_rescale(s, None, None, None, *[C.c_void_p(out[k].ctypes.data) for k in ("r_slice_ptr", "r_dst1", "r_dst2", "r_cref")]))
+        out["r_items"], out["r_nslices"], out["r_slots"] = ni.value, nsr.value, nslots.value
     lib.fk_symbolic_destroy(s)
     out["ntiles"] = T
     out["nnz"] = nnz.value
@@ -73,6 +83,37 @@ def run_plan(plan, Ak):
             vals[g[q]] = contrib[coff[q]:coff[q + 1]].sum() if coff[q + 1] - coff[q] > 8 else sum(contrib[coff[q]:coff[q + 1]], 0.0)
         written[g] += 1
     return vals, written
+
+
+def run_rescale_plan(plan, G10, s0):
+    """Execute the rescale plan (symbolic.hpp: RescalePlan) the way geo_rescale_kernel walks it: one lane per item,
+    contributions left to right, s0[element] * G10[pair, element] rounded separately, the sum written to the item's
+    entry and to its mirror.  G10: 10 x nt unscaled geometric factors (sym_index order).  Returns CSR values and the
+    number of times each stored entry was written."""
+    vs = np.full(plan["nnz_sell"], np.nan)
+    written = np.zeros(plan["nnz_sell"], np.int32)
+    sp, cref = plan["r_slice_ptr"].astype(np.int64), plan["r_cref"]
+    for s in range(plan["r_nslices"]):
+        w = int(sp[s + 1] - sp[s])
+        block = cref[32 * sp[s]: 32 * sp[s + 1]].reshape(w, 32)
+        acc = np.zeros(32)
+        for e in range(w):
+            c = block[e]
+            live = c != 0xFFFFFFFF
+            k = (c & 0x0FFFFFFF).astype(np.int64)
+            q = (c >> 28).astype(np.int64)
+            prod = np.where(live, s0[np.where(live, k, 0)] * G10[np.where(live, q, 0), np.where(live, k, 0)], 0.0)
+            acc = np.where(live, acc + prod, acc)
+            if e > 0:   # a padding slot is never followed by a live one, and elements ascend inside a list
+                prev = block[e - 1]
+                assert not np.any(live & (prev == 0xFFFFFFFF))
+                assert np.all((prev[live] & 0x0FFFFFFF) <= (c[live] & 0x0FFFFFFF))
+        d1, d2 = plan["r_dst1"][32 * s: 32 * s + 32], plan["r_dst2"][32 * s: 32 * s + 32]
+        vs[d1[d1 >= 0]] = acc[d1 >= 0]
+        vs[d2[d2 >= 0]] = acc[d2 >= 0]
+        np.add.at(written, d1[d1 >= 0], 1)
+        np.add.at(written, d2[d2 >= 0], 1)
+    return vs[plan["csr2sell"]], written[plan["csr2sell"]]
 
 
 def sell_spmv(plan, vals_csr, x):

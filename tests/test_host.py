@@ -13,7 +13,7 @@ import femeko_jl_b200 as fk
 from conftest import ROOT, load_golden, rel_err_matrix, abs_sum_scale
 from femeko_jl_b200 import lib as L
 from oracle import oracle as orc
-from plan_emulator import export_symbolic, run_plan, sell_spmv
+from plan_emulator import SYM, export_symbolic, run_plan, run_rescale_plan, sell_spmv
 
 
 def test_library_exports_every_declared_symbol():
@@ -60,6 +60,16 @@ def test_symbolic_pattern_map_and_plan_against_reference(name, opts):
     vals, written = run_plan(plan, g["Ak"] * g["mu"][None, :])
     assert np.all(written == 1)
     assert rel_err_matrix(vals, g["csc_values_mu"], abs_sum_scale(m, g["Ak"], g["mu"])) < 1e-14
+    # the rescale plan (one item per entry pair, contributions in ascending element order) on the same local matrices:
+    # every stored entry written exactly once, 10 contributions per element, values == the reference matrix
+    G10 = np.zeros((10, m.nt))
+    for i in range(4):
+        for j in range(i, 4):
+            G10[SYM[i, j]] = g["Ak"][4 * j + i]
+    rvals, rwritten = run_rescale_plan(plan, G10, g["mu"])
+    assert np.all(rwritten == 1) and plan["r_items"] == (plan["nnz"] + m.nv) // 2
+    assert int((plan["r_cref"] != 0xFFFFFFFF).sum()) == 10 * m.nt
+    assert rel_err_matrix(rvals, g["csc_values_mu"], abs_sum_scale(m, g["Ak"], g["mu"])) < 1e-14
     # every element owned by exactly one tile; every (k,i,j) contribution listed exactly once
     assert int((plan["tile_elems"] >> 31).sum()) == m.nt
     assert plan["tile_ents"].size == 16 * m.nt

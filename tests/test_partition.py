@@ -48,6 +48,30 @@ def test_kuhn_slab_equals_partitioned_global_box(world):
     assert tot == g.nt
 
 
+@pytest.mark.parametrize("N,grid", [(6, (2, 1, 1)), (7, (2, 2, 1)), (6, (2, 2, 2)), (5, (1, 1, 1))])
+def test_kuhn_block_equals_partitioned_global_cube(N, grid):
+    """The strong-scaling generator (one global cube, px x py x pz node blocks, every rank's share built directly)
+    == partition_mesh of the materialised cube: node / element order, surface, inside set, halo plan."""
+    g = fk.kuhn_cube(N, inside_edge=0.4)
+    part = P.block_part(N, grid)
+    world = grid[0] * grid[1] * grid[2]
+    assert set(np.unique(part)) == set(range(world))
+    tot = 0
+    for r in range(world):
+        la, pa = P.partition_mesh(g, part, r, world)
+        lb, pb = P.kuhn_block(N, r, grid, inside_edge=0.4)
+        assert np.array_equal(pa.l2g, pb.l2g) and pa.n_owned == pb.n_owned and pa.nt_owned == pb.nt_owned
+        assert np.array_equal(la.t, lb.t) and np.array_equal(la.p, lb.p)
+        assert np.array_equal(la.surfaceT, lb.surfaceT) and np.array_equal(la.InsideElements, lb.InsideElements)
+        assert np.allclose(la.normal, lb.normal) and np.allclose(la.AE, lb.AE) and np.allclose(la.VE, lb.VE)
+        assert list(pa.neigh) == list(pb.neigh) and np.array_equal(pa.send_idx, pb.send_idx) and np.array_equal(pa.send_ptr, pb.send_ptr)
+        assert np.array_equal(pa.recv_start, pb.recv_start) and np.array_equal(pa.recv_count, pb.recv_count)
+        tot += pa.nt_owned
+    assert tot == g.nt
+    if world == 8:   # Kuhn adjacency is directional: the corner block (0,0,0) talks to all seven others
+        assert len(P.kuhn_block(N, 0, grid)[1].neigh) == 7
+
+
 @pytest.mark.parametrize("mesh,nparts", [("delaunay", 4), ("kuhn", 8)])
 def test_halo_plan_is_consistent_across_ranks(mesh, nparts):
     m = fk.delaunay_ball(1200, seed=9) if mesh == "delaunay" else fk.kuhn_cube(6)
