@@ -171,6 +171,13 @@ def kernel_split(tr):
             continue
         out[nm + "_us"] = round(float(np.median(tr[sel, k, 1] - tr[sel, k, 0])) / 1e3, 3)
         out[nm + "_wait_us"] = round(float(np.median(tr[sel, k, 2])) / 1e3, 3)
+    # fused halo exchange (record 3 of the SpMV): when the flags left and when the first / last warp began to wait for the peers'
+    sel = used[:, 0] & (tr[:, 3, 0] >= 0) & (tr[:, 3, 1] > 0)
+    if sel.sum() >= 4:
+        t0 = tr[sel, 0, 0]
+        out["halo_release_at_us"] = round(float(np.median(tr[sel, 3, 0] - t0)) / 1e3, 3)
+        out["halo_first_wait_at_us"] = round(float(np.median((~tr[sel, 3, 2]) - t0)) / 1e3, 3)
+        out["halo_last_wait_at_us"] = round(float(np.median(tr[sel, 3, 1] - t0)) / 1e3, 3)
     ks = [k for k in names if names[k] + "_us" in out]
     its = np.where(np.all(used[:, ks] & (tr[:, ks, 1] > 0), axis=1))[0]
     if len(its) > 4 and len(ks) >= 2:
@@ -611,8 +618,296 @@ def run_ours(args):
         ctx.dist.destroy_process_group()
 
 
+def run_single_process(args):
+    """bench.py --single-process --gpus N (NOT under torchrun): ONE process, fk_multi_* -- the global mesh goes in, the
+    library partitions it and drives N GPUs with one host thread each; every step passes GLOBAL host arrays through the
+    C ABI (what a single Julia process would do), so the figure is end to end by construction."""
+    import femeko_jl_b200 as fk
+
+    ngpu, N, Piters = args.gpus, args.n, args.pcg_iters
+    t0 = time.time()
+    mesh = fk.kuhn_cube(N, inside_edge=0.2)
+    gen_s = time.time() - t0
+    t0 = time.time()
+    hm = fk.FemekoMulti(mesh, ngpu, use_mesh_VE=False)
+    Hk, muk, _ = gd_table()
+    hm.set_spline(0, fk.Spline1D(Hk, muk, bc="nearest"))
+    hm.set_inside(mesh.InsideElements)
+    hm.set_mu(np.full(mesh.nt, MU0))
+    setup_s = time.time() - t0
+    Bext = np.array([0.5, 0.0, 0.0])
+    h0 = fk.Femeko(mesh, use_mesh_VE=False, device=0) if args.sp_check else None
+    if h0 is not None:
+        rhs = -h0.boundary_integral(mesh.surfaceT, mesh.normal, mesh.AE, Bext, 0)
+    else:
+        tmp = fk.Femeko(mesh, use_mesh_VE=False, device=0)
+        rhs = -tmp.boundary_integral(mesh.surfaceT, mesh.normal, mesh.AE, Bext, 0)
+        tmp.close()
+    u = -(Bext / MU0) @ mesh.p
+    opts = dict(max_iter=Piters, tol_disable=True, check_every=Piters + (Piters & 1), recurrence=args.recurrence)
+    W, K = max(3, args.warmup), args.steps
+
+    def step():
+        div = hm.picard_step(u, slot=0)
+        x, it, rr = hm.pcg(rhs, slot=0, **opts)
+        return x, div
+
+    for _ in range(W):
+        step()
+    t0 = time.time()
+    for _ in range(K):
+        x, div = step()
+    ms = (time.time() - t0) / K * 1e3
+    line = {"metric": METRIC, "value": round(mesh.nt / (ms * 1e-3) / 1e6, 3), "unit": UNIT, "n_gpus": ngpu, "steps": K, "warmup": W,
+            "ms_per_step": round(ms, 4), "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic",
+            "config": {"workload": f"single process, fk_multi_*: ONE Kuhn cube N={N} ({mesh.nt} tets) partitioned by the library over {ngpu} "
+                                   f"GPU(s); step = Picard sweep + {Piters} Jacobi-PCG iterations, GLOBAL host arrays in and out every call "
+                                   "(wall clock, host scatter / gather of the vectors included)",
+                       "parts": {k: [int(v) for v in vals] for k, vals in hm.info().items()}},
+            "e2e": {"value": round(mesh.nt / (ms * 1e-3) / 1e6, 3), "unit": UNIT, "h2d_bytes_per_step": 16 * mesh.nv,
+                    "d2h_bytes_per_step": 8 * mesh.nv, "host_buffers": "pageable"},
+            "components": {"mesh_generation_s": round(gen_s, 1), "setup_s_untimed": round(setup_s, 1)}}
+    if h0 is not None:   # same step on one GPU through the same host-pointer API
+        h0.set_spline(0, fk.Spline1D(Hk, muk, bc="nearest"))
+        h0.set_inside(mesh.InsideElements)
+        h0.set_mu(np.full(mesh.nt, MU0))
+        h0.picard_step(u, slot=0)
+        x1, _, _ = h0.pcg(rhs, slot=0, **opts)
+        line["parity"] = {"against": "the same step on one GPU (fk_picard_step + fk_pcg)", "x_rel_l2": float(np.linalg.norm(x - x1) / np.linalg.norm(x1))}
+        h0.close()
+    hm.close()
+    print(json.dumps(line), flush=True)
+
+
 def h_nnz_sell(sell):
     return int(sell[0])
+
+
+# --------------------------------------------------------------------------------------------------
+# configs[2]: Heat/heat3D.jl implicit time stepping (--workload heat)
+# --------------------------------------------------------------------------------------------------
+HEAT_DT = 1e-3      # heat3D.jl:10
+
+
+class CpuHeat:
+    """heat3D.jl:51-86 on the host: conductivity 1 / 2 inside, T0 = 0 / 10 on the inside nodes, A from the compiled
+    reference stiffnessMatrix (FEMc.cpp:102-133; C port when it is absent), M from the C port of massMatrix
+    (src/FEM3D.jl:466-492: Julia only), every step T <- (M + dt A)^-1 (M T) with Eigen's Jacobi-CG (x0 = 0)."""
+
+    def __init__(self, N, tol):
+        from oracle import oracle as orc
+
+        self.orc, self.tol = orc, tol
+        self.kind = "reference" if orc.have_ref() else "port"
+        m = self.m = mesh_module().kuhn_cube(N, inside_edge=0.2)
+        k = np.ones(m.nt)
+        k[m.InsideElements] = 2.0
+        self.rp, self.ci = orc.pattern(m.t, m.nv)
+        if self.kind == "reference":
+            _, _, A = orc.ref_stiffness(m, k)
+        else:
+            _, _, A = orc.stiffness(m, k, order="eigen")
+        _, _, self.M = orc.mass(m)
+        self.LHS = self.M + HEAT_DT * A
+        self.T = np.zeros(m.nv)
+        self.T[m.InsideNodes] = 10.0
+        self.iters = 0
+
+    def step(self):
+        orc = self.orc
+        b = orc.spmv(self.rp, self.ci, self.M, self.T)
+        if self.kind == "reference":
+            self.T, it = orc.ref_cg(self.rp, self.ci, self.LHS, b, self.tol, 0)[:2]
+        else:
+            self.T, it = orc.pcg(self.rp, self.ci, self.LHS, b, self.tol)[:2]
+        self.iters += int(it)
+
+
+def heat_problem(ctx, args, mesh, part):
+    import torch
+
+    import femeko_jl_b200 as fk
+
+    h = fk.Femeko(mesh, use_mesh_VE=False, device=ctx.local, n_owned=part.n_owned if part is not None else 0)
+    for kv in [t for t in args.tune.split(",") if t]:
+        h.tune(int(kv.split("=")[0]), int(kv.split("=")[1]))
+    h.set_stream(ctx.stream.cuda_stream)
+    if part is not None:
+        part.attach(h, ctx.dist)
+    k = np.ones(mesh.nt)
+    k[mesh.InsideElements] = 2.0
+    h.assemble_stiffness(k, slot=0, want_vals=False)
+    h.assemble_mass(slot=1, want_vals=False)
+    h.matrix_axpby(3, 1.0, 1, HEAT_DT, 0)                    # M + dt A on the shared pattern (heat3D.jl:86)
+    T0 = np.zeros(h.nv)
+    T0[mesh.InsideNodes] = 10.0
+    with torch.cuda.stream(ctx.stream):
+        T_dev = torch.from_numpy(T0).to(ctx.dev)
+    ctx.stream.synchronize()
+    return h, T0, T_dev
+
+
+def run_heat(args):
+    import ctypes as C
+
+    import torch
+
+    import femeko_jl_b200 as fk
+    from femeko_jl_b200 import lib as L
+
+    ctx = Ctx(args)
+    rank, world, stream = ctx.rank, ctx.world, ctx.stream
+    N = args.n
+    t0 = time.time()
+    mesh, part = build_problem(N, rank, world)
+    h, T0, T_dev = heat_problem(ctx, args, mesh, part)
+    setup_s = time.time() - t0
+    n_rows, nv, nt, nnz = h.n_rows, h.nv, h.nt, h.nnz
+    nt_owned = part.nt_owned if part is not None else nt
+    W, K = max(3, args.warmup), args.steps
+    its = []
+
+    def step_dev():
+        it, _ = h.heat_step_dev(T_dev.data_ptr(), 1, 3, tol=args.heat_tol, recurrence=args.recurrence)
+        its.append(it)
+
+    T_host = torch.from_numpy(T0.copy()).pin_memory()
+    o = h.pcg_opts(tol=args.heat_tol, recurrence=args.recurrence)
+    it_c, rr_c = C.c_int(), C.c_double()
+
+    def step_e2e():
+        L.check(h.lib.fk_heat_step(h.h, 1, 3, C.cast(T_host.data_ptr(), L.c_double_p), C.byref(o), C.byref(it_c), C.byref(rr_c)))
+
+    def timed(fn):
+        for _ in range(W):
+            fn()
+        ctx.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        l0 = h.launch_count()
+        e0.record(stream)
+        for _ in range(K):
+            fn()
+        e1.record(stream)
+        ctx.barrier()
+        return ctx.max_over_ranks(e0.elapsed_time(e1)), h.launch_count() - l0
+
+    sampler = ClockSampler(ctx.local)
+    if rank == 0:
+        sampler.start()
+    ms_dev, launches = timed(step_dev)
+    its_timed = its[-K:]
+    ms_e2e, _ = timed(step_e2e)
+    clocks = sampler.stop() if rank == 0 else {}
+    world_tets, world_rows, world_nnz = ctx.sum_over_ranks([nt_owned, n_rows, nnz])
+    sell = h.sell_stats()
+    comm_mode = h.comm_mode()
+    h.close()
+    if rank == 0:
+        peak, peak_src = measured_peaks()
+        ms_step = ms_dev / K
+        tot_it = int(sum(its_timed))
+        # per step: the mass product (12 nnz + 16 n) and `it` PCG iterations + the initial residual product
+        step_bytes = (12 * nnz + 16 * n_rows) * 2 * K + pcg_bytes(n_rows, nnz) * tot_it
+        gbs = step_bytes / (ms_dev * 1e-3) / 1e9
+        line = {
+            "metric": METRIC, "value": round(world_tets / (ms_step * 1e-3) / 1e6, 3), "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
+            "ms_per_step": round(ms_step, 4), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic",
+            "config": {"workload": f"configs[2]: Heat/heat3D.jl implicit time stepping, Kuhn cube N={N} per GPU ({nt_owned} tets, {n_rows} rows per "
+                                   f"GPU), conductivity 1 / 2 inside, T0 = 0 / 10, dt = {HEAT_DT}; a step = T <- (M + dt A)^-1 (M T): mass "
+                                   f"SpMV + Jacobi-PCG to {args.heat_tol:g} warm-started from T (matrices assembled once, untimed); value = tets "
+                                   "advanced one time step per second",
+                       "tets_total": world_tets, "rows_total": world_rows, "pcg_iters_per_step": round(tot_it / K, 2),
+                       "l2": "inputs larger than L2 (matrix stream %.0f MB per GPU vs 126 MB L2)" % (12 * nnz / 1e6),
+                       "parallelism": "single GPU" if world == 1 else f"node-partitioned slabs x{world}, comm mode {comm_mode}"},
+            "components": {"pcg_iters_total": tot_it, "pcg_iters_per_step": its_timed, "setup_s_untimed": round(setup_s, 2)},
+            "e2e": {"value": round(world_tets / (ms_e2e / K * 1e-3) / 1e6, 3), "unit": UNIT, "ms_per_step": round(ms_e2e / K, 4),
+                    "h2d_bytes_per_step": 8 * n_rows, "d2h_bytes_per_step": 8 * n_rows + 64, "host_buffers": "pinned"},
+            "gpu_launches": int(launches),
+            "roofline": {"kernel": "heat step = 2 SpMV (mass product, initial residual) + Jacobi-PCG iterations (spmv_sell_kernel<DOT> + "
+                                   "pcg_update_kernel + pcg_direction_kernel)", "bound": "hbm", "achieved": round(gbs, 1), "peak": peak,
+                         "unit": "GB/s", "frac": round(gbs / peak, 4), "traffic": None, "peak_source": peak_src,
+                         "algorithmic_bytes_per_launch": int(step_bytes / K), "avg_launch_ms": round(ms_step, 5),
+                         "note": "bytes per step by SURVEY 8d's figures (12 nnz + 108 n per iteration, 12 nnz + 16 n per product); with so few "
+                                 "iterations per step the polls and the set-up kernels of every solve weigh in"},
+            "clocks": clocks,
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            cs = CpuHeat(args.cpu_n, args.heat_tol)
+            cs.step()
+            t1 = time.time()
+            reps = 0
+            while reps < 3 or (time.time() - t1 < args.cpu_budget and reps < 50):
+                cs.step()
+                reps += 1
+            per = (time.time() - t1) / reps
+            line["cpu_baseline"] = {"value": round(cs.m.nt / per / 1e6, 4), "unit": UNIT, "cores": 1, "host_cores": os.cpu_count(),
+                                    "kind": cs.kind, "sample": f"Kuhn cube N={args.cpu_n} ({cs.m.nt} tets), {reps} time steps: mass product + "
+                                                               f"Eigen Jacobi-CG to {args.heat_tol:g} on M + dt A (x0 = 0), single thread",
+                                    "s_per_step": round(per, 4)}
+            line["parity"] = heat_parity(args, ctx.local)
+        print(json.dumps(line), flush=True)
+    if ctx.dist is not None:
+        ctx.dist.barrier()
+        ctx.dist.destroy_process_group()
+
+
+def heat_parity(args, device):
+    """Outside the timed region: five time steps at Kuhn N = --heat-parity-n on the GPU against (a) a sparse direct solve of
+    the oracle-assembled M + dt A (what heat3D.jl's `\\` does) and (b) the CPU arm."""
+    import scipy.sparse as sp
+    import scipy.sparse.linalg as spla
+
+    import femeko_jl_b200 as fk
+
+    cs = CpuHeat(args.heat_parity_n, 1e-12)
+    m = cs.m
+    h = fk.Femeko(m, device=device)
+    k = np.ones(m.nt)
+    k[m.InsideElements] = 2.0
+    h.assemble_stiffness(k, slot=0, want_vals=False)
+    h.assemble_mass(slot=1, want_vals=False)
+    h.matrix_axpby(3, 1.0, 1, HEAT_DT, 0)
+    T = cs.T.copy()
+    Td = cs.T.copy()
+    Mm = sp.csr_matrix((cs.M, cs.ci, cs.rp), shape=(m.nv, m.nv))
+    lu = spla.splu(sp.csr_matrix((cs.LHS, cs.ci, cs.rp), shape=(m.nv, m.nv)).tocsc())
+    for _ in range(5):
+        T, _, _ = h.heat_step(T, 1, 3, tol=1e-12, recurrence=args.recurrence)
+        Td = lu.solve(Mm @ Td)
+        cs.step()
+    h.close()
+
+    def rl2(a, b):
+        return float(np.linalg.norm(a - b) / max(np.linalg.norm(b), 1e-300))
+
+    out = {"against": f"Kuhn N={args.heat_parity_n}, 5 steps: sparse direct solve of the oracle / reference matrices; CPU arm ({cs.kind})",
+           "T_rel_l2_vs_direct": rl2(T, Td), "T_rel_l2_vs_cpu_arm": rl2(T, cs.T),
+           "heat_conserved_rel": float(abs((Mm @ T).sum() - (Mm @ Td).sum()) / abs((Mm @ Td).sum()))}
+    out["ok"] = bool(out["T_rel_l2_vs_direct"] < 1e-8 and out["T_rel_l2_vs_cpu_arm"] < 1e-8)
+    return out
+
+
+def run_reference_heat(args):
+    if env_int("RANK", 0) != 0:
+        return
+    W, K = max(1, args.warmup), args.steps
+    cs = CpuHeat(args.cpu_n, args.heat_tol)
+    for _ in range(min(W, 2)):
+        cs.step()
+    t0 = time.time()
+    for _ in range(K):
+        cs.step()
+    per = (time.time() - t0) / K
+    value = round(cs.m.nt / per / 1e6, 4)
+    sample = (f"each step = one implicit time step on a Kuhn cube N={args.cpu_n} ({cs.m.nt} tets): mass product + Eigen Jacobi-CG to "
+              f"{args.heat_tol:g} on M + dt A (x0 = 0); single-threaded reference")
+    print(json.dumps({"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": K, "warmup": W,
+                      "ms_per_step": round(per * 1e3, 3), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+                      "data": "synthetic", "config": {"workload": f"configs[2] bounded sample: heat3D.jl time stepping, Kuhn cube N={args.cpu_n}"},
+                      "cpu_baseline": {"value": value, "unit": UNIT, "cores": 1, "host_cores": os.cpu_count(), "kind": cs.kind, "sample": sample},
+                      "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}), flush=True)
 
 
 # --------------------------------------------------------------------------------------------------
@@ -820,8 +1115,19 @@ def main():
     ap.add_argument("--tune", default="", help="experiments: comma-separated what=value pairs for fk_tune (e.g. 6=0)")
     ap.add_argument("--presolve", type=int, default=1, help="0: skip the untimed linear presolve (profiling runs)")
     ap.add_argument("--full-solve", type=int, default=1, help="also record one complete nonlinear solve (untimed)")
+    ap.add_argument("--workload", default="picard", choices=["picard", "heat"],
+                    help="picard = configs[1] (the headline); heat = configs[2], Heat/heat3D.jl time stepping (use --n 150)")
+    ap.add_argument("--heat-tol", type=float, default=1e-10)
+    ap.add_argument("--heat-parity-n", type=int, default=24)
+    ap.add_argument("--single-process", action="store_true",
+                    help="drive --gpus N GPUs from THIS process through fk_multi_* (do not launch under torchrun); --n = global cube")
+    ap.add_argument("--sp-check", type=int, default=1, help="--single-process: also run the step on one GPU and compare")
     args = ap.parse_args()
-    if args.impl == "reference":
+    if args.single_process:
+        return run_single_process(args)
+    if args.workload == "heat":
+        run_reference_heat(args) if args.impl == "reference" else run_heat(args)
+    elif args.impl == "reference":
         run_reference(args)
     else:
         run_ours(args)

@@ -168,7 +168,7 @@ static void configure_geo(fk_handle h) {
 static void ensure_geo(fk_handle h) {
   if (h->geo_ready) return;
   RescalePlan R;
-  build_rescale_plan(h->sym, 4096, R);
+  build_rescale_plan(h->sym, h->geo_window, R);
   cudaStream_t s = h->stream;
   h->geo_nslices = R.nslices;
   h->geo_slots = R.n_slots;
@@ -209,7 +209,7 @@ static void ensure_state(fk_handle h) {
   h->Hn.ensure((size_t)h->nt);
   h->Hfield.ensure((size_t)3 * h->nt);
   h->matid.ensure((size_t)h->nt);
-  h->tile_max.ensure((size_t)std::max(1, 4 * h->num_sms));   // per-CTA maxima of material_update_kernel
+  h->tile_max.ensure((size_t)std::max(1, 8 * h->num_sms));   // per-CTA maxima of material_update_kernel
   h->errflag.ensure(1);
   h->scal.ensure(16);
   const int g = std::min(cdiv(h->nt, 256), 65535);
@@ -939,6 +939,11 @@ int fk_tune(fk_handle h, int what, int value) {
       case 10:  // rescale assembly: 0 = never (tile kernel only), 1 = from the second Picard sweep on (default), 2 = at once
         need(value >= 0 && value <= 2, "fk_tune: geo mode out of range");
         h->geo_mode = value;
+        break;
+      case 13:  // rescale plan: items are sorted by list length inside windows of this many items (32 = plan order kept); rebuilds
+        need(value >= 32 && value <= (1 << 20), "fk_tune: geo window out of range");
+        h->geo_window = value;
+        h->geo_ready = false;
         break;
       case 12:  // launch shape of geo_rescale_kernel {batch, min CTAs per SM}: 0 {8,4} (default) 1 {4,6} 2 {8,3} 3 {6,5}
         need(value >= 0 && value < kNumGeoVariants, "fk_tune: geo variant out of range");
@@ -1764,9 +1769,10 @@ static int picard_step_dev(fk_handle h, int slot, const double* u_dev, int compa
   a.compat = compat_bug;
   int* errflag = reinterpret_cast<int*>(h->scal.ptr + 7);   // rides in the scalar block: one copy brings back both
   FK_CUDA(cudaMemsetAsync(errflag, 0, sizeof(double), h->stream));
+  const bool have_mat = h->have_material && h->n_mat > 0;
   // 1. material elements: mu(|H|), dmu/dH from the spline and the convergence metric (per-CTA maxima)
   int npart = 1;
-  if (h->have_material && h->n_mat > 0) {
+  if (have_mat) {
     // every material id in use needs its table (a missing one would dereference NULL on the device)
     for (int m = 0; m < FK_MAX_SPLINES / 2; m++)
       need(!(h->mat_used & (1u << m)) || h->spl.s[m].n > 0, "fk_picard_step: a material id in use has no spline (fk_set_spline)");
@@ -1785,8 +1791,8 @@ static int picard_step_dev(fk_handle h, int slot, const double* u_dev, int compa
   h->geo_sweeps++;
   if (h->geo_mode == 2 || (h->geo_mode == 1 && (h->geo_ready || h->geo_sweeps >= 2))) {
     ensure_geo(h);
-    picard_element_kernel<<<cdiv(h->nt, 256), 256, 0, h->stream>>>(h->p4.ptr, h->t4.ptr, a.u, h->mu.ptr, a.VE, h->nt, compat_bug,
-                                                                   h->Hn.ptr, h->Hfield.ptr, h->geo_s0.ptr);
+    picard_element_kernel<<<cdiv(h->nt, kElemThreads), kElemThreads, 0, h->stream>>>(h->p4.ptr, h->t4.ptr, a.u, h->mu.ptr, a.VE, h->nt,
+                                                                                   compat_bug, h->Hn.ptr, h->Hfield.ptr, h->geo_s0.ptr);
     FK_CUDA(cudaGetLastError());
     h->launches++;
     launch_geo_rescale(h, a.vals);
@@ -1932,6 +1938,48 @@ int fk_picard_pcg(fk_handle h, int slot, const double* u, int compat_bug, const 
     FK_CUDA(cudaMemcpyAsync(h->scal.ptr + 7, h->scal.ptr + 13, sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
     FK_CUDA(cudaMemcpyAsync(x, h->st_d.ptr, sizeof(double) * n, cudaMemcpyDeviceToHost, h->stream));
     return picard_collect(h, div_out);
+  });
+}
+
+// ---- implicit heat step (Heat/heat3D.jl:83-86) --------------------------------------------------------
+// T <- (M + dt A)^-1 (M T): mass product (with the halo rows of T refreshed on a partition), then Jacobi-PCG on the
+// slot that holds M + dt A (fk_matrix_axpby), warm-started from T.  One call per time step, no host round trip but the
+// solve's own convergence polls.
+static void heat_step_dev(fk_handle h, int slot_mass, int slot_lhs, double* T_dev, const fk_pcg_opts* opts, int* iters_out,
+                          double* relres_out) {
+  check_slot(slot_mass);
+  check_slot(slot_lhs);
+  need(h->vals[slot_mass].ptr && h->vals[slot_lhs].ptr, "fk_heat_step: matrix slot has not been assembled");
+  ensure_pcg(h);
+  cudaStream_t s = h->stream;
+  if (T_dev != h->u.ptr) FK_CUDA(cudaMemcpyAsync(h->u.ptr, T_dev, sizeof(double) * (size_t)h->n_rows, cudaMemcpyDeviceToDevice, s));
+  if (h->comm) comm_halo_exchange(h, s, h->u.ptr);
+  launch_spmv(h, s, h->vals[slot_mass].ptr, h->u.ptr, h->bvec.ptr, false, nullptr, 0);
+  h->launches++;
+  fk_pcg_opts o{};
+  if (opts) o = *opts;
+  o.warm_start = 1;
+  pcg_dev(h, slot_lhs, h->bvec.ptr, T_dev, &o, iters_out, relres_out);
+}
+int fk_heat_step_dev(fk_handle h, int slot_mass, int slot_lhs, double* T_dev, const fk_pcg_opts* opts, int* iters_out,
+                     double* relres_out) {
+  return guard([&]() {
+    need(h && T_dev, "fk: NULL argument");
+    DeviceGuard dg(h->device);
+    heat_step_dev(h, slot_mass, slot_lhs, T_dev, opts, iters_out, relres_out);
+    return 0;
+  });
+}
+int fk_heat_step(fk_handle h, int slot_mass, int slot_lhs, double* T, const fk_pcg_opts* opts, int* iters_out, double* relres_out) {
+  return guard([&]() {
+    need(h && T, "fk: NULL argument");
+    DeviceGuard dg(h->device);
+    ensure_pcg(h);
+    h->st_d.ensure((size_t)h->nv);
+    FK_CUDA(cudaMemcpyAsync(h->st_d.ptr, T, sizeof(double) * (size_t)h->n_rows, cudaMemcpyHostToDevice, h->stream));
+    heat_step_dev(h, slot_mass, slot_lhs, h->st_d.ptr, opts, iters_out, relres_out);
+    copy_out(h, h->st_d.ptr, T, (size_t)h->n_rows);
+    return 0;
   });
 }
 

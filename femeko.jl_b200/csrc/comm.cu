@@ -283,6 +283,55 @@ HaloFused comm_halo_fused(fk_handle_s* h, double* v, unsigned int* ticket) {
   return a;
 }
 
+// ---- one process, several GPUs (multi.cu): the same peer-memory path without NCCL and without CUDA IPC ----------
+void comm_init_local(fk_handle_s* h, int rank, int nranks, long long n_global) {
+  FK_CUDA(cudaSetDevice(h->device));
+  comm_destroy(h);
+  h->comm = new Comm();
+  h->comm->rank = rank;
+  h->comm->nranks = nranks;
+  h->comm->n_global = n_global;
+  h->scal.ensure(16);
+}
+// all[r] = handle of rank r (same process); remote_start / remote_slot as in fk_comm_p2p_attach
+void comm_attach_local(fk_handle_s* h, fk_handle_s* const* all, const int* remote_start, const int* remote_slot) {
+  Comm* c = h->comm;
+  if (!c || !c->have_halo) throw std::runtime_error("fk: comm_attach_local before the halo plan");
+  if (c->nranks > kMaxRanks || c->nneigh > kMaxNeigh) throw std::runtime_error("fk: too many ranks / neighbours");
+  P2P& P = c->p2p;
+  for (int r = 0; r < c->nranks; r++) {   // every slab exists before any pointer to it is taken
+    FK_CUDA(cudaSetDevice(all[r]->device));
+    ensure_pcg(all[r]);
+    FK_CUDA(cudaStreamSynchronize(all[r]->stream));
+  }
+  FK_CUDA(cudaSetDevice(h->device));
+  P.ctrl = reinterpret_cast<unsigned long long*>(h->pcg_slab.ptr + (size_t)kSlabVecs * h->slab_stride);
+  FK_CUDA(cudaMemset(P.ctrl, 0, kCtrlWords * sizeof(unsigned long long)));
+  for (int r = 0; r < c->nranks; r++) {
+    if (r != c->rank && all[r]->device != h->device) {
+      int can = 0;
+      FK_CUDA(cudaDeviceCanAccessPeer(&can, h->device, all[r]->device));
+      if (!can) throw std::runtime_error("fk: the GPUs of one fk_multi handle need peer access to each other (NVLink / PCIe P2P)");
+      cudaError_t e = cudaDeviceEnablePeerAccess(all[r]->device, 0);
+      if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) FK_CUDA(e);
+      cudaGetLastError();
+    }
+    P.peer_slab[r] = all[r]->pcg_slab.ptr;
+    P.peer_stride[r] = all[r]->slab_stride;
+    P.opened_slab[r] = false;
+    P.peer_ctrl[r] = reinterpret_cast<unsigned long long*>(static_cast<double*>(P.peer_slab[r]) + (size_t)kSlabVecs * P.peer_stride[r]);
+  }
+  for (int q = 0; q < c->nneigh; q++) {
+    P.remote_start[q] = remote_start[q];
+    P.remote_slot[q] = remote_slot[q];
+  }
+  std::vector<unsigned long long*> ptrs(P.peer_ctrl, P.peer_ctrl + kMaxRanks);
+  P.peer_ctrl_dev.upload(ptrs, h->stream);
+  FK_CUDA(cudaStreamSynchronize(h->stream));
+  P.on = true;
+  invalidate_graphs(h);
+}
+
 }  // namespace fk
 
 using namespace fk;

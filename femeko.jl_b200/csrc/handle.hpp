@@ -145,7 +145,7 @@ struct fk_handle_s {
   fk::Comm* comm = nullptr;
   // rescale assembly (rescale.cuh): geometric factors of every contribution, built on demand
   //   geo_mode 0: never; 1 (default): from the second Picard sweep of a handle on; 2: from the first sweep / assembly on
-  int geo_mode = 1, geo_sweeps = 0, geo_nslices = 0, geo_grid = 0, geo_variant = 0;
+  int geo_mode = 1, geo_sweeps = 0, geo_nslices = 0, geo_grid = 0, geo_variant = 0, geo_window = 4096;
   bool geo_ready = false;
   long long geo_slots = 0, geo_items = 0, geo_contrib = 0;
   fk::DevBuf<double> geo_g, geo_s0;

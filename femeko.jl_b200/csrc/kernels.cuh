@@ -143,8 +143,9 @@ __device__ __forceinline__ unsigned long long ld_relaxed_sys(const unsigned long
   return v;
 }
 __device__ __forceinline__ void fence_acq_rel_sys() { asm volatile("fence.acq_rel.sys;" ::: "memory"); }
-// same contract as spin_until, polling with relaxed loads and ONE acquire fence after success (the polls of ~600
-// CTAs then cost an L2 read each instead of an acquire)
+// same contract as spin_until, polling with relaxed loads and ONE acquire load after success (the polls of ~600 CTAs
+// then cost an L2 read each instead of an acquire).  Not a fence: under the load of a running SpMV a system-scope
+// fence (MEMBAR.SYS drains the SM's outstanding writes) was measured at ~8 us per waiting warp (fk_tune 11 timeline).
 __device__ __forceinline__ bool spin_until_relaxed(const unsigned long long* flag, unsigned long long seq, unsigned long long* err) {
   const long long t0 = clock64();
   bool ok = true;
@@ -155,7 +156,7 @@ __device__ __forceinline__ bool spin_until_relaxed(const unsigned long long* fla
       break;
     }
   }
-  fence_acq_rel_sys();
+  (void)ld_acquire_sys(flag);
   return ok;
 }
 // spin until *flag >= seq; gives up after ~2 s (a lost peer must not hang the GPU) and records the failure
@@ -359,10 +360,11 @@ struct TetGeom {
   double vol;      // |det E| / 6  (elementVolume, src/mesh.jl:484-505)
 };
 
+// one node = one aligned 32-byte sector = ONE 256-bit load (LDG.E.256 on sm_100a): the gather kernels are bound by the
+// L1 tag stage (one line per cycle), so half the load instructions is half the tag traffic of the coordinate gathers
 __device__ __forceinline__ void load_node(const double4* __restrict__ p4, int n, double& x, double& y, double& z) {
-  const double2* q = reinterpret_cast<const double2*>(p4 + n);
-  double2 a = __ldg(q), b = __ldg(q + 1);
-  x = a.x; y = a.y; z = b.x;
+  [[maybe_unused]] double w;
+  asm("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(x), "=d"(y), "=d"(z), "=d"(w) : "l"(p4 + n));
 }
 
 __device__ __forceinline__ void tet_geometry_xyz(const double x0, const double y0, const double z0, const double x1, const double y1,

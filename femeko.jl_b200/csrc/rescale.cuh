@@ -53,34 +53,49 @@ static __global__ void __launch_bounds__(256) geo_scale_kernel(const double* __r
 
 // Picard sweep, element part: field recovery of EVERY element (NewtonRaphson.jl:178-197) and its scale s_k = VE[k] mu[k];
 // mu of the material elements was refreshed by material_update_kernel just before.  VE == nullptr: |det| / 6.
-static __global__ void __launch_bounds__(256) picard_element_kernel(const double4* __restrict__ p4, const int4* __restrict__ t4,
-                                                                    const double* __restrict__ u, const double* __restrict__ mu,
-                                                                    const double* __restrict__ VE, int nt, int compat,
-                                                                    double* __restrict__ Hn, double* __restrict__ Hfield,
-                                                                    double* __restrict__ s0) {
+// The kernel is bound by the L1 tag stage (one 128-byte line per cycle and SM), not by HBM: a node is therefore fetched
+// with ONE 256-bit load (load_node: LDG.E.256) instead of two 128-bit ones, and the three components
+// of H leave through a per-warp shared-memory transpose so that a warp writes 768 contiguous bytes with three stores.
+constexpr int kElemThreads = 256;
+static __global__ void __launch_bounds__(kElemThreads) picard_element_kernel(const double4* __restrict__ p4, const int4* __restrict__ t4,
+                                                                             const double* __restrict__ u, const double* __restrict__ mu,
+                                                                             const double* __restrict__ VE, int nt, int compat,
+                                                                             double* __restrict__ Hn, double* __restrict__ Hfield,
+                                                                             double* __restrict__ s0) {
+  __shared__ double hs[kElemThreads / 32][96];
   const int k = blockIdx.x * blockDim.x + threadIdx.x;
-  if (k >= nt) return;
-  const int4 nd = __ldg(t4 + k);
-  const double f = __ldcs(mu + k);
-  const double u0 = __ldg(u + nd.x), u1 = __ldg(u + nd.y), u2 = __ldg(u + nd.z), u3 = __ldg(u + nd.w);
-  TetGeom G;
-  tet_geometry(p4, nd, G);
-  double hx = -(u0 * G.g[0][0]) - u1 * G.g[1][0] - u2 * G.g[2][0] - u3 * G.g[3][0];
-  double hy = -(u0 * G.g[0][1]) - u1 * G.g[1][1] - u2 * G.g[2][1] - u3 * G.g[3][1];
-  double hz = -(u0 * G.g[0][2]) - u1 * G.g[1][2] - u2 * G.g[2][2] - u3 * G.g[3][2];
-  if (compat) { hy += hz; hz = 0.0; }  // NewtonRaphson.jl:187-189: d-term lands in row 2
-  __stcs(Hn + k, norm3(hx, hy, hz));
-  if (Hfield) {
-    __stcs(Hfield + 3 * (size_t)k, hx);
-    __stcs(Hfield + 3 * (size_t)k + 1, hy);
-    __stcs(Hfield + 3 * (size_t)k + 2, hz);
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  double hx = 0.0, hy = 0.0, hz = 0.0;
+  if (k < nt) {
+    const int4 nd = __ldg(t4 + k);
+    const double f = __ldcs(mu + k);
+    const double u0 = __ldg(u + nd.x), u1 = __ldg(u + nd.y), u2 = __ldg(u + nd.z), u3 = __ldg(u + nd.w);
+    TetGeom G;
+    tet_geometry(p4, nd, G);
+    hx = -(u0 * G.g[0][0]) - u1 * G.g[1][0] - u2 * G.g[2][0] - u3 * G.g[3][0];
+    hy = -(u0 * G.g[0][1]) - u1 * G.g[1][1] - u2 * G.g[2][1] - u3 * G.g[3][1];
+    hz = -(u0 * G.g[0][2]) - u1 * G.g[1][2] - u2 * G.g[2][2] - u3 * G.g[3][2];
+    if (compat) { hy += hz; hz = 0.0; }  // NewtonRaphson.jl:187-189: d-term lands in row 2
+    __stcs(Hn + k, norm3(hx, hy, hz));
+    const double V = VE ? __ldcs(VE + k) : G.vol;
+    s0[k] = __dmul_rn(V, f);
   }
-  const double V = VE ? __ldcs(VE + k) : G.vol;
-  s0[k] = __dmul_rn(V, f);
+  if (Hfield) {
+    double* w = hs[wib];
+    w[3 * lane] = hx; w[3 * lane + 1] = hy; w[3 * lane + 2] = hz;
+    __syncwarp();
+    const int kw = k - lane;                       // first element of this warp
+    const int n3 = 3 * max(0, min(32, nt - kw));
+#pragma unroll
+    for (int q = 0; q < 3; q++)
+      if (32 * q + lane < n3) __stcs(Hfield + 3 * (size_t)kw + 32 * q + lane, w[32 * q + lane]);
+  }
 }
 
 // One warp per slice of 32 items; a lane works through its item's contributions in batches of B: the B element ids and
 // factors (coalesced, streaming) and then B independent gathers of s are in flight before the ordered fold starts.
+// (A software pipeline over the slices of a warp -- next slice's first batch requested during the gathers of this
+// one -- measured no faster at 85 registers and 2.3x slower where it spilled: profiles/r02g_*.)
 constexpr int kGeoThreads = 256;
 template <int B, int MINB>
 static __global__ void __launch_bounds__(kGeoThreads, MINB) geo_rescale_kernel(const uint32_t* __restrict__ slice_ptr,

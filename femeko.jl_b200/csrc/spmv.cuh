@@ -181,7 +181,10 @@ static __global__ void __launch_bounds__(kSpmvThreads, MINB) spmv_sell_fused_ker
         __threadfence_system();
         st_release_sys(hf.flag[threadIdx.x], seq);
       }
-      if (threadIdx.x == 0) *hf.ticket = 0u;
+      if (threadIdx.x == 0) {
+        *hf.ticket = 0u;
+        if (tr) atomicMin(trace_rec(ctl, j, 3), gtime_ns());   // timeline record 3: {flags released, latest / ~earliest wait begin}
+      }
     }
   }
   double dot = 0.0;
@@ -202,6 +205,10 @@ static __global__ void __launch_bounds__(kSpmvThreads, MINB) spmv_sell_fused_ker
     } else {
       if (!waited) {   // once per warp: the neighbours' rows of this exchange have landed
         const unsigned long long tw0 = (tr && wib == 0) ? gtime_ns() : 0ULL;
+        if (tr && threadIdx.x == 0) {
+          atomicMax(trace_rec(ctl, j, 3) + 1, tw0);
+          atomicMax(trace_rec(ctl, j, 3) + 2, ~tw0);
+        }
         if (lane < hf.nneigh) spin_until_relaxed(hf.my_ctrl + kOffHalo2 + lane, seq, hf.my_ctrl + kOffErr);
         __syncwarp();
         waited = true;

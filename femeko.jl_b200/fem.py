@@ -240,6 +240,20 @@ class Femeko:
         wv = None if w is None else np.ascontiguousarray(w, dtype=np.float64)
         L.check(self.lib.fk_set_nullspace(self.h, L.dptr(wv)))
 
+    def heat_step(self, T, slot_mass=1, slot_lhs=3, **kw):
+        """T <- (M + dt A)^-1 (M T) (heat3D.jl:86): returns (T, iterations, relative residual)."""
+        Tn = np.array(T, dtype=np.float64, copy=True)
+        o = self.pcg_opts(**kw)
+        it, rr = C.c_int(), C.c_double()
+        L.check(self.lib.fk_heat_step(self.h, slot_mass, slot_lhs, L.dptr(Tn), C.byref(o), C.byref(it), C.byref(rr)))
+        return Tn, it.value, rr.value
+
+    def heat_step_dev(self, T_ptr: int, slot_mass=1, slot_lhs=3, **kw):
+        o = self.pcg_opts(**kw)
+        it, rr = C.c_int(), C.c_double()
+        L.check(self.lib.fk_heat_step_dev(self.h, slot_mass, slot_lhs, C.c_void_p(T_ptr), C.byref(o), C.byref(it), C.byref(rr)))
+        return it.value, rr.value
+
     def pcg(self, b, slot=0, x0=None, **kw):
         """Jacobi-PCG with Eigen's recurrence; returns (x, iterations, relative residual)."""
         b = np.ascontiguousarray(b, dtype=np.float64)
@@ -405,6 +419,112 @@ class Femeko:
     def picard_result(self):
         div = C.c_double()
         L.check(self.lib.fk_picard_result(self.h, C.byref(div)))
+        return div.value
+
+
+class FemekoMulti:
+    """ONE process driving `ngpu` GPUs (fk_multi_*): the global mesh goes in, the library partitions it (RCB of the nodes,
+    owned / halo rows, ghost elements), builds one handle per GPU wired over peer memory, and every call takes and
+    returns global arrays in the mesh's own numbering -- what a single Julia process would @ccall."""
+
+    def __init__(self, mesh: MESH, ngpu: int, use_mesh_VE: bool = True, devices=None, **opts):
+        self.lib = L.load()
+        self.mesh = mesh
+        o = L.fk_create_opts()
+        for k, v in opts.items():
+            setattr(o, k, int(v))
+        p = np.asfortranarray(L.f64(mesh.p))
+        t = np.asfortranarray(L.i32(mesh.t))
+        VE = L.f64(mesh.VE) if (use_mesh_VE and mesh.VE is not None) else None
+        dv = None if devices is None else np.ascontiguousarray(devices, dtype=np.int32)
+        h = C.c_void_p()
+        L.check(self.lib.fk_multi_create(L.dptr(p), L.iptr(t), int(p.shape[1]), int(t.shape[1]), L.dptr(VE), int(ngpu), L.iptr(dv),
+                                         C.byref(o), C.byref(h)))
+        self.h, self.ngpu, self.nv, self.nt = h, int(ngpu), int(p.shape[1]), int(t.shape[1])
+
+    def close(self):
+        if getattr(self, "h", None) is not None and self.h.value:
+            self.lib.fk_multi_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def info(self):
+        """per GPU: owned rows, local nodes (owned + halo), local elements (with ghosts), neighbours"""
+        n = C.c_int()
+        a = [np.zeros(self.ngpu, dtype=np.int32) for _ in range(4)]
+        L.check(self.lib.fk_multi_info(self.h, C.byref(n), *[L.iptr(x) for x in a]))
+        return dict(n_owned=a[0], nv_local=a[1], nt_local=a[2], nneigh=a[3])
+
+    def partition(self, rank):
+        inf = self.info()
+        l2g = np.zeros(int(inf["nv_local"][rank]), dtype=np.int32)
+        e2g = np.zeros(int(inf["nt_local"][rank]), dtype=np.int32)
+        L.check(self.lib.fk_multi_partition(self.h, int(rank), L.iptr(l2g), L.iptr(e2g)))
+        return l2g, e2g
+
+    def _elem(self, f):
+        if f is None:
+            return None
+        f = np.ascontiguousarray(f, dtype=np.float64)
+        assert f.shape == (self.nt,)
+        return f
+
+    def assemble_stiffness(self, f=None, slot=0):
+        L.check(self.lib.fk_multi_assemble_stiffness(self.h, slot, L.dptr(self._elem(f))))
+
+    def assemble_mass(self, rho=None, slot=1):
+        L.check(self.lib.fk_multi_assemble_mass(self.h, slot, L.dptr(self._elem(rho))))
+
+    def matrix_axpby(self, dst, alpha, x, beta=0.0, y=0):
+        L.check(self.lib.fk_multi_matrix_axpby(self.h, dst, float(alpha), x, float(beta), y))
+
+    def set_spline(self, idx, spl):
+        L.check(self.lib.fk_multi_set_spline(self.h, int(idx), L.dptr(spl.t), L.dptr(spl.c), len(spl.t), spl.k, L.BC[spl.bc]))
+
+    def set_inside(self, ids):
+        ids = np.ascontiguousarray(ids, dtype=np.int32)
+        L.check(self.lib.fk_multi_set_inside(self.h, L.iptr(ids), int(ids.size)))
+
+    def set_mu(self, mu):
+        L.check(self.lib.fk_multi_set_mu(self.h, L.dptr(self._elem(mu))))
+
+    def get_mu(self):
+        mu = np.zeros(self.nt)
+        L.check(self.lib.fk_multi_get_mu(self.h, L.dptr(mu)))
+        return mu
+
+    def get_field(self):
+        Hf = np.zeros((3, self.nt), order="F")
+        Hn = np.zeros(self.nt)
+        L.check(self.lib.fk_multi_get_field(self.h, L.dptr(Hf), L.dptr(Hn)))
+        return Hf, Hn
+
+    def reset_field(self):
+        L.check(self.lib.fk_multi_reset_field(self.h))
+
+    def spmv(self, x, slot=0):
+        x = np.ascontiguousarray(x, dtype=np.float64)
+        y = np.zeros(self.nv)
+        L.check(self.lib.fk_multi_spmv(self.h, slot, L.dptr(x), L.dptr(y)))
+        return y
+
+    def pcg(self, b, slot=0, x0=None, **kw):
+        b = np.ascontiguousarray(b, dtype=np.float64)
+        x = np.zeros(self.nv) if x0 is None else np.array(x0, dtype=np.float64, copy=True)
+        o = Femeko.pcg_opts(warm_start=x0 is not None, **kw)
+        it, rr = C.c_int(), C.c_double()
+        L.check(self.lib.fk_multi_pcg(self.h, slot, L.dptr(b), L.dptr(x), C.byref(o), C.byref(it), C.byref(rr)))
+        return x, it.value, rr.value
+
+    def picard_step(self, u, slot=0, compat_bug=False):
+        u = np.ascontiguousarray(u, dtype=np.float64)
+        div = C.c_double()
+        L.check(self.lib.fk_multi_picard_step(self.h, slot, L.dptr(u), int(compat_bug), C.byref(div)))
         return div.value
 
 

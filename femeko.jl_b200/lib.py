@@ -76,6 +76,27 @@ _SIGS = {
                                     C.POINTER(C.c_longlong), c_int_p, C.POINTER(C.c_longlong)]),
     "fk_symbolic_export": (C.c_int, [_H] + [C.c_void_p] * 15),
     "fk_symbolic_colz": (C.c_int, [_H, C.POINTER(C.c_longlong), C.POINTER(C.c_longlong), C.c_void_p, C.c_void_p]),
+    "fk_heat_step": (C.c_int, [_H, C.c_int, C.c_int, c_double_p, C.POINTER(fk_pcg_opts), c_int_p, c_double_p]),
+    "fk_heat_step_dev": (C.c_int, [_H, C.c_int, C.c_int, C.c_void_p, C.POINTER(fk_pcg_opts), c_int_p, c_double_p]),
+    "fk_multi_create": (C.c_int, [c_double_p, c_int_p, C.c_int, C.c_int, c_double_p, C.c_int, c_int_p, C.POINTER(fk_create_opts), C.POINTER(_H)]),
+    "fk_multi_destroy": (C.c_int, [_H]),
+    "fk_multi_info": (C.c_int, [_H, c_int_p, c_int_p, c_int_p, c_int_p, c_int_p]),
+    "fk_multi_handle": (C.c_int, [_H, C.c_int, C.POINTER(_H)]),
+    "fk_multi_partition": (C.c_int, [_H, C.c_int, c_int_p, c_int_p]),
+    "fk_rcb": (C.c_int, [c_double_p, C.c_int, C.c_int, c_int_p]),
+    "fk_partition_local": (C.c_int, [c_double_p, c_int_p, C.c_int, C.c_int, c_int_p, C.c_int] + [c_int_p] * 9),
+    "fk_multi_assemble_stiffness": (C.c_int, [_H, C.c_int, c_double_p]),
+    "fk_multi_assemble_mass": (C.c_int, [_H, C.c_int, c_double_p]),
+    "fk_multi_matrix_axpby": (C.c_int, [_H, C.c_int, C.c_double, C.c_int, C.c_double, C.c_int]),
+    "fk_multi_set_spline": (C.c_int, [_H, C.c_int, c_double_p, c_double_p, C.c_int, C.c_int, C.c_int]),
+    "fk_multi_set_inside": (C.c_int, [_H, c_int_p, C.c_int]),
+    "fk_multi_set_mu": (C.c_int, [_H, c_double_p]),
+    "fk_multi_get_mu": (C.c_int, [_H, c_double_p]),
+    "fk_multi_get_field": (C.c_int, [_H, c_double_p, c_double_p]),
+    "fk_multi_reset_field": (C.c_int, [_H]),
+    "fk_multi_spmv": (C.c_int, [_H, C.c_int, c_double_p, c_double_p]),
+    "fk_multi_pcg": (C.c_int, [_H, C.c_int, c_double_p, c_double_p, C.POINTER(fk_pcg_opts), c_int_p, c_double_p]),
+    "fk_multi_picard_step": (C.c_int, [_H, C.c_int, c_double_p, C.c_int, c_double_p]),
     "fk_set_host_threads": (C.c_int, [C.c_int]),
     "fk_symbolic_rescale": (C.c_int, [_H, C.POINTER(C.c_longlong), c_int_p, C.POINTER(C.c_longlong), C.c_void_p, C.c_void_p, C.c_void_p,
                                       C.c_void_p]),

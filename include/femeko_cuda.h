@@ -266,6 +266,13 @@ int fk_picard_result(fk_handle h, double* div_out);
 int fk_picard_pcg(fk_handle h, int slot, const double* u, int compat_bug, const double* b, double* x,
                   const fk_pcg_opts* opts, double* div_out, int* iters_out, double* relres_out);
 
+/* One implicit time step of the heat equation, heat3D.jl:83-86: T <- (M + dt A)^-1 (M T).  slot_mass holds M
+ * (fk_assemble_mass), slot_lhs holds M + dt A (fk_matrix_axpby); Jacobi-PCG warm-started from T (the reference
+ * re-factorises M + dt A with a sparse Cholesky every step).  T: n_rows values in/out (host / device).          */
+int fk_heat_step(fk_handle h, int slot_mass, int slot_lhs, double* T, const fk_pcg_opts* opts, int* iters_out, double* relres_out);
+int fk_heat_step_dev(fk_handle h, int slot_mass, int slot_lhs, double* T_dev, const fk_pcg_opts* opts, int* iters_out,
+                     double* relres_out);
+
 /* ---- micromagnetics demagnetising field: the repeated solve of the LL time loop ---------------
  * Replaces LL::LL (constructor work) + LL::magnetostaticField of Femeko_jl_C++/Micromagnetics/LL.cpp
  * (:4-66, :287-348; Julia twin Micromagnetics/LL.jl:162-211), reached in the reference through
@@ -311,6 +318,41 @@ int fk_comm_mode(fk_handle h, int* mode);
 /* ---- legacy drop-in: ABI-identical to the reference (magnetostatics.cpp:49-60) --------------- */
 void scalarPotential(double* u_in, double* p_in, int* t_in, int* surfaceT_in, double* normal_in,
                      int nv, int nt, int ns, double* VE, double* mu, double* Hext, int shell_id);
+
+/* ---- ONE process, several GPUs --------------------------------------------------------------------------
+ * The reference's caller is a single Julia process (Femeko_jl_C++/Magnetostatics/run.jl:66-79): fk_multi_* lets that one
+ * process use 2 / 4 / 8 GPUs.  fk_multi_create takes the GLOBAL mesh (as fk_create), partitions its nodes by recursive
+ * coordinate bisection, builds one handle per GPU (owned rows first, halo rows after, ghost elements duplicated) and
+ * wires them over peer memory (cudaDeviceEnablePeerAccess; no NCCL, no IPC).  Every call below takes and returns GLOBAL
+ * host arrays in the caller's numbering; the work runs on one host thread per GPU, and the per-GPU kernels, the halo
+ * exchange fused into the SpMV and the dot products over NVLink are those of the one-process-per-GPU path.
+ * devices: ngpu CUDA ordinals, or NULL for 0 .. ngpu-1.                                                          */
+typedef struct fk_multi_s* fk_multi;
+int fk_multi_create(const double* p, const int* t, int nv, int nt, const double* VE, int ngpu, const int* devices,
+                    const fk_create_opts* opts, fk_multi* out);
+int fk_multi_destroy(fk_multi m);
+/* the host-side decomposition on its own (no GPU needed): recursive coordinate bisection of the nodes, and one rank's
+ * local numbering + halo plan.  Call fk_partition_local with NULL arrays for the sizes first.                     */
+int fk_rcb(const double* p, int nv, int nparts, int* part_out /* nv */);
+int fk_partition_local(const double* p, const int* t, int nv, int nt, const int* part, int rank,
+                       int* sizes /* n_owned, nv_local, nt_local, nneigh, nsend */, int* l2g, int* elem_l2g, int* t_local /* 4 x nt_local */,
+                       int* neigh, int* send_ptr /* nneigh+1 */, int* send_idx, int* recv_start, int* recv_count);
+int fk_multi_info(fk_multi m, int* ngpu, int* n_owned /* ngpu */, int* nv_local, int* nt_local, int* nneigh);
+int fk_multi_handle(fk_multi m, int rank, fk_handle* h);   /* the part's own handle (per-part diagnostics) */
+int fk_multi_partition(fk_multi m, int rank, int* l2g /* nv_local: local node -> global */, int* elem_l2g /* nt_local */);
+int fk_multi_assemble_stiffness(fk_multi m, int slot, const double* f /* nt or NULL */);
+int fk_multi_assemble_mass(fk_multi m, int slot, const double* rho /* nt or NULL */);
+int fk_multi_matrix_axpby(fk_multi m, int dst, double alpha, int x, double beta, int y);
+int fk_multi_set_spline(fk_multi m, int id, const double* t, const double* c, int n, int k, int bc);
+int fk_multi_set_inside(fk_multi m, const int* ids /* global element ids */, int n);
+int fk_multi_set_mu(fk_multi m, const double* mu /* nt */);
+int fk_multi_get_mu(fk_multi m, double* mu_out /* nt */);
+int fk_multi_get_field(fk_multi m, double* Hfield_out /* 3 x nt or NULL */, double* Hnorm_out /* nt or NULL */);
+int fk_multi_reset_field(fk_multi m);
+int fk_multi_spmv(fk_multi m, int slot, const double* x /* nv */, double* y /* nv */);
+int fk_multi_pcg(fk_multi m, int slot, const double* b /* nv */, double* x /* nv in/out */, const fk_pcg_opts* opts, int* iters_out,
+                 double* relres_out);
+int fk_multi_picard_step(fk_multi m, int slot, const double* u /* nv */, int compat_bug, double* div_out);
 
 #ifdef __cplusplus
 }

@@ -62,10 +62,13 @@ report("stiffness_tile", timed(stiff, r), stiff_bytes)
 h.tune(10, 2)
 sweep(); stiff(); h.synchronize()
 print(json.dumps({"geo_stats(items, contributions, slots, bytes)": h.geo_stats()}), flush=True)
-for v in ([0] if short else [0, 1, 2, 3]):
-    h.tune(12, v)
-    sweep(); stiff(); h.synchronize()
-    report(f"picard_sweep_rescale_v{v}", timed(sweep, r), picard_bytes)
-    report(f"stiffness_rescale_v{v}", timed(stiff, r), stiff_bytes)
+for win in ([4096] if short else [int(w) for w in os.environ.get('FK_WINDOWS', '4096,16384,65536,262144,1048576').split(',')]):
+    h.tune(13, win)
+    for v in [0]:
+        h.tune(12, v)
+        sweep(); stiff(); h.synchronize()
+        gs = h.geo_stats()
+        report(f"picard_sweep_rescale_v{v}_win{win}_pad{gs[2] / gs[1]:.3f}", timed(sweep, r), picard_bytes)
+        report(f"stiffness_rescale_v{v}_win{win}", timed(stiff, r), stiff_bytes)
 h.picard_result()
 h.close()

@@ -249,6 +249,12 @@ def test_heat_step_against_direct_solve():
         Tref = lu.solve(M @ Tref)
     assert rel_l2(T, Tref) < 1e-9
     assert abs((M @ T).sum() - (M @ Tref).sum()) < 1e-9 * abs((M @ Tref).sum())   # heat is conserved (natural BC)
+    # the one-call form of the step (fk_heat_step) takes the same steps
+    T2 = np.zeros(m.nv)
+    T2[m.InsideNodes] = 10.0
+    for _ in range(5):
+        T2, it2, _ = h.heat_step(T2, slot_mass=1, slot_lhs=3, tol=1e-12)
+    assert np.array_equal(T2, T)
     h.close()
 
 

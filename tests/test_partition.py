@@ -180,3 +180,35 @@ def test_distributed_pcg_over_gloo_matches_serial_oracle(kind, world, tmp_path):
     xs, its, _, info = orc.pcg(rp, ci, v, b, 1e-10)
     assert info == 0 and abs(it - its) <= 2
     assert rel_l2(x, xs) < 1e-8
+
+
+@pytest.mark.parametrize("mesh,nparts", [("delaunay", 2), ("delaunay", 4), ("kuhn", 8), ("kuhn", 3)])
+def test_cxx_partitioner_equals_python(mesh, nparts):
+    """The C++ decomposition behind fk_multi_create (csrc/multi.cu: fk_rcb, fk_partition_local) == partition.py:
+    node partition, local numbering (owned ascending, halo by owner then id), ghost elements, halo plan."""
+    import ctypes as C
+
+    from femeko_jl_b200 import lib as L
+
+    lib = L.load()
+    m = fk.delaunay_ball(900, seed=4) if mesh == "delaunay" else fk.kuhn_cube(5)
+    p = np.asfortranarray(m.p, dtype=np.float64)
+    t = np.asfortranarray(m.t, dtype=np.int32)
+    part = np.zeros(m.nv, dtype=np.int32)
+    L.check(lib.fk_rcb(L.dptr(p), m.nv, nparts, L.iptr(part)))
+    assert np.array_equal(part, P.rcb(m.p, nparts))
+    for r in range(nparts):
+        lm, pr = P.partition_mesh(m, part, r, nparts)
+        sizes = np.zeros(5, dtype=np.int32)
+        none = [None] * 8
+        L.check(lib.fk_partition_local(L.dptr(p), L.iptr(t), m.nv, m.nt, L.iptr(part), r, L.iptr(sizes), *none))
+        n_owned, nvl, ntl, nn, nsend = (int(v) for v in sizes)
+        assert (n_owned, nvl, ntl, nn) == (pr.n_owned, lm.nv, lm.nt, len(pr.neigh))
+        l2g, e2g, tl = np.zeros(nvl, np.int32), np.zeros(ntl, np.int32), np.zeros((4, ntl), np.int32, order="F")
+        neigh, sp, si = np.zeros(nn, np.int32), np.zeros(nn + 1, np.int32), np.zeros(nsend, np.int32)
+        rs, rc = np.zeros(nn, np.int32), np.zeros(nn, np.int32)
+        L.check(lib.fk_partition_local(L.dptr(p), L.iptr(t), m.nv, m.nt, L.iptr(part), r, L.iptr(sizes), L.iptr(l2g), L.iptr(e2g),
+                                       L.iptr(tl), L.iptr(neigh), L.iptr(sp), L.iptr(si), L.iptr(rs), L.iptr(rc)))
+        assert np.array_equal(l2g, pr.l2g) and np.array_equal(e2g, pr.elem_l2g) and np.array_equal(tl, lm.t)
+        assert list(neigh) == [int(q) for q in pr.neigh] and np.array_equal(sp, pr.send_ptr) and np.array_equal(si, pr.send_idx)
+        assert np.array_equal(rs, pr.recv_start) and np.array_equal(rc, pr.recv_count)
