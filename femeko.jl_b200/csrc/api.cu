@@ -353,8 +353,17 @@ static void configure_l2(fk_handle h, int recurrence) {
   if (h->l2_window_set && !was_set) g_l2_users++;
   if (!h->l2_window_set && was_set) g_l2_users--;
   h->l2_window = attr.accessPolicyWindow;
-  if (h->stream && cudaStreamSetAttribute(h->stream, cudaStreamAttributeAccessPolicyWindow, &attr) != cudaSuccess) cudaGetLastError();
-  if (h->halo_stream && cudaStreamSetAttribute(h->halo_stream, cudaStreamAttributeAccessPolicyWindow, &attr) != cudaSuccess) cudaGetLastError();
+  // The window rides on the kernel nodes of the PCG chunk graphs (build_graph).  It is NOT left on the handle's stream any
+  // more: a stream attribute covers every kernel launched there, and under it the assembly sweep's gathers (scales, node
+  // coordinates: everything outside the window) were treated as streaming (evict-first) lines.  fk_tune(14, 1) restores
+  // the stream attribute (the path without graphs -- NCCL fallback -- always sets it around its launches).
+  cudaStreamAttrValue off{};
+  off.accessPolicyWindow.num_bytes = 0;
+  off.accessPolicyWindow.hitProp = cudaAccessPropertyNormal;
+  off.accessPolicyWindow.missProp = cudaAccessPropertyNormal;
+  const cudaStreamAttrValue& sa = (h->l2_on_stream || (h->comm && !comm_capturable(h))) ? attr : off;
+  if (h->stream && cudaStreamSetAttribute(h->stream, cudaStreamAttributeAccessPolicyWindow, &sa) != cudaSuccess) cudaGetLastError();
+  if (h->halo_stream && cudaStreamSetAttribute(h->halo_stream, cudaStreamAttributeAccessPolicyWindow, &sa) != cudaSuccess) cudaGetLastError();
   invalidate_graphs(h);
 }
 
@@ -639,6 +648,11 @@ static void pcg_dev(fk_handle h, int slot, const double* b_dev, double* x_dev, c
   }
   const bool graphed = !h->comm || comm_capturable(h);
   if (graphed) build_graph(h, slot, chunk, rec);
+  else if (h->l2_window_set) {   // no graph to carry the window (NCCL fallback): the stream does
+    cudaStreamAttrValue attr{};
+    attr.accessPolicyWindow = h->l2_window;
+    if (s && cudaStreamSetAttribute(s, cudaStreamAttributeAccessPolicyWindow, &attr) != cudaSuccess) cudaGetLastError();
+  }
   int launched = 0;
   while (true) {
     if (!graphed) {
@@ -842,6 +856,8 @@ int fk_create(const double* p, const int* t, int nv, int nt, const double* VE, c
       launch_assemble<ASM_TANGENT>(h.get(), dummy, true);
       launch_assemble<ASM_PICARD>(h.get(), dummy, true);
       launch_assemble<ASM_LAGRANGE>(h.get(), dummy, true);
+      launch_assemble<ASM_STIFF2D>(h.get(), dummy, true);
+      launch_assemble<ASM_MASS2D>(h.get(), dummy, true);
     }
 
     // launch geometry of the persistent SpMV / vector kernels: full residency, fixed for determinism
@@ -906,6 +922,8 @@ int fk_tune(fk_handle h, int what, int value) {
         launch_assemble<ASM_TANGENT>(h, dummy, true);
         launch_assemble<ASM_PICARD>(h, dummy, true);
         launch_assemble<ASM_LAGRANGE>(h, dummy, true);
+        launch_assemble<ASM_STIFF2D>(h, dummy, true);
+        launch_assemble<ASM_MASS2D>(h, dummy, true);
         break;
       }
       case 1: h->spmv_ctas = value; configure_spmv(h, value); break;
@@ -939,6 +957,13 @@ int fk_tune(fk_handle h, int what, int value) {
       case 10:  // rescale assembly: 0 = never (tile kernel only), 1 = from the second Picard sweep on (default), 2 = at once
         need(value >= 0 && value <= 2, "fk_tune: geo mode out of range");
         h->geo_mode = value;
+        break;
+      case 14:  // 1: keep the L2 window on the handle's stream too (the behaviour before round 2); 0 (default): graph nodes only
+        h->l2_on_stream = value != 0;
+        configure_l2(h, h->l2_recurrence);
+        break;
+      case 15:  // 1: give the assembly sweep the whole L2 (reset the persisting lines of the PCG vectors before it); default 0
+        h->l2_reset_before_sweep = value != 0;
         break;
       case 13:  // rescale plan: items are sorted by list length inside windows of this many items (32 = plan order kept); rebuilds
         need(value >= 32 && value <= (1 << 20), "fk_tune: geo window out of range");
@@ -1242,6 +1267,38 @@ int fk_assemble_tangential(fk_handle h, int slot, const double* Hfield, const do
     h->st_b.upload(Hfield, (size_t)3 * h->nt, h->stream);
     assemble_tangential_dev(h, slot, h->st_b.ptr, h->st_a.ptr);
     copy_out_matrix(h, h->vals[slot].ptr, vals_out);
+    return 0;
+  });
+}
+// 2-D P1 triangles (src/FEM2D.jl:48-76 stiffnessMatrix2D, :139-161 massMatrix2D) on a handle created from the elements
+// (n0, n1, n2, n2): same plan, same kernels, 3 x 3 local matrices
+int fk_assemble_stiffness2d(fk_handle h, int slot, const double* f, double* vals_out) {
+  return guard([&]() {
+    need(h, "fk: NULL handle");
+    DeviceGuard dg(h->device);
+    const double* fd = nullptr;
+    if (f) { h->st_a.upload(f, (size_t)h->nt, h->stream); fd = h->st_a.ptr; }
+    h->dir_applied &= ~(1u << slot);
+    AsmArgs a = base_args(h, slot_vals(h, slot));
+    a.coef = fd;
+    launch_assemble<ASM_STIFF2D>(h, a);
+    if (vals_out) copy_out_matrix(h, h->vals[slot].ptr, vals_out);
+    else FK_CUDA(cudaStreamSynchronize(h->stream));
+    return 0;
+  });
+}
+int fk_assemble_mass2d(fk_handle h, int slot, const double* rho, double* vals_out) {
+  return guard([&]() {
+    need(h, "fk: NULL handle");
+    DeviceGuard dg(h->device);
+    const double* rd = nullptr;
+    if (rho) { h->st_a.upload(rho, (size_t)h->nt, h->stream); rd = h->st_a.ptr; }
+    h->dir_applied &= ~(1u << slot);
+    AsmArgs a = base_args(h, slot_vals(h, slot));
+    a.coef = rd;
+    launch_assemble<ASM_MASS2D>(h, a);
+    if (vals_out) copy_out_matrix(h, h->vals[slot].ptr, vals_out);
+    else FK_CUDA(cudaStreamSynchronize(h->stream));
     return 0;
   });
 }
@@ -1789,9 +1846,15 @@ static int picard_step_dev(fk_handle h, int slot, const double* u_dev, int compa
   // 2. the sweep: stiffness with the refreshed mu + H, |H| of every element.  A handle that sweeps repeatedly (a Picard
   //    loop) switches to the rescale path (rescale.cuh): same bits, streamed instead of recomputed.
   h->geo_sweeps++;
+  if (h->l2_reset_before_sweep && h->l2_window_set) cudaCtxResetPersistingL2Cache();
   if (h->geo_mode == 2 || (h->geo_mode == 1 && (h->geo_ready || h->geo_sweeps >= 2))) {
     ensure_geo(h);
-    picard_element_kernel<<<cdiv(h->nt, kElemThreads), kElemThreads, 0, h->stream>>>(h->p4.ptr, h->t4.ptr, a.u, h->mu.ptr, a.VE, h->nt,
+    if (h->elem_grid == 0) {
+      int occ = 1;
+      FK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, picard_element_kernel, kElemThreads, 0));
+      h->elem_grid = h->num_sms * std::max(1, occ);
+    }
+    picard_element_kernel<<<std::min(cdiv(h->nt, kElemThreads), h->elem_grid), kElemThreads, 0, h->stream>>>(h->p4.ptr, h->t4.ptr, a.u, h->mu.ptr, a.VE, h->nt,
                                                                                    compat_bug, h->Hn.ptr, h->Hfield.ptr, h->geo_s0.ptr);
     FK_CUDA(cudaGetLastError());
     h->launches++;

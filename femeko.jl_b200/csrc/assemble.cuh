@@ -17,7 +17,10 @@
 // Reference math: src/FEM3D.jl:59-76 (stiffness), :466-476 (mass), :79-105 (tangential),
 // :274-281 (lagrange), NewtonRaphson.jl:178-197 (Picard: H recovery + rescale by mu).
 
-enum AsmMode { ASM_STIFF = 0, ASM_MASS = 1, ASM_TANGENT = 2, ASM_PICARD = 3, ASM_LAGRANGE = 4 };
+// ASM_STIFF2D / ASM_MASS2D: 2-D P1 triangles (src/FEM2D.jl:48-76,139-161) through the same plan.  A triangle (n0,n1,n2)
+// enters the handle as the element (n0,n1,n2,n2): the pattern is the triangle's node adjacency, every local pair that
+// involves the fourth slot carries an exact 0.0 (x + 0.0 == x, so the sums are those of the 3 x 3 local matrices).
+enum AsmMode { ASM_STIFF = 0, ASM_MASS = 1, ASM_TANGENT = 2, ASM_PICARD = 3, ASM_LAGRANGE = 4, ASM_STIFF2D = 5, ASM_MASS2D = 6 };
 
 struct AsmArgs {
   const double* VE;       // nullable: volume from the determinant
@@ -81,6 +84,32 @@ __device__ __forceinline__ void element_local(const AsmArgs& a, const int k, con
                                               const double* __restrict__ us, const uint2 l, const double fpre, const double vpre,
                                               double (&m)[10]) {
   const int l0 = l.x & 0xffff, l1 = l.x >> 16, l2 = l.y & 0xffff, l3 = l.y >> 16;
+  if (MODE == ASM_STIFF2D || MODE == ASM_MASS2D) {
+    // abc of src/FEM2D.jl:5-25 in closed form: f_i = a + b x + c y, b_i = (y_j - y_k) / det, c_i = (x_k - x_j) / det (i,j,k cyclic),
+    // det = (x1-x0)(y2-y0) - (x2-x0)(y1-y0); area = |det| / 2 (mesh.VE of a 2-D mesh)
+    const double x0 = xs[l0], y0 = ys[l0], x1 = xs[l1], y1 = ys[l1], x2 = xs[l2], y2 = ys[l2];
+    const double det = (x1 - x0) * (y2 - y0) - (x2 - x0) * (y1 - y0);
+    const double V = a.VE ? vpre : fabs(det) / 2.0;
+#pragma unroll
+    for (int q = 0; q < 10; q++) m[q] = 0.0;
+    if (MODE == ASM_MASS2D) {   // VE/12 [2 1 1; 1 2 1; 1 1 2], src/FEM2D.jl:139-161
+      const double v = a.coef ? V * fpre : V;
+      const double d = v * ((1.0 / 12.0) * 2.0), o = v * ((1.0 / 12.0) * 1.0);
+      m[0] = d; m[1] = o; m[2] = o; m[4] = d; m[5] = o; m[7] = d;
+      return;
+    }
+    const double inv = 1.0 / det;
+    const double b0 = (y1 - y2) * inv, b1 = (y2 - y0) * inv, b2 = (y0 - y1) * inv;
+    const double c0 = (x2 - x1) * inv, c1 = (x0 - x2) * inv, c2 = (x1 - x0) * inv;
+    const double s0 = V * fpre;   // VE[k]*mu[k]*(b b' + c c'), src/FEM2D.jl:62
+    m[0] = __dmul_rn(s0, __fma_rn(c0, c0, __dmul_rn(b0, b0)));
+    m[1] = __dmul_rn(s0, __fma_rn(c0, c1, __dmul_rn(b0, b1)));
+    m[2] = __dmul_rn(s0, __fma_rn(c0, c2, __dmul_rn(b0, b2)));
+    m[4] = __dmul_rn(s0, __fma_rn(c1, c1, __dmul_rn(b1, b1)));
+    m[5] = __dmul_rn(s0, __fma_rn(c1, c2, __dmul_rn(b1, b2)));
+    m[7] = __dmul_rn(s0, __fma_rn(c2, c2, __dmul_rn(b2, b2)));
+    return;
+  }
   TetGeom G;
   if (MODE == ASM_MASS || MODE == ASM_LAGRANGE) {
     double v;

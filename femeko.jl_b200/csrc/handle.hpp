@@ -81,6 +81,7 @@ struct fk_handle_s {
   bool overlap_halo = true;
   int halo_mode = 2;          // partitions, Eigen recurrence: 2 = exchange fused into the SpMV kernel, 1 = second stream, 0 = serial
   bool l2_miss_normal = false; // fk_tune 8
+  bool l2_on_stream = false, l2_reset_before_sweep = false;   // fk_tune 14 / 15
   int l2_max_vecs = 0;         // fk_tune 9
   int spmv_int_reserve = 0;   // CTA slots per SM the interior SpMV leaves to the halo branch (measured: 0 best)
   cudaStream_t halo_stream = nullptr;
@@ -145,7 +146,7 @@ struct fk_handle_s {
   fk::Comm* comm = nullptr;
   // rescale assembly (rescale.cuh): geometric factors of every contribution, built on demand
   //   geo_mode 0: never; 1 (default): from the second Picard sweep of a handle on; 2: from the first sweep / assembly on
-  int geo_mode = 1, geo_sweeps = 0, geo_nslices = 0, geo_grid = 0, geo_variant = 0, geo_window = 4096;
+  int geo_mode = 1, geo_sweeps = 0, geo_nslices = 0, geo_grid = 0, geo_variant = 0, geo_window = 65536, elem_grid = 0;
   bool geo_ready = false;
   long long geo_slots = 0, geo_items = 0, geo_contrib = 0;
   fk::DevBuf<double> geo_g, geo_s0;

@@ -57,38 +57,50 @@ static __global__ void __launch_bounds__(256) geo_scale_kernel(const double* __r
 // with ONE 256-bit load (load_node: LDG.E.256) instead of two 128-bit ones, and the three components
 // of H leave through a per-warp shared-memory transpose so that a warp writes 768 contiguous bytes with three stores.
 constexpr int kElemThreads = 256;
+// Persistent grid (fk: picard_step_dev launches one wave of resident CTAs): the connectivity and the coefficient of the
+// chunk a CTA will work on NEXT are requested before the gathers of the current one, so the two dependent memory
+// round trips of an element (connectivity -> node / potential gathers) overlap across chunks.
 static __global__ void __launch_bounds__(kElemThreads) picard_element_kernel(const double4* __restrict__ p4, const int4* __restrict__ t4,
                                                                              const double* __restrict__ u, const double* __restrict__ mu,
                                                                              const double* __restrict__ VE, int nt, int compat,
                                                                              double* __restrict__ Hn, double* __restrict__ Hfield,
                                                                              double* __restrict__ s0) {
   __shared__ double hs[kElemThreads / 32][96];
-  const int k = blockIdx.x * blockDim.x + threadIdx.x;
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-  double hx = 0.0, hy = 0.0, hz = 0.0;
-  if (k < nt) {
-    const int4 nd = __ldg(t4 + k);
-    const double f = __ldcs(mu + k);
-    const double u0 = __ldg(u + nd.x), u1 = __ldg(u + nd.y), u2 = __ldg(u + nd.z), u3 = __ldg(u + nd.w);
-    TetGeom G;
-    tet_geometry(p4, nd, G);
-    hx = -(u0 * G.g[0][0]) - u1 * G.g[1][0] - u2 * G.g[2][0] - u3 * G.g[3][0];
-    hy = -(u0 * G.g[0][1]) - u1 * G.g[1][1] - u2 * G.g[2][1] - u3 * G.g[3][1];
-    hz = -(u0 * G.g[0][2]) - u1 * G.g[1][2] - u2 * G.g[2][2] - u3 * G.g[3][2];
-    if (compat) { hy += hz; hz = 0.0; }  // NewtonRaphson.jl:187-189: d-term lands in row 2
-    __stcs(Hn + k, norm3(hx, hy, hz));
-    const double V = VE ? __ldcs(VE + k) : G.vol;
-    s0[k] = __dmul_rn(V, f);
-  }
-  if (Hfield) {
-    double* w = hs[wib];
-    w[3 * lane] = hx; w[3 * lane + 1] = hy; w[3 * lane + 2] = hz;
-    __syncwarp();
-    const int kw = k - lane;                       // first element of this warp
-    const int n3 = 3 * max(0, min(32, nt - kw));
+  const long long stride = (long long)gridDim.x * kElemThreads;
+  long long k = (long long)blockIdx.x * kElemThreads + threadIdx.x;
+  int4 nd = make_int4(0, 0, 0, 0);
+  double f = 0.0, V = 0.0;
+  if (k < nt) { nd = __ldg(t4 + k); f = __ldcs(mu + k); if (VE) V = __ldcs(VE + k); }
+  for (long long k0 = (long long)blockIdx.x * kElemThreads; k0 < nt; k0 += stride, k += stride) {
+    const long long kn = k + stride;
+    int4 ndn = make_int4(0, 0, 0, 0);
+    double fn = 0.0, Vn = 0.0;
+    if (kn < nt) { ndn = __ldg(t4 + kn); fn = __ldcs(mu + kn); if (VE) Vn = __ldcs(VE + kn); }
+    double hx = 0.0, hy = 0.0, hz = 0.0;
+    if (k < nt) {
+      const double u0 = __ldg(u + nd.x), u1 = __ldg(u + nd.y), u2 = __ldg(u + nd.z), u3 = __ldg(u + nd.w);
+      TetGeom G;
+      tet_geometry(p4, nd, G);
+      hx = -(u0 * G.g[0][0]) - u1 * G.g[1][0] - u2 * G.g[2][0] - u3 * G.g[3][0];
+      hy = -(u0 * G.g[0][1]) - u1 * G.g[1][1] - u2 * G.g[2][1] - u3 * G.g[3][1];
+      hz = -(u0 * G.g[0][2]) - u1 * G.g[1][2] - u2 * G.g[2][2] - u3 * G.g[3][2];
+      if (compat) { hy += hz; hz = 0.0; }  // NewtonRaphson.jl:187-189: d-term lands in row 2
+      __stcs(Hn + k, norm3(hx, hy, hz));
+      s0[k] = __dmul_rn(VE ? V : G.vol, f);
+    }
+    if (Hfield) {
+      double* w = hs[wib];
+      __syncwarp();
+      w[3 * lane] = hx; w[3 * lane + 1] = hy; w[3 * lane + 2] = hz;
+      __syncwarp();
+      const long long kw = k - lane;                       // first element of this warp
+      const int n3 = kw < nt ? 3 * (int)min((long long)32, nt - kw) : 0;
 #pragma unroll
-    for (int q = 0; q < 3; q++)
-      if (32 * q + lane < n3) __stcs(Hfield + 3 * (size_t)kw + 32 * q + lane, w[32 * q + lane]);
+      for (int q = 0; q < 3; q++)
+        if (32 * q + lane < n3) __stcs(Hfield + 3 * kw + 32 * q + lane, w[32 * q + lane]);
+    }
+    nd = ndn; f = fn; V = Vn;
   }
 }
 

@@ -43,7 +43,13 @@ class Femeko:
         o.n_owned = int(n_owned)
         p = L.f64(mesh.p)
         t = L.i32(mesh.t)
-        assert p.shape[0] == 3 and t.shape[0] == 4, "mesh.p must be 3 x nv and mesh.t 4 x nt"
+        self.dim = 3
+        if t.shape[0] == 3:   # 2-D P1 triangles ride the same engine as the elements (n0, n1, n2, n2) (fk_assemble_*2d)
+            self.dim = 2
+            t = np.vstack([t, t[2:3]])
+            if p.shape[0] == 2:
+                p = np.vstack([p, np.zeros((1, p.shape[1]))])
+        assert p.shape[0] == 3 and t.shape[0] == 4, "mesh.p must be 3 x nv and mesh.t 4 x nt (3 x nt for triangles)"
         p = np.asfortranarray(p)
         t = np.asfortranarray(t)
         VE = L.f64(mesh.VE) if (use_mesh_VE and mesh.VE is not None) else None
@@ -148,6 +154,18 @@ class Femeko:
         v = self._vals(want_vals)
         f = self._coef(f)
         L.check(self.lib.fk_assemble_stiffness(self.h, slot, L.dptr(f), L.dptr(v)))
+        return v
+
+    def assemble_stiffness2d(self, f=None, slot=0, want_vals=True):
+        assert self.dim == 2, "handle was not created from a triangle mesh"
+        v = self._vals(want_vals)
+        L.check(self.lib.fk_assemble_stiffness2d(self.h, slot, L.dptr(self._coef(f)), L.dptr(v)))
+        return v
+
+    def assemble_mass2d(self, rho=None, slot=1, want_vals=True):
+        assert self.dim == 2, "handle was not created from a triangle mesh"
+        v = self._vals(want_vals)
+        L.check(self.lib.fk_assemble_mass2d(self.h, slot, L.dptr(self._coef(rho)), L.dptr(v)))
         return v
 
     def assemble_mass(self, rho=None, slot=1, want_vals=True):
@@ -566,6 +584,18 @@ def stiffnessMatrix(mesh: MESH, f=None) -> SparseCSR:
 def massMatrix(mesh: MESH) -> SparseCSR:
     fk = _handle(mesh)
     return SparseCSR(fk, 1, fk.assemble_mass(None, slot=1))
+
+
+def stiffnessMatrix2D(mesh: MESH, mu=None) -> SparseCSR:
+    """src/FEM2D.jl:48-76 on a triangle mesh (mesh.t is 3 x nt, mesh.VE the triangle areas)."""
+    fk = _handle(mesh)
+    return SparseCSR(fk, 0, fk.assemble_stiffness2d(mu, slot=0))
+
+
+def massMatrix2D(mesh: MESH) -> SparseCSR:
+    """src/FEM2D.jl:139-161."""
+    fk = _handle(mesh)
+    return SparseCSR(fk, 1, fk.assemble_mass2d(None, slot=1))
 
 
 def tangentialStiffnessMatrix(mesh: MESH, H_vec, dmu) -> SparseCSR:

@@ -288,3 +288,62 @@ def delaunay_ball(npts: int = 4000, seed: int = 1234, R: float = 5.0, inside_hal
     cen = (mesh.p[:, mesh.t[0]] + mesh.p[:, mesh.t[1]] + mesh.p[:, mesh.t[2]] + mesh.p[:, mesh.t[3]]) / 4
     inside = np.all(np.abs(cen) <= inside_half, axis=0)
     return _finish(mesh, inside)
+
+
+# --------------------------------------------------------------------------------------------------
+# 2-D triangle meshes (src/FEM2D.jl operates on MESH with t = 3 x nt, VE = triangle areas)
+# --------------------------------------------------------------------------------------------------
+def _finish2d(mesh: MESH, inside_mask: np.ndarray) -> MESH:
+    p, t = mesh.p, mesh.t
+    a, b, c = p[:2, t[0]], p[:2, t[1]], p[:2, t[2]]
+    det = (b[0] - a[0]) * (c[1] - a[1]) - (c[0] - a[0]) * (b[1] - a[1])
+    mesh.VE = np.abs(det) / 2.0
+    mesh.nv, mesh.nt = int(p.shape[1]), int(t.shape[1])
+    mesh.InsideElements = np.flatnonzero(inside_mask).astype(np.int32)
+    mesh.nInside = int(mesh.InsideElements.size)
+    mesh.InsideNodes = np.unique(t[:, mesh.InsideElements]).astype(np.int32)
+    mesh.nInsideNodes = int(mesh.InsideNodes.size)
+    mesh.surfaceT = np.zeros((4, 0), dtype=np.int32, order="F")
+    mesh.ns = 0
+    return mesh
+
+
+def tri_grid(N: int, L: float = 1.0, inside_edge: float = 0.4) -> MESH:
+    """Square [-L/2, L/2]^2 with N cells per edge, each cut along its low-to-high diagonal: 2 N^2 triangles,
+    (N+1)^2 nodes, node id i (N+1) + j; p is 3 x nv with z = 0 (Gmsh hands 2-D meshes over that way)."""
+    n1 = N + 1
+    g = (np.arange(n1, dtype=np.float64) / N - 0.5) * L
+    X, Y = np.meshgrid(g, g, indexing="ij")
+    mesh = MESH()
+    mesh.p = np.asfortranarray(np.stack([X.ravel(), Y.ravel(), np.zeros(n1 * n1)]))
+    ii, jj = np.meshgrid(np.arange(N, dtype=np.int64), np.arange(N, dtype=np.int64), indexing="ij")
+    c00 = (ii * n1 + jj).ravel()
+    c10, c01, c11 = c00 + n1, c00 + 1, c00 + n1 + 1
+    t = np.empty((c00.size, 2, 3), dtype=np.int32)
+    t[:, 0] = np.stack([c00, c10, c11], axis=1)
+    t[:, 1] = np.stack([c00, c11, c01], axis=1)
+    mesh.t = np.asfortranarray(t.reshape(-1, 3).T)
+    cen = (mesh.p[:2, mesh.t[0]] + mesh.p[:2, mesh.t[1]] + mesh.p[:2, mesh.t[2]]) / 3
+    return _finish2d(mesh, np.all(np.abs(cen) <= 0.5 * inside_edge * L, axis=0))
+
+
+def delaunay_disc(npts: int = 2000, seed: int = 7, R: float = 1.0, inside_half: float = 0.3) -> MESH:
+    """Unstructured stand-in for a Gmsh 2-D mesh: Delaunay triangulation of random points in a disc (slivers removed)."""
+    from scipy.spatial import Delaunay
+
+    rng = np.random.default_rng(seed)
+    r = R * np.sqrt(rng.uniform(0, 1, npts))
+    th = rng.uniform(0, 2 * np.pi, npts)
+    pts = np.stack([r * np.cos(th), r * np.sin(th)], axis=1)
+    tri = Delaunay(pts).simplices.astype(np.int32)
+    a, b, c = pts[tri[:, 0]], pts[tri[:, 1]], pts[tri[:, 2]]
+    area = 0.5 * np.abs((b[:, 0] - a[:, 0]) * (c[:, 1] - a[:, 1]) - (c[:, 0] - a[:, 0]) * (b[:, 1] - a[:, 1]))
+    tri = tri[area > 1e-10 * area.mean()]
+    used = np.unique(tri)
+    remap = -np.ones(npts, dtype=np.int64)
+    remap[used] = np.arange(used.size)
+    mesh = MESH()
+    mesh.p = np.asfortranarray(np.vstack([pts[used].T, np.zeros((1, used.size))]))
+    mesh.t = np.asfortranarray(remap[tri].T.astype(np.int32))
+    cen = (mesh.p[:2, mesh.t[0]] + mesh.p[:2, mesh.t[1]] + mesh.p[:2, mesh.t[2]]) / 3
+    return _finish2d(mesh, np.all(np.abs(cen) <= inside_half, axis=0))

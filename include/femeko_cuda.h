@@ -165,6 +165,12 @@ int fk_assemble_stiffness(fk_handle h, int slot, const double* f, double* vals_o
 int fk_assemble_mass(fk_handle h, int slot, const double* rho, double* vals_out);       /* FEM3D.jl:466-492 */
 int fk_assemble_tangential(fk_handle h, int slot, const double* Hfield /* 3 x nt */,
                            const double* dmu, double* vals_out);                        /* FEM3D.jl:79-119 */
+/* 2-D P1 triangles through the same engine (src/FEM2D.jl:48-76 stiffnessMatrix2D, :139-161 massMatrix2D): create the
+ * handle from the elements (n0, n1, n2, n2) -- fk_create with the triangle's third node repeated, p still 3 x nv with
+ * the z row ignored -- and VE = triangle areas or NULL (|det| / 2).  Local matrices VE mu (b b' + c c') and
+ * VE/12 [2 1 1; 1 2 1; 1 1 2]; pattern, plan, SpMV and PCG are the 3-D ones.                                        */
+int fk_assemble_stiffness2d(fk_handle h, int slot, const double* f /* nt or NULL */, double* vals_out /* nnz or NULL */);
+int fk_assemble_mass2d(fk_handle h, int slot, const double* rho /* nt or NULL */, double* vals_out);
 int fk_local_stiffness(fk_handle h, const double* f, double* Ak /* 16 x nt */);          /* FEM3D.jl:59-76 */
 int fk_assemble_stiffness_dev(fk_handle h, int slot, const double* f_dev);
 int fk_assemble_mass_dev(fk_handle h, int slot, const double* rho_dev);

@@ -489,3 +489,66 @@ def newton_loop(mesh, Bext, tck, tck_dmu, tol=1e-4, max_att=100, shell_id=0, com
             raise FloatingPointError("Nans/Infs in mu")
         hist.append((att, div, residue, alf))
     return dict(u=u, Hfield=Hf, H=H, mu=mu, dmu=dmu, att=att, div=div, history=hist)
+
+
+# --------------------------------------------------------------------------------------------------
+# 2-D P1 triangles (src/FEM2D.jl) -- numpy restatement, test infrastructure only
+# --------------------------------------------------------------------------------------------------
+def abc(p, nds, nd):
+    """src/FEM2D.jl:5-25: coefficients (a, b, c) of the hat function of node nd on the triangle nds, from the 3 x 3
+    solve M \\ [1, 0, 0] with the node itself in the first row."""
+    others = [int(i) for i in nds if i != nd]
+    M = np.array([[1.0, p[0, nd], p[1, nd]], [1.0, p[0, others[0]], p[1, others[0]]], [1.0, p[0, others[1]], p[1, others[1]]]])
+    return np.linalg.solve(M, np.array([1.0, 0.0, 0.0]))
+
+
+def pattern2d(t, nv):
+    """Canonical CSR pattern of a triangle mesh: node adjacency + diagonal, ascending columns."""
+    import scipy.sparse as sp
+
+    r = np.concatenate([t[i] for i in range(3) for _ in range(3)]).astype(np.int64)
+    c = np.concatenate([t[j] for _ in range(3) for j in range(3)]).astype(np.int64)
+    A = sp.csr_matrix((np.ones(r.size), (r, c)), shape=(nv, nv))
+    A.sort_indices()
+    return A.indptr.astype(np.int32), A.indices.astype(np.int32)
+
+
+def _assemble2d(mesh, Ak):
+    """A = sum over the 9 local pairs (i outer, j inner) of sparse(t[i,:], t[j,:], Ak[n,:]), duplicates summed in element
+    order, the 9 partial matrices folded left to right (src/FEM2D.jl:66-73); values on the canonical pattern."""
+    rp, ci = pattern2d(mesh.t, mesh.nv)
+    vals = np.zeros(len(ci))
+    key = {}
+    rows = np.repeat(np.arange(mesh.nv), np.diff(rp))
+    for q, (r, c) in enumerate(zip(rows, ci)):
+        key[(int(r), int(c))] = q
+    n = 0
+    for i in range(3):
+        for j in range(3):
+            part = np.zeros(len(ci))
+            for k in range(mesh.nt):
+                part[key[(int(mesh.t[i, k]), int(mesh.t[j, k]))]] += Ak[n, k]
+            vals = vals + part
+            n += 1
+    return rp, ci, vals
+
+
+def stiffness2d(mesh, mu=None):
+    """stiffnessMatrix2D, src/FEM2D.jl:48-76: Ak[:, k] = vec(VE[k] mu[k] (b b' + c c'))."""
+    mu = np.ones(mesh.nt) if mu is None else np.asarray(mu, dtype=np.float64)
+    Ak = np.zeros((9, mesh.nt))
+    for k in range(mesh.nt):
+        nds = mesh.t[:, k]
+        b, c = np.zeros(3), np.zeros(3)
+        for i in range(3):
+            _, b[i], c[i] = abc(mesh.p, nds, int(nds[i]))
+        aux = mesh.VE[k] * mu[k] * (np.outer(b, b) + np.outer(c, c))
+        Ak[:, k] = aux.ravel(order="F")
+    return _assemble2d(mesh, Ak)
+
+
+def mass2d(mesh):
+    """massMatrix2D, src/FEM2D.jl:139-161."""
+    Ml = (1.0 / 12.0) * np.array([[2.0, 1, 1], [1, 2, 1], [1, 1, 2]])
+    Mk = np.outer(Ml.ravel(order="F"), mesh.VE)
+    return _assemble2d(mesh, Mk)

@@ -70,5 +70,40 @@ for win in ([4096] if short else [int(w) for w in os.environ.get('FK_WINDOWS', '
         gs = h.geo_stats()
         report(f"picard_sweep_rescale_v{v}_win{win}_pad{gs[2] / gs[1]:.3f}", timed(sweep, r), picard_bytes)
         report(f"stiffness_rescale_v{v}_win{win}", timed(stiff, r), stiff_bytes)
+# the sweep as the bench step sees it: right after a PCG solve (its vectors pinned in L2) instead of after an L2 flush
+b = torch.randn(h.nv, dtype=torch.float64, device="cuda")
+x = torch.zeros(h.nv, dtype=torch.float64, device="cuda")
+for persist in ([1] if short else [1, 0]):
+    h.tune(2, persist)
+    ts = []
+    for _ in range(r):
+        h.pcg_dev(b.data_ptr(), x.data_ptr(), slot=1, max_iter=20, tol_disable=True, check_every=20)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        sweep()
+        e1.record()
+        torch.cuda.synchronize()
+        ts.append(e0.elapsed_time(e1))
+    ts.sort()
+    report(f"picard_sweep_rescale_after_pcg_l2persist{persist}", (ts[len(ts) // 2], ts[0]), picard_bytes)
+# what precedes the sweep: (a) an idle GPU (sync, 2 ms of host sleep), (b) a busy one (a 60 us fill kernel, no sync)
+import time as _t
+h.tune(2, 1)
+small = torch.empty(32 << 20, dtype=torch.uint8, device="cuda")
+for name, pre in (("idle_2ms", lambda: (torch.cuda.synchronize(), _t.sleep(0.002))), ("idle_sync_only", lambda: torch.cuda.synchronize()),
+                  ("busy_small_fill", lambda: small.zero_()), ("busy_pcg_nosync", None)):
+    ts = []
+    for _ in range(r):
+        torch.cuda.synchronize()
+        if pre is not None:
+            pre()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        sweep()
+        e1.record()
+        torch.cuda.synchronize()
+        ts.append(e0.elapsed_time(e1))
+    ts.sort()
+    report(f"picard_sweep_rescale_{name}", (ts[len(ts) // 2], ts[0]), picard_bytes)
 h.picard_result()
 h.close()

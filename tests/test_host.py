@@ -190,3 +190,26 @@ def test_mesh_generators_geometry():
     assert np.all(d.VE > 0) and d.nInside > 0 and len(np.unique(d.t)) == d.nv
     F = np.array([0.3, -0.2, 0.9])          # closed boundary: the Neumann load sums to zero
     assert abs(orc.boundary_integral(d, F, [0]).sum()) < 1e-9 * d.AE.sum()
+
+
+def test_2d_triangles_through_the_tet_plan():
+    """2-D P1 (src/FEM2D.jl) rides the same symbolic phase as the elements (n0, n1, n2, n2): the pattern is the triangle
+    mesh's node adjacency, and executing the gather plan on 4 x 4 local matrices whose fourth row / column is zero
+    reproduces the oracle's stiffnessMatrix2D / massMatrix2D."""
+    for m in (fk.tri_grid(9), fk.delaunay_disc(600, seed=5)):
+        m4 = fk.MESH()
+        m4.p, m4.nv, m4.nt = m.p, m.nv, m.nt
+        m4.t = np.asfortranarray(np.vstack([m.t, m.t[2:3]]).astype(np.int32))
+        plan = export_symbolic(m4, _rescale=False)
+        rp, ci, vref = orc.stiffness2d(m, np.linspace(1.0, 2.0, m.nt))
+        assert np.array_equal(plan["rowptr"], rp) and np.array_equal(plan["colind"], ci)
+        Ak = np.zeros((16, m.nt))
+        for k in range(m.nt):
+            nds = m.t[:, k]
+            bc = np.array([orc.abc(m.p, nds, int(nds[i]))[1:] for i in range(3)])
+            loc = np.zeros((4, 4))
+            loc[:3, :3] = m.VE[k] * (1.0 + k / (m.nt - 1.0)) * (bc @ bc.T)
+            Ak[:, k] = loc.ravel(order="F")
+        vals, written = run_plan(plan, Ak)
+        assert np.all(written == 1)
+        assert np.max(np.abs(vals - vref)) < 1e-13 * np.max(np.abs(vref))

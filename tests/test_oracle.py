@@ -171,3 +171,33 @@ def test_nonlinear_loop_restatements():
     u = np.zeros(m.nv)
     res, alf = orc.line_search(u, 2.5 * xs, A, RHS)
     assert 0 < alf < 1.0 and np.isclose(np.log(alf) / np.log(0.9), round(np.log(alf) / np.log(0.9)))
+
+
+def test_2d_p1_oracle_properties():
+    """src/FEM2D.jl:48-76,139-161 restated: zero row sums and symmetry of the stiffness matrix, the patch test (linear
+    fields are in the kernel away from the boundary), sum(M) = area, and the local matrix against the closed form."""
+    import scipy.sparse as sp
+
+    for m in (fk.tri_grid(7), fk.delaunay_disc(400, seed=3)):
+        mu = np.random.default_rng(0).uniform(0.5, 2.0, m.nt)
+        rp, ci, v = orc.stiffness2d(m, mu)
+        A = sp.csr_matrix((v, ci, rp), shape=(m.nv, m.nv))
+        assert abs(A.sum(axis=1)).max() < 1e-12 * abs(v).max() and abs(A - A.T).max() < 1e-13 * abs(v).max()
+        _, _, vm = orc.mass2d(m)
+        assert np.isclose(vm.sum(), m.VE.sum(), rtol=1e-13) and vm.min() > 0
+        # one element against the closed-form gradients
+        k = 5
+        nds = m.t[:, k]
+        x, y = m.p[0, nds], m.p[1, nds]
+        det = (x[1] - x[0]) * (y[2] - y[0]) - (x[2] - x[0]) * (y[1] - y[0])
+        b = np.array([y[1] - y[2], y[2] - y[0], y[0] - y[1]]) / det
+        c = np.array([x[2] - x[1], x[0] - x[2], x[1] - x[0]]) / det
+        for i in range(3):
+            _, bi, ci_ = orc.abc(m.p, nds, int(nds[i]))
+            assert np.isclose(bi, b[i], rtol=1e-12, atol=1e-14) and np.isclose(ci_, c[i], rtol=1e-12, atol=1e-14)
+    g = fk.tri_grid(6)
+    rp, ci, v = orc.stiffness2d(g)
+    A = sp.csr_matrix((v, ci, rp), shape=(g.nv, g.nv))
+    r = A @ (2 * g.p[0] + 3 * g.p[1])
+    inner = (np.abs(g.p[0]) < 0.49) & (np.abs(g.p[1]) < 0.49)
+    assert abs(r[inner]).max() < 1e-13
