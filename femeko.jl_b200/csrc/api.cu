@@ -247,7 +247,10 @@ static void launch_spmv_list(fk_handle h, cudaStream_t s, const double* vals, co
   if (nlist <= 0) return;
   const int4* meta = reinterpret_cast<const int4*>(h->slice_meta.ptr);
   spmv_variant_dispatch(h->spmv_variant, [&](auto G, auto MINB) {
-    if (dot)
+    if (dot && list != nullptr && list == h->slices_bnd.ptr)   // halo-coupled rows beside the interior kernel: coherent gathers
+      spmv_sell_kernel<true, G(), MINB(), true><<<grid, kSpmvThreads, 0, s>>>(meta, h->srow.ptr, h->sell_colz.ptr, vals, x, y, nlist, part,
+                                                                              ra, ctl, j, list);
+    else if (dot)
       launch_k(h->pdl && !h->comm, spmv_sell_kernel<true, G(), MINB()>, grid, kSpmvThreads, s, meta, h->srow.ptr, h->sell_colz.ptr, vals,
                x, y, nlist, part, ra, ctl, j, list);
     else

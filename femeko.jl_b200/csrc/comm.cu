@@ -492,6 +492,46 @@ int fk_comm_p2p_attach(fk_handle h, const unsigned char* all_handles, const int*
   }
 }
 
+// After a peer timeout ("a peer GPU did not answer"): clear the error word, the exchange counters, the halo flags and the
+// mailboxes of THIS rank's control block.  Collective in spirit: every rank calls it between two host barriers of the
+// caller (no kernel of the handle may be in flight anywhere), then the next solve starts from a clean protocol state.
+int fk_comm_reset(fk_handle h) {
+  try {
+    if (!h) throw std::runtime_error("fk: NULL handle");
+    Comm* c = h->comm;
+    if (!c || !c->p2p.on) return 0;
+    FK_CUDA(cudaSetDevice(h->device));
+    FK_CUDA(cudaDeviceSynchronize());
+    unsigned long long lim = 0;
+    FK_CUDA(cudaMemcpy(&lim, c->p2p.ctrl + kOffLimit, sizeof(lim), cudaMemcpyDeviceToHost));
+    FK_CUDA(cudaMemset(c->p2p.ctrl, 0, kCtrlWords * sizeof(unsigned long long)));
+    FK_CUDA(cudaMemcpy(c->p2p.ctrl + kOffLimit, &lim, sizeof(lim), cudaMemcpyHostToDevice));
+    FK_CUDA(cudaMemset(h->tickets.ptr, 0, 8 * sizeof(unsigned int)));
+    invalidate_graphs(h);
+    return 0;
+  } catch (const std::exception& e) {
+    set_error(e.what());
+    return 1;
+  }
+}
+// peer wait limit in milliseconds (0 = default, about 2 s): how long a kernel spins on a peer's flag before it gives up
+int fk_comm_set_timeout(fk_handle h, int ms) {
+  try {
+    if (!h || ms < 0) throw std::runtime_error("fk_comm_set_timeout: bad argument");
+    Comm* c = h->comm;
+    if (!c || !c->p2p.on) throw std::runtime_error("fk_comm_set_timeout: the handle is not on the peer-memory path");
+    FK_CUDA(cudaSetDevice(h->device));
+    int khz = 1900000;
+    cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, h->device);
+    const unsigned long long ticks = (unsigned long long)ms * (unsigned long long)khz;
+    FK_CUDA(cudaMemcpy(c->p2p.ctrl + kOffLimit, &ticks, sizeof(ticks), cudaMemcpyHostToDevice));
+    return 0;
+  } catch (const std::exception& e) {
+    set_error(e.what());
+    return 1;
+  }
+}
+
 int fk_comm_mode(fk_handle h, int* mode) {  // 0 = single GPU, 1 = NCCL, 2 = peer memory
   if (!h || !mode) return 1;
   *mode = !h->comm ? 0 : (h->comm->p2p.on ? 2 : 1);

@@ -125,8 +125,13 @@ constexpr int kOffMail2 = kOffHaloCnt + 1;
 constexpr int kOffHalo2 = kOffMail2 + 2 * kMaxRanks * kMail2Words;
 constexpr int kMail3Words = 8;   // 4 values x 2 LL words
 constexpr int kOffMail3 = kOffHalo2 + kMaxNeigh;
+constexpr int kOffLimit = kOffMail3 + 4 * kMaxRanks * kMail3Words;   // spin limit in clock64 ticks (0 = default, ~2 s): fk_tune 16
 constexpr int kCtrlWords = 512;
-static_assert(kOffMail3 + 4 * kMaxRanks * kMail3Words <= kCtrlWords, "control block too small");
+static_assert(kOffLimit + 1 <= kCtrlWords, "control block too small");
+__device__ __forceinline__ long long spin_limit(const unsigned long long* err) {   // err = ctrl + kOffErr
+  const unsigned long long v = err[kOffLimit - kOffErr];
+  return v ? (long long)v : 4000000000LL;
+}
 constexpr int kSlabVecs = 8;       // x | r | p | Ap (w) | dinv | s | z | potential staging -- then the control block
 
 __device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
@@ -147,10 +152,10 @@ __device__ __forceinline__ void fence_acq_rel_sys() { asm volatile("fence.acq_re
 // then cost an L2 read each instead of an acquire).  Not a fence: under the load of a running SpMV a system-scope
 // fence (MEMBAR.SYS drains the SM's outstanding writes) was measured at ~8 us per waiting warp (fk_tune 11 timeline).
 __device__ __forceinline__ bool spin_until_relaxed(const unsigned long long* flag, unsigned long long seq, unsigned long long* err) {
-  const long long t0 = clock64();
+  const long long t0 = clock64(), lim = spin_limit(err);
   bool ok = true;
   while (ld_relaxed_sys(flag) < seq) {
-    if (clock64() - t0 > 4000000000LL) {
+    if (clock64() - t0 > lim) {
       *err = 1ULL;
       ok = false;
       break;
@@ -161,9 +166,9 @@ __device__ __forceinline__ bool spin_until_relaxed(const unsigned long long* fla
 }
 // spin until *flag >= seq; gives up after ~2 s (a lost peer must not hang the GPU) and records the failure
 __device__ __forceinline__ bool spin_until(const unsigned long long* flag, unsigned long long seq, unsigned long long* err) {
-  const long long t0 = clock64();
+  const long long t0 = clock64(), lim = spin_limit(err);
   while (ld_acquire_sys(flag) < seq) {
-    if (clock64() - t0 > 4000000000LL) {
+    if (clock64() - t0 > lim) {
       *err = 1ULL;
       return false;
     }
@@ -275,13 +280,13 @@ __device__ __forceinline__ void ll_send(unsigned long long* box, const double v,
   st_relaxed_sys(box + 1, (b & 0xffffffff00000000ULL) | (unsigned long long)tag);
 }
 __device__ __forceinline__ double ll_recv(const unsigned long long* box, const unsigned tag, unsigned long long* err) {
-  const long long t0 = clock64();
+  const long long t0 = clock64(), lim = spin_limit(err);
   unsigned long long w0, w1;
   while (true) {
     w0 = ld_relaxed_sys(box);
     w1 = ld_relaxed_sys(box + 1);
     if ((unsigned)w0 == tag && (unsigned)w1 == tag) break;
-    if (clock64() - t0 > 4000000000LL) { *err = 1ULL; break; }   // a lost peer must not hang the GPU
+    if (clock64() - t0 > lim) { *err = 1ULL; break; }   // a lost peer must not hang the GPU
   }
   return __longlong_as_double((long long)((w0 >> 32) | (w1 & 0xffffffff00000000ULL)));
 }

@@ -75,7 +75,10 @@ static __device__ __forceinline__ double sell_slice_row16(const double* __restri
   return acc;
 }
 
-template <bool DOT, int G, int MINB>
+// COH: gather x through L2 only (the halo-coupled rows of the split exchange: their kernel runs beside the interior one,
+// whose CTAs may hold the 128-byte line that straddles the last owned and the first halo row in L1 from before the
+// peer's store landed -- the read-only path promises nothing for a line that is written during the kernel's lifetime)
+template <bool DOT, int G, int MINB, bool COH = false>
 static __global__ void __launch_bounds__(kSpmvThreads, MINB) spmv_sell_kernel(const int4* __restrict__ slice_meta, const int* __restrict__ srow,
                                                                   const unsigned short* __restrict__ colz,
                                                                   const double* __restrict__ vals, const double* __restrict__ x,
@@ -109,8 +112,8 @@ static __global__ void __launch_bounds__(kSpmvThreads, MINB) spmv_sell_kernel(co
     const int r = __ldg(srow + sl * kSellC + lane);
     const double* __restrict__ v = vals + m.x + lane;
     const unsigned short* __restrict__ cz = colz + (size_t)m.z * kSellC;
-    const double acc = m.w >= 0 ? sell_slice_row16<G>(v, reinterpret_cast<const uint2*>(cz) + lane, m.w, m.y, x)
-                                : sell_slice_row32<(G > 2 ? 2 : G)>(v, reinterpret_cast<const int*>(cz) + lane, m.y, x);
+    const double acc = m.w >= 0 ? sell_slice_row16<G, COH>(v, reinterpret_cast<const uint2*>(cz) + lane, m.w, m.y, x)
+                                : sell_slice_row32<(G > 2 ? 2 : G), COH>(v, reinterpret_cast<const int*>(cz) + lane, m.y, x);
     if (r >= 0) {
       y[r] = acc;
       if (DOT) dot += acc * x[r];

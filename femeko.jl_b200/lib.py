@@ -99,6 +99,8 @@ _SIGS = {
     "fk_multi_picard_step": (C.c_int, [_H, C.c_int, c_double_p, C.c_int, c_double_p]),
     "fk_assemble_stiffness2d": (C.c_int, [_H, C.c_int, c_double_p, c_double_p]),
     "fk_assemble_mass2d": (C.c_int, [_H, C.c_int, c_double_p, c_double_p]),
+    "fk_comm_set_timeout": (C.c_int, [_H, C.c_int]),
+    "fk_comm_reset": (C.c_int, [_H]),
     "fk_set_host_threads": (C.c_int, [C.c_int]),
     "fk_symbolic_rescale": (C.c_int, [_H, C.POINTER(C.c_longlong), c_int_p, C.POINTER(C.c_longlong), C.c_void_p, C.c_void_p, C.c_void_p,
                                       C.c_void_p]),

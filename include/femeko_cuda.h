@@ -319,6 +319,11 @@ int fk_set_halo(fk_handle h, int n_owned, int nneigh, const int* neigh_rank, con
 int fk_comm_p2p_export(fk_handle h, unsigned char* handles128);
 int fk_comm_p2p_attach(fk_handle h, const unsigned char* all_handles /* nranks x 128 */, const int* remote_start,
                        const int* remote_slot);
+/* peer-memory path: how long a kernel waits for a peer's flag before it gives up and the next host check reports "a peer
+ * GPU did not answer" (milliseconds; 0 = default, about 2 s -- raise it when a rank may stall on the host, e.g. under a
+ * debugger), and the way back from such an error: every rank calls fk_comm_reset between two barriers of the caller.  */
+int fk_comm_set_timeout(fk_handle h, int ms);
+int fk_comm_reset(fk_handle h);
 int fk_comm_mode(fk_handle h, int* mode);
 
 /* ---- legacy drop-in: ABI-identical to the reference (magnetostatics.cpp:49-60) --------------- */
