@@ -588,7 +588,7 @@ def run_ours(args):
             "roofline_assembly": {"kernel": sweep_name + " (device time of the enqueued sweep; its scalars return with the solve's poll)",
                                   "bound": "hbm", "achieved": round(asm_gbs, 1),
                                   "peak": peak, "unit": "GB/s", "frac": round(asm_gbs / peak, 4),
-                                  "traffic": traffic.get("picard_assembly_bytes"), "algorithmic_bytes_per_launch": asm_bytes,
+                                  "traffic": traffic.get("picard_assembly_bytes") if geo else None, "algorithmic_bytes_per_launch": asm_bytes,
                                   "avg_launch_ms": round(asm_ms, 5)},
             "clocks": P["clocks"],
         }

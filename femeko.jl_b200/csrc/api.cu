@@ -116,7 +116,7 @@ static void launch_assemble(fk_handle h, const AsmArgs& a, bool setup = false) {
 }
 
 static void ensure_geo(fk_handle h);
-static void launch_geo_rescale(fk_handle h, double* vals);
+static void launch_geo_rescale(fk_handle h, double* vals, int grid_cap = 0);
 static void assemble_stiffness_dev(fk_handle h, int slot, const double* f_dev) {
   h->dir_applied &= ~(1u << slot);
   double* vals = slot_vals(h, slot);
@@ -124,6 +124,7 @@ static void assemble_stiffness_dev(fk_handle h, int slot, const double* f_dev) {
     ensure_geo(h);
     geo_scale_kernel<<<cdiv(h->nt, 256), 256, 0, h->stream>>>(h->VE.ptr, f_dev, h->nt, h->geo_s0.ptr);
     h->launches++;
+    h->s0_dirty = true;   // the scales now belong to f, not to mu
     launch_geo_rescale(h, vals);
     return;
   }
@@ -191,10 +192,11 @@ static void ensure_geo(fk_handle h) {
   h->geo_ready = true;
 }
 // vals = sum_k s0[k] G_k on the plan's items (every stored entry is an item or the mirror of one)
-static void launch_geo_rescale(fk_handle h, double* vals) {
+static void launch_geo_rescale(fk_handle h, double* vals, int grid_cap) {
   if (h->geo_nslices == 0) return;
+  const int grid = grid_cap > 0 ? std::min(h->geo_grid, grid_cap) : h->geo_grid;
   geo_variant_dispatch(h->geo_variant, [&](auto B, auto MINB) {
-    geo_rescale_kernel<B(), MINB()><<<h->geo_grid, kGeoThreads, 0, h->stream>>>(h->geo_slice_ptr.ptr, h->geo_dst1.ptr, h->geo_dst2.ptr,
+    geo_rescale_kernel<B(), MINB()><<<grid, kGeoThreads, 0, h->stream>>>(h->geo_slice_ptr.ptr, h->geo_dst1.ptr, h->geo_dst2.ptr,
                                                                                h->geo_ref.ptr, h->geo_g.ptr, h->geo_s0.ptr,
                                                                                h->geo_nslices, vals);
   });
@@ -888,6 +890,9 @@ int fk_destroy(fk_handle h) {
     if (h->ev_fork) { cudaEventDestroy(h->ev_fork); h->ev_fork = nullptr; }
     if (h->ev_join) { cudaEventDestroy(h->ev_join); h->ev_join = nullptr; }
     if (h->halo_stream) { cudaStreamDestroy(h->halo_stream); h->halo_stream = nullptr; }   // comm_destroy below must not destroy it again
+    if (h->asm_fork) cudaEventDestroy(h->asm_fork);
+    if (h->asm_join) cudaEventDestroy(h->asm_join);
+    if (h->asm_stream) cudaStreamDestroy(h->asm_stream);
     if (h->copy_ev) cudaEventDestroy(h->copy_ev);
     if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
     // leave the device as the host application had it: the persisting lines are released when the last handle with a
@@ -967,6 +972,13 @@ int fk_tune(fk_handle h, int what, int value) {
         break;
       case 15:  // 1: give the assembly sweep the whole L2 (reset the persisting lines of the PCG vectors before it); default 0
         h->l2_reset_before_sweep = value != 0;
+        break;
+      case 17:  // rescale sweep: 0 (default) = element kernel then sums, one stream; otherwise 16 a + b = field recovery on b CTAs per
+                // SM beside the streamed sums on a CTAs per SM (measured behind a PCG solve: 0.62-0.75 ms against 0.63 in sequence,
+                // profiles/r2_asm_bench_side_by_side.jsonl -- the two kernels compete for the same miss queues, no gain)
+        need(value >= 0 && value < 256, "fk_tune: split out of range");
+        h->geo_overlap = value != 0;
+        if (value) { h->geo_split_resc = std::max(1, value >> 4); h->geo_split_elem = std::max(1, value & 15); }
         break;
       case 13:  // rescale plan: items are sorted by list length inside windows of this many items (32 = plan order kept); rebuilds
         need(value >= 32 && value <= (1 << 20), "fk_tune: geo window out of range");
@@ -1106,7 +1118,7 @@ int fk_device_ptr(fk_handle h, int which, void** ptr) {
       case 0: *ptr = h->rowptr.ptr; break;
       case 1: *ptr = h->colind.ptr; break;
       case 2: *ptr = h->VE.ptr; break;
-      case 3: *ptr = h->mu.ptr; break;
+      case 3: *ptr = h->mu.ptr; h->s0_dirty = true; break;   // the caller may write mu through this pointer
       case 4: *ptr = h->Hn.ptr; break;
       case 5: *ptr = h->Hfield.ptr; break;
       case 6: ensure_pcg(h); *ptr = h->u.ptr; break;
@@ -1756,6 +1768,7 @@ int fk_set_mu(fk_handle h, const double* mu) {
     DeviceGuard dg(h->device);
     ensure_state(h);
     FK_CUDA(cudaMemcpyAsync(h->mu.ptr, mu, sizeof(double) * (size_t)h->nt, cudaMemcpyHostToDevice, h->stream));
+    h->s0_dirty = true;
     FK_CUDA(cudaStreamSynchronize(h->stream));
     return 0;
   });
@@ -1830,6 +1843,18 @@ static int picard_step_dev(fk_handle h, int slot, const double* u_dev, int compa
   int* errflag = reinterpret_cast<int*>(h->scal.ptr + 7);   // rides in the scalar block: one copy brings back both
   FK_CUDA(cudaMemsetAsync(errflag, 0, sizeof(double), h->stream));
   const bool have_mat = h->have_material && h->n_mat > 0;
+  // A handle that sweeps repeatedly (a Picard loop) switches to the rescale path (rescale.cuh): same bits, streamed
+  // instead of recomputed.
+  h->geo_sweeps++;
+  const bool geo = h->geo_mode == 2 || (h->geo_mode == 1 && (h->geo_ready || h->geo_sweeps >= 2));
+  if (geo) ensure_geo(h);
+  const bool side = geo && h->geo_overlap;   // field recovery beside the streamed sums (needs the scales kept current)
+  if (side && h->s0_dirty) {   // mu may have changed behind the handle's back (fk_set_mu, a tile sweep, the device pointer)
+    geo_scale_kernel<<<cdiv(h->nt, 256), 256, 0, h->stream>>>(h->VE.ptr, h->mu.ptr, h->nt, h->geo_s0.ptr);
+    h->launches++;
+    h->s0_dirty = false;
+  }
+  if (!side) h->s0_dirty = true;
   // 1. material elements: mu(|H|), dmu/dH from the spline and the convergence metric (per-CTA maxima)
   int npart = 1;
   if (have_mat) {
@@ -1840,28 +1865,44 @@ static int picard_step_dev(fk_handle h, int slot, const double* u_dev, int compa
     h->tile_max.ensure((size_t)npart);
     material_update_kernel<<<npart, 256, 0, h->stream>>>(h->p4.ptr, h->t4.ptr, h->mat_list.ptr, h->n_mat,
                                                         h->matid.ptr, a.u, h->spl, compat_bug, h->Hn.ptr, h->mu.ptr, h->dmu.ptr,
-                                                        h->tile_max.ptr, errflag);
+                                                        h->tile_max.ptr, errflag, h->VE.ptr, side ? h->geo_s0.ptr : nullptr);
     FK_CUDA(cudaGetLastError());
     h->launches++;
   } else {
     FK_CUDA(cudaMemsetAsync(h->tile_max.ptr, 0, sizeof(double), h->stream));
   }
-  // 2. the sweep: stiffness with the refreshed mu + H, |H| of every element.  A handle that sweeps repeatedly (a Picard
-  //    loop) switches to the rescale path (rescale.cuh): same bits, streamed instead of recomputed.
-  h->geo_sweeps++;
-  if (h->l2_reset_before_sweep && h->l2_window_set) cudaCtxResetPersistingL2Cache();
-  if (h->geo_mode == 2 || (h->geo_mode == 1 && (h->geo_ready || h->geo_sweeps >= 2))) {
-    ensure_geo(h);
+  // 2. the sweep: stiffness with the refreshed mu + H, |H| of every element
+  if (geo) {
     if (h->elem_grid == 0) {
       int occ = 1;
-      FK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, picard_element_kernel, kElemThreads, 0));
+      FK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, picard_element_kernel<true>, kElemThreads, 0));
       h->elem_grid = h->num_sms * std::max(1, occ);
     }
-    picard_element_kernel<<<std::min(cdiv(h->nt, kElemThreads), h->elem_grid), kElemThreads, 0, h->stream>>>(h->p4.ptr, h->t4.ptr, a.u, h->mu.ptr, a.VE, h->nt,
-                                                                                   compat_bug, h->Hn.ptr, h->Hfield.ptr, h->geo_s0.ptr);
-    FK_CUDA(cudaGetLastError());
-    h->launches++;
-    launch_geo_rescale(h, a.vals);
+    if (side) {
+      // the two streaming kernels of the sweep are independent: run them side by side, each on part of the CTA slots, so
+      // that the memory system always has both their request streams queued (each alone is latency-bound at 50-60 % of HBM)
+      if (!h->asm_stream) {
+        FK_CUDA(cudaStreamCreateWithFlags(&h->asm_stream, cudaStreamNonBlocking));
+        FK_CUDA(cudaEventCreateWithFlags(&h->asm_fork, cudaEventDisableTiming));
+        FK_CUDA(cudaEventCreateWithFlags(&h->asm_join, cudaEventDisableTiming));
+      }
+      FK_CUDA(cudaEventRecord(h->asm_fork, h->stream));
+      FK_CUDA(cudaStreamWaitEvent(h->asm_stream, h->asm_fork, 0));
+      const int ge = std::min(cdiv(h->nt, kElemThreads), h->num_sms * h->geo_split_elem);
+      picard_element_kernel<false><<<ge, kElemThreads, 0, h->asm_stream>>>(h->p4.ptr, h->t4.ptr, a.u, nullptr, nullptr, h->nt, compat_bug,
+                                                                           h->Hn.ptr, h->Hfield.ptr, nullptr);
+      FK_CUDA(cudaGetLastError());
+      FK_CUDA(cudaEventRecord(h->asm_join, h->asm_stream));
+      h->launches++;
+      launch_geo_rescale(h, a.vals, h->num_sms * h->geo_split_resc);
+      FK_CUDA(cudaStreamWaitEvent(h->stream, h->asm_join, 0));
+    } else {
+      picard_element_kernel<true><<<std::min(cdiv(h->nt, kElemThreads), h->elem_grid), kElemThreads, 0, h->stream>>>(
+          h->p4.ptr, h->t4.ptr, a.u, h->mu.ptr, a.VE, h->nt, compat_bug, h->Hn.ptr, h->Hfield.ptr, h->geo_s0.ptr);
+      FK_CUDA(cudaGetLastError());
+      h->launches++;
+      launch_geo_rescale(h, a.vals);
+    }
   } else {
     launch_assemble<ASM_PICARD>(h, a);
   }

@@ -471,7 +471,8 @@ static __global__ void __launch_bounds__(256) material_update_kernel(const doubl
                                                               const double* __restrict__ u, const SplineSet spl, int compat,
                                                               const double* __restrict__ Hn_old, double* __restrict__ mu,
                                                               double* __restrict__ dmu, double* __restrict__ part_max,
-                                                              int* __restrict__ errflag) {
+                                                              int* __restrict__ errflag, const double* __restrict__ VE = nullptr,
+                                                              double* __restrict__ s0 = nullptr) {
   __shared__ double red[33];
   double dmax = 0.0;
   int err = 0;
@@ -496,6 +497,7 @@ static __global__ void __launch_bounds__(256) material_update_kernel(const doubl
     dmax = fmax(dmax, fabs(Hn - Hn_old[k]));
     mu[k] = f;
     if (dmu) dmu[k] = df;
+    if (s0) s0[k] = __dmul_rn(VE ? VE[k] : G.vol, f);   // rescale path: the element scale follows its mu (rescale.cuh)
   }
   if (err) atomicOr(errflag, err);
   dmax = block_max(dmax, red);

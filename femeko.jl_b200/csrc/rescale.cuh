@@ -60,6 +60,9 @@ constexpr int kElemThreads = 256;
 // Persistent grid (fk: picard_step_dev launches one wave of resident CTAs): the connectivity and the coefficient of the
 // chunk a CTA will work on NEXT are requested before the gathers of the current one, so the two dependent memory
 // round trips of an element (connectivity -> node / potential gathers) overlap across chunks.
+// S0 = false: field recovery only -- the scales are kept current by geo_scale_kernel / material_update_kernel, so this
+// kernel and geo_rescale_kernel are independent and run side by side on two streams (api.cu: picard_step_dev).
+template <bool S0>
 static __global__ void __launch_bounds__(kElemThreads) picard_element_kernel(const double4* __restrict__ p4, const int4* __restrict__ t4,
                                                                              const double* __restrict__ u, const double* __restrict__ mu,
                                                                              const double* __restrict__ VE, int nt, int compat,
@@ -71,12 +74,12 @@ static __global__ void __launch_bounds__(kElemThreads) picard_element_kernel(con
   long long k = (long long)blockIdx.x * kElemThreads + threadIdx.x;
   int4 nd = make_int4(0, 0, 0, 0);
   double f = 0.0, V = 0.0;
-  if (k < nt) { nd = __ldg(t4 + k); f = __ldcs(mu + k); if (VE) V = __ldcs(VE + k); }
+  if (k < nt) { nd = __ldg(t4 + k); if (S0) { f = __ldcs(mu + k); if (VE) V = __ldcs(VE + k); } }
   for (long long k0 = (long long)blockIdx.x * kElemThreads; k0 < nt; k0 += stride, k += stride) {
     const long long kn = k + stride;
     int4 ndn = make_int4(0, 0, 0, 0);
     double fn = 0.0, Vn = 0.0;
-    if (kn < nt) { ndn = __ldg(t4 + kn); fn = __ldcs(mu + kn); if (VE) Vn = __ldcs(VE + kn); }
+    if (kn < nt) { ndn = __ldg(t4 + kn); if (S0) { fn = __ldcs(mu + kn); if (VE) Vn = __ldcs(VE + kn); } }
     double hx = 0.0, hy = 0.0, hz = 0.0;
     if (k < nt) {
       const double u0 = __ldg(u + nd.x), u1 = __ldg(u + nd.y), u2 = __ldg(u + nd.z), u3 = __ldg(u + nd.w);
@@ -87,7 +90,7 @@ static __global__ void __launch_bounds__(kElemThreads) picard_element_kernel(con
       hz = -(u0 * G.g[0][2]) - u1 * G.g[1][2] - u2 * G.g[2][2] - u3 * G.g[3][2];
       if (compat) { hy += hz; hz = 0.0; }  // NewtonRaphson.jl:187-189: d-term lands in row 2
       __stcs(Hn + k, norm3(hx, hy, hz));
-      s0[k] = __dmul_rn(VE ? V : G.vol, f);
+      if (S0) s0[k] = __dmul_rn(VE ? V : G.vol, f);
     }
     if (Hfield) {
       double* w = hs[wib];

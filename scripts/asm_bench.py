@@ -86,17 +86,15 @@ for persist in ([1] if short else [1, 0]):
         ts.append(e0.elapsed_time(e1))
     ts.sort()
     report(f"picard_sweep_rescale_after_pcg_l2persist{persist}", (ts[len(ts) // 2], ts[0]), picard_bytes)
-# what precedes the sweep: (a) an idle GPU (sync, 2 ms of host sleep), (b) a busy one (a 60 us fill kernel, no sync)
-import time as _t
+# the two streaming kernels of the sweep side by side (fk_tune 17 = 16 a + b: sums on a CTAs per SM, field recovery on b), timed
+# behind a PCG solve like the bench step
 h.tune(2, 1)
-small = torch.empty(32 << 20, dtype=torch.uint8, device="cuda")
-for name, pre in (("idle_2ms", lambda: (torch.cuda.synchronize(), _t.sleep(0.002))), ("idle_sync_only", lambda: torch.cuda.synchronize()),
-                  ("busy_small_fill", lambda: small.zero_()), ("busy_pcg_nosync", None)):
+for split in ([0x32] if short else [0, 0x32, 0x41, 0x22, 0x31, 0x42, 0x23, 0x33]):
+    h.tune(17, split)
+    sweep(); h.synchronize()
     ts = []
     for _ in range(r):
-        torch.cuda.synchronize()
-        if pre is not None:
-            pre()
+        h.pcg_dev(b.data_ptr(), x.data_ptr(), slot=1, max_iter=20, tol_disable=True, check_every=20)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         sweep()
@@ -104,6 +102,7 @@ for name, pre in (("idle_2ms", lambda: (torch.cuda.synchronize(), _t.sleep(0.002
         torch.cuda.synchronize()
         ts.append(e0.elapsed_time(e1))
     ts.sort()
-    report(f"picard_sweep_rescale_{name}", (ts[len(ts) // 2], ts[0]), picard_bytes)
+    report(f"picard_sweep_rescale_after_pcg_split{split >> 4}_{split & 15}", (ts[len(ts) // 2], ts[0]), picard_bytes)
+h.tune(17, 0x32)
 h.picard_result()
 h.close()
