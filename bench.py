@@ -1099,7 +1099,7 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--n", type=int, default=119, help="Kuhn cells per edge per GPU (119 = configs[1], 10.1 M tets)")
+    ap.add_argument("--n", "--cells", dest="n", type=int, default=119, help="Kuhn cells per edge per GPU (119 = configs[1], 10.1 M tets)")
     ap.add_argument("--pcg-iters", type=int, default=100)
     ap.add_argument("--cpu-n", type=int, default=48, help="Kuhn cells per edge of the bounded CPU sample")
     ap.add_argument("--cpu-budget", type=float, default=20.0)

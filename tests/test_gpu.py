@@ -144,6 +144,17 @@ def test_scalar_potential_dropin(name):
     b = -g["boundary_integral"]
     assert np.linalg.norm(b - A @ u) / np.linalg.norm(b) < 1e-6
     assert rel_l2(u - u.mean(), ref - ref.mean()) < 1e-6
+    # round 2: the drop-in projects the constant mode out of the residual (fk_pcg_opts.project_nullspace = 2), so the
+    # recursion no longer wanders: against a direct solve of the reference's own matrix (one node grounded, means
+    # removed) the potential holds the north star's 1e-8, and the true residual of the consistent system is tiny
+    import scipy.sparse.linalg as spla
+    bc = b - b.mean()
+    xd = np.zeros(m.nv)
+    xd[1:] = spla.spsolve(A.tocsc()[1:, 1:], bc[1:])
+    print(f"scalarPotential {name}: rel-L2 vs direct solve {rel_l2(u - u.mean(), xd - xd.mean()):.2e}, "
+          f"true residual {np.linalg.norm(bc - A @ u) / np.linalg.norm(bc):.2e}")
+    assert rel_l2(u - u.mean(), xd - xd.mean()) < 1e-8
+    assert np.linalg.norm(bc - A @ u) / np.linalg.norm(bc) < 1e-9
     # same matrix, same right-hand side, the golden's tolerance: iteration count and potential of Eigen itself
     h = fk.Femeko(m)
     h.assemble_stiffness(g["mu"], want_vals=False)
