@@ -97,6 +97,7 @@ static void launch_assemble_cfg(fk_handle h, const AsmArgs& a, bool setup) {
 }
 template <int MODE>
 static void launch_assemble(fk_handle h, const AsmArgs& a, bool setup = false) {
+  if (!setup) need(h->sym.npe == 4, "fk: this entry point assembles 4-node elements; the handle holds P2 elements (use fk_assemble_*_p2)");
   if (h->sym.ntiles == 0) return;
   // 0 = measured default: {256, 2} for every mode (two CTAs per SM is what shared memory allows; the 128-register
   // budget keeps phase 1 free of spills)
@@ -116,7 +117,7 @@ static void launch_assemble(fk_handle h, const AsmArgs& a, bool setup = false) {
 }
 
 static void ensure_geo(fk_handle h);
-static void launch_geo_rescale(fk_handle h, double* vals, int grid_cap = 0);
+static void launch_geo_rescale(fk_handle h, double* vals, int grid_cap = 0, const double* g = nullptr);
 static void assemble_stiffness_dev(fk_handle h, int slot, const double* f_dev) {
   h->dir_applied &= ~(1u << slot);
   double* vals = slot_vals(h, slot);
@@ -168,6 +169,7 @@ static void configure_geo(fk_handle h) {
 // the one-off part: plan on the host (symbolic.cpp: build_rescale_plan), factors on the device
 static void ensure_geo(fk_handle h) {
   if (h->geo_ready) return;
+  need(h->sym.npe == 4, "fk: the rescale path of P1 elements was asked for on a P2 handle");
   RescalePlan R;
   build_rescale_plan(h->sym, h->geo_window, R);
   cudaStream_t s = h->stream;
@@ -192,12 +194,13 @@ static void ensure_geo(fk_handle h) {
   h->geo_ready = true;
 }
 // vals = sum_k s0[k] G_k on the plan's items (every stored entry is an item or the mirror of one)
-static void launch_geo_rescale(fk_handle h, double* vals, int grid_cap) {
+static void launch_geo_rescale(fk_handle h, double* vals, int grid_cap, const double* g) {
   if (h->geo_nslices == 0) return;
+  if (!g) g = h->geo_g.ptr;
   const int grid = grid_cap > 0 ? std::min(h->geo_grid, grid_cap) : h->geo_grid;
   geo_variant_dispatch(h->geo_variant, [&](auto B, auto MINB) {
     geo_rescale_kernel<B(), MINB()><<<grid, kGeoThreads, 0, h->stream>>>(h->geo_slice_ptr.ptr, h->geo_dst1.ptr, h->geo_dst2.ptr,
-                                                                               h->geo_ref.ptr, h->geo_g.ptr, h->geo_s0.ptr,
+                                                                               h->geo_ref.ptr, g, h->geo_s0.ptr,
                                                                                h->geo_nslices, vals);
   });
   FK_CUDA(cudaGetLastError());
@@ -751,6 +754,7 @@ static SymbolicOpts to_symbolic_opts(const fk_create_opts& o) {
   if (o.sell_sigma > 0) so.sell_sigma = o.sell_sigma;
   if (o.n_owned > 0) so.n_owned = o.n_owned;
   so.wide_cols = o.sell_wide_cols != 0;
+  if (o.nodes_per_element != 0) so.npe = o.nodes_per_element;
   return so;
 }
 
@@ -761,6 +765,8 @@ static void copy_vec(const std::vector<T>& v, U* dst) {
 }
 
 extern "C" {
+
+static void ensure_p2(fk_handle h);   // P2 contribution plan (defined with the P2 entry points below)
 
 const char* fk_last_error(void) { return fk::g_err.c_str(); }
 int fk_set_host_threads(int n) {
@@ -809,7 +815,17 @@ int fk_create(const double* p, const int* t, int nv, int nt, const double* VE, c
     h->p4.ensure((size_t)nv);
     pad_nodes_kernel<<<cdiv(nv, 256), 256, 0, s>>>(h->st_a.ptr, nv, h->p4.ptr);
     h->t4.ensure((size_t)nt);
-    FK_CUDA(cudaMemcpyAsync(h->t4.ptr, t, sizeof(int) * 4 * (size_t)nt, cudaMemcpyHostToDevice, s));
+    std::vector<int> t4host;   // P2: the vertices of every element (first four of ten) for the geometry kernels
+    if (S.npe == 4) {
+      FK_CUDA(cudaMemcpyAsync(h->t4.ptr, t, sizeof(int) * 4 * (size_t)nt, cudaMemcpyHostToDevice, s));
+    } else {
+      t4host.resize(4 * (size_t)nt);
+      for (int k = 0; k < nt; k++)
+        for (int i = 0; i < 4; i++) t4host[4 * (size_t)k + i] = t[(size_t)S.npe * k + i];
+      FK_CUDA(cudaMemcpyAsync(h->t4.ptr, t4host.data(), sizeof(int) * 4 * (size_t)nt, cudaMemcpyHostToDevice, s));
+      h->tP2.upload(t, (size_t)S.npe * nt, s);
+      FK_CUDA(cudaStreamSynchronize(s));
+    }
     h->VE.ensure((size_t)nt);
     if (VE) {
       h->user_ve = true;
@@ -1060,7 +1076,7 @@ int fk_csr_pattern(fk_handle h, int* rowptr, int* colind) {
 int fk_elem2nnz(fk_handle h, int* map) {
   return guard([&]() {
     need(h && map, "fk: NULL argument");
-    std::memcpy(map, h->sym.e2nnz.data(), sizeof(int) * 16 * (size_t)h->nt);
+    std::memcpy(map, h->sym.e2nnz.data(), sizeof(int) * h->sym.e2nnz.size());   // 16 nt (P1) or 100 nt (P2) entries
     return 0;
   });
 }
@@ -1079,7 +1095,7 @@ int fk_geo_stats(fk_handle h, long long* items, long long* contributions, long l
   return guard([&]() {
     need(h, "fk: NULL handle");
     DeviceGuard dg(h->device);
-    ensure_geo(h);
+    if (h->sym.npe == 10) ensure_p2(h); else ensure_geo(h);
     if (items) *items = h->geo_items;
     if (contributions) *contributions = h->geo_contrib;
     if (slots) *slots = h->geo_slots;
@@ -1285,6 +1301,85 @@ int fk_assemble_tangential(fk_handle h, int slot, const double* Hfield, const do
     return 0;
   });
 }
+// ---- P2 tetrahedra (p2.cuh) ---------------------------------------------------------------------------
+// sum_q w_q phi_i phi_j on the reference element, 15-point rule of GaussQuadrature3D(4) (src/FEM3D.jl:711-745)
+static P2Ref p2_reference_mass() {
+  static const double pts[15][3] = {
+      {0.2500000000000000, 0.2500000000000000, 0.2500000000000000}, {0.0000000000000000, 0.3333333333333333, 0.3333333333333333},
+      {0.3333333333333333, 0.3333333333333333, 0.3333333333333333}, {0.3333333333333333, 0.3333333333333333, 0.0000000000000000},
+      {0.3333333333333333, 0.0000000000000000, 0.3333333333333333}, {0.7272727272727273, 0.0909090909090909, 0.0909090909090909},
+      {0.0909090909090909, 0.0909090909090909, 0.0909090909090909}, {0.0909090909090909, 0.0909090909090909, 0.7272727272727273},
+      {0.0909090909090909, 0.7272727272727273, 0.0909090909090909}, {0.4334498464263357, 0.0665501535736643, 0.0665501535736643},
+      {0.0665501535736643, 0.4334498464263357, 0.0665501535736643}, {0.0665501535736643, 0.0665501535736643, 0.4334498464263357},
+      {0.0665501535736643, 0.4334498464263357, 0.4334498464263357}, {0.4334498464263357, 0.0665501535736643, 0.4334498464263357},
+      {0.4334498464263357, 0.4334498464263357, 0.0665501535736643}};
+  static const double wts[15] = {0.1817020685825351, 0.0361607142857143, 0.0361607142857143, 0.0361607142857143, 0.0361607142857143,
+                                 0.0698714945161738, 0.0698714945161738, 0.0698714945161738, 0.0698714945161738, 0.0656948493683187,
+                                 0.0656948493683187, 0.0656948493683187, 0.0656948493683187, 0.0656948493683187, 0.0656948493683187};
+  static const int ea[6] = {0, 1, 0, 0, 2, 1}, eb[6] = {1, 2, 2, 3, 3, 3};
+  P2Ref R{};
+  for (int q = 0; q < 15; q++) {
+    const double l[4] = {1.0 - pts[q][0] - pts[q][1] - pts[q][2], pts[q][0], pts[q][1], pts[q][2]};
+    double phi[10];
+    for (int v = 0; v < 4; v++) phi[v] = l[v] * (2.0 * l[v] - 1.0);
+    for (int e = 0; e < 6; e++) phi[4 + e] = 4.0 * l[ea[e]] * l[eb[e]];
+    const double w = wts[q] / 6.0;
+    int n = 0;
+    for (int i = 0; i < 10; i++)
+      for (int j = i; j < 10; j++) R.m[n++] += w * phi[i] * phi[j];
+  }
+  return R;
+}
+static void ensure_p2(fk_handle h) {
+  if (h->geo_ready) return;
+  need(h->sym.npe == 10, "fk: the handle does not hold P2 elements (fk_create_opts.nodes_per_element = 10)");
+  RescalePlan R;
+  build_rescale_plan(h->sym, h->geo_window, R);
+  cudaStream_t s = h->stream;
+  h->geo_nslices = R.nslices;
+  h->geo_slots = R.n_slots;
+  h->geo_items = R.n_items;
+  h->geo_contrib = R.n_contrib;
+  h->geo_slice_ptr.upload(R.slice_ptr, s);
+  h->geo_dst1.upload(R.dst1, s);
+  h->geo_dst2.upload(R.dst2, s);
+  h->geo_ref.upload(R.cref, s);
+  h->geo_g.ensure((size_t)std::max<long long>(R.n_slots, 1));
+  h->p2_gmass.ensure((size_t)std::max<long long>(R.n_slots, 1));
+  h->geo_s0.ensure((size_t)h->nt);
+  if (R.n_slots > 0) {
+    p2_geo_build_kernel<<<std::min(cdiv(R.n_slots, 128), h->num_sms * 16), 128, 0, s>>>(h->p4.ptr, h->tP2.ptr, h->VE.ptr, h->geo_ref.ptr,
+                                                                                        R.n_slots, R.pair_shift, p2_reference_mass(),
+                                                                                        h->geo_g.ptr, h->p2_gmass.ptr);
+    FK_CUDA(cudaGetLastError());
+    h->launches++;
+  }
+  FK_CUDA(cudaStreamSynchronize(s));
+  configure_geo(h);
+  h->geo_ready = true;
+}
+static int assemble_p2(fk_handle h, int slot, const double* coef, double* vals_out, bool mass) {
+  need(h, "fk: NULL handle");
+  DeviceGuard dg(h->device);
+  check_slot(slot);
+  ensure_p2(h);
+  const double* cd = nullptr;
+  if (coef) { h->st_a.upload(coef, (size_t)h->nt, h->stream); cd = h->st_a.ptr; }
+  h->dir_applied &= ~(1u << slot);
+  double* vals = slot_vals(h, slot);
+  p2_scale_kernel<<<cdiv(h->nt, 256), 256, 0, h->stream>>>(cd, h->nt, h->geo_s0.ptr);
+  h->launches++;
+  launch_geo_rescale(h, vals, 0, mass ? h->p2_gmass.ptr : h->geo_g.ptr);
+  copy_out_matrix(h, vals, vals_out);
+  return 0;
+}
+int fk_assemble_stiffness_p2(fk_handle h, int slot, const double* mu, double* vals_out) {
+  return guard([&]() { return assemble_p2(h, slot, mu, vals_out, false); });
+}
+int fk_assemble_mass_p2(fk_handle h, int slot, const double* F, double* vals_out) {
+  return guard([&]() { return assemble_p2(h, slot, F, vals_out, true); });
+}
+
 // 2-D P1 triangles (src/FEM2D.jl:48-76 stiffnessMatrix2D, :139-161 massMatrix2D) on a handle created from the elements
 // (n0, n1, n2, n2): same plan, same kernels, 3 x 3 local matrices
 int fk_assemble_stiffness2d(fk_handle h, int slot, const double* f, double* vals_out) {

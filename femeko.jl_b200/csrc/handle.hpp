@@ -155,6 +155,8 @@ struct fk_handle_s {
   fk::DevBuf<double> geo_g, geo_s0;
   fk::DevBuf<uint32_t> geo_ref, geo_slice_ptr;
   fk::DevBuf<int> geo_dst1, geo_dst2;
+  fk::DevBuf<int> tP2;                 // P2 handles: the 10-node connectivity (t4 holds the vertices)
+  fk::DevBuf<double> p2_gmass;         // P2: mass factors per contribution slot (geo_g holds the stiffness factors)
   // fk_tune(h, 11, n): device-side timeline of the PCG kernels (kernels.cuh: trace_rec)
   fk::DevBuf<unsigned long long> trace;
   int trace_cap = 0;

@@ -31,7 +31,10 @@ static inline uint64_t spread21(uint64_t v) {
 void build_symbolic(const double* p, const int* t, int nv, int nt, const SymbolicOpts& o, Symbolic& S) {
   if (nv <= 0 || nt <= 0) throw std::runtime_error("fk: empty mesh (nv and nt must be positive)");
   if (o.tile_max_elems < 1 || o.tile_max_elems > 4096) throw std::runtime_error("fk: tile_max_elems must be in [1, 4096]");
-  if ((int64_t)nt * 4 >= (int64_t)1 << 32) throw std::runtime_error("fk: nt too large for 32-bit incidence ids");
+  const int npe = o.npe;
+  if (npe != 4 && npe != 10) throw std::runtime_error("fk: nodes per element must be 4 (P1) or 10 (P2)");
+  if ((int64_t)nt * npe >= (int64_t)1 << 32) throw std::runtime_error("fk: nt too large for 32-bit incidence ids");
+  S.npe = npe;
   S.nv = nv;
   S.nt = nt;
   S.n_rows = (o.n_owned < 0 || o.n_owned > nv) ? nv : o.n_owned;
@@ -39,16 +42,16 @@ void build_symbolic(const double* p, const int* t, int nv, int nt, const Symboli
 
   // ---- node -> element incidences, ascending element order (counting sort) ------------------
   std::vector<int64_t> n2e_ptr((size_t)nv + 1, 0);
-  for (int64_t q = 0; q < (int64_t)4 * nt; q++) {
+  for (int64_t q = 0; q < (int64_t)npe * nt; q++) {
     int n = t[q];
     if (n < 0 || n >= nv) throw std::runtime_error("fk: connectivity entry out of range (expected 0-based ids < nv)");
     n2e_ptr[(size_t)n + 1]++;
   }
   for (int r = 0; r < nv; r++) n2e_ptr[r + 1] += n2e_ptr[r];
-  std::vector<uint32_t> n2e((size_t)4 * nt);
+  std::vector<uint32_t> n2e((size_t)npe * nt);
   {
     std::vector<int64_t> fill(n2e_ptr.begin(), n2e_ptr.end() - 1);
-    for (int64_t q = 0; q < (int64_t)4 * nt; q++) n2e[(size_t)fill[t[q]]++] = (uint32_t)q;  // q = 4k + i
+    for (int64_t q = 0; q < (int64_t)npe * nt; q++) n2e[(size_t)fill[t[q]]++] = (uint32_t)q;  // q = npe k + i
   }
 
   // ---- row pattern: sorted unique nodes of all incident elements ----------------------------
@@ -61,8 +64,8 @@ void build_symbolic(const double* p, const int* t, int nv, int nt, const Symboli
     for (int r = 0; r < nr; r++) {
       buf.clear();
       for (int64_t q = n2e_ptr[r]; q < n2e_ptr[r + 1]; q++) {
-        const int* e = t + 4 * (size_t)(n2e[q] >> 2);
-        buf.push_back(e[0]); buf.push_back(e[1]); buf.push_back(e[2]); buf.push_back(e[3]);
+        const int* e = t + (size_t)npe * (n2e[q] / (uint32_t)npe);
+        for (int i = 0; i < npe; i++) buf.push_back(e[i]);
       }
       std::sort(buf.begin(), buf.end());
       rowlen[r] = (int)(std::unique(buf.begin(), buf.end()) - buf.begin());
@@ -85,8 +88,8 @@ void build_symbolic(const double* p, const int* t, int nv, int nt, const Symboli
     for (int r = 0; r < nr; r++) {
       buf.clear();
       for (int64_t q = n2e_ptr[r]; q < n2e_ptr[r + 1]; q++) {
-        const int* e = t + 4 * (size_t)(n2e[q] >> 2);
-        buf.push_back(e[0]); buf.push_back(e[1]); buf.push_back(e[2]); buf.push_back(e[3]);
+        const int* e = t + (size_t)npe * (n2e[q] / (uint32_t)npe);
+        for (int i = 0; i < npe; i++) buf.push_back(e[i]);
       }
       std::sort(buf.begin(), buf.end());
       int m = (int)(std::unique(buf.begin(), buf.end()) - buf.begin());
@@ -99,22 +102,124 @@ void build_symbolic(const double* p, const int* t, int nv, int nt, const Symboli
   }
 
   // ---- element -> nnz map ---------------------------------------------------------------------
-  S.e2nnz.resize((size_t)16 * nt);
+  S.e2nnz.resize((size_t)npe * npe * nt);
 #pragma omp parallel for schedule(static)
   for (int k = 0; k < nt; k++) {
-    const int* e = t + 4 * (size_t)k;
-    for (int i = 0; i < 4; i++) {
+    const int* e = t + (size_t)npe * k;
+    for (int i = 0; i < npe; i++) {
       int r = e[i];
-      for (int j = 0; j < 4; j++) {
+      for (int j = 0; j < npe; j++) {
         int idx = -1;
         if (r < nr) {
           const int* b = S.colind.data() + S.rowptr[r];
           const int* en = S.colind.data() + S.rowptr[r + 1];
           idx = (int)(std::lower_bound(b, en, e[j]) - S.colind.data());
         }
-        S.e2nnz[(size_t)16 * k + 4 * i + j] = idx;
+        S.e2nnz[(size_t)npe * npe * k + npe * i + j] = idx;
       }
     }
+  }
+
+  // ---- SELL-32-sigma layout (see symbolic.hpp): independent of the assembly tiles, shared by every element type ------
+  auto build_sell = [&]() {
+    const int C = 32;
+    const int sigma = std::max(1, o.sell_sigma);
+    std::vector<int> ord((size_t)nr);
+    std::iota(ord.begin(), ord.end(), 0);
+    if (sigma > 1)
+      for (int w0 = 0; w0 < nr; w0 += sigma)
+        std::stable_sort(ord.begin() + w0, ord.begin() + std::min(nr, w0 + sigma), [&](int a, int b) { return rowlen[a] > rowlen[b]; });
+    S.nslices = (nr + C - 1) / C;
+    S.srow.assign((size_t)S.nslices * C, -1);
+    std::copy(ord.begin(), ord.end(), S.srow.begin());
+    S.slice_ptr.assign((size_t)S.nslices + 1, 0);
+    int64_t tot = 0;
+    for (int sl = 0; sl < S.nslices; sl++) {
+      int w = 0;
+      for (int l = 0; l < C; l++) {
+        const int r = S.srow[(size_t)sl * C + l];
+        if (r >= 0) w = std::max(w, rowlen[r]);
+      }
+      S.slice_ptr[sl] = (int)tot;
+      tot += (int64_t)w * C;
+      if (tot > 0x7fffffffLL) throw std::runtime_error("fk: more than 2^31-1 padded matrix entries on one GPU; partition the mesh");
+    }
+    S.slice_ptr[S.nslices] = (int)tot;
+    S.nnz_sell = tot;
+    S.sell_col.assign((size_t)tot, 0);
+    S.csr2sell.assign((size_t)S.nnz, -1);
+    S.sell_diag.assign((size_t)nr, -1);
+#pragma omp parallel for schedule(static)
+    for (int sl = 0; sl < S.nslices; sl++) {
+      const int base = S.slice_ptr[sl], w = (S.slice_ptr[sl + 1] - base) / C;
+      for (int l = 0; l < C; l++) {
+        const int r = S.srow[(size_t)sl * C + l];
+        const int len = r >= 0 ? rowlen[r] : 0;
+        for (int k = 0; k < w; k++) {
+          const int idx = base + k * C + l;
+          if (k < len) {
+            const int q = S.rowptr[r] + k;
+            S.sell_col[idx] = S.colind[q];
+            S.csr2sell[q] = idx;
+            if (S.colind[q] == r) S.sell_diag[r] = idx;
+          } else {
+            S.sell_col[idx] = r >= 0 ? r : 0;  // padding: value stays 0, column is a valid index
+          }
+        }
+      }
+    }
+    // packed column stream (symbolic.hpp): 16-bit offsets where a slice's columns span < 65536
+    S.slice_meta.assign((size_t)4 * S.nslices, 0);
+    std::vector<int> cmin((size_t)S.nslices, 0);
+    int64_t units = 0, n16 = 0;
+    for (int sl = 0; sl < S.nslices; sl++) {
+      const int base = S.slice_ptr[sl], w = (S.slice_ptr[sl + 1] - base) / C;
+      int lo = INT_MAX, hi = -1;
+      for (int l = 0; l < C; l++) {
+        const int r = S.srow[(size_t)sl * C + l];
+        if (r < 0) continue;
+        lo = std::min(lo, std::min(r, S.colind[S.rowptr[r]]));   // columns ascend in a row; padding uses r itself
+        hi = std::max(hi, std::max(r, S.colind[S.rowptr[r] + std::max(rowlen[r], 1) - 1]));
+      }
+      if (hi < 0) lo = hi = 0;
+      const bool narrow = !o.wide_cols && (int64_t)hi - lo < 65536;
+      if (units > 0x7fffffffLL - 2 * w - 4) throw std::runtime_error("fk: column stream too large for one GPU; partition the mesh");
+      S.slice_meta[4 * (size_t)sl + 0] = base;
+      S.slice_meta[4 * (size_t)sl + 1] = w;
+      S.slice_meta[4 * (size_t)sl + 2] = (int)units;
+      S.slice_meta[4 * (size_t)sl + 3] = narrow ? lo : -1;
+      cmin[sl] = lo;
+      units += narrow ? 4 * ((w + 3) / 4) : 2 * w;
+      n16 += narrow;
+    }
+    S.n_slices16 = n16;
+    S.sell_colz.assign((size_t)units * C, 0);
+#pragma omp parallel for schedule(static)
+    for (int sl = 0; sl < S.nslices; sl++) {
+      const int* m = &S.slice_meta[4 * (size_t)sl];
+      const int* src = &S.sell_col[(size_t)m[0]];
+      uint16_t* dst = &S.sell_colz[(size_t)m[2] * C];
+      const int n = m[1] * C;
+      if (m[3] >= 0) {   // step k of lane l -> 16-bit word ((k / 4) * 32 + l) * 4 + k % 4 (steps k >= w of the last group: 0)
+        for (int e = 0; e < n; e++) {
+          const int k = e / C, l = e % C;
+          int c = src[e];
+          if (c < m[3] || c - m[3] > 65535) c = m[3];   // padding of an unused lane (value 0): any valid column
+          dst[((size_t)(k / 4) * C + l) * 4 + (k % 4)] = (uint16_t)(c - m[3]);
+        }
+      } else {
+        std::memcpy(dst, src, sizeof(int) * (size_t)n);
+      }
+    }
+  };
+
+  if (npe != 4) {   // 10-node (P2) elements: pattern, map and SELL layout only; assembly goes through the contribution plan
+    build_sell();
+    S.ntiles = 0;
+    S.tile_elem_ptr.assign(1, 0);
+    S.tile_nnz_ptr.assign(1, 0);
+    S.tile_ent_ptr.assign(1, 0);
+    return;
   }
 
   // ---- tiles: rows grouped along a space-filling curve so each tile is a compact blob ---------
@@ -296,98 +401,7 @@ void build_symbolic(const double* p, const int* t, int nv, int nt, const Symboli
   }
   if (bad) throw std::runtime_error("fk: internal error building assembly tiles");
 
-  // ---- SELL-32-sigma layout (see symbolic.hpp) ---------------------------------------------------
-  {
-    const int C = 32;
-    const int sigma = std::max(1, o.sell_sigma);
-    std::vector<int> ord((size_t)nr);
-    std::iota(ord.begin(), ord.end(), 0);
-    if (sigma > 1)
-      for (int w0 = 0; w0 < nr; w0 += sigma)
-        std::stable_sort(ord.begin() + w0, ord.begin() + std::min(nr, w0 + sigma), [&](int a, int b) { return rowlen[a] > rowlen[b]; });
-    S.nslices = (nr + C - 1) / C;
-    S.srow.assign((size_t)S.nslices * C, -1);
-    std::copy(ord.begin(), ord.end(), S.srow.begin());
-    S.slice_ptr.assign((size_t)S.nslices + 1, 0);
-    int64_t tot = 0;
-    for (int sl = 0; sl < S.nslices; sl++) {
-      int w = 0;
-      for (int l = 0; l < C; l++) {
-        const int r = S.srow[(size_t)sl * C + l];
-        if (r >= 0) w = std::max(w, rowlen[r]);
-      }
-      S.slice_ptr[sl] = (int)tot;
-      tot += (int64_t)w * C;
-      if (tot > 0x7fffffffLL) throw std::runtime_error("fk: more than 2^31-1 padded matrix entries on one GPU; partition the mesh");
-    }
-    S.slice_ptr[S.nslices] = (int)tot;
-    S.nnz_sell = tot;
-    S.sell_col.assign((size_t)tot, 0);
-    S.csr2sell.assign((size_t)S.nnz, -1);
-    S.sell_diag.assign((size_t)nr, -1);
-#pragma omp parallel for schedule(static)
-    for (int sl = 0; sl < S.nslices; sl++) {
-      const int base = S.slice_ptr[sl], w = (S.slice_ptr[sl + 1] - base) / C;
-      for (int l = 0; l < C; l++) {
-        const int r = S.srow[(size_t)sl * C + l];
-        const int len = r >= 0 ? rowlen[r] : 0;
-        for (int k = 0; k < w; k++) {
-          const int idx = base + k * C + l;
-          if (k < len) {
-            const int q = S.rowptr[r] + k;
-            S.sell_col[idx] = S.colind[q];
-            S.csr2sell[q] = idx;
-            if (S.colind[q] == r) S.sell_diag[r] = idx;
-          } else {
-            S.sell_col[idx] = r >= 0 ? r : 0;  // padding: value stays 0, column is a valid index
-          }
-        }
-      }
-    }
-    // packed column stream (symbolic.hpp): 16-bit offsets where a slice's columns span < 65536
-    S.slice_meta.assign((size_t)4 * S.nslices, 0);
-    std::vector<int> cmin((size_t)S.nslices, 0);
-    int64_t units = 0, n16 = 0;
-    for (int sl = 0; sl < S.nslices; sl++) {
-      const int base = S.slice_ptr[sl], w = (S.slice_ptr[sl + 1] - base) / C;
-      int lo = INT_MAX, hi = -1;
-      for (int l = 0; l < C; l++) {
-        const int r = S.srow[(size_t)sl * C + l];
-        if (r < 0) continue;
-        lo = std::min(lo, std::min(r, S.colind[S.rowptr[r]]));   // columns ascend in a row; padding uses r itself
-        hi = std::max(hi, std::max(r, S.colind[S.rowptr[r] + std::max(rowlen[r], 1) - 1]));
-      }
-      if (hi < 0) lo = hi = 0;
-      const bool narrow = !o.wide_cols && (int64_t)hi - lo < 65536;
-      if (units > 0x7fffffffLL - 2 * w - 4) throw std::runtime_error("fk: column stream too large for one GPU; partition the mesh");
-      S.slice_meta[4 * (size_t)sl + 0] = base;
-      S.slice_meta[4 * (size_t)sl + 1] = w;
-      S.slice_meta[4 * (size_t)sl + 2] = (int)units;
-      S.slice_meta[4 * (size_t)sl + 3] = narrow ? lo : -1;
-      cmin[sl] = lo;
-      units += narrow ? 4 * ((w + 3) / 4) : 2 * w;
-      n16 += narrow;
-    }
-    S.n_slices16 = n16;
-    S.sell_colz.assign((size_t)units * C, 0);
-#pragma omp parallel for schedule(static)
-    for (int sl = 0; sl < S.nslices; sl++) {
-      const int* m = &S.slice_meta[4 * (size_t)sl];
-      const int* src = &S.sell_col[(size_t)m[0]];
-      uint16_t* dst = &S.sell_colz[(size_t)m[2] * C];
-      const int n = m[1] * C;
-      if (m[3] >= 0) {   // step k of lane l -> 16-bit word ((k / 4) * 32 + l) * 4 + k % 4 (steps k >= w of the last group: 0)
-        for (int e = 0; e < n; e++) {
-          const int k = e / C, l = e % C;
-          int c = src[e];
-          if (c < m[3] || c - m[3] > 65535) c = m[3];   // padding of an unused lane (value 0): any valid column
-          dst[((size_t)(k / 4) * C + l) * 4 + (k % 4)] = (uint16_t)(c - m[3]);
-        }
-      } else {
-        std::memcpy(dst, src, sizeof(int) * (size_t)n);
-      }
-    }
-  }
+  build_sell();
 
   // ---- packed device blobs (see symbolic.hpp) ---------------------------------------------------
   {
@@ -490,15 +504,19 @@ void build_symbolic(const double* p, const int* t, int nv, int nt, const Symboli
 // rescale plan (symbolic.hpp: RescalePlan)
 // ------------------------------------------------------------------------------------------------
 void build_rescale_plan(const Symbolic& S, int window, RescalePlan& R) {
-  const int nt = S.nt;
+  const int nt = S.nt, npe = S.npe, npe2 = S.npe * S.npe;
   const int64_t nnz = S.nnz;
-  if ((int64_t)nt >= ((int64_t)1 << 28)) throw std::runtime_error("fk: too many elements on one GPU for the rescale plan (28-bit ids)");
+  const int shift = npe == 4 ? 28 : 26;   // element id below, local pair (10 or 55 of them) above
+  R.pair_shift = shift;
+  if ((int64_t)nt >= ((int64_t)1 << shift)) throw std::runtime_error("fk: too many elements on one GPU for the contribution plan");
+  // index of the unordered local pair (a <= b) in the packed symmetric layout: row a starts at a npe - a (a - 1) / 2
+  auto pair_index = [npe](int a, int b) { return a * npe - a * (a - 1) / 2 + (b - a); };
   if (window < 32) window = 32;
   window = (window + 31) & ~31;
   const int* e2 = S.e2nnz.data();
   // canonical entry of local pair (a, b), a <= b, of element k; other = its mirror (or -1)
   auto canon = [&](int64_t k, int a, int b, int& other) -> int {
-    const int e1 = e2[16 * k + 4 * a + b], eb = e2[16 * k + 4 * b + a];
+    const int e1 = e2[(int64_t)npe2 * k + npe * a + b], eb = e2[(int64_t)npe2 * k + npe * b + a];
     if (a == b || e1 == eb) { other = -1; return e1; }
     if (e1 >= 0 && eb >= 0) { other = std::max(e1, eb); return std::min(e1, eb); }
     other = -1;
@@ -508,8 +526,8 @@ void build_rescale_plan(const Symbolic& S, int window, RescalePlan& R) {
   std::vector<int> cnt((size_t)nnz, 0), mirror((size_t)nnz, -1);
 #pragma omp parallel for schedule(static)
   for (int64_t k = 0; k < nt; k++)
-    for (int a = 0; a < 4; a++)
-      for (int b = a; b < 4; b++) {
+    for (int a = 0; a < npe; a++)
+      for (int b = a; b < npe; b++) {
         int other;
         const int c = canon(k, a, b, other);
         if (c < 0) continue;
@@ -570,15 +588,15 @@ void build_rescale_plan(const Symbolic& S, int window, RescalePlan& R) {
   int64_t total = 0;
 #pragma omp parallel for schedule(static) reduction(+ : total)
   for (int64_t k = 0; k < nt; k++)
-    for (int a = 0; a < 4; a++)
-      for (int b = a; b < 4; b++) {
+    for (int a = 0; a < npe; a++)
+      for (int b = a; b < npe; b++) {
         int other;
         const int c = canon(k, a, b, other);
         if (c < 0) continue;
         int f;
 #pragma omp atomic capture
         f = fill[c]++;
-        R.cref[(size_t)(slot_of[c] + 32 * (int64_t)f)] = (uint32_t)k | ((uint32_t)sym_index(a, b) << 28);
+        R.cref[(size_t)(slot_of[c] + 32 * (int64_t)f)] = (uint32_t)k | ((uint32_t)pair_index(a, b) << shift);
         total++;
       }
   R.n_contrib = total;
@@ -593,8 +611,9 @@ void build_rescale_plan(const Symbolic& S, int window, RescalePlan& R) {
       const int64_t s0 = slot_of[c];
       buf.resize((size_t)n);
       for (int e = 0; e < n; e++) buf[e] = R.cref[(size_t)(s0 + 32 * (int64_t)e)];
-      std::sort(buf.begin(), buf.end(), [](uint32_t x, uint32_t y) {
-        const uint32_t kx = x & 0x0fffffffu, ky = y & 0x0fffffffu;
+      const uint32_t emask = (1u << shift) - 1u;
+      std::sort(buf.begin(), buf.end(), [emask](uint32_t x, uint32_t y) {
+        const uint32_t kx = x & emask, ky = y & emask;
         return kx != ky ? kx < ky : x < y;
       });
       for (int e = 0; e < n; e++) R.cref[(size_t)(s0 + 32 * (int64_t)e)] = buf[e];

@@ -17,18 +17,20 @@ struct SymbolicOpts {
   int sell_sigma = 1024;      // SELL-32-sigma: rows are sorted by length inside windows of sigma rows (1 = input order)
   int n_owned = -1;  // rows [0, n_owned) get a pattern (multi-GPU: owned rows first); -1 = all
   bool wide_cols = false;  // true: every slice keeps 32-bit columns in the packed column stream (A/B measurements)
+  int npe = 4;             // nodes per element: 4 = P1 tetrahedra (and 2-D P1 as (n0,n1,n2,n2)); 10 = P2 tetrahedra (pattern, map,
+                           // SELL layout and the contribution plan only: no assembly tiles)
 };
 
 // Gather plan of one assembly tile = a set of rows whose every incident element is staged once in
 // shared memory; every CSR entry of those rows is then summed by ONE thread from the staged local
 // matrices in ascending element order (deterministic, no atomics).
 struct Symbolic {
-  int nv = 0, nt = 0, n_rows = 0;
+  int nv = 0, nt = 0, n_rows = 0, npe = 4;
   int64_t nnz = 0;
   std::vector<int> rowptr;   // nv+1
   std::vector<int> colind;   // nnz, ascending per row
   std::vector<int> diag;     // n_rows: CSR index of (r,r)
-  std::vector<int> e2nnz;    // 16*nt: index of (t[i,k], t[j,k]); -1 if the row is not assembled here
+  std::vector<int> e2nnz;    // npe^2 * nt (16 nt for tetrahedra): index of (t[i,k], t[j,k]); -1 if the row is not assembled here
 
   int ntiles = 0;
   std::vector<int64_t> tile_elem_ptr;  // ntiles+1 -> tile_elems
@@ -97,6 +99,7 @@ struct RescalePlan {
   int64_t n_contrib = 0;           // contributions listed (10 per element on an unpartitioned mesh)
   int64_t n_slots = 0;             // padded contribution slots = 32 * slice_ptr[nslices]
   int max_width = 0;
+  int pair_shift = 28;             // cref = element id | local pair << pair_shift (28: 10 pairs of a tetrahedron; 26: 55 pairs of a P2 element)
   std::vector<uint32_t> slice_ptr; // nslices + 1, in units of 32 slots
   std::vector<int> dst1, dst2;     // 32 * nslices: SELL index of the item's entry / of its mirror (-1: none; dst1 -1: padding lane)
   std::vector<uint32_t> cref;      // n_slots: element id | local pair (sym_index) << 28; 0xffffffff = padding

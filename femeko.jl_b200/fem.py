@@ -49,7 +49,9 @@ class Femeko:
             t = np.vstack([t, t[2:3]])
             if p.shape[0] == 2:
                 p = np.vstack([p, np.zeros((1, p.shape[1]))])
-        assert p.shape[0] == 3 and t.shape[0] == 4, "mesh.p must be 3 x nv and mesh.t 4 x nt (3 x nt for triangles)"
+        if t.shape[0] == 10:  # P2 tetrahedra (fk_assemble_*_p2)
+            self.dim, o.nodes_per_element = 3, 10
+        assert p.shape[0] == 3 and t.shape[0] in (4, 10), "mesh.p must be 3 x nv and mesh.t 4 x nt (3 x nt triangles, 10 x nt P2)"
         p = np.asfortranarray(p)
         t = np.asfortranarray(t)
         VE = L.f64(mesh.VE) if (use_mesh_VE and mesh.VE is not None) else None
@@ -166,6 +168,16 @@ class Femeko:
         assert self.dim == 2, "handle was not created from a triangle mesh"
         v = self._vals(want_vals)
         L.check(self.lib.fk_assemble_mass2d(self.h, slot, L.dptr(self._coef(rho)), L.dptr(v)))
+        return v
+
+    def assemble_stiffness_p2(self, mu=None, slot=0, want_vals=True):
+        v = self._vals(want_vals)
+        L.check(self.lib.fk_assemble_stiffness_p2(self.h, slot, L.dptr(self._coef(mu)), L.dptr(v)))
+        return v
+
+    def assemble_mass_p2(self, F=None, slot=1, want_vals=True):
+        v = self._vals(want_vals)
+        L.check(self.lib.fk_assemble_mass_p2(self.h, slot, L.dptr(self._coef(F)), L.dptr(v)))
         return v
 
     def assemble_mass(self, rho=None, slot=1, want_vals=True):
@@ -596,6 +608,19 @@ def massMatrix2D(mesh: MESH) -> SparseCSR:
     """src/FEM2D.jl:139-161."""
     fk = _handle(mesh)
     return SparseCSR(fk, 1, fk.assemble_mass2d(None, slot=1))
+
+
+def quadraticStiffnessMatrix(mesh: MESH, S=None, mu=None) -> SparseCSR:
+    """src/FEM3D.jl:378-395 on a 10-node mesh.  S (the reference's fitted basis coefficients) is accepted for call
+    compatibility and ignored: on straight-sided elements the fits are the Lagrange P2 functions the kernel uses."""
+    fk = _handle(mesh)
+    return SparseCSR(fk, 0, fk.assemble_stiffness_p2(mu, slot=0))
+
+
+def quadraticMassMatrix(mesh: MESH, S=None, F=None) -> SparseCSR:
+    """src/FEM3D.jl:494-561."""
+    fk = _handle(mesh)
+    return SparseCSR(fk, 1, fk.assemble_mass_p2(F, slot=1))
 
 
 def tangentialStiffnessMatrix(mesh: MESH, H_vec, dmu) -> SparseCSR:

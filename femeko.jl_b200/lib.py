@@ -32,7 +32,7 @@ class FemekoError(RuntimeError):
 class fk_create_opts(C.Structure):
     _fields_ = [("tile_max_elems", C.c_int), ("tile_max_rows", C.c_int), ("natural_order", C.c_int),
                 ("sell_sigma", C.c_int), ("device", C.c_int), ("n_owned", C.c_int), ("asm_cfg", C.c_int),
-                ("spmv_ctas_per_sm", C.c_int), ("sell_wide_cols", C.c_int)]
+                ("spmv_ctas_per_sm", C.c_int), ("sell_wide_cols", C.c_int), ("nodes_per_element", C.c_int)]
 
 
 class fk_pcg_opts(C.Structure):
@@ -101,6 +101,8 @@ _SIGS = {
     "fk_assemble_mass2d": (C.c_int, [_H, C.c_int, c_double_p, c_double_p]),
     "fk_comm_set_timeout": (C.c_int, [_H, C.c_int]),
     "fk_comm_reset": (C.c_int, [_H]),
+    "fk_assemble_stiffness_p2": (C.c_int, [_H, C.c_int, c_double_p, c_double_p]),
+    "fk_assemble_mass_p2": (C.c_int, [_H, C.c_int, c_double_p, c_double_p]),
     "fk_set_host_threads": (C.c_int, [C.c_int]),
     "fk_symbolic_rescale": (C.c_int, [_H, C.POINTER(C.c_longlong), c_int_p, C.POINTER(C.c_longlong), C.c_void_p, C.c_void_p, C.c_void_p,
                                       C.c_void_p]),

@@ -347,3 +347,38 @@ def delaunay_disc(npts: int = 2000, seed: int = 7, R: float = 1.0, inside_half: 
     mesh.t = np.asfortranarray(remap[tri].T.astype(np.int32))
     cen = (mesh.p[:2, mesh.t[0]] + mesh.p[:2, mesh.t[1]] + mesh.p[:2, mesh.t[2]]) / 3
     return _finish2d(mesh, np.all(np.abs(cen) <= inside_half, axis=0))
+
+
+# --------------------------------------------------------------------------------------------------
+# P2 (10-node) tetrahedra: mesh.t is 10 x nt, Gmsh order (vertices, then mid nodes of edges 0-1 1-2 0-2 0-3 2-3 1-3)
+# --------------------------------------------------------------------------------------------------
+P2_EDGES = ((0, 1), (1, 2), (0, 2), (0, 3), (2, 3), (1, 3))
+
+
+def to_p2(mesh: MESH) -> MESH:
+    """Order-2 version of a P1 tetrahedral MESH (what Gmsh's setOrder(2) hands the reference, src/mesh.jl:20-21): one mid
+    node per edge appended after the vertices (edge numbering = sorted unique (low, high) vertex pairs), straight edges."""
+    t = np.asarray(mesh.t[:4], dtype=np.int64)
+    nv = int(mesh.p.shape[1])
+    pairs = np.concatenate([np.stack([np.minimum(t[a], t[b]), np.maximum(t[a], t[b])]) for a, b in P2_EDGES], axis=1)
+    key = pairs[0] * nv + pairs[1]
+    uniq, inv = np.unique(key, return_inverse=True)
+    lo, hi = uniq // nv, uniq % nv
+    out = MESH()
+    out.p = np.asfortranarray(np.concatenate([mesh.p, 0.5 * (mesh.p[:, lo] + mesh.p[:, hi])], axis=1))
+    mids = (nv + inv).reshape(6, t.shape[1])
+    out.t = np.asfortranarray(np.vstack([t, mids]).astype(np.int32))
+    out.nv, out.nt = int(out.p.shape[1]), int(t.shape[1])
+    out.VE = np.array(mesh.VE, copy=True)
+    out.InsideElements = np.array(mesh.InsideElements, copy=True)
+    out.nInside = int(out.InsideElements.size)
+    out.InsideNodes = np.unique(out.t[:, out.InsideElements]).astype(np.int32)
+    out.nInsideNodes = int(out.InsideNodes.size)
+    out.surfaceT = np.zeros((4, 0), dtype=np.int32, order="F")
+    out.ns = 0
+    out.order = 2
+    return out
+
+
+def kuhn_cube_p2(N: int, L: float = 1.0, inside_edge: float = 0.2) -> MESH:
+    return to_p2(kuhn_cube(N, L=L, inside_edge=inside_edge))

@@ -45,6 +45,9 @@ typedef struct fk_create_opts {
   int spmv_ctas_per_sm; /* cap on resident SpMV CTAs per SM (0 = as many as fit)               */
   int sell_wide_cols; /* 1: keep 32-bit columns in every SELL slice (default 0: slices whose columns span
                          < 65536 store 16-bit offsets, ~10 instead of 12 bytes per matrix entry)  */
+  int nodes_per_element; /* 0 or 4: P1 tetrahedra, t is 4 x nt; 10: P2 tetrahedra, t is 10 x nt in Gmsh's order (4 vertices,
+                         then the mid nodes of the edges (0,1) (1,2) (0,2) (0,3) (2,3) (1,3)): pattern, SpMV, PCG and
+                         constraints as for P1, matrices through fk_assemble_stiffness_p2 / fk_assemble_mass_p2 */
 } fk_create_opts;
 
 /* PCG options.  Defaults (all 0) reproduce Eigen::ConjugateGradient's: tol = DBL_EPSILON relative
@@ -171,6 +174,12 @@ int fk_assemble_tangential(fk_handle h, int slot, const double* Hfield /* 3 x nt
  * VE/12 [2 1 1; 1 2 1; 1 1 2]; pattern, plan, SpMV and PCG are the 3-D ones.                                        */
 int fk_assemble_stiffness2d(fk_handle h, int slot, const double* f /* nt or NULL */, double* vals_out /* nnz or NULL */);
 int fk_assemble_mass2d(fk_handle h, int slot, const double* rho /* nt or NULL */, double* vals_out);
+/* P2 (10-node) tetrahedra: quadraticStiffnessMatrix(mesh, S, mu) (src/FEM3D.jl:324-395, the reference's 10-node
+ * quadrature) and quadraticMassMatrix(mesh, S, F) (src/FEM3D.jl:494-561, 15-point rule; like the reference's, its weights
+ * sum to 1/6 and multiply VE) on a handle created with nodes_per_element = 10.  The fitted basis functions S of the
+ * reference are the Lagrange P2 functions on straight-sided elements and are used in closed form.  coef: nt or NULL. */
+int fk_assemble_stiffness_p2(fk_handle h, int slot, const double* mu, double* vals_out /* nnz or NULL */);
+int fk_assemble_mass_p2(fk_handle h, int slot, const double* F, double* vals_out);
 int fk_local_stiffness(fk_handle h, const double* f, double* Ak /* 16 x nt */);          /* FEM3D.jl:59-76 */
 int fk_assemble_stiffness_dev(fk_handle h, int slot, const double* f_dev);
 int fk_assemble_mass_dev(fk_handle h, int slot, const double* rho_dev);

@@ -552,3 +552,118 @@ def mass2d(mesh):
     Ml = (1.0 / 12.0) * np.array([[2.0, 1, 1], [1, 2, 1], [1, 1, 2]])
     Mk = np.outer(Ml.ravel(order="F"), mesh.VE)
     return _assemble2d(mesh, Mk)
+
+
+# --------------------------------------------------------------------------------------------------
+# P2 (10-node) tetrahedra (src/FEM3D.jl:21-37, 324-395, 494-561, 653-755) -- numpy restatement, test infrastructure only
+# --------------------------------------------------------------------------------------------------
+def quadratic_basis(p, nds, nd):
+    """quadraticBasis, src/FEM3D.jl:21-37: coefficients S[0..9] of f = S0 + S1 x + S2 y + S3 z + S4 x^2 + S5 xy + S6 xz +
+    S7 y^2 + S8 yz + S9 z^2 with f(nd) = 1 and f = 0 on the element's nine other nodes (10 x 10 solve)."""
+    nodes = [int(nd)] + [int(i) for i in nds if i != nd]
+    x, y, z = p[0, nodes], p[1, nodes], p[2, nodes]
+    M = np.stack([np.ones(10), x, y, z, x * x, x * y, x * z, y * y, y * z, z * z], axis=1)
+    rhs = np.zeros(10)
+    rhs[0] = 1.0
+    return np.linalg.solve(M, rhs)
+
+
+def gauss_quadrature_3d_4():
+    """GaussQuadrature3D(4), src/FEM3D.jl:711-745: 15 points on the reference tetrahedron, weights summing to 1/6."""
+    pts = np.array([
+        [0.2500000000000000, 0.2500000000000000, 0.2500000000000000], [0.0000000000000000, 0.3333333333333333, 0.3333333333333333],
+        [0.3333333333333333, 0.3333333333333333, 0.3333333333333333], [0.3333333333333333, 0.3333333333333333, 0.0000000000000000],
+        [0.3333333333333333, 0.0000000000000000, 0.3333333333333333], [0.7272727272727273, 0.0909090909090909, 0.0909090909090909],
+        [0.0909090909090909, 0.0909090909090909, 0.0909090909090909], [0.0909090909090909, 0.0909090909090909, 0.7272727272727273],
+        [0.0909090909090909, 0.7272727272727273, 0.0909090909090909], [0.4334498464263357, 0.0665501535736643, 0.0665501535736643],
+        [0.0665501535736643, 0.4334498464263357, 0.0665501535736643], [0.0665501535736643, 0.0665501535736643, 0.4334498464263357],
+        [0.0665501535736643, 0.4334498464263357, 0.4334498464263357], [0.4334498464263357, 0.0665501535736643, 0.4334498464263357],
+        [0.4334498464263357, 0.4334498464263357, 0.0665501535736643]])
+    w = np.array([0.1817020685825351] + [0.0361607142857143] * 4 + [0.0698714945161738] * 4 + [0.0656948493683187] * 6) / 6.0
+    return w, pts
+
+
+def quadratic_basis_all(mesh):
+    """S[:, i, k] for every node i of every element k (what the reference drivers precompute once)."""
+    S = np.zeros((10, 10, mesh.nt))
+    for k in range(mesh.nt):
+        nds = mesh.t[:, k]
+        for i in range(10):
+            S[:, i, k] = quadratic_basis(mesh.p, nds, nds[i])
+    return S
+
+
+def pattern_npe(t, nv):
+    import scipy.sparse as sp
+
+    npe = t.shape[0]
+    r = np.concatenate([t[i] for i in range(npe) for _ in range(npe)]).astype(np.int64)
+    c = np.concatenate([t[j] for _ in range(npe) for j in range(npe)]).astype(np.int64)
+    A = sp.csr_matrix((np.ones(r.size), (r, c)), shape=(nv, nv))
+    A.sort_indices()
+    return A.indptr.astype(np.int32), A.indices.astype(np.int32)
+
+
+def _assemble_npe(mesh, Ak):
+    """A = sum over the npe^2 local pairs (i outer, j inner) of sparse(t[i,:], t[j,:], Ak[n,:]) (src/FEM3D.jl:384-391);
+    values on the canonical pattern (duplicates summed by scipy in double precision)."""
+    import scipy.sparse as sp
+
+    npe = mesh.t.shape[0]
+    rp, ci = pattern_npe(mesh.t, mesh.nv)
+    A = sp.csr_matrix((np.zeros(len(ci)), ci, rp), shape=(mesh.nv, mesh.nv))
+    n = 0
+    for i in range(npe):
+        for j in range(npe):
+            A = A + sp.csr_matrix((Ak[n], (mesh.t[i].astype(np.int64), mesh.t[j].astype(np.int64))), shape=(mesh.nv, mesh.nv))
+            n += 1
+    P = sp.csr_matrix((np.ones(len(ci)), ci, rp), shape=(mesh.nv, mesh.nv))   # keep structural zeros
+    A = (A + 0 * P).tocsr()
+    A.sort_indices()
+    out = np.zeros(len(ci))
+    rows = np.repeat(np.arange(mesh.nv), np.diff(rp))
+    key = {(int(r), int(c)): q for q, (r, c) in enumerate(zip(rows, ci))}
+    Ar = np.repeat(np.arange(mesh.nv), np.diff(A.indptr))
+    for r, c, v in zip(Ar, A.indices, A.data):
+        out[key[(int(r), int(c))]] = v
+    return rp, ci, out
+
+
+def quadratic_local_stiffness(mesh, S, mu=None):
+    """quadraticLocalStiffnessMatrix, src/FEM3D.jl:324-376 (the "10 node quadrature": mean over the element's nodes)."""
+    mu = np.ones(mesh.nt) if mu is None else np.asarray(mu, dtype=np.float64)
+    Ak = np.zeros((100, mesh.nt))
+    for k in range(mesh.nt):
+        nds = mesh.t[:, k]
+        x, y, z = mesh.p[0, nds], mesh.p[1, nds], mesh.p[2, nds]
+        Sk = S[:, :, k]
+        dx = Sk[1][:, None] + 2 * Sk[4][:, None] * x + Sk[5][:, None] * y + Sk[6][:, None] * z     # [basis, node]
+        dy = Sk[2][:, None] + 2 * Sk[7][:, None] * y + Sk[5][:, None] * x + Sk[8][:, None] * z
+        dz = Sk[3][:, None] + 2 * Sk[9][:, None] * z + Sk[6][:, None] * x + Sk[8][:, None] * y
+        temp = (dx @ dx.T + dy @ dy.T + dz @ dz.T) / 10 * mu[k] * mesh.VE[k]
+        Ak[:, k] = temp.ravel(order="F")
+    return Ak
+
+
+def quadratic_stiffness(mesh, S=None, mu=None):
+    S = quadratic_basis_all(mesh) if S is None else S
+    return _assemble_npe(mesh, quadratic_local_stiffness(mesh, S, mu))
+
+
+def quadratic_mass(mesh, S=None, F=None):
+    """quadraticMassMatrix, src/FEM3D.jl:494-561 (weights sum to 1/6 and multiply VE, exactly as the reference does)."""
+    S = quadratic_basis_all(mesh) if S is None else S
+    F = np.ones(mesh.nt) if F is None else np.asarray(F, dtype=np.float64)
+    w, pts = gauss_quadrature_3d_4()
+    Ml = np.zeros((100, mesh.nt))
+    for k in range(mesh.nt):
+        v = mesh.p[:, mesh.t[:4, k]]
+        J = (v[:, 1:] - v[:, :1])
+        xyz = v[:, :1] + J @ pts.T                       # 3 x 15
+        x, y, z = xyz
+        Sk = S[:, :, k]
+        mono = np.stack([np.ones_like(x), x, y, z, x * x, x * y, x * z, y * y, y * z, z * z])   # 10 x 15
+        phi = Sk.T @ mono                                 # [basis, point]
+        Mk = (phi * (w * mesh.VE[k])) @ phi.T * F[k]
+        Ml[:, k] = Mk.ravel(order="F")
+    return _assemble_npe(mesh, Ml)

@@ -28,7 +28,7 @@ def export_symbolic(mesh, **opts):
     n_rows = o.n_owned if o.n_owned > 0 else mesh.nv
     out = dict(
         rowptr=np.zeros(mesh.nv + 1, np.int32), colind=np.zeros(nnz.value, np.int32), diag=np.zeros(n_rows, np.int32),
-        e2nnz=np.zeros(16 * mesh.nt, np.int32), tile_elem_ptr=np.zeros(T + 1, np.int64), tile_elems=np.zeros(nte.value, np.uint32),
+        e2nnz=np.zeros(int(opts.get("nodes_per_element", 4) or 4) ** 2 * mesh.nt, np.int32), tile_elem_ptr=np.zeros(T + 1, np.int64), tile_elems=np.zeros(nte.value, np.uint32),
         tile_nnz_ptr=np.zeros(T + 1, np.int64), tile_gidx=np.zeros(nnzt.value, np.int32),
         tile_coff=np.zeros(nnzt.value + T, np.uint16), tile_ent_ptr=np.zeros(T + 1, np.int64),
         tile_ents=np.zeros(nent.value, np.uint16), slice_ptr=np.zeros(nsl.value + 1, np.int32),
@@ -85,7 +85,7 @@ def run_plan(plan, Ak):
     return vals, written
 
 
-def run_rescale_plan(plan, G10, s0):
+def run_rescale_plan(plan, G10, s0, shift=28):
     """Execute the rescale plan (symbolic.hpp: RescalePlan) the way geo_rescale_kernel walks it: one lane per item,
     contributions left to right, s0[element] * G10[pair, element] rounded separately, the sum written to the item's
     entry and to its mirror.  G10: 10 x nt unscaled geometric factors (sym_index order).  Returns CSR values and the
@@ -100,14 +100,14 @@ def run_rescale_plan(plan, G10, s0):
         for e in range(w):
             c = block[e]
             live = c != 0xFFFFFFFF
-            k = (c & 0x0FFFFFFF).astype(np.int64)
-            q = (c >> 28).astype(np.int64)
+            k = (c & ((1 << shift) - 1)).astype(np.int64)
+            q = (c >> shift).astype(np.int64)
             prod = np.where(live, s0[np.where(live, k, 0)] * G10[np.where(live, q, 0), np.where(live, k, 0)], 0.0)
             acc = np.where(live, acc + prod, acc)
             if e > 0:   # a padding slot is never followed by a live one, and elements ascend inside a list
                 prev = block[e - 1]
                 assert not np.any(live & (prev == 0xFFFFFFFF))
-                assert np.all((prev[live] & 0x0FFFFFFF) <= (c[live] & 0x0FFFFFFF))
+                assert np.all((prev[live] & ((1 << shift) - 1)) <= (c[live] & ((1 << shift) - 1)))
         d1, d2 = plan["r_dst1"][32 * s: 32 * s + 32], plan["r_dst2"][32 * s: 32 * s + 32]
         vs[d1[d1 >= 0]] = acc[d1 >= 0]
         vs[d2[d2 >= 0]] = acc[d2 >= 0]

@@ -213,3 +213,31 @@ def test_2d_triangles_through_the_tet_plan():
         vals, written = run_plan(plan, Ak)
         assert np.all(written == 1)
         assert np.max(np.abs(vals - vref)) < 1e-13 * np.max(np.abs(vref))
+
+
+def test_p2_symbolic_and_contribution_plan():
+    """10-node (P2) elements: the generalised symbolic phase gives the clique pattern of every element, the 100-entry
+    element -> nnz map, and a contribution plan (55 local pairs) whose execution on the oracle's local matrices
+    reproduces quadraticStiffnessMatrix (src/FEM3D.jl:378-395)."""
+    m = fk.kuhn_cube_p2(2)
+    plan = export_symbolic(m, nodes_per_element=10)
+    rp, ci = orc.pattern_npe(m.t, m.nv)
+    assert np.array_equal(plan["rowptr"], rp) and np.array_equal(plan["colind"], ci) and plan["ntiles"] == 0
+    rows = np.repeat(np.arange(m.nv), np.diff(rp))
+    e2n = plan["e2nnz"].reshape(m.nt, 10, 10)
+    for i in (0, 3, 7, 9):
+        for j in (0, 4, 9):
+            assert np.array_equal(rows[e2n[:, i, j]], m.t[i]) and np.array_equal(ci[e2n[:, i, j]], m.t[j])
+    S = orc.quadratic_basis_all(m)
+    mu = np.linspace(1.0, 2.0, m.nt)
+    Ak = orc.quadratic_local_stiffness(m, S)            # unscaled (mu = 1): the plan's factors
+    G55 = np.zeros((55, m.nt))
+    n = 0
+    for a in range(10):
+        for b in range(a, 10):
+            G55[n] = Ak[10 * b + a]
+            n += 1
+    vals, written = run_rescale_plan(plan, G55, mu, shift=26)
+    assert np.all(written == 1) and int((plan["r_cref"] != 0xFFFFFFFF).sum()) == 55 * m.nt
+    _, _, vref = orc.quadratic_stiffness(m, S, mu)
+    assert np.max(np.abs(vals - vref)) < 1e-12 * np.max(np.abs(vref))

@@ -201,3 +201,32 @@ def test_2d_p1_oracle_properties():
     r = A @ (2 * g.p[0] + 3 * g.p[1])
     inner = (np.abs(g.p[0]) < 0.49) & (np.abs(g.p[1]) < 0.49)
     assert abs(r[inner]).max() < 1e-13
+
+
+def test_p2_oracle_properties():
+    """src/FEM3D.jl:21-37,324-395,494-561 restated: the fitted basis functions are the Lagrange P2 functions on
+    straight-sided elements (so the kernel's closed forms are legitimate), the stiffness matrix kills constants, the
+    mass matrix sums to V/6 (the reference multiplies VE by weights that sum to 1/6) and is exact for quadratics."""
+    import scipy.sparse as sp
+
+    m = fk.kuhn_cube_p2(2)
+    S = orc.quadratic_basis_all(m)
+    # S reproduces phi = l(2l - 1) / 4 l_a l_b at an interior point of element 3
+    k = 3
+    v = m.p[:, m.t[:4, k]]
+    lam = np.array([0.1, 0.2, 0.3, 0.4])
+    x, y, z = v @ lam
+    mono = np.array([1, x, y, z, x * x, x * y, x * z, y * y, y * z, z * z])
+    phi_fit = S[:, :, k].T @ mono
+    edges = ((0, 1), (1, 2), (0, 2), (0, 3), (2, 3), (1, 3))
+    phi_cf = np.array([lam[i] * (2 * lam[i] - 1) for i in range(4)] + [4 * lam[a] * lam[b] for a, b in edges])
+    assert np.max(np.abs(phi_fit - phi_cf)) < 1e-12
+    rp, ci, v = orc.quadratic_stiffness(m, S, np.linspace(1, 2, m.nt))
+    A = sp.csr_matrix((v, ci, rp), shape=(m.nv, m.nv))
+    assert abs(A @ np.ones(m.nv)).max() < 1e-11 * abs(v).max() and abs(A - A.T).max() < 1e-12 * abs(v).max()
+    _, _, vm = orc.quadratic_mass(m, S)
+    M = sp.csr_matrix((vm, ci, rp), shape=(m.nv, m.nv))
+    assert np.isclose(vm.sum(), m.VE.sum() / 6.0, rtol=1e-12)
+    q = m.p[0] ** 2 + m.p[1] * m.p[2]                    # in the P2 space: 6 q'Mq = int q^2 over the unit cube
+    exact = 1 / 80 + 1 / 144                              # int x^4 + int y^2 z^2 over [-1/2, 1/2]^3 (cross term vanishes)
+    assert np.isclose(6.0 * (q @ (M @ q)), exact, rtol=1e-10)
