@@ -1,6 +1,7 @@
 // C ABI of libfemeko_cuda.so (see include/femeko_cuda.h).  Host-side orchestration only: every
 // floating-point operation of the hot path runs in the kernels of kernels.cuh on the GPU; there is
 // no CPU fallback (fk_create fails when no CUDA device is present).
+#include <chrono>
 #include <algorithm>
 #include <atomic>
 #include <cfloat>
@@ -82,6 +83,24 @@ static AsmArgs base_args(fk_handle h, double* vals) {
   return a;
 }
 
+// The persisting-L2 set-aside that keeps the PCG vectors resident (configure_l2) slows every OTHER kernel down while it
+// is configured -- measured on B200 with identical DRAM bytes, L2 hit rates and clocks: the sweep's element kernel 150 ->
+// 293 us, its streamed sums 325 -> 550 us (profiles/r2_sweep_regimes_l2_set_aside.csv), whether or not any line is
+// actually persisting.  So assembly work takes the set-aside away (cudaLimitPersistingL2CacheSize = 0) and the next solve
+// puts it back (pcg_dev): Picard sweep inside the bench step 0.63 -> 0.49 ms at N=119, 1.57 -> 0.94 ms at N=150.
+// fk_tune(15): 0 leaves the set-aside alone, bit 0 also resets the persisting lines, bit 1 (default) = the above.
+static void l2_release_for_assembly(fk_handle h) {
+  if (!h->l2_window_set) return;
+  if (h->l2_sweep_mode & 1) cudaCtxResetPersistingL2Cache();
+  if ((h->l2_sweep_mode & 2) && !h->l2_limit_zeroed) {
+    const auto t0 = std::chrono::steady_clock::now();
+    if (cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, 0) == cudaSuccess) h->l2_limit_zeroed = true;
+    else cudaGetLastError();
+    h->l2_toggle_ns[0] += std::chrono::duration_cast<std::chrono::nanoseconds>(std::chrono::steady_clock::now() - t0).count();
+    h->l2_toggles++;
+  }
+}
+
 // launch configurations of the assembly kernel: {threads per CTA, min resident CTAs per SM}
 constexpr int kNumAsmCfg = 8;
 template <int MODE, int THREADS, int MINB>
@@ -99,6 +118,7 @@ template <int MODE>
 static void launch_assemble(fk_handle h, const AsmArgs& a, bool setup = false) {
   if (!setup) need(h->sym.npe == 4, "fk: this entry point assembles 4-node elements; the handle holds P2 elements (use fk_assemble_*_p2)");
   if (h->sym.ntiles == 0) return;
+  if (!setup) l2_release_for_assembly(h);
   // 0 = measured default: {256, 2} for every mode (two CTAs per SM is what shared memory allows; the 128-register
   // budget keeps phase 1 free of spills)
   const int cfg = h->asm_cfg > 0 ? h->asm_cfg : 2;
@@ -196,6 +216,7 @@ static void ensure_geo(fk_handle h) {
 // vals = sum_k s0[k] G_k on the plan's items (every stored entry is an item or the mirror of one)
 static void launch_geo_rescale(fk_handle h, double* vals, int grid_cap, const double* g) {
   if (h->geo_nslices == 0) return;
+  l2_release_for_assembly(h);
   if (!g) g = h->geo_g.ptr;
   const int grid = grid_cap > 0 ? std::min(h->geo_grid, grid_cap) : h->geo_grid;
   geo_variant_dispatch(h->geo_variant, [&](auto B, auto MINB) {
@@ -654,6 +675,12 @@ static void pcg_dev(fk_handle h, int slot, const double* b_dev, double* x_dev, c
       if (cudaStreamSetAttribute(h->halo_stream, cudaStreamAttributeAccessPolicyWindow, &attr) != cudaSuccess) cudaGetLastError();
     }
   }
+  if (h->l2_limit_zeroed) {   // the sweep took the persisting set-aside away (fk_tune 15): the solve gets it back
+    const auto t0 = std::chrono::steady_clock::now();
+    if (cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, h->l2_window.num_bytes) != cudaSuccess) cudaGetLastError();
+    h->l2_toggle_ns[1] += std::chrono::duration_cast<std::chrono::nanoseconds>(std::chrono::steady_clock::now() - t0).count();
+    h->l2_limit_zeroed = false;
+  }
   const bool graphed = !h->comm || comm_capturable(h);
   if (graphed) build_graph(h, slot, chunk, rec);
   else if (h->l2_window_set) {   // no graph to carry the window (NCCL fallback): the stream does
@@ -899,6 +926,9 @@ int fk_destroy(fk_handle h) {
     if (!h) return 0;
     DeviceGuard dg(h->device);
     cudaDeviceSynchronize();
+    if (std::getenv("FK_DEBUG") && h->l2_toggles)
+      std::fprintf(stderr, "fk: L2 set-aside toggled %lld times: release %.1f us, restore %.1f us per call (host time, waits included)\n",
+                   h->l2_toggles, h->l2_toggle_ns[0] / 1e3 / h->l2_toggles, h->l2_toggle_ns[1] / 1e3 / h->l2_toggles);
     invalidate_graphs(h);
     if (h->cap_stream) cudaStreamDestroy(h->cap_stream);
     if (h->ctl_host) cudaFreeHost(h->ctl_host);
@@ -986,8 +1016,11 @@ int fk_tune(fk_handle h, int what, int value) {
         h->l2_on_stream = value != 0;
         configure_l2(h, h->l2_recurrence);
         break;
-      case 15:  // 1: give the assembly sweep the whole L2 (reset the persisting lines of the PCG vectors before it); default 0
-        h->l2_reset_before_sweep = value != 0;
+      case 15:  // the assembly sweep and the PCG's persisting L2 set-aside: 0 leave it; bit 0: reset the persisting lines before a
+                // sweep; bit 1: take the set-aside away for the sweep (cudaLimitPersistingL2CacheSize = 0) and put it back
+                // before the next solve
+        need(value >= 0 && value <= 3, "fk_tune: sweep L2 mode out of range");
+        h->l2_sweep_mode = value;
         break;
       case 17:  // rescale sweep: 0 (default) = element kernel then sums, one stream; otherwise 16 a + b = field recovery on b CTAs per
                 // SM beside the streamed sums on a CTAs per SM (measured behind a PCG solve: 0.62-0.75 ms against 0.63 in sequence,
@@ -1941,6 +1974,7 @@ static int picard_step_dev(fk_handle h, int slot, const double* u_dev, int compa
   // A handle that sweeps repeatedly (a Picard loop) switches to the rescale path (rescale.cuh): same bits, streamed
   // instead of recomputed.
   h->geo_sweeps++;
+  l2_release_for_assembly(h);
   const bool geo = h->geo_mode == 2 || (h->geo_mode == 1 && (h->geo_ready || h->geo_sweeps >= 2));
   if (geo) ensure_geo(h);
   const bool side = geo && h->geo_overlap;   // field recovery beside the streamed sums (needs the scales kept current)
@@ -2122,6 +2156,7 @@ int fk_picard_pcg(fk_handle h, int slot, const double* u, int compat_bug, const 
       FK_CUDA(cudaEventCreateWithFlags(&h->copy_ev, cudaEventDisableTiming));
     }
     h->st_d.ensure((size_t)h->nv);
+    l2_release_for_assembly(h);   // before anything is in flight: the limit change waits for the device
     FK_CUDA(cudaMemcpyAsync(h->u.ptr, u, sizeof(double) * (size_t)h->nv, cudaMemcpyHostToDevice, h->stream));
     // bvec / st_d were last touched by work on h->stream: order the side copies after it
     FK_CUDA(cudaEventRecord(h->copy_ev, h->stream));

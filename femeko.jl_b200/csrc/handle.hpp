@@ -81,7 +81,10 @@ struct fk_handle_s {
   bool overlap_halo = true;
   int halo_mode = 2;          // partitions, Eigen recurrence: 2 = exchange fused into the SpMV kernel, 1 = second stream, 0 = serial
   bool l2_miss_normal = false; // fk_tune 8
-  bool l2_on_stream = false, l2_reset_before_sweep = false;   // fk_tune 14 / 15
+  bool l2_on_stream = false;   // fk_tune 14
+  int l2_sweep_mode = 2;       // fk_tune 15: what the assembly sweep does about the PCG's persisting L2 set-aside
+  bool l2_limit_zeroed = false;
+  long long l2_toggles = 0, l2_toggle_ns[2] = {0, 0};   // FK_DEBUG: host time spent in the limit changes
   int l2_max_vecs = 0;         // fk_tune 9
   int spmv_int_reserve = 0;   // CTA slots per SM the interior SpMV leaves to the halo branch (measured: 0 best)
   cudaStream_t halo_stream = nullptr;

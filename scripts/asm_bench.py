@@ -31,10 +31,16 @@ picard_bytes = (16 + 8 + 64 + 24 + 8 + 8) * nt + (24 + 8) * nv + 8 * nnz
 stiff_bytes = 88 * nt + 24 * nv + 8 * nnz
 
 
+rnd = torch.randint(0, 255, (256 << 20,), dtype=torch.uint8, device="cuda") if os.environ.get("FK_FLUSH", "zero") == "random" else None
+
+
 def timed(fn, reps):
     ts = []
     for _ in range(reps):
-        big.zero_()
+        if rnd is not None:
+            big.copy_(rnd)      # flush with ordinary data: L2 is left full of dirty non-zero lines
+        else:
+            big.zero_()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         fn()
