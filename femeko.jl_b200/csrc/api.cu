@@ -191,7 +191,8 @@ static void ensure_geo(fk_handle h) {
   if (h->geo_ready) return;
   need(h->sym.npe == 4, "fk: the rescale path of P1 elements was asked for on a P2 handle");
   RescalePlan R;
-  build_rescale_plan(h->sym, h->geo_window, R);
+  build_rescale_plan(h->sym, h->geo_window, R, h->geo_rowsum_diag);
+  h->geo_plan_rowsum = h->geo_rowsum_diag;
   cudaStream_t s = h->stream;
   h->geo_nslices = R.nslices;
   h->geo_slots = R.n_slots;
@@ -226,6 +227,12 @@ static void launch_geo_rescale(fk_handle h, double* vals, int grid_cap, const do
   });
   FK_CUDA(cudaGetLastError());
   h->launches++;
+  if (h->geo_plan_rowsum && h->sym.npe == 4 && !(h->geo_dbg & 2)) {   // the plan carries no diagonal contributions: a_rr = -(sum of the row's other entries)
+    diag_from_rowsum_kernel<<<cdiv(h->sym.nslices, 8), 256, 0, h->stream>>>(reinterpret_cast<const int4*>(h->slice_meta.ptr), h->srow.ptr,
+                                                                          h->sell_diag.ptr, h->sym.nslices, h->n_rows, vals);
+    FK_CUDA(cudaGetLastError());
+    h->launches++;
+  }
 }
 
 static void ensure_state(fk_handle h) {
@@ -1021,6 +1028,15 @@ int fk_tune(fk_handle h, int what, int value) {
                 // before the next solve
         need(value >= 0 && value <= 3, "fk_tune: sweep L2 mode out of range");
         h->l2_sweep_mode = value;
+        break;
+      case 19:  // profiling experiments only (results are garbage): bit 0 skips the field-recovery kernel of the side-by-side sweep,
+                // bit 1 the row-sum diagonal, bit 2 the streamed sums
+        h->geo_dbg = value;
+        break;
+      case 18:  // rescale path: 1 (default) = diagonal from the row sums (6 contributions per tetrahedron); 0 = diagonal summed from its
+                // own contributions (10 per tetrahedron, bit-identical to the tile kernel).  Rebuilds the plan.
+        h->geo_rowsum_diag = value != 0;
+        if (h->geo_ready && h->geo_plan_rowsum != h->geo_rowsum_diag) h->geo_ready = false;
         break;
       case 17:  // rescale sweep: 0 (default) = element kernel then sums, one stream; otherwise 16 a + b = field recovery on b CTAs per
                 // SM beside the streamed sums on a CTAs per SM (measured behind a PCG solve: 0.62-0.75 ms against 0.63 in sequence,
@@ -2001,6 +2017,7 @@ static int picard_step_dev(fk_handle h, int slot, const double* u_dev, int compa
     FK_CUDA(cudaMemsetAsync(h->tile_max.ptr, 0, sizeof(double), h->stream));
   }
   // 2. the sweep: stiffness with the refreshed mu + H, |H| of every element
+  bool folded = false;
   if (geo) {
     if (h->elem_grid == 0) {
       int occ = 1;
@@ -2008,8 +2025,11 @@ static int picard_step_dev(fk_handle h, int slot, const double* u_dev, int compa
       h->elem_grid = h->num_sms * std::max(1, occ);
     }
     if (side) {
-      // the two streaming kernels of the sweep are independent: run them side by side, each on part of the CTA slots, so
-      // that the memory system always has both their request streams queued (each alone is latency-bound at 50-60 % of HBM)
+      // The two streaming kernels of the sweep are independent once the material pass has set the scales: the sums go first
+      // on the main stream (their persistent grid takes its CTA slots evenly), field recovery runs beside them on a side
+      // stream on the slots that are left, followed there by the fold of the convergence metric; the diagonal follows the
+      // sums.  (Starting field recovery BEFORE the material pass was measured slower, 0.48 vs 0.40 ms: the persistent grid
+      // of the sums then lands unevenly on the SMs.)
       if (!h->asm_stream) {
         FK_CUDA(cudaStreamCreateWithFlags(&h->asm_stream, cudaStreamNonBlocking));
         FK_CUDA(cudaEventCreateWithFlags(&h->asm_fork, cudaEventDisableTiming));
@@ -2017,13 +2037,16 @@ static int picard_step_dev(fk_handle h, int slot, const double* u_dev, int compa
       }
       FK_CUDA(cudaEventRecord(h->asm_fork, h->stream));
       FK_CUDA(cudaStreamWaitEvent(h->asm_stream, h->asm_fork, 0));
+      if (!(h->geo_dbg & 4)) launch_geo_rescale(h, a.vals, h->num_sms * h->geo_split_resc);
       const int ge = std::min(cdiv(h->nt, kElemThreads), h->num_sms * h->geo_split_elem);
-      picard_element_kernel<false><<<ge, kElemThreads, 0, h->asm_stream>>>(h->p4.ptr, h->t4.ptr, a.u, nullptr, nullptr, h->nt, compat_bug,
-                                                                           h->Hn.ptr, h->Hfield.ptr, nullptr);
+      if (!(h->geo_dbg & 1))
+        picard_element_kernel<false><<<ge, kElemThreads, 0, h->asm_stream>>>(h->p4.ptr, h->t4.ptr, a.u, nullptr, nullptr, h->nt, compat_bug,
+                                                                             h->Hn.ptr, h->Hfield.ptr, nullptr);
       FK_CUDA(cudaGetLastError());
-      FK_CUDA(cudaEventRecord(h->asm_join, h->asm_stream));
       h->launches++;
-      launch_geo_rescale(h, a.vals, h->num_sms * h->geo_split_resc);
+      comm_allreduce_partials(h, h->asm_stream, h->tile_max.ptr, npart, npart, 1, 1, h->scal.ptr, nullptr, 0);
+      folded = true;
+      FK_CUDA(cudaEventRecord(h->asm_join, h->asm_stream));
       FK_CUDA(cudaStreamWaitEvent(h->stream, h->asm_join, 0));
     } else {
       picard_element_kernel<true><<<std::min(cdiv(h->nt, kElemThreads), h->elem_grid), kElemThreads, 0, h->stream>>>(
@@ -2036,7 +2059,7 @@ static int picard_step_dev(fk_handle h, int slot, const double* u_dev, int compa
     launch_assemble<ASM_PICARD>(h, a);
   }
   // div = mu0 * max over every rank's material elements (NewtonRaphson.jl:200)
-  comm_allreduce_partials(h, h->stream, h->tile_max.ptr, npart, npart, 1, 1, h->scal.ptr, nullptr, 0);
+  if (!folded) comm_allreduce_partials(h, h->stream, h->tile_max.ptr, npart, npart, 1, 1, h->scal.ptr, nullptr, 0);
   h->picard_pending = true;
   if (!sync) return 0;
   return picard_collect(h, div_out);

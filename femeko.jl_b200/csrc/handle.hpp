@@ -150,8 +150,10 @@ struct fk_handle_s {
   // rescale assembly (rescale.cuh): geometric factors of every contribution, built on demand
   //   geo_mode 0: never; 1 (default): from the second Picard sweep of a handle on; 2: from the first sweep / assembly on
   int geo_mode = 1, geo_sweeps = 0, geo_nslices = 0, geo_grid = 0, geo_variant = 0, geo_window = 65536, elem_grid = 0;
-  bool geo_ready = false, geo_overlap = false, s0_dirty = true;   // s0_dirty: geo_s0 != VE * mu for some element
-  int geo_split_resc = 3, geo_split_elem = 2;                    // CTAs per SM of the two kernels when they run side by side
+  bool geo_ready = false, geo_overlap = true, s0_dirty = true;   // s0_dirty: geo_s0 != VE * mu for some element
+  int geo_dbg = 0;   // fk_tune 19
+  bool geo_rowsum_diag = true, geo_plan_rowsum = false;          // fk_tune 18; what the resident plan was built for
+  int geo_split_resc = 4, geo_split_elem = 1;                    // CTAs per SM of the two kernels when they run side by side
   cudaStream_t asm_stream = nullptr;
   cudaEvent_t asm_fork = nullptr, asm_join = nullptr;
   long long geo_slots = 0, geo_items = 0, geo_contrib = 0;

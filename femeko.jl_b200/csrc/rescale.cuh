@@ -67,7 +67,10 @@ static __global__ void __launch_bounds__(kElemThreads) picard_element_kernel(con
                                                                              const double* __restrict__ u, const double* __restrict__ mu,
                                                                              const double* __restrict__ VE, int nt, int compat,
                                                                              double* __restrict__ Hn, double* __restrict__ Hfield,
-                                                                             double* __restrict__ s0) {
+                                                                             double* __restrict__ s0,
+                                                                             const unsigned char* __restrict__ skip_hn = nullptr) {
+  // skip_hn (side-by-side sweep): |H| of the elements with a B-H curve is written by material_update_kernel, which also
+  // reads their previous |H| -- leaving those entries alone lets the two kernels run concurrently
   __shared__ double hs[kElemThreads / 32][96];
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   const long long stride = (long long)gridDim.x * kElemThreads;
@@ -89,7 +92,7 @@ static __global__ void __launch_bounds__(kElemThreads) picard_element_kernel(con
       hy = -(u0 * G.g[0][1]) - u1 * G.g[1][1] - u2 * G.g[2][1] - u3 * G.g[3][1];
       hz = -(u0 * G.g[0][2]) - u1 * G.g[1][2] - u2 * G.g[2][2] - u3 * G.g[3][2];
       if (compat) { hy += hz; hz = 0.0; }  // NewtonRaphson.jl:187-189: d-term lands in row 2
-      __stcs(Hn + k, norm3(hx, hy, hz));
+      if (!(skip_hn && __ldg(skip_hn + k) != 0)) __stcs(Hn + k, norm3(hx, hy, hz));
       if (S0) s0[k] = __dmul_rn(VE ? V : G.vol, f);
     }
     if (Hfield) {
@@ -145,4 +148,30 @@ static __global__ void __launch_bounds__(kGeoThreads, MINB) geo_rescale_kernel(c
       if (d2 >= 0) vals[d2] = acc;
     }
   }
+}
+
+// Diagonal of a matrix whose local matrices have zero row sums (stiffness: sum_j grad l_i . grad l_j = 0), from the
+// off-diagonal entries the streamed sums just wrote: a_rr = -(sum_{c != r} a_rc), folded left to right in column order.
+// One lane per row over the SELL slices, like the SpMV.  Replaces the 4 diagonal contributions of every element (40 % of
+// the contribution stream); the result differs from the summed diagonal by rounding only (|delta| <~ 1e-15 sum |a_rc|).
+static __global__ void __launch_bounds__(256) diag_from_rowsum_kernel(const int4* __restrict__ slice_meta, const int* __restrict__ srow,
+                                                                      const int* __restrict__ sell_diag, int nslices, int n_rows,
+                                                                      double* __restrict__ vals) {
+  const int lane = threadIdx.x & 31;
+  // last slices first: the streamed sums wrote the values in ascending order, so the tail is what L2 still holds
+  const int sl = nslices - 1 - (int)(blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5));
+  if (sl < 0) return;
+  const int4 m = __ldg(slice_meta + sl);   // {value base, width, ...}
+  const int r = __ldg(srow + sl * 32 + lane);
+  const int dg = (r >= 0 && r < n_rows) ? __ldg(sell_diag + r) : -1;
+  const double* __restrict__ v = vals + m.x + lane;
+  double acc = 0.0;
+  for (int k = 0; k < m.y; k += 4) {
+    double a[4];
+#pragma unroll
+    for (int q = 0; q < 4; q++) a[q] = (k + q < m.y && m.x + (k + q) * 32 + lane != dg) ? __ldcg(v + (size_t)(k + q) * 32) : 0.0;
+#pragma unroll
+    for (int q = 0; q < 4; q++) acc = __dadd_rn(acc, a[q]);
+  }
+  if (dg >= 0) vals[dg] = -acc;
 }

@@ -503,7 +503,7 @@ void build_symbolic(const double* p, const int* t, int nv, int nt, const Symboli
 // ------------------------------------------------------------------------------------------------
 // rescale plan (symbolic.hpp: RescalePlan)
 // ------------------------------------------------------------------------------------------------
-void build_rescale_plan(const Symbolic& S, int window, RescalePlan& R) {
+void build_rescale_plan(const Symbolic& S, int window, RescalePlan& R, bool skip_diag) {
   const int nt = S.nt, npe = S.npe, npe2 = S.npe * S.npe;
   const int64_t nnz = S.nnz;
   const int shift = npe == 4 ? 28 : 26;   // element id below, local pair (10 or 55 of them) above
@@ -527,7 +527,7 @@ void build_rescale_plan(const Symbolic& S, int window, RescalePlan& R) {
 #pragma omp parallel for schedule(static)
   for (int64_t k = 0; k < nt; k++)
     for (int a = 0; a < npe; a++)
-      for (int b = a; b < npe; b++) {
+      for (int b = a + (skip_diag ? 1 : 0); b < npe; b++) {
         int other;
         const int c = canon(k, a, b, other);
         if (c < 0) continue;
@@ -589,7 +589,7 @@ void build_rescale_plan(const Symbolic& S, int window, RescalePlan& R) {
 #pragma omp parallel for schedule(static) reduction(+ : total)
   for (int64_t k = 0; k < nt; k++)
     for (int a = 0; a < npe; a++)
-      for (int b = a; b < npe; b++) {
+      for (int b = a + (skip_diag ? 1 : 0); b < npe; b++) {
         int other;
         const int c = canon(k, a, b, other);
         if (c < 0) continue;

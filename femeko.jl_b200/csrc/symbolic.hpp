@@ -104,7 +104,9 @@ struct RescalePlan {
   std::vector<int> dst1, dst2;     // 32 * nslices: SELL index of the item's entry / of its mirror (-1: none; dst1 -1: padding lane)
   std::vector<uint32_t> cref;      // n_slots: element id | local pair (sym_index) << 28; 0xffffffff = padding
 };
-void build_rescale_plan(const Symbolic& S, int window, RescalePlan& R);
+// skip_diag: leave the pairs (a, a) out -- the caller obtains the diagonal from the row sums (local matrices with zero row
+// sums: stiffness), 6 instead of 10 contributions per tetrahedron
+void build_rescale_plan(const Symbolic& S, int window, RescalePlan& R, bool skip_diag = false);
 
 // p: 3 x nv (may be null when natural_order), t: 4 x nt 0-based.  Throws std::runtime_error on bad input.
 void build_symbolic(const double* p, const int* t, int nv, int nt, const SymbolicOpts& o, Symbolic& S);

@@ -106,8 +106,13 @@ int fk_tune(fk_handle h, int what, int value);
  * %globaltimer; an unused record has start = 2^64 - 1.  Copies min(max_records, 4 cap) records.                    */
 /* Rescale assembly (fk_tune 10: 0 never, 1 = from the second Picard sweep of the handle on (default), 2 = at once; fk_tune 12: its
  * launch shape): the geometric factors grad(lambda_i).grad(lambda_j) of every contribution are computed once and every
- * later stiffness assembly / Picard sweep streams sum_k VE[k] f[k] g, bit-identical to the tile kernel, the way
- * NewtonRaphson.jl:114-127,153-161 keeps Ak and rescales it by mu.  fk_geo_stats builds the plan if needed and reports
+ * later stiffness assembly / Picard sweep streams sum_k VE[k] f[k] g the way NewtonRaphson.jl:114-127,153-161 keeps Ak and
+ * rescales it by mu.  Every off-diagonal entry is bit-identical to the tile kernel's; the diagonal is taken from the row
+ * sums (a_rr = -sum_{c != r} a_rc: the local stiffness matrices have zero row sums), which saves the 4 diagonal
+ * contributions of every element and differs from the summed diagonal by rounding only (fk_tune 18 = 0: sum it instead,
+ * all entries bit-identical).  fk_tune 13: sort window of the plan; 15: what assembly work does about the PCG's
+ * persisting-L2 set-aside (default 2: release it, the next solve restores it); 17: field recovery beside the streamed
+ * sums (16 a + b CTAs per SM, default 4 + 1; 0 = one after the other).  fk_geo_stats builds the plan if needed and reports
  * its size: entry pairs, contributions, padded slots, device bytes (12 B per slot + 8 B per pair + 8 B per element).   */
 int fk_geo_stats(fk_handle h, long long* items, long long* contributions, long long* slots, long long* bytes);
 int fk_trace_read(fk_handle h, unsigned long long* out, int max_records, int* n_records);

@@ -95,7 +95,7 @@ for persist in ([1] if short else [1, 0]):
 # the two streaming kernels of the sweep side by side (fk_tune 17 = 16 a + b: sums on a CTAs per SM, field recovery on b), timed
 # behind a PCG solve like the bench step
 h.tune(2, 1)
-for split in ([0x32] if short else [0, 0x32, 0x41, 0x22, 0x31, 0x42, 0x23, 0x33]):
+for split in ([0x32] if short else [int(v, 16) for v in os.environ.get('FK_SPLITS', '0,32,41,22,31,42,23,33').split(',')]):
     h.tune(17, split)
     sweep(); h.synchronize()
     ts = []
@@ -109,6 +109,20 @@ for split in ([0x32] if short else [0, 0x32, 0x41, 0x22, 0x31, 0x42, 0x23, 0x33]
         ts.append(e0.elapsed_time(e1))
     ts.sort()
     report(f"picard_sweep_rescale_after_pcg_split{split >> 4}_{split & 15}", (ts[len(ts) // 2], ts[0]), picard_bytes)
-h.tune(17, 0x32)
+h.tune(17, 0x41)
+# critical path of the side-by-side sweep: leave one kernel out at a time (fk_tune 19; results are garbage)
+if not short:
+    for dbg, nm in ((0, "all"), (1, "no_field_recovery"), (2, "no_rowsum"), (4, "no_sums"), (3, "sums_only"), (6, "field_recovery_only")):
+        h.tune(19, dbg)
+        sweep(); h.synchronize()
+        ts = []
+        for _ in range(r):
+            h.pcg_dev(b.data_ptr(), x.data_ptr(), slot=1, max_iter=20, tol_disable=True, check_every=20)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(); sweep(); e1.record(); torch.cuda.synchronize()
+            ts.append(e0.elapsed_time(e1))
+        ts.sort()
+        report(f"sweep_4_1_{nm}", (ts[len(ts) // 2], ts[0]), picard_bytes)
+    h.tune(19, 0)
 h.picard_result()
 h.close()
