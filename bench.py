@@ -547,7 +547,8 @@ def run_ours(args):
         floor_bytes = int(8 * sell[0] + sell[3] + 144 * sell[1])
         rec_name = ("single-reduction recurrence: spmv_sell_kernel<DOT> + cg_update_kernel, 2 kernels"
                     if args.recurrence == 1 else "Eigen recurrence: spmv_sell_kernel<DOT> + pcg_update_kernel + pcg_direction_kernel")
-        sweep_name = ("Picard sweep, rescale path: material_update_kernel + picard_element_kernel + geo_rescale_kernel + max fold"
+        sweep_name = ("Picard sweep, rescale path: material_update_kernel, then geo_rescale_kernel + diag_from_rowsum_kernel (4 CTAs "
+                      "per SM) beside picard_element_kernel + max fold (1 CTA per SM, second stream)"
                       if geo else "Picard sweep: material_update_kernel + assemble_kernel<ASM_PICARD> + max fold")
         line = {
             "metric": METRIC, "value": round(value, 3), "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
@@ -593,10 +594,12 @@ def run_ours(args):
             "clocks": P["clocks"],
         }
         if geo:
-            line["roofline_assembly"]["layout_bytes_per_launch"] = int(geo[3] + 8 * h_nnz_sell(sell) + 72 * nt)
+            line["roofline_assembly"]["layout_bytes_per_launch"] = int(geo[3] + 8 * h_nnz_sell(sell) + 64 * nt)
             line["roofline_assembly"]["layout_note"] = ("what the rescale path streams per sweep: 12 B per contribution slot (%d slots for %d "
-                                                        "contributions), 8 B per entry pair, the values written once, ~72 B per element in "
-                                                        "the element kernel" % (geo[2], geo[1]))
+                                                        "contributions; 6 per tetrahedron when the diagonal comes from the row sums), 8 B per "
+                                                        "entry pair, the values written once (the row-sum pass re-reads the off-diagonal values "
+                                                        "it folds, mostly from L2), ~64 B per element in field recovery + material pass"
+                                                        % (geo[2], geo[1]))
         if P["split"]:
             line["roofline"]["kernel_split_us"] = P["split"]
             line["roofline"]["kernel_split_note"] = ("device-side %globaltimer records inside the replayed graph (fk_tune 11), median over the "

@@ -1038,9 +1038,10 @@ int fk_tune(fk_handle h, int what, int value) {
         h->geo_rowsum_diag = value != 0;
         if (h->geo_ready && h->geo_plan_rowsum != h->geo_rowsum_diag) h->geo_ready = false;
         break;
-      case 17:  // rescale sweep: 0 (default) = element kernel then sums, one stream; otherwise 16 a + b = field recovery on b CTAs per
-                // SM beside the streamed sums on a CTAs per SM (measured behind a PCG solve: 0.62-0.75 ms against 0.63 in sequence,
-                // profiles/r2_asm_bench_side_by_side.jsonl -- the two kernels compete for the same miss queues, no gain)
+      case 17:  // rescale sweep: 0 = element kernel then sums, one stream; otherwise 16 a + b = field recovery on b CTAs per SM
+                // beside the streamed sums on a CTAs per SM (default 16*4 + 1).  With the PCG's L2 set-aside released (fk_tune 15)
+                // 4 + 1 measures 0.40 ms against 0.45 in sequence (profiles/r2_asm_bench_rowsum_diag_side_by_side.jsonl); while the
+                // set-aside was still active no split gained anything (profiles/r2_asm_bench_side_by_side.jsonl)
         need(value >= 0 && value < 256, "fk_tune: split out of range");
         h->geo_overlap = value != 0;
         if (value) { h->geo_split_resc = std::max(1, value >> 4); h->geo_split_elem = std::max(1, value & 15); }
