@@ -7,7 +7,8 @@ from .mesh import MESH, kuhn_cube, delaunay_ball, tri_grid, delaunay_disc, to_p2
 from .meshio import save2file, saveMesh, loadMesh, read_msh  # noqa: F401
 from .lib import FemekoError, build, load  # noqa: F401
 from .fem import (Femeko, FemekoMulti, SparseCSR, stiffnessMatrix, massMatrix, stiffnessMatrix2D, massMatrix2D, quadraticStiffnessMatrix, quadraticMassMatrix, tangentialStiffnessMatrix,  # noqa: F401
-                  localStiffnessMatrix, lagrange, BoundaryIntegral, cg, lineSearch, recoverField, Spline1D)
+                  localStiffnessMatrix, lagrange, BoundaryIntegral, cg, lineSearch, recoverField, Spline1D,
+                  residual_norm_noalloc, NOALLOC_MAX_ROWS)
 from .materials import (DATA, gradient, materialPermeability, loadMaterial, synthetic_gd_like,  # noqa: F401
                         synthetic_iron_like)
 from .magnetostatics import picard, newton_raphson, NonlinearResult  # noqa: F401

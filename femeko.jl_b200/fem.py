@@ -668,6 +668,21 @@ def recoverField(mesh: MESH, u, mu=None, compat_bug: bool = False):
     return _handle(mesh).recover_field(u, mu, compat_bug)
 
 
+NOALLOC_MAX_ROWS = 1 << 26   # include/femeko_cuda.h: FK_NOALLOC_MAX_ROWS
+
+
+def residual_norm_noalloc(b_ptr: int, Ax_ptr: int, n: int, r_ptr: int | None = None, norm_dev_ptr: int | None = None,
+                          want_host: bool = True, stream: int | None = None):
+    """fk_residual_norm_noalloc (no counterpart in the reference): r = b - Ax and ||r|| on DEVICE pointers of the current
+    device, with the reduction scratch in the library's static device array -- the call allocates nothing.  Returns the norm
+    (synchronises `stream`) when want_host, else None.  n above NOALLOC_MAX_ROWS raises FemekoError."""
+    lib = L.load()
+    nr = C.c_double()
+    L.check(lib.fk_residual_norm_noalloc(C.c_void_p(b_ptr), C.c_void_p(Ax_ptr), int(n), C.c_void_p(r_ptr), C.c_void_p(norm_dev_ptr),
+                                         C.byref(nr) if want_host else None, C.c_void_p(stream)))
+    return nr.value if want_host else None
+
+
 class Spline1D:
     """Dierckx.jl ``Spline1D(x, y; k=3, s=0, bc)``: interpolating cubic B-spline with FITPACK's
     knot choice; fields ``t`` (knots), ``c`` (coefficients), ``k`` like the Julia object."""

@@ -97,6 +97,7 @@ _SIGS = {
     "fk_multi_spmv": (C.c_int, [_H, C.c_int, c_double_p, c_double_p]),
     "fk_multi_pcg": (C.c_int, [_H, C.c_int, c_double_p, c_double_p, C.POINTER(fk_pcg_opts), c_int_p, c_double_p]),
     "fk_multi_picard_step": (C.c_int, [_H, C.c_int, c_double_p, C.c_int, c_double_p]),
+    "fk_residual_norm_noalloc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_longlong, C.c_void_p, C.c_void_p, c_double_p, C.c_void_p]),
     "fk_assemble_stiffness2d": (C.c_int, [_H, C.c_int, c_double_p, c_double_p]),
     "fk_assemble_mass2d": (C.c_int, [_H, C.c_int, c_double_p, c_double_p]),
     "fk_comm_set_timeout": (C.c_int, [_H, C.c_int]),

@@ -379,6 +379,23 @@ int fk_multi_pcg(fk_multi m, int slot, const double* b /* nv */, double* x /* nv
                  double* relres_out);
 int fk_multi_picard_step(fk_multi m, int slot, const double* u /* nv */, int compat_bug, double* div_out);
 
+/* ---- allocation-free residual norm -----------------------------------------------------------------------------------
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  r = b - Ax (r_dev may be NULL) and
+ * ||r||_2 -- the second half of fk_residual_dev, whose per-CTA partials live in handle-owned buffers -- with the scratch
+ * in a file-scope __device__ array instead (csrc/noalloc.cu, 131 328 bytes held by every GPU that loads the library until
+ * the process exits).  The call allocates nothing: no cudaMalloc / cudaFree / cudaMallocHost, no handle, no library routine
+ * that allocates.  Ax_dev is the caller's product (e.g. from fk_spmv_dev); all four arrays are device pointers of the
+ * CURRENT device, `stream` a cudaStream_t of it (NULL = default stream).  norm_dev_out: device double or NULL;
+ * norm_host_out: host double or NULL -- when given, the call copies the norm back and synchronises the stream (leave it NULL
+ * under stream capture, and make one call outside the capture first: the first call on a device takes the array's address).
+ * n > FK_NOALLOC_MAX_ROWS is rejected (return 1, fk_last_error says so).  Every call on a GPU shares the one scratch array:
+ * calls that overlap on the same GPU (different streams or host threads) race -- serialise them.  Deterministic: the
+ * summation order depends on n alone.                                                                                  */
+#define FK_NOALLOC_MAX_ROWS (1LL << 26)   /* 67 108 864 rows: one partial per 4096 rows in the static scratch */
+int fk_residual_norm_noalloc(const double* b_dev, const double* Ax_dev, long long n, double* r_dev /* n or NULL */,
+                             double* norm_dev_out /* device, or NULL */, double* norm_host_out /* host, or NULL */, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
