@@ -801,6 +801,7 @@ static void copy_vec(const std::vector<T>& v, U* dst) {
 extern "C" {
 
 static void ensure_p2(fk_handle h);   // P2 contribution plan (defined with the P2 entry points below)
+static void ensure_ned(fk_handle h);  // edge elements: the same, 21 local pairs
 
 const char* fk_last_error(void) { return fk::g_err.c_str(); }
 int fk_set_host_threads(int n) {
@@ -814,8 +815,11 @@ int fk_set_host_threads(int n) {
 }
 int fk_version(void) { return 100; }
 
-int fk_create(const double* p, const int* t, int nv, int nt, const double* VE, const fk_create_opts* opts, fk_handle* out) {
-  return guard([&]() {
+// fk_create and fk_create_edge.  t = the connectivity of the DEGREES OF FREEDOM (npe x nt, ids < nv); t_vertices = the four
+// vertices of every element when t does not start with them (edge elements), n_points = points in p
+static int create_impl(const double* p, int n_points, const int* t, int nv, int nt, const double* VE, const fk_create_opts* opts,
+                       const int* t_vertices, fk_handle* out) {
+  {
     need(out != nullptr, "fk_create: out is NULL");
     *out = nullptr;
     need(p && t, "fk_create: p and t must not be NULL");
@@ -835,9 +839,13 @@ int fk_create(const double* p, const int* t, int nv, int nt, const double* VE, c
     h->num_sms = prop.multiProcessorCount;
     h->nv = nv;
     h->nt = nt;
+    h->n_points = n_points;
+    h->edge_dofs = t_vertices != nullptr;
 
     SymbolicOpts so = to_symbolic_opts(o);
-    build_symbolic(p, t, nv, nt, so, h->sym);
+    if (h->edge_dofs) so.npe = 6;
+    else need(so.npe != 6, "fk_create: 6 degrees of freedom per element are edge elements: use fk_create_edge");
+    build_symbolic(h->edge_dofs ? nullptr : p, t, nv, nt, so, h->sym);
     const Symbolic& S = h->sym;
     h->n_rows = S.n_rows;
     h->nnz = S.nnz;
@@ -845,9 +853,9 @@ int fk_create(const double* p, const int* t, int nv, int nt, const double* VE, c
 
     cudaStream_t s = h->stream;
     // mesh: nodes padded to 32 B, connectivity as int4
-    h->st_a.upload(p, (size_t)3 * nv, s);
-    h->p4.ensure((size_t)nv);
-    pad_nodes_kernel<<<cdiv(nv, 256), 256, 0, s>>>(h->st_a.ptr, nv, h->p4.ptr);
+    h->st_a.upload(p, (size_t)3 * n_points, s);
+    h->p4.ensure((size_t)n_points);
+    pad_nodes_kernel<<<cdiv(n_points, 256), 256, 0, s>>>(h->st_a.ptr, n_points, h->p4.ptr);
     h->t4.ensure((size_t)nt);
     std::vector<int> t4host;   // P2: the vertices of every element (first four of ten) for the geometry kernels
     if (S.npe == 4) {
@@ -855,7 +863,11 @@ int fk_create(const double* p, const int* t, int nv, int nt, const double* VE, c
     } else {
       t4host.resize(4 * (size_t)nt);
       for (int k = 0; k < nt; k++)
-        for (int i = 0; i < 4; i++) t4host[4 * (size_t)k + i] = t[(size_t)S.npe * k + i];
+        for (int i = 0; i < 4; i++) {
+          const int v = t_vertices ? t_vertices[4 * (size_t)k + i] : t[(size_t)S.npe * k + i];
+          need(v >= 0 && v < n_points, "fk_create: vertex id out of range");
+          t4host[4 * (size_t)k + i] = v;
+        }
       FK_CUDA(cudaMemcpyAsync(h->t4.ptr, t4host.data(), sizeof(int) * 4 * (size_t)nt, cudaMemcpyHostToDevice, s));
       h->tP2.upload(t, (size_t)S.npe * nt, s);
       FK_CUDA(cudaStreamSynchronize(s));
@@ -925,6 +937,17 @@ int fk_create(const double* p, const int* t, int nv, int nt, const double* VE, c
     h->launches += 2;
     *out = h.release();
     return 0;
+  }
+}
+int fk_create(const double* p, const int* t, int nv, int nt, const double* VE, const fk_create_opts* opts, fk_handle* out) {
+  return guard([&]() { return create_impl(p, nv, t, nv, nt, VE, opts, nullptr, out); });
+}
+int fk_create_edge(const double* p, int n_points, const int* t4, const int* edges6, int n_edges, int nt, const double* VE,
+                   const fk_create_opts* opts, fk_handle* out) {
+  return guard([&]() {
+    need(t4 != nullptr, "fk_create_edge: t4 is NULL");
+    need(n_points > 0 && n_edges > 0, "fk_create_edge: empty mesh");
+    return create_impl(p, n_points, edges6, n_edges, nt, VE, opts, t4, out);
   });
 }
 
@@ -1145,7 +1168,7 @@ int fk_geo_stats(fk_handle h, long long* items, long long* contributions, long l
   return guard([&]() {
     need(h, "fk: NULL handle");
     DeviceGuard dg(h->device);
-    if (h->sym.npe == 10) ensure_p2(h); else ensure_geo(h);
+    if (h->sym.npe == 10) ensure_p2(h); else if (h->sym.npe == 6) ensure_ned(h); else ensure_geo(h);
     if (items) *items = h->geo_items;
     if (contributions) *contributions = h->geo_contrib;
     if (slots) *slots = h->geo_slots;
@@ -1428,6 +1451,138 @@ int fk_assemble_stiffness_p2(fk_handle h, int slot, const double* mu, double* va
 }
 int fk_assemble_mass_p2(fk_handle h, int slot, const double* F, double* vals_out) {
   return guard([&]() { return assemble_p2(h, slot, F, vals_out, true); });
+}
+
+// ---- Nedelec (edge) elements (nedelec.cuh; src/FEM3D.jl:153-271, Magnetostatics/nedelec3D.jl:104-250) ---------------------
+static void ensure_ned(fk_handle h) {
+  need(h->edge_dofs && h->sym.npe == 6, "fk: the handle does not hold edge elements (fk_create_edge)");
+  if (h->geo_ready) return;
+  RescalePlan R;
+  build_rescale_plan(h->sym, h->geo_window, R);
+  cudaStream_t s = h->stream;
+  h->geo_nslices = R.nslices;
+  h->geo_slots = R.n_slots;
+  h->geo_items = R.n_items;
+  h->geo_contrib = R.n_contrib;
+  h->ned_shift = R.pair_shift;
+  h->geo_slice_ptr.upload(R.slice_ptr, s);
+  h->geo_dst1.upload(R.dst1, s);
+  h->geo_dst2.upload(R.dst2, s);
+  h->ned_ref.upload(R.cref, s);
+  const size_t ns = (size_t)std::max<long long>(R.n_slots, 1);
+  h->geo_ref.ensure(ns);
+  h->geo_g.ensure(ns);
+  h->p2_gmass.ensure(ns);
+  h->geo_s0.ensure((size_t)h->nt);
+  if (R.n_slots > 0) {
+    const int grid = std::min(cdiv(R.n_slots, 128), h->num_sms * 16);
+    ned_strip_kernel<<<std::min(cdiv(R.n_slots, 256), h->num_sms * 16), 256, 0, s>>>(h->ned_ref.ptr, R.n_slots, R.pair_shift, h->geo_ref.ptr);
+    ned_slot_kernel<0><<<grid, 128, 0, s>>>(h->p4.ptr, h->t4.ptr, h->VE.ptr, h->ned_ref.ptr, R.n_slots, R.pair_shift, nullptr, nullptr,
+                                           nullptr, 0.0, 0.0, 0.0, h->geo_g.ptr);
+    FK_CUDA(cudaGetLastError());
+    h->launches += 2;
+  }
+  FK_CUDA(cudaStreamSynchronize(s));
+  configure_geo(h);
+  h->geo_ready = true;
+}
+int fk_nedelec_local_stiffness(fk_handle h, double* Ak) {
+  return guard([&]() {
+    need(h && Ak, "fk: NULL argument");
+    need(h->edge_dofs, "fk: the handle does not hold edge elements (fk_create_edge)");
+    DeviceGuard dg(h->device);
+    h->st_b.ensure((size_t)36 * h->nt);
+    ned_local_kernel<<<cdiv(h->nt, 128), 128, 0, h->stream>>>(h->p4.ptr, h->t4.ptr, h->VE.ptr, h->nt, h->st_b.ptr);
+    FK_CUDA(cudaGetLastError());
+    h->launches++;
+    copy_out(h, h->st_b.ptr, Ak, (size_t)36 * h->nt);
+    return 0;
+  });
+}
+int fk_assemble_nedelec_stiffness(fk_handle h, int slot, const double* nu, double* vals_out) {
+  return guard([&]() {
+    need(h, "fk: NULL handle");
+    DeviceGuard dg(h->device);
+    check_slot(slot);
+    ensure_ned(h);
+    const double* cd = nullptr;
+    if (nu) { h->st_a.upload(nu, (size_t)h->nt, h->stream); cd = h->st_a.ptr; }
+    h->dir_applied &= ~(1u << slot);
+    double* vals = slot_vals(h, slot);
+    p2_scale_kernel<<<cdiv(h->nt, 256), 256, 0, h->stream>>>(cd, h->nt, h->geo_s0.ptr);
+    h->launches++;
+    launch_geo_rescale(h, vals, 0, h->geo_g.ptr);
+    copy_out_matrix(h, vals, vals_out);
+    return 0;
+  });
+}
+int fk_assemble_nedelec_tangential(fk_handle h, int slot, const double* dnu, const double* Bfield, const double* B, double* vals_out) {
+  return guard([&]() {
+    need(h && dnu && Bfield && B, "fk: NULL argument");
+    DeviceGuard dg(h->device);
+    check_slot(slot);
+    ensure_ned(h);
+    cudaStream_t s = h->stream;
+    h->st_a.upload(dnu, (size_t)h->nt, s);
+    h->st_b.upload(Bfield, (size_t)3 * h->nt, s);
+    h->st_c.upload(B, (size_t)h->nt, s);
+    h->dir_applied &= ~(1u << slot);
+    double* vals = slot_vals(h, slot);
+    if (h->geo_slots > 0) {
+      ned_slot_kernel<1><<<std::min(cdiv(h->geo_slots, 128), h->num_sms * 16), 128, 0, s>>>(
+          h->p4.ptr, h->t4.ptr, h->VE.ptr, h->ned_ref.ptr, h->geo_slots, h->ned_shift, h->st_a.ptr, h->st_b.ptr, h->st_c.ptr, 0.0, 0.0, 0.0,
+          h->p2_gmass.ptr);
+      FK_CUDA(cudaGetLastError());
+    }
+    p2_scale_kernel<<<cdiv(h->nt, 256), 256, 0, s>>>(nullptr, h->nt, h->geo_s0.ptr);
+    h->launches += 2;
+    launch_geo_rescale(h, vals, 0, h->p2_gmass.ptr);
+    copy_out_matrix(h, vals, vals_out);
+    return 0;
+  });
+}
+int fk_nedelec_load_vector(fk_handle h, const double* Bext, double* rhs_out) {
+  return guard([&]() {
+    need(h && Bext && rhs_out, "fk: NULL argument");
+    DeviceGuard dg(h->device);
+    ensure_ned(h);
+    cudaStream_t s = h->stream;
+    h->ned_vals.ensure((size_t)h->nnz_sell + kSlack);
+    FK_CUDA(cudaMemsetAsync(h->ned_vals.ptr, 0, sizeof(double) * ((size_t)h->nnz_sell + kSlack), s));
+    if (h->geo_slots > 0) {
+      ned_slot_kernel<2><<<std::min(cdiv(h->geo_slots, 128), h->num_sms * 16), 128, 0, s>>>(
+          h->p4.ptr, h->t4.ptr, h->VE.ptr, h->ned_ref.ptr, h->geo_slots, h->ned_shift, nullptr, nullptr, nullptr, Bext[0], Bext[1], Bext[2],
+          h->p2_gmass.ptr);
+      FK_CUDA(cudaGetLastError());
+    }
+    p2_scale_kernel<<<cdiv(h->nt, 256), 256, 0, s>>>(nullptr, h->nt, h->geo_s0.ptr);
+    h->launches += 2;
+    launch_geo_rescale(h, h->ned_vals.ptr, 0, h->p2_gmass.ptr);
+    h->st_d.ensure((size_t)h->nv);
+    gather_diag_kernel<<<cdiv(h->n_rows, 256), 256, 0, s>>>(h->ned_vals.ptr, h->sell_diag.ptr, h->n_rows, h->st_d.ptr);
+    FK_CUDA(cudaGetLastError());
+    h->launches++;
+    copy_out(h, h->st_d.ptr, rhs_out, (size_t)h->n_rows);
+    return 0;
+  });
+}
+int fk_nedelec_recover_field(fk_handle h, const double* u, double* Bfield_out, double* B_out) {
+  return guard([&]() {
+    need(h && u, "fk: NULL argument");
+    need(h->edge_dofs, "fk: the handle does not hold edge elements (fk_create_edge)");
+    DeviceGuard dg(h->device);
+    cudaStream_t s = h->stream;
+    h->st_c.upload(u, (size_t)h->nv, s);
+    h->st_b.ensure((size_t)3 * h->nt);
+    h->st_a.ensure((size_t)h->nt);
+    ned_recover_kernel<<<cdiv(h->nt, 128), 128, 0, s>>>(h->p4.ptr, h->t4.ptr, h->tP2.ptr, h->st_c.ptr, h->nt, h->st_b.ptr, h->st_a.ptr);
+    FK_CUDA(cudaGetLastError());
+    h->launches++;
+    if (Bfield_out) copy_out(h, h->st_b.ptr, Bfield_out, (size_t)3 * h->nt);
+    if (B_out) copy_out(h, h->st_a.ptr, B_out, (size_t)h->nt);
+    FK_CUDA(cudaStreamSynchronize(s));
+    return 0;
+  });
 }
 
 // 2-D P1 triangles (src/FEM2D.jl:48-76 stiffnessMatrix2D, :139-161 massMatrix2D) on a handle created from the elements

@@ -162,6 +162,13 @@ struct fk_handle_s {
   fk::DevBuf<int> geo_dst1, geo_dst2;
   fk::DevBuf<int> tP2;                 // P2 handles: the 10-node connectivity (t4 holds the vertices)
   fk::DevBuf<double> p2_gmass;         // P2: mass factors per contribution slot (geo_g holds the stiffness factors)
+  // Nedelec (edge) handles: nv = number of EDGES (the degrees of freedom), n_points = points of the geometry, t4 = vertices,
+  // tP2 = the 6 edge labels of every element; ned_ref keeps the pair bits geo_ref has lost, p2_gmass is the per-call slot scratch
+  int n_points = 0;
+  bool edge_dofs = false;
+  int ned_shift = 26;
+  fk::DevBuf<uint32_t> ned_ref;
+  fk::DevBuf<double> ned_vals;         // scratch matrix of the load-vector sum
   // fk_tune(h, 11, n): device-side timeline of the PCG kernels (kernels.cuh: trace_rec)
   fk::DevBuf<unsigned long long> trace;
   int trace_cap = 0;

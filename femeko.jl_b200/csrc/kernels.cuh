@@ -459,6 +459,7 @@ __device__ __forceinline__ double splev_dev(const SplineDev& S, double x, int& e
 #include "assemble.cuh"
 #include "rescale.cuh"
 #include "p2.cuh"
+#include "nedelec.cuh"
 #include "demag.cuh"
 
 // mu(|H|), dmu/dH of the material elements from the B-H spline (NewtonRaphson.jl:178-207; manyBodyIntersecting.jl:189-197),

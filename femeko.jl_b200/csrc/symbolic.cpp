@@ -32,7 +32,8 @@ void build_symbolic(const double* p, const int* t, int nv, int nt, const Symboli
   if (nv <= 0 || nt <= 0) throw std::runtime_error("fk: empty mesh (nv and nt must be positive)");
   if (o.tile_max_elems < 1 || o.tile_max_elems > 4096) throw std::runtime_error("fk: tile_max_elems must be in [1, 4096]");
   const int npe = o.npe;
-  if (npe != 4 && npe != 10) throw std::runtime_error("fk: nodes per element must be 4 (P1) or 10 (P2)");
+  if (npe != 4 && npe != 10 && npe != 6)
+    throw std::runtime_error("fk: nodes per element must be 4 (P1), 10 (P2) or 6 (the edges of a Nedelec element)");
   if ((int64_t)nt * npe >= (int64_t)1 << 32) throw std::runtime_error("fk: nt too large for 32-bit incidence ids");
   S.npe = npe;
   S.nv = nv;

@@ -35,6 +35,7 @@ class Femeko:
         self.lib = L.load()
         self.mesh = mesh
         o = L.fk_create_opts()
+        nedelec = bool(opts.pop("nedelec", False))
         for k, v in opts.items():
             setattr(o, k, int(v))
         if device is None:
@@ -49,14 +50,23 @@ class Femeko:
             t = np.vstack([t, t[2:3]])
             if p.shape[0] == 2:
                 p = np.vstack([p, np.zeros((1, p.shape[1]))])
-        if t.shape[0] == 10:  # P2 tetrahedra (fk_assemble_*_p2)
+        self.edge_dofs = nedelec
+        if t.shape[0] == 10 and not self.edge_dofs:  # P2 tetrahedra (fk_assemble_*_p2)
             self.dim, o.nodes_per_element = 3, 10
         assert p.shape[0] == 3 and t.shape[0] in (4, 10), "mesh.p must be 3 x nv and mesh.t 4 x nt (3 x nt triangles, 10 x nt P2)"
         p = np.asfortranarray(p)
         t = np.asfortranarray(t)
         VE = L.f64(mesh.VE) if (use_mesh_VE and mesh.VE is not None) else None
         h = C.c_void_p()
-        L.check(self.lib.fk_create(L.dptr(p), L.iptr(t), int(p.shape[1]), int(t.shape[1]), L.dptr(VE), C.byref(o), C.byref(h)))
+        if self.edge_dofs:    # Nedelec elements on an order-2 mesh: degrees of freedom = edges (Magnetostatics/nedelec3D.jl)
+            from .mesh import edgeDofs
+            assert t.shape[0] == 10, "edge elements need an order-2 mesh (10 x nt connectivity: the mid nodes label the edges)"
+            self.edges6 = edgeDofs(mesh)
+            t4 = np.asfortranarray(t[:4])
+            L.check(self.lib.fk_create_edge(L.dptr(p), int(p.shape[1]), L.iptr(t4), L.iptr(self.edges6), int(mesh.ne), int(t.shape[1]),
+                                            L.dptr(VE), C.byref(o), C.byref(h)))
+        else:
+            L.check(self.lib.fk_create(L.dptr(p), L.iptr(t), int(p.shape[1]), int(t.shape[1]), L.dptr(VE), C.byref(o), C.byref(h)))
         self.h = h
         nv, nt, nnz, ntl = C.c_int(), C.c_int(), C.c_longlong(), C.c_int()
         L.check(self.lib.fk_sizes(h, C.byref(nv), C.byref(nt), C.byref(nnz), C.byref(ntl)))
@@ -179,6 +189,38 @@ class Femeko:
         v = self._vals(want_vals)
         L.check(self.lib.fk_assemble_mass_p2(self.h, slot, L.dptr(self._coef(F)), L.dptr(v)))
         return v
+
+    # -- Nedelec (edge) elements: handles made with Femeko(mesh, nedelec=True) ------------------------------------------
+    def nedelec_local_stiffness(self):
+        """nedelecLocalStiffness (src/FEM3D.jl:153-194): 36 x nt, Ak[6 ie + je, k]."""
+        Ak = np.zeros((36, self.nt), order="F")
+        L.check(self.lib.fk_nedelec_local_stiffness(self.h, L.dptr(Ak)))
+        return Ak
+
+    def assemble_nedelec_stiffness(self, nu=None, slot=0, want_vals=True):
+        v = self._vals(want_vals)
+        L.check(self.lib.fk_assemble_nedelec_stiffness(self.h, slot, L.dptr(self._coef(nu)), L.dptr(v)))
+        return v
+
+    def assemble_nedelec_tangential(self, dnu, Bfield, B, slot=2, want_vals=True):
+        v = self._vals(want_vals)
+        Bf = np.asfortranarray(np.asarray(Bfield, dtype=np.float64))
+        assert Bf.shape == (3, self.nt)
+        L.check(self.lib.fk_assemble_nedelec_tangential(self.h, slot, L.dptr(self._coef(dnu)), L.dptr(Bf), L.dptr(self._coef(B)), L.dptr(v)))
+        return v
+
+    def nedelec_load_vector(self, Bext):
+        rhs = np.zeros(self.nv)
+        L.check(self.lib.fk_nedelec_load_vector(self.h, L.dptr(np.ascontiguousarray(Bext, dtype=np.float64)), L.dptr(rhs)))
+        return rhs
+
+    def nedelec_recover_field(self, u):
+        u = np.ascontiguousarray(u, dtype=np.float64)
+        assert u.shape[0] == self.nv
+        Bf = np.zeros((3, self.nt), order="F")
+        B = np.zeros(self.nt)
+        L.check(self.lib.fk_nedelec_recover_field(self.h, L.dptr(u), L.dptr(Bf), L.dptr(B)))
+        return Bf, B
 
     def assemble_mass(self, rho=None, slot=1, want_vals=True):
         v = self._vals(want_vals)
@@ -461,6 +503,7 @@ class FemekoMulti:
         self.lib = L.load()
         self.mesh = mesh
         o = L.fk_create_opts()
+        nedelec = bool(opts.pop("nedelec", False))
         for k, v in opts.items():
             setattr(o, k, int(v))
         p = np.asfortranarray(L.f64(mesh.p))
@@ -621,6 +664,31 @@ def quadraticMassMatrix(mesh: MESH, S=None, F=None) -> SparseCSR:
     """src/FEM3D.jl:494-561."""
     fk = _handle(mesh)
     return SparseCSR(fk, 1, fk.assemble_mass_p2(F, slot=1))
+
+
+def _edge_handle(mesh: MESH) -> Femeko:
+    fk = getattr(mesh, "_fk_edge", None)
+    if fk is None or not fk.h.value:
+        fk = Femeko(mesh, nedelec=True)
+        mesh._fk_edge = fk
+    return fk
+
+
+def nedelecLocalStiffness(mesh: MESH) -> np.ndarray:
+    """src/FEM3D.jl:153-194 on an order-2 mesh: 36 x nt."""
+    return _edge_handle(mesh).nedelec_local_stiffness()
+
+
+def nedelecStiffnessMatrix(mesh: MESH, nu=None) -> SparseCSR:
+    """The global curl-curl matrix the reference's Newton loop builds inline (Magnetostatics/nedelec3D.jl:163-178)."""
+    fk = _edge_handle(mesh)
+    return SparseCSR(fk, 0, fk.assemble_nedelec_stiffness(nu, slot=0))
+
+
+def nedelecTangentialStiffness(mesh: MESH, dnu, Bfield, B) -> SparseCSR:
+    """src/FEM3D.jl:197-271."""
+    fk = _edge_handle(mesh)
+    return SparseCSR(fk, 2, fk.assemble_nedelec_tangential(dnu, Bfield, B, slot=2))
 
 
 def tangentialStiffnessMatrix(mesh: MESH, H_vec, dmu) -> SparseCSR:

@@ -103,3 +103,63 @@ def newton_raphson(mesh: MESH, Bext, spl: Spline1D, spl_dmu: Spline1D, maxDeviat
     res.Hfield, res.H = fk.get_field()
     res.mu = fk.get_mu()
     return res
+
+
+@dataclass
+class NedelecResult:
+    u: np.ndarray            # magnetic vector potential on the edges
+    Bfield: np.ndarray       # 3 x nt
+    B: np.ndarray            # nt
+    nu: np.ndarray           # relative reluctance
+    dnu: np.ndarray
+    att: int
+    div: float
+    history: list = field(default_factory=list)
+    pcg_iters: int = 0
+
+
+def nedelec3D(mesh: MESH, Bext, spl_nu: Spline1D, spl_dnu: Spline1D, tol: float = 1e-4, maxAtt: int = 30, fk: Femeko | None = None,
+              cg_tol: float = 1e-12, cg_maxiter: int | None = None, verbose: bool = False) -> NedelecResult:
+    """Newton-Raphson on the magnetic vector potential with Nedelec elements (Magnetostatics/nedelec3D.jl:104-250): load
+    vector VE Bext . curlN (:108-146); each pass A = curl-curl matrix scaled by nu (:163-178), At = nedelecTangentialStiffness
+    from the second pass on (:181-185), du = cg(A + At, RHS - A u) (:188), lineSearch (:191), B = curl u and |B| (:194-236),
+    nu = spl(B), dnu = spl_dnu(B) on the inside elements (:239-240), div = max |B - Bold| (:248).  The matrices, the solve, the
+    line search and the field recovery run on the GPU; the two spline evaluations over the inside elements are fk_spline_apply.
+    The curl-curl system is singular (gradients); like the reference's cg call the solve is a plain Jacobi-CG on the
+    consistent system -- B does not depend on the gauge."""
+    fk = fk or Femeko(mesh, nedelec=True)
+    fk.set_spline(0, spl_nu)
+    fk.set_spline(1, spl_dnu)
+    ins = np.asarray(mesh.InsideElements, dtype=np.int64)
+    RHS = fk.nedelec_load_vector(np.asarray(Bext, dtype=np.float64))
+    nu = np.ones(mesh.nt)
+    dnu = np.zeros(mesh.nt)
+    u = np.zeros(fk.nv)
+    Bf = np.zeros((3, mesh.nt), order="F")
+    B = np.zeros(mesh.nt)
+    res = NedelecResult(u=u, Bfield=Bf, B=B, nu=nu, dnu=dnu, att=0, div=np.inf)
+    while res.div > tol and res.att < maxAtt:
+        res.att += 1
+        Bold = B.copy()
+        fk.assemble_nedelec_stiffness(nu, slot=0, want_vals=False)
+        slot = 0
+        if res.att > 1:
+            fk.assemble_nedelec_tangential(dnu, Bf, B, slot=2, want_vals=False)
+            fk.matrix_axpby(3, 1.0, 0, 1.0, 2)                           # A + At
+            slot = 3
+        r, _ = fk.residual(u, RHS, slot=0)                                # RHS - A*u
+        du, it, _ = fk.pcg(r, slot=slot, tol=cg_tol, max_iter=cg_maxiter or 0)
+        residue, step = fk.line_search(u, du, RHS, slot=0)
+        Bf, B = fk.nedelec_recover_field(u)
+        if ins.size:
+            nu[ins] = fk.spline_apply(0, B[ins])
+            dnu[ins] = fk.spline_apply(1, B[ins])
+        if not (np.all(np.isfinite(nu)) and np.all(np.isfinite(dnu))):
+            raise FloatingPointError("Nans in the interpolation")          # nedelec3D.jl:243-245
+        res.div = float(np.max(np.abs(B - Bold)))
+        res.pcg_iters += it
+        res.history.append((res.att, res.div, it, residue, step))
+        if verbose:
+            print(res.att, " , |B(n)-B(n-1)| = ", res.div, " , |y-Ax| = ", residue)
+    res.Bfield, res.B = Bf, B
+    return res

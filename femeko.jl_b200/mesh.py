@@ -46,6 +46,8 @@ class MESH:
     nInside: int = 0
     nInsideNodes: int = 0
     shell_id: list = field(default_factory=list)
+    edges: np.ndarray = None        # order-2 meshes: mid-node label of every edge, in order of first appearance (src/mesh.jl:171)
+    edge2localMap: np.ndarray = None    # mid-node label -> edge label (0-based; -1 where the label is not a mid node)
 
 
 def elementVolume(p: np.ndarray, t: np.ndarray) -> np.ndarray:
@@ -378,6 +380,31 @@ def to_p2(mesh: MESH) -> MESH:
     out.ns = 0
     out.order = 2
     return out
+
+
+# local edge -> local vertex pair before the orientation swap (NodesFromLocalEdge, src/mesh.jl:603-637; Gmsh's edge order)
+NEDELEC_EDGES = ((0, 1), (1, 2), (2, 0), (3, 0), (2, 3), (1, 3))
+
+
+def edgeNumbering(mesh: MESH) -> MESH:
+    """Edge labels of an order-2 mesh as Mesh() makes them (src/mesh.jl:170-185): mesh.edges = unique(t[5:10, :]) -- Julia's
+    unique walks the 6 x nt block column by column and keeps the order of FIRST APPEARANCE --, mesh.ne, and
+    mesh.edge2localMap[mid-node label] = edge label (0-based here).  Returns the mesh."""
+    assert mesh.t.shape[0] == 10, "edge numbering needs an order-2 mesh (10 x nt connectivity)"
+    mids = np.asarray(mesh.t[4:10]).reshape(-1, order="F")
+    uniq, first = np.unique(mids, return_index=True)
+    mesh.edges = uniq[np.argsort(first, kind="stable")].astype(np.int32)
+    mesh.ne = int(mesh.edges.size)
+    mesh.edge2localMap = np.full(int(mesh.edges.max()) + 1, -1, dtype=np.int32)
+    mesh.edge2localMap[mesh.edges] = np.arange(mesh.ne, dtype=np.int32)
+    return mesh
+
+
+def edgeDofs(mesh: MESH) -> np.ndarray:
+    """6 x nt edge labels of every element: edge2localMap[t[5:10, :]] (Magnetostatics/nedelec3D.jl:170)."""
+    if mesh.edge2localMap is None:
+        edgeNumbering(mesh)
+    return np.asfortranarray(mesh.edge2localMap[np.asarray(mesh.t[4:10])].astype(np.int32))
 
 
 def kuhn_cube_p2(N: int, L: float = 1.0, inside_edge: float = 0.2) -> MESH:

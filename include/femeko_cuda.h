@@ -185,6 +185,26 @@ int fk_assemble_mass2d(fk_handle h, int slot, const double* rho /* nt or NULL */
  * reference are the Lagrange P2 functions on straight-sided elements and are used in closed form.  coef: nt or NULL. */
 int fk_assemble_stiffness_p2(fk_handle h, int slot, const double* mu, double* vals_out /* nnz or NULL */);
 int fk_assemble_mass_p2(fk_handle h, int slot, const double* F, double* vals_out);
+/* Nedelec (lowest-order edge) elements: the magnetic vector potential of Magnetostatics/nedelec3D.jl.  Degrees of freedom
+ * = the edges of an order-2 mesh, edge2localMap[t[5:10, :]] (src/mesh.jl:170-185), local edge order and orientation of
+ * NodesFromLocalEdge (src/mesh.jl:603-637: (0,1) (1,2) (2,0) (3,0) (2,3) (1,3), each directed from the lower to the higher
+ * global vertex label), curl N_e = 2 L_e grad(lambda_i) x grad(lambda_j).
+ * fk_create_edge: p = 3 x n_points, t4 = 4 x nt vertex ids, edges6 = 6 x nt edge labels in [0, n_edges); the handle's matrix
+ * is n_edges x n_edges (fk_sizes reports nv = n_edges), pattern = sparsity of the reference's sum of sparse(edge1, edge2, ...).
+ * fk_spmv / fk_pcg / fk_residual / fk_line_search / fk_matrix_axpby / fk_set_dirichlet work on it as on any handle.
+ *   fk_nedelec_local_stiffness      nedelecLocalStiffness (src/FEM3D.jl:153-194): Ak[6 ie + je, k] = VE curlN_ie . curlN_je
+ *   fk_assemble_nedelec_stiffness   the global matrix of nedelec3D.jl:163-178: sum of sparse(edge1, edge2, Ak[n, :] .* nu)
+ *   fk_assemble_nedelec_tangential  nedelecTangentialStiffness (src/FEM3D.jl:197-271); |B| = 0 gives NaN as in the reference
+ *   fk_nedelec_load_vector          RHS[e] += VE Bext . curlN (nedelec3D.jl:108-146)
+ *   fk_nedelec_recover_field        Bfield[:, k] = sum_i u[e_i] curlN_i, B = |Bfield| (nedelec3D.jl:196-236)              */
+int fk_create_edge(const double* p, int n_points, const int* t4, const int* edges6, int n_edges, int nt, const double* VE /* nt or NULL */,
+                   const fk_create_opts* opts, fk_handle* out);
+int fk_nedelec_local_stiffness(fk_handle h, double* Ak /* 36 x nt */);
+int fk_assemble_nedelec_stiffness(fk_handle h, int slot, const double* nu /* nt or NULL */, double* vals_out /* nnz or NULL */);
+int fk_assemble_nedelec_tangential(fk_handle h, int slot, const double* dnu /* nt */, const double* Bfield /* 3 x nt */,
+                                   const double* B /* nt */, double* vals_out /* nnz or NULL */);
+int fk_nedelec_load_vector(fk_handle h, const double* Bext /* 3 */, double* rhs_out /* n_edges */);
+int fk_nedelec_recover_field(fk_handle h, const double* u /* n_edges */, double* Bfield_out /* 3 x nt or NULL */, double* B_out /* nt or NULL */);
 int fk_local_stiffness(fk_handle h, const double* f, double* Ak /* 16 x nt */);          /* FEM3D.jl:59-76 */
 int fk_assemble_stiffness_dev(fk_handle h, int slot, const double* f_dev);
 int fk_assemble_mass_dev(fk_handle h, int slot, const double* rho_dev);

@@ -667,3 +667,155 @@ def quadratic_mass(mesh, S=None, F=None):
         Mk = (phi * (w * mesh.VE[k])) @ phi.T * F[k]
         Ml[:, k] = Mk.ravel(order="F")
     return _assemble_npe(mesh, Ml)
+
+
+# --------------------------------------------------------------------------------------------------
+# Nedelec (lowest-order edge) elements: src/FEM3D.jl:153-271, Magnetostatics/nedelec3D.jl:104-250 -- numpy restatement,
+# test infrastructure only.  Julia-only code (no C++ twin, Julia absent here): parity unpinned against Julia itself.
+# --------------------------------------------------------------------------------------------------
+NED_EDGES = ((0, 1), (1, 2), (2, 0), (3, 0), (2, 3), (1, 3))   # NodesFromLocalEdge before the sort (src/mesh.jl:603-637)
+
+
+def edge_numbering(t10):
+    """mesh.edges / edge2localMap of src/mesh.jl:170-185: unique mid-node labels in order of first appearance (Julia's
+    unique over the column-major 6 x nt block); returns (edges, map) with map[mid label] = 0-based edge label."""
+    mids = np.asarray(t10[4:10]).reshape(-1, order="F")
+    seen, edges = {}, []
+    for m in mids.tolist():
+        if m not in seen:
+            seen[m] = len(edges)
+            edges.append(m)
+    mp = np.full(max(edges) + 1, -1, dtype=np.int64)
+    mp[np.asarray(edges)] = np.arange(len(edges))
+    return np.asarray(edges, dtype=np.int64), mp
+
+
+def _hat_all(mesh):
+    """abcd of the four vertices of every element (src/FEM3D.jl:5-17): hat[k, :, i] = (a, b, c, d) of vertex i."""
+    t = np.asarray(mesh.t[:4], dtype=np.int64)
+    P = np.asarray(mesh.p)[:, t]                                    # 3 x 4 x nt
+    M = np.concatenate([np.ones((1, 4, t.shape[1])), P]).transpose(2, 1, 0)   # nt x vertex x (1, x, y, z)
+    return np.linalg.solve(M, np.broadcast_to(np.eye(4), M.shape))
+
+
+def nedelec_curls(mesh):
+    """curl N_e = 2 L_e grad(lambda_i) x grad(lambda_j) of the six edges of every element, (i, j) = the edge's vertices
+    sorted by global label (src/FEM3D.jl:169-181, src/mesh.jl:630-634): nt x 6 x 3."""
+    t = np.asarray(mesh.t[:4], dtype=np.int64)
+    nt = t.shape[1]
+    hat = _hat_all(mesh)
+    p = np.asarray(mesh.p)
+    ks = np.arange(nt)
+    out = np.zeros((nt, 6, 3))
+    for ie, (a, b) in enumerate(NED_EDGES):
+        swap = t[a] > t[b]
+        i = np.where(swap, b, a)
+        j = np.where(swap, a, b)
+        L = np.linalg.norm(p[:, t[j, ks]] - p[:, t[i, ks]], axis=0)
+        gi = hat[ks, 1:4, i]
+        gj = hat[ks, 1:4, j]
+        out[:, ie] = (2.0 * L)[:, None] * np.cross(gi, gj)
+    return out
+
+
+def nedelec_local_stiffness(mesh):
+    """nedelecLocalStiffness (src/FEM3D.jl:153-194): Ak[6 ie + je, k] = VE[k] curlN_ie . curlN_je."""
+    c = nedelec_curls(mesh)
+    Ak = np.zeros((36, mesh.nt))
+    for ie in range(6):
+        for je in range(6):
+            Ak[6 * ie + je] = mesh.VE * np.einsum("kd,kd->k", c[:, ie], c[:, je])
+    return Ak
+
+
+def _assemble_dofs(E, ndof, Ak):
+    """A = sum over the local pairs (i outer, j inner) of sparse(E[i], E[j], Ak[n], ndof, ndof) on the canonical pattern
+    (nedelec3D.jl:166-178, src/FEM3D.jl:257-268)."""
+    class _M:
+        pass
+    m = _M()
+    m.t, m.nv = np.asarray(E), int(ndof)
+    return _assemble_npe(m, Ak)
+
+
+def nedelec_stiffness(mesh, nu=None):
+    """Global curl-curl matrix of the Newton loop (nedelec3D.jl:163-178): sum of sparse(edge1, edge2, Ak[n, :] .* nu)."""
+    edges, mp = edge_numbering(mesh.t)
+    E = mp[np.asarray(mesh.t[4:10])]
+    Ak = nedelec_local_stiffness(mesh)
+    if nu is not None:
+        Ak = Ak * np.asarray(nu)[None, :]
+    return _assemble_dofs(E, len(edges), Ak)
+
+
+def nedelec_tangential(mesh, dnu, Bfield, B):
+    """nedelecTangentialStiffness (src/FEM3D.jl:197-271): Alocal[i, j] = VE (curlN_i . B)(curlN_j . B) dnu / |B| for j >= i,
+    mirrored below the diagonal."""
+    edges, mp = edge_numbering(mesh.t)
+    E = mp[np.asarray(mesh.t[4:10])]
+    c = nedelec_curls(mesh)
+    Bf = np.asarray(Bfield).T                                       # nt x 3
+    d = np.einsum("ked,kd->ke", c, Bf)
+    Ak = np.zeros((36, mesh.nt))
+    with np.errstate(divide="ignore", invalid="ignore"):
+        for i in range(6):
+            for j in range(i, 6):
+                v = mesh.VE * d[:, i] * d[:, j] * np.asarray(dnu) / np.asarray(B)
+                Ak[6 * i + j] = v
+                Ak[6 * j + i] = v
+    return _assemble_dofs(E, len(edges), Ak)
+
+
+def nedelec_load(mesh, Bext):
+    """Load vector of nedelec3D.jl:108-146: RHS[e] += VE[k] Bext . curlN, elements outer, local edges inner."""
+    edges, mp = edge_numbering(mesh.t)
+    E = mp[np.asarray(mesh.t[4:10])]
+    c = nedelec_curls(mesh)
+    contrib = mesh.VE[:, None] * (c @ np.asarray(Bext, dtype=np.float64))   # nt x 6
+    rhs = np.zeros(len(edges))
+    np.add.at(rhs, E.T.reshape(-1), contrib.reshape(-1))             # k-major, the loop order of the reference
+    return rhs
+
+
+def nedelec_recover_B(mesh, u):
+    """Bfield[:, k] = sum_i u[e_i] curlN_i, B = |Bfield| (nedelec3D.jl:196-236)."""
+    edges, mp = edge_numbering(mesh.t)
+    E = mp[np.asarray(mesh.t[4:10])]
+    c = nedelec_curls(mesh)
+    Bf = np.zeros((3, mesh.nt))
+    for i in range(6):
+        Bf += (np.asarray(u)[E[i]][:, None] * c[:, i]).T
+    return Bf, np.sqrt(Bf[0] ** 2 + Bf[1] ** 2 + Bf[2] ** 2)
+
+
+def nedelec_newton_loop(mesh, Bext, tck_nu, tck_dnu, tol=1e-4, max_att=30, cg_tol=1e-12, bc="nearest"):
+    """Newton-Raphson loop on the magnetic vector potential (nedelec3D.jl:148-250).  The reference solves with
+    IterativeSolvers.cg on the singular curl-curl system; here scipy's CG at cg_tol (B = curl of u is gauge independent)."""
+    import scipy.sparse.linalg as spl
+
+    edges, _ = edge_numbering(mesh.t)
+    ne = len(edges)
+    RHS = nedelec_load(mesh, Bext)
+    nu = np.ones(mesh.nt)
+    dnu = np.zeros(mesh.nt)
+    u = np.zeros(ne)
+    Bf = np.zeros((3, mesh.nt))
+    B = np.zeros(mesh.nt)
+    ins = np.asarray(mesh.InsideElements)
+    att, div, hist = 0, np.inf, []
+    while div > tol and att < max_att:
+        att += 1
+        Bold = B.copy()
+        rp, ci, v = nedelec_stiffness(mesh, nu)
+        A = _csr(rp, ci, v, ne)
+        vt = nedelec_tangential(mesh, dnu, Bf, B)[2] if att > 1 else np.zeros_like(v)
+        du, info = spl.cg(_csr(rp, ci, v + vt, ne), RHS - A @ u, rtol=cg_tol, atol=0.0, maxiter=20 * ne)
+        residue, alf = line_search(u, du, A, RHS)
+        Bf, B = nedelec_recover_B(mesh, u)
+        nu[ins] = splev(tck_nu[0], tck_nu[1], 3, B[ins], bc)
+        dnu[ins] = splev(tck_dnu[0], tck_dnu[1], 3, B[ins], bc)
+        if not (np.all(np.isfinite(nu)) and np.all(np.isfinite(dnu))):
+            raise FloatingPointError("Nans in the interpolation")
+        div = float(np.max(np.abs(B - Bold)))
+        hist.append((att, div, residue, alf))
+    return dict(u=u, Bfield=Bf, B=B, nu=nu, dnu=dnu, att=att, div=div, history=hist)

@@ -241,3 +241,36 @@ def test_p2_symbolic_and_contribution_plan():
     assert np.all(written == 1) and int((plan["r_cref"] != 0xFFFFFFFF).sum()) == 55 * m.nt
     _, _, vref = orc.quadratic_stiffness(m, S, mu)
     assert np.max(np.abs(vals - vref)) < 1e-12 * np.max(np.abs(vref))
+
+
+def test_nedelec_symbolic_and_contribution_plan():
+    """Edge elements: the symbolic phase on the 6 edge labels of every element (edge2localMap[t[5:10, :]], src/mesh.jl:170-185)
+    gives the pattern of the reference's sum of sparse(edge1, edge2, ...) and a contribution plan (21 local pairs) whose
+    execution on the oracle's nedelecLocalStiffness reproduces the global curl-curl matrix (nedelec3D.jl:163-178)."""
+    from femeko_jl_b200 import mesh as M
+
+    m = fk.to_p2(fk.delaunay_ball(200, seed=2))
+    M.edgeNumbering(m)
+    ed, mp = orc.edge_numbering(m.t)                   # the oracle's literal first-appearance walk
+    assert np.array_equal(ed, m.edges) and np.array_equal(mp, m.edge2localMap)
+    assert not np.array_equal(m.edges, np.sort(m.edges)), "Julia's unique() keeps first appearance, not sorted order"
+
+    class Shim:
+        pass
+    e = Shim()
+    e.t, e.nv, e.nt, e.p = M.edgeDofs(m), m.ne, m.nt, np.zeros((3, m.ne), order="F")
+    plan = export_symbolic(e, nodes_per_element=6)
+    rp, ci = orc.pattern_npe(e.t, e.nv)
+    assert np.array_equal(plan["rowptr"], rp) and np.array_equal(plan["colind"], ci) and plan["ntiles"] == 0
+    nu = np.linspace(1.0, 3.0, m.nt)
+    Ak = orc.nedelec_local_stiffness(m)
+    G21 = np.zeros((21, m.nt))
+    n = 0
+    for a in range(6):
+        for b in range(a, 6):
+            G21[n] = Ak[6 * a + b]
+            n += 1
+    vals, written = run_rescale_plan(plan, G21, nu, shift=26)
+    assert np.all(written == 1) and int((plan["r_cref"] != 0xFFFFFFFF).sum()) == 21 * m.nt
+    _, _, vref = orc.nedelec_stiffness(m, nu)
+    assert np.max(np.abs(vals - vref)) < 1e-12 * np.max(np.abs(vref))

@@ -230,3 +230,57 @@ def test_p2_oracle_properties():
     q = m.p[0] ** 2 + m.p[1] * m.p[2]                    # in the P2 space: 6 q'Mq = int q^2 over the unit cube
     exact = 1 / 80 + 1 / 144                              # int x^4 + int y^2 z^2 over [-1/2, 1/2]^3 (cross term vanishes)
     assert np.isclose(6.0 * (q @ (M @ q)), exact, rtol=1e-10)
+
+
+def test_nedelec_restatement_properties():
+    """Edge elements (src/FEM3D.jl:153-271, nedelec3D.jl): no C++ twin and no Julia here, so the restatement is pinned by what the
+    lowest-order Nedelec space must satisfy with the reference's conventions (edge order and orientation of
+    NodesFromLocalEdge, curl N = 2 L grad l_i x grad l_j): gradients lie in the null space of the curl-curl matrix, the
+    interpolant of A = B0 x r / 2 recovers the constant B0 exactly, the matrix is symmetric, the tangential matrix follows
+    its definition entry by entry, and the load vector equals A_1 u for that interpolant (integration by parts on constants)."""
+    import femeko_jl_b200 as fk
+    from femeko_jl_b200 import mesh as M
+    import scipy.sparse as sp
+
+    m = fk.to_p2(fk.delaunay_ball(250, seed=3))
+    M.edgeNumbering(m)
+    E = M.edgeDofs(m)
+    t = m.t[:4].astype(np.int64)
+    rp, ci, v = orc.nedelec_stiffness(m)
+    A = sp.csr_matrix((v, ci, rp), shape=(m.ne, m.ne))
+    assert abs(A - A.T).max() == 0.0
+    rng = np.random.default_rng(0)
+    phi = rng.normal(size=m.nv)
+    B0 = np.array([0.3, -1.2, 0.7])
+    ug, ub = np.zeros(m.ne), np.zeros(m.ne)
+    for ie, (a, b) in enumerate(orc.NED_EDGES):
+        lo, hi = np.minimum(t[a], t[b]), np.maximum(t[a], t[b])
+        d = m.p[:, hi] - m.p[:, lo]
+        Ln = np.linalg.norm(d, axis=0)
+        ug[E[ie]] = (phi[hi] - phi[lo]) / Ln
+        Am = 0.5 * np.cross(B0, (0.5 * (m.p[:, hi] + m.p[:, lo])).T).T
+        ub[E[ie]] = np.einsum("dk,dk->k", Am, d) / Ln
+    scale = np.abs(A).max()
+    assert np.abs(A @ ug).max() < 1e-12 * scale * np.abs(ug).max()
+    Bf, B = orc.nedelec_recover_B(m, ub)
+    assert np.abs(Bf - B0[:, None]).max() < 1e-12 and np.abs(B - np.linalg.norm(B0)).max() < 1e-12
+    assert np.abs(orc.nedelec_recover_B(m, ug)[0]).max() < 1e-11 * np.abs(ug).max()
+    # sum_k VE B0 . curlN_e = (A u_B0)_e
+    rhs = orc.nedelec_load(m, B0)
+    assert np.abs(rhs - A @ ub).max() < 1e-11 * np.abs(rhs).max()
+    # local matrices: symmetric, 36 x nt, equal to VE c_i . c_j
+    Ak = orc.nedelec_local_stiffness(m)
+    c = orc.nedelec_curls(m)
+    assert np.allclose(Ak[6 * 2 + 5], m.VE * np.einsum("kd,kd->k", c[:, 2], c[:, 5]), rtol=1e-14, atol=0)
+    assert np.array_equal(Ak[6 * 2 + 5], Ak[6 * 5 + 2])
+    # tangential matrix: entry by entry against its definition on a random state
+    dnu = rng.uniform(0.1, 1.0, m.nt)
+    Bfr = rng.normal(size=(3, m.nt))
+    Bn = np.linalg.norm(Bfr, axis=0)
+    rpt, cit, vt = orc.nedelec_tangential(m, dnu, Bfr, Bn)
+    At = sp.csr_matrix((vt, cit, rpt), shape=(m.ne, m.ne)).toarray()
+    ref = np.zeros((m.ne, m.ne))
+    d = np.einsum("ked,dk->ke", c, Bfr)
+    for k in range(m.nt):
+        ref[np.ix_(E[:, k], E[:, k])] += m.VE[k] * dnu[k] / Bn[k] * np.outer(d[k], d[k])
+    assert np.abs(At - ref).max() < 1e-12 * np.abs(ref).max()
