@@ -1376,7 +1376,11 @@ int fk_assemble_tangential(fk_handle h, int slot, const double* Hfield, const do
 }
 // ---- P2 tetrahedra (p2.cuh) ---------------------------------------------------------------------------
 // sum_q w_q phi_i phi_j on the reference element, 15-point rule of GaussQuadrature3D(4) (src/FEM3D.jl:711-745)
-static P2Ref p2_reference_mass() {
+struct P2Quad {
+  const double (*pts)[3];
+  const double* wts;
+};
+static P2Quad p2_quadrature() {
   static const double pts[15][3] = {
       {0.2500000000000000, 0.2500000000000000, 0.2500000000000000}, {0.0000000000000000, 0.3333333333333333, 0.3333333333333333},
       {0.3333333333333333, 0.3333333333333333, 0.3333333333333333}, {0.3333333333333333, 0.3333333333333333, 0.0000000000000000},
@@ -1389,6 +1393,12 @@ static P2Ref p2_reference_mass() {
   static const double wts[15] = {0.1817020685825351, 0.0361607142857143, 0.0361607142857143, 0.0361607142857143, 0.0361607142857143,
                                  0.0698714945161738, 0.0698714945161738, 0.0698714945161738, 0.0698714945161738, 0.0656948493683187,
                                  0.0656948493683187, 0.0656948493683187, 0.0656948493683187, 0.0656948493683187, 0.0656948493683187};
+  return P2Quad{pts, wts};
+}
+static P2Ref p2_reference_mass() {
+  const P2Quad Q = p2_quadrature();
+  const double (*pts)[3] = Q.pts;
+  const double* wts = Q.wts;
   static const int ea[6] = {0, 1, 0, 0, 2, 1}, eb[6] = {1, 2, 2, 3, 3, 3};
   P2Ref R{};
   for (int q = 0; q < 15; q++) {
@@ -1417,6 +1427,8 @@ static void ensure_p2(fk_handle h) {
   h->geo_dst1.upload(R.dst1, s);
   h->geo_dst2.upload(R.dst2, s);
   h->geo_ref.upload(R.cref, s);
+  h->ned_ref.upload(R.cref, s);   // the copy that keeps its pair bits (convection: per-call slot values)
+  h->ned_shift = R.pair_shift;
   h->geo_g.ensure((size_t)std::max<long long>(R.n_slots, 1));
   h->p2_gmass.ensure((size_t)std::max<long long>(R.n_slots, 1));
   h->geo_s0.ensure((size_t)h->nt);
@@ -1451,6 +1463,64 @@ int fk_assemble_stiffness_p2(fk_handle h, int slot, const double* mu, double* va
 }
 int fk_assemble_mass_p2(fk_handle h, int slot, const double* F, double* vals_out) {
   return guard([&]() { return assemble_p2(h, slot, F, vals_out, true); });
+}
+
+// T[i][j][m] = sum_q w_q phi_i (d phi_j / d lambda_m) on the reference element (p2.cuh: P2ConvRef), same 15-point rule
+static void p2_reference_convection(P2ConvRef& R) {
+  P2Quad Q = p2_quadrature();
+  std::memset(&R, 0, sizeof(R));
+  static const int ea[6] = {0, 1, 0, 0, 2, 1}, eb[6] = {1, 2, 2, 3, 3, 3};
+  for (int q = 0; q < 15; q++) {
+    const double l[4] = {1.0 - Q.pts[q][0] - Q.pts[q][1] - Q.pts[q][2], Q.pts[q][0], Q.pts[q][1], Q.pts[q][2]};
+    double phi[10], dphi[10][4] = {};
+    for (int v = 0; v < 4; v++) { phi[v] = l[v] * (2.0 * l[v] - 1.0); dphi[v][v] = 4.0 * l[v] - 1.0; }
+    for (int e = 0; e < 6; e++) {
+      phi[4 + e] = 4.0 * l[ea[e]] * l[eb[e]];
+      dphi[4 + e][ea[e]] = 4.0 * l[eb[e]];
+      dphi[4 + e][eb[e]] = 4.0 * l[ea[e]];
+    }
+    const double w = Q.wts[q] / 6.0;
+    for (int i = 0; i < 10; i++)
+      for (int j = 0; j < 10; j++)
+        for (int m = 0; m < 4; m++) R.T[i][j][m] += w * phi[i] * dphi[j][m];
+  }
+}
+int fk_assemble_convection_p2(fk_handle h, int slot, const double* vel, const double* F, int compat_bug, double* vals_out) {
+  return guard([&]() {
+    need(h && vel, "fk: NULL argument");
+    DeviceGuard dg(h->device);
+    check_slot(slot);
+    ensure_p2(h);
+    cudaStream_t s = h->stream;
+    if (!h->p2_conv_ref.ptr) {
+      P2ConvRef R;
+      p2_reference_convection(R);
+      h->p2_conv_ref.upload(&R.T[0][0][0], 400, s);
+      FK_CUDA(cudaStreamSynchronize(s));   // R lives on this stack frame
+    }
+    const size_t ns = (size_t)std::max<long long>(h->geo_slots, 1);
+    h->p2_c1.ensure(ns);
+    h->p2_c2.ensure(ns);
+    h->st_b.upload(vel, (size_t)3 * h->nv, s);
+    const double* cd = nullptr;
+    if (F) { h->st_a.upload(F, (size_t)h->nt, s); cd = h->st_a.ptr; }
+    h->dir_applied &= ~(1u << slot);
+    double* vals = slot_vals(h, slot);
+    p2_scale_kernel<<<cdiv(h->nt, 256), 256, 0, s>>>(cd, h->nt, h->geo_s0.ptr);
+    if (h->geo_slots > 0) {
+      p2_conv_slot_kernel<<<std::min(cdiv(h->geo_slots, 128), h->num_sms * 16), 128, 0, s>>>(
+          h->p4.ptr, h->tP2.ptr, h->VE.ptr, h->ned_ref.ptr, h->geo_slots, h->ned_shift, h->st_b.ptr,
+          reinterpret_cast<const P2ConvRef*>(h->p2_conv_ref.ptr), compat_bug, h->p2_c1.ptr, h->p2_c2.ptr);
+      FK_CUDA(cudaGetLastError());
+      l2_release_for_assembly(h);
+      geo_rescale2_kernel<<<std::max(1, std::min(cdiv(h->geo_nslices, kGeoThreads / 32), h->num_sms * 3)), kGeoThreads, 0, s>>>(
+          h->geo_slice_ptr.ptr, h->geo_dst1.ptr, h->geo_dst2.ptr, h->geo_ref.ptr, h->p2_c1.ptr, h->p2_c2.ptr, h->geo_s0.ptr, h->geo_nslices, vals);
+      FK_CUDA(cudaGetLastError());
+    }
+    h->launches += 3;
+    copy_out_matrix(h, vals, vals_out);
+    return 0;
+  });
 }
 
 // ---- Nedelec (edge) elements (nedelec.cuh; src/FEM3D.jl:153-271, Magnetostatics/nedelec3D.jl:104-250) ---------------------

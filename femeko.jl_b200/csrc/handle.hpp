@@ -169,6 +169,7 @@ struct fk_handle_s {
   int ned_shift = 26;
   fk::DevBuf<uint32_t> ned_ref;
   fk::DevBuf<double> ned_vals;         // scratch matrix of the load-vector sum
+  fk::DevBuf<double> p2_c1, p2_c2, p2_conv_ref;   // P2 convection: per-call slot values (canonical entry / mirror), reference tensor
   // fk_tune(h, 11, n): device-side timeline of the PCG kernels (kernels.cuh: trace_rec)
   fk::DevBuf<unsigned long long> trace;
   int trace_cap = 0;

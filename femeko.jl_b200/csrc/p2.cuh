@@ -82,3 +82,54 @@ static __global__ void __launch_bounds__(256) p2_scale_kernel(const double* __re
   const int k = blockIdx.x * blockDim.x + threadIdx.x;
   if (k < nt) s0[k] = f ? f[k] : 1.0;
 }
+
+// quadraticConvectionMatrix (src/FEM3D.jl:563-648): C_k[i, j] = F VE sum_q w_q phi_i(x_q) (u_avg . grad phi_j(x_q)), u_avg = the mean
+// of the velocity over the four vertices (:594).  With grad phi_j = sum_m (d phi_j / d lambda_m) grad lambda_m the quadrature
+// collapses onto a constant tensor of the reference element,
+//   C_k[i, j] = F VE sum_m (u_avg . grad lambda_m) T[i][j][m],     T[i][j][m] = sum_q w_q phi_i d phi_j / d lambda_m   (15-point rule)
+// The matrix is NOT symmetric: a slot of the pair (a <= b) yields both C_k[a, b] and C_k[b, a]; g1 goes to the item's canonical
+// entry -- the one with the lower row, i.e. the lower global node label --, g2 to its mirror (geo_rescale2_kernel).
+// NOTE the reference assembles the TRANSPOSE of its local matrices (Clocal[:, k] = Ck[:] flattens column-major, the assembly
+// loop n = 10 (i - 1) + j reads row-major, src/FEM3D.jl:632-645): global entry (t_i, t_j) += C_k[j, i].  `transposed` = 1
+// reproduces that (fk_assemble_convection_p2: compat_bug), 0 gives entry (t_i, t_j) += C_k[i, j].
+struct P2ConvRef {
+  double T[10][10][4];
+};
+static __global__ void __launch_bounds__(128) p2_conv_slot_kernel(const double4* __restrict__ p4, const int* __restrict__ t10,
+                                                                  const double* __restrict__ VE, const uint32_t* __restrict__ cref,
+                                                                  long long nslots, int shift, const double* __restrict__ vel,
+                                                                  const P2ConvRef* __restrict__ ref, int transposed,
+                                                                  double* __restrict__ g1, double* __restrict__ g2) {
+  const uint32_t emask = (1u << shift) - 1u;
+  for (long long s = blockIdx.x * (long long)blockDim.x + threadIdx.x; s < nslots; s += (long long)gridDim.x * blockDim.x) {
+    const uint32_t c = cref[s];
+    if (c == 0xffffffffu) { g1[s] = 0.0; g2[s] = 0.0; continue; }
+    const int k = (int)(c & emask), q = (int)(c >> shift);
+    int a = 0, rem = q;
+    while (rem >= 10 - a) { rem -= 10 - a; a++; }
+    const int b = a + rem;
+    const int* e = t10 + 10 * (size_t)k;
+    const int n0 = __ldg(e), n1 = __ldg(e + 1), n2 = __ldg(e + 2), n3 = __ldg(e + 3);
+    TetGeom G;
+    tet_geometry(p4, make_int4(n0, n1, n2, n3), G);
+    double ua[3];
+#pragma unroll
+    for (int d = 0; d < 3; d++)
+      ua[d] = (vel[3 * (size_t)n0 + d] + vel[3 * (size_t)n1 + d] + vel[3 * (size_t)n2 + d] + vel[3 * (size_t)n3 + d]) / 4.0;
+    const double V = VE[k];
+    double cab = 0.0, cba = 0.0;
+#pragma unroll
+    for (int m = 0; m < 4; m++) {
+      const double dm = ua[0] * G.g[m][0] + ua[1] * G.g[m][1] + ua[2] * G.g[m][2];
+      cab += dm * ref->T[a][b][m];
+      cba += dm * ref->T[b][a][m];
+    }
+    cab *= V;
+    cba *= V;
+    // row of the canonical entry = the lower global label.  transposed (the reference's assembly, src/FEM3D.jl:632-645:
+    // Clocal[:, k] = Ck[:] is column-major while the loop over (i, j) reads it row-major): entry (t_i, t_j) receives Ck[j, i]
+    const bool ab_is_canonical = (__ldg(e + a) <= __ldg(e + b)) != (transposed != 0);
+    g1[s] = ab_is_canonical ? cab : cba;
+    g2[s] = ab_is_canonical ? cba : cab;
+  }
+}

@@ -150,6 +150,48 @@ static __global__ void __launch_bounds__(kGeoThreads, MINB) geo_rescale_kernel(c
   }
 }
 
+// The same sums for a NON-SYMMETRIC matrix on the symmetric pattern (P2 convection matrix, p2.cuh): every contribution slot
+// carries two factors, g1 for the item's canonical entry (dst1: the one with the lower row) and g2 for its mirror (dst2).
+static __global__ void __launch_bounds__(kGeoThreads, 3) geo_rescale2_kernel(const uint32_t* __restrict__ slice_ptr,
+                                                                             const int* __restrict__ dst1, const int* __restrict__ dst2,
+                                                                             const uint32_t* __restrict__ cref, const double* __restrict__ g1,
+                                                                             const double* __restrict__ g2, const double* __restrict__ s0,
+                                                                             int nslices, double* __restrict__ vals) {
+  constexpr int B = 4;
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  constexpr int WPB = kGeoThreads / 32;
+  for (int s = blockIdx.x * WPB + wib; s < nslices; s += gridDim.x * WPB) {
+    const uint32_t b0 = __ldg(slice_ptr + s);
+    const int w = (int)(__ldg(slice_ptr + s + 1) - b0);
+    const int d1 = __ldcs(dst1 + (size_t)s * 32 + lane), d2 = __ldcs(dst2 + (size_t)s * 32 + lane);
+    const size_t base = (size_t)b0 * 32 + lane;
+    double acc1 = 0.0, acc2 = 0.0;
+    for (int k = 0; k < w; k += B) {
+      uint32_t rr[B];
+      double ga[B], gb[B], ss[B];
+#pragma unroll
+      for (int q = 0; q < B; q++) rr[q] = (k + q < w) ? __ldcs(cref + base + (size_t)(k + q) * 32) : 0xffffffffu;
+#pragma unroll
+      for (int q = 0; q < B; q++) {
+        ga[q] = (k + q < w) ? __ldcs(g1 + base + (size_t)(k + q) * 32) : 0.0;
+        gb[q] = (k + q < w) ? __ldcs(g2 + base + (size_t)(k + q) * 32) : 0.0;
+      }
+#pragma unroll
+      for (int q = 0; q < B; q++) ss[q] = rr[q] != 0xffffffffu ? __ldg(s0 + rr[q]) : 0.0;
+#pragma unroll
+      for (int q = 0; q < B; q++)
+        if (rr[q] != 0xffffffffu) {
+          acc1 = __dadd_rn(acc1, __dmul_rn(ss[q], ga[q]));
+          acc2 = __dadd_rn(acc2, __dmul_rn(ss[q], gb[q]));
+        }
+    }
+    if (d1 >= 0) {
+      vals[d1] = acc1;
+      if (d2 >= 0) vals[d2] = acc2;
+    }
+  }
+}
+
 // Diagonal of a matrix whose local matrices have zero row sums (stiffness: sum_j grad l_i . grad l_j = 0), from the
 // off-diagonal entries the streamed sums just wrote: a_rr = -(sum_{c != r} a_rc), folded left to right in column order.
 // One lane per row over the SELL slices, like the SpMV.  Replaces the 4 diagonal contributions of every element (40 % of

@@ -185,6 +185,15 @@ class Femeko:
         L.check(self.lib.fk_assemble_stiffness_p2(self.h, slot, L.dptr(self._coef(mu)), L.dptr(v)))
         return v
 
+    def assemble_convection_p2(self, u, F=None, slot=2, want_vals=True, compat_bug=True):
+        """quadraticConvectionMatrix (src/FEM3D.jl:563-648): u = velocity, 3 x nv; the values are not symmetric.  compat_bug:
+        assemble the local matrices transposed, as the reference does (:632-645)."""
+        v = self._vals(want_vals)
+        u = np.asfortranarray(np.asarray(u, dtype=np.float64))
+        assert u.shape == (3, self.nv)
+        L.check(self.lib.fk_assemble_convection_p2(self.h, slot, L.dptr(u), L.dptr(self._coef(F)), int(compat_bug), L.dptr(v)))
+        return v
+
     def assemble_mass_p2(self, F=None, slot=1, want_vals=True):
         v = self._vals(want_vals)
         L.check(self.lib.fk_assemble_mass_p2(self.h, slot, L.dptr(self._coef(F)), L.dptr(v)))
@@ -689,6 +698,13 @@ def nedelecTangentialStiffness(mesh: MESH, dnu, Bfield, B) -> SparseCSR:
     """src/FEM3D.jl:197-271."""
     fk = _edge_handle(mesh)
     return SparseCSR(fk, 2, fk.assemble_nedelec_tangential(dnu, Bfield, B, slot=2))
+
+
+def quadraticConvectionMatrix(mesh: MESH, S=None, u=None, F=None, compat_bug: bool = True) -> SparseCSR:
+    """src/FEM3D.jl:563-648 (S accepted for call compatibility and ignored, as in quadraticStiffnessMatrix); by default the
+    local matrices are assembled transposed, exactly as the reference does."""
+    fk = _handle(mesh)
+    return SparseCSR(fk, 2, fk.assemble_convection_p2(u, F, slot=2, compat_bug=compat_bug))
 
 
 def tangentialStiffnessMatrix(mesh: MESH, H_vec, dmu) -> SparseCSR:

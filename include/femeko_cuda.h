@@ -185,6 +185,13 @@ int fk_assemble_mass2d(fk_handle h, int slot, const double* rho /* nt or NULL */
  * reference are the Lagrange P2 functions on straight-sided elements and are used in closed form.  coef: nt or NULL. */
 int fk_assemble_stiffness_p2(fk_handle h, int slot, const double* mu, double* vals_out /* nnz or NULL */);
 int fk_assemble_mass_p2(fk_handle h, int slot, const double* F, double* vals_out);
+/* quadraticConvectionMatrix(mesh, S, u, F) (src/FEM3D.jl:563-648): local matrices C_k[i, j] = F VE sum_q w_q phi_i (u_avg . grad phi_j),
+ * u_avg = mean of the velocity u (3 x nv, column-major) over the element's four vertices, 15-point rule.  compat_bug = 1 assembles
+ * them as the reference does -- TRANSPOSED: Clocal[:, k] = Ck[:] flattens column-major while the assembly loop reads row-major
+ * (:632-645), so global entry (t_i, t_j) += C_k[j, i]; compat_bug = 0: entry (t_i, t_j) += C_k[i, j].  NON-symmetric values on the
+ * (symmetric) pattern of the handle; fk_spmv / fk_matrix_axpby / fk_matrix_get work on it, fk_pcg does not apply.                */
+int fk_assemble_convection_p2(fk_handle h, int slot, const double* u /* 3 x nv */, const double* F /* nt or NULL */, int compat_bug,
+                              double* vals_out /* nnz or NULL */);
 /* Nedelec (lowest-order edge) elements: the magnetic vector potential of Magnetostatics/nedelec3D.jl.  Degrees of freedom
  * = the edges of an order-2 mesh, edge2localMap[t[5:10, :]] (src/mesh.jl:170-185), local edge order and orientation of
  * NodesFromLocalEdge (src/mesh.jl:603-637: (0,1) (1,2) (2,0) (3,0) (2,3) (1,3), each directed from the lower to the higher

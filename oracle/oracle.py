@@ -669,6 +669,32 @@ def quadratic_mass(mesh, S=None, F=None):
     return _assemble_npe(mesh, Ml)
 
 
+def quadratic_convection(mesh, u, S=None, F=None, compat_bug=True):
+    """quadraticConvectionMatrix, src/FEM3D.jl:563-648, literally: Ck[i, j] += w VE (u_avg . gradPhi_j) phi_i F at the 15 points,
+    u_avg = mean of u over the four vertices; Clocal[:, k] = Ck[:] (COLUMN-major) and then sparse(t[i], t[j], Clocal[n]) with
+    n = 10 i + j (row-major): the reference assembles the transpose of Ck.  compat_bug = False assembles Ck itself."""
+    S = quadratic_basis_all(mesh) if S is None else S
+    F = np.ones(mesh.nt) if F is None else np.asarray(F, dtype=np.float64)
+    u = np.asarray(u, dtype=np.float64)
+    w, pts = gauss_quadrature_3d_4()
+    Cl = np.zeros((100, mesh.nt))
+    for k in range(mesh.nt):
+        v = mesh.p[:, mesh.t[:4, k]]
+        J = (v[:, 1:] - v[:, :1])
+        x, y, z = v[:, :1] + J @ pts.T
+        Sk = S[:, :, k]
+        mono = np.stack([np.ones_like(x), x, y, z, x * x, x * y, x * z, y * y, y * z, z * z])
+        phi = Sk.T @ mono                                                  # [basis, point]
+        gx = Sk[1][:, None] + 2 * Sk[4][:, None] * x + Sk[5][:, None] * y + Sk[6][:, None] * z
+        gy = Sk[2][:, None] + 2 * Sk[7][:, None] * y + Sk[5][:, None] * x + Sk[8][:, None] * z
+        gz = Sk[3][:, None] + 2 * Sk[9][:, None] * z + Sk[6][:, None] * x + Sk[8][:, None] * y
+        ua = u[:, mesh.t[:4, k]].mean(axis=1)
+        gj = ua[0] * gx + ua[1] * gy + ua[2] * gz                          # [basis j, point]
+        Ck = (phi * (w * mesh.VE[k])) @ gj.T * F[k]                        # Ck[i, j]
+        Cl[:, k] = Ck.ravel(order="F") if compat_bug else Ck.ravel(order="C")
+    return _assemble_npe(mesh, Cl)
+
+
 # --------------------------------------------------------------------------------------------------
 # Nedelec (lowest-order edge) elements: src/FEM3D.jl:153-271, Magnetostatics/nedelec3D.jl:104-250 -- numpy restatement,
 # test infrastructure only.  Julia-only code (no C++ twin, Julia absent here): parity unpinned against Julia itself.

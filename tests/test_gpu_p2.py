@@ -60,3 +60,37 @@ def test_p2_poisson_solve_against_direct():
     # solution is only close to the quadratic (the direct solve of the same matrix is the parity check above)
     print(f"P2 Poisson: {it} PCG iterations, |u - u_exact| / |u_exact| = {rel_l2(u, uex):.2e}")
     h.close()
+
+
+@pytest.mark.parametrize("mesh", ["kuhn4", "delaunay"])
+@pytest.mark.parametrize("compat", [True, False])
+def test_p2_convection_matrix_against_oracle(compat, mesh):
+    """quadraticConvectionMatrix (src/FEM3D.jl:563-648) through fk_assemble_convection_p2 (non-symmetric values through the
+    two-factor contribution sums) against the oracle's literal restatement -- including the reference's transposed assembly."""
+    from oracle import oracle as orc
+
+    m = fk.kuhn_cube_p2(4, inside_edge=0.5) if mesh == "kuhn4" else fk.to_p2(fk.delaunay_ball(800, seed=6))
+    tol = 1e-12 if mesh == "kuhn4" else 1e-10      # the reference's 10 x 10 fits lose digits on the slivers of a Delaunay mesh
+    rng = np.random.default_rng(3)
+    u = rng.normal(size=(3, m.nv))
+    F = rng.uniform(0.5, 2.0, m.nt)
+    h = fk.Femeko(m)
+    v = h.assemble_convection_p2(u, F, slot=2, compat_bug=compat)
+    rp, ci, vo = orc.quadratic_convection(m, u, None, F, compat_bug=compat)
+    hp = h.pattern()
+    assert np.array_equal(hp[0], rp) and np.array_equal(hp[1], ci)
+    assert np.max(np.abs(v - vo)) < tol * np.max(np.abs(vo))
+    assert np.array_equal(v, h.assemble_convection_p2(u, F, slot=3, compat_bug=compat))     # bitwise run to run
+    v1 = h.assemble_convection_p2(u, None, slot=2, compat_bug=compat)
+    _, _, v1o = orc.quadratic_convection(m, u, None, None, compat_bug=compat)
+    assert np.max(np.abs(v1 - v1o)) < tol * np.max(np.abs(v1o))
+    if not compat:                                                          # rows sum to zero: C 1 = 0 through the device SpMV
+        y = h.spmv(np.ones(m.nv), slot=2)
+        assert np.max(np.abs(y)) < 1e-12 * np.max(np.abs(v1))
+    # the stiffness / mass factors of the handle are untouched by the convection scratch
+    K = h.assemble_stiffness_p2(None, slot=0)
+    _, _, Ko = orc.quadratic_stiffness(m)
+    assert np.max(np.abs(K - Ko)) < tol * np.max(np.abs(Ko))
+    A = fk.quadraticConvectionMatrix(m, None, u, F, compat_bug=compat)
+    assert np.array_equal(A.vals, v)
+    h.close()

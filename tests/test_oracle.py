@@ -284,3 +284,30 @@ def test_nedelec_restatement_properties():
     for k in range(m.nt):
         ref[np.ix_(E[:, k], E[:, k])] += m.VE[k] * dnu[k] / Bn[k] * np.outer(d[k], d[k])
     assert np.abs(At - ref).max() < 1e-12 * np.abs(ref).max()
+
+
+def test_quadratic_convection_restatement_properties():
+    """quadraticConvectionMatrix (src/FEM3D.jl:563-648): the literal restatement assembles the TRANSPOSE of the local matrices
+    (column-major Ck[:] read row-major), so its COLUMN sums vanish (sum_j grad phi_j = 0); the untransposed form has zero row
+    sums and integrates u . grad f exactly for a linear f (times the reference's 1/6)."""
+    import femeko_jl_b200 as fk
+    import scipy.sparse as sp
+
+    m = fk.to_p2(fk.delaunay_ball(220, seed=5))
+    rng = np.random.default_rng(2)
+    u = rng.normal(size=(3, m.nv))
+    F = rng.uniform(0.5, 2.0, m.nt)
+    S = orc.quadratic_basis_all(m)
+    rp, ci, vT = orc.quadratic_convection(m, u, S, F, compat_bug=True)
+    _, _, v = orc.quadratic_convection(m, u, S, F, compat_bug=False)
+    CT = sp.csr_matrix((vT, ci, rp), shape=(m.nv, m.nv))
+    Cm = sp.csr_matrix((v, ci, rp), shape=(m.nv, m.nv))
+    assert abs(CT - Cm.T).max() < 1e-15 * abs(Cm).max()
+    assert abs(Cm - Cm.T).max() > 1e-3 * abs(Cm).max()                    # genuinely non-symmetric
+    one = np.ones(m.nv)
+    assert np.abs(Cm @ one).max() < 1e-12 * abs(Cm).max() and np.abs(CT.T @ one).max() < 1e-12 * abs(Cm).max()
+    a = np.array([0.7, -0.4, 1.1])
+    f = a @ m.p
+    ua = u[:, m.t[:4]].mean(axis=1)                                        # 3 x nt
+    # (the reference's weights sum to 1/6 AND multiply VE, as in quadraticMassMatrix: the integral carries that 1/6)
+    assert abs(one @ (Cm @ f) - np.sum(F * m.VE * (a @ ua)) / 6.0) < 1e-11 * np.sum(np.abs(F * m.VE * (a @ ua)))
