@@ -95,6 +95,7 @@ for persist in ([1] if short else [1, 0]):
 # the two streaming kernels of the sweep side by side (fk_tune 17 = 16 a + b: sums on a CTAs per SM, field recovery on b), timed
 # behind a PCG solve like the bench step
 h.tune(2, 1)
+h.tune(12, int(os.environ.get('FK_GEO_VARIANT', '0')))     # launch shape of the streamed sums for the split sweep
 for split in ([0x32] if short else [int(v, 16) for v in os.environ.get('FK_SPLITS', '0,32,41,22,31,42,23,33').split(',')]):
     h.tune(17, split)
     sweep(); h.synchronize()
