@@ -916,6 +916,203 @@ def run_reference_heat(args):
 # --------------------------------------------------------------------------------------------------
 # CPU arm: the compiled reference (oracle/_ref) -- or the C port when it is absent
 # --------------------------------------------------------------------------------------------------
+# ---------------------------------------------------------------------------------------------------------------------
+# --workload demag: SURVEY 8 row f-1, the repeated solve of the Landau-Lifshitz loop (LL::magnetostaticField, LL.cpp:287-348):
+# load vector from the nodal magnetisation, Jacobi-PCG on the constant stiffness matrix from x0 = 0 (CG.solve(RHS), LL.cpp:316),
+# element field, box method back to the nodes.  One GPU (fk_demag_* does not take partitioned handles).
+# ---------------------------------------------------------------------------------------------------------------------
+def demag_magnetisations(mesh, count, seed=5):
+    """A short cycle of nodal magnetisations (3 x nv, zero outside the magnet): unit vectors turning about z with a
+    smooth spatial twist, the kind of state an LL time loop hands over step after step."""
+    insn = np.unique(mesh.t[:, mesh.InsideElements])
+    rng = np.random.default_rng(seed)
+    ph0 = rng.uniform(0, 2 * np.pi)
+    out = []
+    for s in range(count):
+        M = np.zeros((3, mesh.nv), order="F")
+        ang = ph0 + 0.05 * s + 2.0 * mesh.p[2, insn]
+        M[0, insn], M[1, insn], M[2, insn] = np.cos(ang), np.sin(ang), 0.2
+        out.append(M)
+    return out
+
+
+class CpuDemag:
+    """LL::magnetostaticField on the host: C port (oracle/) of the load vector, Eigen's Jacobi-CG and the box method, at the
+    tolerance of the GPU arm (the compiled class LL runs Eigen's default epsilon tolerance and cannot be told otherwise)."""
+
+    def __init__(self, N, tol):
+        from oracle import oracle as orc
+
+        self.orc, self.tol = orc, tol
+        self.kind = "port"
+        self.m = mesh_module().kuhn_cube(N, inside_edge=0.5)
+        self.Ms = demag_magnetisations(self.m, 4)
+        self.rp, self.ci, self.A = orc.stiffness(self.m, None, order="eigen")
+        self.vol = orc.node_volumes(self.m, self.m.InsideElements)
+        self.n, self.iters = 0, 0
+
+    def step(self):
+        orc, m = self.orc, self.m
+        rhs = orc.demag_rhs(m, m.InsideElements, self.Ms[self.n % 4])
+        u, it = orc.pcg(self.rp, self.ci, self.A, rhs, self.tol)[:2]
+        self.Hd = orc.demag_box(m, m.InsideElements, u, self.vol)
+        self.n += 1
+        self.iters += int(it)
+
+
+def demag_parity(args, device):
+    """GPU demag field against the oracle on a small cube, same tolerance."""
+    import femeko_jl_b200 as fk
+    from oracle import oracle as orc
+
+    m = mesh_module().kuhn_cube(args.heat_parity_n, inside_edge=0.5)
+    M = demag_magnetisations(m, 1)[0]
+    h = fk.Femeko(m, device=device)
+    h.demag_setup(m.InsideElements.astype(np.int32), slot=0)
+    Hd, it = h.demag_field(M, tol=args.demag_tol)
+    h.close()
+    Ho, _, ito, _, _ = orc.demag_field(m, m.InsideElements, M, tol=args.demag_tol)
+    fin = np.isfinite(Ho)
+    rel = float(np.linalg.norm(Hd[fin] - Ho[fin]) / np.linalg.norm(Ho[fin]))
+    return {"against": f"oracle LL::magnetostaticField restatement, Kuhn N={args.heat_parity_n}, tol {args.demag_tol:g}",
+            "Hd_rel_l2": rel, "iterations": [int(it), int(ito)], "nan_pattern_equal": bool(np.array_equal(fin, np.isfinite(Hd))),
+            "ok": bool(rel < 1e-7 and abs(it - ito) <= 2 and np.array_equal(fin, np.isfinite(Hd)))}
+
+
+def run_demag(args):
+    import ctypes as C
+
+    import torch
+
+    import femeko_jl_b200 as fk
+    from femeko_jl_b200 import lib as L
+
+    if args.gpus != 1:
+        raise SystemExit("bench.py --workload demag runs on one GPU (fk_demag_* does not take partitioned handles)")
+    ctx = Ctx(args)
+    stream = ctx.stream
+    N = args.n
+    t0 = time.time()
+    mesh = mesh_module().kuhn_cube(N, inside_edge=0.5)
+    h = fk.Femeko(mesh, use_mesh_VE=False, device=ctx.local)
+    for kv in [t for t in args.tune.split(",") if t]:
+        h.tune(int(kv.split("=")[0]), int(kv.split("=")[1]))
+    h.set_stream(stream.cuda_stream)
+    h.demag_setup(mesh.InsideElements.astype(np.int32), slot=0)
+    Ms = demag_magnetisations(mesh, 4)
+    with torch.cuda.stream(stream):
+        M_dev = [torch.from_numpy(np.ascontiguousarray(M.T)).to(ctx.dev) for M in Ms]      # 3 x nv column-major
+        Hd_dev = torch.empty_like(M_dev[0])
+    M_pin = [torch.from_numpy(np.ascontiguousarray(M.T)).pin_memory() for M in Ms]
+    Hd_pin = torch.empty_like(M_pin[0]).pin_memory()
+    stream.synchronize()
+    setup_s = time.time() - t0
+    nv, nt, nnz = h.nv, h.nt, h.nnz
+    W, K = max(3, args.warmup), args.steps
+    its, n = [], [0]
+
+    def step_dev(warm=False):
+        it, _ = h.demag_field_dev(M_dev[n[0] % 4].data_ptr(), Hd_dev.data_ptr(), tol=args.demag_tol, warm_start=warm)
+        n[0] += 1
+        its.append(it)
+
+    o = h.pcg_opts(tol=args.demag_tol)
+    it_c, rr_c = C.c_int(), C.c_double()
+
+    def step_e2e():
+        L.check(h.lib.fk_demag_field(h.h, 0, C.cast(M_pin[n[0] % 4].data_ptr(), L.c_double_p), C.byref(o), 1,
+                                     C.cast(Hd_pin.data_ptr(), L.c_double_p), None, C.byref(it_c), C.byref(rr_c)))
+        n[0] += 1
+
+    def timed(fn):
+        for _ in range(W):
+            fn()
+        ctx.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        l0 = h.launch_count()
+        e0.record(stream)
+        for _ in range(K):
+            fn()
+        e1.record(stream)
+        ctx.barrier()
+        return e0.elapsed_time(e1), h.launch_count() - l0
+
+    sampler = ClockSampler(ctx.local)
+    sampler.start()
+    ms_dev, launches = timed(step_dev)
+    its_timed = its[-K:]
+    ms_e2e, _ = timed(step_e2e)
+    clocks = sampler.stop()
+    ms_warm, _ = timed(lambda: step_dev(True))
+    its_warm = its[-K:]
+    h.close()
+    peak, peak_src = measured_peaks()
+    ms_step = ms_dev / K
+    tot_it = int(sum(its_timed))
+    step_bytes = pcg_bytes(nv, nnz) * tot_it + K * (12 * nnz + 16 * nv + 60 * nt)
+    gbs = step_bytes / (ms_dev * 1e-3) / 1e9
+    line = {
+        "metric": METRIC, "value": round(nt / (ms_step * 1e-3) / 1e6, 3), "unit": UNIT, "n_gpus": 1, "steps": K, "warmup": W,
+        "ms_per_step": round(ms_step, 4), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": f"SURVEY 8 f-1: demagnetising field of the Landau-Lifshitz loop (LL::magnetostaticField, LL.cpp:287-348), Kuhn cube "
+                               f"N={N} ({nt} tets, {nv} rows), magnet = the inner half cube ({mesh.nInside} tets); a step = load vector from the "
+                               f"nodal magnetisation + Jacobi-PCG from x0 = 0 to {args.demag_tol:g} on the resident stiffness matrix + element field "
+                               "+ box method to the nodes; value = tets of the mesh per second of one field evaluation",
+                   "tets_total": nt, "rows_total": nv, "pcg_iters_per_step": round(tot_it / K, 1),
+                   "l2": "inputs larger than L2 (matrix stream %.0f MB vs 126 MB L2)" % (12 * nnz / 1e6), "parallelism": "single GPU"},
+        "components": {"pcg_iters_per_step": its_timed, "pcg_us_per_iteration": round(ms_dev * 1e3 / max(tot_it, 1), 2),
+                       "warm_started": {"ms_per_step": round(ms_warm / K, 4), "pcg_iters_per_step": its_warm,
+                                        "note": "same steps with the previous potential as initial guess (fk_pcg_opts.warm_start): what an "
+                                                "LL loop on this library would use; the reference always starts from 0"},
+                       "setup_s_untimed": round(setup_s, 2)},
+        "e2e": {"value": round(nt / (ms_e2e / K * 1e-3) / 1e6, 3), "unit": UNIT, "ms_per_step": round(ms_e2e / K, 4),
+                "h2d_bytes_per_step": 24 * nv, "d2h_bytes_per_step": 24 * nv + 12, "host_buffers": "pinned"},
+        "gpu_launches": int(launches),
+        "roofline": {"kernel": "Jacobi-PCG iterations of the demag solve (spmv_sell_kernel<DOT> + pcg_update_kernel + pcg_direction_kernel) + "
+                               "demag_rhs / element-field / box-method kernels", "bound": "hbm", "achieved": round(gbs, 1), "peak": peak,
+                     "unit": "GB/s", "frac": round(gbs / peak, 4), "traffic": None, "peak_source": peak_src,
+                     "algorithmic_bytes_per_launch": int(step_bytes / K), "avg_launch_ms": round(ms_step, 5),
+                     "note": "bytes per step by SURVEY 8d's figures (12 nnz + 108 n per iteration) + one residual product and the field kernels"},
+        "clocks": clocks,
+    }
+    if not args.no_cpu_baseline:
+        cs = CpuDemag(args.cpu_n, args.demag_tol)
+        cs.step()
+        t1 = time.time()
+        reps = 0
+        while reps < 2 or (time.time() - t1 < args.cpu_budget and reps < 50):
+            cs.step()
+            reps += 1
+        per = (time.time() - t1) / reps
+        line["cpu_baseline"] = {"value": round(cs.m.nt / per / 1e6, 4), "unit": UNIT, "cores": 1, "host_cores": os.cpu_count(), "kind": cs.kind,
+                                "sample": f"Kuhn cube N={args.cpu_n} ({cs.m.nt} tets), {reps} field evaluations (C port of LL::magnetostaticField, "
+                                          f"Eigen's Jacobi-CG from 0 to {args.demag_tol:g}, {cs.iters // (reps + 1)} iterations each)",
+                                "s_per_step": round(per, 4)}
+        line["parity"] = demag_parity(args, ctx.local)
+    print(json.dumps(line), flush=True)
+
+
+def run_reference_demag(args):
+    if env_int("RANK", 0) != 0:
+        return
+    cs = CpuDemag(args.cpu_n, args.demag_tol)
+    W, K = max(1, args.warmup), args.steps
+    for _ in range(W):
+        cs.step()
+    t1 = time.time()
+    for _ in range(K):
+        cs.step()
+    per = (time.time() - t1) / K
+    v = round(cs.m.nt / per / 1e6, 4)
+    print(json.dumps({"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": K, "warmup": W,
+                      "ms_per_step": round(per * 1e3, 3), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+                      "data": "synthetic",
+                      "config": {"workload": f"SURVEY 8 f-1 bounded sample: demagnetising field, Kuhn cube N={args.cpu_n}, Jacobi-PCG from 0 to {args.demag_tol:g}"},
+                      "cpu_baseline": {"value": v, "unit": UNIT, "cores": 1, "host_cores": os.cpu_count(), "kind": cs.kind,
+                                       "sample": f"Kuhn cube N={args.cpu_n} ({cs.m.nt} tets), {K} field evaluations"},
+                      "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}), flush=True)
+
+
 def scipy_spline(x, y):
     """FITPACK curfit(k=3, s=0) through scipy (the Fortran Dierckx.jl wraps): (t, c) of Spline1D(x, y)."""
     from scipy.interpolate import splrep
@@ -1118,8 +1315,10 @@ def main():
     ap.add_argument("--tune", default="", help="experiments: comma-separated what=value pairs for fk_tune (e.g. 6=0)")
     ap.add_argument("--presolve", type=int, default=1, help="0: skip the untimed linear presolve (profiling runs)")
     ap.add_argument("--full-solve", type=int, default=1, help="also record one complete nonlinear solve (untimed)")
-    ap.add_argument("--workload", default="picard", choices=["picard", "heat"],
-                    help="picard = configs[1] (the headline); heat = configs[2], Heat/heat3D.jl time stepping (use --n 150)")
+    ap.add_argument("--workload", default="picard", choices=["picard", "heat", "demag"],
+                    help="picard = configs[1] (the headline); heat = configs[2], Heat/heat3D.jl time stepping (use --n 150); "
+                         "demag = SURVEY 8 f-1, the repeated demagnetising-field solve of the LL loop (one GPU)")
+    ap.add_argument("--demag-tol", type=float, default=1e-10)
     ap.add_argument("--heat-tol", type=float, default=1e-10)
     ap.add_argument("--heat-parity-n", type=int, default=24)
     ap.add_argument("--single-process", action="store_true",
@@ -1130,6 +1329,8 @@ def main():
         return run_single_process(args)
     if args.workload == "heat":
         run_reference_heat(args) if args.impl == "reference" else run_heat(args)
+    elif args.workload == "demag":
+        run_reference_demag(args) if args.impl == "reference" else run_demag(args)
     elif args.impl == "reference":
         run_reference(args)
     else:
