@@ -205,6 +205,27 @@ class Ctx:
         torch.cuda.set_device(self.local)
         self.dev = torch.device("cuda", self.local)
         self.dist = None
+        # N > 1: run this rank (and first-touch its pinned host buffers) on the cores next to its GPU -- eight ranks pushing
+        # their host copies through one socket is what the e2e leg lost most to (FK_BENCH_AFFINITY=0 leaves the affinity alone)
+        self.host_affinity = None
+        if self.world > 1 and os.environ.get("FK_BENCH_AFFINITY", "1") != "0":
+            try:
+                import pynvml
+
+                pynvml.nvmlInit()
+                vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+                idx = int(vis.split(",")[self.local]) if vis and all(v.strip().isdigit() for v in vis.split(",")) else self.local
+                mask = pynvml.nvmlDeviceGetCpuAffinity(pynvml.nvmlDeviceGetHandleByIndex(idx), ((os.cpu_count() or 64) + 63) // 64)
+                cpus = {64 * w + b for w, m in enumerate(mask) for b in range(64) if (int(m) >> b) & 1}
+                allowed = os.sched_getaffinity(0)
+                near = cpus & allowed
+                if near and near != allowed:
+                    os.sched_setaffinity(0, near)
+                    self.host_affinity = f"{len(near)} of {len(allowed)} cores (those next to GPU {idx})"
+                else:
+                    self.host_affinity = f"unchanged ({len(allowed)} cores allowed, {len(near)} of them next to GPU {idx})"
+            except Exception as e:  # noqa: BLE001 -- affinity is an optimisation of the harness, never a requirement
+                self.host_affinity = f"unchanged ({type(e).__name__})"
         if self.world > 1:
             import torch.distributed as dist
 
@@ -214,7 +235,8 @@ class Ctx:
         # torch.distributed.run pins OMP_NUM_THREADS = 1: give every rank its share of the host cores for the symbolic phase
         from femeko_jl_b200 import lib as L
 
-        self.host_threads = L.load().fk_set_host_threads(max(1, (os.cpu_count() or 1) // max(1, self.world)))
+        share = max(1, (os.cpu_count() or 1) // max(1, self.world))
+        self.host_threads = L.load().fk_set_host_threads(max(1, min(share, len(os.sched_getaffinity(0)))))
 
     def barrier(self):
         import torch
@@ -562,7 +584,8 @@ def run_ours(args):
                        "l2": "inputs larger than L2 (CSR values+indices %.0f MB per GPU vs 126 MB L2)" % (12 * nnz / 1e6),
                        "parallelism": "single GPU" if world == 1 else
                        f"node-partitioned slabs x{world}, " + ("halo rows + all-reduce over NVLink peer memory inside the PCG kernels"
-                                                                if comm_mode == 2 else "NCCL send/recv halo + ncclAllReduce")},
+                                                                if comm_mode == 2 else "NCCL send/recv halo + ncclAllReduce"),
+                       "host_affinity": ctx.host_affinity},
             "components": {"picard_assembly_ms": round(asm_ms, 4), "picard_assembly_mtets_per_s": round(nt / asm_ms / 1e3, 1),
                            "pcg_ms": round(pcg_ms, 4), "pcg_iters_per_s": round(Piters / (pcg_ms * 1e-3), 1),
                            "setup_s_untimed": round(P["setup_s"], 2), "linear_presolve_iters": P["it0"]},

@@ -2477,7 +2477,6 @@ int fk_demag_setup(fk_handle h, int slot, const int* inside_elements, int n_insi
   return guard([&]() {
     need(h && (inside_elements || n_inside == 0), "fk: NULL argument");
     need(n_inside >= 0, "fk_demag_setup: negative element count");
-    need(h->comm == nullptr, "fk_demag_setup: partitioned handles are not supported");
     DeviceGuard dg(h->device);
     cudaStream_t s = h->stream;
     const int nv = h->nv, nt = h->nt;
@@ -2530,6 +2529,8 @@ static void demag_field_dev(fk_handle h, int slot, const double* M_dev, const fk
   h->launches += ni ? 2 : 1;
   // u = CG.solve(RHS), LL.cpp:315 (warm_start: from the potential of the previous call, kept in the handle)
   pcg_dev(h, slot, h->bvec.ptr, h->u.ptr, opts, iters_out, relres_out);
+  // partitions: the element field of a ghost element reads the potential on halo nodes (every rank is in this call: fk_pcg's rule)
+  if (h->comm) comm_halo_exchange(h, s, h->u.ptr);
   // element field + box method, LL.cpp:317-346
   if (ni) demag_elem_field_kernel<<<cdiv(ni, 256), 256, 0, s>>>(h->p4.ptr, h->t4.ptr, h->VE.ptr, h->dm_inside.ptr, ni, h->u.ptr, h->dm_w.ptr);
   demag_node_gather_kernel<2><<<cdiv(nv, 256), 256, 0, s>>>(h->dm_n2i_ptr.ptr, h->dm_n2i.ptr, nv, h->dm_w.ptr, nullptr, h->dm_vol.ptr,

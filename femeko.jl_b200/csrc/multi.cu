@@ -427,6 +427,51 @@ int fk_multi_picard_step(fk_multi m, int slot, const double* u, int compat_bug, 
     if (div_out) *div_out = div[0];   // all-reduced over the parts by the sweep itself
   });
 }
+// Demagnetising field of the LL loop (fk_demag_setup / fk_demag_field) on every part: the magnetic elements and the nodal
+// magnetisation in the caller's global numbering; a part works on the magnetic elements it holds (ghost copies included, in
+// ascending global order = the reference's list order when InsideElements is ascending), every owned node gathers all of its
+// incident magnetic elements locally, and the potential's halo rows are refreshed before the element field is taken.
+int fk_multi_demag_setup(fk_multi m, int slot, const int* inside_elements, int n_inside, double* volumes_out) {
+  return mguard([&]() {
+    if (!m || (!inside_elements && n_inside > 0)) throw std::runtime_error("fk: NULL argument");
+    std::vector<char> in((size_t)m->nt, 0);
+    for (int i = 0; i < n_inside; i++) {
+      if (inside_elements[i] < 0 || inside_elements[i] >= m->nt) throw std::runtime_error("fk_multi_demag_setup: element id out of range");
+      if (i > 0 && inside_elements[i] <= inside_elements[i - 1])
+        throw std::runtime_error("fk_multi_demag_setup: the element list must be ascending (the parts keep the reference's summation order that way)");
+      in[inside_elements[i]] = 1;
+    }
+    parallel_ranks(m->ngpu, [&](int r) {
+      const LocalPart& L = m->part[r];
+      std::vector<int> loc;
+      for (int q = 0; q < L.nt; q++)
+        if (in[L.elem_l2g[q]]) loc.push_back(q);
+      std::vector<double> vol((size_t)L.nv, 0.0);
+      ck(fk_demag_setup(m->h[r], slot, loc.data(), (int)loc.size(), vol.data()));
+      if (volumes_out) node_global(m, r, vol.data(), volumes_out);
+    });
+  });
+}
+int fk_multi_demag_field(fk_multi m, int slot, const double* M, const fk_pcg_opts* opts, int nan_outside, double* Hd_out, double* u_out,
+                         int* iters_out, double* relres_out) {
+  return mguard([&]() {
+    if (!m || !M || !Hd_out) throw std::runtime_error("fk: NULL argument");
+    std::vector<int> it((size_t)m->ngpu, 0);
+    std::vector<double> rr((size_t)m->ngpu, 0.0);
+    parallel_ranks(m->ngpu, [&](int r) {
+      const LocalPart& L = m->part[r];
+      std::vector<double> Ml(3 * (size_t)L.nv), Hl(3 * (size_t)L.nv), ul(u_out ? (size_t)L.nv : 0);
+      for (int i = 0; i < L.nv; i++)
+        for (int c = 0; c < 3; c++) Ml[3 * (size_t)i + c] = M[3 * (size_t)L.l2g[i] + c];
+      ck(fk_demag_field(m->h[r], slot, Ml.data(), opts, nan_outside, Hl.data(), u_out ? ul.data() : nullptr, &it[r], &rr[r]));
+      for (int i = 0; i < L.n_owned; i++)
+        for (int c = 0; c < 3; c++) Hd_out[3 * (size_t)L.l2g[i] + c] = Hl[3 * (size_t)i + c];
+      if (u_out) node_global(m, r, ul.data(), u_out);
+    });
+    if (iters_out) *iters_out = it[0];
+    if (relres_out) *relres_out = rr[0];
+  });
+}
 int fk_multi_spmv(fk_multi m, int slot, const double* x, double* y) {
   return mguard([&]() {
     if (!m || !x || !y) throw std::runtime_error("fk: NULL argument");

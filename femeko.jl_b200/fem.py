@@ -512,7 +512,6 @@ class FemekoMulti:
         self.lib = L.load()
         self.mesh = mesh
         o = L.fk_create_opts()
-        nedelec = bool(opts.pop("nedelec", False))
         for k, v in opts.items():
             setattr(o, k, int(v))
         p = np.asfortranarray(L.f64(mesh.p))
@@ -608,6 +607,27 @@ class FemekoMulti:
         div = C.c_double()
         L.check(self.lib.fk_multi_picard_step(self.h, slot, L.dptr(u), int(compat_bug), C.byref(div)))
         return div.value
+
+
+    def demag_setup(self, inside_elements, slot=0):
+        """fk_multi_demag_setup: inside_elements = GLOBAL element ids (ascending); returns the box-method node volumes."""
+        ids = np.ascontiguousarray(inside_elements, dtype=np.int32)
+        vol = np.zeros(self.nv)
+        L.check(self.lib.fk_multi_demag_setup(self.h, slot, L.iptr(ids), int(ids.size), L.dptr(vol)))
+        self._demag_slot = slot
+        return vol
+
+    def demag_field(self, M, nan_outside=True, want_u=False, **kw):
+        """One LL::magnetostaticField() over all parts: M, Hd 3 x nv in the global numbering; returns (Hd, iterations[, u])."""
+        M = np.asfortranarray(M, dtype=np.float64)
+        assert M.shape == (3, self.nv)
+        Hd = np.zeros((3, self.nv), order="F")
+        u = np.zeros(self.nv) if want_u else None
+        o = Femeko.pcg_opts(**kw)
+        it, rr = C.c_int(), C.c_double()
+        L.check(self.lib.fk_multi_demag_field(self.h, self._demag_slot, L.dptr(M), C.byref(o), int(nan_outside), L.dptr(Hd), L.dptr(u),
+                                              C.byref(it), C.byref(rr)))
+        return (Hd, it.value, u) if want_u else (Hd, it.value)
 
 
 class SparseCSR:

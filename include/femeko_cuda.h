@@ -332,7 +332,11 @@ int fk_heat_step_dev(fk_handle h, int slot_mass, int slot_lhs, double* T_dev, co
  *   call's potential), H_k = -sum u grad lambda (:317-326), box method to the nodes (:328-346).
  *   M, Hd are 3 x nv column-major.  Nodes outside the magnetic region have zero node volume: the
  *   reference divides 0/0 there (NaN); nan_outside != 0 reproduces that, 0 writes 0.
- *   u_out (nv) may be NULL.  Single-GPU handles only.                                            */
+ *   u_out (nv) may be NULL.
+ *   Partitioned handles (fk_set_halo; every rank makes the same calls): inside_elements = the magnetic elements the part
+ *   holds, ghost copies included, in ascending global order; M carries the halo rows too (the load vector of a ghost
+ *   element reads them); the potential's halo rows are exchanged before the element field is taken; volumes, Hd and u are
+ *   valid on the owned rows.  fk_multi_demag_* does all of that from global arrays.                                      */
 int fk_demag_setup(fk_handle h, int slot, const int* inside_elements, int n_inside, double* volumes_out);
 int fk_demag_field(fk_handle h, int slot, const double* M, const fk_pcg_opts* opts, int nan_outside,
                    double* Hd_out, double* u_out, int* iters_out, double* relres_out);
@@ -405,6 +409,11 @@ int fk_multi_spmv(fk_multi m, int slot, const double* x /* nv */, double* y /* n
 int fk_multi_pcg(fk_multi m, int slot, const double* b /* nv */, double* x /* nv in/out */, const fk_pcg_opts* opts, int* iters_out,
                  double* relres_out);
 int fk_multi_picard_step(fk_multi m, int slot, const double* u /* nv */, int compat_bug, double* div_out);
+/* fk_demag_setup / fk_demag_field on every part (LL.cpp:4-66,287-348): inside_elements = GLOBAL element ids, ascending; M, Hd, u and
+ * the volumes in the caller's global node numbering.                                                                           */
+int fk_multi_demag_setup(fk_multi m, int slot, const int* inside_elements, int n_inside, double* volumes_out /* nv or NULL */);
+int fk_multi_demag_field(fk_multi m, int slot, const double* M /* 3 x nv */, const fk_pcg_opts* opts, int nan_outside,
+                         double* Hd_out /* 3 x nv */, double* u_out /* nv or NULL */, int* iters_out, double* relres_out);
 
 /* ---- allocation-free residual norm -----------------------------------------------------------------------------------
  * NO COUNTERPART IN THE REFERENCE: added for callers that cannot call cudaMalloc

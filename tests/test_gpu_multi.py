@@ -106,3 +106,49 @@ def test_single_process_multi_gpu_matches_single_gpu(mesh):
     assert np.array_equal(hm.get_mu(), mus) and np.array_equal(Hn, Hns) and np.array_equal(Hf, Hfs)
     assert rl2(y, ys) < 1e-14
     hm.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mesh", ["kuhn", "delaunay"])
+def test_single_process_multi_gpu_demag_field(mesh):
+    """fk_multi_demag_* (the LL loop's repeated solve, LL.cpp:287-348, on partitioned handles): node volumes bit for bit,
+    demagnetising field and potential against a single-GPU handle and against the oracle on the same mesh."""
+    import numpy as np
+
+    import femeko_jl_b200 as fk
+    from oracle import oracle as orc
+
+    n = _ngpu()
+    if n < 2:
+        pytest.skip("needs at least 2 GPUs")
+    ngpu = 2 if n < 4 else 4
+    m = fk.kuhn_cube(14, inside_edge=0.5) if mesh == "kuhn" else fk.delaunay_ball(3000, seed=22)
+    ins = np.sort(m.InsideElements).astype(np.int32)
+    insn = np.unique(m.t[:, ins])
+    rng = np.random.default_rng(4)
+    M = np.zeros((3, m.nv), order="F")
+    M[:, insn] = rng.normal(size=(3, len(insn)))
+
+    hs = fk.Femeko(m, device=0)
+    vol_s = hs.demag_setup(ins, slot=0)
+    Hs, its, us = hs.demag_field(M, want_u=True, tol=1e-12)
+    hs.close()
+
+    hm = fk.FemekoMulti(m, ngpu)
+    vol = hm.demag_setup(ins, slot=0)
+    assert np.array_equal(vol, vol_s) and np.array_equal(vol, orc.node_volumes(m, ins))
+    Hd, it, u = hm.demag_field(M, want_u=True, tol=1e-12)
+    Hd2, it2 = hm.demag_field(M, tol=1e-12)
+    assert np.array_equal(Hd, Hd2, equal_nan=True) and it == it2        # run to run
+    fin = np.isfinite(Hs)
+    assert np.array_equal(fin, np.isfinite(Hd)) and abs(it - its) <= 2
+    assert np.linalg.norm(Hd[fin] - Hs[fin]) < 1e-8 * np.linalg.norm(Hs[fin])
+    assert np.linalg.norm((u - u.mean()) - (us - us.mean())) < 1e-8 * np.linalg.norm(us - us.mean())
+    Ho = orc.demag_box(m, ins, u, vol)                                   # the box method of the oracle on the multi-GPU potential
+    assert np.linalg.norm(Hd[fin] - Ho[fin]) < 1e-12 * np.linalg.norm(Ho[fin])
+    Hz, _ = hm.demag_field(M, nan_outside=False, tol=1e-12)
+    assert np.all(Hz[~fin] == 0.0)
+    # warm start from the converged potential
+    _, itw = hm.demag_field(M, tol=1e-10, warm_start=True)
+    assert itw <= 2
+    hm.close()
