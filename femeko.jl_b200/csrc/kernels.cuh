@@ -474,7 +474,7 @@ static __global__ void __launch_bounds__(256) material_update_kernel(const doubl
                                                               const double* __restrict__ Hn_old, double* __restrict__ mu,
                                                               double* __restrict__ dmu, double* __restrict__ part_max,
                                                               int* __restrict__ errflag, const double* __restrict__ VE = nullptr,
-                                                              double* __restrict__ s0 = nullptr, double* __restrict__ Hn_w = nullptr) {
+                                                              double* __restrict__ s0 = nullptr) {
   __shared__ double red[33];
   double dmax = 0.0;
   int err = 0;
@@ -500,7 +500,6 @@ static __global__ void __launch_bounds__(256) material_update_kernel(const doubl
     mu[k] = f;
     if (dmu) dmu[k] = df;
     if (s0) s0[k] = __dmul_rn(VE ? VE[k] : G.vol, f);   // rescale path: the element scale follows its mu (rescale.cuh)
-    if (Hn_w) Hn_w[k] = Hn;   // side-by-side sweep: this kernel owns |H| of its elements (the field-recovery kernel skips them)
   }
   if (err) atomicOr(errflag, err);
   dmax = block_max(dmax, red);

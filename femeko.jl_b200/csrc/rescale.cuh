@@ -67,10 +67,7 @@ static __global__ void __launch_bounds__(kElemThreads) picard_element_kernel(con
                                                                              const double* __restrict__ u, const double* __restrict__ mu,
                                                                              const double* __restrict__ VE, int nt, int compat,
                                                                              double* __restrict__ Hn, double* __restrict__ Hfield,
-                                                                             double* __restrict__ s0,
-                                                                             const unsigned char* __restrict__ skip_hn = nullptr) {
-  // skip_hn (side-by-side sweep): |H| of the elements with a B-H curve is written by material_update_kernel, which also
-  // reads their previous |H| -- leaving those entries alone lets the two kernels run concurrently
+                                                                             double* __restrict__ s0) {
   __shared__ double hs[kElemThreads / 32][96];
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   const long long stride = (long long)gridDim.x * kElemThreads;
@@ -92,7 +89,7 @@ static __global__ void __launch_bounds__(kElemThreads) picard_element_kernel(con
       hy = -(u0 * G.g[0][1]) - u1 * G.g[1][1] - u2 * G.g[2][1] - u3 * G.g[3][1];
       hz = -(u0 * G.g[0][2]) - u1 * G.g[1][2] - u2 * G.g[2][2] - u3 * G.g[3][2];
       if (compat) { hy += hz; hz = 0.0; }  // NewtonRaphson.jl:187-189: d-term lands in row 2
-      if (!(skip_hn && __ldg(skip_hn + k) != 0)) __stcs(Hn + k, norm3(hx, hy, hz));
+      __stcs(Hn + k, norm3(hx, hy, hz));
       if (S0) s0[k] = __dmul_rn(VE ? V : G.vol, f);
     }
     if (Hfield) {
