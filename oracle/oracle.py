@@ -10,6 +10,9 @@ Two libraries:
 Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs import
 this module.  Parity status: pinned against outputs of the compiled reference (no golden vectors
 exist upstream); Julia-only orderings and Dierckx are pinned via scipy's FITPACK.
+The numpy restatements further down (2-D P1, P2 stiffness / mass / convection, Nedelec elements and its Newton loop) follow code
+that exists in Julia only (no C++ twin, no Julia here): PARITY UNPINNED against Julia itself for those; tests/test_oracle.py pins
+them by the properties the elements must satisfy.
 """
 from __future__ import annotations
 
