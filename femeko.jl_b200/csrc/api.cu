@@ -814,6 +814,22 @@ int fk_set_host_threads(int n) {
 #endif
 }
 int fk_version(void) { return 100; }
+// Page-lock a caller's host array (cudaHostRegister) so that the host-pointer entry points copy at pinned speed: a Julia Array
+// is pageable, and a caller without CUDA.jl has no other way to pin it.  The array must be unregistered before it is freed.
+int fk_host_register(void* ptr, long long bytes) {
+  return guard([&]() {
+    need(ptr != nullptr && bytes > 0, "fk_host_register: NULL pointer or empty range");
+    FK_CUDA(cudaHostRegister(ptr, (size_t)bytes, cudaHostRegisterPortable));
+    return 0;
+  });
+}
+int fk_host_unregister(void* ptr) {
+  return guard([&]() {
+    need(ptr != nullptr, "fk_host_unregister: NULL pointer");
+    FK_CUDA(cudaHostUnregister(ptr));
+    return 0;
+  });
+}
 
 // fk_create and fk_create_edge.  t = the connectivity of the DEGREES OF FREEDOM (npe x nt, ids < nv); t_vertices = the four
 // vertices of every element when t does not start with them (edge elements), n_points = points in p

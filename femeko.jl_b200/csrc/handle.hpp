@@ -13,12 +13,14 @@ namespace fk {
 
 void set_error(const std::string& s);
 
-#define FK_CUDA(call)                                                                                  \
-  do {                                                                                                 \
-    cudaError_t e_ = (call);                                                                           \
-    if (e_ != cudaSuccess)                                                                             \
-      throw std::runtime_error(std::string("CUDA error: ") + cudaGetErrorString(e_) + " at " + __FILE__ + \
-                               ":" + std::to_string(__LINE__) + " (" #call ")");                       \
+#define FK_CUDA(call)                                                                                    \
+  do {                                                                                                   \
+    cudaError_t e_ = (call);                                                                             \
+    if (e_ != cudaSuccess) {                                                                             \
+      (void)cudaGetLastError(); /* clear the (non-sticky) error: a later check must not report it again */ \
+      throw std::runtime_error(std::string("CUDA error: ") + cudaGetErrorString(e_) + " at " + __FILE__ +  \
+                               ":" + std::to_string(__LINE__) + " (" #call ")");                         \
+    }                                                                                                    \
   } while (0)
 
 template <class T>

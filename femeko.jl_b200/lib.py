@@ -99,6 +99,8 @@ _SIGS = {
     "fk_multi_picard_step": (C.c_int, [_H, C.c_int, c_double_p, C.c_int, c_double_p]),
     "fk_multi_demag_setup": (C.c_int, [_H, C.c_int, c_int_p, C.c_int, c_double_p]),
     "fk_multi_demag_field": (C.c_int, [_H, C.c_int, c_double_p, C.POINTER(fk_pcg_opts), C.c_int, c_double_p, c_double_p, c_int_p, c_double_p]),
+    "fk_host_register": (C.c_int, [C.c_void_p, C.c_longlong]),
+    "fk_host_unregister": (C.c_int, [C.c_void_p]),
     "fk_assemble_convection_p2": (C.c_int, [_H, C.c_int, c_double_p, c_double_p, C.c_int, c_double_p]),
     "fk_create_edge": (C.c_int, [c_double_p, C.c_int, c_int_p, c_int_p, C.c_int, C.c_int, c_double_p, C.c_void_p, C.POINTER(_H)]),
     "fk_nedelec_local_stiffness": (C.c_int, [_H, c_double_p]),

@@ -77,6 +77,12 @@ const char* fk_last_error(void);
  * partition take minutes; a driver with one process per GPU gives each process its share of the cores here.        */
 int fk_set_host_threads(int n);
 int fk_version(void);
+/* Host buffers: every host-pointer entry point accepts pageable memory (a Julia Array); its copies then run at about half the
+ * speed of pinned memory (bench.py: e2e.pageable).  fk_host_register page-locks a caller's array in place (cudaHostRegister,
+ * portable across devices) so that later calls with pointers inside it copy at pinned speed; unregister before the array is
+ * freed (in Julia: keep it alive with GC.@preserve / a global until fk_host_unregister).  No counterpart in the reference. */
+int fk_host_register(void* ptr, long long bytes);
+int fk_host_unregister(void* ptr);
 
 /* ---- lifecycle -------------------------------------------------------------------------------
  * fk_create copies p (3 x nv) and t (4 x nt, 0-based) to the GPU, runs the symbolic phase

@@ -128,3 +128,33 @@ def test_error_paths_report_and_do_not_crash():
     v = h.assemble_stiffness(None, slot=0)
     assert np.all(np.isfinite(v))
     h.close()
+
+
+def test_host_register_keeps_results_and_reports_misuse():
+    """fk_host_register / fk_host_unregister: page-locking a caller's (pageable) arrays in place changes copy speed only."""
+    import ctypes as C
+
+    m = fk.kuhn_cube(8, inside_edge=0.5)
+    h = fk.Femeko(m)
+    h.assemble_stiffness(None, slot=0, want_vals=False)
+    rng = np.random.default_rng(1)
+    b = rng.normal(size=m.nv)
+    b -= b.mean()
+    x0, it0, _ = h.pcg(b, slot=0, tol=1e-10)
+    lib = L.load()
+    bb, xx = b.copy(), np.zeros(m.nv)
+    for a in (bb, xx):
+        L.check(lib.fk_host_register(C.c_void_p(a.ctypes.data), a.nbytes))
+    o = h.pcg_opts(tol=1e-10)
+    it, rr = C.c_int(), C.c_double()
+    L.check(lib.fk_pcg(h.h, 0, L.dptr(bb), L.dptr(xx), C.byref(o), C.byref(it), C.byref(rr)))
+    assert it.value == it0 and np.array_equal(xx, x0)
+    for a in (bb, xx):
+        L.check(lib.fk_host_unregister(C.c_void_p(a.ctypes.data)))
+    with pytest.raises(L.FemekoError, match="CUDA error"):
+        L.check(lib.fk_host_unregister(C.c_void_p(bb.ctypes.data)))      # not registered any more
+    with pytest.raises(L.FemekoError, match="NULL"):
+        L.check(lib.fk_host_register(None, 8))
+    x1, it1, _ = h.pcg(b, slot=0, tol=1e-10)                             # the handle is still fine after the reported errors
+    assert it1 == it0 and np.array_equal(x1, x0)
+    h.close()
