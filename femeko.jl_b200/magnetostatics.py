@@ -119,14 +119,14 @@ class NedelecResult:
 
 
 def nedelec3D(mesh: MESH, Bext, spl_nu: Spline1D, spl_dnu: Spline1D, tol: float = 1e-4, maxAtt: int = 30, fk: Femeko | None = None,
-              cg_tol: float = 1e-12, cg_maxiter: int | None = None, verbose: bool = False) -> NedelecResult:
+              cg_tol: float = 1.4901161193847656e-08, cg_maxiter: int | None = None, verbose: bool = False) -> NedelecResult:
     """Newton-Raphson on the magnetic vector potential with Nedelec elements (Magnetostatics/nedelec3D.jl:104-250): load
     vector VE Bext . curlN (:108-146); each pass A = curl-curl matrix scaled by nu (:163-178), At = nedelecTangentialStiffness
     from the second pass on (:181-185), du = cg(A + At, RHS - A u) (:188), lineSearch (:191), B = curl u and |B| (:194-236),
     nu = spl(B), dnu = spl_dnu(B) on the inside elements (:239-240), div = max |B - Bold| (:248).  The matrices, the solve, the
     line search and the field recovery run on the GPU; the two spline evaluations over the inside elements are fk_spline_apply.
     The curl-curl system is singular (gradients); like the reference's cg call the solve is a plain Jacobi-CG on the
-    consistent system -- B does not depend on the gauge."""
+    consistent system at IterativeSolvers' default reltol = sqrt(eps) -- B does not depend on the gauge."""
     fk = fk or Femeko(mesh, nedelec=True)
     fk.set_spline(0, spl_nu)
     fk.set_spline(1, spl_dnu)

@@ -817,9 +817,11 @@ def nedelec_recover_B(mesh, u):
     return Bf, np.sqrt(Bf[0] ** 2 + Bf[1] ** 2 + Bf[2] ** 2)
 
 
-def nedelec_newton_loop(mesh, Bext, tck_nu, tck_dnu, tol=1e-4, max_att=30, cg_tol=1e-12, bc="nearest"):
+def nedelec_newton_loop(mesh, Bext, tck_nu, tck_dnu, tol=1e-4, max_att=30, cg_tol=1.4901161193847656e-08, bc="nearest"):
     """Newton-Raphson loop on the magnetic vector potential (nedelec3D.jl:148-250).  The reference solves with
-    IterativeSolvers.cg on the singular curl-curl system; here scipy's CG at cg_tol (B = curl of u is gauge independent)."""
+    IterativeSolvers.cg on the singular curl-curl system at its default reltol = sqrt(eps); here scipy's CG at cg_tol (B = curl of
+    u is gauge independent).  A much tighter cg_tol than the rounding noise of RHS - A u allows (its null-space component) makes
+    CG run to its iteration limit and drift along the gradients near convergence: keep cg_tol >= ~1e-12 / (last div)."""
     import scipy.sparse.linalg as spl
 
     edges, _ = edge_numbering(mesh.t)

@@ -45,7 +45,7 @@ def test_noalloc_residual_matches_existing_entry_point_twice():
         torch.cuda.synchronize()
         mem0 = torch.cuda.mem_get_info()[0]
         nr_new = fk.residual_norm_noalloc(b_d.data_ptr(), Ax_d.data_ptr(), n, r_new.data_ptr(), norm_d.data_ptr(), stream=stream)
-        assert torch.cuda.mem_get_info()[0] == mem0, "the call changed the amount of free device memory"
+        assert torch.cuda.mem_get_info()[0] >= mem0, "the call took device memory"
         assert torch.equal(r_new, r_ref)                  # same subtraction, element by element: bit for bit
         assert abs(nr_new - nr_ref) <= 1e-13 * nr_ref     # different (both deterministic) summation orders
         assert float(norm_d.item()) == nr_new
