@@ -5,6 +5,9 @@
 #include "symbolic.hpp"
 
 #include <algorithm>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
 #include <climits>
 #include <cmath>
 #include <cstring>
@@ -17,6 +20,20 @@
 #endif
 
 namespace fk {
+namespace {
+// FK_DEBUG: wall-clock split of the symbolic phase on stderr
+struct PhaseTimer {
+  bool on = std::getenv("FK_DEBUG") != nullptr;
+  std::chrono::steady_clock::time_point t0 = std::chrono::steady_clock::now();
+  void lap(const char* what) {
+    if (!on) return;
+    const auto t1 = std::chrono::steady_clock::now();
+    std::fprintf(stderr, "fk symbolic: %-28s %7.3f s\n", what, std::chrono::duration<double>(t1 - t0).count());
+    t0 = t1;
+  }
+};
+}  // namespace
+
 
 static inline uint64_t spread21(uint64_t v) {
   v &= 0x1fffffULL;
@@ -40,6 +57,7 @@ void build_symbolic(const double* p, const int* t, int nv, int nt, const Symboli
   S.nt = nt;
   S.n_rows = (o.n_owned < 0 || o.n_owned > nv) ? nv : o.n_owned;
   const int nr = S.n_rows;
+  PhaseTimer tm;
 
   // ---- node -> element incidences, ascending element order (counting sort) ------------------
   std::vector<int64_t> n2e_ptr((size_t)nv + 1, 0);
@@ -55,6 +73,7 @@ void build_symbolic(const double* p, const int* t, int nv, int nt, const Symboli
     for (int64_t q = 0; q < (int64_t)npe * nt; q++) n2e[(size_t)fill[t[q]]++] = (uint32_t)q;  // q = npe k + i
   }
 
+  tm.lap("node -> element incidences");
   // ---- row pattern: sorted unique nodes of all incident elements ----------------------------
   S.rowptr.assign((size_t)nv + 1, 0);
   std::vector<int> rowlen((size_t)nv, 0);
@@ -102,6 +121,7 @@ void build_symbolic(const double* p, const int* t, int nv, int nt, const Symboli
     }
   }
 
+  tm.lap("row pattern");
   // ---- element -> nnz map ---------------------------------------------------------------------
   S.e2nnz.resize((size_t)npe * npe * nt);
 #pragma omp parallel for schedule(static)
@@ -121,6 +141,7 @@ void build_symbolic(const double* p, const int* t, int nv, int nt, const Symboli
     }
   }
 
+  tm.lap("element -> nnz map");
   // ---- SELL-32-sigma layout (see symbolic.hpp): independent of the assembly tiles, shared by every element type ------
   auto build_sell = [&]() {
     const int C = 32;
@@ -249,6 +270,7 @@ void build_symbolic(const double* p, const int* t, int nv, int nt, const Symboli
     std::sort(order.begin(), order.end(), [&](int a, int b) { return key[a] != key[b] ? key[a] < key[b] : a < b; });
   }
 
+  tm.lap("Morton order");
   std::vector<int> tile_of_row((size_t)nv, -1);
   std::vector<int64_t> tile_row_ptr;  // -> order positions
   std::vector<int> tile_nelem;
@@ -294,6 +316,7 @@ void build_symbolic(const double* p, const int* t, int nv, int nt, const Symboli
       tile_row_ptr.push_back(nr);
     }
   }
+  tm.lap("tile packing");
   const int T = (int)tile_nelem.size();
   S.ntiles = T;
   S.tile_elem_ptr.assign((size_t)T + 1, 0);
@@ -401,8 +424,10 @@ void build_symbolic(const double* p, const int* t, int nv, int nt, const Symboli
     }
   }
   if (bad) throw std::runtime_error("fk: internal error building assembly tiles");
+  tm.lap("tile plans");
 
   build_sell();
+  tm.lap("SELL layout");
 
   // ---- packed device blobs (see symbolic.hpp) ---------------------------------------------------
   {
@@ -499,6 +524,7 @@ void build_symbolic(const double* p, const int* t, int nv, int nt, const Symboli
     }
   }
 
+  tm.lap("device blobs");
 }
 
 // ------------------------------------------------------------------------------------------------
