@@ -456,6 +456,7 @@ void build_symbolic(const double* p, const int* t, int nv, int nt, const Symboli
 #pragma omp parallel for schedule(static)
       for (int tl = 0; tl < T; tl++) std::copy(per[tl].begin(), per[tl].end(), tnodes.begin() + node_ptr[tl]);
     }
+    tm.lap("  blobs: tile node lists");
     S.e_pad = (S.max_tile_elems + 15) & ~15;
     if (10 * (int64_t)S.e_pad > 65535) throw std::runtime_error("fk: tile_max_elems too large for 16-bit staging indices");
     S.tile_hdr.assign((size_t)4 * T, 0);
@@ -476,6 +477,7 @@ void build_symbolic(const double* p, const int* t, int nv, int nt, const Symboli
       S.tile_hdr[4 * (size_t)tl + 3] = b;
     }
     S.tile_blob.assign((size_t)(off[T] / 4), 0u);
+    tm.lap("  blobs: allocate + zero");
 #pragma omp parallel for schedule(static)
     for (int tl = 0; tl < T; tl++) {
       const int ne = tile_nelem[tl], nn = (int)(S.tile_nnz_ptr[tl + 1] - S.tile_nnz_ptr[tl]),
@@ -524,7 +526,19 @@ void build_symbolic(const double* p, const int* t, int nv, int nt, const Symboli
     }
   }
 
-  tm.lap("device blobs");
+  tm.lap("  blobs: fill");
+  if (std::getenv("FK_DEBUG_CHECKSUM")) {   // checksums of what the device receives: a regression guard for changes of this file
+    auto fnv = [](const void* d, size_t n) {
+      uint64_t h = 1469598103934665603ULL;
+      const unsigned char* b = static_cast<const unsigned char*>(d);
+      for (size_t i = 0; i < n; i++) { h ^= b[i]; h *= 1099511628211ULL; }
+      return h;
+    };
+    std::fprintf(stderr, "fk symbolic: checksums blob %016llx hdr %016llx colz %016llx meta %016llx csr2sell %016llx e2nnz %016llx\n",
+                 (unsigned long long)fnv(S.tile_blob.data(), 4 * S.tile_blob.size()), (unsigned long long)fnv(S.tile_hdr.data(), 4 * S.tile_hdr.size()),
+                 (unsigned long long)fnv(S.sell_colz.data(), 2 * S.sell_colz.size()), (unsigned long long)fnv(S.slice_meta.data(), 4 * S.slice_meta.size()),
+                 (unsigned long long)fnv(S.csr2sell.data(), 4 * S.csr2sell.size()), (unsigned long long)fnv(S.e2nnz.data(), 4 * S.e2nnz.size()));
+  }
 }
 
 // ------------------------------------------------------------------------------------------------
